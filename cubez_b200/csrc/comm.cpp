@@ -1,0 +1,136 @@
+// cubez_b200/csrc/comm.cpp -- see comm.h.  Replaces reference src/cz_cpp/cz_comm.cpp:
+// Comm_S (CBrick 6-face halo, :23-38) -> ncclSend/ncclRecv of contiguous j-planes over NVLink;
+// Comm_SUM_1 (MPI_Allreduce, :74-140) -> ncclAllReduce of device-resident doubles.
+#include "comm.h"
+#include <nccl.h>
+#include <dlfcn.h>
+#include <cstring>
+
+namespace czb {
+
+int slab_decompose(const int gsz[3], int nranks, int rank, int sz[3], int head[3], int nID[6], int idx[6]) {
+  const int n = gsz[1] - 2;   // inner planes
+  if (nranks < 1 || rank < 0 || rank >= nranks || n < nranks) return -1;
+  const int base = n / nranks, rem = n % nranks;
+  const int cnt = base + (rank < rem ? 1 : 0);
+  const int first = 2 + rank * base + (rank < rem ? rank : rem);   // global j of first owned inner plane
+  const bool lo_edge = (rank == 0), hi_edge = (rank == nranks - 1);
+  sz[0] = gsz[0]; sz[2] = gsz[2];
+  sz[1] = cnt + (lo_edge ? 1 : 0) + (hi_edge ? 1 : 0);
+  head[0] = 1; head[2] = 1;
+  head[1] = lo_edge ? 1 : first;
+  for (int f = 0; f < 6; ++f) nID[f] = -1;
+  nID[2] = lo_edge ? -1 : rank - 1;   // J_MINUS  (cz_fparam.fi:10-16)
+  nID[3] = hi_edge ? -1 : rank + 1;   // J_PLUS
+  idx[0] = 2; idx[1] = sz[0] - 1;
+  idx[2] = lo_edge ? 2 : 1;
+  idx[3] = hi_edge ? sz[1] - 1 : sz[1];
+  idx[4] = 2; idx[5] = sz[2] - 1;
+  return 0;
+}
+
+namespace {
+
+struct NcclApi {
+  void* lib = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+NcclApi& api() {
+  static NcclApi A;
+  if (A.lib) return A;
+  const char* names[] = {getenv("CZB_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+  for (const char* nm : names) {
+    if (!nm) continue;
+    A.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+    if (A.lib) break;
+  }
+  if (!A.lib) { fprintf(stderr, "czb200: cannot load NCCL (libnccl.so.2): %s\n", dlerror()); abort(); }
+#define CZB_SYM(field, name)                                                     \
+  *(void**)(&A.field) = dlsym(A.lib, name);                                      \
+  if (!A.field) { fprintf(stderr, "czb200: NCCL symbol %s missing\n", name); abort(); }
+  CZB_SYM(GetUniqueId, "ncclGetUniqueId");
+  CZB_SYM(CommInitRank, "ncclCommInitRank");
+  CZB_SYM(CommDestroy, "ncclCommDestroy");
+  CZB_SYM(Send, "ncclSend");
+  CZB_SYM(Recv, "ncclRecv");
+  CZB_SYM(AllReduce, "ncclAllReduce");
+  CZB_SYM(GroupStart, "ncclGroupStart");
+  CZB_SYM(GroupEnd, "ncclGroupEnd");
+  CZB_SYM(GetErrorString, "ncclGetErrorString");
+#undef CZB_SYM
+  return A;
+}
+
+#define CZB_NCCL(call)                                                                         \
+  do {                                                                                         \
+    ncclResult_t r_ = (call);                                                                  \
+    if (r_ != ncclSuccess) {                                                                   \
+      fprintf(stderr, "czb200: NCCL error at %s:%d: %s\n", __FILE__, __LINE__, api().GetErrorString(r_)); \
+      abort();                                                                                 \
+    }                                                                                          \
+  } while (0)
+
+inline ncclDataType_t real_type() { return sizeof(REAL) == 8 ? ncclFloat64 : ncclFloat32; }
+
+}  // namespace
+
+int comm_unique_id(void* id128) {
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  CZB_NCCL(api().GetUniqueId(&id));
+  memcpy(id128, &id, 128);
+  return 0;
+}
+
+Comm* comm_create(int nranks, int rank, const void* id128, int lo, int hi) {
+  Comm* c = new Comm;
+  c->nranks = nranks; c->rank = rank; c->lo = lo; c->hi = hi;
+  if (nranks > 1) {
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    ncclComm_t comm;
+    CZB_NCCL(api().CommInitRank(&comm, nranks, id, rank));
+    c->nccl = (void*)comm;
+  }
+  return c;
+}
+
+void comm_destroy(Comm* c) {
+  if (!c) return;
+  if (c->nccl) api().CommDestroy((ncclComm_t)c->nccl);
+  delete c;
+}
+
+void comm_halo(Comm* c, REAL* f, const Geo& G, int w, cudaStream_t s) {
+  if (!c || c->nranks <= 1 || (c->lo < 0 && c->hi < 0)) return;
+  NcclApi& A = api();
+  ncclComm_t comm = (ncclComm_t)c->nccl;
+  const size_t cnt = (size_t)w * (size_t)G.plane;
+  const long long P = G.plane;
+  CZB_NCCL(A.GroupStart());
+  if (c->lo >= 0) {   // my planes 1..w -> lower neighbour's guard; its top planes -> my planes 1-w..0
+    CZB_NCCL(A.Send(f + (long long)G.g * P, cnt, real_type(), c->lo, comm, s));
+    CZB_NCCL(A.Recv(f + (long long)(G.g - w) * P, cnt, real_type(), c->lo, comm, s));
+  }
+  if (c->hi >= 0) {   // my planes jx-w+1..jx -> upper neighbour's guard; its planes 1..w -> my jx+1..jx+w
+    CZB_NCCL(A.Send(f + (long long)(G.jx - w + G.g) * P, cnt, real_type(), c->hi, comm, s));
+    CZB_NCCL(A.Recv(f + (long long)(G.jx + G.g) * P, cnt, real_type(), c->hi, comm, s));
+  }
+  CZB_NCCL(A.GroupEnd());
+}
+
+void comm_allreduce_sum(Comm* c, double* dev, int count, cudaStream_t s) {
+  if (!c || c->nranks <= 1) return;
+  CZB_NCCL(api().AllReduce(dev, dev, (size_t)count, ncclFloat64, ncclSum, (ncclComm_t)c->nccl, s));
+}
+
+}  // namespace czb

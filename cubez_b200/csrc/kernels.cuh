@@ -1,0 +1,77 @@
+// cubez_b200/csrc/kernels.cuh -- host-side launchers of the sm_100a kernels (kernels.cu,
+// pcr.cu, fused.cu).  All pointers are DEVICE pointers; everything is enqueued on `s`.
+// `st` may be null (per-call ABI); when non-null the kernels are no-ops once st->done is set.
+#pragma once
+#include "common.cuh"
+
+namespace czb {
+
+struct Launch {           // what every launcher needs
+  cudaStream_t s;
+  RedBuf rb;              // reduction scratch (sized for rb_blocks blocks)
+  size_t rb_blocks;
+  const LoopState* st;    // done-flag source (may be null)
+  LoopState* acc_st;      // where reduction totals go: acc_st->acc[slot]
+};
+
+void count_launch(int n = 1);
+
+// ---- stationary sweeps (cz_solver.f90) ------------------------------------------------
+// jacobi (cz_solver.f90:284-387): pnew = p + omg*((ss-b)/dd - p) on inner cells;
+// acc[slot] (+)= sum dp^2.
+void launch_jacobi(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b,
+                   const REAL* cf, REAL omg, int slot, bool add);
+// psor2sma_core (cz_solver.f90:404-493): one colour, in place. kp = ofst + color.
+void launch_rb_color(const Launch& L, const Geo& G, REAL* p, const REAL* b, const REAL* cf,
+                     REAL omg, int kp, int slot, bool add);
+// psor (cz_solver.f90:207-269): lexicographic SOR, exact order through hyperplane wavefronts
+void launch_psor_sweep(const Launch& L, const Geo& G, REAL* p, const REAL* b, const REAL* cf, REAL omg,
+                       int slot, bool add);
+// copy inner cells src -> dst (jacobi copy-back cz_solver.f90:369-375, pcr_j_esa :1659-1665)
+void launch_copy_inner(const Launch& L, const Geo& G, REAL* dst, const REAL* src);
+
+// ---- BLAS-1 / operator (cz_blas.f90) --------------------------------------------------
+void launch_calc_ax(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf,
+                    const REAL* dotwith, int slot);   // dotwith!=null: acc[slot] = (ap, dotwith)
+void launch_calc_rk(const Launch& L, const Geo& G, REAL* r, const REAL* p, const REAL* b,
+                    const REAL* cf);
+void launch_dot1(const Launch& L, const Geo& G, const REAL* p, int slot);
+void launch_dot2(const Launch& L, const Geo& G, const REAL* p, const REAL* q, int slot);
+// z = a*x + y ; a read from device scalar `a_dev` (double holding a REAL value) if non-null
+void launch_triad(const Launch& L, const Geo& G, REAL* z, const REAL* x, const REAL* y, REAL a,
+                  const double* a_dev);
+void launch_bicg1(const Launch& L, const Geo& G, REAL* p, const REAL* r, const REAL* q, REAL beta,
+                  REAL omg, const double* beta_dev, const double* omg_dev);
+void launch_bicg2(const Launch& L, const Geo& G, REAL* z, const REAL* x, const REAL* y, REAL a,
+                  REAL b, const double* a_dev, const double* b_dev);
+void launch_imask(const Launch& L, const Geo& G, REAL* x);
+void launch_copy_in(const Launch& L, const Geo& G, REAL* y, const REAL* x);
+
+// ---- boundary / utility (cz_solver.f90:22-191, cz_utility.f90) --------------------------
+void launch_bc_k(const Launch& L, const Geo& G, REAL* p, REAL dh, const REAL* org, const int* nID);
+void launch_exact(const Launch& L, const Geo& G, REAL* e, REAL dh, const REAL* org);
+// err_t: e <- p - e on inner cells; out[0] = max |p-e| as double bits, out[1] = order index of
+// the first maximum in (j,i,k) loop order.
+void launch_err(const Launch& L, const Geo& G, const REAL* p, REAL* e, unsigned long long* out2);
+
+// ---- line SOR with PCR (cz_solver.f90:497-662, 1261-1469, 1473-1676) --------------------
+struct PcrTables {          // device tables for one (n, pn, last-stage) combination
+  int n, pn, stages, last4;
+  REAL* tab;                // [stages][3][n]  ap, cp, e
+  REAL* fin;                // last-stage tables, see pcr.cu
+};
+void pcr_build_tables(cudaStream_t s, PcrTables& T, int n, int pn, bool last4);
+void pcr_free_tables(PcrTables& T);
+// mode: 0/1 = lines with mod(i+j+ofs,2)==mode ; 2 = all lines (line Jacobi, dst != x) ;
+//       3 = lines with i+j == diag (wavefront for the lexicographic variants)
+void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mode, int ofs, int diag,
+                      const REAL* x, REAL* dst, const REAL* msk, const REAL* rhs, REAL omg, int slot,
+                      bool add);
+
+// ---- loop control (tiny kernels) --------------------------------------------------------
+void launch_state_reset(const Launch& L, LoopState* st);
+// res = sqrt(acc[slot]*res_normal); hist[itr] = res; ++itr; done |= res < eps
+void launch_finish_iteration(const Launch& L, LoopState* st, int slot, double res_normal, double eps,
+                             double* hist, int hist_len);
+
+}  // namespace czb

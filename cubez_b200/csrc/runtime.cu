@@ -1,0 +1,127 @@
+// cubez_b200/csrc/runtime.cu -- runtime singleton + the czb_* utility entry points of
+// include/czb200.h (device selection, stream, allocation, counters).
+#include "runtime.h"
+#include "../../include/czb200.h"
+
+namespace czb {
+
+static Runtime g_rt;
+
+void Runtime::init(int dev) {
+  if (inited) return;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= 0) {
+    fprintf(stderr,
+            "czb200: no CUDA device available (%s). libczb200 is a GPU-only implementation of the CubeZ "
+            "kernel layer; there is no CPU fallback.\n",
+            e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    abort();
+  }
+  if (dev < 0) {
+    const char* env = getenv("CZB_DEVICE");
+    dev = env ? atoi(env) : -1;
+    if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) dev = 0; }
+  }
+  device = dev;
+  CZB_CHECK(cudaSetDevice(device));
+  CZB_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  own_stream = true;
+  rb_blocks = (size_t)1 << 17;
+  CZB_CHECK(cudaMalloc(&rb.partial, sizeof(double) * rb_blocks * CZB_MAX_ACC));
+  CZB_CHECK(cudaMalloc(&rb.ticket, sizeof(unsigned int)));
+  CZB_CHECK(cudaMemset(rb.ticket, 0, sizeof(unsigned int)));
+  CZB_CHECK(cudaMalloc(&d_scratch, sizeof(LoopState)));
+  CZB_CHECK(cudaMemset(d_scratch, 0, sizeof(LoopState)));
+  CZB_CHECK(cudaMallocHost(&h_state, sizeof(LoopState) * 4));
+  CZB_CHECK(cudaMalloc(&d_err, sizeof(unsigned long long) * 4));
+  CZB_CHECK(cudaDeviceSynchronize());
+  inited = true;
+}
+
+Runtime& rt() {
+  if (!g_rt.inited) g_rt.init(-1);
+  return g_rt;
+}
+
+double Runtime::read_acc(int slot) {
+  CZB_CHECK(cudaMemcpyAsync(h_state, d_scratch, sizeof(LoopState), cudaMemcpyDeviceToHost, stream));
+  CZB_CHECK(cudaStreamSynchronize(stream));
+  return h_state->acc[slot];
+}
+
+bool is_device_ptr(const void* p) {
+  cudaPointerAttributes at;
+  cudaError_t e = cudaPointerGetAttributes(&at, p);
+  if (e != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+}  // namespace czb
+
+using namespace czb;
+
+extern "C" {
+
+int czb_real_bytes(void) { return (int)sizeof(REAL); }
+const char* czb_version(void) { return "czb200 0.1 (" CZB_REAL_NAME ", sm_100a)"; }
+
+int czb_init(int device) {
+  if (g_rt.inited) {
+    if (device >= 0 && device != g_rt.device) {
+      fprintf(stderr, "czb200: already initialised on device %d (requested %d)\n", g_rt.device, device);
+      return -1;
+    }
+    return 0;
+  }
+  g_rt.init(device);
+  return 0;
+}
+
+void czb_set_stream(void* cuda_stream) {
+  Runtime& R = rt();
+  CZB_CHECK(cudaStreamSynchronize(R.stream));
+  if (R.own_stream) { cudaStreamDestroy(R.stream); R.own_stream = false; }
+  R.stream = (cudaStream_t)cuda_stream;
+}
+
+void czb_sync(void) { rt().sync(); }
+
+void* czb_malloc(size_t bytes) {
+  Runtime& R = rt();
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, bytes ? bytes : 1);
+  if (e != cudaSuccess) {
+    fprintf(stderr, "czb200: cudaMalloc(%zu) failed: %s\n", bytes, cudaGetErrorString(e));
+    return nullptr;
+  }
+  CZB_CHECK(cudaMemsetAsync(p, 0, bytes, R.stream));
+  return p;
+}
+
+void czb_free(void* p) {
+  if (!p) return;
+  rt().sync();
+  cudaFree(p);
+}
+
+void czb_memcpy_h2d(void* dst, const void* src, size_t bytes) {
+  Runtime& R = rt();
+  CZB_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, R.stream));
+  R.sync();
+}
+void czb_memcpy_d2h(void* dst, const void* src, size_t bytes) {
+  Runtime& R = rt();
+  CZB_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, R.stream));
+  R.sync();
+}
+
+long long czb_launch_count(void) { return czb::launch_count(); }
+
+void czb_staged_bytes(double* h2d, double* d2h) {
+  Runtime& R = rt();
+  if (h2d) *h2d = (double)R.h2d_bytes;
+  if (d2h) *d2h = (double)R.d2h_bytes;
+}
+
+}  // extern "C"

@@ -1,0 +1,82 @@
+// cubez_b200/csrc/runtime.h -- process-wide runtime of libczb200: device, stream, reduction
+// scratch, and the host-pointer staging used by the per-call reference ABI.
+#pragma once
+#include "kernels.cuh"
+#include <unordered_map>
+#include <cstring>
+
+namespace czb {
+
+long long launch_count();
+
+struct Mirror { void* dev; size_t bytes; };
+
+struct Runtime {
+  bool inited = false;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  RedBuf rb{nullptr, nullptr};
+  size_t rb_blocks = 0;
+  LoopState* d_scratch = nullptr;     // device LoopState for per-call ABI reductions
+  LoopState* h_state = nullptr;       // pinned host copy
+  unsigned long long* d_err = nullptr;
+  std::unordered_map<const void*, Mirror> mirrors;
+  PcrTables pcr2{0, 0, 0, 0, nullptr, nullptr};
+  PcrTables pcr4{0, 0, 0, 0, nullptr, nullptr};
+  size_t h2d_bytes = 0, d2h_bytes = 0;   // staged traffic (per-call ABI with host pointers)
+
+  void init(int dev);
+  Launch launch(const LoopState* st = nullptr, LoopState* acc = nullptr) {
+    Launch L; L.s = stream; L.rb = rb; L.rb_blocks = rb_blocks; L.st = st; L.acc_st = acc ? acc : d_scratch;
+    return L;
+  }
+  // read acc[slot] of the scratch state back to the host (synchronises the stream)
+  double read_acc(int slot);
+  void sync() { CZB_CHECK(cudaStreamSynchronize(stream)); }
+};
+
+Runtime& rt();   // initialises lazily on the current device (or CZB_DEVICE)
+
+// Is `p` usable directly by kernels (device or managed memory)?
+bool is_device_ptr(const void* p);
+
+// Argument staging for the reference ABI (cz_Ffunc.h): arrays allocated by the caller with
+// new[] are host memory; they are mirrored on the device for the duration of one call
+// (H2D before when `in`, D2H after when `out`).  Device / managed pointers pass through.
+template <class T>
+class Arg {
+ public:
+  Arg(T* host_or_dev, size_t count, bool in, bool out) : p_(host_or_dev), n_(count), out_(out) {
+    if (!p_ || is_device_ptr(p_)) { d_ = p_; staged_ = false; return; }
+    Runtime& R = rt();
+    const size_t bytes = sizeof(T) * n_;
+    auto it = R.mirrors.find((const void*)p_);
+    if (it == R.mirrors.end() || it->second.bytes < bytes) {
+      if (it != R.mirrors.end()) { cudaFree(it->second.dev); R.mirrors.erase(it); }
+      void* d = nullptr;
+      CZB_CHECK(cudaMalloc(&d, bytes));
+      it = R.mirrors.emplace((const void*)p_, Mirror{d, bytes}).first;
+    }
+    d_ = (T*)it->second.dev;
+    staged_ = true;
+    if (in) {
+      CZB_CHECK(cudaMemcpyAsync(d_, p_, bytes, cudaMemcpyHostToDevice, R.stream));
+      R.h2d_bytes += bytes;
+    }
+  }
+  ~Arg() {
+    if (staged_ && out_) {
+      Runtime& R = rt();
+      CZB_CHECK(cudaMemcpyAsync((void*)p_, d_, sizeof(T) * n_, cudaMemcpyDeviceToHost, R.stream));
+      CZB_CHECK(cudaStreamSynchronize(R.stream));
+      R.d2h_bytes += sizeof(T) * n_;
+    }
+  }
+  T* dev() const { return d_; }
+  bool staged() const { return staged_; }
+ private:
+  T* p_; T* d_; size_t n_; bool out_; bool staged_;
+};
+
+}  // namespace czb

@@ -1,0 +1,551 @@
+// cubez_b200/csrc/solver.cu -- device-resident iteration loops reproducing the control flow of
+// the reference's CZ::JACOBI / PSOR / RBSOR / PBiCGSTAB / LSOR_PCR_* (src/cz_cpp/cz_Poisson.cpp)
+// plus the czb_ctx_* / czb_solve entry points of include/czb200.h.
+//
+// Difference from the reference that matters for speed, not for results: the convergence test
+// `res < eps` is evaluated ON THE DEVICE (k_finish_iteration / k_bicg_scalar set LoopState.done
+// and every later kernel of the stream returns immediately), so the host enqueues iterations in
+// batches and only polls a pinned copy of the state; iteration counts and residual histories
+// are exactly those of a loop that checks after every iteration.
+#include "solver.h"
+#include "../../include/czb200.h"
+#include <cfloat>
+#include <cmath>
+#include <strings.h>
+
+using namespace czb;
+
+namespace {
+
+// BiCGstab scalar recurrences (cz_Poisson.cpp:376-500), all in REAL like the reference's
+// REAL_TYPE locals; dot results are rounded to REAL first (Fdot1/Fdot2 return REAL_TYPE).
+__global__ void k_bicg_scalar(LoopState* st, int phase, double res_normal, double eps, double* hist, int hist_len) {
+  if (st->done) return;
+  if (phase == -1) {           // cz_Poisson.cpp:368-371
+    st->scal[SC_RHO_OLD] = 1.0; st->scal[SC_ALPHA] = 0.0; st->scal[SC_OMEGA] = 1.0;
+    st->scal[SC_NEG_OMEGA] = -1.0; st->scal[SC_BETA] = 0.0; st->scal[SC_RHO] = 0.0;
+  } else if (phase == 0) {     // rho, breakdown test, beta  (:376-393)
+    const REAL rho = (REAL)st->acc[0];
+    st->scal[SC_RHO] = (double)rho;
+    if (fabs((double)rho) < (double)FLT_MIN) { st->done = 1; st->status = 1; return; }
+    if (st->itr >= 1) {
+      const REAL rho_old = (REAL)st->scal[SC_RHO_OLD], alpha = (REAL)st->scal[SC_ALPHA], omega = (REAL)st->scal[SC_OMEGA];
+      const REAL beta = rho / rho_old * alpha / omega;
+      st->scal[SC_BETA] = (double)beta;
+    }
+  } else if (phase == 1) {     // alpha = rho / (q, r0)  (:427-431)
+    const REAL rho = (REAL)st->scal[SC_RHO];
+    const REAL alpha = rho / (REAL)st->acc[1];
+    st->scal[SC_ALPHA] = (double)alpha;
+    st->scal[SC_NEG_ALPHA] = (double)(-alpha);
+  } else if (phase == 2) {     // omega = (t, s) / (t, t)  (:464-465)
+    const REAL omega = (REAL)st->acc[2] / (REAL)st->acc[3];
+    st->scal[SC_OMEGA] = (double)omega;
+    st->scal[SC_NEG_OMEGA] = (double)(-omega);
+  } else {                     // res = Fdot1(r); normalise; history; test; rho_old = rho  (:481-500)
+    double res = (double)(REAL)st->acc[4];
+    res *= res_normal;
+    res = sqrt(res);
+    st->res = res;
+    const int it = st->itr;
+    if (hist && it < hist_len) hist[it] = res;
+    st->itr = it + 1;
+    if (res < eps) { st->done = 1; return; }
+    st->scal[SC_RHO_OLD] = st->scal[SC_RHO];
+  }
+}
+
+int getNumStage(int n) {   // cz.h:293-300
+  int b = 1;
+  for (int i = 1; i < 20; i++) { b *= 2; if (n < b) return i; }
+  return -1;
+}
+
+inline double ipow2(int e) { return (double)(1LL << e); }
+
+}  // namespace
+
+int czb_parse_solver(const char* q) {
+  if (!q) return 0;
+  struct { const char* n; int v; } tab[] = {
+    {"jacobi", LS_JACOBI}, {"psor", LS_PSOR}, {"sor2sma", LS_SOR2SMA}, {"pbicgstab", LS_BICGSTAB},
+    {"pcr_rb", LS_PCR_RB}, {"pcr_rb_esa", LS_PCR_RB_ESA}, {"pcr_j_esa", LS_PCR_J_ESA}, {"pcr", LS_PCR},
+    {"pcr_eda", LS_PCR_EDA}, {"pcr_esa", LS_PCR_ESA},
+    {"jacobi_maf", LS_JACOBI_MAF}, {"psor_maf", LS_PSOR_MAF}, {"sor2sma_maf", LS_SOR2SMA_MAF},
+    {"pbicgstab_maf", LS_BICGSTAB_MAF}, {"pcr_rb_maf", LS_PCR_RB_MAF}, {"pcr_rb_esa_maf", LS_PCR_RB_ESA_MAF},
+    {"pcr_maf", LS_PCR_MAF}, {"pcr_eda_maf", LS_PCR_EDA_MAF}, {"pcr_esa_maf", LS_PCR_ESA_MAF}};
+  for (auto& t : tab) if (!strcasecmp(q, t.n)) return t.v;
+  return 0;
+}
+
+// ============================================================================ helpers
+REAL* czb_ctx::field(REAL*& slot) {
+  if (!slot) {
+    slot = (REAL*)czb_malloc(sizeof(REAL) * field_elems());
+    if (!slot) { fprintf(stderr, "czb200: out of device memory for a work field\n"); abort(); }
+  }
+  return slot;
+}
+
+Launch czb_ctx::launch(bool with_state) {
+  Runtime& R = rt();
+  Launch L = R.launch(with_state ? d_state : nullptr, d_state);
+  return L;
+}
+
+void czb_ctx::Comm_S(REAL* f, int width) {
+  if (comm && comm->nranks > 1) comm_halo(comm, f, G, width, rt().stream);
+}
+
+void czb_ctx::Comm_SUM(int slot, int count) {
+  if (comm && comm->nranks > 1) comm_allreduce_sum(comm, &d_state->acc[slot], count, rt().stream);
+}
+
+void czb_ctx::begin_loop(int itr_max) {
+  Runtime& R = rt();
+  if (hist_cap < itr_max + 2) {
+    if (d_hist) { R.sync(); cudaFree(d_hist); }
+    hist_cap = itr_max + 2;
+    CZB_CHECK(cudaMalloc(&d_hist, sizeof(double) * hist_cap));
+  }
+  launch_state_reset(launch(false), d_state);
+  CZB_CHECK(cudaEventRecord(ev_t0, R.stream));
+}
+
+int czb_ctx::end_loop(int itr_max, double& res, bool bicg) {
+  Runtime& R = rt();
+  CZB_CHECK(cudaEventRecord(ev_t1, R.stream));
+  CZB_CHECK(cudaMemcpyAsync(&h_state[0], d_state, sizeof(LoopState), cudaMemcpyDeviceToHost, R.stream));
+  R.sync();
+  float ms = 0.f;
+  CZB_CHECK(cudaEventElapsedTime(&ms, ev_t0, ev_t1));
+  last_ms = ms;
+  const LoopState& S = h_state[0];
+  res = S.res;
+  if (S.status != 0) return 0;                      // breakdown: "Solver error" (cz_Poisson.cpp:379-383)
+  if (S.done) return S.itr;
+  return bicg ? itr_max : itr_max + 1;              // loop bounds cz_Poisson.cpp:39,373
+}
+
+template <class Body>
+int czb_ctx::run_checked(int itr_max, double& res, Body body) {
+  Runtime& R = rt();
+  begin_loop(itr_max);
+  const int batch = 16;
+  int launched = 0, nb = 0;
+  bool stop = false;
+  while (launched < itr_max && !stop) {
+    const int m = (itr_max - launched < batch) ? itr_max - launched : batch;
+    for (int q = 0; q < m; ++q) body(launched + q + 1);
+    launched += m;
+    const int slot = nb & 1;
+    CZB_CHECK(cudaMemcpyAsync(&h_state[1 + slot], d_state, sizeof(LoopState), cudaMemcpyDeviceToHost, R.stream));
+    CZB_CHECK(cudaEventRecord(ev[slot], R.stream));
+    if (nb >= 1) {   // look at the batch before this one while this one runs
+      const int ps = (nb - 1) & 1;
+      CZB_CHECK(cudaEventSynchronize(ev[ps]));
+      if (h_state[1 + ps].done) stop = true;
+    }
+    ++nb;
+  }
+  return end_loop(itr_max, res, false);
+}
+
+// ============================================================================ loops
+// CZ::JACOBI (cz_Poisson.cpp:30-82).  The reference's copy-back pass (cz_solver.f90:369-375) is
+// replaced by ping-pong between X and WRK; both hold the same boundary/guard values.
+int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check) {
+  Runtime& R = rt();
+  REAL* W = field(WRK);
+  if (converge_check) {
+    CZB_CHECK(cudaMemcpyAsync(W, X, sizeof(REAL) * field_elems(), cudaMemcpyDeviceToDevice, R.stream));
+    wrk_guards_zero = false;
+  } else if (!wrk_guards_zero) {   // preconditioner call: xx is all-zero outside the inner cells
+    CZB_CHECK(cudaMemsetAsync(W, 0, sizeof(REAL) * field_elems(), R.stream));
+    wrk_guards_zero = true;
+  }
+  const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
+  auto body = [&](int it) {
+    REAL* src = (it & 1) ? X : W;
+    REAL* dst = (it & 1) ? W : X;
+    Launch L = launch();
+    launch_jacobi(L, G, src, dst, B, cf, ac1, rs, false);
+    Comm_S(dst, 1);
+    if (converge_check) {
+      Comm_SUM(0);
+      launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+      launch_bc_k(L, G, dst, pitch, origin, nID);
+    }
+  };
+  int itr, done_iters;
+  if (converge_check) {
+    itr = run_checked(itr_max, res, body);
+    done_iters = h_state[0].itr;
+  } else {
+    for (int it = 1; it <= itr_max; ++it) body(it);
+    itr = itr_max + 1; done_iters = itr_max;
+  }
+  if (done_iters & 1) launch_copy_inner(launch(false), G, X, W);
+  flop += 18.0 * G.cells() * done_iters;
+  return itr;
+}
+
+// CZ::PSOR (cz_Poisson.cpp:95-146): lexicographic SOR in the reference's 1-thread order.
+int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check) {
+  const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
+  auto body = [&](int) {
+    Launch L = launch();
+    launch_psor_sweep(L, G, X, B, cf, ac1, rs, false);
+    Comm_S(X, 1);
+    if (converge_check) {
+      Comm_SUM(0);
+      launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+      launch_bc_k(L, G, X, pitch, origin, nID);
+    }
+  };
+  int itr, done_iters;
+  if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
+  else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+  flop += 18.0 * G.cells() * done_iters;
+  return itr;
+}
+
+// CZ::RBSOR (cz_Poisson.cpp:159-235).  Multi-rank: halo exchange after EACH colour so that the
+// result equals the single-domain one (the reference's MPI build exchanges once per iteration
+// and therefore differs from its own serial result).
+int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check) {
+  const int ip = parity_ip();
+  const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
+  auto body = [&](int) {
+    Launch L = launch();
+    for (int color = 0; color < 2; ++color) {
+      launch_rb_color(L, G, X, B, cf, ac1, ip + color, rs, color == 1);
+      Comm_S(X, 1);
+    }
+    if (converge_check) {
+      Comm_SUM(0);
+      launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+      launch_bc_k(L, G, X, pitch, origin, nID);
+    }
+  };
+  int itr, done_iters;
+  if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
+  else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+  flop += 18.0 * G.cells() * done_iters;
+  return itr;
+}
+
+static double pcr_iter_flop(const Geo& G, int pn, bool last4, double per4) {
+  const double nk = G.ked - G.kst + 1;
+  const double lines = (double)(G.jed - G.jst + 1) * (G.ied - G.ist + 1);
+  const double f = last4 ? (nk * 6.0 + nk * (pn - 2) * 14.0 + ipow2(pn - 2) * per4 + nk * 6.0 + 6.0)
+                         : (nk * 6.0 + nk * (pn - 1) * 14.0 + ipow2(pn - 1) * 9.0 + nk * 6.0 + 6.0);
+  return lines * f;
+}
+
+static REAL* ensure_mask(czb_ctx* c) {
+  if (!c->MSK) {
+    c->field(c->MSK);
+    launch_imask(c->launch(false), c->G, c->MSK);   // cz_Evaluate.cpp:390
+  }
+  return c->MSK;
+}
+
+// CZ::LSOR_PCR_RB (cz_Poisson.cpp:518-608) and LSOR_PCR_RB_ESA (:621-733, last4)
+int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool last4, bool converge_check) {
+  const int n = G.ked - G.kst + 1;
+  const int pn = getNumStage(n);
+  if (pn < 0) { printf("error : number of stage\n"); return 0; }
+  PcrTables& T = last4 ? pcr4 : pcr2;
+  pcr_build_tables(rt().stream, T, n, pn, last4);
+  REAL* M = ensure_mask(this);
+  const int ofs = (head[0] + head[1]) & 1;   // global (i+j) parity; 0 on a single domain
+  const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
+  auto body = [&](int) {
+    Launch L = launch();
+    for (int color = 0; color < 2; ++color) {
+      launch_pcr_lines(L, G, T, color, ofs, 0, X, X, M, B, ac1, rs, color == 1);
+      Comm_S(X, 1);
+    }
+    if (converge_check) {
+      Comm_SUM(0);
+      launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+      launch_bc_k(L, G, X, pitch, origin, nID);
+    }
+  };
+  int itr, done_iters;
+  if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
+  else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+  flop += pcr_iter_flop(G, pn, last4, 78.0) * done_iters;
+  return itr;
+}
+
+// CZ::LSOR_PCR (:745-816, 4x4), LSOR_PCR_ESA (:910-1005, 4x4), LSOR_PCR_EDA (:828-898, 2x2):
+// all lines in (j,i) order in place = Gauss-Seidel between lines; reproduced in the reference's
+// 1-thread order by wavefronts over the anti-diagonals i+j = const.
+int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool last4, bool converge_check) {
+  const int n = G.ked - G.kst + 1;
+  const int pn = getNumStage(n);
+  if (pn < 0) { printf("error : number of stage\n"); return 0; }
+  PcrTables& T = last4 ? pcr4 : pcr2;
+  pcr_build_tables(rt().stream, T, n, pn, last4);
+  REAL* M = ensure_mask(this);
+  const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
+  auto body = [&](int) {
+    Launch L = launch();
+    bool first = true;
+    for (int d = G.ist + G.jst; d <= G.ied + G.jed; ++d) {
+      launch_pcr_lines(L, G, T, 3, 0, d, X, X, M, B, ac1, rs, !first);
+      first = false;
+    }
+    Comm_S(X, 1);
+    if (converge_check) {
+      Comm_SUM(0);
+      launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+      launch_bc_k(L, G, X, pitch, origin, nID);
+    }
+  };
+  int itr, done_iters;
+  if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
+  else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+  flop += pcr_iter_flop(G, pn, last4, 74.0) * done_iters;
+  return itr;
+}
+
+// CZ::LSOR_PCR_J_ESA (cz_Poisson.cpp:1008-1095): line Jacobi
+int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check) {
+  const int n = G.ked - G.kst + 1;
+  const int pn = getNumStage(n);
+  if (pn < 0) { printf("error : number of stage\n"); return 0; }
+  pcr_build_tables(rt().stream, pcr2, n, pn, false);
+  REAL* M = ensure_mask(this);
+  REAL* W = field(WRK);
+  wrk_guards_zero = false;
+  const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
+  auto body = [&](int) {
+    Launch L = launch();
+    launch_pcr_lines(L, G, pcr2, 2, 0, 0, X, W, M, B, ac1, rs, false);
+    launch_copy_inner(L, G, X, W);
+    Comm_S(X, 1);
+    if (converge_check) {
+      Comm_SUM(0);
+      launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+      launch_bc_k(L, G, X, pitch, origin, nID);
+    }
+  };
+  int itr, done_iters;
+  if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
+  else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+  flop += pcr_iter_flop(G, pn, false, 0.0) * done_iters;
+  return itr;
+}
+
+// CZ::Preconditioner (cz_Poisson.cpp:273-322): lc_max = 8 sweeps without convergence check,
+// starting from the caller-cleared xx; unknown / "none" -> copy.
+void czb_ctx::Preconditioner(REAL* xx, REAL* bb, double& flop, int pc_type) {
+  double res = 0.0;
+  const int lc_max = 8;
+  switch (pc_type) {
+    case LS_JACOBI:     JACOBI(res, xx, bb, lc_max, flop, false); break;
+    case LS_PSOR:       PSOR(res, xx, bb, lc_max, flop, false); break;
+    case LS_SOR2SMA:    RBSOR(res, xx, bb, lc_max, flop, false); break;
+    case LS_PCR:        LSOR_PCR(res, xx, bb, lc_max, flop, true, false); break;
+    case LS_PCR_EDA:    LSOR_PCR(res, xx, bb, lc_max, flop, false, false); break;
+    case LS_PCR_RB:     LSOR_PCR_RB(res, xx, bb, lc_max, flop, false, false); break;
+    case LS_PCR_RB_ESA: LSOR_PCR_RB(res, xx, bb, lc_max, flop, true, false); break;
+    default:
+      CZB_CHECK(cudaMemcpyAsync(xx, bb, sizeof(REAL) * field_elems(), cudaMemcpyDeviceToDevice, rt().stream));
+  }
+}
+
+// CZ::PBiCGSTAB (cz_Poisson.cpp:332-504).  Scalars rho/alpha/beta/omega live in LoopState.scal
+// on the device (k_bicg_scalar), the vector kernels read them from there.
+int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, int pc_type) {
+  Runtime& R = rt();
+  const size_t bytes = sizeof(REAL) * field_elems();
+  REAL *p = field(pcg_p), *p_ = field(pcg_p_), *r = field(pcg_r), *r0 = field(pcg_r0), *q = field(pcg_q),
+       *s = field(pcg_s), *s_ = field(pcg_s_), *t_ = field(pcg_t_);
+  double* sc = d_state->scal;
+  double pflop = 0.0;
+
+  begin_loop(ItrMax);
+  {
+    Launch L = launch();
+    CZB_CHECK(cudaMemsetAsync(q, 0, bytes, R.stream));                       // :344
+    launch_calc_rk(L, G, r, X, B, cf);                                       // :356
+    Comm_S(r, 1);                                                            // :362
+    CZB_CHECK(cudaMemcpyAsync(r0, r, bytes, cudaMemcpyDeviceToDevice, R.stream));   // :365
+    k_bicg_scalar<<<1, 1, 0, R.stream>>>(d_state, -1, res_normal, eps, d_hist, hist_cap);
+    count_launch();
+  }
+  auto scalar = [&](int phase) {
+    k_bicg_scalar<<<1, 1, 0, R.stream>>>(d_state, phase, res_normal, eps, d_hist, hist_cap);
+    count_launch();
+  };
+  auto body = [&](int itr) {
+    Launch L = launch();
+    launch_dot2(L, G, r, r0, 0); Comm_SUM(0); scalar(0);                     // rho :376-383
+    if (itr == 1) {
+      CZB_CHECK(cudaMemcpyAsync(p, r, bytes, cudaMemcpyDeviceToDevice, R.stream));   // :388
+    } else {
+      launch_bicg1(L, G, p, r, q, 0, 0, &sc[SC_BETA], &sc[SC_OMEGA]);        // :397
+    }
+    Comm_S(p, 1);                                                            // :402
+    CZB_CHECK(cudaMemsetAsync(p_, 0, bytes, R.stream));                      // :405
+    Preconditioner(p_, p, pflop, pc_type);                                   // :409
+    launch_calc_ax(L, G, q, p_, cf, r0, 1); Comm_SUM(1); scalar(1);          // q = A p_, alpha :421-431
+    launch_triad(L, G, s, q, r, 0, &sc[SC_NEG_ALPHA]);                       // s = r - alpha q :434
+    Comm_S(s, 1);                                                            // :438
+    CZB_CHECK(cudaMemsetAsync(s_, 0, bytes, R.stream));                      // :441
+    Preconditioner(s_, s, pflop, pc_type);                                   // :445
+    launch_calc_ax(L, G, t_, s_, cf, s, 2);                                  // t = A s_, (t,s) :457-464
+    launch_dot1(L, G, t_, 3); Comm_SUM(2, 2); scalar(2);                     // (t,t), omega
+    launch_bicg2(L, G, X, p_, s_, 0, 0, &sc[SC_ALPHA], &sc[SC_OMEGA]);       // x += alpha p_ + omega s_ :470
+    launch_triad(L, G, r, t_, s, 0, &sc[SC_NEG_OMEGA]);                      // r = s - omega t :476
+    launch_dot1(L, G, r, 4);                                                 // :481
+    Comm_S(X, 1); Comm_SUM(4);                                               // :486-488
+    scalar(3);                                                               // :490-500
+    launch_bc_k(L, G, X, pitch, origin, nID);                                // :495
+  };
+  // for (itr=1; itr<ItrMax; itr++)  (cz_Poisson.cpp:373)
+  const int n_it = ItrMax - 1;
+  const int batch = 4;
+  int launched = 0, nb = 0;
+  bool stop = false;
+  while (launched < n_it && !stop) {
+    const int m = (n_it - launched < batch) ? n_it - launched : batch;
+    for (int k = 0; k < m; ++k) body(launched + k + 1);
+    launched += m;
+    const int slot = nb & 1;
+    CZB_CHECK(cudaMemcpyAsync(&h_state[1 + slot], d_state, sizeof(LoopState), cudaMemcpyDeviceToHost, R.stream));
+    CZB_CHECK(cudaEventRecord(ev[slot], R.stream));
+    if (nb >= 1) {
+      const int ps = (nb - 1) & 1;
+      CZB_CHECK(cudaEventSynchronize(ev[ps]));
+      if (h_state[1 + ps].done) stop = true;
+    }
+    ++nb;
+  }
+  const int itr = end_loop(ItrMax, res, true);
+  const int done_iters = h_state[0].itr;
+  flop += (14.0 + (double)done_iters * (2 + 4 + 13 + 2 + 2 + 13 + 4 + 4 + 2 + 2)) * G.cells();
+  if (launched > 0) flop += pflop * ((double)done_iters / (double)launched);
+  return itr;
+}
+
+// ============================================================================ C entry points
+extern "C" {
+
+int czb_slab_decompose(const int gsz[3], int nranks, int rank, int sz[3], int head[3], int nID[6], int idx[6]) {
+  return czb::slab_decompose(gsz, nranks, rank, sz, head, nID, idx);
+}
+
+czb_ctx* czb_ctx_create(const int sz[3], const int idx[6], const int nID[6], CZB_REAL dh, const CZB_REAL org[3]) {
+  Runtime& R = rt();
+  czb_ctx* c = new czb_ctx();
+  memset((void*)c, 0, sizeof(czb_ctx));
+  c->gc = 2;
+  for (int a = 0; a < 3; ++a) { c->size[a] = sz[a]; c->head[a] = 1; c->origin[a] = org ? org[a] : (REAL)0; }
+  for (int f = 0; f < 6; ++f) c->nID[f] = nID ? nID[f] : -1;
+  if (idx) { for (int a = 0; a < 6; ++a) c->innerFidx[a] = idx[a]; }
+  else {   // CZ::range_inner_index, cz_miscel.cpp:20-52
+    c->innerFidx[0] = 2; c->innerFidx[2] = 2; c->innerFidx[4] = 2;
+    c->innerFidx[1] = c->nID[1] < 0 ? sz[0] - 1 : sz[0];
+    c->innerFidx[3] = c->nID[3] < 0 ? sz[1] - 1 : sz[1];
+    c->innerFidx[5] = c->nID[5] < 0 ? sz[2] - 1 : sz[2];
+  }
+  c->pitch = dh;
+  for (int a = 0; a < 6; ++a) c->cf[a] = (REAL)1.0;   // cz.h:169-172
+  c->cf[6] = (REAL)6.0;
+  c->eps = 1.0e-5;                                    // cz.h:162
+  c->G = make_geo(c->size, c->innerFidx, c->gc);
+  c->res_normal = 1.0 / c->G.cells();
+  c->wrk_guards_zero = false;
+  CZB_CHECK(cudaMalloc(&c->d_state, sizeof(LoopState)));
+  CZB_CHECK(cudaMemset(c->d_state, 0, sizeof(LoopState)));
+  CZB_CHECK(cudaMallocHost(&c->h_state, sizeof(LoopState) * 4));
+  CZB_CHECK(cudaEventCreate(&c->ev[0])); CZB_CHECK(cudaEventCreate(&c->ev[1]));
+  CZB_CHECK(cudaEventCreate(&c->ev_t0)); CZB_CHECK(cudaEventCreate(&c->ev_t1));
+  (void)R;
+  return c;
+}
+
+void czb_ctx_destroy(czb_ctx* c) {
+  if (!c) return;
+  rt().sync();
+  REAL* fields[] = {c->WRK, c->MSK, c->pcg_p, c->pcg_p_, c->pcg_r, c->pcg_r0, c->pcg_q, c->pcg_s, c->pcg_s_,
+                    c->pcg_t_, c->Xd, c->Bd};
+  for (REAL* f : fields) if (f) cudaFree(f);
+  pcr_free_tables(c->pcr2); pcr_free_tables(c->pcr4);
+  if (c->d_hist) cudaFree(c->d_hist);
+  cudaFree(c->d_state); cudaFreeHost(c->h_state);
+  cudaEventDestroy(c->ev[0]); cudaEventDestroy(c->ev[1]); cudaEventDestroy(c->ev_t0); cudaEventDestroy(c->ev_t1);
+  comm_destroy(c->comm);
+  delete c;
+}
+
+void czb_ctx_set_eps(czb_ctx* c, double eps) { c->eps = eps; }
+void czb_ctx_set_res_normal(czb_ctx* c, double v) { c->res_normal = v; }
+void czb_ctx_set_head(czb_ctx* c, const int head[3]) { for (int a = 0; a < 3; ++a) c->head[a] = head[a]; }
+void czb_ctx_set_variant(czb_ctx* c, int v) { c->variant = v; }
+double czb_last_solve_ms(czb_ctx* c) { return c->last_ms; }
+
+int czb_comm_unique_id(void* id128) { return comm_unique_id(id128); }
+
+int czb_ctx_comm_init(czb_ctx* c, int nranks, int rank, const void* id128) {
+  rt();
+  if (c->comm) comm_destroy(c->comm);
+  c->comm = comm_create(nranks, rank, id128, c->nID[2], c->nID[3]);
+  return 0;
+}
+
+int czb_solve(czb_ctx* c, const char* solver, const char* precond, CZB_REAL* X, CZB_REAL* B, int itr_max,
+              CZB_REAL omg, double* res_out, double* hist, int hist_len, double* flop_out) {
+  Runtime& R = rt();
+  const int ls = czb_parse_solver(solver);
+  if (ls == 0) { printf("Invalid solver\n"); return 0; }           // CZ::setLS, cz_Evaluate.cpp:799-802
+  if (ls >= LS_PSOR_MAF) {
+    fprintf(stderr, "czb200: solver '%s' (stretched-grid MAF) is outside the accelerated hot path; no CPU fallback.\n", solver);
+    return 0;
+  }
+  int pc = 0;
+  if (ls == LS_BICGSTAB) {
+    pc = czb_parse_solver(precond);
+    if (pc == 0 && precond) printf("precon=%s\n", precond);        // CZ::setStrPre falls through to copy
+    if (pc >= LS_PSOR_MAF || pc == LS_BICGSTAB || pc == LS_PCR_ESA || pc == LS_PCR_J_ESA) pc = 0;
+  }
+  c->ac1 = omg;
+  const size_t bytes = sizeof(REAL) * c->field_elems();
+  REAL* Xdev = X; REAL* Bdev = B;
+  const bool xh = !is_device_ptr(X), bh = !is_device_ptr(B);
+  if (xh) { Xdev = c->field(c->Xd); CZB_CHECK(cudaMemcpyAsync(Xdev, X, bytes, cudaMemcpyHostToDevice, R.stream)); R.h2d_bytes += bytes; }
+  if (bh) { Bdev = c->field(c->Bd); CZB_CHECK(cudaMemcpyAsync(Bdev, B, bytes, cudaMemcpyHostToDevice, R.stream)); R.h2d_bytes += bytes; }
+  double res = 0.0, flop = 0.0;
+  int itr = 0;
+  switch (ls) {
+    case LS_JACOBI:     itr = c->JACOBI(res, Xdev, Bdev, itr_max, flop); break;
+    case LS_PSOR:       itr = c->PSOR(res, Xdev, Bdev, itr_max, flop); break;
+    case LS_SOR2SMA:    itr = c->RBSOR(res, Xdev, Bdev, itr_max, flop); break;
+    case LS_BICGSTAB:   itr = c->PBiCGSTAB(res, Xdev, Bdev, itr_max, flop, pc); break;
+    case LS_PCR:        itr = c->LSOR_PCR(res, Xdev, Bdev, itr_max, flop, true); break;
+    case LS_PCR_ESA:    itr = c->LSOR_PCR(res, Xdev, Bdev, itr_max, flop, true); break;
+    case LS_PCR_EDA:    itr = c->LSOR_PCR(res, Xdev, Bdev, itr_max, flop, false); break;
+    case LS_PCR_RB:     itr = c->LSOR_PCR_RB(res, Xdev, Bdev, itr_max, flop, false); break;
+    case LS_PCR_RB_ESA: itr = c->LSOR_PCR_RB(res, Xdev, Bdev, itr_max, flop, true); break;
+    case LS_PCR_J_ESA:  itr = c->LSOR_PCR_J_ESA(res, Xdev, Bdev, itr_max, flop); break;
+    default: break;
+  }
+  const int n_hist = c->h_state[0].itr;
+  if (hist && hist_len > 0 && n_hist > 0) {
+    const int m = n_hist < hist_len ? n_hist : hist_len;
+    CZB_CHECK(cudaMemcpyAsync(hist, c->d_hist, sizeof(double) * m, cudaMemcpyDeviceToHost, R.stream));
+    R.d2h_bytes += sizeof(double) * m;
+  }
+  if (xh) { CZB_CHECK(cudaMemcpyAsync(X, Xdev, bytes, cudaMemcpyDeviceToHost, R.stream)); R.d2h_bytes += bytes; }
+  R.sync();
+  if (res_out) *res_out = res;
+  if (flop_out) *flop_out += flop;
+  return itr;
+}
+
+}  // extern "C"

@@ -1,0 +1,74 @@
+// cubez_b200/csrc/solver.h -- czb_ctx: host-side mirror of the reference's `class CZ`
+// (src/cz_cpp/cz.h:80-588) restricted to the state the iteration loops of
+// src/cz_cpp/cz_Poisson.cpp need.  Method names and argument meaning follow the reference.
+#pragma once
+#include "runtime.h"
+#include "comm.h"
+#include <string>
+#include <vector>
+
+// reference src/cz_cpp/cz_Define.h:68-89
+enum LinearSolver {
+  LS_PSOR = 1, LS_SOR2SMA, LS_BICGSTAB, LS_JACOBI, LS_PCR, LS_PCR_EDA, LS_PCR_ESA, LS_PCR_RB, LS_PCR_RB_ESA,
+  LS_PCR_J_ESA, LS_PSOR_MAF, LS_SOR2SMA_MAF, LS_BICGSTAB_MAF, LS_JACOBI_MAF, LS_PCR_MAF, LS_PCR_EDA_MAF,
+  LS_PCR_ESA_MAF, LS_PCR_RB_MAF, LS_PCR_RB_ESA_MAF
+};
+
+struct czb_ctx {
+  // ---- CZ state (cz.h) ----
+  int size[3];            // local size
+  int innerFidx[6];
+  int nID[6];
+  int head[3];
+  int gc;                 // GUIDE = 2 (cz_Define.h:40)
+  REAL pitch;             // dh
+  REAL origin[3];
+  REAL cf[7];             // {1,1,1,1,1,1,6} (cz.h:169-172)
+  REAL ac1;               // omega (cz_Evaluate.cpp:99)
+  double eps;             // 1e-5 (cz.h:162)
+  double res_normal;      // 1 / (global inner cells) (cz_Evaluate.cpp:222-224)
+  int variant;            // 0 auto, 1 baseline kernels only
+
+  czb::Geo G;
+  czb::Comm* comm;
+
+  // ---- device work arrays (allocated on first use) ----
+  REAL* WRK; REAL* MSK;
+  REAL *pcg_p, *pcg_p_, *pcg_r, *pcg_r0, *pcg_q, *pcg_s, *pcg_s_, *pcg_t_;
+  REAL* Xd; REAL* Bd;     // staging when the caller passes host pointers
+  bool wrk_guards_zero;
+  czb::PcrTables pcr2, pcr4;
+
+  czb::LoopState* d_state;
+  czb::LoopState* h_state;   // pinned, 2 slots
+  double* d_hist; int hist_cap;
+  cudaEvent_t ev[2], ev_t0, ev_t1;
+  double last_ms;
+  int hist_len_req;
+
+  // ---- helpers ----
+  size_t field_elems() const { return (size_t)G.total; }
+  REAL* field(REAL*& slot);
+  czb::Launch launch(bool with_state = true);
+  void Comm_S(REAL* f, int width = 1);            // cz_comm.cpp:23-38
+  void Comm_SUM(int slot, int count = 1);         // cz_comm.cpp:74-140 on device scalars
+  int parity_ip() const { return (head[0] + head[1] + head[2] + 1) % 2; }   // cz_Poisson.cpp:181
+
+  // ---- iteration loops (cz_Poisson.cpp) ----
+  int JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check = true);
+  int PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check = true);
+  int RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check = true);
+  int LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool last4, bool converge_check = true);
+  int LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool last4, bool converge_check = true);
+  int LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check = true);
+  void Preconditioner(REAL* xx, REAL* bb, double& flop, int pc_type);
+  int PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, int pc_type);
+
+  // generic driver: enqueue `body(it)` for it = 1..itr_max in batches, polling the device
+  // state without stalling the queue.  Returns the reference's iteration count.
+  template <class Body> int run_checked(int itr_max, double& res, Body body);
+  void begin_loop(int itr_max);
+  int end_loop(int itr_max, double& res, bool bicg);
+};
+
+int czb_parse_solver(const char* name);   // CZ::setLS / setStrPre names -> LinearSolver, 0 unknown

@@ -1,0 +1,186 @@
+/* include/czb200.h -- C ABI of libczb200_f32.so / libczb200_f64.so
+ *
+ * B200 (sm_100a) implementation of the iterative-solver hot path of kenoogl/CubeZ behind the
+ * reference's own kernel boundary.  One library per precision, exactly like the reference
+ * (REAL_TYPE = float unless -D_REAL_IS_DOUBLE_, reference src/cz_cpp/cz_Define.h:28-37).
+ *
+ * PART 1 are the symbols of the reference's Fortran kernel layer, src/cz_cpp/cz_Ffunc.h:16-578:
+ * same names (lower case + trailing underscore = the Fortran mangling the reference links by),
+ * same argument order, every argument by pointer, void return.  They are callable from C/C++
+ * and from Fortran (interface blocks with bind(C,name='jacobi_') and non-value dummies, see
+ * INTEGRATION.md).  Array arguments may be DEVICE (cudaMalloc / czb_malloc / managed) pointers
+ * -> zero-copy, or plain HOST pointers (what the unmodified reference driver passes) -> staged
+ * through a device mirror for the duration of the call.  Scalar in/out arguments (res, flop,
+ * dot results) are host memory, as in the reference.  There is no CPU fallback: without a
+ * CUDA device every entry point aborts with a message.
+ *
+ * PART 2 are extensions the reference ABI lacks and a GPU drop-in needs: device allocation,
+ * stream selection, and fused device-resident solve loops that reproduce the control flow of
+ * CZ::JACOBI / RBSOR / PBiCGSTAB / LSOR_PCR_* (src/cz_cpp/cz_Poisson.cpp) without a host
+ * round-trip per kernel.
+ */
+#ifndef CZB200_H_
+#define CZB200_H_
+#include <stddef.h>
+
+#ifdef _REAL_IS_DOUBLE_
+typedef double CZB_REAL;
+#else
+typedef float CZB_REAL;
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ===================================================================== PART 1
+ * sz[3] = {ix,jx,kx} local size without guard cells; idx[6] = {ist,ied,jst,jed,kst,ked}
+ * inclusive Fortran indices of the computed cells; g = guard width (2); arrays are
+ * (kx+2g, ix+2g, jx+2g) with k contiguous (cz_solver.f90:218); cf[7] = {c1..c6, dd};
+ * res and flop are ACCUMULATED into, dot results are overwritten.                         */
+
+/* cz_Ffunc.h:16-21  <- cz_solver.f90:22-191   Dirichlet faces where nID[face] < 0 */
+void bc_k_(int* sz, int* g, CZB_REAL* p, CZB_REAL* dh, CZB_REAL* org, int* nID);
+/* cz_Ffunc.h:23-32  <- cz_solver.f90:284-387  relaxed Jacobi sweep, wk2 = scratch field */
+void jacobi_(CZB_REAL* p, int* sz, int* idx, int* g, CZB_REAL* cf, CZB_REAL* omg, CZB_REAL* b,
+             double* res, CZB_REAL* wk2, double* flop);
+/* cz_Ffunc.h:35-43  <- cz_solver.f90:207-269  lexicographic point SOR (hyperplane wavefront) */
+void psor_(CZB_REAL* p, int* sz, int* idx, int* g, CZB_REAL* cf, CZB_REAL* omg, CZB_REAL* b,
+           double* res, double* flop);
+/* cz_Ffunc.h:48-58  <- cz_solver.f90:404-493  one colour of red-black SOR */
+void psor2sma_core_(CZB_REAL* p, int* sz, int* idx, int* g, CZB_REAL* cf, int* ip, int* color,
+                    CZB_REAL* omg, CZB_REAL* b, double* res, double* flop);
+/* cz_Ffunc.h:60-77  <- cz_solver.f90:497-662  red-black line SOR, PCR pn-1 stages + 2x2 */
+void pcr_rb_(int* sz, int* idx, int* g, int* pn, int* ofst, int* color, CZB_REAL* x,
+             CZB_REAL* msk, CZB_REAL* rhs, CZB_REAL* WA, CZB_REAL* WC, CZB_REAL* WD,
+             CZB_REAL* WAA, CZB_REAL* WCC, CZB_REAL* WDD, CZB_REAL* omg, double* res, double* flop);
+/* cz_Ffunc.h:79-97  <- cz_solver.f90:1261-1469  as pcr_rb_, pn-2 stages + 4x4 Cramer */
+void pcr_rb_esa_(int* sz, int* idx, int* g, int* pn, int* ofst, int* color, int* s, CZB_REAL* x,
+                 CZB_REAL* msk, CZB_REAL* rhs, CZB_REAL* WA, CZB_REAL* WC, CZB_REAL* WD,
+                 CZB_REAL* WAA, CZB_REAL* WCC, CZB_REAL* WDD, CZB_REAL* omg, double* res,
+                 double* flop);
+/* cz_Ffunc.h:99-114 <- cz_solver.f90:666-878  lexicographic line SOR (line wavefront), 4x4 */
+void pcr_(int* sz, int* idx, int* g, int* pn, CZB_REAL* x, CZB_REAL* msk, CZB_REAL* rhs,
+          CZB_REAL* WA, CZB_REAL* WC, CZB_REAL* WD, CZB_REAL* WAA, CZB_REAL* WCC, CZB_REAL* WDD,
+          CZB_REAL* omg, double* res, double* flop);
+/* cz_Ffunc.h:116-128 <- cz_solver.f90:883-1045  as pcr_, pn-1 stages + 2x2 */
+void pcr_eda_(int* sz, int* idx, int* g, int* pn, CZB_REAL* x, CZB_REAL* msk, CZB_REAL* rhs,
+              CZB_REAL* WA, CZB_REAL* WC, CZB_REAL* WD, CZB_REAL* omg, double* res, double* flop);
+/* cz_Ffunc.h:130-146 <- cz_solver.f90:1050-1257 as pcr_ with zero-padded work arrays */
+void pcr_esa_(int* sz, int* idx, int* g, int* pn, int* s, CZB_REAL* x, CZB_REAL* msk,
+              CZB_REAL* rhs, CZB_REAL* SA, CZB_REAL* SC, CZB_REAL* SD, CZB_REAL* WA, CZB_REAL* WC,
+              CZB_REAL* WD, CZB_REAL* omg, double* res, double* flop);
+/* cz_Ffunc.h:148-166 <- cz_solver.f90:1473-1676 line Jacobi, pn-1 stages + 2x2 */
+void pcr_j_esa_(int* sz, int* idx, int* g, int* pn, int* s, CZB_REAL* x, CZB_REAL* msk,
+                CZB_REAL* rhs, CZB_REAL* SA, CZB_REAL* SC, CZB_REAL* SD, CZB_REAL* WA,
+                CZB_REAL* WC, CZB_REAL* WD, CZB_REAL* SRC, CZB_REAL* WRK, CZB_REAL* omg,
+                double* res, double* flop);
+
+/* cz_Ffunc.h:442-578 <- cz_blas.f90 */
+void imask_k_(CZB_REAL* x, int* sz, int* idx, int* g);                       /* :24-103  */
+void blas_clear_(CZB_REAL* x, int* sz, int* g);                              /* :112-149 */
+void blas_copy_(CZB_REAL* dst, CZB_REAL* src, int* sz, int* g);              /* :159-195 */
+void blas_copy_in_(CZB_REAL* dst, CZB_REAL* src, int* sz, int* g);           /* :205-242 */
+void blas_triad_(CZB_REAL* z, CZB_REAL* x, CZB_REAL* y, CZB_REAL* a, int* sz, int* idx, int* g,
+                 double* flop);                                              /* :255-308 */
+void blas_dot1_(CZB_REAL* r, CZB_REAL* p, int* sz, int* idx, int* g, double* flop);   /* :320-373 */
+void blas_dot2_(CZB_REAL* r, CZB_REAL* p, CZB_REAL* q, int* sz, int* idx, int* g,
+                double* flop);                                               /* :386-437 */
+void blas_bicg_1_(CZB_REAL* p, CZB_REAL* r, CZB_REAL* q, CZB_REAL* beta, CZB_REAL* omg, int* sz,
+                  int* idx, int* g, double* flop);                           /* :452-502 */
+void blas_bicg_2_(CZB_REAL* z, CZB_REAL* x, CZB_REAL* y, CZB_REAL* a, CZB_REAL* b, int* sz,
+                  int* idx, int* g, double* flop);                           /* :517-566 */
+void blas_calc_ax_(CZB_REAL* ap, CZB_REAL* p, int* sz, int* idx, int* g, CZB_REAL* cf,
+                   double* flop);                                            /* :579-644 */
+void blas_calc_rk_(CZB_REAL* r, CZB_REAL* p, CZB_REAL* b, int* sz, int* idx, int* g,
+                   CZB_REAL* cf, double* flop);                              /* :658-723 */
+void search_pivot_(CZB_REAL* pvt, int* sz, int* idx, int* g, CZB_REAL* X, CZB_REAL* Y,
+                   CZB_REAL* Z);                                             /* :947-1039 */
+
+/* cz_Ffunc.h <- cz_utility.f90:17-129 */
+void fileout_t_(int* sz, int* g, CZB_REAL* s, CZB_REAL* dh, CZB_REAL* org, char* fname);
+void exact_t_(int* sz, int* g, CZB_REAL* e, CZB_REAL* dh, CZB_REAL* org);
+void err_t_(int* sz, int* idx, int* g, double* d, CZB_REAL* p, CZB_REAL* e, int* loc);
+
+/* Stretched-grid ("MAF") twins, cz_maf.f90 + cz_blas.f90:738,845: OUT OF SCOPE (SURVEY.md
+ * §8f-2).  Exported so the reference driver links; they abort with a message if reached. */
+void jacobi_maf_(CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+                 CZB_REAL*, double*, CZB_REAL*, CZB_REAL*, double*);
+void psor_maf_(CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+               double*, double*);
+void psor2sma_core_maf_(CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, int*, int*,
+                        CZB_REAL*, CZB_REAL*, double*, CZB_REAL*, double*);
+void pcr_rb_maf_(int*, int*, int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+                 CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+                 CZB_REAL*, CZB_REAL*, double*, CZB_REAL*, double*);
+void pcr_rb_esa_maf_(int*, int*, int*, int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+                     CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+                     CZB_REAL*, CZB_REAL*, CZB_REAL*, double*, CZB_REAL*, double*);
+void pcr_maf_(int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+              CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+              CZB_REAL*, double*, CZB_REAL*, double*);
+void pcr_eda_maf_(int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+                  CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, double*, CZB_REAL*,
+                  double*);
+void pcr_esa_maf_(int*, int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+                  CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+                  CZB_REAL*, CZB_REAL*, double*, CZB_REAL*, double*);
+void calc_rk_maf_(CZB_REAL*, CZB_REAL*, CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*,
+                  CZB_REAL*, CZB_REAL*, double*);
+void calc_ax_maf_(CZB_REAL*, CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
+                  CZB_REAL*, double*);
+
+/* ===================================================================== PART 2 */
+
+/* Runtime ------------------------------------------------------------------- */
+int czb_real_bytes(void);                 /* 4 or 8 */
+const char* czb_version(void);
+int czb_init(int device);                 /* select device + create stream; 0 on success.  Aborts
+                                             with a message when no CUDA device is present. */
+void czb_set_stream(void* cuda_stream);   /* run on a caller-owned cudaStream_t (e.g. torch's) */
+void czb_sync(void);
+void* czb_malloc(size_t bytes);           /* device memory, zero-filled */
+void czb_free(void* p);
+void czb_memcpy_h2d(void* dst, const void* src, size_t bytes);   /* synchronous wrt the stream */
+void czb_memcpy_d2h(void* dst, const void* src, size_t bytes);
+long long czb_launch_count(void);         /* kernels launched by this library so far */
+void czb_staged_bytes(double* h2d, double* d2h);   /* bytes staged for host-pointer arguments */
+
+/* Slab decomposition along j (the slowest axis), SURVEY.md §8(e).  Pure host logic. ------ */
+/* For global size gsz[3] and `nranks` slabs: local size, 1-based head index, neighbour table
+ * nID[6] (cz_fparam.fi order; -1 = physical boundary) and inner index range of `rank`.
+ * Returns 0, or -1 when nranks exceeds the number of inner planes. */
+int czb_slab_decompose(const int gsz[3], int nranks, int rank, int sz[3], int head[3],
+                       int nID[6], int idx[6]);
+
+/* Solver context = the state CZ::Evaluate sets up (cz_Evaluate.cpp:56-390) -------------- */
+typedef struct czb_ctx czb_ctx;
+/* idx may be NULL: computed like CZ::range_inner_index (cz_miscel.cpp:20-52) from nID. */
+czb_ctx* czb_ctx_create(const int sz[3], const int idx[6], const int nID[6], CZB_REAL dh,
+                        const CZB_REAL org[3]);
+void czb_ctx_destroy(czb_ctx* c);
+void czb_ctx_set_eps(czb_ctx* c, double eps);                /* default 1e-5, cz.h:162 */
+void czb_ctx_set_res_normal(czb_ctx* c, double res_normal);  /* default 1/inner cells */
+void czb_ctx_set_head(czb_ctx* c, const int head[3]);        /* global colouring offset */
+void czb_ctx_set_variant(czb_ctx* c, int variant);           /* 0 = auto (fused), 1 = baseline kernels */
+/* Multi-rank: NCCL communicator over the j-slab ring.  id = 128-byte ncclUniqueId made by
+ * czb_comm_unique_id on rank 0 and distributed by the caller (torch.distributed / MPI). */
+int czb_comm_unique_id(void* id128);
+int czb_ctx_comm_init(czb_ctx* c, int nranks, int rank, const void* id128);
+
+/* Fused solve loop.  solver/precond names follow CZ::setLS / setStrPre
+ * (cz_Evaluate.cpp:571-803): jacobi psor sor2sma pbicgstab pcr pcr_eda pcr_esa pcr_rb
+ * pcr_rb_esa pcr_j_esa.  X (in/out) and B are device or host pointers, (sz+2g)^3 REALs.
+ * hist (host, may be NULL) receives the normalised residual of each iteration
+ * (the reference's history file, cz_Poisson.cpp:71); *res the last residual.
+ * Returns the reference's iteration count: the converging iteration, itr_max+1 (stationary)
+ * or itr_max (pbicgstab) when not converged, 0 on breakdown / unknown solver. */
+int czb_solve(czb_ctx* c, const char* solver, const char* precond, CZB_REAL* X, CZB_REAL* B,
+              int itr_max, CZB_REAL omg, double* res, double* hist, int hist_len, double* flop);
+/* Wall-clock milliseconds (CUDA events on the solve stream) of the last czb_solve loop. */
+double czb_last_solve_ms(czb_ctx* c);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CZB200_H_ */

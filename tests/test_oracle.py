@@ -1,0 +1,100 @@
+"""CPU tests of the ORACLE (test infrastructure): pins the C++ restatement of the reference's
+Fortran kernels against every known answer the reference offers and against
+the committed golden histories produced by the reference's unmodified C++ driver."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_util as ou
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = json.load(open(os.path.join(HERE, "golden", "histories.json")))
+
+
+def _golden(real, n, solver, precond=None, coef=None):
+    for c in GOLDEN:
+        if (c["real"], c["n"], c["solver"], c["precond"]) == (real, n, solver, precond) and (coef is None or c["coef"] == coef):
+            return c
+    raise KeyError((real, n, solver, precond))
+
+
+def test_thomas_3x3_known_answer():
+    # reference example/tri/test1.cpp:25-31 : b=[2,4,-1] c=[3,-3] a=[4,3] d=[8,3,3] -> (1,2,3)
+    d = ou.load("f64")
+    n = C.c_int(3)
+    a = np.array([0.0, 4.0, 3.0]); b = np.array([2.0, 4.0, -1.0]); c = np.array([3.0, -3.0, 0.0])
+    rhs = np.array([8.0, 3.0, 3.0]); w = np.zeros(3)
+    d.tdma_0_(C.byref(n), ou.ptr(rhs), ou.ptr(a), ou.ptr(b), ou.ptr(c), ou.ptr(w))
+    np.testing.assert_allclose(rhs, [1.0, 2.0, 3.0], rtol=0, atol=1e-14)
+
+
+@pytest.mark.parametrize("real,tol", [("f32", 2e-5), ("f64", 1e-12)])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_pcr_line_linear_known_answer(real, tol, mode):
+    # reference example/tri/test3.cpp:37-50, test5.cpp:146-177: 1-D Laplace, N=23, Dirichlet
+    # -3 / 9 -> x_i = -3 + 0.5 i ; solved with the PCR line solver (2x2 and 4x4 last stage)
+    # and cross-checked with Thomas tdma_p (obsolete.f90:65-84).
+    d = ou.load(real); dt = np.float32 if real == "f32" else np.float64
+    n = 23
+    a = np.full(n, -0.5, dt); c = np.full(n, -0.5, dt); a[0] = 0; c[-1] = 0
+    rhs = np.zeros(n, dt); rhs[0] = 0.5 * -3.0; rhs[-1] = 0.5 * 9.0
+    x = np.zeros(n, dt)
+    nn, mm = C.c_int(n), C.c_int(mode)
+    d.oracle_pcr_line_(C.byref(nn), C.byref(mm), ou.ptr(a), ou.ptr(c), ou.ptr(rhs), ou.ptr(x))
+    exact = -3.0 + 0.5 * np.arange(1, n + 1)
+    np.testing.assert_allclose(x, exact, rtol=0, atol=tol * 10)
+    t = rhs.copy(); w = np.zeros(n, dt)
+    d.tdma_p_(C.byref(nn), ou.ptr(t), ou.ptr(a), ou.ptr(c), ou.ptr(w))
+    np.testing.assert_allclose(x, t, rtol=0, atol=tol * 10)
+
+
+def test_analytic_solution_error_is_discretisation_level():
+    # cz_Evaluate.cpp:550-563 "Error max" of converged runs: O(h^2), far below the field's O(1)
+    for c in GOLDEN:
+        if c["solver"] in ("sor2sma", "pbicgstab", "pcr_rb") and c["n"] == 32:
+            assert float(c["errmax"]) < 1.0e-3, c
+
+
+def test_memo_pcr_eda_same_iteration_count_as_pcr():
+    # reference doc/Memo.md:131-134
+    assert _golden("f32", 32, "pcr")["itr"] == _golden("f32", 32, "pcr_eda")["itr"]
+    assert _golden("f32", 32, "pcr")["history"] == _golden("f32", 32, "pcr_esa")["history"]
+
+
+CASES = [("f32", 32, "jacobi", None), ("f32", 32, "sor2sma", None), ("f32", 32, "psor", None),
+         ("f32", 32, "pcr_rb", None), ("f32", 32, "pcr_rb_esa", None), ("f32", 32, "pcr_j_esa", None),
+         ("f32", 32, "pcr", None), ("f32", 32, "pcr_eda", None),
+         ("f32", 32, "pbicgstab", "sor2sma"), ("f32", 32, "pbicgstab", "jacobi"), ("f32", 32, "pbicgstab", "none"),
+         ("f32", 32, "pbicgstab", "pcr_rb"),
+         ("f64", 32, "jacobi", None), ("f64", 32, "sor2sma", None), ("f64", 32, "pcr_rb", None),
+         ("f64", 32, "pbicgstab", "sor2sma")]
+
+
+@pytest.mark.parametrize("real,n,solver,precond", CASES)
+def test_python_loops_reproduce_reference_driver_history(real, n, solver, precond):
+    """tests/oracle_util.OracleCZ (Python restatement of cz_Poisson.cpp over the oracle kernels)
+    must print the same history as the reference's own driver did (tests/golden)."""
+    g = _golden(real, n, solver, precond)
+    o = ou.OracleCZ([n] * 3, real)
+    P, RHS = o.setup_laplace()
+    if solver == "pbicgstab":
+        itr, res, hist = o.pbicgstab(P, RHS, g["itr_max"], float(g["coef"]), precond)
+    else:
+        itr, res, hist = o.stationary(solver, P, RHS, g["itr_max"], float(g["coef"]))
+    assert itr == g["itr"]
+    assert ["%13.6e" % h for h in hist] == ["%13s" % h for h in g["history"]]
+
+
+def test_double_and_real_sum_modes_agree_to_float_rounding():
+    # ORACLE_SUM=real bounds the reference's own drift; here only the default
+    # (double accumulation) is exercised and must be independent of the thread count.
+    o = ou.OracleCZ([32] * 3, "f32")
+    X, B = ou.random_fields(o.shape, o.dt)
+    o.ac1 = o.dt(1.1)
+    r1 = C.c_double(0); Xa = X.copy(); o.sweep_rb(Xa, B, r1)
+    os.environ["OMP_NUM_THREADS"] = "3"
+    r2 = C.c_double(0); Xb = X.copy(); o.sweep_rb(Xb, B, r2)
+    assert np.array_equal(Xa, Xb) and r1.value == r2.value
