@@ -25,7 +25,7 @@ def load(real="f32"):
         raise RuntimeError(
             "cubez_b200: %s is missing -- build it with `make -C cubez_b200/csrc` "
             "(or __graft_entry__.build()). There is no CPU/PyTorch fallback." % path)
-    dll = C.CDLL(path, mode=C.RTLD_GLOBAL)
+    dll = C.CDLL(path, mode=C.RTLD_LOCAL)
     ffi.bind_reference_symbols(dll)
     ffi.bind_czb_symbols(dll, C.c_float if real == "f32" else C.c_double)
     assert dll.czb_real_bytes() == (4 if real == "f32" else 8)
