@@ -1,4 +1,481 @@
-// cubez_b200/csrc/fused.cu -- bandwidth-optimised fused kernels (filled in after the baseline
-// kernels are parity-green on the GPU).
+// cubez_b200/csrc/fused.cu -- bandwidth-optimised plane-marching kernels (sm_100a).
+//
+// One CTA owns a (k,i) tile of the cube and marches along j (the slowest axis).  Every j-plane
+// of the tile (+2 halo cells per side) is fetched ONCE by a TMA tiled load
+// (cp.async.bulk.tensor.3d -> UTMALDG) into a ring of shared-memory slots, several planes
+// ahead of the compute; completion is tracked with mbarriers.  Each thread owns CPT
+// "pair columns" (two k-adjacent cells, one red one black) whose last four planes live in
+// registers, so j-neighbours never touch memory again; in-plane neighbours come from a
+// de-interleaved (even-k / odd-k) shared copy of two planes, which makes every neighbour read
+// stride-1 across the warp (no bank conflicts).
+//
+//   MODE_RB2 : BOTH colours of one red-black SOR iteration (2 x psor2sma_core,
+//              cz_solver.f90:404-493) in ONE pass over memory: at step s the CTA relaxes the
+//              red cells of plane s+1 and then the black cells of plane s (which need the new
+//              reds of planes s-1, s, s+1).  Reds of the 1-cell ring around the tile and of the
+//              planes next to the j-chunk are recomputed redundantly, so CTAs never exchange
+//              data; results go to a second array (ping-pong), which removes the in-place
+//              hazard.  HBM traffic: read p, read b, write p = 12 B/cell.iteration (float)
+//              against 24 B for two in-place stride-2 passes.
+//   MODE_JAC : relaxed Jacobi sweep (cz_solver.f90:284-387) without the copy-back pass.
+//   MODE_AX  : 7-point operator ap = ss - dd*p (cz_blas.f90:579-644) fused with (ap, w).
+//
+// Arithmetic is the reference's, operation for operation (see kernels.cu), so every cell is
+// bit-identical to the baseline kernels and to the oracle.
 #include "kernels.cuh"
-namespace czb {}
+#include <cuda.h>
+#include <map>
+#include <tuple>
+
+namespace czb {
+
+namespace {
+
+enum { MODE_RB2 = 0, MODE_JAC = 1, MODE_AX = 2 };
+
+constexpr int PR = 64;          // pairs per tile row  -> box width EKB = 128 cells
+constexpr int EKB = 2 * PR;
+constexpr int CPT = 4;          // pair columns per thread
+constexpr int NSP = 3;          // raw TMA slots for p  (planes s+2, s+3, s+4)
+constexpr int NSB = 3;          // raw TMA slots for b  (planes s+1, s+2, s+3)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// Bounded wait: a lost TMA must abort the kernel, never hang the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (ok) return;
+  }
+  __trap();
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
+struct Coef7 { REAL c1, c2, c3, c4, c5, c6, dd; };
+
+struct MarchArgs {
+  Geo G;
+  int ei;                 // tile rows (box height); owned rows = ei - 4
+  int ntk, nti, njc;      // tiles along k, i and chunks along j
+  int jl;                 // planes per j-chunk
+  int jr0, jr1;           // planes on which reds are relaxed (Fortran j)
+  int jb0, jb1;           // owned planes (blacks relaxed, results stored, residual counted)
+  int ip;                 // colour offset: cell is red iff (k-kst + i + j + ip) is even
+  Coef7 c; REAL omg;
+  REAL* out;              // MODE_RB2/JAC: new field ; MODE_AX: ap
+  const REAL* w;          // MODE_AX: dot operand (may be null)
+  const LoopState* st;
+  LoopState* acc_st; int slot; int add;
+  RedBuf rb;
+};
+
+struct FinStoreF {
+  LoopState* st; int slot; int add;
+  __device__ void operator()(double (&tot)[1]) const {
+    if (st) st->acc[slot] = (add ? st->acc[slot] : 0.0) + tot[0];
+  }
+};
+
+// One relaxation, exactly cz_solver.f90:339-347.  UNIT: all six off-diagonal coefficients are
+// 1.0 (the CubeZ problem, cz.h:169-172); 1.0*x == x bit for bit, so the products are skipped.
+template <bool UNIT>
+__device__ __forceinline__ REAL relax(const Coef7& c, REAL omg, REAL pp, REAL bb, REAL ie, REAL iw, REAL jn, REAL js,
+                                      REAL kt, REAL kb, REAL& dp) {
+  REAL ss;
+  if (UNIT) ss = ie + iw + jn + js + kt + kb;
+  else ss = c.c1 * ie + c.c2 * iw + c.c3 * jn + c.c4 * js + c.c5 * kt + c.c6 * kb;
+  dp = ((ss - bb) / c.dd - pp) * omg;
+  return pp + dp;
+}
+template <bool UNIT>
+__device__ __forceinline__ REAL apply_ax(const Coef7& c, REAL pp, REAL ie, REAL iw, REAL jn, REAL js, REAL kt, REAL kb) {
+  REAL ss;
+  if (UNIT) ss = ie + iw + jn + js + kt + kb;
+  else ss = c.c1 * ie + c.c2 * iw + c.c3 * jn + c.c4 * js + c.c5 * kt + c.c6 * kb;
+  return ss - c.dd * pp;
+}
+
+struct R2 { REAL x, y; };   // a pair column value: x = even-k cell (A), y = odd-k cell (B)
+
+__device__ __forceinline__ R2 lds2(const REAL* p) {
+#ifdef _REAL_IS_DOUBLE_
+  double2 v = *reinterpret_cast<const double2*>(p); return R2{v.x, v.y};
+#else
+  float2 v = *reinterpret_cast<const float2*>(p); return R2{v.x, v.y};
+#endif
+}
+__device__ __forceinline__ void stg2(REAL* p, R2 v) {
+#ifdef _REAL_IS_DOUBLE_
+  *reinterpret_cast<double2*>(p) = make_double2(v.x, v.y);
+#else
+  *reinterpret_cast<float2*>(p) = make_float2(v.x, v.y);
+#endif
+}
+
+// Per-column constant data.
+struct Col {
+  int eraw;      // offset of the pair in a raw (interleaved) tile slot
+  int ed;        // offset of the pair in a de-interleaved half plane
+  int gcol;      // element offset of cell A inside a j-plane of the global array (-1: outside)
+  unsigned fl;   // bit0/1 red-ok A/B, bit2/3 owned A/B, bit4 store pair, bit5 parity of A
+};
+
+template <int MODE, int NT, bool UNIT>
+__global__ void __launch_bounds__(NT, 1)
+k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b, const MarchArgs a) {
+  if (a.st && a.st->done) return;
+  constexpr int RP = NT / PR;              // tile rows covered by one pass of the CTA
+  const Geo& G = a.G;
+  const int EI = a.ei;
+  const int T = EI * EKB;                  // cells per tile plane
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  REAL* raw_p = reinterpret_cast<REAL*>(smem_raw);                 // [NSP][T]
+  REAL* raw_b = raw_p + (size_t)NSP * T;                           // [NSB][T]   (RB2/JAC only)
+  REAL* dei = raw_b + (size_t)(MODE == MODE_AX ? 0 : NSB) * T;     // [3][2][T/2]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(dei + 3 * (size_t)T);   // [NSP + NSB]
+  const int tid = threadIdx.x;
+
+  // ---- tile / chunk geometry ------------------------------------------------------------
+  const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk, jc = blockIdx.y;
+  const int kst_c = G.kst + G.g - 1, ist_c = G.ist + G.g - 1;     // C offsets of the first inner cell
+  const int P0 = (kst_c >> 1) - 1 + tk * (PR - 2);                 // first (halo) pair of the box
+  const int R0 = ist_c - 2 + ti * (EI - 4);                        // first (halo) row of the box
+  const int ja = a.jb0 + jc * a.jl;                                // owned planes of this chunk
+  const int jb = min(ja + a.jl - 1, a.jb1);
+  const int pl0 = (MODE == MODE_RB2) ? ja - 2 : ja - 1;            // first p plane fetched
+  const int bpl0 = (MODE == MODE_RB2) ? ja - 1 : ja;               // first b plane fetched
+  const int nsteps = (MODE == MODE_RB2) ? (jb - ja + 3) : (jb - ja + 1);
+  const int npl = nsteps + 2;                                      // p planes fetched
+  const int nbpl = nsteps;                                         // b planes fetched
+  const uint32_t tile_bytes = (uint32_t)T * sizeof(REAL);
+
+  if (tid == 0) {
+    for (int s = 0; s < NSP + NSB; ++s) mbar_init(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  auto issue_p = [&](int t) {   // plane pl0+t -> slot t % NSP
+    uint64_t* bar = &bars[t % NSP];
+    mbar_expect_tx(bar, tile_bytes);
+    tma_load_3d(raw_p + (size_t)(t % NSP) * T, &tm_p, bar, 2 * P0, R0, pl0 + t + G.g - 1);
+  };
+  auto issue_b = [&](int t) {
+    uint64_t* bar = &bars[NSP + t % NSB];
+    mbar_expect_tx(bar, tile_bytes);
+    tma_load_3d(raw_b + (size_t)(t % NSB) * T, &tm_b, bar, 2 * P0, R0, bpl0 + t + G.g - 1);
+  };
+  if (tid == 0) {
+    for (int t = 0; t < NSP && t < npl; ++t) issue_p(t);
+    if (MODE != MODE_AX) for (int t = 0; t < NSB && t < nbpl; ++t) issue_b(t);
+  }
+
+  // ---- per-column constants -----------------------------------------------------------------
+  Col col[CPT];
+  const int q = tid % PR;
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) {
+    const int r = tid / PR + RP * m;
+    Col c; c.eraw = r * EKB + 2 * q; c.ed = r * PR + q; c.fl = 0; c.gcol = -1;
+    const int kcA = 2 * (P0 + q), ic = R0 + r;
+    if (r < EI && ic < G.ni && kcA + 1 < G.nk) {
+      const int iF = ic - G.g + 1, kFA = kcA - G.g + 1, kFB = kFA + 1;
+      const bool rowin = (iF >= G.ist && iF <= G.ied);
+      const bool inA = rowin && kFA >= G.kst && kFA <= G.ked, inB = rowin && kFB >= G.kst && kFB <= G.ked;
+      const int dr = min(r, EI - 1 - r);
+      const int dq = min(q, PR - 1 - q);          // 0: halo pair
+      const bool ring1 = (dr >= 1) && (dq >= 1 || false);
+      // cell-level k distance to the box edge: A of pair q has 2q cells on its left, B has 2q+1
+      const bool redA = inA && dr >= 1 && q >= 1;                     // needs k-1 inside the box
+      const bool redB = inB && dr >= 1 && q <= PR - 2;                // needs k+1 inside the box
+      const bool own = (dr >= 2) && (dq >= 1);
+      (void)ring1;
+      c.fl = (redA ? 1u : 0u) | (redB ? 2u : 0u) | ((own && inA) ? 4u : 0u) | ((own && inB) ? 8u : 0u) |
+             ((own && (inA || inB)) ? 16u : 0u) | ((((kFA - G.kst + iF + a.ip) & 1) != 0) ? 32u : 0u);
+      c.gcol = kcA + G.nk * ic;
+    }
+    col[m] = c;
+  }
+
+  R2 cm1[CPT], c0[CPT], c1[CPT], c2[CPT], bprev[CPT], bcur[CPT];
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) { cm1[m] = c0[m] = c1[m] = c2[m] = bprev[m] = bcur[m] = R2{(REAL)0, (REAL)0}; }
+  double acc[1] = {0.0};
+  const int HP = T / 2;   // cells per de-interleaved half plane
+
+  // ---- prologue: planes pl0 (-> c0) and pl0+1 (-> c1 + de-interleaved copy) --------------------
+  mbar_wait(&bars[0], 0);
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) if (tid / PR + RP * m < EI) c0[m] = lds2(raw_p + col[m].eraw);
+  mbar_wait(&bars[1 % NSP], 0);
+  {
+    REAL* E = dei + (size_t)1 * T;   // plane pl0+1 <-> ring index (u+1)%3 at u = 0
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) if (tid / PR + RP * m < EI) {
+      c1[m] = lds2(raw_p + (size_t)1 * T + col[m].eraw);
+      E[col[m].ed] = c1[m].x; E[HP + col[m].ed] = c1[m].y;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) { if (NSP < npl) issue_p(NSP); if (NSP + 1 < npl) issue_p(NSP + 1); }
+
+  // ---- main loop ----------------------------------------------------------------------------------
+  for (int u = 0; u < nsteps; ++u) {
+    const int s = pl0 + u;                 // RB2: blacks of plane s, reds of s+1 ; JAC/AX: plane s+1
+    const int tp = u + 2;                  // p plane index arriving as c2
+    mbar_wait(&bars[tp % NSP], (tp / NSP) & 1);
+    REAL* E2 = dei + (size_t)((u + 2) % 3) * T;   // planes s+2, s+1, s (ring of three)
+    REAL* E1 = dei + (size_t)((u + 1) % 3) * T;
+    REAL* E0 = dei + (size_t)(u % 3) * T;
+    const REAL* rp = raw_p + (size_t)(tp % NSP) * T;
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) if (tid / PR + RP * m < EI) {
+      c2[m] = lds2(rp + col[m].eraw);
+      E2[col[m].ed] = c2[m].x; E2[HP + col[m].ed] = c2[m].y;
+    }
+    if (MODE != MODE_AX) {
+      mbar_wait(&bars[NSP + u % NSB], (u / NSB) & 1);
+      const REAL* rbp = raw_b + (size_t)(u % NSB) * T;
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) if (tid / PR + RP * m < EI) bcur[m] = lds2(rbp + col[m].eraw);
+    }
+    const long long gpl1 = (long long)(s + 1 + G.g - 1) * G.plane;   // global offset of plane s+1
+    const long long gpl0 = (long long)(s + G.g - 1) * G.plane;       // global offset of plane s
+
+    if (MODE == MODE_RB2) {
+      const bool do_red = (s + 1 >= a.jr0 && s + 1 <= a.jr1);
+      const bool red_owned = (s + 1 >= ja && s + 1 <= jb);
+      const bool do_black = (s >= ja && s <= jb);
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) {
+        const unsigned fl = col[m].fl;
+        const int ed = col[m].ed;
+        // is A the red cell of plane s+1 ?  red iff (parA + j) even
+        const bool xa = ((((fl >> 5) & 1u) + (unsigned)(s + 1)) & 1u) == 0u;
+        if (xa) {
+          if (do_red && (fl & 1u)) {
+            REAL dp;
+            const REAL nv = relax<UNIT>(a.c, a.omg, c1[m].x, bcur[m].x, E1[ed + PR], E1[ed - PR], c2[m].x, c0[m].x,
+                                        c1[m].y, E1[HP + ed - 1], dp);
+            c1[m].x = nv; E1[ed] = nv;
+            if (red_owned && (fl & 4u)) acc[0] += (double)(dp * dp);
+          }
+          if (do_black && (fl & 4u)) {
+            REAL dp;
+            const REAL nv = relax<UNIT>(a.c, a.omg, c0[m].x, bprev[m].x, E0[ed + PR], E0[ed - PR], c1[m].x, cm1[m].x,
+                                        c0[m].y, E0[HP + ed - 1], dp);
+            c0[m].x = nv;
+            acc[0] += (double)(dp * dp);
+          }
+        } else {
+          if (do_red && (fl & 2u)) {
+            REAL dp;
+            const REAL nv = relax<UNIT>(a.c, a.omg, c1[m].y, bcur[m].y, E1[HP + ed + PR], E1[HP + ed - PR], c2[m].y,
+                                        c0[m].y, E1[ed + 1], c1[m].x, dp);
+            c1[m].y = nv; E1[HP + ed] = nv;
+            if (red_owned && (fl & 8u)) acc[0] += (double)(dp * dp);
+          }
+          if (do_black && (fl & 8u)) {
+            REAL dp;
+            const REAL nv = relax<UNIT>(a.c, a.omg, c0[m].y, bprev[m].y, E0[HP + ed + PR], E0[HP + ed - PR], c1[m].y,
+                                        cm1[m].y, E0[ed + 1], c0[m].x, dp);
+            c0[m].y = nv;
+            acc[0] += (double)(dp * dp);
+          }
+        }
+        if (do_black && (fl & 16u)) stg2(a.out + gpl0 + col[m].gcol, c0[m]);
+      }
+    } else {
+      // Jacobi / operator: plane s+1, both cells of the pair, old values only
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) {
+        const unsigned fl = col[m].fl;
+        const int ed = col[m].ed;
+        if (fl & 16u) {
+          R2 o = c1[m];
+          if (MODE == MODE_JAC) {
+            REAL dp;
+            if (fl & 4u) {
+              o.x = relax<UNIT>(a.c, a.omg, c1[m].x, bcur[m].x, E1[ed + PR], E1[ed - PR], c2[m].x, c0[m].x, c1[m].y,
+                                E1[HP + ed - 1], dp);
+              acc[0] += (double)(dp * dp);
+            }
+            if (fl & 8u) {
+              o.y = relax<UNIT>(a.c, a.omg, c1[m].y, bcur[m].y, E1[HP + ed + PR], E1[HP + ed - PR], c2[m].y, c0[m].y,
+                                E1[ed + 1], c1[m].x, dp);
+              acc[0] += (double)(dp * dp);
+            }
+            stg2(a.out + gpl1 + col[m].gcol, o);
+          } else {
+            // MODE_AX (solver-internal): non-inner cells of a stored pair are boundary nodes of
+            // q / t_, which the reference leaves at their initial 0 (blas_clear / zero-filled
+            // allocation) -> store 0 there.
+            R2 v{(REAL)0, (REAL)0};
+            R2 wv{(REAL)0, (REAL)0};
+            if (a.w) wv = lds2(a.w + gpl1 + col[m].gcol);
+            if (fl & 4u) {
+              v.x = apply_ax<UNIT>(a.c, c1[m].x, E1[ed + PR], E1[ed - PR], c2[m].x, c0[m].x, c1[m].y, E1[HP + ed - 1]);
+              if (a.w) acc[0] += (double)(v.x * wv.x);
+            }
+            if (fl & 8u) {
+              v.y = apply_ax<UNIT>(a.c, c1[m].y, E1[HP + ed + PR], E1[HP + ed - PR], c2[m].y, c0[m].y, E1[ed + 1], c1[m].x);
+              if (a.w) acc[0] += (double)(v.y * wv.y);
+            }
+            stg2(a.out + gpl1 + col[m].gcol, v);
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      if (tp + NSP < npl) issue_p(tp + NSP);
+      if (MODE != MODE_AX && u + NSB < nbpl) issue_b(u + NSB);
+    }
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) { cm1[m] = c0[m]; c0[m] = c1[m]; c1[m] = c2[m]; bprev[m] = bcur[m]; }
+  }
+  grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
+}
+
+}  // namespace
+
+// ============================================================================ host side
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    CZB_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+    if (!p || qres != cudaDriverEntryPointSuccess) { fprintf(stderr, "czb200: cuTensorMapEncodeTiled unavailable\n"); abort(); }
+    fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+typedef std::tuple<const void*, int, int, int, int> TmKey;
+std::map<TmKey, CUtensorMap> g_tmaps;
+
+const CUtensorMap& tmap_for(const REAL* base, const Geo& G, int ei) {
+  TmKey key(base, G.nk, G.ni, G.nj, ei);
+  auto it = g_tmaps.find(key);
+  if (it != g_tmaps.end()) return it->second;
+  CUtensorMap tm;
+  cuuint64_t gdim[3] = {(cuuint64_t)G.nk, (cuuint64_t)G.ni, (cuuint64_t)G.nj};
+  cuuint64_t gstr[2] = {(cuuint64_t)G.nk * sizeof(REAL), (cuuint64_t)G.plane * sizeof(REAL)};
+  cuuint32_t box[3] = {(cuuint32_t)EKB, (cuuint32_t)ei, 1u};
+  cuuint32_t estr[3] = {1u, 1u, 1u};
+  CUresult r = encode_fn()(&tm, sizeof(REAL) == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3,
+                           (void*)base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { fprintf(stderr, "czb200: cuTensorMapEncodeTiled failed (%d)\n", (int)r); abort(); }
+  if (g_tmaps.size() > 256) g_tmaps.clear();
+  return g_tmaps.emplace(key, tm).first->second;
+}
+
+template <int MODE, int NT>
+void launch_march_t(const Launch& L, const MarchArgs& a, const CUtensorMap& tp, const CUtensorMap& tb, bool unit, size_t smem) {
+  dim3 grid(a.ntk * a.nti, a.njc, 1);
+  if (unit) {
+    static bool set = false;
+    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+    k_march<MODE, NT, true><<<grid, NT, smem, L.s>>>(tp, tb, a);
+  } else {
+    static bool set = false;
+    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+    k_march<MODE, NT, false><<<grid, NT, smem, L.s>>>(tp, tb, a);
+  }
+  CZB_CHECK(cudaGetLastError());
+  count_launch();
+}
+
+#ifdef _REAL_IS_DOUBLE_
+constexpr int NT_MARCH = 256;   // 128x16 tiles of doubles: 9 x 16 KB of shared memory
+#else
+constexpr int NT_MARCH = 512;   // 128x32 tiles of floats:  9 x 16 KB of shared memory
+#endif
+
+bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_or_w, REAL* out, const REAL* cf,
+           REAL omg, int ip, int jr0, int jr1, int slot, bool add) {
+  if (!fused_eligible(G)) return false;
+  MarchArgs a;
+  a.G = G;
+  a.ei = (NT_MARCH / PR) * CPT;
+  const int kst_c = G.kst + G.g - 1, ked_c = G.ked + G.g - 1;
+  const int npairs = (ked_c >> 1) - (kst_c >> 1) + 1;
+  a.ntk = (npairs + PR - 3) / (PR - 2);
+  const int ni = G.ied - G.ist + 1, nj = G.jed - G.jst + 1;
+  a.nti = (ni + a.ei - 5) / (a.ei - 4);
+  // j-chunks: enough CTAs for ~8 rounds over the SMs, chunks no shorter than 32 planes
+  int njc = (148 * 8 + a.ntk * a.nti - 1) / (a.ntk * a.nti);
+  if (njc > (nj + 31) / 32) njc = (nj + 31) / 32;
+  if (njc < 1) njc = 1;
+  a.jl = (nj + njc - 1) / njc;
+  a.njc = (nj + a.jl - 1) / a.jl;
+  if ((size_t)a.ntk * a.nti * a.njc > L.rb_blocks) return false;
+  a.jr0 = jr0; a.jr1 = jr1; a.jb0 = G.jst; a.jb1 = G.jed;
+  a.ip = ip;
+  a.c = Coef7{cf[0], cf[1], cf[2], cf[3], cf[4], cf[5], cf[6]};
+  a.omg = omg;
+  a.out = out; a.w = (mode == MODE_AX) ? b_or_w : nullptr;
+  a.st = L.st; a.acc_st = L.acc_st; a.slot = slot; a.add = add ? 1 : 0;
+  a.rb = L.rb;
+  const bool unit = cf[0] == (REAL)1 && cf[1] == (REAL)1 && cf[2] == (REAL)1 && cf[3] == (REAL)1 && cf[4] == (REAL)1 &&
+                    cf[5] == (REAL)1;
+  const size_t T = (size_t)a.ei * EKB;
+  const CUtensorMap& tp = tmap_for(p, G, a.ei);
+  const CUtensorMap& tb = (mode == MODE_AX) ? tp : tmap_for(b_or_w, G, a.ei);
+  const size_t smem = ((mode == MODE_AX ? NSP : NSP + NSB) + 3) * T * sizeof(REAL) + 8 * (NSP + NSB);
+  if (mode == MODE_RB2)      launch_march_t<MODE_RB2, NT_MARCH>(L, a, tp, tb, unit, smem);
+  else if (mode == MODE_JAC) launch_march_t<MODE_JAC, NT_MARCH>(L, a, tp, tb, unit, smem);
+  else                       launch_march_t<MODE_AX, NT_MARCH>(L, a, tp, tb, unit, smem);
+  return true;
+}
+
+}  // namespace
+
+bool fused_eligible(const Geo& G) {
+  // TMA needs 16-byte row pitch; pair columns need an even row length
+  if (((size_t)G.nk * sizeof(REAL)) % 16 != 0 || (G.nk & 1)) return false;
+  if (G.g < 2) return false;
+  if (G.ked < G.kst || G.ied < G.ist || G.jed < G.jst) return false;
+  return true;
+}
+
+bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf, REAL omg,
+                      int ip, int jr0, int jr1, int slot, bool add) {
+  return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add);
+}
+bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
+                         REAL omg, int slot, bool add) {
+  return march(MODE_JAC, L, G, p, b, pnew, cf, omg, 0, G.jst, G.jed, slot, add);
+}
+bool launch_ax_fused(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf, const REAL* dotwith,
+                     int slot) {
+  return march(MODE_AX, L, G, p, dotwith, ap, cf, (REAL)0, 0, G.jst, G.jed, slot, false);
+}
+
+}  // namespace czb

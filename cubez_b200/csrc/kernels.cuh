@@ -68,6 +68,19 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
                       const REAL* x, REAL* dst, const REAL* msk, const REAL* rhs, REAL omg, int slot,
                       bool add);
 
+// ---- fused TMA-staged marching kernels (fused.cu); return false when the geometry is not
+// eligible (row pitch not a multiple of 16 B) and the caller must use the baseline kernels ----
+bool fused_eligible(const Geo& G);
+// both colours of one red-black SOR iteration, p -> pnew (ping-pong). Reds are relaxed on planes
+// jr0..jr1 (includes halo planes owned by a neighbour rank), blacks/stores on jst..jed.
+bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
+                      REAL omg, int ip, int jr0, int jr1, int slot, bool add);
+bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
+                         REAL omg, int slot, bool add);
+// ap = A p on inner cells, 0 on the other cells of stored pairs; acc[slot] = (ap, dotwith)
+bool launch_ax_fused(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf, const REAL* dotwith,
+                     int slot);
+
 // ---- loop control (tiny kernels) --------------------------------------------------------
 void launch_state_reset(const Launch& L, LoopState* st);
 // res = sqrt(acc[slot]*res_normal); hist[itr] = res; ++itr; done |= res < eps

@@ -169,7 +169,8 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     REAL* src = (it & 1) ? X : W;
     REAL* dst = (it & 1) ? W : X;
     Launch L = launch();
-    launch_jacobi(L, G, src, dst, B, cf, ac1, rs, false);
+    if (!(variant == 0 && launch_jacobi_fused(L, G, src, dst, B, cf, ac1, rs, false)))
+      launch_jacobi(L, G, src, dst, B, cf, ac1, rs, false);
     Comm_S(dst, 1);
     if (converge_check) {
       Comm_SUM(0);
@@ -216,21 +217,55 @@ int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool
 int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check) {
   const int ip = parity_ip();
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
-  auto body = [&](int) {
-    Launch L = launch();
-    for (int color = 0; color < 2; ++color) {
-      launch_rb_color(L, G, X, B, cf, ac1, ip + color, rs, color == 1);
-      Comm_S(X, 1);
-    }
-    if (converge_check) {
-      Comm_SUM(0);
-      launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, X, pitch, origin, nID);
-    }
-  };
+  const bool fused = (variant == 0) && fused_eligible(G);
   int itr, done_iters;
-  if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
-  else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+  if (fused) {
+    // Both colours in one pass (fused.cu MODE_RB2), ping-pong between X and WRK.  Multi-rank: one
+    // exchange of TWO planes per iteration; the reds of the neighbour's edge plane are recomputed
+    // locally from them, which keeps the result equal to the single-domain one.
+    Runtime& R = rt();
+    REAL* W = field(WRK);
+    if (converge_check) {
+      Comm_S(X, 2);
+      CZB_CHECK(cudaMemcpyAsync(W, X, sizeof(REAL) * field_elems(), cudaMemcpyDeviceToDevice, R.stream));
+      wrk_guards_zero = false;
+    } else if (!wrk_guards_zero) {
+      CZB_CHECK(cudaMemsetAsync(W, 0, sizeof(REAL) * field_elems(), R.stream));
+      wrk_guards_zero = true;
+    }
+    Comm_S(B, 2);
+    const int jr0 = G.jst - (nID[2] >= 0 ? 1 : 0), jr1 = G.jed + (nID[3] >= 0 ? 1 : 0);
+    auto body = [&](int it) {
+      REAL* src = (it & 1) ? X : W;
+      REAL* dst = (it & 1) ? W : X;
+      Launch L = launch();
+      launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, rs, false);
+      Comm_S(dst, 2);
+      if (converge_check) {
+        Comm_SUM(0);
+        launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+        launch_bc_k(L, G, dst, pitch, origin, nID);
+      }
+    };
+    if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
+    else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+    if (done_iters & 1) launch_copy_inner(launch(false), G, X, W);
+  } else {
+    auto body = [&](int) {
+      Launch L = launch();
+      for (int color = 0; color < 2; ++color) {
+        launch_rb_color(L, G, X, B, cf, ac1, ip + color, rs, color == 1);
+        Comm_S(X, 1);
+      }
+      if (converge_check) {
+        Comm_SUM(0);
+        launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+        launch_bc_k(L, G, X, pitch, origin, nID);
+      }
+    };
+    if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
+    else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+  }
   flop += 18.0 * G.cells() * done_iters;
   return itr;
 }
@@ -393,12 +428,13 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
     Comm_S(p, 1);                                                            // :402
     CZB_CHECK(cudaMemsetAsync(p_, 0, bytes, R.stream));                      // :405
     Preconditioner(p_, p, pflop, pc_type);                                   // :409
-    launch_calc_ax(L, G, q, p_, cf, r0, 1); Comm_SUM(1); scalar(1);          // q = A p_, alpha :421-431
+    if (!(variant == 0 && launch_ax_fused(L, G, q, p_, cf, r0, 1))) launch_calc_ax(L, G, q, p_, cf, r0, 1);
+    Comm_SUM(1); scalar(1);          // q = A p_, alpha :421-431
     launch_triad(L, G, s, q, r, 0, &sc[SC_NEG_ALPHA]);                       // s = r - alpha q :434
     Comm_S(s, 1);                                                            // :438
     CZB_CHECK(cudaMemsetAsync(s_, 0, bytes, R.stream));                      // :441
     Preconditioner(s_, s, pflop, pc_type);                                   // :445
-    launch_calc_ax(L, G, t_, s_, cf, s, 2);                                  // t = A s_, (t,s) :457-464
+    if (!(variant == 0 && launch_ax_fused(L, G, t_, s_, cf, s, 2))) launch_calc_ax(L, G, t_, s_, cf, s, 2);   // t = A s_, (t,s) :457-464
     launch_dot1(L, G, t_, 3); Comm_SUM(2, 2); scalar(2);                     // (t,t), omega
     launch_bicg2(L, G, X, p_, s_, 0, 0, &sc[SC_ALPHA], &sc[SC_OMEGA]);       // x += alpha p_ + omega s_ :470
     launch_triad(L, G, r, t_, s, 0, &sc[SC_NEG_OMEGA]);                      // r = s - omega t :476
