@@ -131,27 +131,100 @@ __device__ __forceinline__ void stg2(REAL* p, R2 v) {
 #endif
 }
 
+// ---- shared-memory access with 32-bit addresses and immediate offsets ---------------------
+#ifdef _REAL_IS_DOUBLE_
+#define CZB_LD "ld.shared.f64"
+#define CZB_ST "st.shared.f64"
+#define CZB_LD2 "ld.shared.v2.f64"
+#define CZB_RC "d"
+#else
+#define CZB_LD "ld.shared.f32"
+#define CZB_ST "st.shared.f32"
+#define CZB_LD2 "ld.shared.v2.f32"
+#define CZB_RC "f"
+#endif
+template <int OFF>
+__device__ __forceinline__ REAL lds(uint32_t addr) {
+  REAL v;
+  asm volatile(CZB_LD " %0, [%1+%2];" : "=" CZB_RC(v) : "r"(addr), "n"(OFF) : "memory");
+  return v;
+}
+template <int OFF>
+__device__ __forceinline__ void sts(uint32_t addr, REAL v) {
+  asm volatile(CZB_ST " [%0+%1], %2;" ::"r"(addr), "n"(OFF), CZB_RC(v) : "memory");
+}
+__device__ __forceinline__ R2 lds_pair(uint32_t addr) {
+  R2 v;
+  asm volatile(CZB_LD2 " {%0, %1}, [%2];" : "=" CZB_RC(v.x), "=" CZB_RC(v.y) : "r"(addr) : "memory");
+  return v;
+}
+
+// (ss - bb)/dd.  DIVK: dd == 6 (the CubeZ operator).  a/6 is evaluated as q = a*y, r = fma(-6,q,a),
+// q' = fma(r,y,q) with y = RN(1/6): for float this was checked EXHAUSTIVELY against IEEE division
+// for every a with biased exponent in [27,247] (0 mismatches of 3.7e9; tests/test_div6.py keeps a
+// sampled version); zeros keep their sign; anything else (subnormal / huge / non-finite) takes
+// the IEEE division.  The IEEE sequence costs ~45 instructions when an operand is zero or
+// subnormal, which is the common case while the solution front is still spreading from the walls.
+template <bool DIVK>
+__device__ __forceinline__ REAL div_dd(REAL a, REAL dd) {
+  if (!DIVK) return a / dd;
+#ifdef _REAL_IS_DOUBLE_
+  const unsigned e = ((unsigned)__double2hiint(a) >> 20) & 0x7ffu;
+  if (e - 123u <= 1800u) {
+    const double y = 1.0 / 6.0;
+    const double q = a * y;
+    const double r = fma(-6.0, q, a);
+    return fma(r, y, q);
+  }
+  if (a == 0.0) return a;
+  return a / dd;
+#else
+  const unsigned e = (__float_as_uint(a) >> 23) & 0xffu;
+  if (e - 27u <= 220u) {
+    const float y = 1.0f / 6.0f;
+    const float q = a * y;
+    const float r = __fmaf_rn(-6.0f, q, a);
+    return __fmaf_rn(r, y, q);
+  }
+  if (a == 0.0f) return a;
+  return a / dd;
+#endif
+}
+
+template <bool UNIT>
+__device__ __forceinline__ REAL sum6(const Coef7& c, REAL ie, REAL iw, REAL jn, REAL js, REAL kt, REAL kb) {
+  // cz_solver.f90:339-344 order: i+1, i-1, j+1, j-1, k+1, k-1
+  if (UNIT) return ie + iw + jn + js + kt + kb;
+  return c.c1 * ie + c.c2 * iw + c.c3 * jn + c.c4 * js + c.c5 * kt + c.c6 * kb;
+}
+
 // Per-column constant data.
 struct Col {
-  int eraw;      // offset of the pair in a raw (interleaved) tile slot
-  int ed;        // offset of the pair in a de-interleaved half plane
-  int gcol;      // element offset of cell A inside a j-plane of the global array (-1: outside)
-  unsigned fl;   // bit0/1 red-ok A/B, bit2/3 owned A/B, bit4 store pair, bit5 parity of A
+  uint32_t araw;   // byte offset of the pair inside a raw (interleaved) tile slot
+  uint32_t ad;     // byte offset of the pair inside the even-k half of a de-interleaved plane
+  int gcol;        // element offset of cell A inside a j-plane of the global array
+  unsigned fl;     // bit0/1 red-ok A/B, bit2/3 owned A/B, bit4 store pair
 };
 
-template <int MODE, int NT, bool UNIT>
+template <int MODE, int NT, bool UNIT, bool DIVK>
 __global__ void __launch_bounds__(NT, 1)
 k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b, const MarchArgs a) {
   if (a.st && a.st->done) return;
   constexpr int RP = NT / PR;              // tile rows covered by one pass of the CTA
+  constexpr int EI = RP * CPT;             // tile rows
+  constexpr int T = EI * EKB;              // cells per tile plane
+  constexpr int SZ = (int)sizeof(REAL);
+  constexpr int TB = T * SZ;               // bytes per tile plane
+  constexpr int HPB = TB / 2;              // bytes per de-interleaved half plane (even-k, then odd-k)
+  constexpr int PRB = PR * SZ;             // bytes per row of a half plane
+  constexpr int NB = (MODE == MODE_AX) ? 0 : NSB;
   const Geo& G = a.G;
-  const int EI = a.ei;
-  const int T = EI * EKB;                  // cells per tile plane
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  REAL* raw_p = reinterpret_cast<REAL*>(smem_raw);                 // [NSP][T]
-  REAL* raw_b = raw_p + (size_t)NSP * T;                           // [NSB][T]   (RB2/JAC only)
-  REAL* dei = raw_b + (size_t)(MODE == MODE_AX ? 0 : NSB) * T;     // [3][2][T/2]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(dei + 3 * (size_t)T);   // [NSP + NSB]
+  const uint32_t sm0 = smem_u32(smem_raw);
+  const uint32_t raw_p = sm0;                          // [NSP][TB]
+  const uint32_t raw_b = raw_p + NSP * TB;             // [NB][TB]
+  const uint32_t dei = raw_b + NB * TB;                // [3][TB]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + (size_t)(NSP + NB + 3) * TB);   // [NSP + NSB]
   const int tid = threadIdx.x;
 
   // ---- tile / chunk geometry ------------------------------------------------------------
@@ -166,7 +239,6 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
   const int nsteps = (MODE == MODE_RB2) ? (jb - ja + 3) : (jb - ja + 1);
   const int npl = nsteps + 2;                                      // p planes fetched
   const int nbpl = nsteps;                                         // b planes fetched
-  const uint32_t tile_bytes = (uint32_t)T * sizeof(REAL);
 
   if (tid == 0) {
     for (int s = 0; s < NSP + NSB; ++s) mbar_init(&bars[s], 1);
@@ -175,13 +247,13 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
   __syncthreads();
   auto issue_p = [&](int t) {   // plane pl0+t -> slot t % NSP
     uint64_t* bar = &bars[t % NSP];
-    mbar_expect_tx(bar, tile_bytes);
-    tma_load_3d(raw_p + (size_t)(t % NSP) * T, &tm_p, bar, 2 * P0, R0, pl0 + t + G.g - 1);
+    mbar_expect_tx(bar, (uint32_t)TB);
+    tma_load_3d(smem_raw + (size_t)(t % NSP) * TB, &tm_p, bar, 2 * P0, R0, pl0 + t + G.g - 1);
   };
   auto issue_b = [&](int t) {
     uint64_t* bar = &bars[NSP + t % NSB];
-    mbar_expect_tx(bar, tile_bytes);
-    tma_load_3d(raw_b + (size_t)(t % NSB) * T, &tm_b, bar, 2 * P0, R0, bpl0 + t + G.g - 1);
+    mbar_expect_tx(bar, (uint32_t)TB);
+    tma_load_3d(smem_raw + (size_t)(NSP + t % NSB) * TB, &tm_b, bar, 2 * P0, R0, bpl0 + t + G.g - 1);
   };
   if (tid == 0) {
     for (int t = 0; t < NSP && t < npl; ++t) issue_p(t);
@@ -189,27 +261,28 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
   }
 
   // ---- per-column constants -----------------------------------------------------------------
+  // RP is even, so all CPT columns of a thread have the same row parity and therefore the same
+  // colour phase: `par` (parity of cell A at plane 0) is a per-thread (in fact per-warp) value.
   Col col[CPT];
   const int q = tid % PR;
+  const int kcA = 2 * (P0 + q);
+  const int kFA = kcA - G.g + 1;
+  const unsigned par = (unsigned)(kFA - G.kst + (R0 + tid / PR - G.g + 1) + a.ip) & 1u;
 #pragma unroll
   for (int m = 0; m < CPT; ++m) {
     const int r = tid / PR + RP * m;
-    Col c; c.eraw = r * EKB + 2 * q; c.ed = r * PR + q; c.fl = 0; c.gcol = -1;
-    const int kcA = 2 * (P0 + q), ic = R0 + r;
-    if (r < EI && ic < G.ni && kcA + 1 < G.nk) {
-      const int iF = ic - G.g + 1, kFA = kcA - G.g + 1, kFB = kFA + 1;
+    Col c; c.araw = (uint32_t)(r * EKB + 2 * q) * SZ; c.ad = (uint32_t)(r * PR + q) * SZ; c.fl = 0; c.gcol = 0;
+    const int ic = R0 + r;
+    if (ic < G.ni && kcA + 1 < G.nk) {
+      const int iF = ic - G.g + 1, kFB = kFA + 1;
       const bool rowin = (iF >= G.ist && iF <= G.ied);
       const bool inA = rowin && kFA >= G.kst && kFA <= G.ked, inB = rowin && kFB >= G.kst && kFB <= G.ked;
       const int dr = min(r, EI - 1 - r);
-      const int dq = min(q, PR - 1 - q);          // 0: halo pair
-      const bool ring1 = (dr >= 1) && (dq >= 1 || false);
-      // cell-level k distance to the box edge: A of pair q has 2q cells on its left, B has 2q+1
       const bool redA = inA && dr >= 1 && q >= 1;                     // needs k-1 inside the box
       const bool redB = inB && dr >= 1 && q <= PR - 2;                // needs k+1 inside the box
-      const bool own = (dr >= 2) && (dq >= 1);
-      (void)ring1;
+      const bool own = (dr >= 2) && (q >= 1) && (q <= PR - 2);
       c.fl = (redA ? 1u : 0u) | (redB ? 2u : 0u) | ((own && inA) ? 4u : 0u) | ((own && inB) ? 8u : 0u) |
-             ((own && (inA || inB)) ? 16u : 0u) | ((((kFA - G.kst + iF + a.ip) & 1) != 0) ? 32u : 0u);
+             ((own && (inA || inB)) ? 16u : 0u);
       c.gcol = kcA + G.nk * ic;
     }
     col[m] = c;
@@ -219,20 +292,18 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
 #pragma unroll
   for (int m = 0; m < CPT; ++m) { cm1[m] = c0[m] = c1[m] = c2[m] = bprev[m] = bcur[m] = R2{(REAL)0, (REAL)0}; }
   double acc[1] = {0.0};
-  const int HP = T / 2;   // cells per de-interleaved half plane
+  const Coef7 cf = a.c;
+  const REAL omg = a.omg;
 
-  // ---- prologue: planes pl0 (-> c0) and pl0+1 (-> c1 + de-interleaved copy) --------------------
+  // ---- prologue: planes pl0 (-> c0) and pl0+1 (-> c1 + de-interleaved copy in ring slot 1) -----
   mbar_wait(&bars[0], 0);
 #pragma unroll
-  for (int m = 0; m < CPT; ++m) if (tid / PR + RP * m < EI) c0[m] = lds2(raw_p + col[m].eraw);
-  mbar_wait(&bars[1 % NSP], 0);
-  {
-    REAL* E = dei + (size_t)1 * T;   // plane pl0+1 <-> ring index (u+1)%3 at u = 0
+  for (int m = 0; m < CPT; ++m) c0[m] = lds_pair(raw_p + col[m].araw);
+  mbar_wait(&bars[1], 0);
 #pragma unroll
-    for (int m = 0; m < CPT; ++m) if (tid / PR + RP * m < EI) {
-      c1[m] = lds2(raw_p + (size_t)1 * T + col[m].eraw);
-      E[col[m].ed] = c1[m].x; E[HP + col[m].ed] = c1[m].y;
-    }
+  for (int m = 0; m < CPT; ++m) {
+    c1[m] = lds_pair(raw_p + TB + col[m].araw);
+    sts<0>(dei + TB + col[m].ad, c1[m].x); sts<HPB>(dei + TB + col[m].ad, c1[m].y);
   }
   __syncthreads();
   if (tid == 0) { if (NSP < npl) issue_p(NSP); if (NSP + 1 < npl) issue_p(NSP + 1); }
@@ -241,103 +312,134 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
   for (int u = 0; u < nsteps; ++u) {
     const int s = pl0 + u;                 // RB2: blacks of plane s, reds of s+1 ; JAC/AX: plane s+1
     const int tp = u + 2;                  // p plane index arriving as c2
+    const uint32_t e2 = dei + (uint32_t)((u + 2) % 3) * TB;   // de-interleaved planes s+2, s+1, s
+    const uint32_t e1 = dei + (uint32_t)((u + 1) % 3) * TB;
+    const uint32_t e0 = dei + (uint32_t)(u % 3) * TB;
     mbar_wait(&bars[tp % NSP], (tp / NSP) & 1);
-    REAL* E2 = dei + (size_t)((u + 2) % 3) * T;   // planes s+2, s+1, s (ring of three)
-    REAL* E1 = dei + (size_t)((u + 1) % 3) * T;
-    REAL* E0 = dei + (size_t)(u % 3) * T;
-    const REAL* rp = raw_p + (size_t)(tp % NSP) * T;
+    {
+      const uint32_t rp = raw_p + (uint32_t)(tp % NSP) * TB;
 #pragma unroll
-    for (int m = 0; m < CPT; ++m) if (tid / PR + RP * m < EI) {
-      c2[m] = lds2(rp + col[m].eraw);
-      E2[col[m].ed] = c2[m].x; E2[HP + col[m].ed] = c2[m].y;
+      for (int m = 0; m < CPT; ++m) c2[m] = lds_pair(rp + col[m].araw);
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) { sts<0>(e2 + col[m].ad, c2[m].x); sts<HPB>(e2 + col[m].ad, c2[m].y); }
     }
     if (MODE != MODE_AX) {
       mbar_wait(&bars[NSP + u % NSB], (u / NSB) & 1);
-      const REAL* rbp = raw_b + (size_t)(u % NSB) * T;
+      const uint32_t rbp = raw_b + (uint32_t)(u % NSB) * TB;
 #pragma unroll
-      for (int m = 0; m < CPT; ++m) if (tid / PR + RP * m < EI) bcur[m] = lds2(rbp + col[m].eraw);
+      for (int m = 0; m < CPT; ++m) bcur[m] = lds_pair(rbp + col[m].araw);
     }
     const long long gpl1 = (long long)(s + 1 + G.g - 1) * G.plane;   // global offset of plane s+1
     const long long gpl0 = (long long)(s + G.g - 1) * G.plane;       // global offset of plane s
 
     if (MODE == MODE_RB2) {
-      const bool do_red = (s + 1 >= a.jr0 && s + 1 <= a.jr1);
+      const bool do_red = (s + 1 >= a.jr0 && s + 1 <= a.jr1);      // CTA-uniform
       const bool red_owned = (s + 1 >= ja && s + 1 <= jb);
       const bool do_black = (s >= ja && s <= jb);
+      // A is the red cell of plane s+1 iff (par + s + 1) is even  (warp-uniform)
+      const bool xa = ((par + (unsigned)(s + 1)) & 1u) == 0u;
+      REAL kn1[CPT], ie1[CPT], iw1[CPT], kn0[CPT], ie0[CPT], iw0[CPT];
+      if (xa) {
+        // in-plane neighbours of cell A: k-1 = odd half [q-1], k+1 = own B, i+-1 = even half rows r+-1
 #pragma unroll
-      for (int m = 0; m < CPT; ++m) {
-        const unsigned fl = col[m].fl;
-        const int ed = col[m].ed;
-        // is A the red cell of plane s+1 ?  red iff (parA + j) even
-        const bool xa = ((((fl >> 5) & 1u) + (unsigned)(s + 1)) & 1u) == 0u;
-        if (xa) {
-          if (do_red && (fl & 1u)) {
-            REAL dp;
-            const REAL nv = relax<UNIT>(a.c, a.omg, c1[m].x, bcur[m].x, E1[ed + PR], E1[ed - PR], c2[m].x, c0[m].x,
-                                        c1[m].y, E1[HP + ed - 1], dp);
-            c1[m].x = nv; E1[ed] = nv;
-            if (red_owned && (fl & 4u)) acc[0] += (double)(dp * dp);
+        for (int m = 0; m < CPT; ++m) {
+          const uint32_t a1 = e1 + col[m].ad, a0 = e0 + col[m].ad;
+          kn1[m] = lds<HPB - SZ>(a1); ie1[m] = lds<PRB>(a1); iw1[m] = lds<-PRB>(a1);
+          kn0[m] = lds<HPB - SZ>(a0); ie0[m] = lds<PRB>(a0); iw0[m] = lds<-PRB>(a0);
+        }
+#pragma unroll
+        for (int m = 0; m < CPT; ++m) {
+          const unsigned fl = col[m].fl;
+          if (do_red) {
+            const REAL pp = c1[m].x;
+            const REAL ss = sum6<UNIT>(cf, ie1[m], iw1[m], c2[m].x, c0[m].x, c1[m].y, kn1[m]);
+            const REAL dp = (div_dd<DIVK>(ss - bcur[m].x, cf.dd) - pp) * omg;
+            const bool ok = (fl & 1u) != 0u;
+            const REAL nv = ok ? pp + dp : pp;
+            c1[m].x = nv;
+            if (ok) sts<0>(e1 + col[m].ad, nv);
+            const REAL d2 = (ok && red_owned && (fl & 4u)) ? dp * dp : (REAL)0;
+            acc[0] += (double)d2;
           }
-          if (do_black && (fl & 4u)) {
-            REAL dp;
-            const REAL nv = relax<UNIT>(a.c, a.omg, c0[m].x, bprev[m].x, E0[ed + PR], E0[ed - PR], c1[m].x, cm1[m].x,
-                                        c0[m].y, E0[HP + ed - 1], dp);
-            c0[m].x = nv;
-            acc[0] += (double)(dp * dp);
-          }
-        } else {
-          if (do_red && (fl & 2u)) {
-            REAL dp;
-            const REAL nv = relax<UNIT>(a.c, a.omg, c1[m].y, bcur[m].y, E1[HP + ed + PR], E1[HP + ed - PR], c2[m].y,
-                                        c0[m].y, E1[ed + 1], c1[m].x, dp);
-            c1[m].y = nv; E1[HP + ed] = nv;
-            if (red_owned && (fl & 8u)) acc[0] += (double)(dp * dp);
-          }
-          if (do_black && (fl & 8u)) {
-            REAL dp;
-            const REAL nv = relax<UNIT>(a.c, a.omg, c0[m].y, bprev[m].y, E0[HP + ed + PR], E0[HP + ed - PR], c1[m].y,
-                                        cm1[m].y, E0[ed + 1], c0[m].x, dp);
-            c0[m].y = nv;
-            acc[0] += (double)(dp * dp);
+          if (do_black) {
+            const REAL pp = c0[m].x;
+            const REAL ss = sum6<UNIT>(cf, ie0[m], iw0[m], c1[m].x, cm1[m].x, c0[m].y, kn0[m]);
+            const REAL dp = (div_dd<DIVK>(ss - bprev[m].x, cf.dd) - pp) * omg;
+            const bool ok = (fl & 4u) != 0u;
+            c0[m].x = ok ? pp + dp : pp;
+            acc[0] += (double)(ok ? dp * dp : (REAL)0);
+            if (fl & 16u) stg2(a.out + gpl0 + col[m].gcol, c0[m]);
           }
         }
-        if (do_black && (fl & 16u)) stg2(a.out + gpl0 + col[m].gcol, c0[m]);
+      } else {
+        // cell B: k-1 = own A, k+1 = even half [q+1], i+-1 = odd half rows r+-1
+#pragma unroll
+        for (int m = 0; m < CPT; ++m) {
+          const uint32_t a1 = e1 + col[m].ad, a0 = e0 + col[m].ad;
+          kn1[m] = lds<SZ>(a1); ie1[m] = lds<HPB + PRB>(a1); iw1[m] = lds<HPB - PRB>(a1);
+          kn0[m] = lds<SZ>(a0); ie0[m] = lds<HPB + PRB>(a0); iw0[m] = lds<HPB - PRB>(a0);
+        }
+#pragma unroll
+        for (int m = 0; m < CPT; ++m) {
+          const unsigned fl = col[m].fl;
+          if (do_red) {
+            const REAL pp = c1[m].y;
+            const REAL ss = sum6<UNIT>(cf, ie1[m], iw1[m], c2[m].y, c0[m].y, kn1[m], c1[m].x);
+            const REAL dp = (div_dd<DIVK>(ss - bcur[m].y, cf.dd) - pp) * omg;
+            const bool ok = (fl & 2u) != 0u;
+            const REAL nv = ok ? pp + dp : pp;
+            c1[m].y = nv;
+            if (ok) sts<HPB>(e1 + col[m].ad, nv);
+            const REAL d2 = (ok && red_owned && (fl & 8u)) ? dp * dp : (REAL)0;
+            acc[0] += (double)d2;
+          }
+          if (do_black) {
+            const REAL pp = c0[m].y;
+            const REAL ss = sum6<UNIT>(cf, ie0[m], iw0[m], c1[m].y, cm1[m].y, kn0[m], c0[m].x);
+            const REAL dp = (div_dd<DIVK>(ss - bprev[m].y, cf.dd) - pp) * omg;
+            const bool ok = (fl & 8u) != 0u;
+            c0[m].y = ok ? pp + dp : pp;
+            acc[0] += (double)(ok ? dp * dp : (REAL)0);
+            if (fl & 16u) stg2(a.out + gpl0 + col[m].gcol, c0[m]);
+          }
+        }
       }
     } else {
       // Jacobi / operator: plane s+1, both cells of the pair, old values only
+      REAL kmA[CPT], ieA[CPT], iwA[CPT], ktB[CPT], ieB[CPT], iwB[CPT];
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) {
+        const uint32_t a1 = e1 + col[m].ad;
+        kmA[m] = lds<HPB - SZ>(a1); ieA[m] = lds<PRB>(a1); iwA[m] = lds<-PRB>(a1);
+        ktB[m] = lds<SZ>(a1); ieB[m] = lds<HPB + PRB>(a1); iwB[m] = lds<HPB - PRB>(a1);
+      }
 #pragma unroll
       for (int m = 0; m < CPT; ++m) {
         const unsigned fl = col[m].fl;
-        const int ed = col[m].ed;
-        if (fl & 16u) {
-          R2 o = c1[m];
-          if (MODE == MODE_JAC) {
-            REAL dp;
-            if (fl & 4u) {
-              o.x = relax<UNIT>(a.c, a.omg, c1[m].x, bcur[m].x, E1[ed + PR], E1[ed - PR], c2[m].x, c0[m].x, c1[m].y,
-                                E1[HP + ed - 1], dp);
-              acc[0] += (double)(dp * dp);
-            }
-            if (fl & 8u) {
-              o.y = relax<UNIT>(a.c, a.omg, c1[m].y, bcur[m].y, E1[HP + ed + PR], E1[HP + ed - PR], c2[m].y, c0[m].y,
-                                E1[ed + 1], c1[m].x, dp);
-              acc[0] += (double)(dp * dp);
-            }
-            stg2(a.out + gpl1 + col[m].gcol, o);
-          } else {
-            // MODE_AX (solver-internal): non-inner cells of a stored pair are boundary nodes of
-            // q / t_, which the reference leaves at their initial 0 (blas_clear / zero-filled
-            // allocation) -> store 0 there.
-            R2 v{(REAL)0, (REAL)0};
-            R2 wv{(REAL)0, (REAL)0};
-            if (a.w) wv = lds2(a.w + gpl1 + col[m].gcol);
-            if (fl & 4u) {
-              v.x = apply_ax<UNIT>(a.c, c1[m].x, E1[ed + PR], E1[ed - PR], c2[m].x, c0[m].x, c1[m].y, E1[HP + ed - 1]);
-              if (a.w) acc[0] += (double)(v.x * wv.x);
-            }
-            if (fl & 8u) {
-              v.y = apply_ax<UNIT>(a.c, c1[m].y, E1[HP + ed + PR], E1[HP + ed - PR], c2[m].y, c0[m].y, E1[ed + 1], c1[m].x);
-              if (a.w) acc[0] += (double)(v.y * wv.y);
+        const REAL ssA = sum6<UNIT>(cf, ieA[m], iwA[m], c2[m].x, c0[m].x, c1[m].y, kmA[m]);
+        const REAL ssB = sum6<UNIT>(cf, ieB[m], iwB[m], c2[m].y, c0[m].y, ktB[m], c1[m].x);
+        const bool okA = (fl & 4u) != 0u, okB = (fl & 8u) != 0u;
+        if (MODE == MODE_JAC) {
+          const REAL dpA = (div_dd<DIVK>(ssA - bcur[m].x, cf.dd) - c1[m].x) * omg;
+          const REAL dpB = (div_dd<DIVK>(ssB - bcur[m].y, cf.dd) - c1[m].y) * omg;
+          R2 o;
+          o.x = okA ? c1[m].x + dpA : c1[m].x;
+          o.y = okB ? c1[m].y + dpB : c1[m].y;
+          acc[0] += (double)(okA ? dpA * dpA : (REAL)0);
+          acc[0] += (double)(okB ? dpB * dpB : (REAL)0);
+          if (fl & 16u) stg2(a.out + gpl1 + col[m].gcol, o);
+        } else {
+          // MODE_AX (solver-internal): non-inner cells of a stored pair are boundary nodes of
+          // q / t_, which the reference leaves at their initial 0 (blas_clear / zero-filled
+          // allocation) -> store 0 there.
+          if (fl & 16u) {
+            R2 v;
+            v.x = okA ? ssA - cf.dd * c1[m].x : (REAL)0;
+            v.y = okB ? ssB - cf.dd * c1[m].y : (REAL)0;
+            if (a.w) {
+              const R2 wv = lds2(a.w + gpl1 + col[m].gcol);
+              acc[0] += (double)(okA ? v.x * wv.x : (REAL)0);
+              acc[0] += (double)(okB ? v.y * wv.y : (REAL)0);
             }
             stg2(a.out + gpl1 + col[m].gcol, v);
           }
@@ -397,16 +499,16 @@ const CUtensorMap& tmap_for(const REAL* base, const Geo& G, int ei) {
 }
 
 template <int MODE, int NT>
-void launch_march_t(const Launch& L, const MarchArgs& a, const CUtensorMap& tp, const CUtensorMap& tb, bool unit, size_t smem) {
+void launch_march_t(const Launch& L, const MarchArgs& a, const CUtensorMap& tp, const CUtensorMap& tb, bool fast, size_t smem) {
   dim3 grid(a.ntk * a.nti, a.njc, 1);
-  if (unit) {
+  if (fast) {   // unit off-diagonals and dd == 6: the CubeZ operator (cz.h:169-172)
     static bool set = false;
-    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
-    k_march<MODE, NT, true><<<grid, NT, smem, L.s>>>(tp, tb, a);
+    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+    k_march<MODE, NT, true, true><<<grid, NT, smem, L.s>>>(tp, tb, a);
   } else {
     static bool set = false;
-    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
-    k_march<MODE, NT, false><<<grid, NT, smem, L.s>>>(tp, tb, a);
+    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+    k_march<MODE, NT, false, false><<<grid, NT, smem, L.s>>>(tp, tb, a);
   }
   CZB_CHECK(cudaGetLastError());
   count_launch();
@@ -444,11 +546,12 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
   a.st = L.st; a.acc_st = L.acc_st; a.slot = slot; a.add = add ? 1 : 0;
   a.rb = L.rb;
   const bool unit = cf[0] == (REAL)1 && cf[1] == (REAL)1 && cf[2] == (REAL)1 && cf[3] == (REAL)1 && cf[4] == (REAL)1 &&
-                    cf[5] == (REAL)1;
+                    cf[5] == (REAL)1 && cf[6] == (REAL)6;
   const size_t T = (size_t)a.ei * EKB;
   const CUtensorMap& tp = tmap_for(p, G, a.ei);
   const CUtensorMap& tb = (mode == MODE_AX) ? tp : tmap_for(b_or_w, G, a.ei);
-  const size_t smem = ((mode == MODE_AX ? NSP : NSP + NSB) + 3) * T * sizeof(REAL) + 8 * (NSP + NSB);
+  // + 1 KB: halo columns read (and discard) neighbours up to one half-plane row past the last plane
+  const size_t smem = ((mode == MODE_AX ? NSP : NSP + NSB) + 3) * T * sizeof(REAL) + 8 * (NSP + NSB) + 1024;
   if (mode == MODE_RB2)      launch_march_t<MODE_RB2, NT_MARCH>(L, a, tp, tb, unit, smem);
   else if (mode == MODE_JAC) launch_march_t<MODE_JAC, NT_MARCH>(L, a, tp, tb, unit, smem);
   else                       launch_march_t<MODE_AX, NT_MARCH>(L, a, tp, tb, unit, smem);
