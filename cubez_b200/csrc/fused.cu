@@ -26,6 +26,7 @@
 #include <cuda.h>
 #include <map>
 #include <tuple>
+#include <type_traits>
 
 namespace czb {
 
@@ -165,30 +166,49 @@ __device__ __forceinline__ R2 lds_pair(uint32_t addr) {
 // sampled version); zeros keep their sign; anything else (subnormal / huge / non-finite) takes
 // the IEEE division.  The IEEE sequence costs ~45 instructions when an operand is zero or
 // subnormal, which is the common case while the solution front is still spreading from the walls.
+// Out-of-line IEEE division for the rare operands outside the guarded range; __noinline__ keeps
+// the compiler from speculating the ~45-instruction sequence onto the common path.
+__device__ __noinline__ REAL div_rare(REAL a, REAL dd) { return a / dd; }
+
+#ifdef _REAL_IS_DOUBLE_
+__device__ __forceinline__ bool div_guard_fail(double a) {
+  const unsigned e = ((unsigned)__double2hiint(a) >> 20) & 0x7ffu;
+  return (e - 123u > 1800u) && (a != 0.0);
+}
+#else
+__device__ __forceinline__ bool div_guard_fail(float a) {
+  const unsigned e = (__float_as_uint(a) >> 23) & 0xffu;
+  return (e - 27u > 220u) && (a != 0.0f);
+}
+#endif
+// Branch-free part: the fast quotient (exact inside the guard, and for +-0 after the select);
+// `rare` is OR-ed with "operand outside the guard" so that the caller can patch a whole group of
+// quotients behind ONE rarely taken branch (div_fix).
+template <bool DIVK>
+__device__ __forceinline__ REAL div_fast(REAL a, REAL dd, bool& rare) {
+  if (!DIVK) return a / dd;
+  const REAL y = (REAL)1.0 / (REAL)6.0;
+  const REAL q = a * y;
+#ifdef _REAL_IS_DOUBLE_
+  const REAL r = fma(-6.0, q, a);
+  REAL res = fma(r, y, q);
+#else
+  const REAL r = __fmaf_rn(-6.0f, q, a);
+  REAL res = __fmaf_rn(r, y, q);
+#endif
+  res = (a == (REAL)0) ? a : res;          // +-0 / 6 = +-0
+  rare = rare || div_guard_fail(a);
+  return res;
+}
+__device__ __forceinline__ REAL div_fix(REAL a, REAL q, REAL dd) {
+  return div_guard_fail(a) ? div_rare(a, dd) : q;
+}
 template <bool DIVK>
 __device__ __forceinline__ REAL div_dd(REAL a, REAL dd) {
-  if (!DIVK) return a / dd;
-#ifdef _REAL_IS_DOUBLE_
-  const unsigned e = ((unsigned)__double2hiint(a) >> 20) & 0x7ffu;
-  if (e - 123u <= 1800u) {
-    const double y = 1.0 / 6.0;
-    const double q = a * y;
-    const double r = fma(-6.0, q, a);
-    return fma(r, y, q);
-  }
-  if (a == 0.0) return a;
-  return a / dd;
-#else
-  const unsigned e = (__float_as_uint(a) >> 23) & 0xffu;
-  if (e - 27u <= 220u) {
-    const float y = 1.0f / 6.0f;
-    const float q = a * y;
-    const float r = __fmaf_rn(-6.0f, q, a);
-    return __fmaf_rn(r, y, q);
-  }
-  if (a == 0.0f) return a;
-  return a / dd;
-#endif
+  bool rare = false;
+  REAL q = div_fast<DIVK>(a, dd, rare);
+  if (DIVK && rare) q = div_rare(a, dd);
+  return q;
 }
 
 template <bool UNIT>
@@ -309,25 +329,28 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
   if (tid == 0) { if (NSP < npl) issue_p(NSP); if (NSP + 1 < npl) issue_p(NSP + 1); }
 
   // ---- main loop ----------------------------------------------------------------------------------
-  for (int u = 0; u < nsteps; ++u) {
+  // One step.  The four plane registers rotate roles every step; instead of moving 32 registers
+  // the step body is instantiated four times with the roles permuted (see the 4x unrolled loop).
+  int ring = 0;          // u % 3 : ring slot of de-interleaved plane s; raw b slot of this step
+  int phase = 0;         // (u / 3) & 1 : mbarrier parity of the b slot; p slot (u+2)%3 has parity pphase
+  auto step = [&](int u, R2 (&wm1)[CPT], R2 (&w0)[CPT], R2 (&w1)[CPT], R2 (&w2)[CPT], R2 (&bp)[CPT], R2 (&bc)[CPT]) {
     const int s = pl0 + u;                 // RB2: blacks of plane s, reds of s+1 ; JAC/AX: plane s+1
-    const int tp = u + 2;                  // p plane index arriving as c2
-    const uint32_t e2 = dei + (uint32_t)((u + 2) % 3) * TB;   // de-interleaved planes s+2, s+1, s
-    const uint32_t e1 = dei + (uint32_t)((u + 1) % 3) * TB;
-    const uint32_t e0 = dei + (uint32_t)(u % 3) * TB;
-    mbar_wait(&bars[tp % NSP], (tp / NSP) & 1);
+    const int r0 = ring, r1 = (ring == 2) ? 0 : ring + 1, r2 = (ring == 0) ? 2 : ring - 1;   // u%3, (u+1)%3, (u+2)%3
+    const uint32_t e0 = dei + (uint32_t)r0 * TB, e1 = dei + (uint32_t)r1 * TB, e2 = dei + (uint32_t)r2 * TB;
+    const int pphase = (ring == 0) ? phase : phase ^ 1;        // ((u+2)/3)&1
+    mbar_wait(&bars[r2], (uint32_t)pphase);
     {
-      const uint32_t rp = raw_p + (uint32_t)(tp % NSP) * TB;
+      const uint32_t rp = raw_p + (uint32_t)r2 * TB;
 #pragma unroll
-      for (int m = 0; m < CPT; ++m) c2[m] = lds_pair(rp + col[m].araw);
+      for (int m = 0; m < CPT; ++m) w2[m] = lds_pair(rp + col[m].araw);
 #pragma unroll
-      for (int m = 0; m < CPT; ++m) { sts<0>(e2 + col[m].ad, c2[m].x); sts<HPB>(e2 + col[m].ad, c2[m].y); }
+      for (int m = 0; m < CPT; ++m) { sts<0>(e2 + col[m].ad, w2[m].x); sts<HPB>(e2 + col[m].ad, w2[m].y); }
     }
     if (MODE != MODE_AX) {
-      mbar_wait(&bars[NSP + u % NSB], (u / NSB) & 1);
-      const uint32_t rbp = raw_b + (uint32_t)(u % NSB) * TB;
+      mbar_wait(&bars[NSP + r0], (uint32_t)phase);
+      const uint32_t rbp = raw_b + (uint32_t)r0 * TB;
 #pragma unroll
-      for (int m = 0; m < CPT; ++m) bcur[m] = lds_pair(rbp + col[m].araw);
+      for (int m = 0; m < CPT; ++m) bc[m] = lds_pair(rbp + col[m].araw);
     }
     const long long gpl1 = (long long)(s + 1 + G.g - 1) * G.plane;   // global offset of plane s+1
     const long long gpl0 = (long long)(s + G.g - 1) * G.plane;       // global offset of plane s
@@ -338,72 +361,78 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
       const bool do_black = (s >= ja && s <= jb);
       // A is the red cell of plane s+1 iff (par + s + 1) is even  (warp-uniform)
       const bool xa = ((par + (unsigned)(s + 1)) & 1u) == 0u;
-      REAL kn1[CPT], ie1[CPT], iw1[CPT], kn0[CPT], ie0[CPT], iw0[CPT];
-      if (xa) {
-        // in-plane neighbours of cell A: k-1 = odd half [q-1], k+1 = own B, i+-1 = even half rows r+-1
+      // One colour phase over the CPT columns of the thread, X = A (xb false) or B (xb true):
+      // straight-line code for all columns, a single rare branch for operands of the division
+      // outside its guarded range.
+      auto both = [&](auto xb) {
+        constexpr bool XB = decltype(xb)::value;
+        REAL kn1[CPT], ie1[CPT], iw1[CPT], kn0[CPT], ie0[CPT], iw0[CPT];
 #pragma unroll
         for (int m = 0; m < CPT; ++m) {
           const uint32_t a1 = e1 + col[m].ad, a0 = e0 + col[m].ad;
-          kn1[m] = lds<HPB - SZ>(a1); ie1[m] = lds<PRB>(a1); iw1[m] = lds<-PRB>(a1);
-          kn0[m] = lds<HPB - SZ>(a0); ie0[m] = lds<PRB>(a0); iw0[m] = lds<-PRB>(a0);
+          if (!XB) {   // cell A: k-1 = odd half [q-1], k+1 = own B, i+-1 = even half rows r+-1
+            kn1[m] = lds<HPB - SZ>(a1); ie1[m] = lds<PRB>(a1); iw1[m] = lds<-PRB>(a1);
+            kn0[m] = lds<HPB - SZ>(a0); ie0[m] = lds<PRB>(a0); iw0[m] = lds<-PRB>(a0);
+          } else {     // cell B: k-1 = own A, k+1 = even half [q+1], i+-1 = odd half rows r+-1
+            kn1[m] = lds<SZ>(a1); ie1[m] = lds<HPB + PRB>(a1); iw1[m] = lds<HPB - PRB>(a1);
+            kn0[m] = lds<SZ>(a0); ie0[m] = lds<HPB + PRB>(a0); iw0[m] = lds<HPB - PRB>(a0);
+          }
         }
+        if (do_red) {
+          REAL num[CPT], quo[CPT];
+          bool rare = false;
 #pragma unroll
-        for (int m = 0; m < CPT; ++m) {
-          const unsigned fl = col[m].fl;
-          if (do_red) {
-            const REAL pp = c1[m].x;
-            const REAL ss = sum6<UNIT>(cf, ie1[m], iw1[m], c2[m].x, c0[m].x, c1[m].y, kn1[m]);
-            const REAL dp = (div_dd<DIVK>(ss - bcur[m].x, cf.dd) - pp) * omg;
-            const bool ok = (fl & 1u) != 0u;
+          for (int m = 0; m < CPT; ++m) {
+            const REAL ss = XB ? sum6<UNIT>(cf, ie1[m], iw1[m], w2[m].y, w0[m].y, kn1[m], w1[m].x)
+                               : sum6<UNIT>(cf, ie1[m], iw1[m], w2[m].x, w0[m].x, w1[m].y, kn1[m]);
+            num[m] = ss - (XB ? bc[m].y : bc[m].x);
+            quo[m] = div_fast<DIVK>(num[m], cf.dd, rare);
+          }
+          if (DIVK && rare) {
+#pragma unroll
+            for (int m = 0; m < CPT; ++m) quo[m] = div_fix(num[m], quo[m], cf.dd);
+          }
+#pragma unroll
+          for (int m = 0; m < CPT; ++m) {
+            const unsigned fl = col[m].fl;
+            const REAL pp = XB ? w1[m].y : w1[m].x;
+            const REAL dp = (quo[m] - pp) * omg;
+            const bool ok = (fl & (XB ? 2u : 1u)) != 0u;
             const REAL nv = ok ? pp + dp : pp;
-            c1[m].x = nv;
-            if (ok) sts<0>(e1 + col[m].ad, nv);
-            const REAL d2 = (ok && red_owned && (fl & 4u)) ? dp * dp : (REAL)0;
+            if (XB) w1[m].y = nv; else w1[m].x = nv;
+            if (ok) sts<XB ? HPB : 0>(e1 + col[m].ad, nv);
+            const REAL d2 = (ok && red_owned && (fl & (XB ? 8u : 4u))) ? dp * dp : (REAL)0;
             acc[0] += (double)d2;
           }
-          if (do_black) {
-            const REAL pp = c0[m].x;
-            const REAL ss = sum6<UNIT>(cf, ie0[m], iw0[m], c1[m].x, cm1[m].x, c0[m].y, kn0[m]);
-            const REAL dp = (div_dd<DIVK>(ss - bprev[m].x, cf.dd) - pp) * omg;
-            const bool ok = (fl & 4u) != 0u;
-            c0[m].x = ok ? pp + dp : pp;
-            acc[0] += (double)(ok ? dp * dp : (REAL)0);
-            if (fl & 16u) stg2(a.out + gpl0 + col[m].gcol, c0[m]);
+        }
+        if (do_black) {
+          REAL num[CPT], quo[CPT];
+          bool rare = false;
+#pragma unroll
+          for (int m = 0; m < CPT; ++m) {
+            const REAL ss = XB ? sum6<UNIT>(cf, ie0[m], iw0[m], w1[m].y, wm1[m].y, kn0[m], w0[m].x)
+                               : sum6<UNIT>(cf, ie0[m], iw0[m], w1[m].x, wm1[m].x, w0[m].y, kn0[m]);
+            num[m] = ss - (XB ? bp[m].y : bp[m].x);
+            quo[m] = div_fast<DIVK>(num[m], cf.dd, rare);
           }
-        }
-      } else {
-        // cell B: k-1 = own A, k+1 = even half [q+1], i+-1 = odd half rows r+-1
+          if (DIVK && rare) {
 #pragma unroll
-        for (int m = 0; m < CPT; ++m) {
-          const uint32_t a1 = e1 + col[m].ad, a0 = e0 + col[m].ad;
-          kn1[m] = lds<SZ>(a1); ie1[m] = lds<HPB + PRB>(a1); iw1[m] = lds<HPB - PRB>(a1);
-          kn0[m] = lds<SZ>(a0); ie0[m] = lds<HPB + PRB>(a0); iw0[m] = lds<HPB - PRB>(a0);
-        }
+            for (int m = 0; m < CPT; ++m) quo[m] = div_fix(num[m], quo[m], cf.dd);
+          }
 #pragma unroll
-        for (int m = 0; m < CPT; ++m) {
-          const unsigned fl = col[m].fl;
-          if (do_red) {
-            const REAL pp = c1[m].y;
-            const REAL ss = sum6<UNIT>(cf, ie1[m], iw1[m], c2[m].y, c0[m].y, kn1[m], c1[m].x);
-            const REAL dp = (div_dd<DIVK>(ss - bcur[m].y, cf.dd) - pp) * omg;
-            const bool ok = (fl & 2u) != 0u;
+          for (int m = 0; m < CPT; ++m) {
+            const unsigned fl = col[m].fl;
+            const REAL pp = XB ? w0[m].y : w0[m].x;
+            const REAL dp = (quo[m] - pp) * omg;
+            const bool ok = (fl & (XB ? 8u : 4u)) != 0u;
             const REAL nv = ok ? pp + dp : pp;
-            c1[m].y = nv;
-            if (ok) sts<HPB>(e1 + col[m].ad, nv);
-            const REAL d2 = (ok && red_owned && (fl & 8u)) ? dp * dp : (REAL)0;
-            acc[0] += (double)d2;
-          }
-          if (do_black) {
-            const REAL pp = c0[m].y;
-            const REAL ss = sum6<UNIT>(cf, ie0[m], iw0[m], c1[m].y, cm1[m].y, kn0[m], c0[m].x);
-            const REAL dp = (div_dd<DIVK>(ss - bprev[m].y, cf.dd) - pp) * omg;
-            const bool ok = (fl & 8u) != 0u;
-            c0[m].y = ok ? pp + dp : pp;
+            if (XB) w0[m].y = nv; else w0[m].x = nv;
             acc[0] += (double)(ok ? dp * dp : (REAL)0);
-            if (fl & 16u) stg2(a.out + gpl0 + col[m].gcol, c0[m]);
+            if (fl & 16u) stg2(a.out + gpl0 + col[m].gcol, w0[m]);
           }
         }
-      }
+      };
+      if (xa) both(std::false_type{}); else both(std::true_type{});
     } else {
       // Jacobi / operator: plane s+1, both cells of the pair, old values only
       REAL kmA[CPT], ieA[CPT], iwA[CPT], ktB[CPT], ieB[CPT], iwB[CPT];
@@ -416,15 +445,15 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
 #pragma unroll
       for (int m = 0; m < CPT; ++m) {
         const unsigned fl = col[m].fl;
-        const REAL ssA = sum6<UNIT>(cf, ieA[m], iwA[m], c2[m].x, c0[m].x, c1[m].y, kmA[m]);
-        const REAL ssB = sum6<UNIT>(cf, ieB[m], iwB[m], c2[m].y, c0[m].y, ktB[m], c1[m].x);
+        const REAL ssA = sum6<UNIT>(cf, ieA[m], iwA[m], w2[m].x, w0[m].x, w1[m].y, kmA[m]);
+        const REAL ssB = sum6<UNIT>(cf, ieB[m], iwB[m], w2[m].y, w0[m].y, ktB[m], w1[m].x);
         const bool okA = (fl & 4u) != 0u, okB = (fl & 8u) != 0u;
         if (MODE == MODE_JAC) {
-          const REAL dpA = (div_dd<DIVK>(ssA - bcur[m].x, cf.dd) - c1[m].x) * omg;
-          const REAL dpB = (div_dd<DIVK>(ssB - bcur[m].y, cf.dd) - c1[m].y) * omg;
+          const REAL dpA = (div_dd<DIVK>(ssA - bc[m].x, cf.dd) - w1[m].x) * omg;
+          const REAL dpB = (div_dd<DIVK>(ssB - bc[m].y, cf.dd) - w1[m].y) * omg;
           R2 o;
-          o.x = okA ? c1[m].x + dpA : c1[m].x;
-          o.y = okB ? c1[m].y + dpB : c1[m].y;
+          o.x = okA ? w1[m].x + dpA : w1[m].x;
+          o.y = okB ? w1[m].y + dpB : w1[m].y;
           acc[0] += (double)(okA ? dpA * dpA : (REAL)0);
           acc[0] += (double)(okB ? dpB * dpB : (REAL)0);
           if (fl & 16u) stg2(a.out + gpl1 + col[m].gcol, o);
@@ -434,8 +463,8 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
           // allocation) -> store 0 there.
           if (fl & 16u) {
             R2 v;
-            v.x = okA ? ssA - cf.dd * c1[m].x : (REAL)0;
-            v.y = okB ? ssB - cf.dd * c1[m].y : (REAL)0;
+            v.x = okA ? ssA - cf.dd * w1[m].x : (REAL)0;
+            v.y = okB ? ssB - cf.dd * w1[m].y : (REAL)0;
             if (a.w) {
               const R2 wv = lds2(a.w + gpl1 + col[m].gcol);
               acc[0] += (double)(okA ? v.x * wv.x : (REAL)0);
@@ -447,12 +476,20 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
       }
     }
     __syncthreads();
-    if (tid == 0) {
-      if (tp + NSP < npl) issue_p(tp + NSP);
+    if (tid == 0) {   // both slots consumed by every thread: refill them three planes ahead
+      if (u + 2 + NSP < npl) issue_p(u + 2 + NSP);
       if (MODE != MODE_AX && u + NSB < nbpl) issue_b(u + NSB);
     }
-#pragma unroll
-    for (int m = 0; m < CPT; ++m) { cm1[m] = c0[m]; c0[m] = c1[m]; c1[m] = c2[m]; bprev[m] = bcur[m]; }
+    if (ring == 2) { ring = 0; phase ^= 1; } else ++ring;
+  };
+  for (int u = 0; u < nsteps; u += 4) {
+    step(u, cm1, c0, c1, c2, bprev, bcur);
+    if (u + 1 >= nsteps) break;
+    step(u + 1, c0, c1, c2, cm1, bcur, bprev);
+    if (u + 2 >= nsteps) break;
+    step(u + 2, c1, c2, cm1, c0, bprev, bcur);
+    if (u + 3 >= nsteps) break;
+    step(u + 3, c2, cm1, c0, c1, bcur, bprev);
   }
   grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
 }
