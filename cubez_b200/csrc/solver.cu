@@ -175,7 +175,7 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, dst, pitch, origin, nID);
+      launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
     }
   };
   int itr, done_iters;
@@ -201,7 +201,7 @@ int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, X, pitch, origin, nID);
+      launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
     }
   };
   int itr, done_iters;
@@ -244,7 +244,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (converge_check) {
         Comm_SUM(0);
         launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-        launch_bc_k(L, G, dst, pitch, origin, nID);
+        launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
@@ -260,7 +260,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (converge_check) {
         Comm_SUM(0);
         launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-        launch_bc_k(L, G, X, pitch, origin, nID);
+        launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
@@ -305,7 +305,7 @@ int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flo
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, X, pitch, origin, nID);
+      launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
     }
   };
   int itr, done_iters;
@@ -337,7 +337,7 @@ int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, 
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, X, pitch, origin, nID);
+      launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
     }
   };
   int itr, done_iters;
@@ -365,7 +365,7 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, X, pitch, origin, nID);
+      launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
     }
   };
   int itr, done_iters;
@@ -441,7 +441,7 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
     launch_dot1(L, G, r, 4);                                                 // :481
     Comm_S(X, 1); Comm_SUM(4);                                               // :486-488
     scalar(3);                                                               // :490-500
-    launch_bc_k(L, G, X, pitch, origin, nID);                                // :495
+    launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);                                // :495
   };
   // for (itr=1; itr<ItrMax; itr++)  (cz_Poisson.cpp:373)
   const int n_it = ItrMax - 1;
@@ -481,7 +481,7 @@ czb_ctx* czb_ctx_create(const int sz[3], const int idx[6], const int nID[6], CZB
   czb_ctx* c = new czb_ctx();
   memset((void*)c, 0, sizeof(czb_ctx));
   c->gc = 2;
-  for (int a = 0; a < 3; ++a) { c->size[a] = sz[a]; c->head[a] = 1; c->origin[a] = org ? org[a] : (REAL)0; }
+  for (int a = 0; a < 3; ++a) { c->size[a] = sz[a]; c->head[a] = 1; c->origin[a] = org ? org[a] : (REAL)0; c->bc_origin[a] = c->origin[a]; }
   for (int f = 0; f < 6; ++f) c->nID[f] = nID ? nID[f] : -1;
   if (idx) { for (int a = 0; a < 6; ++a) c->innerFidx[a] = idx[a]; }
   else {   // CZ::range_inner_index, cz_miscel.cpp:20-52
@@ -522,7 +522,18 @@ void czb_ctx_destroy(czb_ctx* c) {
 
 void czb_ctx_set_eps(czb_ctx* c, double eps) { c->eps = eps; }
 void czb_ctx_set_res_normal(czb_ctx* c, double v) { c->res_normal = v; }
-void czb_ctx_set_head(czb_ctx* c, const int head[3]) { for (int a = 0; a < 3; ++a) c->head[a] = head[a]; }
+void czb_ctx_set_head(czb_ctx* c, const int head[3]) {
+  for (int a = 0; a < 3; ++a) c->head[a] = head[a];
+  // Dirichlet data in global coordinates: y = G_origin + dh*(j_global-1) with G_origin = 0 (cz.h),
+  // instead of the reference's origin + dh*(j_local-1), whose rounding depends on the decomposition
+  c->bc_origin[1] = (head[1] > 1) ? (REAL)0 : c->origin[1];
+}
+
+void czb_ctx_bc_k(czb_ctx* c, CZB_REAL* p) {
+  Runtime& R = rt();
+  Arg<REAL> ap(p, c->field_elems(), true, true);
+  launch_bc_k(R.launch(), c->G, ap.dev(), c->pitch, c->bc_origin, c->nID, c->head[1] - 1);
+}
 void czb_ctx_set_variant(czb_ctx* c, int v) { c->variant = v; }
 double czb_last_solve_ms(czb_ctx* c) { return c->last_ms; }
 

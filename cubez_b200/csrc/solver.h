@@ -23,6 +23,7 @@ struct czb_ctx {
   int gc;                 // GUIDE = 2 (cz_Define.h:40)
   REAL pitch;             // dh
   REAL origin[3];
+  REAL bc_origin[3];      // origin used for the Dirichlet data (global y origin on j-slabs)
   REAL cf[7];             // {1,1,1,1,1,1,6} (cz.h:169-172)
   REAL ac1;               // omega (cz_Evaluate.cpp:99)
   double eps;             // 1e-5 (cz.h:162)

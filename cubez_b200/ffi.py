@@ -27,7 +27,7 @@ CZB_SYMBOLS = [
     "czb_real_bytes", "czb_version", "czb_init", "czb_set_stream", "czb_sync", "czb_malloc", "czb_free",
     "czb_memcpy_h2d", "czb_memcpy_d2h", "czb_launch_count", "czb_staged_bytes", "czb_slab_decompose",
     "czb_ctx_create", "czb_ctx_destroy", "czb_ctx_set_eps", "czb_ctx_set_res_normal", "czb_ctx_set_head",
-    "czb_ctx_set_variant", "czb_comm_unique_id", "czb_ctx_comm_init", "czb_solve", "czb_last_solve_ms",
+    "czb_ctx_set_variant", "czb_ctx_bc_k", "czb_comm_unique_id", "czb_ctx_comm_init", "czb_solve", "czb_last_solve_ms",
 ]
 
 
@@ -59,6 +59,7 @@ def bind_czb_symbols(dll, real_ctype):
     dll.czb_ctx_set_res_normal.argtypes = [P, C.c_double]; dll.czb_ctx_set_res_normal.restype = None
     dll.czb_ctx_set_head.argtypes = [P, PI]; dll.czb_ctx_set_head.restype = None
     dll.czb_ctx_set_variant.argtypes = [P, C.c_int]; dll.czb_ctx_set_variant.restype = None
+    dll.czb_ctx_bc_k.argtypes = [P, P]; dll.czb_ctx_bc_k.restype = None
     dll.czb_comm_unique_id.argtypes = [P]; dll.czb_comm_unique_id.restype = C.c_int
     dll.czb_ctx_comm_init.argtypes = [P, C.c_int, C.c_int, P]; dll.czb_ctx_comm_init.restype = C.c_int
     dll.czb_solve.argtypes = [P, C.c_char_p, C.c_char_p, P, P, C.c_int, real_ctype, PD, PD, C.c_int, PD]

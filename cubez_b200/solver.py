@@ -82,7 +82,7 @@ class CZ:
 
     # ---- problem setup (cz_Evaluate.cpp:375-390) -----------------------------------------
     def bc_k(self, p):
-        self.dll.bc_k_(self._sz, C.byref(self._g), self._ptr(p), self._dh, self._org, self._nID)
+        self.dll.czb_ctx_bc_k(self.ctx, self._ptr(p))
 
     def setup_laplace(self):
         """P and RHS of the reference problem: zero field, Dirichlet faces from bc_k."""

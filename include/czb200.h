@@ -162,7 +162,10 @@ void czb_ctx_destroy(czb_ctx* c);
 void czb_ctx_set_eps(czb_ctx* c, double eps);                /* default 1e-5, cz.h:162 */
 void czb_ctx_set_res_normal(czb_ctx* c, double res_normal);  /* default 1/inner cells */
 void czb_ctx_set_head(czb_ctx* c, const int head[3]);        /* global colouring offset */
-void czb_ctx_set_variant(czb_ctx* c, int variant);           /* 0 = auto (fused), 1 = baseline kernels */
+void czb_ctx_set_variant(czb_ctx* c, int variant);
+/* bc_k with the context's geometry.  On a j-slab (head[1] > 1) y is evaluated from the GLOBAL plane
+ * index, y = dh*(j_global-1), so that the Dirichlet data do not depend on the decomposition. */
+void czb_ctx_bc_k(czb_ctx* c, CZB_REAL* p);           /* 0 = auto (fused), 1 = baseline kernels */
 /* Multi-rank: NCCL communicator over the j-slab ring.  id = 128-byte ncclUniqueId made by
  * czb_comm_unique_id on rank 0 and distributed by the caller (torch.distributed / MPI). */
 int czb_comm_unique_id(void* id128);
