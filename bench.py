@@ -37,7 +37,7 @@ N_CUBE = int(os.environ.get("CZB_BENCH_N", "1024"))
 OMEGA = 1.5
 SOLVER = "sor2sma"
 ALGO_BYTES_PER_CELL = 16.0      # red-black SOR, float, 4R per cell.iteration
-NCU_TRAFFIC_PER_ITER = None     # filled from profiles/ (dram read+write bytes per launch)
+NCU_TRAFFIC_PER_ITER = 13.24e9     # dram read+write bytes per k_march<RB2> launch (profiles/r01_rb2_summary.md, 1 GPU)
 
 
 def measured_peak():
