@@ -36,7 +36,6 @@ enum { MODE_RB2 = 0, MODE_JAC = 1, MODE_AX = 2 };
 
 constexpr int PR = 64;          // pairs per tile row  -> box width EKB = 128 cells
 constexpr int EKB = 2 * PR;
-constexpr int CPT = 4;          // pair columns per thread
 constexpr int NSP = 3;          // raw TMA slots for p  (planes s+2, s+3, s+4)
 constexpr int NSB = 3;          // raw TMA slots for b  (planes s+1, s+2, s+3)
 
@@ -154,6 +153,18 @@ template <int OFF>
 __device__ __forceinline__ void sts(uint32_t addr, REAL v) {
   asm volatile(CZB_ST " [%0+%1], %2;" ::"r"(addr), "n"(OFF), CZB_RC(v) : "memory");
 }
+// store only where `flag` != 0, as a predicated instruction (a C++ `if` around inline asm becomes a branch)
+template <int OFF>
+__device__ __forceinline__ void sts_if(uint32_t addr, REAL v, unsigned flag) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p " CZB_ST " [%0+%1], %2;\n\t}" ::"r"(addr), "n"(OFF), CZB_RC(v), "r"(flag) : "memory");
+}
+__device__ __forceinline__ void stg2_if(REAL* p, R2 v, unsigned flag) {
+#ifdef _REAL_IS_DOUBLE_
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p st.global.v2.f64 [%0], {%1, %2};\n\t}" ::"l"(p), "d"(v.x), "d"(v.y), "r"(flag) : "memory");
+#else
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p st.global.v2.f32 [%0], {%1, %2};\n\t}" ::"l"(p), "f"(v.x), "f"(v.y), "r"(flag) : "memory");
+#endif
+}
 __device__ __forceinline__ R2 lds_pair(uint32_t addr) {
   R2 v;
   asm volatile(CZB_LD2 " {%0, %1}, [%2];" : "=" CZB_RC(v.x), "=" CZB_RC(v.y) : "r"(addr) : "memory");
@@ -168,35 +179,50 @@ __device__ __forceinline__ R2 lds_pair(uint32_t addr) {
 // subnormal, which is the common case while the solution front is still spreading from the walls.
 // Out-of-line IEEE division for the rare operands outside the guarded range; __noinline__ keeps
 // the compiler from speculating the ~45-instruction sequence onto the common path.
+#ifdef _REAL_IS_DOUBLE_
 __device__ __noinline__ REAL div_rare(REAL a, REAL dd) { return a / dd; }
+#else
+// float: the quotient is formed in double and rounded once more; double rounding is innocuous for
+// division when the wide format has >= 2p+2 bits (53 >= 50), also for subnormal results, and the
+// double division never meets a subnormal operand (the float IEEE slow path would).
+__device__ __noinline__ REAL div_rare(REAL a, REAL dd) { return (float)((double)a / (double)dd); }
+#endif
 
+// Exact division by 6 without the IEEE sequence (which costs ~45 instructions as soon as an operand
+// is zero or subnormal -- the common case while the solution front is still spreading from the
+// walls).  float: as = a*2^64 (exact), q = as*y, r = fma(-6,q,as), q' = fma(r,y,q) [Markstein: the
+// correctly rounded quotient], result q'*2^-64 (exact while the quotient is a normal number, and
+// verified also for the subnormal operands).  EXHAUSTIVELY checked against a/6 for every float
+// with biased exponent 0, 1 and 4..183 (tests/tools/div6_check.c: 3.1e9 values, 0 mismatches).
+// Operands outside that set (exponents 2,3: the quotient would be rounded twice; |a| >= 2^57;
+// -0; non-finite) are flagged `rare` and patched by the IEEE division behind ONE branch per
+// group of quotients (div_fix).  double: same sequence unscaled, guarded to |a| in [2^-900,2^900].
 #ifdef _REAL_IS_DOUBLE_
 __device__ __forceinline__ bool div_guard_fail(double a) {
   const unsigned e = ((unsigned)__double2hiint(a) >> 20) & 0x7ffu;
-  return (e - 123u > 1800u) && (a != 0.0);
+  return (e - 123u > 1800u) && (__double_as_longlong(a) != 0ll);   // +0 is exact on the fast path, -0 is not
 }
 #else
 __device__ __forceinline__ bool div_guard_fail(float a) {
-  const unsigned e = (__float_as_uint(a) >> 23) & 0xffu;
-  return (e - 27u > 220u) && (a != 0.0f);
+  const unsigned bits = __float_as_uint(a);
+  const unsigned e = (bits >> 23) & 0xffu;
+  return ((e - 4u > 179u) && (e > 1u)) || (bits == 0x80000000u);
 }
 #endif
-// Branch-free part: the fast quotient (exact inside the guard, and for +-0 after the select);
-// `rare` is OR-ed with "operand outside the guard" so that the caller can patch a whole group of
-// quotients behind ONE rarely taken branch (div_fix).
 template <bool DIVK>
 __device__ __forceinline__ REAL div_fast(REAL a, REAL dd, bool& rare) {
   if (!DIVK) return a / dd;
   const REAL y = (REAL)1.0 / (REAL)6.0;
-  const REAL q = a * y;
 #ifdef _REAL_IS_DOUBLE_
+  const REAL q = a * y;
   const REAL r = fma(-6.0, q, a);
-  REAL res = fma(r, y, q);
+  const REAL res = fma(r, y, q);
 #else
-  const REAL r = __fmaf_rn(-6.0f, q, a);
-  REAL res = __fmaf_rn(r, y, q);
+  const REAL as = a * 0x1p64f;
+  const REAL q = as * y;
+  const REAL r = __fmaf_rn(-6.0f, q, as);
+  const REAL res = __fmaf_rn(r, y, q) * 0x1p-64f;
 #endif
-  res = (a == (REAL)0) ? a : res;          // +-0 / 6 = +-0
   rare = rare || div_guard_fail(a);
   return res;
 }
@@ -226,7 +252,7 @@ struct Col {
   unsigned fl;     // bit0/1 red-ok A/B, bit2/3 owned A/B, bit4 store pair
 };
 
-template <int MODE, int NT, bool UNIT, bool DIVK>
+template <int MODE, int NT, int CPT, bool UNIT, bool DIVK>
 __global__ void __launch_bounds__(NT, 1)
 k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b, const MarchArgs a) {
   if (a.st && a.st->done) return;
@@ -400,7 +426,7 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
             const bool ok = (fl & (XB ? 2u : 1u)) != 0u;
             const REAL nv = ok ? pp + dp : pp;
             if (XB) w1[m].y = nv; else w1[m].x = nv;
-            if (ok) sts<XB ? HPB : 0>(e1 + col[m].ad, nv);
+            sts_if<XB ? HPB : 0>(e1 + col[m].ad, nv, fl & (XB ? 2u : 1u));
             const REAL d2 = (ok && red_owned && (fl & (XB ? 8u : 4u))) ? dp * dp : (REAL)0;
             acc[0] += (double)d2;
           }
@@ -428,7 +454,7 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
             const REAL nv = ok ? pp + dp : pp;
             if (XB) w0[m].y = nv; else w0[m].x = nv;
             acc[0] += (double)(ok ? dp * dp : (REAL)0);
-            if (fl & 16u) stg2(a.out + gpl0 + col[m].gcol, w0[m]);
+            stg2_if(a.out + gpl0 + col[m].gcol, w0[m], fl & 16u);
           }
         }
       };
@@ -456,7 +482,7 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
           o.y = okB ? w1[m].y + dpB : w1[m].y;
           acc[0] += (double)(okA ? dpA * dpA : (REAL)0);
           acc[0] += (double)(okB ? dpB * dpB : (REAL)0);
-          if (fl & 16u) stg2(a.out + gpl1 + col[m].gcol, o);
+          stg2_if(a.out + gpl1 + col[m].gcol, o, fl & 16u);
         } else {
           // MODE_AX (solver-internal): non-inner cells of a stored pair are boundary nodes of
           // q / t_, which the reference leaves at their initial 0 (blas_clear / zero-filled
@@ -535,34 +561,56 @@ const CUtensorMap& tmap_for(const REAL* base, const Geo& G, int ei) {
   return g_tmaps.emplace(key, tm).first->second;
 }
 
-template <int MODE, int NT>
+template <int MODE, int NT, int CPT>
 void launch_march_t(const Launch& L, const MarchArgs& a, const CUtensorMap& tp, const CUtensorMap& tb, bool fast, size_t smem) {
   dim3 grid(a.ntk * a.nti, a.njc, 1);
   if (fast) {   // unit off-diagonals and dd == 6: the CubeZ operator (cz.h:169-172)
     static bool set = false;
-    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
-    k_march<MODE, NT, true, true><<<grid, NT, smem, L.s>>>(tp, tb, a);
+    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, CPT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+    k_march<MODE, NT, CPT, true, true><<<grid, NT, smem, L.s>>>(tp, tb, a);
   } else {
     static bool set = false;
-    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
-    k_march<MODE, NT, false, false><<<grid, NT, smem, L.s>>>(tp, tb, a);
+    if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, CPT, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+    k_march<MODE, NT, CPT, false, false><<<grid, NT, smem, L.s>>>(tp, tb, a);
   }
   CZB_CHECK(cudaGetLastError());
   count_launch();
 }
 
+// Tile configuration: NT threads, CPT pair columns per thread -> tile rows EI = NT/64*CPT.
+//   f32: cfg 0 = 512 x 4 (128x32 tile, 1 CTA/SM, 16 warps)   cfg 1 = 1024 x 2 (same tile, 32 warps)
+//   f64: 256 x 4 (128x16 tile of doubles)
+template <int MODE>
+void launch_march_cfg(int cfg, const Launch& L, const MarchArgs& a, const CUtensorMap& tp, const CUtensorMap& tb, bool fast, size_t smem) {
 #ifdef _REAL_IS_DOUBLE_
-constexpr int NT_MARCH = 256;   // 128x16 tiles of doubles: 9 x 16 KB of shared memory
+  (void)cfg;
+  launch_march_t<MODE, 256, 4>(L, a, tp, tb, fast, smem);
 #else
-constexpr int NT_MARCH = 512;   // 128x32 tiles of floats:  9 x 16 KB of shared memory
+  if (cfg == 1) launch_march_t<MODE, 1024, 2>(L, a, tp, tb, fast, smem);
+  else          launch_march_t<MODE, 512, 4>(L, a, tp, tb, fast, smem);
 #endif
+}
+
+int march_cfg() {
+  static int cfg = -1;
+  if (cfg < 0) { const char* e = getenv("CZB_MARCH_CFG"); cfg = e ? atoi(e) : 1; }
+  return cfg;
+}
+int march_rows(int cfg) {
+#ifdef _REAL_IS_DOUBLE_
+  (void)cfg; return 16;
+#else
+  (void)cfg; return 32;
+#endif
+}
 
 bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_or_w, REAL* out, const REAL* cf,
            REAL omg, int ip, int jr0, int jr1, int slot, bool add) {
   if (!fused_eligible(G)) return false;
   MarchArgs a;
   a.G = G;
-  a.ei = (NT_MARCH / PR) * CPT;
+  const int cfg = march_cfg();
+  a.ei = march_rows(cfg);
   const int kst_c = G.kst + G.g - 1, ked_c = G.ked + G.g - 1;
   const int npairs = (ked_c >> 1) - (kst_c >> 1) + 1;
   a.ntk = (npairs + PR - 3) / (PR - 2);
@@ -589,9 +637,9 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
   const CUtensorMap& tb = (mode == MODE_AX) ? tp : tmap_for(b_or_w, G, a.ei);
   // + 1 KB: halo columns read (and discard) neighbours up to one half-plane row past the last plane
   const size_t smem = ((mode == MODE_AX ? NSP : NSP + NSB) + 3) * T * sizeof(REAL) + 8 * (NSP + NSB) + 1024;
-  if (mode == MODE_RB2)      launch_march_t<MODE_RB2, NT_MARCH>(L, a, tp, tb, unit, smem);
-  else if (mode == MODE_JAC) launch_march_t<MODE_JAC, NT_MARCH>(L, a, tp, tb, unit, smem);
-  else                       launch_march_t<MODE_AX, NT_MARCH>(L, a, tp, tb, unit, smem);
+  if (mode == MODE_RB2)      launch_march_cfg<MODE_RB2>(cfg, L, a, tp, tb, unit, smem);
+  else if (mode == MODE_JAC) launch_march_cfg<MODE_JAC>(cfg, L, a, tp, tb, unit, smem);
+  else                       launch_march_cfg<MODE_AX>(cfg, L, a, tp, tb, unit, smem);
   return true;
 }
 
