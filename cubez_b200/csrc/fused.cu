@@ -50,6 +50,7 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 // Bounded wait: a lost TMA must abort the kernel, never hang the GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
+#pragma unroll 1
   for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
     uint32_t ok;
     asm volatile(
@@ -520,6 +521,10 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
   grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
 }
 
+#ifndef _REAL_IS_DOUBLE_
+#include "fused_pk.cuh"
+#endif
+
 }  // namespace
 
 // ============================================================================ host side
@@ -591,9 +596,21 @@ void launch_march_cfg(int cfg, const Launch& L, const MarchArgs& a, const CUtens
 #endif
 }
 
+#ifndef _REAL_IS_DOUBLE_
+template <int NT, int CPT>
+void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const CUtensorMap& tp, const CUtensorMap& tb, size_t smem) {
+  dim3 grid(a.ntk * a.nti, a.njc, 1);
+  static bool set = false;
+  if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+  k_rb2_pk<NT, CPT><<<grid, NT, smem, L.s>>>(tp, tb, a);
+  CZB_CHECK(cudaGetLastError());
+  count_launch();
+}
+#endif
+
 int march_cfg() {
   static int cfg = -1;
-  if (cfg < 0) { const char* e = getenv("CZB_MARCH_CFG"); cfg = e ? atoi(e) : 1; }
+  if (cfg < 0) { const char* e = getenv("CZB_MARCH_CFG"); cfg = e ? atoi(e) : 2; }
   return cfg;
 }
 int march_rows(int cfg) {
@@ -611,9 +628,22 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
   a.G = G;
   const int cfg = march_cfg();
   a.ei = march_rows(cfg);
+  const bool unit = cf[0] == (REAL)1 && cf[1] == (REAL)1 && cf[2] == (REAL)1 && cf[3] == (REAL)1 && cf[4] == (REAL)1 &&
+                    cf[5] == (REAL)1 && cf[6] == (REAL)6;
   const int kst_c = G.kst + G.g - 1, ked_c = G.ked + G.g - 1;
-  const int npairs = (ked_c >> 1) - (kst_c >> 1) + 1;
-  a.ntk = (npairs + PR - 3) / (PR - 2);
+#ifndef _REAL_IS_DOUBLE_
+  // packed-f32x2 kernel (fused_pk.cuh): the CubeZ operator only; needs 16-byte aligned units
+  const bool packed = (mode == MODE_RB2) && unit && cfg >= 2 && (G.nk % 4 == 0);
+#else
+  const bool packed = false;
+#endif
+  if (packed) {
+    const int npairs = (ked_c >> 1) - ((kst_c >> 1) & ~1) + 1;     // tiles start at an even pair
+    a.ntk = (npairs + PR - 5) / (PR - 4);
+  } else {
+    const int npairs = (ked_c >> 1) - (kst_c >> 1) + 1;
+    a.ntk = (npairs + PR - 3) / (PR - 2);
+  }
   const int ni = G.ied - G.ist + 1, nj = G.jed - G.jst + 1;
   a.nti = (ni + a.ei - 5) / (a.ei - 4);
   // j-chunks: enough CTAs for ~8 rounds over the SMs, chunks no shorter than 32 planes
@@ -630,13 +660,14 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
   a.out = out; a.w = (mode == MODE_AX) ? b_or_w : nullptr;
   a.st = L.st; a.acc_st = L.acc_st; a.slot = slot; a.add = add ? 1 : 0;
   a.rb = L.rb;
-  const bool unit = cf[0] == (REAL)1 && cf[1] == (REAL)1 && cf[2] == (REAL)1 && cf[3] == (REAL)1 && cf[4] == (REAL)1 &&
-                    cf[5] == (REAL)1 && cf[6] == (REAL)6;
   const size_t T = (size_t)a.ei * EKB;
   const CUtensorMap& tp = tmap_for(p, G, a.ei);
   const CUtensorMap& tb = (mode == MODE_AX) ? tp : tmap_for(b_or_w, G, a.ei);
   // + 1 KB: halo columns read (and discard) neighbours up to one half-plane row past the last plane
   const size_t smem = ((mode == MODE_AX ? NSP : NSP + NSB) + 3) * T * sizeof(REAL) + 8 * (NSP + NSB) + 1024;
+#ifndef _REAL_IS_DOUBLE_
+  if (packed) { launch_rb2_pk_t<512, 2>(L, a, tp, tb, smem); return true; }
+#endif
   if (mode == MODE_RB2)      launch_march_cfg<MODE_RB2>(cfg, L, a, tp, tb, unit, smem);
   else if (mode == MODE_JAC) launch_march_cfg<MODE_JAC>(cfg, L, a, tp, tb, unit, smem);
   else                       launch_march_cfg<MODE_AX>(cfg, L, a, tp, tb, unit, smem);
