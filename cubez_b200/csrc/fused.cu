@@ -597,12 +597,16 @@ void launch_march_cfg(int cfg, const Launch& L, const MarchArgs& a, const CUtens
 }
 
 #ifndef _REAL_IS_DOUBLE_
-template <int NT, int CPT>
-void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const CUtensorMap& tp, const CUtensorMap& tb, size_t smem) {
+template <int NT, int CPT, int NSP_, int NSB_>
+void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const REAL* b) {
+  constexpr int EI = NT / 32 * CPT;
   dim3 grid(a.ntk * a.nti, a.njc, 1);
+  const size_t smem = (size_t)(NSP_ + NSB_ + NDE) * EI * EKB * sizeof(float) + 1024;
   static bool set = false;
-  if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
-  k_rb2_pk<NT, CPT><<<grid, NT, smem, L.s>>>(tp, tb, a);
+  if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT, NSP_, NSB_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+  const CUtensorMap& tp = tmap_for(p, a.G, EI);
+  const CUtensorMap& tb = tmap_for(b, a.G, EI);
+  k_rb2_pk<NT, CPT, NSP_, NSB_><<<grid, NT, smem, L.s>>>(tp, tb, a);
   CZB_CHECK(cudaGetLastError());
   count_launch();
 }
@@ -647,7 +651,9 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
   const int ni = G.ied - G.ist + 1, nj = G.jed - G.jst + 1;
   a.nti = (ni + a.ei - 5) / (a.ei - 4);
   // j-chunks: enough CTAs for ~8 rounds over the SMs, chunks no shorter than 32 planes
-  int njc = (148 * 8 + a.ntk * a.nti - 1) / (a.ntk * a.nti);
+  static int rounds = -1;
+  if (rounds < 0) { const char* e = getenv("CZB_ROUNDS"); rounds = e ? atoi(e) : 8; }
+  int njc = (148 * rounds + a.ntk * a.nti - 1) / (a.ntk * a.nti);
   if (njc > (nj + 31) / 32) njc = (nj + 31) / 32;
   if (njc < 1) njc = 1;
   a.jl = (nj + njc - 1) / njc;
@@ -666,7 +672,13 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
   // + 1 KB: halo columns read (and discard) neighbours up to one half-plane row past the last plane
   const size_t smem = ((mode == MODE_AX ? NSP : NSP + NSB) + 3) * T * sizeof(REAL) + 8 * (NSP + NSB) + 1024;
 #ifndef _REAL_IS_DOUBLE_
-  if (packed) { launch_rb2_pk_t<512, 2>(L, a, tp, tb, smem); return true; }
+  if (packed) {   // look-ahead (raw TMA slots for p, b): cfg 2 = 3+3, 3 = 4+3, 4 = 5+4, 5 = 5+5
+    if (cfg == 3)      launch_rb2_pk_t<512, 2, 4, 3>(L, a, p, b_or_w);
+    else if (cfg == 4) launch_rb2_pk_t<512, 2, 5, 4>(L, a, p, b_or_w);
+    else if (cfg == 5) launch_rb2_pk_t<512, 2, 5, 5>(L, a, p, b_or_w);
+    else               launch_rb2_pk_t<512, 2, 3, 3>(L, a, p, b_or_w);
+    return true;
+  }
 #endif
   if (mode == MODE_RB2)      launch_march_cfg<MODE_RB2>(cfg, L, a, tp, tb, unit, smem);
   else if (mode == MODE_JAC) launch_march_cfg<MODE_JAC>(cfg, L, a, tp, tb, unit, smem);

@@ -58,7 +58,6 @@ __device__ __forceinline__ void stg_unit_if(float* p, U4 v, unsigned flag) {
   asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %5, 0;\n\t@p st.global.v4.f32 [%0], {%1, %2, %3, %4};\n\t}" ::"l"(p),
                "f"(lo(v.a)), "f"(lo(v.b)), "f"(hi(v.a)), "f"(hi(v.b)), "r"(flag) : "memory");
 }
-
 // Exact a/6 for two cells (see div_fast in fused.cu: scaled Markstein sequence, exhaustively
 // verified for biased exponents 0, 1 and 4..183).
 __device__ __forceinline__ F2 div6_2(F2 a) {
@@ -80,9 +79,33 @@ __device__ __noinline__ float4 div6_fix4(float4 n, float4 q) {
 }
 
 constexpr int PKH = 2;          // halo pairs on each k side of a tile (one unit)
+constexpr int NDE = 4;          // de-interleaved plane copies kept in shared memory (planes s-1 .. s+2)
+
+__device__ __forceinline__ void mbar_wait_a(uint32_t addr, uint32_t parity) {   // bounded wait, 32-bit smem address
+#pragma unroll 1
+  for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (ok) return;
+  }
+  __trap();
+}
 
 // Both colours of one red-black SOR iteration, unit coefficients / dd = 6 (the CubeZ operator).
-template <int NT, int CPT>
+//
+// Software pipeline: at step u (s = first plane + u) the CTA relaxes the RED cells of plane s+1 and the
+// BLACK cells of plane s-1.  The blacks of plane s-1 need the new reds of planes s-2, s-1, s -- all
+// finished in earlier steps -- so the two relaxations of a step are independent instruction
+// streams (the blacks trail the reds by two planes instead of one), which doubles the ILP of the
+// dependent add/divide chains.  Per step: one TMA plane of p and one of b arrive (NSP_/NSB_ slots
+// of look-ahead), one plane is stored, one __syncthreads.
+template <int NT, int CPT, int NSP_, int NSB_>
 __global__ void __launch_bounds__(NT, 1)
 k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b, const MarchArgs a) {
   if (a.st && a.st->done) return;
@@ -93,13 +116,14 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   constexpr int HPB = TB / 2;              // bytes per de-interleaved half plane (even-k, then odd-k)
   constexpr int PRB = PR * 4;              // bytes per row of a half plane
   static_assert(RPW % 2 == 0, "all units of a thread must share the row parity");
+  static_assert(CPT == 2, "flag layout below assumes two units per thread");
   const Geo& G = a.G;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   const uint32_t sm0 = smem_u32(smem_raw);
-  const uint32_t raw_p = sm0;                          // [NSP][TB]
-  const uint32_t raw_b = raw_p + NSP * TB;             // [NSB][TB]
-  const uint32_t dei = raw_b + NSB * TB;               // [3][TB]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + (size_t)(NSP + NSB + 3) * TB);   // [NSP + NSB]
+  const uint32_t raw_p = sm0;                          // [NSP_][TB]
+  const uint32_t raw_b = raw_p + NSP_ * TB;            // [NSB_][TB]
+  const uint32_t dei = raw_b + NSB_ * TB;              // [NDE][TB]
+  const uint32_t bar0 = dei + NDE * TB + 512;          // [NSP_ + NSB_] mbarriers (after a pad row)
   const int tid = threadIdx.x;
   const int lane = tid & 31, wrow = tid >> 5;
 
@@ -112,61 +136,47 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   const int jb = min(ja + a.jl - 1, a.jb1);
   const int pl0 = ja - 2;                                          // first p plane fetched
   const int bpl0 = ja - 1;                                         // first b plane fetched
-  const int nsteps = jb - ja + 3;
-  const int npl = nsteps + 2;                                      // p planes fetched
-  const int nbpl = nsteps;                                         // b planes fetched
+  const int nsteps = jb - ja + 4;                                  // s = ja-2 .. jb+1
+  const int npl = nsteps + 1;                                      // p planes ja-2 .. jb+2
+  const int nbpl = nsteps - 1;                                     // b planes ja-1 .. jb+1
 
   if (tid == 0) {
-    for (int s = 0; s < NSP + NSB; ++s) mbar_init(&bars[s], 1);
+    for (int s = 0; s < NSP_ + NSB_; ++s)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u * s) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  auto issue_p = [&](int t) {   // plane pl0+t -> slot t % NSP
-    uint64_t* bar = &bars[t % NSP];
-    mbar_expect_tx(bar, (uint32_t)TB);
-    tma_load_3d(smem_raw + (size_t)(t % NSP) * TB, &tm_p, bar, 2 * P0, R0, pl0 + t + G.g - 1);
+  auto issue_plane = [&](uint32_t dst, uint32_t bar, const CUtensorMap* tm, int plane) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)TB) : "memory");
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(dst), "l"(tm), "r"(bar), "r"(2 * P0), "r"(R0), "r"(plane) : "memory");
+  };
+  auto issue_p = [&](int t) {   // plane pl0+t -> slot t % NSP_
+    issue_plane(raw_p + (uint32_t)(t % NSP_) * TB, bar0 + 8u * (uint32_t)(t % NSP_), &tm_p, pl0 + t + G.g - 1);
   };
   auto issue_b = [&](int t) {
-    uint64_t* bar = &bars[NSP + t % NSB];
-    mbar_expect_tx(bar, (uint32_t)TB);
-    tma_load_3d(smem_raw + (size_t)(NSP + t % NSB) * TB, &tm_b, bar, 2 * P0, R0, bpl0 + t + G.g - 1);
+    issue_plane(raw_b + (uint32_t)(t % NSB_) * TB, bar0 + 8u * (uint32_t)(NSP_ + t % NSB_), &tm_b, bpl0 + t + G.g - 1);
   };
   if (tid == 0) {
-    for (int t = 0; t < NSP && t < npl; ++t) issue_p(t);
-    for (int t = 0; t < NSB && t < nbpl; ++t) issue_b(t);
+    for (int t = 0; t < NSP_ && t < npl; ++t) issue_p(t);
+    for (int t = 0; t < NSB_ && t < nbpl; ++t) issue_b(t);
   }
 
   // ---- per-thread constants ---------------------------------------------------------------
-  // Bit masks (all ones / zero) per cell of the thread's units: MR = the red cell may be relaxed here
-  // (inner cell, row and k neighbours inside the box), MK = the cell is owned by this tile (blacks are
-  // relaxed, residual counted, results stored).  Masks are applied with bitwise selects, so whatever
-  // the never-referenced guard cells hold (even NaN) cannot leak into a kept value or the residual.
+  // Flag word: bit x*4+m*2+e     : the X cell (x = 0 A / 1 B) of pair e of unit m may be relaxed as a RED
+  //                                cell here (inner cell, row and k neighbours inside the box);
+  //            bit 8+x*4+m*2+e   : that cell is owned by this tile (blacks relaxed, residual counted);
+  //            bit 16+m          : unit m is stored.
+  // Masks are applied with selects, so whatever the never-referenced guard cells hold (even NaN)
+  // cannot leak into a kept value or the residual.
   const float omg = a.omg;
   const F2 omg2 = pk(omg, omg);
-  bool kRb[2][2], kOb[2][2];   // [X = A/B][e]
-  bool kany = false;
-#pragma unroll
-  for (int e = 0; e < 2; ++e) {
-    const int q = 2 * lane + e;
-    const int kcA = 2 * (P0 + q);
-    const bool ownq = (q >= PKH) && (q <= PR - 1 - PKH);
-#pragma unroll
-    for (int x = 0; x < 2; ++x) {
-      const int kc = kcA + x, kF = kc - G.g + 1;
-      const bool kin = kc >= 0 && kc < G.nk && kF >= G.kst && kF <= G.ked;
-      const bool nb = x ? (q <= PR - 2) : (q >= 1);
-      kRb[x][e] = kin && nb;
-      kOb[x][e] = kin && ownq;
-      kany = kany || (kin && ownq);
-    }
-  }
   const int kc0 = 2 * (P0 + 2 * lane);            // C index of cell A0 of the thread's units
   const bool unit_in = kc0 >= 0 && kc0 + 3 < G.nk;
   // parity of cell A0 at plane 0 (Fortran indices, cz_solver.f90:466): all units of a thread share it
   const unsigned par = (unsigned)((kc0 - G.g + 1) - G.kst + (R0 + wrow - G.g + 1) + a.ip) & 1u;
   uint32_t araw[CPT], ad[CPT];
-  unsigned stf[CPT];
-  uint2 MR[2][CPT], MK[2][CPT];
+  unsigned fl = 0u;
   float* outp[CPT];
 #pragma unroll
   for (int m = 0; m < CPT; ++m) {
@@ -177,167 +187,219 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
     const bool rowin = ic >= 0 && ic < G.ni && iF >= G.ist && iF <= G.ied;
     const int dr = min(r, EI - 1 - r);
     const bool rR = rowin && dr >= 1, rO = rowin && dr >= 2;
+    bool kany = false;
 #pragma unroll
-    for (int x = 0; x < 2; ++x) {
-      MR[x][m] = make_uint2((kRb[x][0] && rR) ? ~0u : 0u, (kRb[x][1] && rR) ? ~0u : 0u);
-      MK[x][m] = make_uint2((kOb[x][0] && rO) ? ~0u : 0u, (kOb[x][1] && rO) ? ~0u : 0u);
+    for (int e = 0; e < 2; ++e) {
+      const int q = 2 * lane + e;
+      const bool ownq = (q >= PKH) && (q <= PR - 1 - PKH);
+#pragma unroll
+      for (int x = 0; x < 2; ++x) {
+        const int kc = 2 * (P0 + q) + x, kF = kc - G.g + 1;
+        const bool kin = kc >= 0 && kc < G.nk && kF >= G.kst && kF <= G.ked;
+        const bool nb = x ? (q <= PR - 2) : (q >= 1);
+        if (kin && nb && rR) fl |= 1u << (x * 4 + m * 2 + e);
+        if (kin && ownq && rO) fl |= 1u << (8 + x * 4 + m * 2 + e);
+        kany = kany || (kin && ownq);
+      }
     }
-    stf[m] = (rO && kany && unit_in) ? 1u : 0u;
-    // running store pointer: unit (r, lane) of plane pl0 (advanced by one plane per step)
-    outp[m] = a.out + ((long long)(pl0 + G.g - 1) * G.plane + (long long)G.nk * (stf[m] ? ic : 0) + (stf[m] ? kc0 : 0));
+    const bool st = rO && kany && unit_in;
+    if (st) fl |= 1u << (16 + m);
+    // running store pointer: unit (r, lane) of plane s-1 (advanced by one plane per step)
+    outp[m] = a.out + ((long long)(pl0 - 1 + G.g - 1) * G.plane + (long long)G.nk * (st ? ic : 0) + (st ? kc0 : 0));
   }
 
-  U4 cm1[CPT], c0[CPT], c1[CPT], c2[CPT], bprev[CPT], bcur[CPT];
-#pragma unroll
-  for (int m = 0; m < CPT; ++m) { cm1[m] = c0[m] = c1[m] = c2[m] = bprev[m] = bcur[m] = U4{0ull, 0ull}; }
-  double acc[1] = {0.0};
-
-  // ---- prologue: planes pl0 (-> c0) and pl0+1 (-> c1 + de-interleaved copy in ring slot 1) -----
-  mbar_wait(&bars[0], 0);
-#pragma unroll
-  for (int m = 0; m < CPT; ++m) c0[m] = lds_unit(raw_p + araw[m]);
-  mbar_wait(&bars[1], 0);
+  U4 P[4][CPT];          // planes s-1, s, s+1, s+2 (roles rotate with the step, see STEP below)
+  F2 hb[2][CPT];         // right-hand side of the black cells of planes s-1 and s
 #pragma unroll
   for (int m = 0; m < CPT; ++m) {
-    c1[m] = lds_unit(raw_p + TB + araw[m]);
-    sts64<0>(dei + TB + ad[m], c1[m].a); sts64<HPB>(dei + TB + ad[m], c1[m].b);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) P[c][m] = U4{0ull, 0ull};
+    hb[0][m] = hb[1][m] = 0ull;
+  }
+  double acc[1] = {0.0};
+
+  // ---- prologue: planes pl0 (-> P[0], "s") and pl0+1 (-> P[1], "s+1", + de-interleaved copy) ---------
+  mbar_wait_a(bar0, 0);
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) P[0][m] = lds_unit(raw_p + araw[m]);
+  mbar_wait_a(bar0 + 8, 0);
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) {
+    P[1][m] = lds_unit(raw_p + TB + araw[m]);
+    sts64<0>(dei + TB + ad[m], P[1][m].a); sts64<HPB>(dei + TB + ad[m], P[1][m].b);
   }
   __syncthreads();
-  if (tid == 0) { if (NSP < npl) issue_p(NSP); if (NSP + 1 < npl) issue_p(NSP + 1); }
+  if (tid == 0) { if (NSP_ < npl) issue_p(NSP_); if (NSP_ + 1 < npl) issue_p(NSP_ + 1); }
 
   // ---- main loop ----------------------------------------------------------------------------------
-  // Step u: reds of plane s+1, then blacks of plane s (s = pl0+u).  The four plane registers rotate
-  // roles every step; the body is instantiated four times with permuted roles (no register moves).
-  int ring = 0;          // u % 3 : ring slot of de-interleaved plane s; raw b slot of this step
-  int phase = 0;         // (u / 3) & 1 : mbarrier parity of the b slot; p slot (u+2)%3 has parity pphase
-  auto step = [&](int u, U4 (&wm1)[CPT], U4 (&w0)[CPT], U4 (&w1)[CPT], U4 (&w2)[CPT], U4 (&bp)[CPT], U4 (&bc)[CPT]) {
+  int sp = 2 % NSP_, pp = (2 / NSP_) & 1;   // raw p slot / mbarrier parity of plane index u+2
+  int sb = 0, pb = 0;                       // raw b slot / parity of plane index u
+
+  // Numerators ss - b of the X cells (xb: false = A, true = B) of one plane for all units of the thread.
+  // wc = the plane (own other-colour pairs give the k neighbours, plus one shuffle), en = its
+  // de-interleaved copy (i neighbours), jn/js = the X pairs of planes j+1 / j-1, bb = right-hand side.
+  // Order of the sum: cz_solver.f90:468-473 (i+1, i-1, j+1, j-1, k+1, k-1).
+  auto numer = [&](auto xb, const uint32_t en, const U4 (&wc)[CPT], const F2 (&jn)[CPT], const F2 (&js)[CPT],
+                   const F2 (&bb)[CPT], F2 (&num)[CPT]) {
+    constexpr bool XB = decltype(xb)::value;
+    constexpr int XO = XB ? HPB : 0;
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) {
+      const uint32_t an = en + ad[m];
+      const F2 ie = lds64<XO + PRB>(an), iw = lds64<XO - PRB>(an);
+      F2 ss = add2(add2(add2(ie, iw), jn[m]), js[m]);
+      if (!XB) {
+        // cells (A0,A1): k+1 = own (B0,B1) ; k-1 = (B1 of the unit to the left, own B0)
+        const float bl = __shfl_up_sync(0xffffffffu, hi(wc[m].b), 1);
+        ss = add2(ss, wc[m].b);
+        ss = pk(lo(ss) + bl, hi(ss) + lo(wc[m].b));
+      } else {
+        // cells (B0,B1): k+1 = (own A1, A0 of the unit to the right) ; k-1 = own (A0,A1)
+        const float ar = __shfl_down_sync(0xffffffffu, lo(wc[m].a), 1);
+        ss = pk(lo(ss) + hi(wc[m].a), hi(ss) + ar);
+        ss = add2(ss, wc[m].a);
+      }
+      num[m] = sub2(ss, bb[m]);
+    }
+  };
+  auto bit = [&](unsigned f, int b) -> bool { return ((f >> b) & 1u) != 0u; };
+  auto sel = [&](bool c, F2 x, F2 y, bool c2) -> F2 {   // (c ? x.lo : y.lo, c2 ? x.hi : y.hi)
+    return pk(c ? lo(x) : lo(y), c2 ? hi(x) : hi(y));
+  };
+
+  // One step.  C = u % 4 (which register set holds which plane), XB = the red cells of plane s+1 (and the
+  // black cells of plane s-1... of the OTHER position) -- both compile-time, see the unrolled loop below.
+  auto step = [&](int u, auto cc, auto xb) {
+    constexpr int C = decltype(cc)::value;
+    constexpr bool XB = decltype(xb)::value;       // position of the reds of plane s+1; blacks of plane s-1 are !XB
+    constexpr int XO = XB ? HPB : 0, YO = XB ? 0 : HPB;
+    U4 (&wm1)[CPT] = P[(C + 3) & 3];
+    U4 (&w0)[CPT] = P[C];
+    U4 (&w1)[CPT] = P[(C + 1) & 3];
+    U4 (&w2)[CPT] = P[(C + 2) & 3];
     const int s = pl0 + u;
-    const int r0 = ring, r1 = (ring == 2) ? 0 : ring + 1, r2 = (ring == 0) ? 2 : ring - 1;   // u%3, (u+1)%3, (u+2)%3
-    const uint32_t e0 = dei + (uint32_t)r0 * TB, e1 = dei + (uint32_t)r1 * TB, e2 = dei + (uint32_t)r2 * TB;
-    const int pphase = (ring == 0) ? phase : phase ^ 1;        // ((u+2)/3)&1
-    mbar_wait(&bars[r2], (uint32_t)pphase);
-    {
-      const uint32_t rp = raw_p + (uint32_t)r2 * TB;
+    const uint32_t em1 = dei + (uint32_t)((C + 3) & 3) * TB, e1 = dei + (uint32_t)((C + 1) & 3) * TB,
+                   e2 = dei + (uint32_t)((C + 2) & 3) * TB;
+    // j-1 neighbours of the blacks of plane s-1: reds of plane s-2, still in the registers that
+    // receive plane s+2 below
+    F2 jsk[CPT];
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) jsk[m] = XB ? w2[m].a : w2[m].b;
+    if (u + 2 < npl) {
+      mbar_wait_a(bar0 + 8u * (uint32_t)sp, (uint32_t)pp);
+      const uint32_t rp = raw_p + (uint32_t)sp * TB;
 #pragma unroll
       for (int m = 0; m < CPT; ++m) w2[m] = lds_unit(rp + araw[m]);
 #pragma unroll
       for (int m = 0; m < CPT; ++m) { sts64<0>(e2 + ad[m], w2[m].a); sts64<HPB>(e2 + ad[m], w2[m].b); }
     }
-    mbar_wait(&bars[NSP + r0], (uint32_t)phase);
-    {
-      const uint32_t rbp = raw_b + (uint32_t)r0 * TB;
+    U4 bc[CPT];
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) bc[m] = U4{0ull, 0ull};
+    if (u < nbpl) {
+      mbar_wait_a(bar0 + 8u * (uint32_t)(NSP_ + sb), (uint32_t)pb);
+      const uint32_t rbp = raw_b + (uint32_t)sb * TB;
 #pragma unroll
       for (int m = 0; m < CPT; ++m) bc[m] = lds_unit(rbp + araw[m]);
     }
-    const bool do_red = (s + 1 >= a.jr0 && s + 1 <= a.jr1);      // CTA-uniform
+    // step-uniform activity: reds of plane s+1, blacks of plane s-1
+    const bool do_red = (s + 1 >= a.jr0 && s + 1 <= a.jr1);
     const bool red_owned = (s + 1 >= ja && s + 1 <= jb);
-    const bool do_black = (s >= ja && s <= jb);
-    // A is the red cell of plane s+1 (and the black cell of plane s) iff (par + s + 1) is even  (warp-uniform)
-    const bool xa = ((par + (unsigned)(s + 1)) & 1u) == 0u;
+    const bool do_black = (s - 1 >= ja && s - 1 <= jb);
+    const unsigned fR = do_red ? (XB ? (fl >> 4) : fl) & 0xfu : 0u;                 // bit m*2+e
+    const unsigned fRO = (do_red && red_owned) ? (XB ? (fl >> 12) : (fl >> 8)) & 0xfu : 0u;
+    const unsigned fK = do_black ? (XB ? (fl >> 8) : (fl >> 12)) & 0xfu : 0u;      // blacks sit at !XB
+    const unsigned fS = do_black ? (fl >> 16) & 0x3u : 0u;
 
-    // One relaxation of the X cells (X = A: xb false, X = B: xb true) of plane `wc` for all units of the
-    // thread.  en = de-interleaved copy of that plane, wn/ws = planes j+1 / j-1, bb = right-hand side.
-    auto relax = [&](auto xb, const uint32_t en, U4 (&wc)[CPT], const U4 (&wn)[CPT], const U4 (&ws)[CPT], const U4 (&bb)[CPT],
-                     const uint2 (&msk)[CPT], F2 (&dp)[CPT]) {
-      constexpr bool XB = decltype(xb)::value;
-      constexpr int XO = XB ? HPB : 0;
-      F2 num[CPT], quo[CPT];
+    F2 numR[CPT], numK[CPT], jnR[CPT], jsR[CPT], bbR[CPT], jnK[CPT];
 #pragma unroll
-      for (int m = 0; m < CPT; ++m) {
-        const uint32_t an = en + ad[m];
-        const F2 ie = lds64<XO + PRB>(an), iw = lds64<XO - PRB>(an);
-        F2 ss = add2(ie, iw);                                    // i+1, i-1
-        if (!XB) {
-          // cells (A0,A1): k+1 = own (B0,B1) ; k-1 = (B1 of the unit to the left, own B0)
-          const float bl = __shfl_up_sync(0xffffffffu, hi(wc[m].b), 1);
-          ss = add2(add2(add2(ss, wn[m].a), ws[m].a), wc[m].b);  // j+1, j-1, k+1
-          ss = pk(lo(ss) + bl, hi(ss) + lo(wc[m].b));            // k-1
-          num[m] = sub2(ss, bb[m].a);
-        } else {
-          // cells (B0,B1): k+1 = (own A1, A0 of the unit to the right) ; k-1 = own (A0,A1)
-          const float ar = __shfl_down_sync(0xffffffffu, lo(wc[m].a), 1);
-          ss = add2(add2(ss, wn[m].b), ws[m].b);                 // j+1, j-1
-          ss = pk(lo(ss) + hi(wc[m].a), hi(ss) + ar);            // k+1
-          ss = add2(ss, wc[m].a);                                // k-1
-          num[m] = sub2(ss, bb[m].b);
-        }
-        quo[m] = div6_2(num[m]);
-      }
-      // numerators outside the verified range of the fast division (tiny, huge, -0, non-finite): rare
+    for (int m = 0; m < CPT; ++m) {
+      jnR[m] = XB ? w2[m].b : w2[m].a;  jsR[m] = XB ? w0[m].b : w0[m].a;  bbR[m] = XB ? bc[m].b : bc[m].a;
+      jnK[m] = XB ? w0[m].a : w0[m].b;
+    }
+    numer(xb, e1, w1, jnR, jsR, bbR, numR);
+    numer(std::integral_constant<bool, !XB>{}, em1, wm1, jnK, jsk, hb[C & 1], numK);
+    F2 quoR[CPT], quoK[CPT];
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) { quoR[m] = div6_2(numR[m]); quoK[m] = div6_2(numK[m]); }
+    {  // numerators outside the verified range of the fast division (tiny, huge, -0, non-finite): rare
       float mx = 0.0f, mn = 3.0e38f;
       unsigned orb = 0u;
 #pragma unroll
       for (int m = 0; m < CPT; ++m) {
-        const float n0 = lo(num[m]), n1 = hi(num[m]);
-        mx = fmaxf(mx, fmaxf(fabsf(n0), fabsf(n1)));
-        mn = fminf(mn, fminf(fabsf(n0), fabsf(n1)));
-        orb |= __float_as_uint(n0) | __float_as_uint(n1);
+        const float n0 = lo(numR[m]), n1 = hi(numR[m]), n2 = lo(numK[m]), n3 = hi(numK[m]);
+        mx = fmaxf(fmaxf(mx, fmaxf(fabsf(n0), fabsf(n1))), fmaxf(fabsf(n2), fabsf(n3)));
+        mn = fminf(fminf(mn, fminf(fabsf(n0), fabsf(n1))), fminf(fabsf(n2), fabsf(n3)));
+        orb |= __float_as_uint(n0) | __float_as_uint(n1) | __float_as_uint(n2) | __float_as_uint(n3);
       }
-      if (!(orb == 0u || (mn >= 0x1p-123f && mx < 0x1p57f))) {
-        static_assert(CPT % 2 == 0, "rare-division fix works on groups of two units");
-#pragma unroll
-        for (int m = 0; m < CPT; m += 2) {
-          const float4 f = div6_fix4(make_float4(lo(num[m]), hi(num[m]), lo(num[m + 1]), hi(num[m + 1])),
-                                     make_float4(lo(quo[m]), hi(quo[m]), lo(quo[m + 1]), hi(quo[m + 1])));
-          quo[m] = pk(f.x, f.y); quo[m + 1] = pk(f.z, f.w);
-        }
+      if (!((mn >= 0x1p-123f && mx < 0x1p57f) || orb == 0u)) {
+        const float4 f = div6_fix4(make_float4(lo(numR[0]), hi(numR[0]), lo(numR[1]), hi(numR[1])),
+                                   make_float4(lo(quoR[0]), hi(quoR[0]), lo(quoR[1]), hi(quoR[1])));
+        quoR[0] = pk(f.x, f.y); quoR[1] = pk(f.z, f.w);
+        const float4 h = div6_fix4(make_float4(lo(numK[0]), hi(numK[0]), lo(numK[1]), hi(numK[1])),
+                                   make_float4(lo(quoK[0]), hi(quoK[0]), lo(quoK[1]), hi(quoK[1])));
+        quoK[0] = pk(h.x, h.y); quoK[1] = pk(h.z, h.w);
       }
-#pragma unroll
-      for (int m = 0; m < CPT; ++m) {
-        const F2 pp = XB ? wc[m].b : wc[m].a;
-        dp[m] = mul2(sub2(quo[m], pp), omg2);                    // ((ss-b)/dd - p)*omg
-        const F2 nv = sel2(add2(pp, dp[m]), pp, msk[m]);         // p + dp where the cell may move
-        if (XB) wc[m].b = nv; else wc[m].a = nv;
-      }
-    };
-    auto both = [&](auto xb) {
-      constexpr bool XB = decltype(xb)::value;
-      constexpr int XO = XB ? HPB : 0;
-      F2 dp[CPT];
-      if (do_red) {
-        relax(xb, e1, w1, w2, w0, bc, MR[XB], dp);
-#pragma unroll
-        for (int m = 0; m < CPT; ++m) sts64<XO>(e1 + ad[m], XB ? w1[m].b : w1[m].a);
-        if (red_owned) {
-#pragma unroll
-          for (int m = 0; m < CPT; ++m) {
-            const F2 dk = and2(dp[m], MK[XB][m]);
-            const F2 d2 = mul2(dk, dk);
-            acc[0] += (double)lo(d2);
-            acc[0] += (double)hi(d2);
-          }
-        }
-      }
-      if (do_black) {
-        relax(xb, e0, w0, w1, wm1, bp, MK[XB], dp);
-#pragma unroll
-        for (int m = 0; m < CPT; ++m) {
-          const F2 dk = and2(dp[m], MK[XB][m]);
-          const F2 d2 = mul2(dk, dk);
-          acc[0] += (double)lo(d2);
-          acc[0] += (double)hi(d2);
-          stg_unit_if(outp[m], w0[m], stf[m]);
-        }
-      }
-    };
-    if (xa) both(std::false_type{}); else both(std::true_type{});
-#pragma unroll
-    for (int m = 0; m < CPT; ++m) outp[m] += G.plane;
-    __syncthreads();
-    if (tid == 0) {   // both slots consumed by every thread: refill them three planes ahead
-      if (u + 2 + NSP < npl) issue_p(u + 2 + NSP);
-      if (u + NSB < nbpl) issue_b(u + NSB);
     }
-    if (ring == 2) { ring = 0; phase ^= 1; } else ++ring;
+    const F2 zero2 = 0ull;
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) {
+      // reds of plane s+1:  dp = ((ss-b)/dd - p)*omg ; p += dp   (cz_solver.f90:474-476)
+      const F2 ppR = XB ? w1[m].b : w1[m].a;
+      const F2 dpR = mul2(sub2(quoR[m], ppR), omg2);
+      const F2 nvR = sel(bit(fR, m * 2), add2(ppR, dpR), ppR, bit(fR, m * 2 + 1));
+      if (XB) w1[m].b = nvR; else w1[m].a = nvR;
+      sts64<XO>(e1 + ad[m], nvR);
+      const F2 dkR = sel(bit(fRO, m * 2), dpR, zero2, bit(fRO, m * 2 + 1));
+      const F2 d2R = mul2(dkR, dkR);
+      // blacks of plane s-1
+      const F2 ppK = XB ? wm1[m].a : wm1[m].b;
+      const F2 dpK = mul2(sub2(quoK[m], ppK), omg2);
+      const F2 nvK = sel(bit(fK, m * 2), add2(ppK, dpK), ppK, bit(fK, m * 2 + 1));
+      if (XB) wm1[m].a = nvK; else wm1[m].b = nvK;
+      const F2 dkK = sel(bit(fK, m * 2), dpK, zero2, bit(fK, m * 2 + 1));
+      const F2 d2K = mul2(dkK, dkK);
+      acc[0] += (double)lo(d2R);
+      acc[0] += (double)hi(d2R);
+      acc[0] += (double)lo(d2K);
+      acc[0] += (double)hi(d2K);
+      stg_unit_if(outp[m], wm1[m], (fS >> m) & 1u);
+      outp[m] += G.plane;
+      hb[C & 1][m] = XB ? bc[m].a : bc[m].b;     // right-hand side of the blacks of plane s+1 (used at step u+2)
+    }
+    (void)YO;
+    __syncthreads();
+    if (tid == 0) {   // the two raw slots read in this step are free: refill them
+      if (u + 2 + NSP_ < npl) issue_p(u + 2 + NSP_);
+      if (u + NSB_ < nbpl) issue_b(u + NSB_);
+    }
+    if (++sp == NSP_) { sp = 0; pp ^= 1; }
+    if (++sb == NSB_) { sb = 0; pb ^= 1; }
   };
-  for (int u = 0; u < nsteps; u += 4) {
-    step(u, cm1, c0, c1, c2, bprev, bcur);
-    if (u + 1 >= nsteps) break;
-    step(u + 1, c0, c1, c2, cm1, bcur, bprev);
-    if (u + 2 >= nsteps) break;
-    step(u + 2, c1, c2, cm1, c0, bprev, bcur);
-    if (u + 3 >= nsteps) break;
-    step(u + 3, c2, cm1, c0, c1, bcur, bprev);
+  // A is the red cell of plane s+1 iff (par + s + 1) is even (warp-uniform); it alternates with the step,
+  // so the 4x unrolled body exists in two variants (A-B-A-B and B-A-B-A) chosen once.
+  using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
+  using I2 = std::integral_constant<int, 2>; using I3 = std::integral_constant<int, 3>;
+  if (((par + (unsigned)(pl0 + 1)) & 1u) == 0u) {
+    for (int u = 0; u < nsteps; u += 4) {
+      step(u, I0{}, std::false_type{});
+      if (u + 1 >= nsteps) break;
+      step(u + 1, I1{}, std::true_type{});
+      if (u + 2 >= nsteps) break;
+      step(u + 2, I2{}, std::false_type{});
+      if (u + 3 >= nsteps) break;
+      step(u + 3, I3{}, std::true_type{});
+    }
+  } else {
+    for (int u = 0; u < nsteps; u += 4) {
+      step(u, I0{}, std::true_type{});
+      if (u + 1 >= nsteps) break;
+      step(u + 1, I1{}, std::false_type{});
+      if (u + 2 >= nsteps) break;
+      step(u + 2, I2{}, std::true_type{});
+      if (u + 3 >= nsteps) break;
+      step(u + 3, I3{}, std::false_type{});
+    }
   }
   grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
 }
