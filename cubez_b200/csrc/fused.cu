@@ -614,7 +614,7 @@ void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const R
 
 int march_cfg() {
   static int cfg = -1;
-  if (cfg < 0) { const char* e = getenv("CZB_MARCH_CFG"); cfg = e ? atoi(e) : 2; }
+  if (cfg < 0) { const char* e = getenv("CZB_MARCH_CFG"); cfg = e ? atoi(e) : 4; }
   return cfg;
 }
 int march_rows(int cfg) {

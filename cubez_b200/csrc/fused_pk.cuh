@@ -21,9 +21,9 @@
 
 typedef unsigned long long F2;   // two packed floats: low word = first cell, high word = second
 
-__device__ __forceinline__ F2 pk(float x, float y) { F2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(x), "f"(y)); return r; }
-__device__ __forceinline__ float lo(F2 v) { float x, y; asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(v)); return x; }
-__device__ __forceinline__ float hi(F2 v) { float x, y; asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(v)); return y; }
+__device__ __forceinline__ F2 pk(float x, float y) { return (F2)__float_as_uint(x) | ((F2)__float_as_uint(y) << 32); }
+__device__ __forceinline__ float lo(F2 v) { return __uint_as_float((unsigned)v); }
+__device__ __forceinline__ float hi(F2 v) { return __uint_as_float((unsigned)(v >> 32)); }
 __device__ __forceinline__ F2 add2(F2 a, F2 b) { F2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ F2 sub2(F2 a, F2 b) { F2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ F2 mul2(F2 a, F2 b) { F2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
@@ -341,23 +341,24 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
         quoK[0] = pk(h.x, h.y); quoK[1] = pk(h.z, h.w);
       }
     }
-    const F2 zero2 = 0ull;
+    // A cell that must not move gets dp = -0.0: p + (-0) == p bit for bit (also for p = +-0) and
+    // (-0)^2 adds nothing to the residual, so one select per cell serves both.
+    const F2 nz2 = pk(-0.0f, -0.0f);
 #pragma unroll
     for (int m = 0; m < CPT; ++m) {
       // reds of plane s+1:  dp = ((ss-b)/dd - p)*omg ; p += dp   (cz_solver.f90:474-476)
       const F2 ppR = XB ? w1[m].b : w1[m].a;
       const F2 dpR = mul2(sub2(quoR[m], ppR), omg2);
-      const F2 nvR = sel(bit(fR, m * 2), add2(ppR, dpR), ppR, bit(fR, m * 2 + 1));
+      const F2 nvR = add2(ppR, sel(bit(fR, m * 2), dpR, nz2, bit(fR, m * 2 + 1)));
       if (XB) w1[m].b = nvR; else w1[m].a = nvR;
       sts64<XO>(e1 + ad[m], nvR);
-      const F2 dkR = sel(bit(fRO, m * 2), dpR, zero2, bit(fRO, m * 2 + 1));
+      const F2 dkR = sel(bit(fRO, m * 2), dpR, nz2, bit(fRO, m * 2 + 1));
       const F2 d2R = mul2(dkR, dkR);
       // blacks of plane s-1
       const F2 ppK = XB ? wm1[m].a : wm1[m].b;
-      const F2 dpK = mul2(sub2(quoK[m], ppK), omg2);
-      const F2 nvK = sel(bit(fK, m * 2), add2(ppK, dpK), ppK, bit(fK, m * 2 + 1));
+      const F2 dkK = sel(bit(fK, m * 2), mul2(sub2(quoK[m], ppK), omg2), nz2, bit(fK, m * 2 + 1));
+      const F2 nvK = add2(ppK, dkK);
       if (XB) wm1[m].a = nvK; else wm1[m].b = nvK;
-      const F2 dkK = sel(bit(fK, m * 2), dpK, zero2, bit(fK, m * 2 + 1));
       const F2 d2K = mul2(dkK, dkK);
       acc[0] += (double)lo(d2R);
       acc[0] += (double)hi(d2R);

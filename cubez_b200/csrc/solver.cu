@@ -244,12 +244,18 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (converge_check) {
         Comm_SUM(0);
         launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-        launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
+        // bc_k (cz_Poisson.cpp:226) is idempotent: the sweep never changes a boundary node and carries
+        // the boundary nodes it stores over from src, so once both ping-pong buffers have received the
+        // Dirichlet values (iterations 1 and 2) every later call would rewrite identical data.
+        if (it <= 2) launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
     else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
-    if (done_iters & 1) launch_copy_inner(launch(false), G, X, W);
+    if (done_iters & 1) {
+      launch_copy_inner(launch(false), G, X, W);
+      if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
+    }
   } else {
     auto body = [&](int) {
       Launch L = launch();
