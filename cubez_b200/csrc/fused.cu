@@ -87,6 +87,7 @@ struct MarchArgs {
   const LoopState* st;
   LoopState* acc_st; int slot; int add;
   RedBuf rb;
+  int slot2;              // packed MODE_AX: second accumulator (ap, ap), -1 = none
 };
 
 struct FinStoreF {
@@ -612,6 +613,22 @@ void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const R
 }
 #endif
 
+#ifndef _REAL_IS_DOUBLE_
+template <int MODE, int NT, int CPT, int NSP_, int NSB_>
+void launch_lin_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const REAL* b) {
+  constexpr int EI = NT / 32 * CPT;
+  dim3 grid(a.ntk * a.nti, a.njc, 1);
+  const size_t smem = (size_t)(NSP_ + (MODE == MODE_JAC ? NSB_ : 0) + 2) * EI * EKB * sizeof(float) + 1024;
+  static bool set = false;
+  if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_lin_pk<MODE, NT, CPT, NSP_, NSB_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+  const CUtensorMap& tp = tmap_for(p, a.G, EI);
+  const CUtensorMap& tb = (MODE == MODE_JAC) ? tmap_for(b, a.G, EI) : tp;
+  k_lin_pk<MODE, NT, CPT, NSP_, NSB_><<<grid, NT, smem, L.s>>>(tp, tb, a);
+  CZB_CHECK(cudaGetLastError());
+  count_launch();
+}
+#endif
+
 int march_cfg() {
   static int cfg = -1;
   if (cfg < 0) { const char* e = getenv("CZB_MARCH_CFG"); cfg = e ? atoi(e) : 4; }
@@ -625,9 +642,10 @@ int march_rows(int cfg) {
 #endif
 }
 
-bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_or_w, REAL* out, const REAL* cf,
-           REAL omg, int ip, int jr0, int jr1, int slot, bool add) {
-  if (!fused_eligible(G)) return false;
+// returns 0 = not eligible, 1 = done, 2 = done including the second accumulator slot2 (packed MODE_AX)
+int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_or_w, REAL* out, const REAL* cf,
+          REAL omg, int ip, int jr0, int jr1, int slot, bool add, int slot2 = -1) {
+  if (!fused_eligible(G)) return 0;
   MarchArgs a;
   a.G = G;
   const int cfg = march_cfg();
@@ -637,9 +655,11 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
   const int kst_c = G.kst + G.g - 1, ked_c = G.ked + G.g - 1;
 #ifndef _REAL_IS_DOUBLE_
   // packed-f32x2 kernel (fused_pk.cuh): the CubeZ operator only; needs 16-byte aligned units
-  const bool packed = (mode == MODE_RB2) && unit && cfg >= 2 && (G.nk % 4 == 0);
+  const bool packed = unit && cfg >= 2 && (G.nk % 4 == 0);
+  const bool lin = packed && mode != MODE_RB2;
 #else
   const bool packed = false;
+  const bool lin = false;
 #endif
   if (packed) {
     const int npairs = (ked_c >> 1) - ((kst_c >> 1) & ~1) + 1;     // tiles start at an even pair
@@ -649,7 +669,7 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
     a.ntk = (npairs + PR - 3) / (PR - 2);
   }
   const int ni = G.ied - G.ist + 1, nj = G.jed - G.jst + 1;
-  a.nti = (ni + a.ei - 5) / (a.ei - 4);
+  a.nti = lin ? (ni + a.ei - 3) / (a.ei - 2) : (ni + a.ei - 5) / (a.ei - 4);
   // j-chunks: enough CTAs for ~8 rounds over the SMs, chunks no shorter than 32 planes
   static int rounds = -1;
   if (rounds < 0) { const char* e = getenv("CZB_ROUNDS"); rounds = e ? atoi(e) : 8; }
@@ -658,7 +678,7 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
   if (njc < 1) njc = 1;
   a.jl = (nj + njc - 1) / njc;
   a.njc = (nj + a.jl - 1) / a.jl;
-  if ((size_t)a.ntk * a.nti * a.njc > L.rb_blocks) return false;
+  if ((size_t)a.ntk * a.nti * a.njc > L.rb_blocks) return 0;
   a.jr0 = jr0; a.jr1 = jr1; a.jb0 = G.jst; a.jb1 = G.jed;
   a.ip = ip;
   a.c = Coef7{cf[0], cf[1], cf[2], cf[3], cf[4], cf[5], cf[6]};
@@ -666,24 +686,30 @@ bool march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b
   a.out = out; a.w = (mode == MODE_AX) ? b_or_w : nullptr;
   a.st = L.st; a.acc_st = L.acc_st; a.slot = slot; a.add = add ? 1 : 0;
   a.rb = L.rb;
+  a.slot2 = lin ? slot2 : -1;
   const size_t T = (size_t)a.ei * EKB;
   const CUtensorMap& tp = tmap_for(p, G, a.ei);
   const CUtensorMap& tb = (mode == MODE_AX) ? tp : tmap_for(b_or_w, G, a.ei);
   // + 1 KB: halo columns read (and discard) neighbours up to one half-plane row past the last plane
   const size_t smem = ((mode == MODE_AX ? NSP : NSP + NSB) + 3) * T * sizeof(REAL) + 8 * (NSP + NSB) + 1024;
 #ifndef _REAL_IS_DOUBLE_
+  if (lin) {
+    if (mode == MODE_JAC) launch_lin_pk_t<MODE_JAC, 512, 2, 5, 4>(L, a, p, b_or_w);
+    else                  launch_lin_pk_t<MODE_AX, 512, 2, 6, 0>(L, a, p, b_or_w);
+    return (mode == MODE_AX && slot2 >= 0) ? 2 : 1;
+  }
   if (packed) {   // look-ahead (raw TMA slots for p, b): cfg 2 = 3+3, 3 = 4+3, 4 = 5+4, 5 = 5+5
     if (cfg == 3)      launch_rb2_pk_t<512, 2, 4, 3>(L, a, p, b_or_w);
     else if (cfg == 4) launch_rb2_pk_t<512, 2, 5, 4>(L, a, p, b_or_w);
     else if (cfg == 5) launch_rb2_pk_t<512, 2, 5, 5>(L, a, p, b_or_w);
     else               launch_rb2_pk_t<512, 2, 3, 3>(L, a, p, b_or_w);
-    return true;
+    return 1;
   }
 #endif
   if (mode == MODE_RB2)      launch_march_cfg<MODE_RB2>(cfg, L, a, tp, tb, unit, smem);
   else if (mode == MODE_JAC) launch_march_cfg<MODE_JAC>(cfg, L, a, tp, tb, unit, smem);
   else                       launch_march_cfg<MODE_AX>(cfg, L, a, tp, tb, unit, smem);
-  return true;
+  return 1;
 }
 
 }  // namespace
@@ -698,15 +724,15 @@ bool fused_eligible(const Geo& G) {
 
 bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf, REAL omg,
                       int ip, int jr0, int jr1, int slot, bool add) {
-  return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add);
+  return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add) != 0;
 }
 bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
                          REAL omg, int slot, bool add) {
-  return march(MODE_JAC, L, G, p, b, pnew, cf, omg, 0, G.jst, G.jed, slot, add);
+  return march(MODE_JAC, L, G, p, b, pnew, cf, omg, 0, G.jst, G.jed, slot, add) != 0;
 }
-bool launch_ax_fused(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf, const REAL* dotwith,
-                     int slot) {
-  return march(MODE_AX, L, G, p, dotwith, ap, cf, (REAL)0, 0, G.jst, G.jed, slot, false);
+int launch_ax_fused(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf, const REAL* dotwith,
+                    int slot, int slot2) {
+  return march(MODE_AX, L, G, p, dotwith, ap, cf, (REAL)0, 0, G.jst, G.jed, slot, false, slot2);
 }
 
 }  // namespace czb

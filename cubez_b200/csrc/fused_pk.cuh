@@ -78,6 +78,29 @@ __device__ __noinline__ float4 div6_fix4(float4 n, float4 q) {
   return q;
 }
 
+// ss = p(i+1) + p(i-1) + p(j+1) + p(j-1) + p(k+1) + p(k-1) in exactly this order (cz_solver.f90:339-344,
+// :468-473; cz_blas.f90:626-631) for the two X cells (XB false: A0,A1 ; true: B0,B1) of one unit.
+// an = shared address of the unit in the de-interleaved copy of the plane, wc = the plane (own
+// other-colour pairs are the k neighbours, plus one shuffle), jn / js = the X pairs of planes j+1 / j-1.
+template <bool XB, int HPB_, int PRB_>
+__device__ __forceinline__ F2 sum6_pk(uint32_t an, const U4& wc, F2 jn, F2 js) {
+  constexpr int XO = XB ? HPB_ : 0;
+  const F2 ie = lds64<XO + PRB_>(an), iw = lds64<XO - PRB_>(an);
+  F2 ss = add2(add2(add2(ie, iw), jn), js);
+  if (!XB) {
+    // cells (A0,A1): k+1 = own (B0,B1) ; k-1 = (B1 of the unit to the left, own B0)
+    const float bl = __shfl_up_sync(0xffffffffu, hi(wc.b), 1);
+    ss = add2(ss, wc.b);
+    ss = pk(lo(ss) + bl, hi(ss) + lo(wc.b));
+  } else {
+    // cells (B0,B1): k+1 = (own A1, A0 of the unit to the right) ; k-1 = own (A0,A1)
+    const float ar = __shfl_down_sync(0xffffffffu, lo(wc.a), 1);
+    ss = pk(lo(ss) + hi(wc.a), hi(ss) + ar);
+    ss = add2(ss, wc.a);
+  }
+  return ss;
+}
+
 constexpr int PKH = 2;          // halo pairs on each k side of a tile (one unit)
 constexpr int NDE = 4;          // de-interleaved plane copies kept in shared memory (planes s-1 .. s+2)
 
@@ -242,25 +265,8 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   auto numer = [&](auto xb, const uint32_t en, const U4 (&wc)[CPT], const F2 (&jn)[CPT], const F2 (&js)[CPT],
                    const F2 (&bb)[CPT], F2 (&num)[CPT]) {
     constexpr bool XB = decltype(xb)::value;
-    constexpr int XO = XB ? HPB : 0;
 #pragma unroll
-    for (int m = 0; m < CPT; ++m) {
-      const uint32_t an = en + ad[m];
-      const F2 ie = lds64<XO + PRB>(an), iw = lds64<XO - PRB>(an);
-      F2 ss = add2(add2(add2(ie, iw), jn[m]), js[m]);
-      if (!XB) {
-        // cells (A0,A1): k+1 = own (B0,B1) ; k-1 = (B1 of the unit to the left, own B0)
-        const float bl = __shfl_up_sync(0xffffffffu, hi(wc[m].b), 1);
-        ss = add2(ss, wc[m].b);
-        ss = pk(lo(ss) + bl, hi(ss) + lo(wc[m].b));
-      } else {
-        // cells (B0,B1): k+1 = (own A1, A0 of the unit to the right) ; k-1 = own (A0,A1)
-        const float ar = __shfl_down_sync(0xffffffffu, lo(wc[m].a), 1);
-        ss = pk(lo(ss) + hi(wc[m].a), hi(ss) + ar);
-        ss = add2(ss, wc[m].a);
-      }
-      num[m] = sub2(ss, bb[m]);
-    }
+    for (int m = 0; m < CPT; ++m) num[m] = sub2(sum6_pk<XB, HPB, PRB>(en + ad[m], wc[m], jn[m], js[m]), bb[m]);
   };
   auto bit = [&](unsigned f, int b) -> bool { return ((f >> b) & 1u) != 0u; };
   auto sel = [&](bool c, F2 x, F2 y, bool c2) -> F2 {   // (c ? x.lo : y.lo, c2 ? x.hi : y.hi)
@@ -403,4 +409,259 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
     }
   }
   grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
+}
+
+// ================================================================================================
+// One-plane-per-step packed kernels: every cell of plane j from the OLD planes j-1, j, j+1.
+//   MODE_JAC : relaxed Jacobi sweep (cz_solver.f90:284-387) without the copy-back pass, residual fused
+//   MODE_AX  : ap = ss - dd*p (blas_calc_ax, cz_blas.f90:579-644) fused with the dots (ap, w) and,
+//              when a.slot2 >= 0, (ap, ap)  -> PBiCGstab's q = A p^ + (q, r0) and t = A s^ + (t, s) + (t, t)
+// Same tile, unit and TMA machinery as k_rb2_pk; tile halo is one row on each i side.
+struct FinStore2F {
+  LoopState* st; int slot; int slot2;
+  __device__ void operator()(double (&tot)[2]) const {
+    if (st) { st->acc[slot] = tot[0]; if (slot2 >= 0) st->acc[slot2] = tot[1]; }
+  }
+};
+
+template <int MODE, int NT, int CPT, int NSP_, int NSB_>
+__global__ void __launch_bounds__(NT, 1)
+k_lin_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b, const MarchArgs a) {
+  if (a.st && a.st->done) return;
+  constexpr int RPW = NT / 32;
+  constexpr int EI = RPW * CPT;
+  constexpr int T = EI * EKB;
+  constexpr int TB = T * 4;
+  constexpr int HPB = TB / 2;
+  constexpr int PRB = PR * 4;
+  constexpr int NB = (MODE == MODE_JAC) ? NSB_ : 0;
+  static_assert(CPT == 2, "flag layout below assumes two units per thread");
+  const Geo& G = a.G;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  const uint32_t sm0 = smem_u32(smem_raw);
+  const uint32_t raw_p = sm0;                          // [NSP_][TB]
+  const uint32_t raw_b = raw_p + NSP_ * TB;            // [NB][TB]
+  const uint32_t dei = raw_b + NB * TB;                // [2][TB]
+  const uint32_t bar0 = dei + 2 * TB + 512;            // [NSP_ + NB] mbarriers (after a pad row)
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, wrow = tid >> 5;
+
+  const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk, jc = blockIdx.y;
+  const int kst_c = G.kst + G.g - 1, ist_c = G.ist + G.g - 1;
+  const int P0 = (((kst_c >> 1) & ~1) - PKH) + tk * (PR - 2 * PKH);
+  const int R0 = ist_c - 1 + ti * (EI - 2);
+  const int ja = a.jb0 + jc * a.jl;
+  const int jb = min(ja + a.jl - 1, a.jb1);
+  const int pl0 = ja - 1;                                          // first p plane fetched
+  const int nsteps = jb - ja + 1;                                  // plane j = ja + u
+  const int npl = nsteps + 2;
+
+  if (tid == 0) {
+    for (int s = 0; s < NSP_ + NB; ++s)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u * s) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  auto issue_plane = [&](uint32_t dst, uint32_t bar, const CUtensorMap* tm, int plane) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)TB) : "memory");
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(dst), "l"(tm), "r"(bar), "r"(2 * P0), "r"(R0), "r"(plane) : "memory");
+  };
+  auto issue_p = [&](int t) {
+    issue_plane(raw_p + (uint32_t)(t % NSP_) * TB, bar0 + 8u * (uint32_t)(t % NSP_), &tm_p, pl0 + t + G.g - 1);
+  };
+  auto issue_b = [&](int t) {   // right-hand side of plane ja + t
+    constexpr int NBD = NSB_ > 0 ? NSB_ : 1;
+    issue_plane(raw_b + (uint32_t)(t % NBD) * TB, bar0 + 8u * (uint32_t)(NSP_ + t % NBD), &tm_b, ja + t + G.g - 1);
+  };
+  if (tid == 0) {
+    for (int t = 0; t < NSP_ && t < npl; ++t) issue_p(t);
+    if (MODE == MODE_JAC) for (int t = 0; t < NSB_ && t < nsteps; ++t) issue_b(t);
+  }
+
+  // flag word: bit x*4+m*2+e = the X cell of pair e of unit m is an inner cell owned by this tile;
+  //            bit 8+m = unit m is stored
+  const float omg = a.omg;
+  const F2 omg2 = pk(omg, omg);
+  const int kc0 = 2 * (P0 + 2 * lane);
+  const bool unit_in = kc0 >= 0 && kc0 + 3 < G.nk;
+  uint32_t araw[CPT], ad[CPT];
+  unsigned fl = 0u;
+  float* outp[CPT];
+  const float* wp[CPT];
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) {
+    const int r = wrow + RPW * m;
+    araw[m] = (uint32_t)(r * EKB + 4 * lane) * 4u;
+    ad[m] = (uint32_t)(r * PR + 2 * lane) * 4u;
+    const int ic = R0 + r, iF = ic - G.g + 1;
+    const bool rowin = ic >= 0 && ic < G.ni && iF >= G.ist && iF <= G.ied;
+    const bool rO = rowin && r >= 1 && r <= EI - 2;
+    bool kany = false;
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int q = 2 * lane + e;
+      const bool ownq = (q >= PKH) && (q <= PR - 1 - PKH);
+#pragma unroll
+      for (int x = 0; x < 2; ++x) {
+        const int kc = 2 * (P0 + q) + x, kF = kc - G.g + 1;
+        const bool kin = kc >= 0 && kc < G.nk && kF >= G.kst && kF <= G.ked;
+        if (kin && ownq && rO) fl |= 1u << (x * 4 + m * 2 + e);
+        kany = kany || (kin && ownq);
+      }
+    }
+    const bool st = rO && kany && unit_in;
+    if (st) fl |= 1u << (8 + m);
+    const long long off = (long long)(ja + G.g - 1) * G.plane + (long long)G.nk * (st ? ic : 0) + (st ? kc0 : 0);
+    outp[m] = a.out + off;
+    wp[m] = (MODE == MODE_AX && a.w) ? a.w + off : nullptr;
+  }
+  auto bit = [&](int b) -> bool { return ((fl >> b) & 1u) != 0u; };
+  auto sel = [&](bool c, F2 x, F2 y, bool c2) -> F2 { return pk(c ? lo(x) : lo(y), c2 ? hi(x) : hi(y)); };
+
+  U4 P[3][CPT];
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) { P[0][m] = P[1][m] = P[2][m] = U4{0ull, 0ull}; }
+  double acc[2] = {0.0, 0.0};
+  float4 wv[CPT];      // MODE_AX: dot operand of the plane computed in this step (loaded one step ahead)
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) wv[m] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  // prologue: plane ja-1 -> P[0], plane ja -> P[1] + de-interleaved copy (slot 1)
+  mbar_wait_a(bar0, 0);
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) P[0][m] = lds_unit(raw_p + araw[m]);
+  mbar_wait_a(bar0 + 8, 0);
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) {
+    P[1][m] = lds_unit(raw_p + TB + araw[m]);
+    sts64<0>(dei + TB + ad[m], P[1][m].a); sts64<HPB>(dei + TB + ad[m], P[1][m].b);
+    if (MODE == MODE_AX && wp[m] && bit(8 + m)) wv[m] = __ldg(reinterpret_cast<const float4*>(wp[m]));
+  }
+  __syncthreads();
+  if (tid == 0) { if (NSP_ < npl) issue_p(NSP_); if (NSP_ + 1 < npl) issue_p(NSP_ + 1); }
+
+  int sp = 2 % NSP_, pp = (2 / NSP_) & 1;   // raw p slot / parity of plane index u+2
+  int sb = 0, pb = 0;                       // raw b slot / parity of plane index u
+  auto step = [&](int u, auto cc) {
+    constexpr int C = decltype(cc)::value;
+    U4 (&w0)[CPT] = P[C];
+    U4 (&w1)[CPT] = P[(C + 1) % 3];
+    U4 (&w2)[CPT] = P[(C + 2) % 3];
+    const uint32_t ecur = dei + (uint32_t)((u + 1) & 1) * TB, enext = dei + (uint32_t)(u & 1) * TB;
+    // plane j+1 (always exists: npl = nsteps + 2)
+    mbar_wait_a(bar0 + 8u * (uint32_t)sp, (uint32_t)pp);
+    {
+      const uint32_t rp = raw_p + (uint32_t)sp * TB;
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) w2[m] = lds_unit(rp + araw[m]);
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) { sts64<0>(enext + ad[m], w2[m].a); sts64<HPB>(enext + ad[m], w2[m].b); }
+    }
+    U4 bc[CPT];
+    float4 wn[CPT];
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) { bc[m] = U4{0ull, 0ull}; wn[m] = make_float4(0.f, 0.f, 0.f, 0.f); }
+    if (MODE == MODE_JAC) {
+      mbar_wait_a(bar0 + 8u * (uint32_t)(NSP_ + sb), (uint32_t)pb);
+      const uint32_t rbp = raw_b + (uint32_t)sb * TB;
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) bc[m] = lds_unit(rbp + araw[m]);
+    } else {
+#pragma unroll
+      for (int m = 0; m < CPT; ++m)   // dot operand of the NEXT plane
+        if (wp[m] && bit(8 + m) && u + 1 < nsteps) wn[m] = __ldg(reinterpret_cast<const float4*>(wp[m] + G.plane));
+    }
+    F2 ssA[CPT], ssB[CPT];
+#pragma unroll
+    for (int m = 0; m < CPT; ++m) {
+      ssA[m] = sum6_pk<false, HPB, PRB>(ecur + ad[m], w1[m], w2[m].a, w0[m].a);
+      ssB[m] = sum6_pk<true, HPB, PRB>(ecur + ad[m], w1[m], w2[m].b, w0[m].b);
+    }
+    if (MODE == MODE_JAC) {
+      F2 numA[CPT], numB[CPT], quoA[CPT], quoB[CPT];
+      float mx = 0.0f, mn = 3.0e38f;
+      unsigned orb = 0u;
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) {
+        numA[m] = sub2(ssA[m], bc[m].a); numB[m] = sub2(ssB[m], bc[m].b);
+        quoA[m] = div6_2(numA[m]); quoB[m] = div6_2(numB[m]);
+        const float n0 = lo(numA[m]), n1 = hi(numA[m]), n2 = lo(numB[m]), n3 = hi(numB[m]);
+        mx = fmaxf(fmaxf(mx, fmaxf(fabsf(n0), fabsf(n1))), fmaxf(fabsf(n2), fabsf(n3)));
+        mn = fminf(fminf(mn, fminf(fabsf(n0), fabsf(n1))), fminf(fabsf(n2), fabsf(n3)));
+        orb |= __float_as_uint(n0) | __float_as_uint(n1) | __float_as_uint(n2) | __float_as_uint(n3);
+      }
+      if (!((mn >= 0x1p-123f && mx < 0x1p57f) || orb == 0u)) {
+        const float4 f = div6_fix4(make_float4(lo(numA[0]), hi(numA[0]), lo(numA[1]), hi(numA[1])),
+                                   make_float4(lo(quoA[0]), hi(quoA[0]), lo(quoA[1]), hi(quoA[1])));
+        quoA[0] = pk(f.x, f.y); quoA[1] = pk(f.z, f.w);
+        const float4 h = div6_fix4(make_float4(lo(numB[0]), hi(numB[0]), lo(numB[1]), hi(numB[1])),
+                                   make_float4(lo(quoB[0]), hi(quoB[0]), lo(quoB[1]), hi(quoB[1])));
+        quoB[0] = pk(h.x, h.y); quoB[1] = pk(h.z, h.w);
+      }
+      const F2 nz2 = pk(-0.0f, -0.0f);
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) {
+        // dp = ((ss-b)/dd - p)*omg ; wk2 = p + dp ; res += dp*dp   (cz_solver.f90:345-348)
+        const F2 dA = sel(bit(m * 2), mul2(sub2(quoA[m], w1[m].a), omg2), nz2, bit(m * 2 + 1));
+        const F2 dB = sel(bit(4 + m * 2), mul2(sub2(quoB[m], w1[m].b), omg2), nz2, bit(4 + m * 2 + 1));
+        const U4 o = U4{add2(w1[m].a, dA), add2(w1[m].b, dB)};
+        const F2 qA = mul2(dA, dA), qB = mul2(dB, dB);
+        acc[0] += (double)lo(qA); acc[0] += (double)hi(qA);
+        acc[0] += (double)lo(qB); acc[0] += (double)hi(qB);
+        stg_unit_if(outp[m], o, (fl >> (8 + m)) & 1u);
+        outp[m] += G.plane;
+      }
+    } else {
+      const F2 zero2 = 0ull;
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) {
+        // ap = ss - dd*p on inner cells (cz_blas.f90:626-632); the other cells of a stored unit are
+        // boundary nodes of q / t_, which the reference leaves at their initial 0.
+        // dd*p with dd = 6 is formed as (4p) + (2p): doublings are exact, so the single rounding of the
+        // sum is RN(6p) -- and there is no multiply that ptxas could contract with the subtraction
+        // into an FFMA2 (it does so for mul.rn.f32x2 + sub.rn.f32x2, which changes the rounding).
+        const F2 a2 = add2(w1[m].a, w1[m].a), b2 = add2(w1[m].b, w1[m].b);
+        const F2 a6 = add2(add2(a2, a2), a2), b6 = add2(add2(b2, b2), b2);
+        const F2 vA = sel(bit(m * 2), sub2(ssA[m], a6), zero2, bit(m * 2 + 1));
+        const F2 vB = sel(bit(4 + m * 2), sub2(ssB[m], b6), zero2, bit(4 + m * 2 + 1));
+        if (wp[m]) {
+          const F2 dA = mul2(vA, pk(wv[m].x, wv[m].z)), dB = mul2(vB, pk(wv[m].y, wv[m].w));
+          acc[0] += (double)lo(dA); acc[0] += (double)hi(dA);
+          acc[0] += (double)lo(dB); acc[0] += (double)hi(dB);
+          wp[m] += G.plane;
+        }
+        if (a.slot2 >= 0) {
+          const F2 qA = mul2(vA, vA), qB = mul2(vB, vB);
+          acc[1] += (double)lo(qA); acc[1] += (double)hi(qA);
+          acc[1] += (double)lo(qB); acc[1] += (double)hi(qB);
+        }
+        stg_unit_if(outp[m], U4{vA, vB}, (fl >> (8 + m)) & 1u);
+        outp[m] += G.plane;
+        wv[m] = wn[m];
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      if (u + 2 + NSP_ < npl) issue_p(u + 2 + NSP_);
+      if (MODE == MODE_JAC && u + NSB_ < nsteps) issue_b(u + NSB_);
+    }
+    if (++sp == NSP_) { sp = 0; pp ^= 1; }
+    if (MODE == MODE_JAC) { if (++sb == NSB_) { sb = 0; pb ^= 1; } }
+  };
+  using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
+  using I2 = std::integral_constant<int, 2>;
+  for (int u = 0; u < nsteps; u += 3) {
+    step(u, I0{});
+    if (u + 1 >= nsteps) break;
+    step(u + 1, I1{});
+    if (u + 2 >= nsteps) break;
+    step(u + 2, I2{});
+  }
+  if (MODE == MODE_JAC) {
+    double a1[1] = {acc[0]};
+    grid_reduce<1>(a1, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
+  } else {
+    grid_reduce<2>(acc, a.rb, FinStore2F{a.acc_st, a.slot, a.slot2});
+  }
 }

@@ -79,9 +79,11 @@ bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, 
                       REAL omg, int ip, int jr0, int jr1, int slot, bool add);
 bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
                          REAL omg, int slot, bool add);
-// ap = A p on inner cells, 0 on the other cells of stored pairs; acc[slot] = (ap, dotwith)
-bool launch_ax_fused(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf, const REAL* dotwith,
-                     int slot);
+// ap = A p on inner cells, 0 on the other cells of stored pairs; acc[slot] = (ap, dotwith).
+// Returns 0 = not eligible (use launch_calc_ax), 1 = done, 2 = done and acc[slot2] = (ap, ap) as well
+// (slot2 < 0: not wanted).
+int launch_ax_fused(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf, const REAL* dotwith,
+                    int slot, int slot2 = -1);
 
 // ---- loop control (tiny kernels) --------------------------------------------------------
 void launch_state_reset(const Launch& L, LoopState* st);

@@ -440,8 +440,12 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
     Comm_S(s, 1);                                                            // :438
     CZB_CHECK(cudaMemsetAsync(s_, 0, bytes, R.stream));                      // :441
     Preconditioner(s_, s, pflop, pc_type);                                   // :445
-    if (!(variant == 0 && launch_ax_fused(L, G, t_, s_, cf, s, 2))) launch_calc_ax(L, G, t_, s_, cf, s, 2);   // t = A s_, (t,s) :457-464
-    launch_dot1(L, G, t_, 3); Comm_SUM(2, 2); scalar(2);                     // (t,t), omega
+    {   // t = A s_, (t,s), (t,t) :457-464
+      const int f = (variant == 0) ? launch_ax_fused(L, G, t_, s_, cf, s, 2, 3) : 0;
+      if (f == 0) launch_calc_ax(L, G, t_, s_, cf, s, 2);
+      if (f != 2) launch_dot1(L, G, t_, 3);
+    }
+    Comm_SUM(2, 2); scalar(2);                                               // omega
     launch_bicg2(L, G, X, p_, s_, 0, 0, &sc[SC_ALPHA], &sc[SC_OMEGA]);       // x += alpha p_ + omega s_ :470
     launch_triad(L, G, r, t_, s, 0, &sc[SC_NEG_OMEGA]);                      // r = s - omega t :476
     launch_dot1(L, G, r, 4);                                                 // :481
@@ -550,6 +554,38 @@ int czb_ctx_comm_init(czb_ctx* c, int nranks, int rank, const void* id128) {
   if (c->comm) comm_destroy(c->comm);
   c->comm = comm_create(nranks, rank, id128, c->nID[2], c->nID[3]);
   return 0;
+}
+
+static double read_state_acc(czb_ctx* c, int slot) {
+  Runtime& R = rt();
+  CZB_CHECK(cudaMemcpyAsync(&c->h_state[0], c->d_state, sizeof(LoopState), cudaMemcpyDeviceToHost, R.stream));
+  R.sync();
+  return c->h_state[0].acc[slot];
+}
+
+int czb_sweep_rbsor(czb_ctx* c, const CZB_REAL* x, CZB_REAL* xnew, const CZB_REAL* b, CZB_REAL omg, double* res) {
+  Launch L = c->launch(false);
+  const int jr0 = c->G.jst - (c->nID[2] >= 0 ? 1 : 0), jr1 = c->G.jed + (c->nID[3] >= 0 ? 1 : 0);
+  if (!launch_rb2_fused(L, c->G, x, xnew, b, c->cf, omg, c->parity_ip(), jr0, jr1, 0, false)) return 0;
+  if (res) *res = read_state_acc(c, 0);
+  return 1;
+}
+
+int czb_sweep_jacobi(czb_ctx* c, const CZB_REAL* x, CZB_REAL* xnew, const CZB_REAL* b, CZB_REAL omg, double* res) {
+  Launch L = c->launch(false);
+  if (!launch_jacobi_fused(L, c->G, x, xnew, b, c->cf, omg, 0, false)) return 0;
+  if (res) *res = read_state_acc(c, 0);
+  return 1;
+}
+
+int czb_apply_ax(czb_ctx* c, CZB_REAL* ap, const CZB_REAL* p, const CZB_REAL* w, double* dot_w, double* dot_self) {
+  Launch L = c->launch(false);
+  const int f = launch_ax_fused(L, c->G, ap, p, c->cf, w, 0, dot_self ? 1 : -1);
+  if (f == 0) return 0;
+  if (dot_self && f != 2) launch_dot1(L, c->G, ap, 1);
+  if (dot_w && w) *dot_w = read_state_acc(c, 0);
+  if (dot_self) *dot_self = read_state_acc(c, 1);
+  return 1;
 }
 
 int czb_solve(czb_ctx* c, const char* solver, const char* precond, CZB_REAL* X, CZB_REAL* B, int itr_max,

@@ -28,6 +28,7 @@ CZB_SYMBOLS = [
     "czb_memcpy_h2d", "czb_memcpy_d2h", "czb_launch_count", "czb_staged_bytes", "czb_slab_decompose",
     "czb_ctx_create", "czb_ctx_destroy", "czb_ctx_set_eps", "czb_ctx_set_res_normal", "czb_ctx_set_head",
     "czb_ctx_set_variant", "czb_ctx_bc_k", "czb_comm_unique_id", "czb_ctx_comm_init", "czb_solve", "czb_last_solve_ms",
+    "czb_sweep_rbsor", "czb_sweep_jacobi", "czb_apply_ax",
 ]
 
 
@@ -65,4 +66,7 @@ def bind_czb_symbols(dll, real_ctype):
     dll.czb_solve.argtypes = [P, C.c_char_p, C.c_char_p, P, P, C.c_int, real_ctype, PD, PD, C.c_int, PD]
     dll.czb_solve.restype = C.c_int
     dll.czb_last_solve_ms.argtypes = [P]; dll.czb_last_solve_ms.restype = C.c_double
+    dll.czb_sweep_rbsor.argtypes = [P, P, P, P, real_ctype, PD]; dll.czb_sweep_rbsor.restype = C.c_int
+    dll.czb_sweep_jacobi.argtypes = [P, P, P, P, real_ctype, PD]; dll.czb_sweep_jacobi.restype = C.c_int
+    dll.czb_apply_ax.argtypes = [P, P, P, P, PD, PD]; dll.czb_apply_ax.restype = C.c_int
     return dll

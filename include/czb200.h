@@ -171,6 +171,20 @@ void czb_ctx_bc_k(czb_ctx* c, CZB_REAL* p);           /* 0 = auto (fused), 1 = b
 int czb_comm_unique_id(void* id128);
 int czb_ctx_comm_init(czb_ctx* c, int nranks, int rank, const void* id128);
 
+/* Single fused sweeps on DEVICE fields: the kernels the solve loops below are built from (fused.cu /
+ * fused_pk.cuh), exposed so that they can be checked one call at a time against the per-colour reference
+ * kernels.  All use the context's geometry and the CubeZ coefficients cf = {1,1,1,1,1,1,6}.  *res / *dot
+ * are overwritten.  Return 1 when the fused TMA kernel ran, 0 when the geometry is not eligible (row
+ * pitch not a multiple of 16 bytes) and nothing was done.
+ *   czb_sweep_rbsor : xnew = both colours of psor2sma_core_ (colour 0 then 1, cz_Poisson.cpp:197-203)
+ *                     applied to x; *res = sum dp^2 of both colours.  x itself is not modified.
+ *   czb_sweep_jacobi: xnew = jacobi_ applied to x (without the copy-back), *res = sum dp^2.
+ *   czb_apply_ax    : ap = blas_calc_ax_(p) on inner cells, 0 elsewhere in the stored range;
+ *                     *dot_w = (ap, w) if w != NULL, *dot_self = (ap, ap) if dot_self != NULL. */
+int czb_sweep_rbsor(czb_ctx* c, const CZB_REAL* x, CZB_REAL* xnew, const CZB_REAL* b, CZB_REAL omg, double* res);
+int czb_sweep_jacobi(czb_ctx* c, const CZB_REAL* x, CZB_REAL* xnew, const CZB_REAL* b, CZB_REAL omg, double* res);
+int czb_apply_ax(czb_ctx* c, CZB_REAL* ap, const CZB_REAL* p, const CZB_REAL* w, double* dot_w, double* dot_self);
+
 /* Fused solve loop.  solver/precond names follow CZ::setLS / setStrPre
  * (cz_Evaluate.cpp:571-803): jacobi psor sor2sma pbicgstab pcr pcr_eda pcr_esa pcr_rb
  * pcr_rb_esa pcr_j_esa.  X (in/out) and B are device or host pointers, (sz+2g)^3 REALs.

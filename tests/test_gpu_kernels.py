@@ -205,3 +205,47 @@ def test_bc_exact_err(real, ulp, n):
     assert dg.value == do.value and tuple(lg) == tuple(lo)
     assert _bits_equal(E2.cpu().numpy(), E1)
     cz.close()
+
+
+# The fused TMA kernels (fused.cu / fused_pk.cuh) one call at a time: bit-exact against the oracle's
+# per-colour / per-pass kernels.  Sizes cover one tile (16), ragged tiles in k, i and j (44, 100),
+# several k tiles + several j chunks (132) and a row pitch TMA cannot address (37: returns 0).
+@pytest.mark.parametrize("real", ["f32", "f64"])
+@pytest.mark.parametrize("n", [16, 37, 44, 100, 132])
+def test_fused_sweeps(real, n):
+    cz, o = _mk(n, real)
+    X, B, W = ou.random_fields(o.shape, o.dt, n=3)
+    o.ac1 = o.dt(1.3)
+    Xg, Bg, Wg = _dev(cz, X), _dev(cz, B), _dev(cz, W)
+    eligible = ((n + 4) * (4 if real == "f32" else 8)) % 16 == 0 and (n + 4) % 2 == 0
+    # red-black SOR, both colours
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_rb(Xo, B, ro)
+    Ng = _dev(cz, X); rg = C.c_double(0)
+    ok = cz.dll.czb_sweep_rbsor(cz.ctx, cz._ptr(Xg), cz._ptr(Ng), cz._ptr(Bg), cz.creal(1.3), C.byref(rg))
+    assert ok == (1 if eligible else 0)
+    if ok:
+        assert _bits_equal(Ng.cpu().numpy(), Xo)
+        assert rg.value == pytest.approx(ro.value, rel=SUM_RTOL)
+        assert _bits_equal(Xg.cpu().numpy(), X)          # the source field is untouched
+    # Jacobi
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_jacobi(Xo, B, ro)
+    Ng = _dev(cz, X); rg = C.c_double(0)
+    ok = cz.dll.czb_sweep_jacobi(cz.ctx, cz._ptr(Xg), cz._ptr(Ng), cz._ptr(Bg), cz.creal(1.3), C.byref(rg))
+    if ok:
+        assert _bits_equal(Ng.cpu().numpy(), Xo)
+        assert rg.value == pytest.approx(ro.value, rel=SUM_RTOL)
+    # operator + dots
+    cf = np.array([1, 1, 1, 1, 1, 1, 6], dtype=o.dt)
+    flop = C.c_double(0)
+    Ao = np.zeros_like(X); o.dll.blas_calc_ax_(ou.ptr(Ao), ou.ptr(X), o._sz, o._idx, o.g(), ou.ptr(cf), C.byref(flop))
+    Ag = _dev(cz, np.zeros_like(X)); dw, ds = C.c_double(0), C.c_double(0)
+    ok = cz.dll.czb_apply_ax(cz.ctx, cz._ptr(Ag), cz._ptr(Xg), cz._ptr(Wg), C.byref(dw), C.byref(ds))
+    if ok:
+        assert _bits_equal(Ag.cpu().numpy(), Ao)
+        inner = (slice(3, -3),) * 3      # Fortran 2..N-1 of an array with two guard layers
+        a = Ao[inner].astype(o.dt)
+        ref_w = float(np.sum((a * W[inner]).astype(o.dt).astype(np.float64)))
+        ref_s = float(np.sum((a * a).astype(o.dt).astype(np.float64)))
+        assert dw.value == pytest.approx(ref_w, rel=1e-11, abs=1e-9 * abs(ref_s))
+        assert ds.value == pytest.approx(ref_s, rel=1e-11)
+    cz.close()
