@@ -88,6 +88,7 @@ struct MarchArgs {
   LoopState* acc_st; int slot; int add;
   RedBuf rb;
   int slot2;              // packed MODE_AX: second accumulator (ap, ap), -1 = none
+  int zsrc;               // packed MODE_RB2: the source field is all zero and is not read
 };
 
 struct FinStoreF {
@@ -644,7 +645,7 @@ int march_rows(int cfg) {
 
 // returns 0 = not eligible, 1 = done, 2 = done including the second accumulator slot2 (packed MODE_AX)
 int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_or_w, REAL* out, const REAL* cf,
-          REAL omg, int ip, int jr0, int jr1, int slot, bool add, int slot2 = -1) {
+          REAL omg, int ip, int jr0, int jr1, int slot, bool add, int slot2 = -1, bool zsrc = false) {
   if (!fused_eligible(G)) return 0;
   MarchArgs a;
   a.G = G;
@@ -687,6 +688,8 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
   a.st = L.st; a.acc_st = L.acc_st; a.slot = slot; a.add = add ? 1 : 0;
   a.rb = L.rb;
   a.slot2 = lin ? slot2 : -1;
+  a.zsrc = (zsrc && packed && !lin) ? 1 : 0;
+  if (zsrc && !a.zsrc) return 0;   // only the packed two-colour kernel can skip the source
   const size_t T = (size_t)a.ei * EKB;
   const CUtensorMap& tp = tmap_for(p, G, a.ei);
   const CUtensorMap& tb = (mode == MODE_AX) ? tp : tmap_for(b_or_w, G, a.ei);
@@ -723,8 +726,16 @@ bool fused_eligible(const Geo& G) {
 }
 
 bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf, REAL omg,
-                      int ip, int jr0, int jr1, int slot, bool add) {
-  return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add) != 0;
+                      int ip, int jr0, int jr1, int slot, bool add, bool zero_src) {
+  return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add, -1, zero_src) != 0;
+}
+bool rb2_zero_src_supported(const Geo& G, const REAL* cf) {
+#ifdef _REAL_IS_DOUBLE_
+  (void)G; (void)cf; return false;
+#else
+  const bool unit = cf[0] == 1.f && cf[1] == 1.f && cf[2] == 1.f && cf[3] == 1.f && cf[4] == 1.f && cf[5] == 1.f && cf[6] == 6.f;
+  return fused_eligible(G) && unit && march_cfg() >= 2 && (G.nk % 4 == 0);
+#endif
 }
 bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
                          REAL omg, int slot, bool add) {

@@ -180,8 +180,11 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   auto issue_b = [&](int t) {
     issue_plane(raw_b + (uint32_t)(t % NSB_) * TB, bar0 + 8u * (uint32_t)(NSP_ + t % NSB_), &tm_b, bpl0 + t + G.g - 1);
   };
+  // a.zsrc: the source field is known to be all zero (first preconditioner sweep, cz_Poisson.cpp:405-409):
+  // its planes are not fetched at all.
+  const bool zsrc = a.zsrc != 0;
   if (tid == 0) {
-    for (int t = 0; t < NSP_ && t < npl; ++t) issue_p(t);
+    if (!zsrc) for (int t = 0; t < NSP_ && t < npl; ++t) issue_p(t);
     for (int t = 0; t < NSB_ && t < nbpl; ++t) issue_b(t);
   }
 
@@ -242,17 +245,18 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   double acc[1] = {0.0};
 
   // ---- prologue: planes pl0 (-> P[0], "s") and pl0+1 (-> P[1], "s+1", + de-interleaved copy) ---------
-  mbar_wait_a(bar0, 0);
+  if (!zsrc) {
+    mbar_wait_a(bar0, 0);
 #pragma unroll
-  for (int m = 0; m < CPT; ++m) P[0][m] = lds_unit(raw_p + araw[m]);
-  mbar_wait_a(bar0 + 8, 0);
+    for (int m = 0; m < CPT; ++m) P[0][m] = lds_unit(raw_p + araw[m]);
+    mbar_wait_a(bar0 + 8, 0);
 #pragma unroll
-  for (int m = 0; m < CPT; ++m) {
-    P[1][m] = lds_unit(raw_p + TB + araw[m]);
-    sts64<0>(dei + TB + ad[m], P[1][m].a); sts64<HPB>(dei + TB + ad[m], P[1][m].b);
+    for (int m = 0; m < CPT; ++m) P[1][m] = lds_unit(raw_p + TB + araw[m]);
   }
+#pragma unroll
+  for (int m = 0; m < CPT; ++m) { sts64<0>(dei + TB + ad[m], P[1][m].a); sts64<HPB>(dei + TB + ad[m], P[1][m].b); }
   __syncthreads();
-  if (tid == 0) { if (NSP_ < npl) issue_p(NSP_); if (NSP_ + 1 < npl) issue_p(NSP_ + 1); }
+  if (tid == 0 && !zsrc) { if (NSP_ < npl) issue_p(NSP_); if (NSP_ + 1 < npl) issue_p(NSP_ + 1); }
 
   // ---- main loop ----------------------------------------------------------------------------------
   int sp = 2 % NSP_, pp = (2 / NSP_) & 1;   // raw p slot / mbarrier parity of plane index u+2
@@ -292,10 +296,15 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
 #pragma unroll
     for (int m = 0; m < CPT; ++m) jsk[m] = XB ? w2[m].a : w2[m].b;
     if (u + 2 < npl) {
-      mbar_wait_a(bar0 + 8u * (uint32_t)sp, (uint32_t)pp);
-      const uint32_t rp = raw_p + (uint32_t)sp * TB;
+      if (!zsrc) {
+        mbar_wait_a(bar0 + 8u * (uint32_t)sp, (uint32_t)pp);
+        const uint32_t rp = raw_p + (uint32_t)sp * TB;
 #pragma unroll
-      for (int m = 0; m < CPT; ++m) w2[m] = lds_unit(rp + araw[m]);
+        for (int m = 0; m < CPT; ++m) w2[m] = lds_unit(rp + araw[m]);
+      } else {
+#pragma unroll
+        for (int m = 0; m < CPT; ++m) w2[m] = U4{0ull, 0ull};
+      }
 #pragma unroll
       for (int m = 0; m < CPT; ++m) { sts64<0>(e2 + ad[m], w2[m].a); sts64<HPB>(e2 + ad[m], w2[m].b); }
     }
@@ -377,7 +386,7 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
     (void)YO;
     __syncthreads();
     if (tid == 0) {   // the two raw slots read in this step are free: refill them
-      if (u + 2 + NSP_ < npl) issue_p(u + 2 + NSP_);
+      if (!zsrc && u + 2 + NSP_ < npl) issue_p(u + 2 + NSP_);
       if (u + NSB_ < nbpl) issue_b(u + NSB_);
     }
     if (++sp == NSP_) { sp = 0; pp ^= 1; }

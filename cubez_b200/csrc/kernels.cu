@@ -167,6 +167,27 @@ struct OpBicg2 {   // z = a*x + b*y + z   (cz_blas.f90:553)
     z[off] = aa * x[off] + bb * y[off] + z[off];
   }
 };
+// PBiCGstab tail in one pass (cz_Poisson.cpp:470-488): x += alpha*p_ + omega*s_ (blas_bicg_2, cz_blas.f90:553),
+// r = s - omega*t (blas_triad :296), acc[0] = (r, r) (blas_dot1) and acc[1] = (r, r0) (the blas_dot2 that opens
+// the next iteration, :376) -- 6 reads + 2 writes per cell instead of 10 + 3 in four kernels.
+struct OpBicgTail {
+  REAL* x; const REAL* p_; const REAL* s_; REAL* r; const REAL* t; const REAL* s; const REAL* r0;
+  const double* al_dev; const double* om_dev; const double* nom_dev;
+  __device__ void operator()(const Geo&, int, int, int, long long off, double* acc) const {
+    const REAL al = (REAL)(*al_dev), om = (REAL)(*om_dev), nom = (REAL)(*nom_dev);
+    x[off] = al * p_[off] + om * s_[off] + x[off];
+    const REAL rr = nom * t[off] + s[off];
+    r[off] = rr;
+    acc[0] += (double)(rr * rr);
+    acc[1] += (double)(rr * r0[off]);
+  }
+};
+struct FinStore2 {   // acc[slot0] = total0 ; acc[slot1] = total1
+  LoopState* st; int slot0, slot1;
+  __device__ void operator()(double (&tot)[2]) const {
+    if (st) { st->acc[slot0] = tot[0]; st->acc[slot1] = tot[1]; }
+  }
+};
 struct OpOne {
   REAL* x;
   __device__ void operator()(const Geo&, int, int, int, long long off, double*) const { x[off] = (REAL)1.0; }
@@ -416,6 +437,12 @@ void launch_bicg1(const Launch& L, const Geo& G, REAL* p, const REAL* r, const R
 void launch_bicg2(const Launch& L, const Geo& G, REAL* z, const REAL* x, const REAL* y, REAL a, REAL b,
                   const double* a_dev, const double* b_dev) {
   run_cells<0>(L, G, OpBicg2{z, x, y, a, b, a_dev, b_dev}, FinNone{});
+}
+
+void launch_bicg_tail(const Launch& L, const Geo& G, REAL* x, const REAL* p_, const REAL* s_, REAL* r, const REAL* t,
+                      const REAL* s, const REAL* r0, const double* al_dev, const double* om_dev, const double* nom_dev,
+                      int slot_rr, int slot_rho) {
+  run_cells<2>(L, G, OpBicgTail{x, p_, s_, r, t, s, r0, al_dev, om_dev, nom_dev}, FinStore2{L.acc_st, slot_rr, slot_rho});
 }
 
 void launch_imask(const Launch& L, const Geo& G, REAL* x) {   // cz_blas.f90:24-103

@@ -44,6 +44,11 @@ void launch_bicg1(const Launch& L, const Geo& G, REAL* p, const REAL* r, const R
                   REAL omg, const double* beta_dev, const double* omg_dev);
 void launch_bicg2(const Launch& L, const Geo& G, REAL* z, const REAL* x, const REAL* y, REAL a,
                   REAL b, const double* a_dev, const double* b_dev);
+// x += alpha*p_ + omega*s_ ; r = s - omega*t ; acc[slot_rr] = (r,r) ; acc[slot_rho] = (r,r0).  The scalars are
+// read from device memory (LoopState.scal, doubles holding REAL values).
+void launch_bicg_tail(const Launch& L, const Geo& G, REAL* x, const REAL* p_, const REAL* s_, REAL* r, const REAL* t,
+                      const REAL* s, const REAL* r0, const double* al_dev, const double* om_dev, const double* nom_dev,
+                      int slot_rr, int slot_rho);
 void launch_imask(const Launch& L, const Geo& G, REAL* x);
 void launch_copy_in(const Launch& L, const Geo& G, REAL* y, const REAL* x);
 
@@ -76,7 +81,9 @@ bool fused_eligible(const Geo& G);
 // both colours of one red-black SOR iteration, p -> pnew (ping-pong). Reds are relaxed on planes
 // jr0..jr1 (includes halo planes owned by a neighbour rank), blacks/stores on jst..jed.
 bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
-                      REAL omg, int ip, int jr0, int jr1, int slot, bool add);
+                      REAL omg, int ip, int jr0, int jr1, int slot, bool add, bool zero_src = false);
+// zero_src: p is known to be all zero and is not read at all (packed float kernel only; check first)
+bool rb2_zero_src_supported(const Geo& G, const REAL* cf);
 bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
                          REAL omg, int slot, bool add);
 // ap = A p on inner cells, 0 on the other cells of stored pairs; acc[slot] = (ap, dotwith).

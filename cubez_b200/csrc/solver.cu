@@ -239,7 +239,8 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
       Launch L = launch();
-      launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, rs, false);
+      // first preconditioner sweep: xx is all zero by contract (cz_Poisson.cpp:405,441) and is not read
+      launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, rs, false, !converge_check && it == 1 && pre_zero_src);
       Comm_S(dst, 2);
       if (converge_check) {
         Comm_SUM(0);
@@ -408,6 +409,10 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
        *s = field(pcg_s), *s_ = field(pcg_s_), *t_ = field(pcg_t_);
   double* sc = d_state->scal;
   double pflop = 0.0;
+  // With the packed two-colour kernel as preconditioner the first of the 8 sweeps treats its source as zero
+  // without reading it, so p_ / s_ need no clearing: every cell the sweeps do not store stays at the zero
+  // the field was allocated with (czb_malloc), every stored cell is rewritten by sweep 2.
+  const bool zs = (pc_type == LS_SOR2SMA) && variant == 0 && rb2_zero_src_supported(G, cf);
 
   begin_loop(ItrMax);
   {
@@ -425,30 +430,35 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
   };
   auto body = [&](int itr) {
     Launch L = launch();
-    launch_dot2(L, G, r, r0, 0); Comm_SUM(0); scalar(0);                     // rho :376-383
+    if (itr == 1 || variant != 0) launch_dot2(L, G, r, r0, 0);              // rho :376-383 (later: fused into the tail)
+    Comm_SUM(0); scalar(0);
     if (itr == 1) {
       CZB_CHECK(cudaMemcpyAsync(p, r, bytes, cudaMemcpyDeviceToDevice, R.stream));   // :388
     } else {
       launch_bicg1(L, G, p, r, q, 0, 0, &sc[SC_BETA], &sc[SC_OMEGA]);        // :397
     }
     Comm_S(p, 1);                                                            // :402
-    CZB_CHECK(cudaMemsetAsync(p_, 0, bytes, R.stream));                      // :405
-    Preconditioner(p_, p, pflop, pc_type);                                   // :409
+    if (!zs) CZB_CHECK(cudaMemsetAsync(p_, 0, bytes, R.stream));             // :405 (zs: first sweep does not read p_)
+    pre_zero_src = zs; Preconditioner(p_, p, pflop, pc_type); pre_zero_src = false;   // :409
     if (!(variant == 0 && launch_ax_fused(L, G, q, p_, cf, r0, 1))) launch_calc_ax(L, G, q, p_, cf, r0, 1);
     Comm_SUM(1); scalar(1);          // q = A p_, alpha :421-431
     launch_triad(L, G, s, q, r, 0, &sc[SC_NEG_ALPHA]);                       // s = r - alpha q :434
     Comm_S(s, 1);                                                            // :438
-    CZB_CHECK(cudaMemsetAsync(s_, 0, bytes, R.stream));                      // :441
-    Preconditioner(s_, s, pflop, pc_type);                                   // :445
+    if (!zs) CZB_CHECK(cudaMemsetAsync(s_, 0, bytes, R.stream));             // :441
+    pre_zero_src = zs; Preconditioner(s_, s, pflop, pc_type); pre_zero_src = false;   // :445
     {   // t = A s_, (t,s), (t,t) :457-464
       const int f = (variant == 0) ? launch_ax_fused(L, G, t_, s_, cf, s, 2, 3) : 0;
       if (f == 0) launch_calc_ax(L, G, t_, s_, cf, s, 2);
       if (f != 2) launch_dot1(L, G, t_, 3);
     }
     Comm_SUM(2, 2); scalar(2);                                               // omega
-    launch_bicg2(L, G, X, p_, s_, 0, 0, &sc[SC_ALPHA], &sc[SC_OMEGA]);       // x += alpha p_ + omega s_ :470
-    launch_triad(L, G, r, t_, s, 0, &sc[SC_NEG_OMEGA]);                      // r = s - omega t :476
-    launch_dot1(L, G, r, 4);                                                 // :481
+    if (variant == 0) {   // x += alpha p_ + omega s_ :470, r = s - omega t :476, (r,r) :481, (r,r0) :376 in one pass
+      launch_bicg_tail(L, G, X, p_, s_, r, t_, s, r0, &sc[SC_ALPHA], &sc[SC_OMEGA], &sc[SC_NEG_OMEGA], 4, 0);
+    } else {
+      launch_bicg2(L, G, X, p_, s_, 0, 0, &sc[SC_ALPHA], &sc[SC_OMEGA]);
+      launch_triad(L, G, r, t_, s, 0, &sc[SC_NEG_OMEGA]);
+      launch_dot1(L, G, r, 4);
+    }
     Comm_S(X, 1); Comm_SUM(4);                                               // :486-488
     scalar(3);                                                               // :490-500
     launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);                                // :495

@@ -38,6 +38,7 @@ struct czb_ctx {
   REAL *pcg_p, *pcg_p_, *pcg_r, *pcg_r0, *pcg_q, *pcg_s, *pcg_s_, *pcg_t_;
   REAL* Xd; REAL* Bd;     // staging when the caller passes host pointers
   bool wrk_guards_zero;
+  bool pre_zero_src;      // the next preconditioner call may skip reading its (all-zero) start vector
   czb::PcrTables pcr2, pcr4;
 
   czb::LoopState* d_state;
