@@ -14,7 +14,7 @@ One JSON line on rank 0:
                with CUDA events on the launching stream, max over ranks
   e2e          the same K iterations through the public call CZ.solve() with HOST (pinned) arrays:
                H2D of X and B, the solve loop, D2H of X and of the residual history, all timed
-  roofline     dominant kernel (fused two-colour sweep k_march<MODE_RB2>): algorithmic bytes
+  roofline     dominant kernel (fused two-colour sweep k_rb2_pk): algorithmic bytes
                (4R = 16 B per cell.iteration) / measured time per iteration,
                against the measured HBM copy bandwidth of MEASURED_PEAKS.json
   cpu_baseline the CPU oracle port of the reference kernel (oracle/, "port") on all host cores,
@@ -37,7 +37,7 @@ N_CUBE = int(os.environ.get("CZB_BENCH_N", "1024"))
 OMEGA = 1.5
 SOLVER = "sor2sma"
 ALGO_BYTES_PER_CELL = 16.0      # red-black SOR, float, 4R per cell.iteration
-NCU_TRAFFIC_PER_ITER = 13.24e9     # dram read+write bytes per k_march<RB2> launch (profiles/r01_rb2_summary.md, 1 GPU)
+NCU_TRAFFIC_PER_ITER = 14.24e9     # dram read+write bytes per k_rb2_pk launch (profiles/r01_rb2_summary.md, 1 GPU)
 
 
 def measured_peak():
@@ -186,6 +186,27 @@ def run_gpu(args, rank, world, local_rank):
     glups = cells * args.steps / (ms_total * 1e-3) / 1e9
     ms_iter = ms_loop / args.steps
 
+    # ---- the other solvers of the north-star target on the same grid (device resident, after the
+    # headline region; reported under "also", not part of value/e2e) -------------------------------
+    also = {}
+    if not args.no_also:
+        for name, pre, omg, bpc, k in (("pbicgstab", "sor2sma", OMEGA, 340.0, 6), ("jacobi", None, 0.8, 12.0, 10)):
+            P2, R2 = cz.setup_laplace()
+            P2[2:-2, 2:-2, 2:-2] = torch.rand(P2[2:-2, 2:-2, 2:-2].shape, generator=gen, device="cuda") * 2 - 1
+            cz.bc_k(P2)
+            cz.solve(name, P2, R2, 3, omg, precond=pre, want_history=False)
+            barrier()
+            o2 = cz.solve(name, P2, R2, k, omg, precond=pre, want_history=False)
+            barrier()
+            done = (k - 1) if name == "pbicgstab" else k
+            ms2 = max_over_ranks(o2["ms"]) / done
+            gl = cells / (ms2 * 1e-3) / 1e9
+            also[name + ("+" + pre if pre else "")] = {
+                "value": gl, "unit": "G cell-iterations/s", "ms_per_iteration": ms2,
+                "algorithmic_bytes_per_cell": bpc, "hbm_frac_of_measured": gl * bpc / world / measured_peak()[0]}
+            del P2, R2
+        torch.cuda.empty_cache()
+
     # ---- end to end: host arrays through the public call ------------------------------------------
     Ph = torch.empty(cz.shape, dtype=torch.float32).pin_memory()
     Bh = torch.empty(cz.shape, dtype=torch.float32).pin_memory()
@@ -224,13 +245,15 @@ def run_gpu(args, rank, world, local_rank):
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": NCU_TRAFFIC_PER_ITER, "peak_source": peak_src,
-                     "kernel": "k_march<MODE_RB2> (fused two-colour sweep, TMA-staged)",
+                     "kernel": "k_rb2_pk (fused two-colour sweep, TMA-staged, packed f32x2)",
                      "algorithmic_bytes_per_cell": ALGO_BYTES_PER_CELL, "ms_per_launch": ms_iter,
                      "frac_of_8000": achieved / 8000.0},
         "clocks": clocks,
     }
     if cpu:
         line["cpu_baseline"] = cpu
+    if also:
+        line["also"] = also
     print(json.dumps(line), flush=True)
     cz.close()
     if dist is not None:
@@ -244,6 +267,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cubez_b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-also", action="store_true", help="skip the PBiCGstab / Jacobi side measurements")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
