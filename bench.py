@@ -34,6 +34,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_CUBE = int(os.environ.get("CZB_BENCH_N", "1024"))
+N_Y = int(os.environ.get("CZB_BENCH_NY", str(N_CUBE)))     # experiments only: shorter j extent (slab axis)
 OMEGA = 1.5
 SOLVER = "sor2sma"
 ALGO_BYTES_PER_CELL = 16.0      # red-black SOR, float, 4R per cell.iteration
@@ -140,7 +141,7 @@ def run_gpu(args, rank, world, local_rank):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n = N_CUBE
-    cz = cubez_b200.CZ([n, n, n], "f32", device=local_rank, nranks=world, rank=rank, eps=0.0)  # eps=0: never stops early
+    cz = cubez_b200.CZ([n, N_Y, n], "f32", device=local_rank, nranks=world, rank=rank, eps=0.0)  # eps=0: never stops early
     if world > 1:
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:

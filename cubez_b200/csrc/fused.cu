@@ -33,6 +33,7 @@ namespace czb {
 namespace {
 
 enum { MODE_RB2 = 0, MODE_JAC = 1, MODE_AX = 2 };
+constexpr int RB2_EDGE = 2;     // planes a j-slab sends to each neighbour after a two-colour sweep
 
 constexpr int PR = 64;          // pairs per tile row  -> box width EKB = 128 cells
 constexpr int EKB = 2 * PR;
@@ -89,6 +90,8 @@ struct MarchArgs {
   RedBuf rb;
   int slot2;              // packed MODE_AX: second accumulator (ap, ap), -1 = none
   int zsrc;               // packed MODE_RB2: the source field is all zero and is not read
+  int edges;              // packed MODE_RB2: relax only the first and last jl planes of jb0..jb1 (grid.y = 2)
+  unsigned int* sig;      // packed MODE_RB2: edge-plane completion counters {low, high} or null (fused_pk.cuh)
 };
 
 struct FinStoreF {
@@ -645,7 +648,8 @@ int march_rows(int cfg) {
 
 // returns 0 = not eligible, 1 = done, 2 = done including the second accumulator slot2 (packed MODE_AX)
 int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_or_w, REAL* out, const REAL* cf,
-          REAL omg, int ip, int jr0, int jr1, int slot, bool add, int slot2 = -1, bool zsrc = false) {
+          REAL omg, int ip, int jr0, int jr1, int slot, bool add, int slot2 = -1, bool zsrc = false, int part = 0,
+          unsigned int* sig = nullptr, int* sig_ctas = nullptr) {
   if (!fused_eligible(G)) return 0;
   MarchArgs a;
   a.G = G;
@@ -669,7 +673,11 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
     const int npairs = (ked_c >> 1) - (kst_c >> 1) + 1;
     a.ntk = (npairs + PR - 3) / (PR - 2);
   }
-  const int ni = G.ied - G.ist + 1, nj = G.jed - G.jst + 1;
+  // part (packed MODE_RB2 only): 0 = all owned planes, 1 = the RB2_EDGE first and last planes, 2 = the planes between
+  if (part != 0 && !(packed && !lin)) return 0;
+  const int jlo = (part == 2) ? G.jst + RB2_EDGE : G.jst, jhi = (part == 2) ? G.jed - RB2_EDGE : G.jed;
+  if (part != 0 && G.jed - G.jst + 1 < 2 * RB2_EDGE + 1) return 0;
+  const int ni = G.ied - G.ist + 1, nj = jhi - jlo + 1;
   a.nti = lin ? (ni + a.ei - 3) / (a.ei - 2) : (ni + a.ei - 5) / (a.ei - 4);
   // j-chunks: enough CTAs for ~8 rounds over the SMs, chunks no shorter than 32 planes
   static int rounds = -1;
@@ -679,8 +687,10 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
   if (njc < 1) njc = 1;
   a.jl = (nj + njc - 1) / njc;
   a.njc = (nj + a.jl - 1) / a.jl;
+  a.edges = 0;
+  if (part == 1) { a.edges = 1; a.jl = RB2_EDGE; a.njc = 2; }
   if ((size_t)a.ntk * a.nti * a.njc > L.rb_blocks) return 0;
-  a.jr0 = jr0; a.jr1 = jr1; a.jb0 = G.jst; a.jb1 = G.jed;
+  a.jr0 = jr0; a.jr1 = jr1; a.jb0 = jlo; a.jb1 = jhi;
   a.ip = ip;
   a.c = Coef7{cf[0], cf[1], cf[2], cf[3], cf[4], cf[5], cf[6]};
   a.omg = omg;
@@ -688,6 +698,9 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
   a.st = L.st; a.acc_st = L.acc_st; a.slot = slot; a.add = add ? 1 : 0;
   a.rb = L.rb;
   a.slot2 = lin ? slot2 : -1;
+  a.sig = (packed && !lin && part == 0) ? sig : nullptr;
+  if (sig && !a.sig) return 0;
+  if (sig_ctas) *sig_ctas = a.ntk * a.nti;
   a.zsrc = (zsrc && packed && !lin) ? 1 : 0;
   if (zsrc && !a.zsrc) return 0;   // only the packed two-colour kernel can skip the source
   const size_t T = (size_t)a.ei * EKB;
@@ -726,8 +739,9 @@ bool fused_eligible(const Geo& G) {
 }
 
 bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf, REAL omg,
-                      int ip, int jr0, int jr1, int slot, bool add, bool zero_src) {
-  return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add, -1, zero_src) != 0;
+                      int ip, int jr0, int jr1, int slot, bool add, bool zero_src, int part, unsigned int* sig,
+                      int* sig_ctas) {
+  return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add, -1, zero_src, part, sig, sig_ctas) != 0;
 }
 bool rb2_zero_src_supported(const Geo& G, const REAL* cf) {
 #ifdef _REAL_IS_DOUBLE_
@@ -736,6 +750,9 @@ bool rb2_zero_src_supported(const Geo& G, const REAL* cf) {
   const bool unit = cf[0] == 1.f && cf[1] == 1.f && cf[2] == 1.f && cf[3] == 1.f && cf[4] == 1.f && cf[5] == 1.f && cf[6] == 6.f;
   return fused_eligible(G) && unit && march_cfg() >= 2 && (G.nk % 4 == 0);
 #endif
+}
+bool rb2_parts_supported(const Geo& G, const REAL* cf) {
+  return rb2_zero_src_supported(G, cf) && (G.jed - G.jst + 1 >= 2 * RB2_EDGE + 1);
 }
 bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
                          REAL omg, int slot, bool add) {

@@ -131,7 +131,6 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t addr, uint32_t parity) {   
 template <int NT, int CPT, int NSP_, int NSB_>
 __global__ void __launch_bounds__(NT, 1)
 k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b, const MarchArgs a) {
-  if (a.st && a.st->done) return;
   constexpr int RPW = NT / 32;             // tile rows covered by one pass of the CTA (one warp per row)
   constexpr int EI = RPW * CPT;            // tile rows
   constexpr int T = EI * EKB;              // cells per tile plane
@@ -151,11 +150,23 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   const int lane = tid & 31, wrow = tid >> 5;
 
   // ---- tile / chunk geometry ------------------------------------------------------------
-  const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk, jc = blockIdx.y;
+  // a.sig (j-slab of a multi-GPU run): the last chunk is scheduled first and counts its finished CTAs in
+  // sig[1], the CTAs of the first chunk count in sig[0] once their first two planes are stored; the
+  // communication stream waits on the two counters (stream memory operation) and sends the slab's edge
+  // planes while the rest of this launch is still running.
+  const int jc = (a.sig && a.njc > 1) ? (blockIdx.y == 0 ? a.njc - 1 : (int)blockIdx.y - 1) : (int)blockIdx.y;
+  const bool sig_lo = a.sig && jc == 0, sig_hi = a.sig && jc == a.njc - 1;
+  if (a.st && a.st->done) {   // converged: nothing to do, but the counters must still advance
+    if (threadIdx.x == 0) { if (sig_lo) atomicAdd(a.sig, 1u); if (sig_hi) atomicAdd(a.sig + 1, 1u); }
+    return;
+  }
+  const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk;
   const int kst_c = G.kst + G.g - 1, ist_c = G.ist + G.g - 1;     // C offsets of the first inner cell
   const int P0 = (((kst_c >> 1) & ~1) - PKH) + tk * (PR - 2 * PKH);   // first (halo) pair of the box, even
   const int R0 = ist_c - 2 + ti * (EI - 4);                        // first (halo) row of the box
-  const int ja = a.jb0 + jc * a.jl;                                // owned planes of this chunk
+  // owned planes of this chunk; a.edges: two chunks of a.jl planes at the two ends of jb0..jb1 (the planes
+  // a j-slab sends to its neighbours, relaxed first so that the exchange overlaps the interior launch)
+  const int ja = a.edges ? (jc == 0 ? a.jb0 : a.jb1 - a.jl + 1) : a.jb0 + jc * a.jl;
   const int jb = min(ja + a.jl - 1, a.jb1);
   const int pl0 = ja - 2;                                          // first p plane fetched
   const int bpl0 = ja - 1;                                         // first b plane fetched
@@ -384,7 +395,10 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
       hb[C & 1][m] = XB ? bc[m].a : bc[m].b;     // right-hand side of the blacks of plane s+1 (used at step u+2)
     }
     (void)YO;
+    const bool lo_now = sig_lo && u == min(4, nsteps - 1);   // planes ja, ja+1 are stored (step 4 stores ja+1)
+    if (lo_now) __threadfence();
     __syncthreads();
+    if (lo_now && tid == 0) atomicAdd(a.sig, 1u);
     if (tid == 0) {   // the two raw slots read in this step are free: refill them
       if (!zsrc && u + 2 + NSP_ < npl) issue_p(u + 2 + NSP_);
       if (u + NSB_ < nbpl) issue_b(u + NSB_);
@@ -416,6 +430,11 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
       if (u + 3 >= nsteps) break;
       step(u + 3, I3{}, std::false_type{});
     }
+  }
+  if (sig_hi) {
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) atomicAdd(a.sig + 1, 1u);
   }
   grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
 }

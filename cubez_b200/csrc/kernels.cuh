@@ -81,9 +81,15 @@ bool fused_eligible(const Geo& G);
 // both colours of one red-black SOR iteration, p -> pnew (ping-pong). Reds are relaxed on planes
 // jr0..jr1 (includes halo planes owned by a neighbour rank), blacks/stores on jst..jed.
 bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
-                      REAL omg, int ip, int jr0, int jr1, int slot, bool add, bool zero_src = false);
+                      REAL omg, int ip, int jr0, int jr1, int slot, bool add, bool zero_src = false, int part = 0,
+                      unsigned int* sig = nullptr, int* sig_ctas = nullptr);
+// sig (part 0, packed float kernel only): two device counters; the launch adds *sig_ctas to each, sig[0] as soon as
+// the first two owned planes are stored everywhere, sig[1] when the last chunk (scheduled first) is complete.
 // zero_src: p is known to be all zero and is not read at all (packed float kernel only; check first)
 bool rb2_zero_src_supported(const Geo& G, const REAL* cf);
+// part = 1: only the two planes at each end of the owned j range (what a slab sends to its neighbours),
+// part = 2: only the planes between; 1 then 2 equals one part = 0 sweep (packed float kernel only; check first)
+bool rb2_parts_supported(const Geo& G, const REAL* cf);
 bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
                          REAL omg, int slot, bool add);
 // ap = A p on inner cells, 0 on the other cells of stored pairs; acc[slot] = (ap, dotwith).

@@ -12,6 +12,7 @@
 #include <cfloat>
 #include <cmath>
 #include <strings.h>
+#include <cuda.h>
 
 using namespace czb;
 
@@ -101,6 +102,40 @@ void czb_ctx::Comm_SUM(int slot, int count) {
   if (comm && comm->nranks > 1) comm_allreduce_sum(comm, &d_state->acc[slot], count, rt().stream);
 }
 
+// cuStreamWaitValue32 through the runtime's driver entry point (no link dependency on libcuda)
+static void stream_wait_geq(cudaStream_t s, unsigned int* dev, unsigned int value) {
+  typedef CUresult (*Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+  static Fn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    CZB_CHECK(cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q));
+    if (!p || q != cudaDriverEntryPointSuccess) { fprintf(stderr, "czb200: cuStreamWaitValue32 unavailable\n"); abort(); }
+    fn = (Fn)p;
+  }
+  const CUresult r = fn((CUstream)s, (CUdeviceptr)(uintptr_t)dev, value, CU_STREAM_WAIT_VALUE_GEQ);
+  if (r != CUDA_SUCCESS) { fprintf(stderr, "czb200: cuStreamWaitValue32 failed (%d)\n", (int)r); abort(); }
+}
+
+void czb_ctx::ensure_comm_stream() {
+  if (cs) return;
+  CZB_CHECK(cudaMalloc(&d_sig, 2 * sizeof(unsigned int)));
+  CZB_CHECK(cudaMemset(d_sig, 0, 2 * sizeof(unsigned int)));
+  sig_target = 0;
+  int lo = 0, hi = 0;
+  CZB_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  CZB_CHECK(cudaStreamCreateWithPriority(&cs, cudaStreamNonBlocking, hi));
+  cudaEvent_t* evs[] = {&ev_edge, &ev_int, &ev_halo[0], &ev_halo[1], &ev_fin[0], &ev_fin[1], &ev_join};
+  for (cudaEvent_t* e : evs) CZB_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+}
+
+void czb_ctx::join_comm_stream() {
+  if (!cs || !cs_used) return;
+  CZB_CHECK(cudaEventRecord(ev_join, cs));
+  CZB_CHECK(cudaStreamWaitEvent(rt().stream, ev_join, 0));
+  cs_used = false;
+}
+
 void czb_ctx::begin_loop(int itr_max) {
   Runtime& R = rt();
   if (hist_cap < itr_max + 2) {
@@ -114,6 +149,10 @@ void czb_ctx::begin_loop(int itr_max) {
 
 int czb_ctx::end_loop(int itr_max, double& res, bool bicg) {
   Runtime& R = rt();
+  join_comm_stream();
+  // an iteration started before `done` became visible may have left the reduction ticket of a partly
+  // skipped launch behind: re-arm it
+  CZB_CHECK(cudaMemsetAsync(R.rb.ticket, 0, sizeof(unsigned int), R.stream));
   CZB_CHECK(cudaEventRecord(ev_t1, R.stream));
   CZB_CHECK(cudaMemcpyAsync(&h_state[0], d_state, sizeof(LoopState), cudaMemcpyDeviceToHost, R.stream));
   R.sync();
@@ -235,7 +274,57 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     }
     Comm_S(B, 2);
     const int jr0 = G.jst - (nID[2] >= 0 ? 1 : 0), jr1 = G.jed + (nID[3] >= 0 ? 1 : 0);
+    // Multi-rank overlap: the two planes at each end of the slab are relaxed first (part 1) and sent while
+    // the planes between are relaxed (part 2); the residual all-reduce and the convergence test of
+    // iteration k run on the communication stream next to iteration k+1.  Iteration k+1 only reads the
+    // converged field (it writes the other ping-pong buffer), iteration k+2 waits for the test of k, so
+    // iteration counts, histories and the returned field are those of a loop that tests every iteration.
+    static const bool no_ovl = getenv("CZB_NO_OVERLAP") != nullptr;
+    const bool ovl = comm && comm->nranks > 1 && !no_ovl && rb2_parts_supported(G, cf);
+    if (ovl) ensure_comm_stream();
+    static const bool no_sig = getenv("CZB_NO_SIGNAL") != nullptr;   // fall back to edge launch + interior launch
+    const bool use_sig = ovl && !no_sig;
+    auto body_ovl = [&](int it) {
+      REAL* src = (it & 1) ? X : W;
+      REAL* dst = (it & 1) ? W : X;
+      Launch L = launch();
+      const int slot = converge_check ? ((it & 1) ? 0 : 6) : rs;
+      const bool zs = !converge_check && it == 1 && pre_zero_src;
+      if (it >= 2) CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_halo[(it - 1) & 1], 0));   // halo planes of src
+      if (converge_check && it >= 3) CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_fin[(it - 2) & 1], 0));
+      if (use_sig) {
+        // one launch; the communication stream is released by the kernel's edge counters
+        int ctas = 0;
+        launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 0, d_sig, &ctas);
+        sig_target += (unsigned int)ctas;
+        stream_wait_geq(cs, d_sig, sig_target);
+        stream_wait_geq(cs, d_sig + 1, sig_target);
+        comm_halo(comm, dst, G, 2, cs);
+        CZB_CHECK(cudaEventRecord(ev_halo[it & 1], cs));
+      } else {
+        launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 1);
+        CZB_CHECK(cudaEventRecord(ev_edge, R.stream));
+        CZB_CHECK(cudaStreamWaitEvent(cs, ev_edge, 0));
+        comm_halo(comm, dst, G, 2, cs);
+        CZB_CHECK(cudaEventRecord(ev_halo[it & 1], cs));
+        launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, true, zs, 2);
+      }
+      if (converge_check) {
+        CZB_CHECK(cudaEventRecord(ev_int, R.stream));
+        CZB_CHECK(cudaStreamWaitEvent(cs, ev_int, 0));
+        comm_allreduce_sum(comm, &d_state->acc[slot], 1, cs);
+        Launch Lc = L; Lc.s = cs;
+        launch_finish_iteration(Lc, d_state, slot, res_normal, eps, d_hist, hist_cap);
+        CZB_CHECK(cudaEventRecord(ev_fin[it & 1], cs));
+        if (it <= 2) {   // bc_k after the exchange, as in the plain loop below
+          CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_halo[it & 1], 0));
+          launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
+        }
+      }
+      cs_used = true;
+    };
     auto body = [&](int it) {
+      if (ovl) { body_ovl(it); return; }
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
       Launch L = launch();
@@ -252,7 +341,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
-    else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+    else { for (int it = 1; it <= itr_max; ++it) body(it); join_comm_stream(); itr = itr_max + 1; done_iters = itr_max; }
     if (done_iters & 1) {
       launch_copy_inner(launch(false), G, X, W);
       if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
@@ -517,6 +606,7 @@ czb_ctx* czb_ctx_create(const int sz[3], const int idx[6], const int nID[6], CZB
   c->G = make_geo(c->size, c->innerFidx, c->gc);
   c->res_normal = 1.0 / c->G.cells();
   c->wrk_guards_zero = false;
+  c->pre_zero_src = false; c->cs = nullptr; c->cs_used = false; c->d_sig = nullptr; c->sig_target = 0;
   CZB_CHECK(cudaMalloc(&c->d_state, sizeof(LoopState)));
   CZB_CHECK(cudaMemset(c->d_state, 0, sizeof(LoopState)));
   CZB_CHECK(cudaMallocHost(&c->h_state, sizeof(LoopState) * 4));
@@ -536,6 +626,13 @@ void czb_ctx_destroy(czb_ctx* c) {
   if (c->d_hist) cudaFree(c->d_hist);
   cudaFree(c->d_state); cudaFreeHost(c->h_state);
   cudaEventDestroy(c->ev[0]); cudaEventDestroy(c->ev[1]); cudaEventDestroy(c->ev_t0); cudaEventDestroy(c->ev_t1);
+  if (c->cs) {
+    cudaStreamSynchronize(c->cs);
+    cudaEvent_t evs[] = {c->ev_edge, c->ev_int, c->ev_halo[0], c->ev_halo[1], c->ev_fin[0], c->ev_fin[1], c->ev_join};
+    for (cudaEvent_t e : evs) cudaEventDestroy(e);
+    cudaStreamDestroy(c->cs);
+    cudaFree(c->d_sig);
+  }
   comm_destroy(c->comm);
   delete c;
 }

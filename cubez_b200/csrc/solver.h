@@ -46,6 +46,11 @@ struct czb_ctx {
   double* d_hist; int hist_cap;
   cudaEvent_t ev[2], ev_t0, ev_t1;
   double last_ms;
+  // multi-rank overlap (RBSOR): halo exchange / residual all-reduce run on a second, high-priority stream
+  cudaStream_t cs; cudaEvent_t ev_edge, ev_int, ev_halo[2], ev_fin[2], ev_join;
+  bool cs_used;
+  unsigned int* d_sig;         // edge-plane completion counters {low, high} of the two-colour kernel
+  unsigned int sig_target;     // value both counters reach when the launches enqueued so far are done
   int hist_len_req;
 
   // ---- helpers ----
@@ -69,6 +74,8 @@ struct czb_ctx {
   // generic driver: enqueue `body(it)` for it = 1..itr_max in batches, polling the device
   // state without stalling the queue.  Returns the reference's iteration count.
   template <class Body> int run_checked(int itr_max, double& res, Body body);
+  void ensure_comm_stream();
+  void join_comm_stream();                        // the solve stream waits for everything queued on cs
   void begin_loop(int itr_max);
   int end_loop(int itr_max, double& res, bool bicg);
 };
