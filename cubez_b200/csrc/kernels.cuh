@@ -73,7 +73,9 @@ void pcr_free_tables(PcrTables& T);
 //       3 = lines with i+j == diag (wavefront for the lexicographic variants)
 void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mode, int ofs, int diag,
                       const REAL* x, REAL* dst, const REAL* msk, const REAL* rhs, REAL omg, int slot,
-                      bool add);
+                      bool add, bool mask_is_inner = false);
+// mask_is_inner: the caller guarantees msk == imask_k of G (1 on the inner range = on every cell of every
+// line); multiplying by exactly 1 changes nothing, so the warp-per-line kernel does not read it.
 
 // ---- fused TMA-staged marching kernels (fused.cu); return false when the geometry is not
 // eligible (row pitch not a multiple of 16 B) and the caller must use the baseline kernels ----

@@ -10,6 +10,7 @@
 // => bitwise the same d as the reference, ~3x less shared-memory traffic, no divisions.
 // Out-of-range neighbours are 0 (their coefficient is exactly 0).
 #include "kernels.cuh"
+#include <type_traits>
 
 namespace czb {
 namespace {
@@ -182,6 +183,188 @@ __global__ void __launch_bounds__(256) k_pcr_lines(Geo G, int n, int pn, int sta
   grid_reduce<1>(acc, rb, finst);
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// One WARP per line, the right-hand side d in registers.  Lane l owns the EPL consecutive cells
+// k = EPL*l .. EPL*l+EPL-1 ("blocked" layout), so a PCR stage with stride s gets its neighbours d(k-s),
+// d(k+s) from the lane's own registers (s < EPL, except the s cells next to a lane boundary) or with one
+// warp shuffle from lane l -+ s/EPL (s >= EPL): no block-wide barrier, no shared-memory traffic for d.
+// The coefficient tables (identical for every line, see above) are staged once per CTA in shared memory
+// in a lane-interleaved layout that makes every lane's 128-bit read conflict free.  Loads and stores of
+// the fields are done in the "cyclic" layout k = lane + 32*m (coalesced 128 B per instruction); the two
+// layouts are exchanged through a small per-warp shared buffer.  Arithmetic and its order are those of
+// k_pcr_lines (= cz_solver.f90:569-648), so results are bit-identical.
+template <int EPL>
+struct PcrLay {
+  static constexpr int NQ = EPL / 4;            // 16-byte chunks per lane
+  static constexpr int QSTR = 32 * 4 + 8;       // floats between chunk q and q+1 of a row (padded: conflict-free both ways)
+  static constexpr int ROW = NQ * QSTR;         // floats per interleaved row of 32*EPL cells
+  __device__ static __forceinline__ int pos(int k) {   // position of cell k inside an interleaved row
+    const int L = k / EPL, r = k - L * EPL;
+    return (r >> 2) * QSTR + L * 4 + (r & 3);
+  }
+};
+
+template <int EPL>
+__global__ void __launch_bounds__(EPL == 32 ? 512 : 256, EPL == 32 ? 1 : 2) k_pcr_warp(Geo G, int n, int pn, int stages, const REAL* __restrict__ tab,
+                                                  const REAL* __restrict__ fin, LineSel sel, const REAL* x, REAL* dst,
+                                                  const REAL* __restrict__ msk, const REAL* __restrict__ rhs, REAL omg,
+                                                  const LoopState* st, RedBuf rb, FinStoreP finst) {
+  if (st && st->done) return;
+  typedef PcrLay<EPL> LY;
+  constexpr int NQ = LY::NQ, ROW = LY::ROW, NP = 32 * EPL;
+  extern __shared__ double sm_raw[];
+  REAL* ts = reinterpret_cast<REAL*>(sm_raw);          // [stages][3][ROW] ap, cp, e ; then F1, F2 ; then per-warp buffers
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  REAL* F1 = ts + (size_t)stages * 3 * ROW;
+  REAL* F2 = F1 + ROW;
+  REAL* wb = F2 + ROW + (size_t)warp * ROW;            // this warp's layout-exchange buffer
+  const REAL zero = (REAL)0.0;
+  const int s2 = 1 << (pn - 1);
+  // ---- stage the tables (zero beyond n: cells k >= n then stay exactly 0 through every stage) ----
+  for (int idx = tid; idx < stages * 3 * NP; idx += blockDim.x) {
+    const int row = idx / NP, k = idx - row * NP;
+    ts[(size_t)row * ROW + LY::pos(k)] = (k < n) ? tab[(size_t)row * n + k] : zero;
+  }
+  for (int k = tid; k < NP; k += blockDim.x) {          // last 2x2 stage, cz_solver.f90:612-630, per own cell
+    REAL f1 = zero, f2 = zero;
+    if (k < n) {
+      if (k < s2) { f1 = fin[k]; f2 = fin[2 * (size_t)s2 + k]; }
+      else        { f1 = fin[(size_t)s2 + (k - s2)]; f2 = fin[2 * (size_t)s2 + (k - s2)]; }
+    }
+    F1[LY::pos(k)] = f1; F2[LY::pos(k)] = f2;
+  }
+  __syncthreads();
+  const REAL r = (REAL)1.0 / (REAL)6.0;
+  const int t2 = s2 / EPL;                              // lane distance of the 2x2 partner (>= 32: none)
+  double acc[1] = {0.0};
+  for (int line = blockIdx.x * nwarp + warp; line < sel.nlines; line += gridDim.x * nwarp) {
+    int i, j;
+    if (sel.mode <= 1) {          // mod(i+j+ofs,2) == mode  (cz_solver.f90:549)
+      const int jj = line / sel.per_j, m = line - jj * sel.per_j;
+      j = G.jst + jj;
+      i = G.ist + ((G.ist + j + sel.ofs + sel.mode) & 1) + 2 * m;
+    } else if (sel.mode == 2) {   // all lines
+      const int jj = line / sel.per_j, m = line - jj * sel.per_j;
+      j = G.jst + jj; i = G.ist + m;
+    } else {                      // wavefront i+j == diag
+      j = sel.jlo + line; i = sel.diag - j;
+    }
+    if (i > G.ied) continue;      // warp-uniform
+    const long long base = G.at(G.kst, i, j);
+    // ---- source term in the cyclic layout (cz_solver.f90:569-579) -> exchange buffer ----
+    // loads are issued CH cells at a time before anything is stored, so that they overlap (x and dst may
+    // alias, the compiler must keep loads and stores in program order)
+    constexpr int CH = EPL < 8 ? EPL : 8;
+#pragma unroll
+    for (int m0 = 0; m0 < EPL; m0 += CH) {
+      REAL vs[CH], vn[CH], vw[CH], ve[CH], vb[CH], vm[CH];
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        const int k = lane + 32 * (m0 + c);
+        const long long off = base + (k < n ? k : 0);
+        vs[c] = x[off - G.plane]; vn[c] = x[off + G.plane]; vw[c] = x[off - G.nk]; ve[c] = x[off + G.nk];
+        vb[c] = rhs[off]; vm[c] = msk ? msk[off] : (REAL)1.0;
+      }
+      const REAL xlo = x[base - 1], xhi = x[base + n];
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        const int k = lane + 32 * (m0 + c);
+        REAL d = ((vs[c] + vn[c] + vw[c] + ve[c] - vb[c]) * r) * vm[c];
+        if (k == 0) d = (d + xlo * r) * vm[c];
+        if (k == n - 1) d = (d + xhi * r) * vm[c];
+        wb[LY::pos(k)] = (k < n) ? d : zero;
+      }
+    }
+    __syncwarp();
+    REAL d[EPL];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+      const float4 v = *reinterpret_cast<const float4*>(wb + q * LY::QSTR + lane * 4);
+      d[4 * q] = v.x; d[4 * q + 1] = v.y; d[4 * q + 2] = v.z; d[4 * q + 3] = v.w;
+    }
+    // ---- PCR stages: d1(k) = e*(d(k) - ap*d(k-s) - cp*d(k+s))  (cz_solver.f90:602) ----
+#pragma unroll
+    for (int p = 0; p < 5 + (EPL == 4 ? 2 : EPL == 8 ? 3 : EPL == 16 ? 4 : 5); ++p) {
+      if (p < stages) {
+        const int s = 1 << p;
+        const int t = s / EPL;                       // lane distance when s >= EPL
+        const REAL* tp = ts + (size_t)p * 3 * ROW + lane * 4;
+        REAL dn[EPL];
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+          const float4 ap4 = *reinterpret_cast<const float4*>(tp + q * LY::QSTR);
+          const float4 cp4 = *reinterpret_cast<const float4*>(tp + ROW + q * LY::QSTR);
+          const float4 e4 = *reinterpret_cast<const float4*>(tp + 2 * ROW + q * LY::QSTR);
+          const REAL apv[4] = {ap4.x, ap4.y, ap4.z, ap4.w}, cpv[4] = {cp4.x, cp4.y, cp4.z, cp4.w};
+          const REAL ev[4] = {e4.x, e4.y, e4.z, e4.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int m = 4 * q + e;
+            REAL dl, dr;
+            if (s < EPL) {
+              // left neighbour k-s: own register m-s, or register m-s+EPL of the lane below; right alike
+              if (m >= s) dl = d[m - s];
+              else { const REAL v = __shfl_up_sync(0xffffffffu, d[(m - s + EPL) & (EPL - 1)], 1); dl = lane >= 1 ? v : zero; }
+              if (m + s < EPL) dr = d[m + s];
+              else { const REAL v = __shfl_down_sync(0xffffffffu, d[(m + s - EPL) & (EPL - 1)], 1); dr = lane < 31 ? v : zero; }
+            } else {
+              const REAL vl = __shfl_up_sync(0xffffffffu, d[m], t), vr = __shfl_down_sync(0xffffffffu, d[m], t);
+              dl = lane >= t ? vl : zero;
+              dr = lane + t < 32 ? vr : zero;
+            }
+            dn[m] = ev[e] * (d[m] - apv[e] * dl - cpv[e] * dr);
+          }
+        }
+#pragma unroll
+        for (int m = 0; m < EPL; ++m) d[m] = dn[m];
+      }
+    }
+    // ---- last 2x2 stage (cz_solver.f90:612-630): d1 = (d_own - F1*d_partner)*F2, partner = k -+ s2 ----
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+      const float4 f1 = *reinterpret_cast<const float4*>(F1 + q * LY::QSTR + lane * 4);
+      const float4 f2 = *reinterpret_cast<const float4*>(F2 + q * LY::QSTR + lane * 4);
+      float4 o;
+      REAL pr[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const REAL v = __shfl_xor_sync(0xffffffffu, d[4 * q + e], t2 & 31);
+        pr[e] = (t2 < 32) ? v : zero;
+      }
+      o.x = (d[4 * q] - f1.x * pr[0]) * f2.x;
+      o.y = (d[4 * q + 1] - f1.y * pr[1]) * f2.y;
+      o.z = (d[4 * q + 2] - f1.z * pr[2]) * f2.z;
+      o.w = (d[4 * q + 3] - f1.w * pr[3]) * f2.w;
+      *reinterpret_cast<float4*>(wb + q * LY::QSTR + lane * 4) = o;
+    }
+    __syncwarp();
+    // ---- relaxation in the cyclic layout (cz_solver.f90:642-648) ----
+#pragma unroll
+    for (int m0 = 0; m0 < EPL; m0 += CH) {
+      REAL pp[CH], mk[CH];
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        const int k = lane + 32 * (m0 + c);
+        const long long off = base + (k < n ? k : 0);
+        pp[c] = x[off]; mk[c] = msk ? msk[off] : (REAL)1.0;
+      }
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        const int k = lane + 32 * (m0 + c);
+        if (k < n) {
+          const REAL dp = (wb[LY::pos(k)] - pp[c]) * omg * mk[c];
+          dst[base + k] = pp[c] + dp;
+          acc[0] += (double)(dp * dp);
+        }
+      }
+    }
+    __syncwarp();
+  }
+  grid_reduce<1>(acc, rb, finst);
+}
+
 }  // namespace
 
 void pcr_build_tables(cudaStream_t s, PcrTables& T, int n, int pn, bool last4) {
@@ -210,7 +393,7 @@ void pcr_free_tables(PcrTables& T) {
 }
 
 void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mode, int ofs, int diag, const REAL* x,
-                      REAL* dst, const REAL* msk, const REAL* rhs, REAL omg, int slot, bool add) {
+                      REAL* dst, const REAL* msk, const REAL* rhs, REAL omg, int slot, bool add, bool mask_is_inner) {
   const int n = G.ked - G.kst + 1;
   const int ni = G.ied - G.ist + 1, nj = G.jed - G.jst + 1;
   if (n != T.n) { fprintf(stderr, "czb200: pcr tables built for n=%d, called with n=%d\n", T.n, n); abort(); }
@@ -228,6 +411,32 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
   if ((size_t)grid > L.rb_blocks) grid = (int)L.rb_blocks;
   const size_t smem = 2 * (size_t)n * sizeof(REAL);
   FinStoreP fs{L.acc_st, slot, add ? 1 : 0};
+#ifndef _REAL_IS_DOUBLE_
+  static const bool no_warp = getenv("CZB_PCR_BLOCK") != nullptr;
+  if (!T.last4 && !no_warp && n >= 17 && n <= 1024) {   // warp-per-line kernel (2x2 last stage)
+    auto go = [&](auto epl) {
+      constexpr int EPL = decltype(epl)::value;
+      typedef PcrLay<EPL> LY;
+      const int wpb = (EPL == 32) ? 16 : 8;   // warps (= lines in flight) per CTA; one table copy per CTA
+      const size_t sm = sizeof(REAL) * ((size_t)T.stages * 3 * LY::ROW + 2 * LY::ROW + (size_t)wpb * LY::ROW);
+      int g = (sel.nlines + wpb - 1) / wpb;
+      const int cap = 148 * (int)(sm > 110 * 1024 ? 1 : 2);
+      if (g > cap) g = cap;
+      if ((size_t)g > L.rb_blocks) g = (int)L.rb_blocks;
+      static bool set = false;
+      if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp<EPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); set = true; }
+      // mask_is_inner: msk is imask_k of this geometry, i.e. exactly 1 on every cell of every line -> not read
+      k_pcr_warp<EPL><<<g, wpb * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, mask_is_inner ? nullptr : msk, rhs, omg, L.st, L.rb, fs);
+    };
+    if (n <= 128)      go(std::integral_constant<int, 4>{});
+    else if (n <= 256) go(std::integral_constant<int, 8>{});
+    else if (n <= 512) go(std::integral_constant<int, 16>{});
+    else               go(std::integral_constant<int, 32>{});
+    CZB_CHECK(cudaGetLastError());
+    count_launch();
+    return;
+  }
+#endif
   if (T.last4) {
     CZB_CHECK(cudaFuncSetAttribute(k_pcr_lines<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_pcr_lines<1><<<grid, nt, smem, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, msk, rhs, omg, L.st, L.rb, fs);

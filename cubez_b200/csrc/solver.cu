@@ -395,7 +395,7 @@ int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flo
   auto body = [&](int) {
     Launch L = launch();
     for (int color = 0; color < 2; ++color) {
-      launch_pcr_lines(L, G, T, color, ofs, 0, X, X, M, B, ac1, rs, color == 1);
+      launch_pcr_lines(L, G, T, color, ofs, 0, X, X, M, B, ac1, rs, color == 1, true);
       Comm_S(X, 1);
     }
     if (converge_check) {
@@ -426,7 +426,7 @@ int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, 
     Launch L = launch();
     bool first = true;
     for (int d = G.ist + G.jst; d <= G.ied + G.jed; ++d) {
-      launch_pcr_lines(L, G, T, 3, 0, d, X, X, M, B, ac1, rs, !first);
+      launch_pcr_lines(L, G, T, 3, 0, d, X, X, M, B, ac1, rs, !first, true);
       first = false;
     }
     Comm_S(X, 1);
@@ -455,7 +455,7 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
   auto body = [&](int) {
     Launch L = launch();
-    launch_pcr_lines(L, G, pcr2, 2, 0, 0, X, W, M, B, ac1, rs, false);
+    launch_pcr_lines(L, G, pcr2, 2, 0, 0, X, W, M, B, ac1, rs, false, true);
     launch_copy_inner(L, G, X, W);
     Comm_S(X, 1);
     if (converge_check) {
