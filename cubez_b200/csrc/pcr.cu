@@ -365,6 +365,208 @@ __global__ void __launch_bounds__(EPL == 32 ? 512 : 256, EPL == 32 ? 1 : 2) k_pc
   grid_reduce<1>(acc, rb, finst);
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// The same kernel with the NEXT line's source term fetched while the current line is reduced: stage p of
+// the current line issues the global loads of CPS cells per lane of the next line before its arithmetic
+// and turns them into d (cz_solver.f90:569-579) after it, so the memory latency hides behind the stage
+// and the loads need only 5*CPS registers.  Each warp owns two exchange buffers (current result / next
+// source).  Only for msk == 1 on all line cells (the solve loops); arithmetic identical to k_pcr_warp.
+template <int EPL>
+__device__ __forceinline__ void pcr_stage(REAL (&d)[EPL], const int p, const REAL* ts, const int lane) {
+  typedef PcrLay<EPL> LY;
+  constexpr int NQ = LY::NQ, ROW = LY::ROW;
+  const REAL zero = (REAL)0.0;
+  const int s = 1 << p;
+  const int t = s / EPL;                       // lane distance when s >= EPL
+  const REAL* tp = ts + (size_t)p * 3 * ROW + lane * 4;
+  REAL dn[EPL];
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    const float4 ap4 = *reinterpret_cast<const float4*>(tp + q * LY::QSTR);
+    const float4 cp4 = *reinterpret_cast<const float4*>(tp + ROW + q * LY::QSTR);
+    const float4 e4 = *reinterpret_cast<const float4*>(tp + 2 * ROW + q * LY::QSTR);
+    const REAL apv[4] = {ap4.x, ap4.y, ap4.z, ap4.w}, cpv[4] = {cp4.x, cp4.y, cp4.z, cp4.w};
+    const REAL ev[4] = {e4.x, e4.y, e4.z, e4.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int m = 4 * q + e;
+      REAL dl, dr;
+      if (s < EPL) {
+        if (m >= s) dl = d[m - s];
+        else { const REAL v = __shfl_up_sync(0xffffffffu, d[(m - s + EPL) & (EPL - 1)], 1); dl = lane >= 1 ? v : zero; }
+        if (m + s < EPL) dr = d[m + s];
+        else { const REAL v = __shfl_down_sync(0xffffffffu, d[(m + s - EPL) & (EPL - 1)], 1); dr = lane < 31 ? v : zero; }
+      } else {
+        const REAL vl = __shfl_up_sync(0xffffffffu, d[m], t), vr = __shfl_down_sync(0xffffffffu, d[m], t);
+        dl = lane >= t ? vl : zero;
+        dr = lane + t < 32 ? vr : zero;
+      }
+      dn[m] = ev[e] * (d[m] - apv[e] * dl - cpv[e] * dr);
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < EPL; ++m) d[m] = dn[m];
+}
+
+// source term of cells c0 .. c0+NC-1 (cyclic layout k = lane + 32 c) of the line starting at b:
+// pcr_src_load issues the loads, pcr_src_put turns them into d (msk == 1) in the exchange buffer
+template <int NC>
+__device__ __forceinline__ void pcr_src_load(REAL (&v)[6][NC], const REAL* x, const REAL* __restrict__ rhs, const Geo& G,
+                                             const long long b, const int c0, const int n, const int lane) {
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const int k = lane + 32 * (c0 + c);
+    const long long off = b + (k < n ? k : 0);
+    v[0][c] = x[off - G.plane]; v[1][c] = x[off + G.plane]; v[2][c] = x[off - G.nk]; v[3][c] = x[off + G.nk];
+    v[4][c] = rhs[off];
+    v[5][c] = (REAL)0.0;
+    if (k == 0) v[5][c] = x[b - 1];
+    if (k == n - 1) v[5][c] = x[b + n];
+  }
+}
+template <int EPL, int NC>
+__device__ __forceinline__ void pcr_src_put(const REAL (&v)[6][NC], REAL* wb, const int c0, const int n, const int lane, const REAL r) {
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const int k = lane + 32 * (c0 + c);
+    REAL d = (v[0][c] + v[1][c] + v[2][c] + v[3][c] - v[4][c]) * r;
+    if (k == 0 || k == n - 1) d = d + v[5][c] * r;
+    wb[PcrLay<EPL>::pos(k)] = (k < n) ? d : (REAL)0.0;
+  }
+}
+
+template <int EPL, int WPB>
+__global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo G, int n, int pn, int stages, const REAL* __restrict__ tab,
+                                                  const REAL* __restrict__ fin, LineSel sel, const REAL* x, REAL* dst,
+                                                  const REAL* __restrict__ rhs, REAL omg,
+                                                  const LoopState* st, RedBuf rb, FinStoreP finst) {
+  if (st && st->done) return;
+  typedef PcrLay<EPL> LY;
+  constexpr int NQ = LY::NQ, ROW = LY::ROW, NP = 32 * EPL;
+  constexpr int CPS = EPL == 4 ? 1 : EPL == 32 ? 4 : 2;      // next-line cells per lane fetched per stage
+  constexpr int MAXST = 5 + (EPL == 4 ? 2 : EPL == 8 ? 3 : EPL == 16 ? 4 : 5);
+  extern __shared__ double sm_raw[];
+  REAL* ts = reinterpret_cast<REAL*>(sm_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  REAL* F1 = ts + (size_t)stages * 3 * ROW;
+  REAL* F2 = F1 + ROW;
+  REAL* wb0 = F2 + ROW + (size_t)warp * 2 * ROW;       // this warp's two exchange buffers
+  const REAL zero = (REAL)0.0;
+  const int s2 = 1 << (pn - 1);
+  for (int idx = tid; idx < stages * 3 * NP; idx += WPB * 32) {
+    const int row = idx / NP, k = idx - row * NP;
+    ts[(size_t)row * ROW + LY::pos(k)] = (k < n) ? tab[(size_t)row * n + k] : zero;
+  }
+  for (int k = tid; k < NP; k += WPB * 32) {
+    REAL f1 = zero, f2 = zero;
+    if (k < n) {
+      if (k < s2) { f1 = fin[k]; f2 = fin[2 * (size_t)s2 + k]; }
+      else        { f1 = fin[(size_t)s2 + (k - s2)]; f2 = fin[2 * (size_t)s2 + (k - s2)]; }
+    }
+    F1[LY::pos(k)] = f1; F2[LY::pos(k)] = f2;
+  }
+  __syncthreads();
+  const REAL r = (REAL)1.0 / (REAL)6.0;
+  const int t2 = s2 / EPL;
+  double acc[1] = {0.0};
+  // first cell of line `line`, or -1 when the line does not exist
+  auto line_base = [&](int line) -> long long {
+    if (line >= sel.nlines) return -1;
+    int i, j;
+    if (sel.mode <= 1) {
+      const int jj = line / sel.per_j, m = line - jj * sel.per_j;
+      j = G.jst + jj;
+      i = G.ist + ((G.ist + j + sel.ofs + sel.mode) & 1) + 2 * m;
+    } else if (sel.mode == 2) {
+      const int jj = line / sel.per_j, m = line - jj * sel.per_j;
+      j = G.jst + jj; i = G.ist + m;
+    } else {
+      j = sel.jlo + line; i = sel.diag - j;
+    }
+    return (i > G.ied) ? -1 : G.at(G.kst, i, j);
+  };
+  auto full_load = [&](long long b, REAL* wb) {
+    constexpr int CH = EPL < 8 ? EPL : 8;
+#pragma unroll
+    for (int m0 = 0; m0 < EPL; m0 += CH) {
+      REAL v[6][CH];
+      pcr_src_load<CH>(v, x, rhs, G, b, m0, n, lane);
+      pcr_src_put<EPL, CH>(v, wb, m0, n, lane, r);
+    }
+  };
+  const int lstride = gridDim.x * WPB;
+  int line = blockIdx.x * WPB + warp;
+  long long base = line_base(line);
+  int buf = 0;
+  if (base >= 0) full_load(base, wb0);
+  while (line < sel.nlines) {
+    const int nline = line + lstride;
+    const long long nbase = line_base(nline);
+    REAL* wc = wb0 + buf * ROW;
+    REAL* wn = wb0 + (buf ^ 1) * ROW;
+    __syncwarp();
+    if (base >= 0) {
+      REAL d[EPL];
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
+        const float4 v = *reinterpret_cast<const float4*>(wc + q * LY::QSTR + lane * 4);
+        d[4 * q] = v.x; d[4 * q + 1] = v.y; d[4 * q + 2] = v.z; d[4 * q + 3] = v.w;
+      }
+#pragma unroll
+      for (int p = 0; p < MAXST; ++p) {
+        if (p < stages) {
+          REAL v[6][CPS];
+          const bool pf = (nbase >= 0) && (p * CPS < EPL);
+          if (pf) pcr_src_load<CPS>(v, x, rhs, G, nbase, p * CPS, n, lane);
+          pcr_stage<EPL>(d, p, ts, lane);
+          if (pf) pcr_src_put<EPL, CPS>(v, wn, p * CPS, n, lane, r);
+        }
+      }
+      // own-line values for the relaxation, in flight during the 2x2 stage
+      REAL pp[EPL];
+#pragma unroll
+      for (int c = 0; c < EPL; ++c) {
+        const int k = lane + 32 * c;
+        pp[c] = x[base + (k < n ? k : 0)];
+      }
+      // ---- last 2x2 stage (cz_solver.f90:612-630) ----
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
+        const float4 f1 = *reinterpret_cast<const float4*>(F1 + q * LY::QSTR + lane * 4);
+        const float4 f2 = *reinterpret_cast<const float4*>(F2 + q * LY::QSTR + lane * 4);
+        float4 o;
+        REAL pr[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const REAL v = __shfl_xor_sync(0xffffffffu, d[4 * q + e], t2 & 31);
+          pr[e] = (t2 < 32) ? v : zero;
+        }
+        o.x = (d[4 * q] - f1.x * pr[0]) * f2.x;
+        o.y = (d[4 * q + 1] - f1.y * pr[1]) * f2.y;
+        o.z = (d[4 * q + 2] - f1.z * pr[2]) * f2.z;
+        o.w = (d[4 * q + 3] - f1.w * pr[3]) * f2.w;
+        *reinterpret_cast<float4*>(wc + q * LY::QSTR + lane * 4) = o;
+      }
+      __syncwarp();
+      // ---- relaxation in the cyclic layout (cz_solver.f90:642-648), msk == 1 ----
+#pragma unroll
+      for (int c = 0; c < EPL; ++c) {
+        const int k = lane + 32 * c;
+        if (k < n) {
+          const REAL dp = (wc[LY::pos(k)] - pp[c]) * omg;
+          dst[base + k] = pp[c] + dp;
+          acc[0] += (double)(dp * dp);
+        }
+      }
+    } else if (nbase >= 0) {
+      full_load(nbase, wn);
+    }
+    line = nline; base = nbase; buf ^= 1;
+  }
+  grid_reduce<1>(acc, rb, finst);
+}
+
 }  // namespace
 
 void pcr_build_tables(cudaStream_t s, PcrTables& T, int n, int pn, bool last4) {
@@ -414,6 +616,29 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
 #ifndef _REAL_IS_DOUBLE_
   static const bool no_warp = getenv("CZB_PCR_BLOCK") != nullptr;
   if (!T.last4 && !no_warp && n >= 17 && n <= 1024) {   // warp-per-line kernel (2x2 last stage)
+    auto go_pf = [&](auto epl, auto wpb_) {   // prefetching variant, msk not read
+      constexpr int EPL = decltype(epl)::value, WPB = decltype(wpb_)::value;
+      typedef PcrLay<EPL> LY;
+      const size_t sm = sizeof(REAL) * ((size_t)T.stages * 3 * LY::ROW + 2 * LY::ROW + (size_t)WPB * 2 * LY::ROW);
+      int g = (sel.nlines + WPB - 1) / WPB;
+      const int cap = 148 * (EPL == 32 ? 1 : 2);
+      if (g > cap) g = cap;
+      if ((size_t)g > L.rb_blocks) g = (int)L.rb_blocks;
+      static size_t sm_set = 0;
+      if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_pf<EPL, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
+      k_pcr_warp_pf<EPL, WPB><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, L.st, L.rb, fs);
+    };
+    static const bool no_pf = getenv("CZB_PCR_NOPF") != nullptr;
+    const int cps = n <= 128 ? 1 : n <= 512 ? 2 : 4, epl = n <= 128 ? 4 : n <= 256 ? 8 : n <= 512 ? 16 : 32;
+    if (mask_is_inner && !no_pf && T.stages * cps >= epl) {
+      if (n <= 128)      go_pf(std::integral_constant<int, 4>{}, std::integral_constant<int, 8>{});
+      else if (n <= 256) go_pf(std::integral_constant<int, 8>{}, std::integral_constant<int, 8>{});
+      else if (n <= 512) go_pf(std::integral_constant<int, 16>{}, std::integral_constant<int, 8>{});
+      else               go_pf(std::integral_constant<int, 32>{}, std::integral_constant<int, 12>{});
+      CZB_CHECK(cudaGetLastError());
+      count_launch();
+      return;
+    }
     auto go = [&](auto epl) {
       constexpr int EPL = decltype(epl)::value;
       typedef PcrLay<EPL> LY;
