@@ -376,7 +376,6 @@ template <int EPL>
 __device__ __forceinline__ void pcr_stage(REAL (&d)[EPL], const int p, const REAL* ts, const int lane) {
   typedef PcrLay<EPL> LY;
   constexpr int NQ = LY::NQ, ROW = LY::ROW;
-  const REAL zero = (REAL)0.0;
   const int s = 1 << p;
   const int t = s / EPL;                       // lane distance when s >= EPL
   const REAL* tp = ts + (size_t)p * 3 * ROW + lane * 4;
@@ -393,14 +392,15 @@ __device__ __forceinline__ void pcr_stage(REAL (&d)[EPL], const int p, const REA
       const int m = 4 * q + e;
       REAL dl, dr;
       if (s < EPL) {
+        // A neighbour outside the line needs no select: its coefficient ap / cp is exactly 0 (k_pcr_tables:
+        // a(k) = 0 for k < s, c(k) = 0 for k + s >= n) and the shuffle then returns the lane's own finite d.
         if (m >= s) dl = d[m - s];
-        else { const REAL v = __shfl_up_sync(0xffffffffu, d[(m - s + EPL) & (EPL - 1)], 1); dl = lane >= 1 ? v : zero; }
+        else dl = __shfl_up_sync(0xffffffffu, d[(m - s + EPL) & (EPL - 1)], 1);
         if (m + s < EPL) dr = d[m + s];
-        else { const REAL v = __shfl_down_sync(0xffffffffu, d[(m + s - EPL) & (EPL - 1)], 1); dr = lane < 31 ? v : zero; }
+        else dr = __shfl_down_sync(0xffffffffu, d[(m + s - EPL) & (EPL - 1)], 1);
       } else {
-        const REAL vl = __shfl_up_sync(0xffffffffu, d[m], t), vr = __shfl_down_sync(0xffffffffu, d[m], t);
-        dl = lane >= t ? vl : zero;
-        dr = lane + t < 32 ? vr : zero;
+        dl = __shfl_up_sync(0xffffffffu, d[m], t);
+        dr = __shfl_down_sync(0xffffffffu, d[m], t);
       }
       dn[m] = ev[e] * (d[m] - apv[e] * dl - cpv[e] * dr);
     }
@@ -409,30 +409,34 @@ __device__ __forceinline__ void pcr_stage(REAL (&d)[EPL], const int p, const REA
   for (int m = 0; m < EPL; ++m) d[m] = dn[m];
 }
 
-// source term of cells c0 .. c0+NC-1 (cyclic layout k = lane + 32 c) of the line starting at b:
-// pcr_src_load issues the loads, pcr_src_put turns them into d (msk == 1) in the exchange buffer
+// source term of cells c0 .. c0+NC-1 (cyclic layout k = lane + 32 c) of a line: pcr_src_load issues the
+// loads, pcr_src_put turns them into d (msk == 1) in the exchange buffer.  PcrSrc holds the addresses of
+// the lane's cell k = lane in the four neighbour lines and in the source array, so every load is
+// pointer + immediate offset; xl / xh point at the two Dirichlet-side neighbours x(kst-1), x(ked+1).
+struct PcrSrc { const REAL *ps, *pn, *pw, *pe, *pb, *xl; };
 template <int NC>
-__device__ __forceinline__ void pcr_src_load(REAL (&v)[6][NC], const REAL* x, const REAL* __restrict__ rhs, const Geo& G,
-                                             const long long b, const int c0, const int n, const int lane) {
+__device__ __forceinline__ void pcr_src_load(REAL (&v)[6][NC], const PcrSrc& P, const int c0, const int n, const int lane) {
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
-    const int k = lane + 32 * (c0 + c);
-    const long long off = b + (k < n ? k : 0);
-    v[0][c] = x[off - G.plane]; v[1][c] = x[off + G.plane]; v[2][c] = x[off - G.nk]; v[3][c] = x[off + G.nk];
-    v[4][c] = rhs[off];
-    v[5][c] = (REAL)0.0;
-    if (k == 0) v[5][c] = x[b - 1];
-    if (k == n - 1) v[5][c] = x[b + n];
+    const int cc = c0 + c;
+    const bool ok = lane < n - 32 * cc;          // k = lane + 32 cc < n
+    v[0][c] = v[1][c] = v[2][c] = v[3][c] = v[4][c] = v[5][c] = (REAL)0.0;
+    if (ok) {
+      v[0][c] = P.ps[32 * cc]; v[1][c] = P.pn[32 * cc]; v[2][c] = P.pw[32 * cc]; v[3][c] = P.pe[32 * cc];
+      v[4][c] = P.pb[32 * cc];
+    }
+    if (cc == 0 && lane == 0) v[5][c] = P.xl[0];
+    if (lane == n - 1 - 32 * cc) v[5][c] = P.xl[n + 1];
   }
 }
 template <int EPL, int NC>
-__device__ __forceinline__ void pcr_src_put(const REAL (&v)[6][NC], REAL* wb, const int c0, const int n, const int lane, const REAL r) {
+__device__ __forceinline__ void pcr_src_put(const REAL (&v)[6][NC], REAL* wbl, const int c0, const int n, const int lane, const REAL r) {
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
-    const int k = lane + 32 * (c0 + c);
+    const int cc = c0 + c;
     REAL d = (v[0][c] + v[1][c] + v[2][c] + v[3][c] - v[4][c]) * r;
-    if (k == 0 || k == n - 1) d = d + v[5][c] * r;
-    wb[PcrLay<EPL>::pos(k)] = (k < n) ? d : (REAL)0.0;
+    if ((cc == 0 && lane == 0) || lane == n - 1 - 32 * cc) d = d + v[5][c] * r;
+    wbl[(128 / EPL) * cc] = d;                   // wbl = wb + pos(lane); pos(lane + 32 cc) = pos(lane) + (32/EPL)*4*cc
   }
 }
 
@@ -486,13 +490,19 @@ __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo
     }
     return (i > G.ied) ? -1 : G.at(G.kst, i, j);
   };
+  const int posl = LY::pos(lane);                       // pos(lane + 32 c) = posl + (128/EPL) c
+  auto src_of = [&](long long b) -> PcrSrc {
+    const REAL* px = x + b + lane;
+    return PcrSrc{px - G.plane, px + G.plane, px - G.nk, px + G.nk, rhs + b + lane, x + b - 1};
+  };
   auto full_load = [&](long long b, REAL* wb) {
     constexpr int CH = EPL < 8 ? EPL : 8;
+    const PcrSrc P = src_of(b);
 #pragma unroll
     for (int m0 = 0; m0 < EPL; m0 += CH) {
       REAL v[6][CH];
-      pcr_src_load<CH>(v, x, rhs, G, b, m0, n, lane);
-      pcr_src_put<EPL, CH>(v, wb, m0, n, lane, r);
+      pcr_src_load<CH>(v, P, m0, n, lane);
+      pcr_src_put<EPL, CH>(v, wb + posl, m0, n, lane, r);
     }
   };
   const int lstride = gridDim.x * WPB;
@@ -507,6 +517,7 @@ __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo
     REAL* wn = wb0 + (buf ^ 1) * ROW;
     __syncwarp();
     if (base >= 0) {
+      const PcrSrc P = src_of(nbase >= 0 ? nbase : base);
       REAL d[EPL];
 #pragma unroll
       for (int q = 0; q < NQ; ++q) {
@@ -518,18 +529,17 @@ __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo
         if (p < stages) {
           REAL v[6][CPS];
           const bool pf = (nbase >= 0) && (p * CPS < EPL);
-          if (pf) pcr_src_load<CPS>(v, x, rhs, G, nbase, p * CPS, n, lane);
+          if (pf) pcr_src_load<CPS>(v, P, p * CPS, n, lane);
           pcr_stage<EPL>(d, p, ts, lane);
-          if (pf) pcr_src_put<EPL, CPS>(v, wn, p * CPS, n, lane, r);
+          if (pf) pcr_src_put<EPL, CPS>(v, wn + posl, p * CPS, n, lane, r);
         }
       }
       // own-line values for the relaxation, in flight during the 2x2 stage
+      const REAL* px = x + base + lane;
+      REAL* pd = dst + base + lane;
       REAL pp[EPL];
 #pragma unroll
-      for (int c = 0; c < EPL; ++c) {
-        const int k = lane + 32 * c;
-        pp[c] = x[base + (k < n ? k : 0)];
-      }
+      for (int c = 0; c < EPL; ++c) pp[c] = (lane < n - 32 * c) ? px[32 * c] : zero;
       // ---- last 2x2 stage (cz_solver.f90:612-630) ----
 #pragma unroll
       for (int q = 0; q < NQ; ++q) {
@@ -549,15 +559,12 @@ __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo
         *reinterpret_cast<float4*>(wc + q * LY::QSTR + lane * 4) = o;
       }
       __syncwarp();
-      // ---- relaxation in the cyclic layout (cz_solver.f90:642-648), msk == 1 ----
+      // ---- relaxation in the cyclic layout (cz_solver.f90:642-648), msk == 1; cells k >= n hold 0 - 0 ----
 #pragma unroll
       for (int c = 0; c < EPL; ++c) {
-        const int k = lane + 32 * c;
-        if (k < n) {
-          const REAL dp = (wc[LY::pos(k)] - pp[c]) * omg;
-          dst[base + k] = pp[c] + dp;
-          acc[0] += (double)(dp * dp);
-        }
+        const REAL dp = (wc[posl + (128 / EPL) * c] - pp[c]) * omg;
+        if (lane < n - 32 * c) pd[32 * c] = pp[c] + dp;
+        acc[0] += (double)(dp * dp);
       }
     } else if (nbase >= 0) {
       full_load(nbase, wn);
