@@ -366,6 +366,7 @@ __global__ void __launch_bounds__(EPL == 32 ? 512 : 256, EPL == 32 ? 1 : 2) k_pc
 }
 
 
+#ifndef _REAL_IS_DOUBLE_
 // ------------------------------------------------------------------------------------------------
 // The same kernel with the NEXT line's source term fetched while the current line is reduced: stage p of
 // the current line issues the global loads of CPS cells per lane of the next line before its arithmetic
@@ -409,6 +410,58 @@ __device__ __forceinline__ void pcr_stage(REAL (&d)[EPL], const int p, const REA
   for (int m = 0; m < EPL; ++m) d[m] = dn[m];
 }
 
+// Packed variant: two neighbouring cells of a lane travel as one 64-bit register pair and are reduced by
+// Blackwell's FADD2 / FMUL2 / FFMA2.  ptxas contracts mul.rn.f32x2 + sub.rn.f32x2 into one FFMA2 (one rounding
+// instead of two) even with --fmad false, so a product that feeds a subtraction is written fma(a, b, -0) with
+// the -0 pair coming from a kernel argument: a*b + (-0) rounds exactly like a*b and cannot be contracted.
+typedef unsigned long long pk_t;
+__device__ __forceinline__ pk_t pk2(float x, float y) { pk_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(x), "f"(y)); return r; }
+__device__ __forceinline__ float lo2(pk_t v) { return __uint_as_float((unsigned)v); }
+__device__ __forceinline__ float hi2(pk_t v) { return __uint_as_float((unsigned)(v >> 32)); }
+__device__ __forceinline__ pk_t sub2(pk_t a, pk_t b) { pk_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ pk_t mul2(pk_t a, pk_t b) { pk_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ pk_t fma2(pk_t a, pk_t b, pk_t c) { pk_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
+template <int EPL>
+__device__ __forceinline__ void pcr_stage_pk(pk_t (&D)[EPL / 2], const int p, const REAL* ts, const int lane, const pk_t nz) {
+  typedef PcrLay<EPL> LY;
+  constexpr int NQ = LY::NQ, ROW = LY::ROW, NH = EPL / 2;
+  const int s = 1 << p;
+  const int t = s / EPL;
+  const REAL* tp = ts + (size_t)p * 3 * ROW + lane * 4;
+  pk_t DN[NH];
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    const ulonglong2 ap4 = *reinterpret_cast<const ulonglong2*>(tp + q * LY::QSTR);
+    const ulonglong2 cp4 = *reinterpret_cast<const ulonglong2*>(tp + ROW + q * LY::QSTR);
+    const ulonglong2 e4 = *reinterpret_cast<const ulonglong2*>(tp + 2 * ROW + q * LY::QSTR);
+    const pk_t apv[2] = {ap4.x, ap4.y}, cpv[2] = {cp4.x, cp4.y}, ev[2] = {e4.x, e4.y};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int j = 2 * q + h;                   // pair j = cells 2j, 2j+1 of the lane
+      pk_t dl, dr;
+      if (s == 1) {                              // neighbours straddle the pairs
+        const float l0 = (j >= 1) ? hi2(D[j - 1]) : __shfl_up_sync(0xffffffffu, hi2(D[NH - 1]), 1);
+        const float r1 = (j + 1 < NH) ? lo2(D[j + 1]) : __shfl_down_sync(0xffffffffu, lo2(D[0]), 1);
+        dl = pk2(l0, lo2(D[j]));
+        dr = pk2(hi2(D[j]), r1);
+      } else if (s < EPL) {
+        const int hs = s / 2;
+        if (j >= hs) dl = D[j - hs];
+        else dl = __shfl_up_sync(0xffffffffu, D[(j - hs + NH) & (NH - 1)], 1);
+        if (j + hs < NH) dr = D[j + hs];
+        else dr = __shfl_down_sync(0xffffffffu, D[(j + hs - NH) & (NH - 1)], 1);
+      } else {
+        dl = __shfl_up_sync(0xffffffffu, D[j], t);
+        dr = __shfl_down_sync(0xffffffffu, D[j], t);
+      }
+      DN[j] = mul2(ev[h], sub2(sub2(D[j], fma2(apv[h], dl, nz)), fma2(cpv[h], dr, nz)));
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NH; ++j) D[j] = DN[j];
+}
+
 // source term of cells c0 .. c0+NC-1 (cyclic layout k = lane + 32 c) of a line: pcr_src_load issues the
 // loads, pcr_src_put turns them into d (msk == 1) in the exchange buffer.  PcrSrc holds the addresses of
 // the lane's cell k = lane in the four neighbour lines and in the source array, so every load is
@@ -443,7 +496,7 @@ __device__ __forceinline__ void pcr_src_put(const REAL (&v)[6][NC], REAL* wbl, c
 template <int EPL, int WPB>
 __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo G, int n, int pn, int stages, const REAL* __restrict__ tab,
                                                   const REAL* __restrict__ fin, LineSel sel, const REAL* x, REAL* dst,
-                                                  const REAL* __restrict__ rhs, REAL omg,
+                                                  const REAL* __restrict__ rhs, REAL omg, pk_t nz,
                                                   const LoopState* st, RedBuf rb, FinStoreP finst) {
   if (st && st->done) return;
   typedef PcrLay<EPL> LY;
@@ -518,11 +571,11 @@ __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo
     __syncwarp();
     if (base >= 0) {
       const PcrSrc P = src_of(nbase >= 0 ? nbase : base);
-      REAL d[EPL];
+      pk_t D[EPL / 2];
 #pragma unroll
       for (int q = 0; q < NQ; ++q) {
-        const float4 v = *reinterpret_cast<const float4*>(wc + q * LY::QSTR + lane * 4);
-        d[4 * q] = v.x; d[4 * q + 1] = v.y; d[4 * q + 2] = v.z; d[4 * q + 3] = v.w;
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(wc + q * LY::QSTR + lane * 4);
+        D[2 * q] = v.x; D[2 * q + 1] = v.y;
       }
 #pragma unroll
       for (int p = 0; p < MAXST; ++p) {
@@ -530,7 +583,7 @@ __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo
           REAL v[6][CPS];
           const bool pf = (nbase >= 0) && (p * CPS < EPL);
           if (pf) pcr_src_load<CPS>(v, P, p * CPS, n, lane);
-          pcr_stage<EPL>(d, p, ts, lane);
+          pcr_stage_pk<EPL>(D, p, ts, lane, nz);
           if (pf) pcr_src_put<EPL, CPS>(v, wn + posl, p * CPS, n, lane, r);
         }
       }
@@ -543,20 +596,18 @@ __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo
       // ---- last 2x2 stage (cz_solver.f90:612-630) ----
 #pragma unroll
       for (int q = 0; q < NQ; ++q) {
-        const float4 f1 = *reinterpret_cast<const float4*>(F1 + q * LY::QSTR + lane * 4);
-        const float4 f2 = *reinterpret_cast<const float4*>(F2 + q * LY::QSTR + lane * 4);
-        float4 o;
-        REAL pr[4];
+        const ulonglong2 f1 = *reinterpret_cast<const ulonglong2*>(F1 + q * LY::QSTR + lane * 4);
+        const ulonglong2 f2 = *reinterpret_cast<const ulonglong2*>(F2 + q * LY::QSTR + lane * 4);
+        pk_t pr[2];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const REAL v = __shfl_xor_sync(0xffffffffu, d[4 * q + e], t2 & 31);
-          pr[e] = (t2 < 32) ? v : zero;
+        for (int h = 0; h < 2; ++h) {
+          const pk_t v = __shfl_xor_sync(0xffffffffu, D[2 * q + h], t2 & 31);
+          pr[h] = (t2 < 32) ? v : 0ull;
         }
-        o.x = (d[4 * q] - f1.x * pr[0]) * f2.x;
-        o.y = (d[4 * q + 1] - f1.y * pr[1]) * f2.y;
-        o.z = (d[4 * q + 2] - f1.z * pr[2]) * f2.z;
-        o.w = (d[4 * q + 3] - f1.w * pr[3]) * f2.w;
-        *reinterpret_cast<float4*>(wc + q * LY::QSTR + lane * 4) = o;
+        ulonglong2 o;
+        o.x = mul2(sub2(D[2 * q], fma2(f1.x, pr[0], nz)), f2.x);
+        o.y = mul2(sub2(D[2 * q + 1], fma2(f1.y, pr[1], nz)), f2.y);
+        *reinterpret_cast<ulonglong2*>(wc + q * LY::QSTR + lane * 4) = o;
       }
       __syncwarp();
       // ---- relaxation in the cyclic layout (cz_solver.f90:642-648), msk == 1; cells k >= n hold 0 - 0 ----
@@ -573,6 +624,7 @@ __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo
   }
   grid_reduce<1>(acc, rb, finst);
 }
+#endif  // !_REAL_IS_DOUBLE_
 
 }  // namespace
 
@@ -633,7 +685,7 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       if ((size_t)g > L.rb_blocks) g = (int)L.rb_blocks;
       static size_t sm_set = 0;
       if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_pf<EPL, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
-      k_pcr_warp_pf<EPL, WPB><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, L.st, L.rb, fs);
+      k_pcr_warp_pf<EPL, WPB><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
     };
     static const bool no_pf = getenv("CZB_PCR_NOPF") != nullptr;
     const int cps = n <= 128 ? 1 : n <= 512 ? 2 : 4, epl = n <= 128 ? 4 : n <= 256 ? 8 : n <= 512 ? 16 : 32;
