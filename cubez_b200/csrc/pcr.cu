@@ -624,6 +624,270 @@ __global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo
   }
   grid_reduce<1>(acc, rb, finst);
 }
+
+// ------------------------------------------------------------------------------------------------
+// Coefficient tables in TENSOR MEMORY.  In the kernel above the shared-memory pipe is the limiter (ncu:
+// l1tex 90 % busy, 2/3 of its wavefronts are the table reads: 3 values per cell and stage).  The tables
+// are per-lane private data ("lane l needs the coefficients of its own EPL cells"), which is exactly the
+// shape of Blackwell's tensor memory: 128 lanes x 512 columns x 32 bit per SM, read with tcgen05.ld
+// (32x32b: thread i of a warp reads TMEM lane 32*(warp%4)+i, N consecutive columns) at many times the
+// shared-memory bandwidth and off the LSU pipe.  Row R of the table set (3 per stage: ap, cp, e; then
+// the two rows of the last 2x2 stage) occupies columns R*EPL .. R*EPL+EPL-1; the four lane quarters
+// hold identical copies, written once per CTA with tcgen05.st.  No MMA is involved.  EPL = 32 (lines of
+// 513..1024 cells) has 29 rows x 32 columns > 512: its stages >= 5 and the 2x2 rows stay in shared memory.
+struct Tm24 { uint32_t a[8], c[8], e[8]; };
+__device__ __forceinline__ void tm_ld8(uint32_t (&r)[8], const uint32_t addr) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(addr));
+}
+template <int EPL>
+__device__ __forceinline__ void tm_issue(Tm24& t, const uint32_t tl, const int p, const int h) {
+  const uint32_t col = tl + (uint32_t)(3 * p * EPL + 8 * h);
+  tm_ld8(t.a, col); tm_ld8(t.c, col + EPL); tm_ld8(t.e, col + 2 * EPL);
+}
+// the registers of t are valid only after this wait; passing them through makes the dependence explicit
+__device__ __forceinline__ void tm_wait(Tm24& t) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(t.a[0]), "+r"(t.a[1]), "+r"(t.a[2]), "+r"(t.a[3]), "+r"(t.a[4]), "+r"(t.a[5]), "+r"(t.a[6]), "+r"(t.a[7]),
+                 "+r"(t.c[0]), "+r"(t.c[1]), "+r"(t.c[2]), "+r"(t.c[3]), "+r"(t.c[4]), "+r"(t.c[5]), "+r"(t.c[6]), "+r"(t.c[7]),
+                 "+r"(t.e[0]), "+r"(t.e[1]), "+r"(t.e[2]), "+r"(t.e[3]), "+r"(t.e[4]), "+r"(t.e[5]), "+r"(t.e[6]), "+r"(t.e[7])
+               :: "memory");
+}
+__device__ __forceinline__ pk_t pku(uint32_t lo, uint32_t hi) { pk_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi)); return r; }
+
+template <int EPL, int WPB>
+__global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int pn, int stages, const REAL* __restrict__ tab,
+                                                  const REAL* __restrict__ fin, LineSel sel, const REAL* x, REAL* dst,
+                                                  const REAL* __restrict__ rhs, REAL omg, pk_t nz,
+                                                  const LoopState* st, RedBuf rb, FinStoreP finst) {
+  if (st && st->done) return;
+  typedef PcrLay<EPL> LY;
+  constexpr int NQ = LY::NQ, ROW = LY::ROW, NP = 32 * EPL, NH = EPL / 2, GH = EPL / 8;
+  constexpr int CPS = EPL == 32 ? 4 : 2;
+  constexpr int MAXST = 5 + (EPL == 8 ? 3 : EPL == 16 ? 4 : 5);
+  constexpr int TP = EPL == 32 ? 5 : MAXST;              // stages whose tables live in tensor memory
+  constexpr bool FTM = EPL != 32;                        // 2x2 rows in tensor memory
+  static_assert(EPL >= 8 && WPB >= 4, "tensor-memory variant: EPL 8, 16, 32");
+  extern __shared__ double sm_raw[];
+  __shared__ uint32_t tm_base_s;
+  REAL* sm = reinterpret_cast<REAL*>(sm_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const REAL zero = (REAL)0.0;
+  const int s2 = 1 << (pn - 1);
+  const int rows = 3 * stages + 2;
+  const int rows_tm = FTM ? rows : (stages < TP ? 3 * stages : 3 * TP);
+  const int rows_sm = rows - rows_tm;                    // shared-memory rows: rows_tm .. rows-1
+  REAL* ts_s = sm - (size_t)rows_tm * ROW;               // so that row R sits at ts_s + R*ROW
+  REAL* wb0 = sm + (size_t)rows_sm * ROW + (size_t)warp * 2 * ROW;
+  auto table = [&](int R, int k) -> REAL {               // entry of row R for cell k (0 beyond the line)
+    if (k >= n) return zero;
+    if (R < 3 * stages) return tab[(size_t)R * n + k];
+    if (R == 3 * stages) return (k < s2) ? fin[k] : fin[(size_t)s2 + (k - s2)];
+    return (k < s2) ? fin[2 * (size_t)s2 + k] : fin[2 * (size_t)s2 + (k - s2)];
+  };
+  // ---- tensor memory: allocate all 512 columns (one CTA per SM), fill the four lane quarters ----
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 :: "r"((uint32_t)__cvta_generic_to_shared(&tm_base_s)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  for (int idx = tid; idx < rows_sm * NP; idx += WPB * 32) {
+    const int row = idx / NP, k = idx - row * NP;
+    sm[(size_t)row * ROW + LY::pos(k)] = table(rows_tm + row, k);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tl = tm_base_s + ((uint32_t)((warp & 3) * 32) << 16);   // this warp's lane quarter
+  if (warp < 4) {
+    for (int R = 0; R < rows_tm; ++R) {
+#pragma unroll
+      for (int m0 = 0; m0 < EPL; m0 += 4) {
+        uint32_t v[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[e] = __float_as_uint(table(R, EPL * lane + m0 + e));
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
+                     :: "r"(tl + (uint32_t)(R * EPL + m0)), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
+      }
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+  const REAL r = (REAL)1.0 / (REAL)6.0;
+  const int t2 = s2 / EPL;
+  double acc[1] = {0.0};
+  auto line_base = [&](int line) -> long long {
+    if (line >= sel.nlines) return -1;
+    int i, j;
+    if (sel.mode <= 1) {
+      const int jj = line / sel.per_j, m = line - jj * sel.per_j;
+      j = G.jst + jj;
+      i = G.ist + ((G.ist + j + sel.ofs + sel.mode) & 1) + 2 * m;
+    } else if (sel.mode == 2) {
+      const int jj = line / sel.per_j, m = line - jj * sel.per_j;
+      j = G.jst + jj; i = G.ist + m;
+    } else {
+      j = sel.jlo + line; i = sel.diag - j;
+    }
+    return (i > G.ied) ? -1 : G.at(G.kst, i, j);
+  };
+  const int posl = LY::pos(lane);
+  auto src_of = [&](long long b) -> PcrSrc {
+    const REAL* px = x + b + lane;
+    return PcrSrc{px - G.plane, px + G.plane, px - G.nk, px + G.nk, rhs + b + lane, x + b - 1};
+  };
+  auto full_load = [&](long long b, REAL* wb) {
+    constexpr int CH = 8;
+    const PcrSrc P = src_of(b);
+#pragma unroll
+    for (int m0 = 0; m0 < EPL; m0 += CH) {
+      REAL v[6][CH];
+      pcr_src_load<CH>(v, P, m0, n, lane);
+      pcr_src_put<EPL, CH>(v, wb + posl, m0, n, lane, r);
+    }
+  };
+  const int lstride = gridDim.x * WPB;
+  int line = blockIdx.x * WPB + warp;
+  long long base = line_base(line);
+  int buf = 0;
+  if (base >= 0) full_load(base, wb0);
+  while (line < sel.nlines) {
+    const int nline = line + lstride;
+    const long long nbase = line_base(nline);
+    REAL* wc = wb0 + buf * ROW;
+    REAL* wn = wb0 + (buf ^ 1) * ROW;
+    __syncwarp();
+    if (base >= 0) {
+      const PcrSrc P = src_of(nbase >= 0 ? nbase : base);
+      pk_t D[NH];
+      Tm24 T[2];
+      tm_issue<EPL>(T[0], tl, 0, 0);
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(wc + q * LY::QSTR + lane * 4);
+        D[2 * q] = v.x; D[2 * q + 1] = v.y;
+      }
+#pragma unroll
+      for (int p = 0; p < MAXST; ++p) {
+        if (p < stages) {
+          REAL v[6][CPS];
+          const bool pf = (nbase >= 0) && (p * CPS < EPL);
+          if (pf) pcr_src_load<CPS>(v, P, p * CPS, n, lane);
+          if (p < TP) {
+            const int s = 1 << p;
+            const int t = s / EPL;
+            pk_t DN[NH];
+#pragma unroll
+            for (int h = 0; h < GH; ++h) {
+              const int g = p * GH + h;
+              Tm24& cur = T[g & 1];
+              tm_wait(cur);
+              const int p1 = (h + 1 < GH) ? p : p + 1, h1 = (h + 1 < GH) ? h + 1 : 0;
+              if (p1 < TP && p1 < stages) tm_issue<EPL>(T[(g + 1) & 1], tl, p1, h1);
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj) {
+                const int j = 4 * h + jj;
+                pk_t dl, dr;
+                if (s == 1) {
+                  const float l0 = (j >= 1) ? hi2(D[j - 1]) : __shfl_up_sync(0xffffffffu, hi2(D[NH - 1]), 1);
+                  const float r1 = (j + 1 < NH) ? lo2(D[j + 1]) : __shfl_down_sync(0xffffffffu, lo2(D[0]), 1);
+                  dl = pk2(l0, lo2(D[j]));
+                  dr = pk2(hi2(D[j]), r1);
+                } else if (s < EPL) {
+                  const int hs = s / 2;
+                  if (j >= hs) dl = D[j - hs];
+                  else dl = __shfl_up_sync(0xffffffffu, D[(j - hs + NH) & (NH - 1)], 1);
+                  if (j + hs < NH) dr = D[j + hs];
+                  else dr = __shfl_down_sync(0xffffffffu, D[(j + hs - NH) & (NH - 1)], 1);
+                } else {
+                  dl = __shfl_up_sync(0xffffffffu, D[j], t);
+                  dr = __shfl_down_sync(0xffffffffu, D[j], t);
+                }
+                const pk_t ap = pku(cur.a[2 * jj], cur.a[2 * jj + 1]), cp = pku(cur.c[2 * jj], cur.c[2 * jj + 1]);
+                const pk_t ee = pku(cur.e[2 * jj], cur.e[2 * jj + 1]);
+                DN[j] = mul2(ee, sub2(sub2(D[j], fma2(ap, dl, nz)), fma2(cp, dr, nz)));
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < NH; ++j) D[j] = DN[j];
+          } else {
+            pcr_stage_pk<EPL>(D, p, ts_s, lane, nz);
+          }
+          if (pf) pcr_src_put<EPL, CPS>(v, wn + posl, p * CPS, n, lane, r);
+        }
+      }
+      // own-line values for the relaxation, in flight during the 2x2 stage
+      const REAL* px = x + base + lane;
+      REAL* pd = dst + base + lane;
+      REAL pp[EPL];
+#pragma unroll
+      for (int c = 0; c < EPL; ++c) pp[c] = (lane < n - 32 * c) ? px[32 * c] : zero;
+      // ---- last 2x2 stage (cz_solver.f90:612-630) ----
+      if (FTM) {
+        const uint32_t fcol = tl + (uint32_t)(3 * stages * EPL);
+#pragma unroll
+        for (int h = 0; h < GH; ++h) {
+          Tm24 F;
+          tm_ld8(F.a, fcol + 8 * h); tm_ld8(F.c, fcol + EPL + 8 * h);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) F.e[e] = 0u;
+          tm_wait(F);
+#pragma unroll
+          for (int jj = 0; jj < 4; jj += 2) {
+            ulonglong2 o;
+            pk_t prt[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const pk_t v = __shfl_xor_sync(0xffffffffu, D[4 * h + jj + u], t2 & 31);
+              prt[u] = (t2 < 32) ? v : 0ull;
+            }
+            o.x = mul2(sub2(D[4 * h + jj], fma2(pku(F.a[2 * jj], F.a[2 * jj + 1]), prt[0], nz)), pku(F.c[2 * jj], F.c[2 * jj + 1]));
+            o.y = mul2(sub2(D[4 * h + jj + 1], fma2(pku(F.a[2 * jj + 2], F.a[2 * jj + 3]), prt[1], nz)), pku(F.c[2 * jj + 2], F.c[2 * jj + 3]));
+            *reinterpret_cast<ulonglong2*>(wc + (2 * h + jj / 2) * LY::QSTR + lane * 4) = o;
+          }
+        }
+      } else {
+        const REAL* F1 = ts_s + (size_t)(3 * stages) * ROW;
+        const REAL* F2 = F1 + ROW;
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+          const ulonglong2 f1 = *reinterpret_cast<const ulonglong2*>(F1 + q * LY::QSTR + lane * 4);
+          const ulonglong2 f2 = *reinterpret_cast<const ulonglong2*>(F2 + q * LY::QSTR + lane * 4);
+          pk_t prt[2];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const pk_t v = __shfl_xor_sync(0xffffffffu, D[2 * q + h], t2 & 31);
+            prt[h] = (t2 < 32) ? v : 0ull;
+          }
+          ulonglong2 o;
+          o.x = mul2(sub2(D[2 * q], fma2(f1.x, prt[0], nz)), f2.x);
+          o.y = mul2(sub2(D[2 * q + 1], fma2(f1.y, prt[1], nz)), f2.y);
+          *reinterpret_cast<ulonglong2*>(wc + q * LY::QSTR + lane * 4) = o;
+        }
+      }
+      __syncwarp();
+      // ---- relaxation in the cyclic layout (cz_solver.f90:642-648), msk == 1; cells k >= n hold 0 - 0 ----
+#pragma unroll
+      for (int c = 0; c < EPL; ++c) {
+        const REAL dp = (wc[posl + (128 / EPL) * c] - pp[c]) * omg;
+        if (lane < n - 32 * c) pd[32 * c] = pp[c] + dp;
+        acc[0] += (double)(dp * dp);
+      }
+    } else if (nbase >= 0) {
+      full_load(nbase, wn);
+    }
+    line = nline; base = nbase; buf ^= 1;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tm_base_s), "r"(512u) : "memory");
+  }
+  grid_reduce<1>(acc, rb, finst);
+}
 #endif  // !_REAL_IS_DOUBLE_
 
 }  // namespace
@@ -687,7 +951,30 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_pf<EPL, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
       k_pcr_warp_pf<EPL, WPB><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
     };
+    auto go_tm = [&](auto epl, auto wpb_) {   // prefetching variant with the tables in tensor memory
+      constexpr int EPL = decltype(epl)::value, WPB = decltype(wpb_)::value;
+      typedef PcrLay<EPL> LY;
+      const int rows = 3 * T.stages + 2;
+      const int rows_tm = EPL != 32 ? rows : (T.stages < 5 ? 3 * T.stages : 15);
+      const size_t sm = sizeof(REAL) * ((size_t)(rows - rows_tm) * LY::ROW + (size_t)WPB * 2 * LY::ROW);
+      int g = (sel.nlines + WPB - 1) / WPB;
+      if (g > 148) g = 148;
+      if ((size_t)g > L.rb_blocks) g = (int)L.rb_blocks;
+      static size_t sm_set = 0;
+      if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_tm<EPL, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
+      k_pcr_warp_tm<EPL, WPB><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
+    };
     static const bool no_pf = getenv("CZB_PCR_NOPF") != nullptr;
+    static const bool no_tm = getenv("CZB_PCR_NOTMEM") != nullptr;
+    if (mask_is_inner && !no_pf && !no_tm && n > 128 && (n <= 256 ? 2 : n <= 512 ? 2 : 4) * T.stages >= (n <= 256 ? 8 : n <= 512 ? 16 : 32)
+        && 3 * T.stages + 2 <= (n <= 256 ? 64 : n <= 512 ? 32 : 29)) {
+      if (n <= 256)      go_tm(std::integral_constant<int, 8>{}, std::integral_constant<int, 16>{});
+      else if (n <= 512) go_tm(std::integral_constant<int, 16>{}, std::integral_constant<int, 16>{});
+      else               go_tm(std::integral_constant<int, 32>{}, std::integral_constant<int, 12>{});
+      CZB_CHECK(cudaGetLastError());
+      count_launch();
+      return;
+    }
     const int cps = n <= 128 ? 1 : n <= 512 ? 2 : 4, epl = n <= 128 ? 4 : n <= 256 ? 8 : n <= 512 ? 16 : 32;
     if (mask_is_inner && !no_pf && T.stages * cps >= epl) {
       if (n <= 128)      go_pf(std::integral_constant<int, 4>{}, std::integral_constant<int, 8>{});
