@@ -655,7 +655,7 @@ __device__ __forceinline__ void tm_wait(Tm24& t) {
 }
 __device__ __forceinline__ pk_t pku(uint32_t lo, uint32_t hi) { pk_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi)); return r; }
 
-template <int EPL, int WPB>
+template <int EPL, int WPB, bool BULK>
 __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int pn, int stages, const REAL* __restrict__ tab,
                                                   const REAL* __restrict__ fin, LineSel sel, const REAL* x, REAL* dst,
                                                   const REAL* __restrict__ rhs, REAL omg, pk_t nz,
@@ -667,9 +667,10 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
   constexpr int MAXST = 5 + (EPL == 8 ? 3 : EPL == 16 ? 4 : 5);
   constexpr int TP = EPL == 32 ? 5 : MAXST;              // stages whose tables live in tensor memory
   constexpr bool FTM = EPL != 32;                        // 2x2 rows in tensor memory
-  static_assert(EPL >= 8 && WPB >= 4, "tensor-memory variant: EPL 8, 16, 32");
+  static_assert(EPL >= 8 && WPB % 4 == 0, "tensor-memory variant: EPL 8, 16, 32");
   extern __shared__ double sm_raw[];
   __shared__ uint32_t tm_base_s;
+  __shared__ unsigned long long mbar_s[WPB];
   REAL* sm = reinterpret_cast<REAL*>(sm_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const REAL zero = (REAL)0.0;
@@ -678,7 +679,15 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
   const int rows_tm = FTM ? rows : (stages < TP ? 3 * stages : 3 * TP);
   const int rows_sm = rows - rows_tm;                    // shared-memory rows: rows_tm .. rows-1
   REAL* ts_s = sm - (size_t)rows_tm * ROW;               // so that row R sits at ts_s + R*ROW
-  REAL* wb0 = sm + (size_t)rows_sm * ROW + (size_t)warp * 2 * ROW;
+  // per warp: BULK: five raw neighbour / source rows (TMA bulk copies) + one exchange buffer; else two exchange buffers
+  const int rawf = BULK ? 5 * G.nk : ROW;
+  REAL* wb0 = sm + (size_t)rows_sm * ROW + (size_t)warp * (rawf + ROW) + (BULK ? rawf : 0);
+  REAL* raw = wb0 - rawf;
+  const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_s[warp]);
+  if (BULK && lane == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(mbar) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   auto table = [&](int R, int k) -> REAL {               // entry of row R for cell k (0 beyond the line)
     if (k >= n) return zero;
     if (R < 3 * stages) return tab[(size_t)R * n + k];
@@ -699,16 +708,16 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tl = tm_base_s + ((uint32_t)((warp & 3) * 32) << 16);   // this warp's lane quarter
-  if (warp < 4) {
-    for (int R = 0; R < rows_tm; ++R) {
+  {   // every warp writes part of the rows of its own lane quarter
+#pragma unroll 2
+    for (int R = warp >> 2; R < rows_tm; R += WPB / 4) {
+      uint32_t v[EPL];
 #pragma unroll
-      for (int m0 = 0; m0 < EPL; m0 += 4) {
-        uint32_t v[4];
+      for (int m = 0; m < EPL; ++m) v[m] = __float_as_uint(table(R, EPL * lane + m));
 #pragma unroll
-        for (int e = 0; e < 4; ++e) v[e] = __float_as_uint(table(R, EPL * lane + m0 + e));
+      for (int m0 = 0; m0 < EPL; m0 += 4)
         asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
-                     :: "r"(tl + (uint32_t)(R * EPL + m0)), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
-      }
+                     :: "r"(tl + (uint32_t)(R * EPL + m0)), "r"(v[m0]), "r"(v[m0 + 1]), "r"(v[m0 + 2]), "r"(v[m0 + 3]) : "memory");
     }
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
   }
@@ -750,6 +759,171 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
     }
   };
   const int lstride = gridDim.x * WPB;
+  if constexpr (BULK) {
+    // ---- rows of the next line arrive by TMA bulk copies while the current line is reduced ----
+    const int koff = G.kst + G.g - 1;                     // first line cell inside a row of nk
+    const uint32_t rowb = (uint32_t)G.nk * (uint32_t)sizeof(REAL);
+    const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(raw);
+    auto next_valid = [&](int l, long long& b) -> int {   // first existing line >= l (stride lstride), or nlines
+      while (l < sel.nlines) { b = line_base(l); if (b >= 0) return l; l += lstride; }
+      b = -1; return sel.nlines;
+    };
+    REAL elo = zero, ehi = zero;                          // Dirichlet-side neighbours x(kst-1), x(ked+1) of the staged line
+    auto issue = [&](long long b) {
+      if (lane == 0) {
+        const REAL* px = x + b - koff;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mbar), "r"(5u * rowb) : "memory");
+        const REAL* src[5] = {px - G.plane, px + G.plane, px - G.nk, px + G.nk, rhs + b - koff};
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       :: "r"(raw_s + (uint32_t)q * rowb), "l"(src[q]), "r"(rowb), "r"(mbar) : "memory");
+      }
+      if (lane == 0) elo = x[b - 1];
+      if (lane == ((n - 1) & 31)) ehi = x[b + n];
+    };
+    __syncwarp();
+    long long base;
+    int line = next_valid(blockIdx.x * WPB + warp, base);
+    if (line < sel.nlines) issue(base);
+    uint32_t ph = 0;
+    while (line < sel.nlines) {
+      long long nbase;
+      const int nline = next_valid(line + lstride, nbase);
+      REAL* wc = wb0;
+      // ---- source term (cz_solver.f90:569-579) from the staged rows -> exchange buffer ----
+      {
+        uint32_t ok = 0;
+        while (!ok) asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                                 : "=r"(ok) : "r"(mbar), "r"(ph) : "memory");
+        ph ^= 1u;
+        const REAL* rk = raw + koff + lane;
+#pragma unroll
+        for (int c = 0; c < EPL; ++c) {
+          const bool in = lane < n - 32 * c;
+          REAL d = zero;
+          if (in) d = (rk[32 * c] + rk[G.nk + 32 * c] + rk[2 * G.nk + 32 * c] + rk[3 * G.nk + 32 * c] - rk[4 * G.nk + 32 * c]) * r;
+          if (c == 0 && lane == 0) d = d + elo * r;
+          if (lane == n - 1 - 32 * c) d = d + ehi * r;
+          wc[posl + (128 / EPL) * c] = d;
+        }
+      }
+      __syncwarp();
+      if (nline < sel.nlines) issue(nbase);
+      pk_t D[NH];
+      Tm24 T[2];
+      tm_issue<EPL>(T[0], tl, 0, 0);
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(wc + q * LY::QSTR + lane * 4);
+        D[2 * q] = v.x; D[2 * q + 1] = v.y;
+      }
+#pragma unroll
+      for (int p = 0; p < MAXST; ++p) {
+        if (p < stages) {
+          if (p < TP) {
+            const int s = 1 << p;
+            const int t = s / EPL;
+            pk_t DN[NH];
+#pragma unroll
+            for (int h = 0; h < GH; ++h) {
+              const int g = p * GH + h;
+              Tm24& cur = T[g & 1];
+              tm_wait(cur);
+              const int p1 = (h + 1 < GH) ? p : p + 1, h1 = (h + 1 < GH) ? h + 1 : 0;
+              if (p1 < TP && p1 < stages) tm_issue<EPL>(T[(g + 1) & 1], tl, p1, h1);
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj) {
+                const int j = 4 * h + jj;
+                pk_t dl, dr;
+                if (s == 1) {
+                  const float l0 = (j >= 1) ? hi2(D[j - 1]) : __shfl_up_sync(0xffffffffu, hi2(D[NH - 1]), 1);
+                  const float r1 = (j + 1 < NH) ? lo2(D[j + 1]) : __shfl_down_sync(0xffffffffu, lo2(D[0]), 1);
+                  dl = pk2(l0, lo2(D[j]));
+                  dr = pk2(hi2(D[j]), r1);
+                } else if (s < EPL) {
+                  const int hs = s / 2;
+                  if (j >= hs) dl = D[j - hs];
+                  else dl = __shfl_up_sync(0xffffffffu, D[(j - hs + NH) & (NH - 1)], 1);
+                  if (j + hs < NH) dr = D[j + hs];
+                  else dr = __shfl_down_sync(0xffffffffu, D[(j + hs - NH) & (NH - 1)], 1);
+                } else {
+                  dl = __shfl_up_sync(0xffffffffu, D[j], t);
+                  dr = __shfl_down_sync(0xffffffffu, D[j], t);
+                }
+                const pk_t ap = pku(cur.a[2 * jj], cur.a[2 * jj + 1]), cp = pku(cur.c[2 * jj], cur.c[2 * jj + 1]);
+                const pk_t ee = pku(cur.e[2 * jj], cur.e[2 * jj + 1]);
+                DN[j] = mul2(ee, sub2(sub2(D[j], fma2(ap, dl, nz)), fma2(cp, dr, nz)));
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < NH; ++j) D[j] = DN[j];
+          } else {
+            pcr_stage_pk<EPL>(D, p, ts_s, lane, nz);
+          }
+        }
+      }
+      // own-line values for the relaxation, in flight during the 2x2 stage
+      const REAL* px = x + base + lane;
+      REAL* pd = dst + base + lane;
+      REAL pp[EPL];
+#pragma unroll
+      for (int c = 0; c < EPL; ++c) pp[c] = (lane < n - 32 * c) ? px[32 * c] : zero;
+      // ---- last 2x2 stage (cz_solver.f90:612-630) ----
+      if (FTM) {
+        const uint32_t fcol = tl + (uint32_t)(3 * stages * EPL);
+#pragma unroll
+        for (int h = 0; h < GH; ++h) {
+          Tm24 F;
+          tm_ld8(F.a, fcol + 8 * h); tm_ld8(F.c, fcol + EPL + 8 * h);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) F.e[e] = 0u;
+          tm_wait(F);
+#pragma unroll
+          for (int jj = 0; jj < 4; jj += 2) {
+            ulonglong2 o;
+            pk_t prt[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const pk_t v = __shfl_xor_sync(0xffffffffu, D[4 * h + jj + u], t2 & 31);
+              prt[u] = (t2 < 32) ? v : 0ull;
+            }
+            o.x = mul2(sub2(D[4 * h + jj], fma2(pku(F.a[2 * jj], F.a[2 * jj + 1]), prt[0], nz)), pku(F.c[2 * jj], F.c[2 * jj + 1]));
+            o.y = mul2(sub2(D[4 * h + jj + 1], fma2(pku(F.a[2 * jj + 2], F.a[2 * jj + 3]), prt[1], nz)), pku(F.c[2 * jj + 2], F.c[2 * jj + 3]));
+            *reinterpret_cast<ulonglong2*>(wc + (2 * h + jj / 2) * LY::QSTR + lane * 4) = o;
+          }
+        }
+      } else {
+        const REAL* F1 = ts_s + (size_t)(3 * stages) * ROW;
+        const REAL* F2 = F1 + ROW;
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+          const ulonglong2 f1 = *reinterpret_cast<const ulonglong2*>(F1 + q * LY::QSTR + lane * 4);
+          const ulonglong2 f2 = *reinterpret_cast<const ulonglong2*>(F2 + q * LY::QSTR + lane * 4);
+          pk_t prt[2];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const pk_t v = __shfl_xor_sync(0xffffffffu, D[2 * q + h], t2 & 31);
+            prt[h] = (t2 < 32) ? v : 0ull;
+          }
+          ulonglong2 o;
+          o.x = mul2(sub2(D[2 * q], fma2(f1.x, prt[0], nz)), f2.x);
+          o.y = mul2(sub2(D[2 * q + 1], fma2(f1.y, prt[1], nz)), f2.y);
+          *reinterpret_cast<ulonglong2*>(wc + q * LY::QSTR + lane * 4) = o;
+        }
+      }
+      __syncwarp();
+      // ---- relaxation in the cyclic layout (cz_solver.f90:642-648), msk == 1; cells k >= n hold 0 - 0 ----
+#pragma unroll
+      for (int c = 0; c < EPL; ++c) {
+        const REAL dp = (wc[posl + (128 / EPL) * c] - pp[c]) * omg;
+        if (lane < n - 32 * c) pd[32 * c] = pp[c] + dp;
+        acc[0] += (double)(dp * dp);
+      }
+      __syncwarp();
+      line = nline; base = nbase;
+    }
+  } else {
   int line = blockIdx.x * WPB + warp;
   long long base = line_base(line);
   int buf = 0;
@@ -881,6 +1055,7 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
     }
     line = nline; base = nbase; buf ^= 1;
   }
+  }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 0) {
@@ -951,26 +1126,34 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_pf<EPL, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
       k_pcr_warp_pf<EPL, WPB><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
     };
-    auto go_tm = [&](auto epl, auto wpb_) {   // prefetching variant with the tables in tensor memory
+    auto go_tm = [&](auto epl, auto wpb_, auto bulk_) {   // prefetching variants with the tables in tensor memory
       constexpr int EPL = decltype(epl)::value, WPB = decltype(wpb_)::value;
+      constexpr bool BULK = decltype(bulk_)::value;
       typedef PcrLay<EPL> LY;
       const int rows = 3 * T.stages + 2;
       const int rows_tm = EPL != 32 ? rows : (T.stages < 5 ? 3 * T.stages : 15);
-      const size_t sm = sizeof(REAL) * ((size_t)(rows - rows_tm) * LY::ROW + (size_t)WPB * 2 * LY::ROW);
+      const size_t per_warp = BULK ? (size_t)5 * G.nk + LY::ROW : (size_t)2 * LY::ROW;
+      const size_t sm = sizeof(REAL) * ((size_t)(rows - rows_tm) * LY::ROW + (size_t)WPB * per_warp);
       int g = (sel.nlines + WPB - 1) / WPB;
       if (g > 148) g = 148;
       if ((size_t)g > L.rb_blocks) g = (int)L.rb_blocks;
       static size_t sm_set = 0;
-      if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_tm<EPL, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
-      k_pcr_warp_tm<EPL, WPB><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
+      if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_tm<EPL, WPB, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
+      k_pcr_warp_tm<EPL, WPB, BULK><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
     };
     static const bool no_pf = getenv("CZB_PCR_NOPF") != nullptr;
     static const bool no_tm = getenv("CZB_PCR_NOTMEM") != nullptr;
     if (mask_is_inner && !no_pf && !no_tm && n > 128 && (n <= 256 ? 2 : n <= 512 ? 2 : 4) * T.stages >= (n <= 256 ? 8 : n <= 512 ? 16 : 32)
         && 3 * T.stages + 2 <= (n <= 256 ? 64 : n <= 512 ? 32 : 29)) {
-      if (n <= 256)      go_tm(std::integral_constant<int, 8>{}, std::integral_constant<int, 16>{});
-      else if (n <= 512) go_tm(std::integral_constant<int, 16>{}, std::integral_constant<int, 16>{});
-      else               go_tm(std::integral_constant<int, 32>{}, std::integral_constant<int, 12>{});
+      // rows staged by TMA bulk copies: row pitch and base addresses 16-byte aligned, 5 rows + exchange buffer per warp
+      static const bool no_bulk = getenv("CZB_PCR_NOBULK") != nullptr;
+      const bool bulk = !no_bulk && n <= 512 && G.nk % 4 == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)rhs % 16) == 0;
+      using std::integral_constant;
+      if (n <= 256)      { if (bulk) go_tm(integral_constant<int, 8>{}, integral_constant<int, 16>{}, std::true_type{});
+                           else      go_tm(integral_constant<int, 8>{}, integral_constant<int, 16>{}, std::false_type{}); }
+      else if (n <= 512) { if (bulk) go_tm(integral_constant<int, 16>{}, integral_constant<int, 16>{}, std::true_type{});
+                           else      go_tm(integral_constant<int, 16>{}, integral_constant<int, 16>{}, std::false_type{}); }
+      else               go_tm(integral_constant<int, 32>{}, integral_constant<int, 12>{}, std::false_type{});
       CZB_CHECK(cudaGetLastError());
       count_launch();
       return;
