@@ -707,7 +707,8 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tl = tm_base_s + ((uint32_t)((warp & 3) * 32) << 16);   // this warp's lane quarter
+  // this warp's lane quarter (the shuffle tells the compiler that the address is warp-uniform)
+  const uint32_t tl = __shfl_sync(0xffffffffu, tm_base_s + ((uint32_t)((warp & 3) * 32) << 16), 0);
   {   // every warp writes part of the rows of its own lane quarter
 #pragma unroll 2
     for (int R = warp >> 2; R < rows_tm; R += WPB / 4) {
@@ -813,6 +814,9 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
       pk_t D[NH];
       Tm24 T[2];
       tm_issue<EPL>(T[0], tl, 0, 0);
+      const REAL* px = x + base + lane;
+      REAL* pd = dst + base + lane;
+      REAL pp[EPL];
 #pragma unroll
       for (int q = 0; q < NQ; ++q) {
         const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(wc + q * LY::QSTR + lane * 4);
@@ -821,6 +825,10 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
 #pragma unroll
       for (int p = 0; p < MAXST; ++p) {
         if (p < stages) {
+          if (p == stages - 1) {   // own-line values for the relaxation: in flight during the last stage and the 2x2 stage
+#pragma unroll
+            for (int c = 0; c < EPL; ++c) pp[c] = (lane < n - 32 * c) ? px[32 * c] : zero;
+          }
           if (p < TP) {
             const int s = 1 << p;
             const int t = s / EPL;
@@ -863,33 +871,22 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
           }
         }
       }
-      // own-line values for the relaxation, in flight during the 2x2 stage
-      const REAL* px = x + base + lane;
-      REAL* pd = dst + base + lane;
-      REAL pp[EPL];
-#pragma unroll
-      for (int c = 0; c < EPL; ++c) pp[c] = (lane < n - 32 * c) ? px[32 * c] : zero;
       // ---- last 2x2 stage (cz_solver.f90:612-630) ----
       if (FTM) {
         const uint32_t fcol = tl + (uint32_t)(3 * stages * EPL);
+        tm_ld8(T[0].a, fcol); tm_ld8(T[0].c, fcol + EPL);
 #pragma unroll
         for (int h = 0; h < GH; ++h) {
-          Tm24 F;
-          tm_ld8(F.a, fcol + 8 * h); tm_ld8(F.c, fcol + EPL + 8 * h);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) F.e[e] = 0u;
+          Tm24& F = T[h & 1];
           tm_wait(F);
+          if (h + 1 < GH) { tm_ld8(T[(h + 1) & 1].a, fcol + 8 * (h + 1)); tm_ld8(T[(h + 1) & 1].c, fcol + EPL + 8 * (h + 1)); }
 #pragma unroll
           for (int jj = 0; jj < 4; jj += 2) {
             ulonglong2 o;
-            pk_t prt[2];
-#pragma unroll
-            for (int u = 0; u < 2; ++u) {
-              const pk_t v = __shfl_xor_sync(0xffffffffu, D[4 * h + jj + u], t2 & 31);
-              prt[u] = (t2 < 32) ? v : 0ull;
-            }
-            o.x = mul2(sub2(D[4 * h + jj], fma2(pku(F.a[2 * jj], F.a[2 * jj + 1]), prt[0], nz)), pku(F.c[2 * jj], F.c[2 * jj + 1]));
-            o.y = mul2(sub2(D[4 * h + jj + 1], fma2(pku(F.a[2 * jj + 2], F.a[2 * jj + 3]), prt[1], nz)), pku(F.c[2 * jj + 2], F.c[2 * jj + 3]));
+            const pk_t pr0 = __shfl_xor_sync(0xffffffffu, D[4 * h + jj], 16);       // partner k -+ s2: lane distance s2/EPL = 16
+            const pk_t pr1 = __shfl_xor_sync(0xffffffffu, D[4 * h + jj + 1], 16);
+            o.x = mul2(sub2(D[4 * h + jj], fma2(pku(F.a[2 * jj], F.a[2 * jj + 1]), pr0, nz)), pku(F.c[2 * jj], F.c[2 * jj + 1]));
+            o.y = mul2(sub2(D[4 * h + jj + 1], fma2(pku(F.a[2 * jj + 2], F.a[2 * jj + 3]), pr1, nz)), pku(F.c[2 * jj + 2], F.c[2 * jj + 3]));
             *reinterpret_cast<ulonglong2*>(wc + (2 * h + jj / 2) * LY::QSTR + lane * 4) = o;
           }
         }
@@ -1143,7 +1140,7 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
     };
     static const bool no_pf = getenv("CZB_PCR_NOPF") != nullptr;
     static const bool no_tm = getenv("CZB_PCR_NOTMEM") != nullptr;
-    if (mask_is_inner && !no_pf && !no_tm && n > 128 && (n <= 256 ? 2 : n <= 512 ? 2 : 4) * T.stages >= (n <= 256 ? 8 : n <= 512 ? 16 : 32)
+    if (mask_is_inner && !no_pf && !no_tm && n > 128 && (1 << T.pn) == 32 * (n <= 256 ? 8 : n <= 512 ? 16 : 32) && (n <= 256 ? 2 : n <= 512 ? 2 : 4) * T.stages >= (n <= 256 ? 8 : n <= 512 ? 16 : 32)
         && 3 * T.stages + 2 <= (n <= 256 ? 64 : n <= 512 ? 32 : 29)) {
       // rows staged by TMA bulk copies: row pitch and base addresses 16-byte aligned, 5 rows + exchange buffer per warp
       static const bool no_bulk = getenv("CZB_PCR_NOBULK") != nullptr;
