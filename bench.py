@@ -191,7 +191,8 @@ def run_gpu(args, rank, world, local_rank):
     # headline region; reported under "also", not part of value/e2e) -------------------------------
     also = {}
     if not args.no_also:
-        for name, pre, omg, bpc, k in (("pbicgstab", "sor2sma", OMEGA, 340.0, 6), ("jacobi", None, 0.8, 12.0, 10)):
+        for name, pre, omg, bpc, k in (("pbicgstab", "sor2sma", OMEGA, 340.0, 6), ("jacobi", None, 0.8, 12.0, 10),
+                                       ("pcr_rb", None, OMEGA, 20.0, 8)):
             P2, R2 = cz.setup_laplace()
             P2[2:-2, 2:-2, 2:-2] = torch.rand(P2[2:-2, 2:-2, 2:-2].shape, generator=gen, device="cuda") * 2 - 1
             cz.bc_k(P2)
@@ -268,7 +269,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cubez_b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-also", action="store_true", help="skip the PBiCGstab / Jacobi side measurements")
+    ap.add_argument("--no-also", action="store_true", help="skip the PBiCGstab / Jacobi / line-SOR side measurements")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

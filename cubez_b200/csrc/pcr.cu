@@ -1156,7 +1156,11 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       return;
     }
     const int cps = n <= 128 ? 1 : n <= 512 ? 2 : 4, epl = n <= 128 ? 4 : n <= 256 ? 8 : n <= 512 ? 16 : 32;
-    if (mask_is_inner && !no_pf && T.stages * cps >= epl) {
+    // the prefetching kernel needs its tables + two exchange buffers per warp in shared memory (n = 1024 = 2^10
+    // has one stage more than 513..1023 and does not fit: k_pcr_warp below)
+    const size_t row_b = sizeof(REAL) * (size_t)(epl / 4) * (32 * 4 + 8);
+    const size_t sm_pf = ((size_t)T.stages * 3 + 2 + 2 * (size_t)(epl == 32 ? 12 : 8)) * row_b;
+    if (mask_is_inner && !no_pf && T.stages * cps >= epl && sm_pf <= 225 * 1024) {
       if (n <= 128)      go_pf(std::integral_constant<int, 4>{}, std::integral_constant<int, 8>{});
       else if (n <= 256) go_pf(std::integral_constant<int, 8>{}, std::integral_constant<int, 8>{});
       else if (n <= 512) go_pf(std::integral_constant<int, 16>{}, std::integral_constant<int, 8>{});
@@ -1174,8 +1178,8 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       const int cap = 148 * (int)(sm > 110 * 1024 ? 1 : 2);
       if (g > cap) g = cap;
       if ((size_t)g > L.rb_blocks) g = (int)L.rb_blocks;
-      static bool set = false;
-      if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp<EPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); set = true; }
+      static size_t sm_set = 0;
+      if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp<EPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
       // mask_is_inner: msk is imask_k of this geometry, i.e. exactly 1 on every cell of every line -> not read
       k_pcr_warp<EPL><<<g, wpb * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, mask_is_inner ? nullptr : msk, rhs, omg, L.st, L.rb, fs);
     };

@@ -146,3 +146,38 @@ def test_cz_driver_cli():
     np.testing.assert_allclose(hist, [float(h) for h in g["history"]], rtol=2e-6)
     p = subprocess.run([exe, "64", "64", "64", "nosuch", "10", "1.0"], capture_output=True, text=True)
     assert "Invalid solver" in p.stdout
+
+
+# Line SOR on LONG lines: the solve loops use the warp-per-line kernels with the coefficient tables in
+# tensor memory (lines of 129..1024 cells) and, where the row pitch allows it, TMA bulk staging of the
+# neighbour rows; the golden cases above only reach lines of <= 62 cells.  Non-cubic grids keep the oracle
+# fast: many lines (more than one per warp), few planes.  Fields must agree bit for bit with the oracle.
+@pytest.mark.parametrize("sz,solver,coef", [
+    ([84, 80, 132], "pcr_rb", 1.5),      # 130-cell lines: 8 cells per lane, bulk staging
+    ([84, 80, 200], "pcr_rb", 1.5),      # 198
+    ([84, 80, 258], "pcr_rb", 1.5),      # 256 = 2^8 exactly
+    ([84, 80, 300], "pcr_rb", 1.5),      # 298: 16 cells per lane, bulk staging
+    ([84, 80, 302], "pcr_rb", 1.5),      # 300: row pitch not a multiple of 16 B -> register prefetch path
+    ([84, 80, 300], "pcr_j_esa", 0.9),   # all lines in one pass, separate output array
+    ([84, 80, 300], "pcr_eda", 1.5),     # wavefront launches
+    ([44, 40, 514], "pcr_rb", 1.5),      # 512 = 2^9
+    ([44, 40, 600], "pcr_rb", 1.5),      # 598: 32 cells per lane, late stages from shared memory
+    ([44, 40, 1026], "pcr_rb", 1.5),     # 1024, the longest line of the warp kernels
+    ([24, 20, 1100], "pcr_rb", 1.5),     # 1098 > 1024: block-per-line kernel
+])
+def test_line_sor_long_lines(sz, solver, coef):
+    import cubez_b200
+    cz = cubez_b200.CZ(sz, "f32", eps=0.0)
+    o = ou.OracleCZ(sz, "f32", eps=0.0)
+    assert tuple(cz.shape) == tuple(o.shape)
+    X, B = ou.random_fields(o.shape, o.dt)
+    o.bc_k(X)
+    Xg, Bg = cz.from_numpy(X), cz.from_numpy(B)
+    iters = 3
+    out = cz.solve(solver, Xg, Bg, iters, coef)
+    itr, res, hist = o.stationary(solver, X, B, iters, coef)
+    assert out["itr"] == itr == iters + 1
+    got = Xg.cpu().numpy()
+    assert np.array_equal(got, X), "field differs from the oracle (max %g)" % np.abs(got - X).max()
+    np.testing.assert_allclose(out["history"], hist, rtol=1e-12)
+    cz.close()
