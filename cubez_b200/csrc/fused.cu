@@ -608,10 +608,15 @@ void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const R
   dim3 grid(a.ntk * a.nti, a.njc, 1);
   const size_t smem = (size_t)(NSP_ + NSB_ + NDE) * EI * EKB * sizeof(float) + 1024;
   static bool set = false;
-  if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT, NSP_, NSB_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
+  if (!set) {
+    CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT, NSP_, NSB_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT, NSP_, NSB_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    set = true;
+  }
   const CUtensorMap& tp = tmap_for(p, a.G, EI);
   const CUtensorMap& tb = tmap_for(b, a.G, EI);
-  k_rb2_pk<NT, CPT, NSP_, NSB_><<<grid, NT, smem, L.s>>>(tp, tb, a);
+  if (a.sig) k_rb2_pk<NT, CPT, NSP_, NSB_, true><<<grid, NT, smem, L.s>>>(tp, tb, a);    // j-slab with edge-plane signals
+  else       k_rb2_pk<NT, CPT, NSP_, NSB_, false><<<grid, NT, smem, L.s>>>(tp, tb, a);
   CZB_CHECK(cudaGetLastError());
   count_launch();
 }

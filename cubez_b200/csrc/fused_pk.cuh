@@ -128,7 +128,7 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t addr, uint32_t parity) {   
 // streams (the blacks trail the reds by two planes instead of one), which doubles the ILP of the
 // dependent add/divide chains.  Per step: one TMA plane of p and one of b arrive (NSP_/NSB_ slots
 // of look-ahead), one plane is stored, one __syncthreads.
-template <int NT, int CPT, int NSP_, int NSB_>
+template <int NT, int CPT, int NSP_, int NSB_, bool SIG>
 __global__ void __launch_bounds__(NT, 1)
 k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b, const MarchArgs a) {
   constexpr int RPW = NT / 32;             // tile rows covered by one pass of the CTA (one warp per row)
@@ -154,8 +154,9 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   // sig[1], the CTAs of the first chunk count in sig[0] once their first two planes are stored; the
   // communication stream waits on the two counters (stream memory operation) and sends the slab's edge
   // planes while the rest of this launch is still running.
-  const int jc = (a.sig && a.njc > 1) ? (blockIdx.y == 0 ? a.njc - 1 : (int)blockIdx.y - 1) : (int)blockIdx.y;
-  const bool sig_lo = a.sig && jc == 0, sig_hi = a.sig && jc == a.njc - 1;
+  // SIG is a template parameter: the single-GPU instantiation carries none of this.
+  const int jc = (SIG && a.njc > 1) ? (blockIdx.y == 0 ? a.njc - 1 : (int)blockIdx.y - 1) : (int)blockIdx.y;
+  const bool sig_lo = SIG && jc == 0, sig_hi = SIG && jc == a.njc - 1;
   if (a.st && a.st->done) {   // converged: nothing to do, but the counters must still advance
     if (threadIdx.x == 0) { if (sig_lo) atomicAdd(a.sig, 1u); if (sig_hi) atomicAdd(a.sig + 1, 1u); }
     return;
