@@ -396,10 +396,7 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
       hb[C & 1][m] = XB ? bc[m].a : bc[m].b;     // right-hand side of the blacks of plane s+1 (used at step u+2)
     }
     (void)YO;
-    const bool lo_now = sig_lo && u == min(4, nsteps - 1);   // planes ja, ja+1 are stored (step 4 stores ja+1)
-    if (lo_now) __threadfence();
     __syncthreads();
-    if (lo_now && tid == 0) atomicAdd(a.sig, 1u);
     if (tid == 0) {   // the two raw slots read in this step are free: refill them
       if (!zsrc && u + 2 + NSP_ < npl) issue_p(u + 2 + NSP_);
       if (u + NSB_ < nbpl) issue_b(u + NSB_);
@@ -411,8 +408,18 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   // so the 4x unrolled body exists in two variants (A-B-A-B and B-A-B-A) chosen once.
   using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
   using I2 = std::integral_constant<int, 2>; using I3 = std::integral_constant<int, 3>;
+  // first chunk of a j-slab: its planes ja, ja+1 are stored once step 4 is done (step u stores plane ja-3+u);
+  // checked between the unrolled groups of four steps, i.e. after step 7, or at the end of a shorter chunk
+  bool lo_pending = sig_lo;
+  auto signal_lo = [&]() {
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) atomicAdd(a.sig, 1u);
+    lo_pending = false;
+  };
   if (((par + (unsigned)(pl0 + 1)) & 1u) == 0u) {
     for (int u = 0; u < nsteps; u += 4) {
+      if (SIG && lo_pending && u >= 8) signal_lo();
       step(u, I0{}, std::false_type{});
       if (u + 1 >= nsteps) break;
       step(u + 1, I1{}, std::true_type{});
@@ -423,6 +430,7 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
     }
   } else {
     for (int u = 0; u < nsteps; u += 4) {
+      if (SIG && lo_pending && u >= 8) signal_lo();
       step(u, I0{}, std::true_type{});
       if (u + 1 >= nsteps) break;
       step(u + 1, I1{}, std::false_type{});
@@ -432,6 +440,7 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
       step(u + 3, I3{}, std::false_type{});
     }
   }
+  if (SIG && lo_pending) signal_lo();
   if (sig_hi) {
     __threadfence();
     __syncthreads();
