@@ -418,6 +418,7 @@ typedef unsigned long long pk_t;
 __device__ __forceinline__ pk_t pk2(float x, float y) { pk_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(x), "f"(y)); return r; }
 __device__ __forceinline__ float lo2(pk_t v) { return __uint_as_float((unsigned)v); }
 __device__ __forceinline__ float hi2(pk_t v) { return __uint_as_float((unsigned)(v >> 32)); }
+__device__ __forceinline__ pk_t add2(pk_t a, pk_t b) { pk_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ pk_t sub2(pk_t a, pk_t b) { pk_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ pk_t mul2(pk_t a, pk_t b) { pk_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ pk_t fma2(pk_t a, pk_t b, pk_t c) { pk_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
@@ -655,7 +656,7 @@ __device__ __forceinline__ void tm_wait(Tm24& t) {
 }
 __device__ __forceinline__ pk_t pku(uint32_t lo, uint32_t hi) { pk_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi)); return r; }
 
-template <int EPL, int WPB, bool BULK>
+template <int EPL, int WPB, bool BULK, bool L4>
 __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int pn, int stages, const REAL* __restrict__ tab,
                                                   const REAL* __restrict__ fin, LineSel sel, const REAL* x, REAL* dst,
                                                   const REAL* __restrict__ rhs, REAL omg, pk_t nz,
@@ -668,6 +669,7 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
   constexpr int TP = EPL == 32 ? 5 : MAXST;              // stages whose tables live in tensor memory
   constexpr bool FTM = EPL != 32;                        // 2x2 rows in tensor memory
   static_assert(EPL >= 8 && WPB % 4 == 0, "tensor-memory variant: EPL 8, 16, 32");
+  static_assert(!L4 || (BULK && EPL != 32), "4x4 last stage: lines of <= 512 cells with bulk staging");
   extern __shared__ double sm_raw[];
   __shared__ uint32_t tm_base_s;
   __shared__ unsigned long long mbar_s[WPB];
@@ -675,7 +677,9 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const REAL zero = (REAL)0.0;
   const int s2 = 1 << (pn - 1);
-  const int rows = 3 * stages + 2;
+  // L4 (pcr_rb_esa & co, cz_solver.f90:1391-1438): pn-2 stages, then 4x4 systems by Cramer's rule; their 7
+  // coefficient rows (cc1 cc2 cc3 aa2 aa3 aa4 1/det) occupy 32 TMEM columns after the stage tables
+  const int rows = L4 ? 3 * stages : 3 * stages + 2;
   const int rows_tm = FTM ? rows : (stages < TP ? 3 * stages : 3 * TP);
   const int rows_sm = rows - rows_tm;                    // shared-memory rows: rows_tm .. rows-1
   REAL* ts_s = sm - (size_t)rows_tm * ROW;               // so that row R sits at ts_s + R*ROW
@@ -719,6 +723,20 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
       for (int m0 = 0; m0 < EPL; m0 += 4)
         asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
                      :: "r"(tl + (uint32_t)(R * EPL + m0)), "r"(v[m0]), "r"(v[m0 + 1]), "r"(v[m0 + 2]), "r"(v[m0 + 3]) : "memory");
+    }
+    if (L4 && warp < 4) {
+      // lane (L = lane & 7, g = lane >> 3) solves the systems k = EPL*L + SPL*g + jj, jj < SPL = EPL/4 (k < s = 8*EPL):
+      // column SPL*r + jj of the block holds fin[r][k]
+      const int s4 = 1 << (pn - 2);
+      constexpr int SPL = EPL / 4;
+      const int k0 = EPL * (lane & 7) + SPL * (lane >> 3);
+      uint32_t v[32];
+#pragma unroll
+      for (int c = 0; c < 32; ++c) v[c] = (c < 7 * SPL) ? __float_as_uint(fin[(size_t)(c / SPL) * s4 + k0 + (c % SPL)]) : 0u;
+#pragma unroll
+      for (int c = 0; c < 8 * SPL; c += 4)
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
+                     :: "r"(tl + (uint32_t)(3 * stages * EPL + c)), "r"(v[c]), "r"(v[c + 1]), "r"(v[c + 2]), "r"(v[c + 3]) : "memory");
     }
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
   }
@@ -872,6 +890,67 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
         }
       }
       // ---- last 2x2 stage (cz_solver.f90:612-630) ----
+      if constexpr (L4) {
+        // ---- 4x4 systems {k, k+s, k+2s, k+3s}, s = 8*EPL: their members sit in lanes L, L+8, L+16, L+24 at the
+        // same register.  Through the exchange buffer every lane takes SPL = EPL/4 complete systems (the cells
+        // SPL*g .. SPL*g+SPL-1 of the lanes L+8j; L = lane & 7, g = lane >> 3), solves them as packed pairs with
+        // the reference's expression order and writes the results back in place. ----
+        constexpr int SPL = EPL / 4, NPR = SPL / 2;
+        const uint32_t fcol = tl + (uint32_t)(3 * stages * EPL);
+        tm_ld8(T[0].a, fcol); tm_ld8(T[0].c, fcol + 8);
+        if (SPL == 4) { tm_ld8(T[0].e, fcol + 16); tm_ld8(T[1].a, fcol + 24); }
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+          ulonglong2 o; o.x = D[2 * q]; o.y = D[2 * q + 1];
+          *reinterpret_cast<ulonglong2*>(wc + q * LY::QSTR + lane * 4) = o;
+        }
+        __syncwarp();
+        const int m0 = SPL * (lane >> 3);
+        REAL* sys = wc + (m0 >> 2) * LY::QSTR + (lane & 7) * 4 + (m0 & 3);   // member j at + 32*j floats
+        pk_t dd[4][NPR];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int h = 0; h < NPR; ++h) dd[j][h] = *reinterpret_cast<const pk_t*>(sys + 32 * j + 2 * h);
+        if (SPL != 4) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) T[0].e[e] = 0u;
+        }
+        tm_wait(T[0]);
+        if (SPL == 4) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { T[1].c[e] = 0u; T[1].e[e] = 0u; }
+          tm_wait(T[1]);
+        }
+        auto F = [&](int c) -> uint32_t {   // column c of the coefficient block (c is a constant after unrolling)
+          return c < 8 ? T[0].a[c & 7] : c < 16 ? T[0].c[c & 7] : c < 24 ? T[0].e[c & 7] : T[1].a[c & 7];
+        };
+        auto P = [&](pk_t u, pk_t v) -> pk_t { return fma2(u, v, nz); };   // product that may feed an add / sub
+        auto neg = [&](pk_t u) -> pk_t { return u ^ 0x8000000080000000ull; };
+#pragma unroll
+        for (int h = 0; h < NPR; ++h) {
+          const pk_t cc1 = pku(F(0 * SPL + 2 * h), F(0 * SPL + 2 * h + 1)), cc2 = pku(F(1 * SPL + 2 * h), F(1 * SPL + 2 * h + 1));
+          const pk_t cc3 = pku(F(2 * SPL + 2 * h), F(2 * SPL + 2 * h + 1)), aa2 = pku(F(3 * SPL + 2 * h), F(3 * SPL + 2 * h + 1));
+          const pk_t aa3 = pku(F(4 * SPL + 2 * h), F(4 * SPL + 2 * h + 1)), aa4 = pku(F(5 * SPL + 2 * h), F(5 * SPL + 2 * h + 1));
+          const pk_t inv = pku(F(6 * SPL + 2 * h), F(6 * SPL + 2 * h + 1));
+          const pk_t dd1 = dd[0][h], dd2 = dd[1][h], dd3 = dd[2][h], dd4 = dd[3][h];
+          // cz_solver.f90:1391-1438, evaluated left to right as k_pcr_lines<1> does
+          pk_t in1 = sub2(add2(P(aa4, dd1), P(P(cc1, cc2), dd4)), P(P(aa4, cc1), dd2));
+          pk_t d1 = add2(P(neg(cc3), in1), dd1);
+          d1 = add2(d1, P(P(cc1, cc2), dd3)); d1 = sub2(d1, P(P(aa3, cc2), dd1)); d1 = sub2(d1, P(cc1, dd2));
+          pk_t d2 = add2(dd2, P(P(cc2, cc3), dd4));
+          d2 = sub2(d2, P(P(aa4, cc3), dd2)); d2 = sub2(d2, P(cc2, dd3));
+          d2 = sub2(d2, P(aa2, sub2(dd1, P(P(aa4, cc3), dd1))));
+          pk_t d3 = sub2(dd3, P(cc3, dd4)); d3 = sub2(d3, P(aa3, dd2));
+          d3 = sub2(d3, P(aa2, sub2(sub2(P(cc1, dd3), P(P(cc1, cc3), dd4)), P(aa3, dd1))));
+          pk_t d4 = add2(dd4, P(P(aa3, aa4), dd2)); d4 = sub2(d4, P(aa4, dd3)); d4 = sub2(d4, P(P(aa3, cc2), dd4));
+          d4 = sub2(d4, P(aa2, sub2(add2(P(cc1, dd4), P(P(aa3, aa4), dd1)), P(P(aa4, cc1), dd3))));
+          *reinterpret_cast<pk_t*>(sys + 2 * h) = mul2(d1, inv);
+          *reinterpret_cast<pk_t*>(sys + 32 + 2 * h) = mul2(d2, inv);
+          *reinterpret_cast<pk_t*>(sys + 64 + 2 * h) = mul2(d3, inv);
+          *reinterpret_cast<pk_t*>(sys + 96 + 2 * h) = mul2(d4, inv);
+        }
+      } else
       if (FTM) {
         const uint32_t fcol = tl + (uint32_t)(3 * stages * EPL);
         tm_ld8(T[0].a, fcol); tm_ld8(T[0].c, fcol + EPL);
@@ -1110,7 +1189,11 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
   FinStoreP fs{L.acc_st, slot, add ? 1 : 0};
 #ifndef _REAL_IS_DOUBLE_
   static const bool no_warp = getenv("CZB_PCR_BLOCK") != nullptr;
-  if (!T.last4 && !no_warp && n >= 17 && n <= 1024) {   // warp-per-line kernel (2x2 last stage)
+  // 4x4 last stage (pcr_rb_esa & co) on the tensor-memory kernel: solve loops, lines of 129..512 cells, bulk staging
+  const bool l4_ok = T.last4 && mask_is_inner && n > 128 && n <= 512 && (1 << T.pn) == 32 * (n <= 256 ? 8 : 16) &&
+                     G.nk % 4 == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)rhs % 16) == 0 &&
+                     getenv("CZB_PCR_NOTMEM") == nullptr && getenv("CZB_PCR_NOBULK") == nullptr;
+  if ((!T.last4 || l4_ok) && !no_warp && n >= 17 && n <= 1024) {   // warp-per-line kernels
     auto go_pf = [&](auto epl, auto wpb_) {   // prefetching variant, msk not read
       constexpr int EPL = decltype(epl)::value, WPB = decltype(wpb_)::value;
       typedef PcrLay<EPL> LY;
@@ -1123,11 +1206,11 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_pf<EPL, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
       k_pcr_warp_pf<EPL, WPB><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
     };
-    auto go_tm = [&](auto epl, auto wpb_, auto bulk_) {   // prefetching variants with the tables in tensor memory
+    auto go_tm = [&](auto epl, auto wpb_, auto bulk_, auto l4_) {   // prefetching variants with the tables in tensor memory
       constexpr int EPL = decltype(epl)::value, WPB = decltype(wpb_)::value;
-      constexpr bool BULK = decltype(bulk_)::value;
+      constexpr bool BULK = decltype(bulk_)::value, L4 = decltype(l4_)::value;
       typedef PcrLay<EPL> LY;
-      const int rows = 3 * T.stages + 2;
+      const int rows = L4 ? 3 * T.stages : 3 * T.stages + 2;
       const int rows_tm = EPL != 32 ? rows : (T.stages < 5 ? 3 * T.stages : 15);
       const size_t per_warp = BULK ? (size_t)5 * G.nk + LY::ROW : (size_t)2 * LY::ROW;
       const size_t sm = sizeof(REAL) * ((size_t)(rows - rows_tm) * LY::ROW + (size_t)WPB * per_warp);
@@ -1135,9 +1218,17 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       if (g > 148) g = 148;
       if ((size_t)g > L.rb_blocks) g = (int)L.rb_blocks;
       static size_t sm_set = 0;
-      if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_tm<EPL, WPB, BULK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
-      k_pcr_warp_tm<EPL, WPB, BULK><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
+      if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_tm<EPL, WPB, BULK, L4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
+      k_pcr_warp_tm<EPL, WPB, BULK, L4><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
     };
+    if (T.last4) {
+      using std::integral_constant;
+      if (n <= 256) go_tm(integral_constant<int, 8>{}, integral_constant<int, 16>{}, std::true_type{}, std::true_type{});
+      else          go_tm(integral_constant<int, 16>{}, integral_constant<int, 16>{}, std::true_type{}, std::true_type{});
+      CZB_CHECK(cudaGetLastError());
+      count_launch();
+      return;
+    }
     static const bool no_pf = getenv("CZB_PCR_NOPF") != nullptr;
     static const bool no_tm = getenv("CZB_PCR_NOTMEM") != nullptr;
     if (mask_is_inner && !no_pf && !no_tm && n > 128 && (1 << T.pn) == 32 * (n <= 256 ? 8 : n <= 512 ? 16 : 32) && (n <= 256 ? 2 : n <= 512 ? 2 : 4) * T.stages >= (n <= 256 ? 8 : n <= 512 ? 16 : 32)
@@ -1146,11 +1237,11 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       static const bool no_bulk = getenv("CZB_PCR_NOBULK") != nullptr;
       const bool bulk = !no_bulk && n <= 512 && G.nk % 4 == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)rhs % 16) == 0;
       using std::integral_constant;
-      if (n <= 256)      { if (bulk) go_tm(integral_constant<int, 8>{}, integral_constant<int, 16>{}, std::true_type{});
-                           else      go_tm(integral_constant<int, 8>{}, integral_constant<int, 16>{}, std::false_type{}); }
-      else if (n <= 512) { if (bulk) go_tm(integral_constant<int, 16>{}, integral_constant<int, 16>{}, std::true_type{});
-                           else      go_tm(integral_constant<int, 16>{}, integral_constant<int, 16>{}, std::false_type{}); }
-      else               go_tm(integral_constant<int, 32>{}, integral_constant<int, 12>{}, std::false_type{});
+      if (n <= 256)      { if (bulk) go_tm(integral_constant<int, 8>{}, integral_constant<int, 16>{}, std::true_type{}, std::false_type{});
+                           else      go_tm(integral_constant<int, 8>{}, integral_constant<int, 16>{}, std::false_type{}, std::false_type{}); }
+      else if (n <= 512) { if (bulk) go_tm(integral_constant<int, 16>{}, integral_constant<int, 16>{}, std::true_type{}, std::false_type{});
+                           else      go_tm(integral_constant<int, 16>{}, integral_constant<int, 16>{}, std::false_type{}, std::false_type{}); }
+      else               go_tm(integral_constant<int, 32>{}, integral_constant<int, 12>{}, std::false_type{}, std::false_type{});
       CZB_CHECK(cudaGetLastError());
       count_launch();
       return;

@@ -160,6 +160,10 @@ def test_cz_driver_cli():
     ([84, 80, 302], "pcr_rb", 1.5),      # 300: row pitch not a multiple of 16 B -> register prefetch path
     ([84, 80, 300], "pcr_j_esa", 0.9),   # all lines in one pass, separate output array
     ([84, 80, 300], "pcr_eda", 1.5),     # wavefront launches
+    ([84, 80, 200], "pcr_rb_esa", 1.5),  # 4x4 Cramer last stage on the tensor-memory kernel, 8 cells per lane
+    ([84, 80, 300], "pcr_rb_esa", 1.5),  # 16 cells per lane
+    ([84, 80, 302], "pcr_rb_esa", 1.5),  # no bulk staging possible -> block-per-line kernel
+    ([44, 40, 300], "pcr_esa", 1.5),     # 4x4, wavefront launches
     ([44, 40, 514], "pcr_rb", 1.5),      # 512 = 2^9
     ([44, 40, 600], "pcr_rb", 1.5),      # 598: 32 cells per lane, late stages from shared memory
     ([44, 40, 1026], "pcr_rb", 1.5),     # 1024, the longest line of the warp kernels
