@@ -688,11 +688,18 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
   if (part != 0 && G.jed - G.jst + 1 < 2 * RB2_EDGE + 1) return 0;
   const int ni = G.ied - G.ist + 1, nj = jhi - jlo + 1;
   a.nti = lin ? (ni + a.ei - 3) / (a.ei - 2) : (ni + a.ei - 5) / (a.ei - 4);
-  // j-chunks: enough CTAs for ~8 rounds over the SMs, chunks no shorter than 32 planes
+  // j-chunks: enough CTAs for ~8 rounds over the SMs, chunks no shorter than 32 planes (measured flat between 4 and
+  // 16 rounds at 512^3)
   static int rounds = -1;
   if (rounds < 0) { const char* e = getenv("CZB_ROUNDS"); rounds = e ? atoi(e) : 8; }
   int njc = (148 * rounds + a.ntk * a.nti - 1) / (a.ntk * a.nti);
   if (njc > (nj + 31) / 32) njc = (nj + 31) / 32;
+  // small grids: fewer tiles than SMs even with 32-plane chunks -> shorter chunks (>= 8 planes) until every SM has one
+  static const bool no_small = getenv("CZB_NO_SMALL") != nullptr;
+  if (!no_small && a.ntk * a.nti * njc < 148) {
+    njc = (148 + a.ntk * a.nti - 1) / (a.ntk * a.nti);
+    if (njc > (nj + 7) / 8) njc = (nj + 7) / 8;
+  }
   if (njc < 1) njc = 1;
   a.jl = (nj + njc - 1) / njc;
   a.njc = (nj + a.jl - 1) / a.jl;
