@@ -700,6 +700,7 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
     njc = (148 + a.ntk * a.nti - 1) / (a.ntk * a.nti);
     if (njc > (nj + 7) / 8) njc = (nj + 7) / 8;
   }
+  { static const char* e = getenv("CZB_NJC"); if (e && part == 0) njc = atoi(e); }   // experiments
   if (njc < 1) njc = 1;
   a.jl = (nj + njc - 1) / njc;
   a.njc = (nj + a.jl - 1) / a.jl;
