@@ -670,10 +670,10 @@ __global__ void __launch_bounds__(WPB * 32, 1) k_pcr_warp_tm(Geo G, int n, int p
   constexpr bool FTM = EPL != 32;                        // 2x2 rows in tensor memory
   static_assert(EPL >= 8 && WPB % 4 == 0, "tensor-memory variant: EPL 8, 16, 32");
   static_assert(!L4 || (BULK && EPL != 32), "4x4 last stage: lines of <= 512 cells with bulk staging");
-  extern __shared__ double sm_raw[];
+  extern __shared__ __align__(128) unsigned char sm_tm[];   // TMA bulk destinations need 16-byte alignment
   __shared__ uint32_t tm_base_s;
   __shared__ unsigned long long mbar_s[WPB];
-  REAL* sm = reinterpret_cast<REAL*>(sm_raw);
+  REAL* sm = reinterpret_cast<REAL*>(sm_tm);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const REAL zero = (REAL)0.0;
   const int s2 = 1 << (pn - 1);
