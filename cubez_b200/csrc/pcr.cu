@@ -368,48 +368,9 @@ __global__ void __launch_bounds__(EPL == 32 ? 512 : 256, EPL == 32 ? 1 : 2) k_pc
 
 #ifndef _REAL_IS_DOUBLE_
 // ------------------------------------------------------------------------------------------------
-// The same kernel with the NEXT line's source term fetched while the current line is reduced: stage p of
-// the current line issues the global loads of CPS cells per lane of the next line before its arithmetic
-// and turns them into d (cz_solver.f90:569-579) after it, so the memory latency hides behind the stage
-// and the loads need only 5*CPS registers.  Each warp owns two exchange buffers (current result / next
-// source).  Only for msk == 1 on all line cells (the solve loops); arithmetic identical to k_pcr_warp.
-template <int EPL>
-__device__ __forceinline__ void pcr_stage(REAL (&d)[EPL], const int p, const REAL* ts, const int lane) {
-  typedef PcrLay<EPL> LY;
-  constexpr int NQ = LY::NQ, ROW = LY::ROW;
-  const int s = 1 << p;
-  const int t = s / EPL;                       // lane distance when s >= EPL
-  const REAL* tp = ts + (size_t)p * 3 * ROW + lane * 4;
-  REAL dn[EPL];
-#pragma unroll
-  for (int q = 0; q < NQ; ++q) {
-    const float4 ap4 = *reinterpret_cast<const float4*>(tp + q * LY::QSTR);
-    const float4 cp4 = *reinterpret_cast<const float4*>(tp + ROW + q * LY::QSTR);
-    const float4 e4 = *reinterpret_cast<const float4*>(tp + 2 * ROW + q * LY::QSTR);
-    const REAL apv[4] = {ap4.x, ap4.y, ap4.z, ap4.w}, cpv[4] = {cp4.x, cp4.y, cp4.z, cp4.w};
-    const REAL ev[4] = {e4.x, e4.y, e4.z, e4.w};
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int m = 4 * q + e;
-      REAL dl, dr;
-      if (s < EPL) {
-        // A neighbour outside the line needs no select: its coefficient ap / cp is exactly 0 (k_pcr_tables:
-        // a(k) = 0 for k < s, c(k) = 0 for k + s >= n) and the shuffle then returns the lane's own finite d.
-        if (m >= s) dl = d[m - s];
-        else dl = __shfl_up_sync(0xffffffffu, d[(m - s + EPL) & (EPL - 1)], 1);
-        if (m + s < EPL) dr = d[m + s];
-        else dr = __shfl_down_sync(0xffffffffu, d[(m + s - EPL) & (EPL - 1)], 1);
-      } else {
-        dl = __shfl_up_sync(0xffffffffu, d[m], t);
-        dr = __shfl_down_sync(0xffffffffu, d[m], t);
-      }
-      dn[m] = ev[e] * (d[m] - apv[e] * dl - cpv[e] * dr);
-    }
-  }
-#pragma unroll
-  for (int m = 0; m < EPL; ++m) d[m] = dn[m];
-}
-
+// Building blocks of the solve-loop kernel k_pcr_warp_tm below (msk == 1 on all line cells, so it is not read):
+// packed PCR stage with shared-memory tables, source-term loads of the NEXT line issued during the stages
+// of the current one.  Arithmetic identical to k_pcr_warp.
 // Packed variant: two neighbouring cells of a lane travel as one 64-bit register pair and are reduced by
 // Blackwell's FADD2 / FMUL2 / FFMA2.  ptxas contracts mul.rn.f32x2 + sub.rn.f32x2 into one FFMA2 (one rounding
 // instead of two) even with --fmad false, so a product that feeds a subtraction is written fma(a, b, -0) with
@@ -494,140 +455,8 @@ __device__ __forceinline__ void pcr_src_put(const REAL (&v)[6][NC], REAL* wbl, c
   }
 }
 
-template <int EPL, int WPB>
-__global__ void __launch_bounds__(WPB * 32, EPL == 32 ? 1 : 2) k_pcr_warp_pf(Geo G, int n, int pn, int stages, const REAL* __restrict__ tab,
-                                                  const REAL* __restrict__ fin, LineSel sel, const REAL* x, REAL* dst,
-                                                  const REAL* __restrict__ rhs, REAL omg, pk_t nz,
-                                                  const LoopState* st, RedBuf rb, FinStoreP finst) {
-  if (st && st->done) return;
-  typedef PcrLay<EPL> LY;
-  constexpr int NQ = LY::NQ, ROW = LY::ROW, NP = 32 * EPL;
-  constexpr int CPS = EPL == 4 ? 1 : EPL == 32 ? 4 : 2;      // next-line cells per lane fetched per stage
-  constexpr int MAXST = 5 + (EPL == 4 ? 2 : EPL == 8 ? 3 : EPL == 16 ? 4 : 5);
-  extern __shared__ double sm_raw[];
-  REAL* ts = reinterpret_cast<REAL*>(sm_raw);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  REAL* F1 = ts + (size_t)stages * 3 * ROW;
-  REAL* F2 = F1 + ROW;
-  REAL* wb0 = F2 + ROW + (size_t)warp * 2 * ROW;       // this warp's two exchange buffers
-  const REAL zero = (REAL)0.0;
-  const int s2 = 1 << (pn - 1);
-  for (int idx = tid; idx < stages * 3 * NP; idx += WPB * 32) {
-    const int row = idx / NP, k = idx - row * NP;
-    ts[(size_t)row * ROW + LY::pos(k)] = (k < n) ? tab[(size_t)row * n + k] : zero;
-  }
-  for (int k = tid; k < NP; k += WPB * 32) {
-    REAL f1 = zero, f2 = zero;
-    if (k < n) {
-      if (k < s2) { f1 = fin[k]; f2 = fin[2 * (size_t)s2 + k]; }
-      else        { f1 = fin[(size_t)s2 + (k - s2)]; f2 = fin[2 * (size_t)s2 + (k - s2)]; }
-    }
-    F1[LY::pos(k)] = f1; F2[LY::pos(k)] = f2;
-  }
-  __syncthreads();
-  const REAL r = (REAL)1.0 / (REAL)6.0;
-  const int t2 = s2 / EPL;
-  double acc[1] = {0.0};
-  // first cell of line `line`, or -1 when the line does not exist
-  auto line_base = [&](int line) -> long long {
-    if (line >= sel.nlines) return -1;
-    int i, j;
-    if (sel.mode <= 1) {
-      const int jj = line / sel.per_j, m = line - jj * sel.per_j;
-      j = G.jst + jj;
-      i = G.ist + ((G.ist + j + sel.ofs + sel.mode) & 1) + 2 * m;
-    } else if (sel.mode == 2) {
-      const int jj = line / sel.per_j, m = line - jj * sel.per_j;
-      j = G.jst + jj; i = G.ist + m;
-    } else {
-      j = sel.jlo + line; i = sel.diag - j;
-    }
-    return (i > G.ied) ? -1 : G.at(G.kst, i, j);
-  };
-  const int posl = LY::pos(lane);                       // pos(lane + 32 c) = posl + (128/EPL) c
-  auto src_of = [&](long long b) -> PcrSrc {
-    const REAL* px = x + b + lane;
-    return PcrSrc{px - G.plane, px + G.plane, px - G.nk, px + G.nk, rhs + b + lane, x + b - 1};
-  };
-  auto full_load = [&](long long b, REAL* wb) {
-    constexpr int CH = EPL < 8 ? EPL : 8;
-    const PcrSrc P = src_of(b);
-#pragma unroll
-    for (int m0 = 0; m0 < EPL; m0 += CH) {
-      REAL v[6][CH];
-      pcr_src_load<CH>(v, P, m0, n, lane);
-      pcr_src_put<EPL, CH>(v, wb + posl, m0, n, lane, r);
-    }
-  };
-  const int lstride = gridDim.x * WPB;
-  int line = blockIdx.x * WPB + warp;
-  long long base = line_base(line);
-  int buf = 0;
-  if (base >= 0) full_load(base, wb0);
-  while (line < sel.nlines) {
-    const int nline = line + lstride;
-    const long long nbase = line_base(nline);
-    REAL* wc = wb0 + buf * ROW;
-    REAL* wn = wb0 + (buf ^ 1) * ROW;
-    __syncwarp();
-    if (base >= 0) {
-      const PcrSrc P = src_of(nbase >= 0 ? nbase : base);
-      pk_t D[EPL / 2];
-#pragma unroll
-      for (int q = 0; q < NQ; ++q) {
-        const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(wc + q * LY::QSTR + lane * 4);
-        D[2 * q] = v.x; D[2 * q + 1] = v.y;
-      }
-#pragma unroll
-      for (int p = 0; p < MAXST; ++p) {
-        if (p < stages) {
-          REAL v[6][CPS];
-          const bool pf = (nbase >= 0) && (p * CPS < EPL);
-          if (pf) pcr_src_load<CPS>(v, P, p * CPS, n, lane);
-          pcr_stage_pk<EPL>(D, p, ts, lane, nz);
-          if (pf) pcr_src_put<EPL, CPS>(v, wn + posl, p * CPS, n, lane, r);
-        }
-      }
-      // own-line values for the relaxation, in flight during the 2x2 stage
-      const REAL* px = x + base + lane;
-      REAL* pd = dst + base + lane;
-      REAL pp[EPL];
-#pragma unroll
-      for (int c = 0; c < EPL; ++c) pp[c] = (lane < n - 32 * c) ? px[32 * c] : zero;
-      // ---- last 2x2 stage (cz_solver.f90:612-630) ----
-#pragma unroll
-      for (int q = 0; q < NQ; ++q) {
-        const ulonglong2 f1 = *reinterpret_cast<const ulonglong2*>(F1 + q * LY::QSTR + lane * 4);
-        const ulonglong2 f2 = *reinterpret_cast<const ulonglong2*>(F2 + q * LY::QSTR + lane * 4);
-        pk_t pr[2];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const pk_t v = __shfl_xor_sync(0xffffffffu, D[2 * q + h], t2 & 31);
-          pr[h] = (t2 < 32) ? v : 0ull;
-        }
-        ulonglong2 o;
-        o.x = mul2(sub2(D[2 * q], fma2(f1.x, pr[0], nz)), f2.x);
-        o.y = mul2(sub2(D[2 * q + 1], fma2(f1.y, pr[1], nz)), f2.y);
-        *reinterpret_cast<ulonglong2*>(wc + q * LY::QSTR + lane * 4) = o;
-      }
-      __syncwarp();
-      // ---- relaxation in the cyclic layout (cz_solver.f90:642-648), msk == 1; cells k >= n hold 0 - 0 ----
-#pragma unroll
-      for (int c = 0; c < EPL; ++c) {
-        const REAL dp = (wc[posl + (128 / EPL) * c] - pp[c]) * omg;
-        if (lane < n - 32 * c) pd[32 * c] = pp[c] + dp;
-        acc[0] += (double)(dp * dp);
-      }
-    } else if (nbase >= 0) {
-      full_load(nbase, wn);
-    }
-    line = nline; base = nbase; buf ^= 1;
-  }
-  grid_reduce<1>(acc, rb, finst);
-}
-
 // ------------------------------------------------------------------------------------------------
-// Coefficient tables in TENSOR MEMORY.  In the kernel above the shared-memory pipe is the limiter (ncu:
+// Coefficient tables in TENSOR MEMORY.  With the tables in shared memory the LSU pipe is the limiter (ncu:
 // l1tex 90 % busy, 2/3 of its wavefronts are the table reads: 3 values per cell and stage).  The tables
 // are per-lane private data ("lane l needs the coefficients of its own EPL cells"), which is exactly the
 // shape of Blackwell's tensor memory: 128 lanes x 512 columns x 32 bit per SM, read with tcgen05.ld
@@ -1194,18 +1023,6 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
                      G.nk % 4 == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)rhs % 16) == 0 &&
                      getenv("CZB_PCR_NOTMEM") == nullptr && getenv("CZB_PCR_NOBULK") == nullptr;
   if ((!T.last4 || l4_ok) && !no_warp && n >= 17 && n <= 1024) {   // warp-per-line kernels
-    auto go_pf = [&](auto epl, auto wpb_) {   // prefetching variant, msk not read
-      constexpr int EPL = decltype(epl)::value, WPB = decltype(wpb_)::value;
-      typedef PcrLay<EPL> LY;
-      const size_t sm = sizeof(REAL) * ((size_t)T.stages * 3 * LY::ROW + 2 * LY::ROW + (size_t)WPB * 2 * LY::ROW);
-      int g = (sel.nlines + WPB - 1) / WPB;
-      const int cap = 148 * (EPL == 32 ? 1 : 2);
-      if (g > cap) g = cap;
-      if ((size_t)g > L.rb_blocks) g = (int)L.rb_blocks;
-      static size_t sm_set = 0;
-      if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp_pf<EPL, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
-      k_pcr_warp_pf<EPL, WPB><<<g, WPB * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, rhs, omg, 0x8000000080000000ull, L.st, L.rb, fs);
-    };
     auto go_tm = [&](auto epl, auto wpb_, auto bulk_, auto l4_) {   // prefetching variants with the tables in tensor memory
       constexpr int EPL = decltype(epl)::value, WPB = decltype(wpb_)::value;
       constexpr bool BULK = decltype(bulk_)::value, L4 = decltype(l4_)::value;
@@ -1229,9 +1046,8 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       count_launch();
       return;
     }
-    static const bool no_pf = getenv("CZB_PCR_NOPF") != nullptr;
     static const bool no_tm = getenv("CZB_PCR_NOTMEM") != nullptr;
-    if (mask_is_inner && !no_pf && !no_tm && n > 128 && (1 << T.pn) == 32 * (n <= 256 ? 8 : n <= 512 ? 16 : 32) && (n <= 256 ? 2 : n <= 512 ? 2 : 4) * T.stages >= (n <= 256 ? 8 : n <= 512 ? 16 : 32)
+    if (mask_is_inner && !no_tm && n > 128 && (1 << T.pn) == 32 * (n <= 256 ? 8 : n <= 512 ? 16 : 32) && (n <= 256 ? 2 : n <= 512 ? 2 : 4) * T.stages >= (n <= 256 ? 8 : n <= 512 ? 16 : 32)
         && 3 * T.stages + 2 <= (n <= 256 ? 64 : n <= 512 ? 32 : 29)) {
       // rows staged by TMA bulk copies: row pitch and base addresses 16-byte aligned, 5 rows + exchange buffer per warp
       static const bool no_bulk = getenv("CZB_PCR_NOBULK") != nullptr;
@@ -1242,20 +1058,6 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       else if (n <= 512) { if (bulk) go_tm(integral_constant<int, 16>{}, integral_constant<int, 16>{}, std::true_type{}, std::false_type{});
                            else      go_tm(integral_constant<int, 16>{}, integral_constant<int, 16>{}, std::false_type{}, std::false_type{}); }
       else               go_tm(integral_constant<int, 32>{}, integral_constant<int, 12>{}, std::false_type{}, std::false_type{});
-      CZB_CHECK(cudaGetLastError());
-      count_launch();
-      return;
-    }
-    const int cps = n <= 128 ? 1 : n <= 512 ? 2 : 4, epl = n <= 128 ? 4 : n <= 256 ? 8 : n <= 512 ? 16 : 32;
-    // the prefetching kernel needs its tables + two exchange buffers per warp in shared memory (n = 1024 = 2^10
-    // has one stage more than 513..1023 and does not fit: k_pcr_warp below)
-    const size_t row_b = sizeof(REAL) * (size_t)(epl / 4) * (32 * 4 + 8);
-    const size_t sm_pf = ((size_t)T.stages * 3 + 2 + 2 * (size_t)(epl == 32 ? 12 : 8)) * row_b;
-    if (mask_is_inner && !no_pf && T.stages * cps >= epl && sm_pf <= 225 * 1024) {
-      if (n <= 128)      go_pf(std::integral_constant<int, 4>{}, std::integral_constant<int, 8>{});
-      else if (n <= 256) go_pf(std::integral_constant<int, 8>{}, std::integral_constant<int, 8>{});
-      else if (n <= 512) go_pf(std::integral_constant<int, 16>{}, std::integral_constant<int, 8>{});
-      else               go_pf(std::integral_constant<int, 32>{}, std::integral_constant<int, 12>{});
       CZB_CHECK(cudaGetLastError());
       count_launch();
       return;
