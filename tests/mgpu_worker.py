@@ -21,10 +21,12 @@ def main():
     torch.cuda.set_device(lr)
     dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     n = int(os.environ.get("CZB_MGPU_N", "64"))
-    cases = [("sor2sma", None, 1.5, 60, 0), ("sor2sma", None, 1.5, 60, 1), ("jacobi", None, 0.8, 40, 0),
-             ("pcr_rb", None, 1.5, 30, 0), ("pbicgstab", "sor2sma", 1.1, 30, 0)]
+    n2 = int(os.environ.get("CZB_MGPU_N2", "200"))   # long lines: tensor-memory line-SOR kernels on slabs
+    cases = [(n, "sor2sma", None, 1.5, 60, 0), (n, "sor2sma", None, 1.5, 60, 1), (n, "jacobi", None, 0.8, 40, 0),
+             (n, "pcr_rb", None, 1.5, 30, 0), (n, "pbicgstab", "sor2sma", 1.1, 30, 0),
+             (n2, "pcr_rb", None, 1.5, 8, 0), (n2, "pcr_rb_esa", None, 1.5, 8, 0), (n2, "sor2sma", None, 1.5, 12, 0)]
     ok = True
-    for solver, pc, omega, iters, variant in cases:
+    for n, solver, pc, omega, iters, variant in cases:
         cz = cubez_b200.CZ([n, n, n], "f32", device=lr, nranks=world, rank=rank, eps=1e-5 if solver == "pbicgstab" else 0.0)
         cz.variant(variant)
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -55,8 +57,8 @@ def main():
                 good = good and np.allclose(out["history"][:m - 1], o1["history"][:m - 1], rtol=1e-3)
             else:
                 good = same_itr and np.array_equal(full, ref) and np.allclose(out["history"][:m], o1["history"][:m], rtol=1e-12)
-            print("mgpu %-10s pc=%-8s variant=%d ranks=%d itr %d/%d maxdiff %.3e %s" % (
-                solver, pc, variant, world, out["itr"], o1["itr"], float(np.abs(full - ref).max()),
+            print("mgpu n=%d %-10s pc=%-8s variant=%d ranks=%d itr %d/%d maxdiff %.3e %s" % (
+                n, solver, pc, variant, world, out["itr"], o1["itr"], float(np.abs(full - ref).max()),
                 "OK" if good else "FAIL"), flush=True)
             ok = ok and good
             c1.close()
