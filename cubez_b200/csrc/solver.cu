@@ -214,7 +214,8 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
+      // bc_k (cz_Poisson.cpp:73) is idempotent once both ping-pong buffers hold the Dirichlet values (see RBSOR)
+      if (it <= 2) launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
     }
   };
   int itr, done_iters;
@@ -225,7 +226,10 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     for (int it = 1; it <= itr_max; ++it) body(it);
     itr = itr_max + 1; done_iters = itr_max;
   }
-  if (done_iters & 1) launch_copy_inner(launch(false), G, X, W);
+  if (done_iters & 1) {
+    launch_copy_inner(launch(false), G, X, W);
+    if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // X missed the bc_k of an odd last iteration
+  }
   flop += 18.0 * G.cells() * done_iters;
   return itr;
 }
@@ -233,14 +237,14 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
 // CZ::PSOR (cz_Poisson.cpp:95-146): lexicographic SOR in the reference's 1-thread order.
 int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check) {
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
-  auto body = [&](int) {
+  auto body = [&](int it) {
     Launch L = launch();
     launch_psor_sweep(L, G, X, B, cf, ac1, rs, false);
     Comm_S(X, 1);
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
+      if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -347,7 +351,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
     }
   } else {
-    auto body = [&](int) {
+    auto body = [&](int it) {
       Launch L = launch();
       for (int color = 0; color < 2; ++color) {
         launch_rb_color(L, G, X, B, cf, ac1, ip + color, rs, color == 1);
@@ -356,7 +360,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (converge_check) {
         Comm_SUM(0);
         launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-        launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
+        if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
@@ -392,7 +396,7 @@ int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flo
   REAL* M = ensure_mask(this);
   const int ofs = (head[0] + head[1]) & 1;   // global (i+j) parity; 0 on a single domain
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
-  auto body = [&](int) {
+  auto body = [&](int it) {
     Launch L = launch();
     for (int color = 0; color < 2; ++color) {
       launch_pcr_lines(L, G, T, color, ofs, 0, X, X, M, B, ac1, rs, color == 1, true);
@@ -401,7 +405,7 @@ int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flo
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
+      if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -422,7 +426,7 @@ int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, 
   pcr_build_tables(rt().stream, T, n, pn, last4);
   REAL* M = ensure_mask(this);
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
-  auto body = [&](int) {
+  auto body = [&](int it) {
     Launch L = launch();
     bool first = true;
     for (int d = G.ist + G.jst; d <= G.ied + G.jed; ++d) {
@@ -433,7 +437,7 @@ int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, 
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
+      if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -453,7 +457,7 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
   REAL* W = field(WRK);
   wrk_guards_zero = false;
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
-  auto body = [&](int) {
+  auto body = [&](int it) {
     Launch L = launch();
     launch_pcr_lines(L, G, pcr2, 2, 0, 0, X, W, M, B, ac1, rs, false, true);
     launch_copy_inner(L, G, X, W);
@@ -461,7 +465,7 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);
+      if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
