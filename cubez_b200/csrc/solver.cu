@@ -457,20 +457,36 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
   REAL* W = field(WRK);
   wrk_guards_zero = false;
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
-  auto body = [&](int it) {
-    Launch L = launch();
-    launch_pcr_lines(L, G, pcr2, 2, 0, 0, X, W, M, B, ac1, rs, false, true);
-    launch_copy_inner(L, G, X, W);
-    Comm_S(X, 1);
-    if (converge_check) {
+  int itr, done_iters;
+  if (converge_check) {
+    // The reference writes the new lines to wrk and copies them back (cz_solver.f90:1632-1665); here X and WRK
+    // alternate as source and destination (both hold the same boundary / guard values), as in JACOBI.
+    CZB_CHECK(cudaMemcpyAsync(W, X, sizeof(REAL) * field_elems(), cudaMemcpyDeviceToDevice, rt().stream));
+    auto body = [&](int it) {
+      REAL* src = (it & 1) ? X : W;
+      REAL* dst = (it & 1) ? W : X;
+      Launch L = launch();
+      launch_pcr_lines(L, G, pcr2, 2, 0, 0, src, dst, M, B, ac1, rs, false, true);
+      Comm_S(dst, 1);
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 2) launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
+    };
+    itr = run_checked(itr_max, res, body);
+    done_iters = h_state[0].itr;
+    if (done_iters & 1) {
+      launch_copy_inner(launch(false), G, X, W);
+      launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
     }
-  };
-  int itr, done_iters;
-  if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
-  else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
+  } else {
+    for (int it = 1; it <= itr_max; ++it) {
+      Launch L = launch();
+      launch_pcr_lines(L, G, pcr2, 2, 0, 0, X, W, M, B, ac1, rs, false, true);
+      launch_copy_inner(L, G, X, W);
+      Comm_S(X, 1);
+    }
+    itr = itr_max + 1; done_iters = itr_max;
+  }
   flop += pcr_iter_flop(G, pn, false, 0.0) * done_iters;
   return itr;
 }
