@@ -1018,10 +1018,16 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
   FinStoreP fs{L.acc_st, slot, add ? 1 : 0};
 #ifndef _REAL_IS_DOUBLE_
   static const bool no_warp = getenv("CZB_PCR_BLOCK") != nullptr;
-  // 4x4 last stage (pcr_rb_esa & co) on the tensor-memory kernel: solve loops, lines of 129..512 cells, bulk staging
-  const bool l4_ok = T.last4 && mask_is_inner && n > 128 && n <= 512 && (1 << T.pn) == 32 * (n <= 256 ? 8 : 16) &&
-                     G.nk % 4 == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)rhs % 16) == 0 &&
-                     getenv("CZB_PCR_NOTMEM") == nullptr && getenv("CZB_PCR_NOBULK") == nullptr;
+  static const bool no_tm = getenv("CZB_PCR_NOTMEM") != nullptr;
+  static const bool no_bulk = getenv("CZB_PCR_NOBULK") != nullptr;
+  const int epl = n <= 128 ? 4 : n <= 256 ? 8 : n <= 512 ? 16 : 32;      // cells per lane of the warp kernels
+  // tensor-memory kernel: solve loops (mask not read), lines of 129..1024 cells that fill more than half of the
+  // 32*epl slots (n = 2^m has one stage more and its 2x2 partner outside the warp: k_pcr_warp)
+  const bool tm_ok = mask_is_inner && !no_tm && n > 128 && (1 << T.pn) == 32 * epl;
+  // rows staged by TMA bulk copies: row pitch and base addresses 16-byte aligned, 5 rows + exchange buffer per warp
+  const bool bulk = !no_bulk && n <= 512 && G.nk % 4 == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)rhs % 16) == 0;
+  // 4x4 last stage (pcr_rb_esa & co): only on the tensor-memory kernel with bulk staging, else k_pcr_lines<1>
+  const bool l4_ok = T.last4 && tm_ok && bulk;
   if ((!T.last4 || l4_ok) && !no_warp && n >= 17 && n <= 1024) {   // warp-per-line kernels
     auto go_tm = [&](auto epl, auto wpb_, auto bulk_, auto l4_) {   // prefetching variants with the tables in tensor memory
       constexpr int EPL = decltype(epl)::value, WPB = decltype(wpb_)::value;
@@ -1046,12 +1052,8 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
       count_launch();
       return;
     }
-    static const bool no_tm = getenv("CZB_PCR_NOTMEM") != nullptr;
-    if (mask_is_inner && !no_tm && n > 128 && (1 << T.pn) == 32 * (n <= 256 ? 8 : n <= 512 ? 16 : 32) && (n <= 256 ? 2 : n <= 512 ? 2 : 4) * T.stages >= (n <= 256 ? 8 : n <= 512 ? 16 : 32)
-        && 3 * T.stages + 2 <= (n <= 256 ? 64 : n <= 512 ? 32 : 29)) {
-      // rows staged by TMA bulk copies: row pitch and base addresses 16-byte aligned, 5 rows + exchange buffer per warp
-      static const bool no_bulk = getenv("CZB_PCR_NOBULK") != nullptr;
-      const bool bulk = !no_bulk && n <= 512 && G.nk % 4 == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)rhs % 16) == 0;
+    // without bulk staging the source term is prefetched through registers, (epl == 32 ? 4 : 2) cells per stage
+    if (tm_ok && (epl == 32 ? 4 : 2) * T.stages >= epl) {
       using std::integral_constant;
       if (n <= 256)      { if (bulk) go_tm(integral_constant<int, 8>{}, integral_constant<int, 16>{}, std::true_type{}, std::false_type{});
                            else      go_tm(integral_constant<int, 8>{}, integral_constant<int, 16>{}, std::false_type{}, std::false_type{}); }
