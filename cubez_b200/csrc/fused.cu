@@ -554,7 +554,8 @@ EncodeTiledFn encode_fn() {
 typedef std::tuple<const void*, int, int, int, int> TmKey;
 std::map<TmKey, CUtensorMap> g_tmaps;
 
-const CUtensorMap& tmap_for(const REAL* base, const Geo& G, int ei) {
+// Returned by value: a later call may evict the cache, a reference into it would dangle.
+CUtensorMap tmap_for(const REAL* base, const Geo& G, int ei) {
   TmKey key(base, G.nk, G.ni, G.nj, ei);
   auto it = g_tmaps.find(key);
   if (it != g_tmaps.end()) return it->second;
