@@ -98,3 +98,58 @@ def test_double_and_real_sum_modes_agree_to_float_rounding():
     os.environ["OMP_NUM_THREADS"] = "3"
     r2 = C.c_double(0); Xb = X.copy(); o.sweep_rb(Xb, B, r2)
     assert np.array_equal(Xa, Xb) and r1.value == r2.value
+
+
+# ---- the C++ port against an independent numpy restatement of the same Fortran (oracle/np_restatement.py) ----
+import sys
+sys.path.insert(0, os.path.join(os.path.dirname(HERE), "oracle"))
+import np_restatement as npr  # noqa: E402
+
+
+def _np_case(real, sz):
+    o = ou.OracleCZ(sz, real)
+    X, B = ou.random_fields(o.shape, o.dt)
+    return o, X, B
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+@pytest.mark.parametrize("sz", [[9, 9, 9], [12, 7, 23], [16, 16, 37]])
+def test_port_equals_numpy_restatement_sweeps(real, sz):
+    o, X, B = _np_case(real, sz)
+    cf = [1, 1, 1, 1, 1, 1, 6]
+    # Jacobi (cz_solver.f90:284-387)
+    o.ac1 = o.dt(0.8)
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_jacobi(Xo, B, ro)
+    Xn = X.copy(); rn = npr.jacobi(Xn, B, o.idx, cf, 0.8)
+    assert np.array_equal(Xo, Xn)
+    assert ro.value == pytest.approx(rn, rel=1e-12)
+    # red-black SOR, colour 0 then colour 1 (cz_solver.f90:404-493, cz_Poisson.cpp:197-203)
+    o.ac1 = o.dt(1.5)
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_rb(Xo, B, ro)
+    Xn = X.copy(); rn = npr.psor2sma_core(Xn, B, o.idx, cf, 0, 0, 1.5) + npr.psor2sma_core(Xn, B, o.idx, cf, 0, 1, 1.5)
+    assert np.array_equal(Xo, Xn)
+    assert ro.value == pytest.approx(rn, rel=1e-12)
+    # operator and residual vector (cz_blas.f90:579-644, 658-723)
+    cfa = np.array(cf, dtype=o.dt); flop = C.c_double(0)
+    Ao = np.zeros_like(X); o.dll.blas_calc_ax_(ou.ptr(Ao), ou.ptr(X), o._sz, o._idx, o.g(), ou.ptr(cfa), C.byref(flop))
+    An = np.zeros_like(X); npr.blas_calc_ax(An, X, o.idx, cf)
+    assert np.array_equal(Ao, An)
+    Ro = np.zeros_like(X); o.dll.blas_calc_rk_(ou.ptr(Ro), ou.ptr(X), ou.ptr(B), o._sz, o._idx, o.g(), ou.ptr(cfa), C.byref(flop))
+    Rn = np.zeros_like(X); npr.blas_calc_rk(Rn, X, B, o.idx, cf)
+    assert np.array_equal(Ro, Rn)
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+@pytest.mark.parametrize("sz", [[9, 9, 9], [12, 7, 23], [10, 8, 34], [8, 6, 66], [6, 6, 131]])
+def test_port_equals_numpy_restatement_line_sor(real, sz):
+    """pcr_rb (cz_solver.f90:497-662) incl. line lengths of 2^m and 2^m +- 1 cells; the numpy version carries the
+    coefficient recurrences a, c, e along with d exactly as the Fortran does (the CUDA kernels tabulate them)."""
+    o, X, B = _np_case(real, sz)
+    o.ac1 = o.dt(1.3)
+    M = o.mask()
+    n = o.idx[5] - o.idx[4] + 1
+    pn = ou.get_num_stage(n)
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_pcr("pcr_rb", Xo, B, ro)
+    Xn = X.copy(); rn = npr.pcr_rb(Xn, M, B, o.idx, pn, 0, 1.3) + npr.pcr_rb(Xn, M, B, o.idx, pn, 1, 1.3)
+    assert np.array_equal(Xo, Xn), np.abs(Xo - Xn).max()
+    assert ro.value == pytest.approx(rn, rel=1e-12)
