@@ -131,3 +131,55 @@ def pcr_rb(x, msk, rhs, idx, pn, color, omg):
     dp = (d1[:, 1:n + 1] - pp) * t(omg) * mk
     x[jc, ic, ks] = pp + dp
     return float(np.sum((dp * dp).astype(np.float64)))
+
+
+def pcr_rb_esa(x, msk, rhs, idx, pn, color, omg):
+    """cz_solver.f90:1261-1469: pn-2 PCR stages on zero-padded work arrays (no index clamps), then the 4x4
+    systems {k, k+s, k+2s, k+3s}, s = 2^(pn-2), by Cramer's rule (:1391-1438).  The pads are wide enough for
+    every index the last stage forms (the reference pads by s and relies on zeroed work arrays, cz_Poisson.cpp:655-661)."""
+    t = x.dtype.type
+    ist, ied, jst, jed, kst, ked = idx
+    o = G - 1
+    n = ked - kst + 1
+    r = t(1.0) / t(6.0)
+    J, I = np.meshgrid(np.arange(jst, jed + 1), np.arange(ist, ied + 1), indexing="ij")
+    m = ((I + J) % 2) == color
+    jc, ic = J[m] + o, I[m] + o
+    ks = slice(kst + o, ked + o + 1)
+    sq = 2 ** (pn - 2)
+    P = 4 * sq                                             # pad; cell k (0-based) lives at index P + k
+    a = np.zeros(n + 2 * P, dtype=x.dtype); c = np.zeros(n + 2 * P, dtype=x.dtype)
+    a[P + 1:P + n] = -r                                    # :1311-1319
+    c[P:P + n - 1] = -r                                    # :1320-1328
+    mk = msk[jc, ic, ks]
+    d = np.zeros((len(jc), n + 2 * P), dtype=x.dtype)
+    d[:, P:P + n] = ((x[jc - 1, ic, ks] + x[jc + 1, ic, ks] + x[jc, ic - 1, ks] + x[jc, ic + 1, ks]
+                      - rhs[jc, ic, ks]) * r) * mk
+    d[:, P] = (d[:, P] + x[jc, ic, kst + o - 1] * r) * mk[:, 0]
+    d[:, P + n - 1] = (d[:, P + n - 1] + x[jc, ic, ked + o + 1] * r) * mk[:, n - 1]
+    k = np.arange(P, P + n)
+    for p in range(1, pn - 1):                             # :1346-1363
+        s = 2 ** (p - 1)
+        ap = a[k]; cp = c[k]
+        e = t(1.0) / (t(1.0) - ap * c[k - s] - cp * a[k + s])
+        a1 = -e * ap * a[k - s]
+        c1 = -e * cp * c[k + s]
+        d1 = e * (d[:, k] - ap * d[:, k - s] - cp * d[:, k + s])
+        a[k] = a1; c[k] = c1; d[:, k] = d1
+    k = np.arange(P, P + sq)                               # :1365-1438
+    kl, km, kr = k + sq, k + 2 * sq, k + 3 * sq
+    cc1, cc2, cc3 = c[k], c[kl], c[km]
+    aa2, aa3, aa4 = a[kl], a[km], a[kr]
+    dd1, dd2, dd3, dd4 = d[:, k], d[:, kl], d[:, km], d[:, kr]
+    one = t(1.0)
+    inv = one / (one - aa4 * cc3 - aa3 * cc2 - aa2 * cc1 * (one - cc3 * aa4))
+    det1 = -(cc3 * (aa4 * dd1 + cc1 * cc2 * dd4 - aa4 * cc1 * dd2)) + dd1 + cc1 * cc2 * dd3 - aa3 * cc2 * dd1 - cc1 * dd2
+    det2 = dd2 + cc2 * cc3 * dd4 - aa4 * cc3 * dd2 - cc2 * dd3 - aa2 * (dd1 - aa4 * cc3 * dd1)
+    det3 = dd3 - cc3 * dd4 - aa3 * dd2 - aa2 * (cc1 * dd3 - cc1 * cc3 * dd4 - aa3 * dd1)
+    det4 = dd4 + aa3 * aa4 * dd2 - aa4 * dd3 - aa3 * cc2 * dd4 - aa2 * (cc1 * dd4 + aa3 * aa4 * dd1 - aa4 * cc1 * dd3)
+    d1 = np.zeros_like(d)
+    d1[:, k] = det1 * inv; d1[:, kl] = det2 * inv; d1[:, km] = det3 * inv; d1[:, kr] = det4 * inv
+    pp = x[jc, ic, ks]
+    dp = (d1[:, P:P + n] - pp) * t(omg) * mk
+    x[jc, ic, ks] = pp + dp
+    return float(np.sum((dp * dp).astype(np.float64)))

@@ -153,3 +153,9 @@ def test_port_equals_numpy_restatement_line_sor(real, sz):
     Xn = X.copy(); rn = npr.pcr_rb(Xn, M, B, o.idx, pn, 0, 1.3) + npr.pcr_rb(Xn, M, B, o.idx, pn, 1, 1.3)
     assert np.array_equal(Xo, Xn), np.abs(Xo - Xn).max()
     assert ro.value == pytest.approx(rn, rel=1e-12)
+    # pcr_rb_esa (cz_solver.f90:1261-1469): 4x4 systems by Cramer's rule in the last stage
+    if pn >= 3:
+        Xo = X.copy(); ro = C.c_double(0); o.sweep_pcr("pcr_rb_esa", Xo, B, ro)
+        Xn = X.copy(); rn = npr.pcr_rb_esa(Xn, M, B, o.idx, pn, 0, 1.3) + npr.pcr_rb_esa(Xn, M, B, o.idx, pn, 1, 1.3)
+        assert np.array_equal(Xo, Xn), np.abs(Xo - Xn).max()
+        assert ro.value == pytest.approx(rn, rel=1e-12)
