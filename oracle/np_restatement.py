@@ -82,83 +82,35 @@ def blas_calc_rk(r, p, b, idx, cf):
     r[sl] = b[sl] - (_stencil_sum(p, sl, cf) - p.dtype.type(cf[6]) * p[sl])
 
 
-def pcr_rb(x, msk, rhs, idx, pn, color, omg):
-    """cz_solver.f90:497-662, all lines of one colour at once ([line][k] arrays; a and c are re-initialised
-    per line to the same constants, :556-564, so they stay 1-D).  Work arrays carry one zero slot on each
-    side: the reference clamps k-s / k+s to kst-1 / ked+1, slots it never writes (:588-589)."""
+def _line_source(x, msk, rhs, idx, jc, ic):
+    """d(k) of the lines (jc, ic) (C indices), cz_solver.f90:569-579: [line][k] array, plus the mask rows."""
     t = x.dtype.type
-    ist, ied, jst, jed, kst, ked = idx
+    kst, ked = idx[4], idx[5]
     o = G - 1
     n = ked - kst + 1
     r = t(1.0) / t(6.0)
-    J, I = np.meshgrid(np.arange(jst, jed + 1), np.arange(ist, ied + 1), indexing="ij")
-    m = ((I + J) % 2) == color                             # :549  if(mod(i+j,2) /= color) cycle
-    jc, ic = J[m] + o, I[m] + o                            # C indices of the selected lines
     ks = slice(kst + o, ked + o + 1)
-    a = np.zeros(n + 2, dtype=x.dtype); c = np.zeros(n + 2, dtype=x.dtype)
-    a[2:n + 1] = -r                                        # a(kst) = 0, a(kst+1..ked) = -r
-    c[1:n] = -r                                            # c(kst..ked-1) = -r, c(ked) = 0
     mk = msk[jc, ic, ks]
-    d = np.zeros((len(jc), n + 2), dtype=x.dtype)
-    d[:, 1:n + 1] = ((x[jc - 1, ic, ks] + x[jc + 1, ic, ks] + x[jc, ic - 1, ks] + x[jc, ic + 1, ks]
-                      - rhs[jc, ic, ks]) * r) * mk         # :569-575
-    d[:, 1] = (d[:, 1] + x[jc, ic, kst + o - 1] * r) * mk[:, 0]          # :578
-    d[:, n] = (d[:, n] + x[jc, ic, ked + o + 1] * r) * mk[:, n - 1]      # :579
-    k = np.arange(1, n + 1)
-    for p in range(1, pn):                                 # :584-608
-        s = 2 ** (p - 1)
-        kl = np.maximum(k - s, 0); kr = np.minimum(k + s, n + 1)
-        ap = a[k]; cp = c[k]
-        e = t(1.0) / (t(1.0) - ap * c[kl] - cp * a[kr])
-        a1 = -e * ap * a[kl]
-        c1 = -e * cp * c[kr]
-        d1 = e * (d[:, k] - ap * d[:, kl] - cp * d[:, kr])
-        a[k] = a1; c[k] = c1; d[:, k] = d1
-    s = 2 ** (pn - 1)                                      # :612-630
-    d1 = np.zeros_like(d)
-    k = np.arange(1, s + 1)
-    kr = np.minimum(k + s, n + 1)
-    cc1 = c[k]; aa2 = a[kr]
-    f1 = d[:, k]; f2 = d[:, kr]
-    jj = t(1.0) / (t(1.0) - aa2 * cc1)
-    dd1 = (f1 - cc1 * f2) * jj
-    dd2 = (f2 - aa2 * f1) * jj
-    # the reference stores d1(k) and d1(kr) pair by pair in ascending k; a clamped kr = ked+1 is a guard slot that
-    # is rewritten by later pairs and never read, so the pairwise order does not matter
-    d1[:, k] = dd1
-    d1[:, kr] = dd2
-    pp = x[jc, ic, ks]                                     # :642-648
-    dp = (d1[:, 1:n + 1] - pp) * t(omg) * mk
-    x[jc, ic, ks] = pp + dp
-    return float(np.sum((dp * dp).astype(np.float64)))
+    d = ((x[jc - 1, ic, ks] + x[jc + 1, ic, ks] + x[jc, ic - 1, ks] + x[jc, ic + 1, ks] - rhs[jc, ic, ks]) * r) * mk
+    d[:, 0] = (d[:, 0] + x[jc, ic, kst + o - 1] * r) * mk[:, 0]
+    d[:, n - 1] = (d[:, n - 1] + x[jc, ic, ked + o + 1] * r) * mk[:, n - 1]
+    return d, mk, ks
 
 
-def pcr_rb_esa(x, msk, rhs, idx, pn, color, omg):
-    """cz_solver.f90:1261-1469: pn-2 PCR stages on zero-padded work arrays (no index clamps), then the 4x4
-    systems {k, k+s, k+2s, k+3s}, s = 2^(pn-2), by Cramer's rule (:1391-1438).  The pads are wide enough for
-    every index the last stage forms (the reference pads by s and relies on zeroed work arrays, cz_Poisson.cpp:655-661)."""
-    t = x.dtype.type
-    ist, ied, jst, jed, kst, ked = idx
-    o = G - 1
-    n = ked - kst + 1
+def _pcr_stages(dsrc, nstages, P):
+    """The PCR stages (cz_solver.f90:584-608 / 1346-1363) on work arrays padded by P zeros per side (an index the
+    reference clamps to kst-1 / ked+1, or reads from its zeroed pads, finds a zero here).  a and c start from the
+    per-line constants (:556-564) and are the same for every line, so they stay 1-D.  Returns padded a, c, d."""
+    t = dsrc.dtype.type
+    L, n = dsrc.shape
     r = t(1.0) / t(6.0)
-    J, I = np.meshgrid(np.arange(jst, jed + 1), np.arange(ist, ied + 1), indexing="ij")
-    m = ((I + J) % 2) == color
-    jc, ic = J[m] + o, I[m] + o
-    ks = slice(kst + o, ked + o + 1)
-    sq = 2 ** (pn - 2)
-    P = 4 * sq                                             # pad; cell k (0-based) lives at index P + k
-    a = np.zeros(n + 2 * P, dtype=x.dtype); c = np.zeros(n + 2 * P, dtype=x.dtype)
-    a[P + 1:P + n] = -r                                    # :1311-1319
-    c[P:P + n - 1] = -r                                    # :1320-1328
-    mk = msk[jc, ic, ks]
-    d = np.zeros((len(jc), n + 2 * P), dtype=x.dtype)
-    d[:, P:P + n] = ((x[jc - 1, ic, ks] + x[jc + 1, ic, ks] + x[jc, ic - 1, ks] + x[jc, ic + 1, ks]
-                      - rhs[jc, ic, ks]) * r) * mk
-    d[:, P] = (d[:, P] + x[jc, ic, kst + o - 1] * r) * mk[:, 0]
-    d[:, P + n - 1] = (d[:, P + n - 1] + x[jc, ic, ked + o + 1] * r) * mk[:, n - 1]
+    a = np.zeros(n + 2 * P, dtype=dsrc.dtype); c = np.zeros(n + 2 * P, dtype=dsrc.dtype)
+    a[P + 1:P + n] = -r                                    # a(kst) = 0, a(kst+1..ked) = -r
+    c[P:P + n - 1] = -r                                    # c(kst..ked-1) = -r, c(ked) = 0
+    d = np.zeros((L, n + 2 * P), dtype=dsrc.dtype)
+    d[:, P:P + n] = dsrc
     k = np.arange(P, P + n)
-    for p in range(1, pn - 1):                             # :1346-1363
+    for p in range(1, nstages + 1):
         s = 2 ** (p - 1)
         ap = a[k]; cp = c[k]
         e = t(1.0) / (t(1.0) - ap * c[k - s] - cp * a[k + s])
@@ -166,7 +118,35 @@ def pcr_rb_esa(x, msk, rhs, idx, pn, color, omg):
         c1 = -e * cp * c[k + s]
         d1 = e * (d[:, k] - ap * d[:, k - s] - cp * d[:, k + s])
         a[k] = a1; c[k] = c1; d[:, k] = d1
-    k = np.arange(P, P + sq)                               # :1365-1438
+    return a, c, d
+
+
+def _solve_2x2(dsrc, pn):
+    """pn-1 stages, then the 2x2 systems {k, k+s}, s = 2^(pn-1) (cz_solver.f90:612-630)."""
+    t = dsrc.dtype.type
+    n = dsrc.shape[1]
+    s = 2 ** (pn - 1)
+    P = 2 * s
+    a, c, d = _pcr_stages(dsrc, pn - 1, P)
+    k = np.arange(P, P + s)
+    cc1 = c[k]; aa2 = a[k + s]
+    f1 = d[:, k]; f2 = d[:, k + s]
+    jj = t(1.0) / (t(1.0) - aa2 * cc1)
+    d1 = np.zeros_like(d)
+    d1[:, k] = (f1 - cc1 * f2) * jj
+    d1[:, k + s] = (f2 - aa2 * f1) * jj
+    return d1[:, P:P + n]
+
+
+def _solve_4x4(dsrc, pn):
+    """pn-2 stages, then the 4x4 systems {k, k+s, k+2s, k+3s}, s = 2^(pn-2), by Cramer's rule
+    (cz_solver.f90:788-844, 1177-1225, 1391-1438)."""
+    t = dsrc.dtype.type
+    n = dsrc.shape[1]
+    sq = 2 ** (pn - 2)
+    P = 4 * sq
+    a, c, d = _pcr_stages(dsrc, pn - 2, P)
+    k = np.arange(P, P + sq)
     kl, km, kr = k + sq, k + 2 * sq, k + 3 * sq
     cc1, cc2, cc3 = c[k], c[kl], c[km]
     aa2, aa3, aa4 = a[kl], a[km], a[kr]
@@ -179,7 +159,110 @@ def pcr_rb_esa(x, msk, rhs, idx, pn, color, omg):
     det4 = dd4 + aa3 * aa4 * dd2 - aa4 * dd3 - aa3 * cc2 * dd4 - aa2 * (cc1 * dd4 + aa3 * aa4 * dd1 - aa4 * cc1 * dd3)
     d1 = np.zeros_like(d)
     d1[:, k] = det1 * inv; d1[:, kl] = det2 * inv; d1[:, km] = det3 * inv; d1[:, kr] = det4 * inv
+    return d1[:, P:P + n]
+
+
+def _relax_lines(x, dst, msk, rhs, idx, pn, omg, jc, ic, four):
+    """Source term, line solve and relaxation (cz_solver.f90:642-648) of the lines (jc, ic): reads x, writes dst."""
+    t = x.dtype.type
+    d, mk, ks = _line_source(x, msk, rhs, idx, jc, ic)
+    d1 = _solve_4x4(d, pn) if four else _solve_2x2(d, pn)
     pp = x[jc, ic, ks]
-    dp = (d1[:, P:P + n] - pp) * t(omg) * mk
-    x[jc, ic, ks] = pp + dp
+    dp = (d1 - pp) * t(omg) * mk
+    dst[jc, ic, ks] = pp + dp
     return float(np.sum((dp * dp).astype(np.float64)))
+
+
+def _lines(idx, color=None):
+    ist, ied, jst, jed = idx[:4]
+    o = G - 1
+    J, I = np.meshgrid(np.arange(jst, jed + 1), np.arange(ist, ied + 1), indexing="ij")
+    m = np.ones_like(J, dtype=bool) if color is None else ((I + J) % 2) == color   # :549 mod(i+j,2) /= color -> cycle
+    return J[m] + o, I[m] + o
+
+
+def pcr_rb(x, msk, rhs, idx, pn, color, omg):
+    """cz_solver.f90:497-662: the lines of one colour only read lines of the other colour -> all at once, in place."""
+    jc, ic = _lines(idx, color)
+    return _relax_lines(x, x, msk, rhs, idx, pn, omg, jc, ic, False)
+
+
+def pcr_rb_esa(x, msk, rhs, idx, pn, color, omg):
+    """cz_solver.f90:1261-1469: as pcr_rb with pn-2 stages and the 4x4 last stage."""
+    jc, ic = _lines(idx, color)
+    return _relax_lines(x, x, msk, rhs, idx, pn, omg, jc, ic, True)
+
+
+def pcr_j_esa(x, msk, rhs, idx, pn, omg):
+    """cz_solver.f90:1473-1676: every line from the OLD field (source term to `src`, result to `wrk`, copy back)."""
+    jc, ic = _lines(idx)
+    wrk = x.copy()
+    res = _relax_lines(x, wrk, msk, rhs, idx, pn, omg, jc, ic, False)
+    x[...] = wrk
+    return res
+
+
+def _lexicographic(x, msk, rhs, idx, pn, omg, four):
+    """pcr :666-872 (4x4), pcr_esa :1050-1257 (4x4, padded), pcr_eda :883-1046 (2x2): the lines one after the
+    other in (j, i) order, in place (Gauss-Seidel between lines; the reference's 1-thread order)."""
+    jc, ic = _lines(idx)
+    res = 0.0
+    for q in range(len(jc)):
+        res += _relax_lines(x, x, msk, rhs, idx, pn, omg, jc[q:q + 1], ic[q:q + 1], four)
+    return res
+
+
+def pcr(x, msk, rhs, idx, pn, omg):
+    return _lexicographic(x, msk, rhs, idx, pn, omg, True)
+
+
+def pcr_esa(x, msk, rhs, idx, pn, omg):
+    return _lexicographic(x, msk, rhs, idx, pn, omg, True)
+
+
+def pcr_eda(x, msk, rhs, idx, pn, omg):
+    return _lexicographic(x, msk, rhs, idx, pn, omg, False)
+
+
+def psor(p, b, idx, cf, omg):
+    """cz_solver.f90:207-269: lexicographic SOR, cell by cell in (j, i, k) order (scalar loop: small grids only)."""
+    t = p.dtype.type
+    ist, ied, jst, jed, kst, ked = idx
+    o = G - 1
+    c = [t(v) for v in cf]
+    om = t(omg)
+    res = 0.0
+    for j in range(jst + o, jed + o + 1):
+        for i in range(ist + o, ied + o + 1):
+            for k in range(kst + o, ked + o + 1):
+                pp = p[j, i, k]
+                ss = c[0] * p[j, i + 1, k]
+                ss = ss + c[1] * p[j, i - 1, k]
+                ss = ss + c[2] * p[j + 1, i, k]
+                ss = ss + c[3] * p[j - 1, i, k]
+                ss = ss + c[4] * p[j, i, k + 1]
+                ss = ss + c[5] * p[j, i, k - 1]
+                dp = ((ss - b[j, i, k]) / c[6] - pp) * om
+                p[j, i, k] = pp + dp
+                res += float(dp * dp)
+    return res
+
+
+def blas_triad(z, x, y, a, idx):
+    """cz_blas.f90:255-307  z = a*x + y on the inner cells."""
+    sl = _rng(idx)
+    z[sl] = z.dtype.type(a) * x[sl] + y[sl]
+
+
+def blas_bicg_1(p, r, q, beta, omg, idx):
+    """cz_blas.f90:452-504  p = r + beta*(p - omg*q)."""
+    t = p.dtype.type
+    sl = _rng(idx)
+    p[sl] = r[sl] + t(beta) * (p[sl] - t(omg) * q[sl])
+
+
+def blas_bicg_2(z, x, y, a, b, idx):
+    """cz_blas.f90:517-569  z = a*x + b*y + z."""
+    t = z.dtype.type
+    sl = _rng(idx)
+    z[sl] = t(a) * x[sl] + t(b) * y[sl] + z[sl]

@@ -159,3 +159,41 @@ def test_port_equals_numpy_restatement_line_sor(real, sz):
         Xn = X.copy(); rn = npr.pcr_rb_esa(Xn, M, B, o.idx, pn, 0, 1.3) + npr.pcr_rb_esa(Xn, M, B, o.idx, pn, 1, 1.3)
         assert np.array_equal(Xo, Xn), np.abs(Xo - Xn).max()
         assert ro.value == pytest.approx(rn, rel=1e-12)
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+@pytest.mark.parametrize("sz", [[9, 9, 9], [7, 6, 23], [6, 5, 34]])
+@pytest.mark.parametrize("kind", ["pcr_j_esa", "pcr", "pcr_eda", "pcr_esa"])
+def test_port_equals_numpy_restatement_other_line_sor(real, sz, kind):
+    """Line Jacobi and the lexicographic (Gauss-Seidel between lines) variants, cz_solver.f90:666-1257, 1473-1676."""
+    o, X, B = _np_case(real, sz)
+    o.ac1 = o.dt(0.9 if kind == "pcr_j_esa" else 1.3)
+    M = o.mask()
+    pn = ou.get_num_stage(o.idx[5] - o.idx[4] + 1)
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_pcr(kind, Xo, B, ro)
+    Xn = X.copy(); rn = getattr(npr, kind)(Xn, M, B, o.idx, pn, float(o.ac1))
+    assert np.array_equal(Xo, Xn), np.abs(Xo - Xn).max()
+    assert ro.value == pytest.approx(rn, rel=1e-12)
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+def test_port_equals_numpy_restatement_psor_and_blas1(real):
+    o, X, B = _np_case(real, [9, 8, 11])
+    cf = [1, 1, 1, 1, 1, 1, 6]
+    o.ac1 = o.dt(1.5)
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_psor(Xo, B, ro)
+    Xn = X.copy(); rn = npr.psor(Xn, B, o.idx, cf, 1.5)
+    assert np.array_equal(Xo, Xn)
+    assert ro.value == pytest.approx(rn, rel=1e-12)
+    Y, Z = ou.random_fields(o.shape, o.dt, seed=7)
+    flop = C.c_double(0)
+    a, b = o.creal(0.37), o.creal(-1.21)
+    Zo = Z.copy(); o.dll.blas_triad_(ou.ptr(Zo), ou.ptr(X), ou.ptr(Y), C.byref(a), o._sz, o._idx, o.g(), C.byref(flop))
+    Zn = Z.copy(); npr.blas_triad(Zn, X, Y, a.value, o.idx)
+    assert np.array_equal(Zo, Zn)
+    Po = X.copy(); o.dll.blas_bicg_1_(ou.ptr(Po), ou.ptr(Y), ou.ptr(Z), C.byref(a), C.byref(b), o._sz, o._idx, o.g(), C.byref(flop))
+    Pn = X.copy(); npr.blas_bicg_1(Pn, Y, Z, a.value, b.value, o.idx)
+    assert np.array_equal(Po, Pn)
+    Zo = Z.copy(); o.dll.blas_bicg_2_(ou.ptr(Zo), ou.ptr(X), ou.ptr(Y), C.byref(a), C.byref(b), o._sz, o._idx, o.g(), C.byref(flop))
+    Zn = Z.copy(); npr.blas_bicg_2(Zn, X, Y, a.value, b.value, o.idx)
+    assert np.array_equal(Zo, Zn)
