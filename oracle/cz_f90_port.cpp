@@ -241,11 +241,6 @@ void solve_line(LineWork& w, const Grid& G, REAL* x, REAL* dst, const REAL* rhs,
 
 double ipow2(int e) { return (double)(1L << e); }
 
-[[noreturn]] void maf_unsupported(const char* name) {
-  fprintf(stderr, "oracle: %s (stretched-grid MAF kernel, cz_maf.f90) is out of scope (SURVEY.md §8f-2)\n", name);
-  abort();
-}
-
 }  // namespace
 
 extern "C" {
@@ -788,31 +783,314 @@ void oracle_pcr_line_(int* n_, int* mode, REAL* a, REAL* c, REAL* d, REAL* xout)
 int oracle_real_bytes_() { return (int)sizeof(REAL); }
 
 // ------------------------------------------------------------------ cz_maf.f90 / cz_blas.f90:738,845
-// Stretched-grid twins: out of scope for SURVEY.md §8(a)-(e); symbols exist so that the
-// unmodified reference driver links.  They abort loudly if ever reached.
-void jacobi_maf_(REAL*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, double*, REAL*,
-                 REAL*, double*) { maf_unsupported("jacobi_maf_"); }
-void psor_maf_(REAL*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, double*, double*)
-{ maf_unsupported("psor_maf_"); }
-void psor2sma_core_maf_(REAL*, int*, int*, int*, REAL*, REAL*, REAL*, int*, int*, REAL*, REAL*,
-                        double*, REAL*, double*) { maf_unsupported("psor2sma_core_maf_"); }
-void pcr_rb_maf_(int*, int*, int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
-                 REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, double*, REAL*, double*)
-{ maf_unsupported("pcr_rb_maf_"); }
-void pcr_rb_esa_maf_(int*, int*, int*, int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*,
-                     REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, double*,
-                     REAL*, double*) { maf_unsupported("pcr_rb_esa_maf_"); }
-void pcr_maf_(int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
-              REAL*, REAL*, REAL*, REAL*, REAL*, double*, REAL*, double*)
-{ maf_unsupported("pcr_maf_"); }
-void pcr_eda_maf_(int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
-                  REAL*, REAL*, REAL*, double*, REAL*, double*) { maf_unsupported("pcr_eda_maf_"); }
-void pcr_esa_maf_(int*, int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
-                  REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, double*, REAL*, double*)
-{ maf_unsupported("pcr_esa_maf_"); }
-void calc_rk_maf_(REAL*, REAL*, REAL*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, double*)
-{ maf_unsupported("calc_rk_maf_"); }
-void calc_ax_maf_(REAL*, REAL*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, double*)
-{ maf_unsupported("calc_ax_maf_"); }
+// Stretched-grid ("MAF") twins.  Coordinates X(-1:sz(1)+2) etc.: Fortran index
+// m -> C offset m+1.  The metric coefficients are recomputed per cell exactly as the reference
+// does (they round differently per (i,j,k), so they cannot be tabulated per axis).
+}  // extern "C"
+
+namespace {
+
+// cz_maf.f90:70-99 (psor_maf; identical block in jacobi_maf :205-234, psor2sma_core_maf
+// :383-412, calc_rk_maf cz_blas.f90:785-812, calc_ax_maf :888-915, search_pivot :987-1014)
+struct MafCell { REAL C1, C2, C3, C7, C8, C9; };
+inline MafCell maf_cell(const REAL* X, const REAL* Y, const REAL* Z, int i, int j, int k) {
+  const REAL XG = (REAL)0.5 * (X[i + 2] - X[i]);
+  const REAL YE = (REAL)0.5 * (Y[j + 2] - Y[j]);
+  const REAL ZT = (REAL)0.5 * (Z[k + 2] - Z[k]);
+  const REAL XGG = X[i + 2] - (REAL)2.0 * X[i + 1] + X[i];
+  const REAL YEE = Y[j + 2] - (REAL)2.0 * Y[j + 1] + Y[j];
+  const REAL ZTT = Z[k + 2] - (REAL)2.0 * Z[k + 1] + Z[k];
+  const REAL YJA = XG * YE * ZT;
+  const REAL YJAI = (REAL)1.0 / YJA;
+  const REAL GX = YE * ZT * YJAI;
+  const REAL EY = XG * ZT * YJAI;
+  const REAL TZ = XG * YE * YJAI;
+  MafCell m;
+  m.C1 = GX * GX; m.C2 = EY * EY; m.C3 = TZ * TZ;
+  m.C7 = -XGG * m.C1 * GX; m.C8 = -YEE * m.C2 * EY; m.C9 = -ZTT * m.C3 * TZ;
+  return m;
+}
+
+// cz_maf.f90:102-112: dd, rp (note "+ bb": the MAF point sweeps ADD the source term), dp
+inline REAL maf_point_dp(const MafCell& m, const Grid& G, const REAL* p, long q, REAL bb, REAL pp,
+                         REAL omg) {
+  const REAL half = (REAL)0.5;
+  const REAL dd = (REAL)2.0 * (m.C1 + m.C2 + m.C3);
+  const REAL rp = (m.C1 + half * m.C7) * p[q + G.nk] + (m.C1 - half * m.C7) * p[q - G.nk] +
+                  (m.C2 + half * m.C8) * p[q + G.nk * G.ni] + (m.C2 - half * m.C8) * p[q - G.nk * G.ni] +
+                  (m.C3 + half * m.C9) * p[q + 1] + (m.C3 - half * m.C9) * p[q - 1] + bb;
+  return (rp / dd - pp) * omg;
+}
+
+// One line of the MAF line-SOR routines: cz_maf.f90:522-647 (pcr_rb_maf); pcr_maf :744-870,
+// pcr_eda_maf :981-1093, pcr_esa_maf :1194-1314, pcr_rb_esa_maf :1419-1539 run the same
+// statements (pn-1 PCR stages + 2x2 last stage in all five; they differ in the line selection
+// and in clamped vs zero-padded neighbour indices, which the padded LineWork covers: the
+// clamped routines read a/c/d(kst-1), (ked+1), which they never initialise, only multiplied by
+// coefficients that are exactly zero).
+void solve_line_maf(LineWork& w, const Grid& G, REAL* x, const REAL* rhs, const REAL* msk,
+                    const REAL* XX, const REAL* YY, const REAL* ZZ, int i, int j, int pn, REAL omg,
+                    Acc& acc, REAL* tmp) {
+  const REAL half = (REAL)0.5, two = (REAL)2.0;
+  const int kst = w.kst, ked = w.ked;
+  const REAL GX = two / (XX[i + 2] - XX[i]);
+  const REAL EY = two / (YY[j + 2] - YY[j]);
+  const REAL C1 = GX * GX;
+  const REAL C2 = EY * EY;
+  const REAL C7 = -(XX[i + 2] - two * XX[i + 1] + XX[i]) * C1 * GX;
+  const REAL C8 = -(YY[j + 2] - two * YY[j + 1] + YY[j]) * C2 * EY;
+  const REAL dd1 = C1 + half * C7, dd2 = C1 - half * C7;
+  const REAL cc1 = C2 + half * C8, cc2 = C2 - half * C8;
+  std::fill(w.a.begin(), w.a.end(), (REAL)0);
+  std::fill(w.c.begin(), w.c.end(), (REAL)0);
+  std::fill(w.d.begin(), w.d.end(), (REAL)0);
+  for (int k = kst; k <= ked; ++k) {   // :534-543 -> a1 = C3, c1 = C9, d1 = 1/R7
+    const REAL f1 = ZZ[k + 2], f2 = ZZ[k];
+    const REAL TZ = two / (f1 - f2);
+    const REAL ZTT = f1 - two * ZZ[k + 1] + f2;
+    const REAL f3 = TZ * TZ;
+    w.a1[w.o(k)] = f3;
+    w.c1[w.o(k)] = -ZTT * f3 * TZ;
+    w.d1[w.o(k)] = half / (C1 + C2 + f3);
+  }
+  const int ok = w.o(kst), oe = w.o(ked);
+  w.a[ok] = (REAL)0;                                                   // :545
+  w.c[ok] = -(w.a1[ok] + half * w.c1[ok]) * w.d1[ok];                  // :546
+  for (int k = kst + 1; k <= ked - 1; ++k) {                           // :548-554
+    const int o = w.o(k);
+    const REAL f1 = w.a1[o], f2 = w.c1[o], aa3 = w.d1[o];
+    w.a[o] = -(f1 - half * f2) * aa3;
+    w.c[o] = -(f1 + half * f2) * aa3;
+  }
+  w.a[oe] = -(w.a1[oe] - half * w.c1[oe]) * w.d1[oe];                  // :556
+  w.c[oe] = (REAL)0;                                                   // :557
+  const long pl = G.nk * G.ni;
+  for (int k = kst; k <= ked; ++k) {                                   // :560-568 (note "- rhs")
+    const long q = G.at(k, i, j);
+    w.d[w.o(k)] = (dd1 * x[q + G.nk] + dd2 * x[q - G.nk] + cc1 * x[q + pl] + cc2 * x[q - pl] - rhs[q]) *
+                  w.d1[w.o(k)] * msk[q];
+  }
+  w.d[ok] = (w.d[ok] + (w.a1[ok] - half * w.c1[ok]) * w.d1[ok] * x[G.at(kst - 1, i, j)]) * msk[G.at(kst, i, j)];
+  w.d[oe] = (w.d[oe] + (w.a1[oe] + half * w.c1[oe]) * w.d1[oe] * x[G.at(ked + 1, i, j)]) * msk[G.at(ked, i, j)];
+  line_pcr_stages(w, pn - 1);                                          // :580-601
+  line_last_2x2(w, pn);                                                // :605-620
+  for (int k = kst; k <= ked; ++k) {                                   // :630-637
+    const long q = G.at(k, i, j);
+    const REAL pp = x[q];
+    const REAL dp = (w.d1[w.o(k)] - pp) * omg * msk[q];
+    x[q] = pp + dp;
+    if (tmp) tmp[k + 1] = tmp[k + 1] + dp * dp;
+    acc.add(dp * dp);
+  }
+}
+
+// flop formulas cz_maf.f90:493-505 (all exact small integers)
+double pcr_maf_flop(const Range& R, int pn, double per2) {
+  const double nk = R.ked - R.kst + 1;
+  const double lines = (double)(R.jed - R.jst + 1) * (double)(R.ied - R.ist + 1);
+  return lines * ((24.0 + 3.0 * 2.0 + 12.0) + nk * (11.0 + 10.0) + (nk - 2.0) * 6.0 + nk * (pn - 1) * 16.0 +
+                  ipow2(pn - 1) * per2 + nk * 6.0);
+}
+
+// The five MAF line routines add every dp*dp TWICE: once into res1 and once into tmp(k), and
+// tmp is summed into res1 at the end (cz_maf.f90:635-636, 657-660).  Double mode: 2 * sum;
+// real mode: the reference's 1-thread REAL accumulation order.
+void pcr_maf_sweep(int* sz, int* idx, int* g, int pn, int color /* <0: all lines, (j,i) order */, REAL* x,
+                   REAL* msk, REAL* rhs, REAL* XX, REAL* YY, REAL* ZZ, REAL omg, double* res, REAL* tmp) {
+  const Grid G(sz, *g);
+  const Range R(idx);
+  for (int k = 0; k < sz[2] + 4; ++k) tmp[k] = (REAL)0;                // "tmp = 0.0"
+  if (real_mode() || color < 0) {
+    Acc acc;
+    LineWork w(R.kst, R.ked, pn);
+    const bool rm = real_mode();
+    for (int j = R.jst; j <= R.jed; ++j)
+      for (int i = R.ist; i <= R.ied; ++i) {
+        if (color >= 0 && ((i + j) % 2 + 2) % 2 != color) continue;
+        solve_line_maf(w, G, x, rhs, msk, XX, YY, ZZ, i, j, pn, omg, acc, rm ? tmp : nullptr);
+      }
+    if (rm) {
+      REAL r1 = acc.r;
+      for (int k = R.kst; k <= R.ked; ++k) r1 = r1 + tmp[k + 1];
+      *res += (double)r1;
+    } else {
+      *res += 2.0 * acc.value();
+    }
+    return;
+  }
+  const double s = reduce_planes(R.jst, R.jed, true, [&](int j, Acc& acc) {
+    LineWork w(R.kst, R.ked, pn);
+    for (int i = R.ist; i <= R.ied; ++i) {
+      if (((i + j) % 2 + 2) % 2 != color) continue;
+      solve_line_maf(w, G, x, rhs, msk, XX, YY, ZZ, i, j, pn, omg, acc, nullptr);
+    }
+  });
+  *res += 2.0 * s;
+}
+
+}  // namespace
+
+extern "C" {
+
+// ------------------------------------------------------------------ cz_maf.f90:131-282
+void jacobi_maf_(REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z, REAL* omg, REAL* b,
+                 double* res, REAL* wk2, REAL* tmp, double* flop) {
+  (void)tmp;   // used only under _SVR
+  const Grid G(sz, *g);
+  const Range R(idx);
+  const REAL w = *omg;
+  *flop += 66.0 * R.cells();
+  const double s = reduce_planes(R.jst, R.jed, true, [&](int j, Acc& acc) {
+    for (int i = R.ist; i <= R.ied; ++i)
+      for (int k = R.kst; k <= R.ked; ++k) {
+        const long q = G.at(k, i, j);
+        const REAL bb = b[q], pp = p[q];
+        const MafCell m = maf_cell(X, Y, Z, i, j, k);
+        const REAL dp = maf_point_dp(m, G, p, q, bb, pp, w);
+        wk2[q] = pp + dp;
+        acc.add(dp * dp);
+      }
+  });
+  for_planes(R.jst, R.jed, [&](int j) {   // :258-264 copy-back
+    for (int i = R.ist; i <= R.ied; ++i) {
+      const long q = G.at(0, i, j);
+      for (int k = R.kst; k <= R.ked; ++k) p[q + k] = wk2[q + k];
+    }
+  });
+  *res += s;
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:23-114
+// Lexicographic, racy under OpenMP in the reference -> 1-thread order.
+void psor_maf_(REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z, REAL* omg, REAL* b,
+               double* res, double* flop) {
+  const Grid G(sz, *g);
+  const Range R(idx);
+  const REAL w = *omg;
+  *flop += 66.0 * R.cells();
+  Acc acc;
+  for (int j = R.jst; j <= R.jed; ++j)
+    for (int i = R.ist; i <= R.ied; ++i)
+      for (int k = R.kst; k <= R.ked; ++k) {
+        const long q = G.at(k, i, j);
+        const REAL bb = b[q], pp = p[q];
+        const MafCell m = maf_cell(X, Y, Z, i, j, k);
+        const REAL dp = maf_point_dp(m, G, p, q, bb, pp, w);
+        p[q] = pp + dp;
+        acc.add(dp * dp);
+      }
+  *res += acc.value();
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:301-438
+void psor2sma_core_maf_(REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z, int* ofst,
+                        int* color, REAL* omg, REAL* b, double* res, REAL* tmp, double* flop) {
+  (void)tmp;   // used only under _SVR
+  const Grid G(sz, *g);
+  const Range R(idx);
+  const REAL w = *omg;
+  const int kp = *ofst + *color;
+  *flop += 66.0 * 0.5 * R.cells();
+  const double s = reduce_planes(R.jst, R.jed, true, [&](int j, Acc& acc) {
+    for (int i = R.ist; i <= R.ied; ++i)
+      for (int k = R.kst + ((i + j + kp) % 2 + 2) % 2; k <= R.ked; k += 2) {
+        const long q = G.at(k, i, j);
+        const REAL pp = p[q], bb = b[q];
+        const MafCell m = maf_cell(X, Y, Z, i, j, k);
+        const REAL dp = maf_point_dp(m, G, p, q, bb, pp, w);
+        p[q] = pp + dp;
+        acc.add(dp * dp);
+      }
+  });
+  *res += s;
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:442-668
+void pcr_rb_maf_(int* sz, int* idx, int* g, int* pn, int* ofst, int* color, REAL* x, REAL* msk,
+                 REAL* rhs, REAL* XX, REAL* YY, REAL* ZZ, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
+                 REAL* omg, double* res, REAL* tmp, double* flop) {
+  (void)ofst;   // ip = ofst + color is computed but not used (:507, 526)
+  *flop += pcr_maf_flop(Range(idx), *pn, 11.0) * 0.5;
+  pcr_maf_sweep(sz, idx, g, *pn, *color, x, msk, rhs, XX, YY, ZZ, *omg, res, tmp);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:1339-1560
+void pcr_rb_esa_maf_(int* sz, int* idx, int* g, int* pn, int* ofst, int* color, int* s, REAL* x,
+                     REAL* msk, REAL* rhs, REAL* XX, REAL* YY, REAL* ZZ, REAL*, REAL*, REAL*, REAL*,
+                     REAL*, REAL*, REAL* omg, double* res, REAL* tmp, double* flop) {
+  (void)ofst; (void)s;
+  *flop += pcr_maf_flop(Range(idx), *pn, 11.0) * 0.5;
+  pcr_maf_sweep(sz, idx, g, *pn, *color, x, msk, rhs, XX, YY, ZZ, *omg, res, tmp);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:672-892
+// All lines in (j,i) order, in place: racy under OpenMP in the reference -> 1-thread order.
+void pcr_maf_(int* sz, int* idx, int* g, int* pn, REAL* x, REAL* msk, REAL* rhs, REAL* XX, REAL* YY,
+              REAL* ZZ, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL* omg, double* res, REAL* tmp,
+              double* flop) {
+  *flop += pcr_maf_flop(Range(idx), *pn, 11.0);
+  pcr_maf_sweep(sz, idx, g, *pn, -1, x, msk, rhs, XX, YY, ZZ, *omg, res, tmp);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:896-1113
+// Allocates a,c,d(kst-2^(pn-2) : ked+2^(pn-2)) itself; the 2x2 stage reads a(k+2^(pn-1)), which
+// lies inside that allocation only when n >= 3*2^(pn-2) (true for the driver's 2^m-2 sizes).
+void pcr_eda_maf_(int* sz, int* idx, int* g, int* pn, REAL* x, REAL* msk, REAL* rhs, REAL* XX,
+                  REAL* YY, REAL* ZZ, REAL*, REAL*, REAL*, REAL* omg, double* res, REAL* tmp,
+                  double* flop) {
+  *flop += pcr_maf_flop(Range(idx), *pn, 9.0);
+  pcr_maf_sweep(sz, idx, g, *pn, -1, x, msk, rhs, XX, YY, ZZ, *omg, res, tmp);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:1117-1335
+void pcr_esa_maf_(int* sz, int* idx, int* g, int* pn, int* s, REAL* x, REAL* msk, REAL* rhs, REAL* XX,
+                  REAL* YY, REAL* ZZ, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL* omg, double* res,
+                  REAL* tmp, double* flop) {
+  (void)s;
+  *flop += pcr_maf_flop(Range(idx), *pn, 9.0);
+  pcr_maf_sweep(sz, idx, g, *pn, -1, x, msk, rhs, XX, YY, ZZ, *omg, res, tmp);
+}
+
+// ------------------------------------------------------------------ cz_blas.f90:738-829
+void calc_rk_maf_(REAL* r, REAL* p, REAL* b, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z,
+                  REAL* pvt, double* flop) {
+  const Grid G(sz, *g);
+  const Range R(idx);
+  const REAL half = (REAL)0.5;
+  const long pl = G.nk * G.ni;
+  *flop += 63.0 * R.cells();
+  for_planes(R.jst, R.jed, [&](int j) {
+    for (int i = R.ist; i <= R.ied; ++i)
+      for (int k = R.kst; k <= R.ked; ++k) {
+        const long q = G.at(k, i, j);
+        const MafCell m = maf_cell(X, Y, Z, i, j, k);
+        r[q] = (b[q] + (REAL)2.0 * (m.C1 + m.C2 + m.C3) * p[q] - (m.C1 + half * m.C7) * p[q + G.nk] -
+                (m.C1 - half * m.C7) * p[q - G.nk] - (m.C2 + half * m.C8) * p[q + pl] -
+                (m.C2 - half * m.C8) * p[q - pl] - (m.C3 + half * m.C9) * p[q + 1] -
+                (m.C3 - half * m.C9) * p[q - 1]) * pvt[q];
+      }
+  });
+}
+
+// ------------------------------------------------------------------ cz_blas.f90:845-935
+void calc_ax_maf_(REAL* ap, REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z, REAL* pvt,
+                  double* flop) {
+  const Grid G(sz, *g);
+  const Range R(idx);
+  const REAL half = (REAL)0.5;
+  const long pl = G.nk * G.ni;
+  *flop += 63.0 * R.cells();
+  for_planes(R.jst, R.jed, [&](int j) {
+    for (int i = R.ist; i <= R.ied; ++i)
+      for (int k = R.kst; k <= R.ked; ++k) {
+        const long q = G.at(k, i, j);
+        const MafCell m = maf_cell(X, Y, Z, i, j, k);
+        ap[q] = ((m.C1 + half * m.C7) * p[q + G.nk] + (m.C1 - half * m.C7) * p[q - G.nk] +
+                 (m.C2 + half * m.C8) * p[q + pl] + (m.C2 - half * m.C8) * p[q - pl] +
+                 (m.C3 + half * m.C9) * p[q + 1] + (m.C3 - half * m.C9) * p[q - 1] -
+                 (REAL)2.0 * (m.C1 + m.C2 + m.C3) * p[q]) * pvt[q];
+      }
+  });
+}
 
 }  // extern "C"

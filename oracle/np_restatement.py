@@ -266,3 +266,208 @@ def blas_bicg_2(z, x, y, a, b, idx):
     t = z.dtype.type
     sl = _rng(idx)
     z[sl] = t(a) * x[sl] + t(b) * y[sl] + z[sl]
+
+
+# ======================================================================================================
+# Stretched-grid ("MAF") twins, src/cz_f90/cz_maf.f90 and cz_blas.f90:738-1039.  Coordinate arrays are the
+# Fortran X(-1:sz(1)+2) etc.: Fortran index m -> C offset m + 1.
+# ======================================================================================================
+def _maf_metrics(X, Y, Z, idx):
+    """C1, C2, C3, C7, C8, C9 of every inner cell as [j][i][k] arrays, cz_maf.f90:70-99 statement by statement;
+    the products involve factors from all three axes, so every cell rounds on its own."""
+    t = X.dtype.type
+    ist, ied, jst, jed, kst, ked = idx
+    i = np.arange(ist, ied + 1)[None, :, None]
+    j = np.arange(jst, jed + 1)[:, None, None]
+    k = np.arange(kst, ked + 1)[None, None, :]
+    half, two, one = t(0.5), t(2.0), t(1.0)
+    XG = half * (X[i + 2] - X[i]); YE = half * (Y[j + 2] - Y[j]); ZT = half * (Z[k + 2] - Z[k])
+    XGG = X[i + 2] - two * X[i + 1] + X[i]
+    YEE = Y[j + 2] - two * Y[j + 1] + Y[j]
+    ZTT = Z[k + 2] - two * Z[k + 1] + Z[k]
+    YJA = XG * YE * ZT
+    YJAI = one / YJA
+    GX = YE * ZT * YJAI; EY = XG * ZT * YJAI; TZ = XG * YE * YJAI
+    C1 = GX * GX; C2 = EY * EY; C3 = TZ * TZ
+    C7 = -XGG * C1 * GX; C8 = -YEE * C2 * EY; C9 = -ZTT * C3 * TZ
+    return C1, C2, C3, C7, C8, C9
+
+
+def _maf_offdiag(p, sl, m):
+    """(C1+.5C7) p(i+1) + (C1-.5C7) p(i-1) + (C2+.5C8) p(j+1) + (C2-.5C8) p(j-1) + (C3+.5C9) p(k+1) + (C3-.5C9) p(k-1),
+    left to right (cz_maf.f90:103-108)."""
+    C1, C2, C3, C7, C8, C9 = m
+    h = p.dtype.type(0.5)
+    s = (C1 + h * C7) * p[_shift(sl, di=1)]
+    s = s + (C1 - h * C7) * p[_shift(sl, di=-1)]
+    s = s + (C2 + h * C8) * p[_shift(sl, dj=1)]
+    s = s + (C2 - h * C8) * p[_shift(sl, dj=-1)]
+    s = s + (C3 + h * C9) * p[_shift(sl, dk=1)]
+    s = s + (C3 - h * C9) * p[_shift(sl, dk=-1)]
+    return s
+
+
+def _maf_dp(p, b, sl, m, omg):
+    t = p.dtype.type
+    dd = t(2.0) * (m[0] + m[1] + m[2])                     # :102
+    rp = _maf_offdiag(p, sl, m) + b[sl]                    # :103-109, the source term is ADDED
+    return (rp / dd - p[sl]) * t(omg)                      # :110
+
+
+def jacobi_maf(p, b, idx, X, Y, Z, omg):
+    """cz_maf.f90:131-282."""
+    sl = _rng(idx)
+    dp = _maf_dp(p, b, sl, _maf_metrics(X, Y, Z, idx), omg)
+    p[sl] = p[sl] + dp
+    return float(np.sum((dp * dp).astype(np.float64)))
+
+
+def psor2sma_core_maf(p, b, idx, X, Y, Z, ofst, color, omg):
+    """cz_maf.f90:301-438."""
+    ist, ied, jst, jed, kst, ked = idx
+    sl = _rng(idx)
+    kp = ofst + color
+    jj, ii, kk = np.meshgrid(np.arange(jst, jed + 1), np.arange(ist, ied + 1), np.arange(kst, ked + 1), indexing="ij")
+    sel = ((kk - kst) % 2) == ((ii + jj + kp) % 2)
+    dp = _maf_dp(p, b, sl, _maf_metrics(X, Y, Z, idx), omg)
+    p[sl] = np.where(sel, p[sl] + dp, p[sl])
+    return float(np.sum((dp[sel] * dp[sel]).astype(np.float64)))
+
+
+def psor_maf(p, b, idx, X, Y, Z, omg):
+    """cz_maf.f90:23-114: lexicographic, cell by cell in (j, i, k) order (scalar loop: small grids only)."""
+    t = p.dtype.type
+    ist, ied, jst, jed, kst, ked = idx
+    o = G - 1
+    C1, C2, C3, C7, C8, C9 = _maf_metrics(X, Y, Z, idx)
+    h, two, om = t(0.5), t(2.0), t(omg)
+    res = 0.0
+    for j in range(jst, jed + 1):
+        for i in range(ist, ied + 1):
+            for k in range(kst, ked + 1):
+                q = (j - jst, i - ist, k - kst)
+                c1, c2, c3, c7, c8, c9 = C1[q], C2[q], C3[q], C7[q], C8[q], C9[q]
+                J, I, K = j + o, i + o, k + o
+                pp = p[J, I, K]
+                dd = two * (c1 + c2 + c3)
+                rp = (c1 + h * c7) * p[J, I + 1, K]
+                rp = rp + (c1 - h * c7) * p[J, I - 1, K]
+                rp = rp + (c2 + h * c8) * p[J + 1, I, K]
+                rp = rp + (c2 - h * c8) * p[J - 1, I, K]
+                rp = rp + (c3 + h * c9) * p[J, I, K + 1]
+                rp = rp + (c3 - h * c9) * p[J, I, K - 1]
+                rp = rp + b[J, I, K]
+                dp = (rp / dd - pp) * om
+                p[J, I, K] = pp + dp
+                res += float(dp * dp)
+    return res
+
+
+def calc_ax_maf(ap, p, idx, X, Y, Z, pvt):
+    """cz_blas.f90:845-935."""
+    t = p.dtype.type
+    sl = _rng(idx)
+    m = _maf_metrics(X, Y, Z, idx)
+    ap[sl] = (_maf_offdiag(p, sl, m) - t(2.0) * (m[0] + m[1] + m[2]) * p[sl]) * pvt[sl]
+
+
+def calc_rk_maf(r, p, b, idx, X, Y, Z, pvt):
+    """cz_blas.f90:738-829: b + 2(C1+C2+C3) p - ... , each neighbour product subtracted in turn."""
+    t = p.dtype.type
+    sl = _rng(idx)
+    C1, C2, C3, C7, C8, C9 = _maf_metrics(X, Y, Z, idx)
+    h = t(0.5)
+    s = b[sl] + t(2.0) * (C1 + C2 + C3) * p[sl]
+    s = s - (C1 + h * C7) * p[_shift(sl, di=1)]
+    s = s - (C1 - h * C7) * p[_shift(sl, di=-1)]
+    s = s - (C2 + h * C8) * p[_shift(sl, dj=1)]
+    s = s - (C2 - h * C8) * p[_shift(sl, dj=-1)]
+    s = s - (C3 + h * C9) * p[_shift(sl, dk=1)]
+    s = s - (C3 - h * C9) * p[_shift(sl, dk=-1)]
+    r[sl] = s * pvt[sl]
+
+
+def search_pivot(pvt, idx, X, Y, Z):
+    """cz_blas.f90:947-1039: reciprocal of the largest |coefficient| of the row."""
+    t = X.dtype.type
+    C1, C2, C3, C7, C8, C9 = _maf_metrics(X, Y, Z, idx)
+    h = t(0.5)
+    cand = [np.abs(C1 + h * C7), np.abs(C1 - h * C7), np.abs(C2 + h * C8), np.abs(C2 - h * C8),
+            np.abs(C3 + h * C9), np.abs(C3 - h * C9), np.abs(t(2.0) * (C1 + C2 + C3))]
+    ss = cand[0]
+    for c in cand[1:]:
+        ss = np.maximum(ss, c)
+    pvt[_rng(idx)] = t(1.0) / ss
+
+
+def _relax_lines_maf(x, msk, rhs, idx, pn, omg, jc, ic, XX, YY, ZZ):
+    """One batch of MAF lines (jc, ic) (C indices), cz_maf.f90:522-647: line-dependent coefficients a, c are carried
+    through the PCR stages next to d; pn-1 stages + 2x2 in all five MAF line routines."""
+    t = x.dtype.type
+    kst, ked = idx[4], idx[5]
+    o = G - 1
+    n = ked - kst + 1
+    L = len(jc)
+    half, two, one = t(0.5), t(2.0), t(1.0)
+    fi = ic - o; fj = jc - o                               # Fortran i, j of each line
+    GX = two / (XX[fi + 2] - XX[fi]); EY = two / (YY[fj + 2] - YY[fj])
+    C1 = GX * GX; C2 = EY * EY
+    C7 = -(XX[fi + 2] - two * XX[fi + 1] + XX[fi]) * C1 * GX
+    C8 = -(YY[fj + 2] - two * YY[fj + 1] + YY[fj]) * C2 * EY
+    dd1 = (C1 + half * C7)[:, None]; dd2 = (C1 - half * C7)[:, None]
+    cc1 = (C2 + half * C8)[:, None]; cc2 = (C2 - half * C8)[:, None]
+    fk = np.arange(kst, ked + 1)
+    f1 = ZZ[fk + 2]; f2 = ZZ[fk]
+    TZ = two / (f1 - f2)
+    ZTT = f1 - two * ZZ[fk + 1] + f2
+    f3 = TZ * TZ
+    aw = np.broadcast_to(f3[None, :], (L, n))              # C3
+    cw = np.broadcast_to((-ZTT * f3 * TZ)[None, :], (L, n))   # C9
+    dw = half / ((C1 + C2)[:, None] + f3[None, :])         # 1/R7
+    s = 2 ** (pn - 1)
+    P = 2 * s
+    a = np.zeros((L, n + 2 * P), dtype=x.dtype); c = np.zeros_like(a); d = np.zeros_like(a)
+    av = -(aw - half * cw) * dw; cv = -(aw + half * cw) * dw
+    a[:, P:P + n] = av; c[:, P:P + n] = cv
+    a[:, P] = 0; c[:, P + n - 1] = 0                       # :545, :557
+    ks = slice(kst + o, ked + o + 1)
+    mk = msk[jc, ic, ks]
+    dk = (dd1 * x[jc, ic + 1, ks] + dd2 * x[jc, ic - 1, ks] + cc1 * x[jc + 1, ic, ks] + cc2 * x[jc - 1, ic, ks]
+          - rhs[jc, ic, ks]) * dw * mk                     # :560-568, the source term is SUBTRACTED here
+    dk[:, 0] = (dk[:, 0] + (aw[:, 0] - half * cw[:, 0]) * dw[:, 0] * x[jc, ic, kst + o - 1]) * mk[:, 0]
+    dk[:, n - 1] = (dk[:, n - 1] + (aw[:, n - 1] + half * cw[:, n - 1]) * dw[:, n - 1] * x[jc, ic, ked + o + 1]) * mk[:, n - 1]
+    d[:, P:P + n] = dk
+    k = np.arange(P, P + n)
+    for p in range(1, pn):                                 # :580-601
+        q = 2 ** (p - 1)
+        ap = a[:, k]; cp = c[:, k]
+        e = one / (one - ap * c[:, k - q] - cp * a[:, k + q])
+        a1 = -e * ap * a[:, k - q]
+        c1 = -e * cp * c[:, k + q]
+        d1 = e * (d[:, k] - ap * d[:, k - q] - cp * d[:, k + q])
+        a[:, k] = a1; c[:, k] = c1; d[:, k] = d1
+    k = np.arange(P, P + s)                                # :605-620
+    cc = c[:, k]; aa = a[:, k + s]; g1 = d[:, k]; g2 = d[:, k + s]
+    jj = one / (one - aa * cc)
+    sol = np.zeros_like(d)
+    sol[:, k] = (g1 - cc * g2) * jj
+    sol[:, k + s] = (g2 - aa * g1) * jj
+    pp = x[jc, ic, ks]
+    dp = (sol[:, P:P + n] - pp) * t(omg) * mk              # :630-637
+    x[jc, ic, ks] = pp + dp
+    return 2.0 * float(np.sum((dp * dp).astype(np.float64)))   # every dp*dp is added to res1 AND tmp(k): :635-636, 657-660
+
+
+def pcr_rb_maf(x, msk, rhs, idx, pn, color, omg, XX, YY, ZZ):
+    """cz_maf.f90:442-668 (and pcr_rb_esa_maf :1339-1560, same arithmetic on padded arrays)."""
+    jc, ic = _lines(idx, color)
+    return _relax_lines_maf(x, msk, rhs, idx, pn, omg, jc, ic, XX, YY, ZZ)
+
+
+def pcr_maf(x, msk, rhs, idx, pn, omg, XX, YY, ZZ):
+    """cz_maf.f90:672-892 (pcr_eda_maf :896-1113, pcr_esa_maf :1117-1335: same arithmetic): lines in (j, i) order."""
+    jc, ic = _lines(idx)
+    res = 0.0
+    for q in range(len(jc)):
+        res += _relax_lines_maf(x, msk, rhs, idx, pn, omg, jc[q:q + 1], ic[q:q + 1], XX, YY, ZZ)
+    return res

@@ -41,6 +41,21 @@ CASES = [
     ("f32", 64, "sor2sma", 4000, "1.9", None),
     ("f32", 64, "pbicgstab", 400, "1.1", "sor2sma"),
     ("f32", 64, "pcr_rb", 4000, "1.8", None),
+    # stretched-grid (MAF) twins on the driver's uniform mesh
+    ("f32", 32, "jacobi_maf", 2000, "0.8", None),
+    ("f32", 32, "sor2sma_maf", 2000, "1.5", None),
+    ("f32", 32, "psor_maf", 2000, "1.5", None),
+    ("f32", 32, "pcr_rb_maf", 2000, "1.5", None),
+    ("f32", 32, "pcr_rb_esa_maf", 2000, "1.5", None),
+    ("f32", 32, "pcr_maf", 2000, "1.5", None),
+    ("f32", 32, "pcr_eda_maf", 2000, "1.5", None),
+    ("f32", 32, "pcr_esa_maf", 2000, "1.5", None),
+    ("f32", 32, "pbicgstab_maf", 200, "1.1", "sor2sma_maf"),
+    ("f32", 32, "pbicgstab_maf", 200, "1.1", "pcr_rb_maf"),
+    ("f32", 32, "pbicgstab_maf", 200, "1.1", "none"),
+    ("f64", 32, "sor2sma_maf", 2000, "1.5", None),
+    ("f64", 32, "pcr_rb_maf", 2000, "1.5", None),
+    ("f64", 32, "pbicgstab_maf", 200, "1.1", "sor2sma_maf"),
 ]
 
 

@@ -156,16 +156,86 @@ class OracleCZ:
         else:
             raise ValueError(kind)
 
+    # ---- stretched-grid (MAF) twins, cz_maf.f90 / cz_blas.f90:738-1039 --------------------------------
+    def mesh(self, stretch=0.0):
+        """xc, yc, zc as the reference driver sets them (cz_Evaluate.cpp:342-362): (REAL)(i-1)*pitch for the C index
+        i = 0..size+3 (= Fortran X(-1:sz+2)); stretch > 0 adds a smooth monotone perturbation for kernel tests."""
+        out = []
+        for a in range(3):
+            n = self.sz[a] + 2 * GUIDE
+            i = np.arange(n)
+            x = ((i - 1).astype(self.dt) * self.pitch).astype(self.dt)
+            if stretch:
+                x = (x + self.dt(stretch) * self.pitch * np.sin(self.dt(0.37 + a) * i.astype(self.dt))).astype(self.dt)
+            out.append(np.ascontiguousarray(x))
+        return out
+
+    def pivot(self, mesh):
+        pvt = self.zeros()
+        self.dll.search_pivot_(ptr(pvt), self._sz, self._idx, self.g(), ptr(mesh[0]), ptr(mesh[1]), ptr(mesh[2]))
+        return pvt
+
+    def sweep_maf(self, kind, X, B, res, mesh, ip=0):
+        """One iteration of the MAF twin `kind` (jacobi_maf, psor_maf, sor2sma_maf, pcr_rb_maf, pcr_rb_esa_maf,
+        pcr_maf, pcr_eda_maf, pcr_esa_maf) with the argument lists of cz_Poisson.cpp:50,112,197,565,689,778,861,966."""
+        d = self.dll
+        flop = C.c_double(0); om = self.creal(self.ac1); cip = C.c_int(ip)
+        xc, yc, zc = [ptr(m) for m in mesh]
+        tmp = np.zeros(self.sz[2] + 2 * GUIDE, dtype=self.dt)
+        if kind == "jacobi_maf":
+            if self.WRK is None:
+                self.WRK = self.zeros()
+            d.jacobi_maf_(ptr(X), self._sz, self._idx, self.g(), xc, yc, zc, C.byref(om), ptr(B), C.byref(res),
+                          ptr(self.WRK), ptr(tmp), C.byref(flop))
+            return
+        if kind == "psor_maf":
+            d.psor_maf_(ptr(X), self._sz, self._idx, self.g(), xc, yc, zc, C.byref(om), ptr(B), C.byref(res),
+                        C.byref(flop))
+            return
+        if kind == "sor2sma_maf":
+            for color in (0, 1):
+                cc = C.c_int(color)
+                d.psor2sma_core_maf_(ptr(X), self._sz, self._idx, self.g(), xc, yc, zc, C.byref(cip), C.byref(cc),
+                                     C.byref(om), ptr(B), C.byref(res), ptr(tmp), C.byref(flop))
+            return
+        n = self.idx[5] - self.idx[4] + 1
+        pn = C.c_int(get_num_stage(n)); s = C.c_int(2 ** (pn.value - 2))
+        M = self.mask(); w = [ptr(a) for a in self.work1d]
+        head = (self._sz, self._idx, self.g(), C.byref(pn))
+        tail = (C.byref(om), C.byref(res), ptr(tmp), C.byref(flop))
+        if kind == "pcr_rb_maf":
+            for color in (0, 1):
+                cc = C.c_int(color)
+                d.pcr_rb_maf_(*head, C.byref(cip), C.byref(cc), ptr(X), ptr(M), ptr(B), xc, yc, zc, *w, *tail)
+        elif kind == "pcr_rb_esa_maf":
+            for color in (0, 1):
+                cc = C.c_int(color)
+                d.pcr_rb_esa_maf_(*head, C.byref(cip), C.byref(cc), C.byref(s), ptr(X), ptr(M), ptr(B), xc, yc, zc, *w,
+                                  *tail)
+        elif kind == "pcr_maf":
+            d.pcr_maf_(*head, ptr(X), ptr(M), ptr(B), xc, yc, zc, *w, *tail)
+        elif kind == "pcr_eda_maf":
+            d.pcr_eda_maf_(*head, ptr(X), ptr(M), ptr(B), xc, yc, zc, *w[:3], *tail)
+        elif kind == "pcr_esa_maf":
+            d.pcr_esa_maf_(*head, C.byref(s), ptr(X), ptr(M), ptr(B), xc, yc, zc, *w, *tail)
+        else:
+            raise ValueError(kind)
+
     # ---- loops (cz_Poisson.cpp) ------------------------------------------------------------
-    def stationary(self, kind, X, B, itr_max, coef, converge_check=True):
-        """CZ::JACOBI/PSOR/RBSOR/LSOR_PCR_*: returns (itr, res, history)."""
+    def stationary(self, kind, X, B, itr_max, coef, converge_check=True, mesh=None):
+        """CZ::JACOBI/PSOR/RBSOR/LSOR_PCR_*: returns (itr, res, history).  `*_maf` kinds use `mesh` (default: the
+        driver's uniform mesh)."""
         self.ac1 = self.dt(coef)
+        if kind.endswith("_maf") and mesh is None:
+            mesh = self.mesh()
         hist = []
         res_v = 0.0
         itr = 1
         while itr <= itr_max:
             res = C.c_double(0.0)
-            if kind == "jacobi":
+            if kind.endswith("_maf"):
+                self.sweep_maf(kind, X, B, res, mesh)
+            elif kind == "jacobi":
                 self.sweep_jacobi(X, B, res)
             elif kind == "sor2sma":
                 self.sweep_rb(X, B, res)
@@ -192,19 +262,32 @@ class OracleCZ:
         self.dll.blas_dot2_(C.byref(r), ptr(x), ptr(y), self._sz, self._idx, self.g(), C.byref(flop))
         return self.dt(r.value)
 
-    def precond(self, xx, bb, pc):
-        if pc in ("jacobi", "psor", "sor2sma", "pcr", "pcr_eda", "pcr_rb", "pcr_rb_esa"):
-            self.stationary(pc, xx, bb, 8, self.ac1, converge_check=False)
+    def precond(self, xx, bb, pc, mesh=None):
+        if pc in ("jacobi", "psor", "sor2sma", "pcr", "pcr_eda", "pcr_rb", "pcr_rb_esa",
+                  "jacobi_maf", "psor_maf", "sor2sma_maf", "pcr_maf", "pcr_eda_maf", "pcr_rb_maf", "pcr_rb_esa_maf"):
+            self.stationary(pc, xx, bb, 8, self.ac1, converge_check=False, mesh=mesh)   # cz_Poisson.cpp:282-317
         else:
             xx[...] = bb
 
-    def pbicgstab(self, X, B, itr_max, coef, pc):
-        """CZ::PBiCGSTAB (cz_Poisson.cpp:332-504): returns (itr, res, history)."""
+    def pbicgstab(self, X, B, itr_max, coef, pc, maf=False, mesh=None):
+        """CZ::PBiCGSTAB (cz_Poisson.cpp:332-504): returns (itr, res, history).  maf: pbicgstab_maf, i.e.
+        calc_rk_maf / calc_ax_maf scaled by pvt (:350-358, 415-419, 451-455)."""
         self.ac1 = self.dt(coef)
         d = self.dll; dt = self.dt
         flop = C.c_double(0)
         p, p_, r, r0, q, s, s_, t_ = [self.zeros() for _ in range(8)]
-        d.blas_calc_rk_(ptr(r), ptr(X), ptr(B), self._sz, self._idx, self.g(), ptr(self.cf), C.byref(flop))
+        if maf:
+            mesh = mesh if mesh is not None else self.mesh()
+            pvt = self.pivot(mesh)
+            mp = [ptr(m) for m in mesh]
+
+            def apply_ax(out, v):
+                d.calc_ax_maf_(ptr(out), ptr(v), self._sz, self._idx, self.g(), *mp, ptr(pvt), C.byref(flop))
+            d.calc_rk_maf_(ptr(r), ptr(X), ptr(B), self._sz, self._idx, self.g(), *mp, ptr(pvt), C.byref(flop))
+        else:
+            def apply_ax(out, v):
+                d.blas_calc_ax_(ptr(out), ptr(v), self._sz, self._idx, self.g(), ptr(self.cf), C.byref(flop))
+            d.blas_calc_rk_(ptr(r), ptr(X), ptr(B), self._sz, self._idx, self.g(), ptr(self.cf), C.byref(flop))
         r0[...] = r
         rho_old, alpha, omega = dt(1.0), dt(0.0), dt(1.0)
         hist = []; res_v = 0.0
@@ -222,14 +305,14 @@ class OracleCZ:
                 d.blas_bicg_1_(ptr(p), ptr(r), ptr(q), C.byref(cb), C.byref(co), self._sz, self._idx, self.g(),
                                C.byref(flop))
             p_[...] = 0
-            self.precond(p_, p, pc)
-            d.blas_calc_ax_(ptr(q), ptr(p_), self._sz, self._idx, self.g(), ptr(self.cf), C.byref(flop))
+            self.precond(p_, p, pc, mesh)
+            apply_ax(q, p_)
             alpha = dt(rho / self.dot2(q, r0))
             ra = self.creal(-alpha)
             d.blas_triad_(ptr(s), ptr(q), ptr(r), C.byref(ra), self._sz, self._idx, self.g(), C.byref(flop))
             s_[...] = 0
-            self.precond(s_, s, pc)
-            d.blas_calc_ax_(ptr(t_), ptr(s_), self._sz, self._idx, self.g(), ptr(self.cf), C.byref(flop))
+            self.precond(s_, s, pc, mesh)
+            apply_ax(t_, s_)
             omega = dt(self.dot2(t_, s) / self.dot1(t_))
             ca, co = self.creal(alpha), self.creal(omega)
             d.blas_bicg_2_(ptr(X), ptr(p_), ptr(s_), C.byref(ca), C.byref(co), self._sz, self._idx, self.g(),

@@ -197,3 +197,103 @@ def test_port_equals_numpy_restatement_psor_and_blas1(real):
     Zo = Z.copy(); o.dll.blas_bicg_2_(ou.ptr(Zo), ou.ptr(X), ou.ptr(Y), C.byref(a), C.byref(b), o._sz, o._idx, o.g(), C.byref(flop))
     Zn = Z.copy(); npr.blas_bicg_2(Zn, X, Y, a.value, b.value, o.idx)
     assert np.array_equal(Zo, Zn)
+
+
+# ---- stretched-grid (MAF) twins, SURVEY.md §8f-2: cz_maf.f90, cz_blas.f90:738-1039 ----------------------------
+MAF_CASES = [("f32", 32, "jacobi_maf", None), ("f32", 32, "sor2sma_maf", None), ("f32", 32, "psor_maf", None),
+             ("f32", 32, "pcr_rb_maf", None), ("f32", 32, "pcr_rb_esa_maf", None), ("f32", 32, "pcr_maf", None),
+             ("f32", 32, "pcr_eda_maf", None), ("f32", 32, "pcr_esa_maf", None),
+             ("f32", 32, "pbicgstab_maf", "sor2sma_maf"), ("f32", 32, "pbicgstab_maf", "pcr_rb_maf"),
+             ("f32", 32, "pbicgstab_maf", "none"),
+             ("f64", 32, "sor2sma_maf", None), ("f64", 32, "pcr_rb_maf", None), ("f64", 32, "pbicgstab_maf", "sor2sma_maf")]
+
+
+@pytest.mark.parametrize("real,n,solver,precond", MAF_CASES)
+def test_python_loops_reproduce_reference_driver_history_maf(real, n, solver, precond):
+    g = _golden(real, n, solver, precond)
+    o = ou.OracleCZ([n] * 3, real)
+    P, RHS = o.setup_laplace()
+    if solver == "pbicgstab_maf":
+        itr, res, hist = o.pbicgstab(P, RHS, g["itr_max"], float(g["coef"]), precond, maf=True)
+    else:
+        itr, res, hist = o.stationary(solver, P, RHS, g["itr_max"], float(g["coef"]))
+    assert itr == g["itr"]
+    assert ["%13.6e" % h for h in hist] == ["%13s" % h for h in g["history"]]
+
+
+def test_maf_twins_on_the_uniform_mesh_reproduce_the_plain_solvers():
+    """What pins the MAF port: on the driver's uniform mesh the metric coefficients are 1/h^2 up to rounding, so the
+    reference's own runs of X_maf must track X (golden histories written by the unmodified reference driver)."""
+    for real, solver, rel in (("f32", "jacobi", 1e-3), ("f32", "sor2sma", 1e-3), ("f32", "psor", 1e-3), ("f64", "sor2sma", 1e-9)):
+        a, b = _golden(real, 32, solver), _golden(real, 32, solver + "_maf")
+        assert a["itr"] == b["itr"]
+        np.testing.assert_allclose([float(h) for h in b["history"]], [float(h) for h in a["history"]], rtol=rel)
+    # the five MAF line routines add every dp^2 twice (cz_maf.f90:635-636, 657-660): residuals are sqrt(2) larger
+    a, b = _golden("f64", 32, "pcr_rb"), _golden("f64", 32, "pcr_rb_maf")
+    m = min(len(a["history"]), len(b["history"]))
+    np.testing.assert_allclose([float(h) for h in b["history"][:m]], np.sqrt(2.0) * np.array([float(h) for h in a["history"][:m]]),
+                               rtol=2e-6)
+    assert _golden("f32", 32, "pcr_maf")["history"] == _golden("f32", 32, "pcr_eda_maf")["history"] == _golden("f32", 32, "pcr_esa_maf")["history"]
+    assert _golden("f32", 32, "pcr_rb_maf")["history"] == _golden("f32", 32, "pcr_rb_esa_maf")["history"]
+    for c in GOLDEN:
+        if c["solver"].endswith("_maf") and c["solver"] != "jacobi_maf" and c["precond"] != "none":
+            assert float(c["errmax"]) < 1.0e-3, c
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+@pytest.mark.parametrize("sz", [[9, 9, 9], [12, 7, 23], [10, 8, 34]])
+def test_port_equals_numpy_restatement_maf(real, sz):
+    """The C++ port of the MAF routines against the independent numpy restatement, bit for bit, on a STRETCHED mesh
+    (so that the first- and second-derivative metric terms are all non-trivial) and random fields."""
+    o, X, B = _np_case(real, sz)
+    mesh = o.mesh(stretch=0.3)
+    xc, yc, zc = mesh
+    M = o.mask()
+    # point sweeps
+    o.ac1 = o.dt(0.8)
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("jacobi_maf", Xo, B, ro, mesh)
+    Xn = X.copy(); rn = npr.jacobi_maf(Xn, B, o.idx, xc, yc, zc, 0.8)
+    assert np.array_equal(Xo, Xn)
+    assert ro.value == pytest.approx(rn, rel=1e-12)
+    o.ac1 = o.dt(1.5)
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("sor2sma_maf", Xo, B, ro, mesh)
+    Xn = X.copy(); rn = npr.psor2sma_core_maf(Xn, B, o.idx, xc, yc, zc, 0, 0, 1.5) + npr.psor2sma_core_maf(Xn, B, o.idx, xc, yc, zc, 0, 1, 1.5)
+    assert np.array_equal(Xo, Xn)
+    assert ro.value == pytest.approx(rn, rel=1e-12)
+    # pivot, operator, residual vector
+    Po = o.pivot(mesh)
+    Pn = np.zeros_like(X); npr.search_pivot(Pn, o.idx, xc, yc, zc)
+    assert np.array_equal(Po, Pn)
+    flop = C.c_double(0); mp = [ou.ptr(m) for m in mesh]
+    Ao = np.zeros_like(X); o.dll.calc_ax_maf_(ou.ptr(Ao), ou.ptr(X), o._sz, o._idx, o.g(), *mp, ou.ptr(Po), C.byref(flop))
+    An = np.zeros_like(X); npr.calc_ax_maf(An, X, o.idx, xc, yc, zc, Pn)
+    assert np.array_equal(Ao, An)
+    Ro = np.zeros_like(X); o.dll.calc_rk_maf_(ou.ptr(Ro), ou.ptr(X), ou.ptr(B), o._sz, o._idx, o.g(), *mp, ou.ptr(Po), C.byref(flop))
+    Rn = np.zeros_like(X); npr.calc_rk_maf(Rn, X, B, o.idx, xc, yc, zc, Pn)
+    assert np.array_equal(Ro, Rn)
+    assert flop.value == 2 * 63.0 * (sz[0] - 2) * (sz[1] - 2) * (sz[2] - 2)
+    # line SOR: red-black (both argument lists) and lexicographic (three argument lists)
+    pn = ou.get_num_stage(o.idx[5] - o.idx[4] + 1)
+    o.ac1 = o.dt(1.3)
+    Xn = X.copy(); rn = npr.pcr_rb_maf(Xn, M, B, o.idx, pn, 0, 1.3, xc, yc, zc) + npr.pcr_rb_maf(Xn, M, B, o.idx, pn, 1, 1.3, xc, yc, zc)
+    for kind in ("pcr_rb_maf", "pcr_rb_esa_maf"):
+        Xo = X.copy(); ro = C.c_double(0); o.sweep_maf(kind, Xo, B, ro, mesh)
+        assert np.array_equal(Xo, Xn), (kind, np.abs(Xo - Xn).max())
+        assert ro.value == pytest.approx(rn, rel=1e-12)
+    if sz[0] * sz[1] <= 100:
+        Xn = X.copy(); rn = npr.pcr_maf(Xn, M, B, o.idx, pn, 1.3, xc, yc, zc)
+        for kind in ("pcr_maf", "pcr_eda_maf", "pcr_esa_maf"):
+            Xo = X.copy(); ro = C.c_double(0); o.sweep_maf(kind, Xo, B, ro, mesh)
+            assert np.array_equal(Xo, Xn), (kind, np.abs(Xo - Xn).max())
+            assert ro.value == pytest.approx(rn, rel=1e-12)
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+def test_port_equals_numpy_restatement_psor_maf(real):
+    o, X, B = _np_case(real, [8, 7, 10])
+    mesh = o.mesh(stretch=0.3)
+    o.ac1 = o.dt(1.5)
+    Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("psor_maf", Xo, B, ro, mesh)
+    Xn = X.copy(); rn = npr.psor_maf(Xn, B, o.idx, *mesh, 1.5)
+    assert np.array_equal(Xo, Xn)
+    assert ro.value == pytest.approx(rn, rel=1e-12)
