@@ -12,13 +12,6 @@ namespace {
 
 inline double ipow2(int e) { return (double)(1LL << e); }
 
-[[noreturn]] void maf_unsupported(const char* name) {
-  fprintf(stderr,
-          "czb200: %s (stretched-grid MAF kernel, reference src/cz_f90/cz_maf.f90) is outside the accelerated "
-          "hot path (SURVEY.md §8f-2); no CPU fallback exists.\n", name);
-  abort();
-}
-
 // run one PCR-type sweep for the per-call ABI
 void pcr_call(int* sz, int* idx, int* g, int* pn, int mode_kind /*0 rb,1 lex,2 jacobi*/, int color, bool last4,
               REAL* x, REAL* msk, REAL* rhs, REAL* wrk, REAL* omg, double* res) {
@@ -51,6 +44,48 @@ inline double pcr_flop(const int* idx, int pn, bool last4, double per4, bool hal
   const double f = last4 ? (nk * 6.0 + nk * (pn - 2) * 14.0 + ipow2(pn - 2) * per4 + nk * 6.0 + 6.0)
                          : (nk * 6.0 + nk * (pn - 1) * 14.0 + ipow2(pn - 1) * 9.0 + nk * 6.0 + 6.0);
   return lines * f * (half ? 0.5 : 1.0);
+}
+
+
+// flop formulas of the MAF line routines (cz_maf.f90:493-505, 713-725, 924-936, 1150-1162, 1373-1385)
+inline double pcr_maf_flop(const int* idx, int pn, double per2, bool half) {
+  const double nk = idx[5] - idx[4] + 1;
+  const double lines = (double)(idx[3] - idx[2] + 1) * (idx[1] - idx[0] + 1);
+  const double f = (24.0 + 3.0 * 2.0 + 12.0) + nk * (11.0 + 10.0) + (nk - 2.0) * 6.0 + nk * (pn - 1) * 16.0 +
+                   ipow2(pn - 1) * per2 + nk * 6.0;
+  return lines * f * (half ? 0.5 : 1.0);
+}
+
+// coordinate vectors of the MAF ABI: X(-1:sz(1)+2), Y(-1:sz(2)+2), Z(-1:sz(3)+2), host or device
+struct MafArgs {
+  Arg<REAL> x, y, z;
+  MafArgs(REAL* X, REAL* Y, REAL* Z, const int* sz, int g)
+      : x(X, (size_t)sz[0] + 2 * g, true, false), y(Y, (size_t)sz[1] + 2 * g, true, false),
+        z(Z, (size_t)sz[2] + 2 * g, true, false) {}
+  MafAxes axes() const { return MafAxes{x.dev(), y.dev(), z.dev()}; }
+};
+
+// one MAF line-SOR sweep for the per-call ABI: color >= 0 red-black, < 0 lexicographic (wavefronts i+j = const)
+void pcr_maf_call(int* sz, int* idx, int* g, int* pn, int color, REAL* x, REAL* msk, REAL* rhs, REAL* XX, REAL* YY,
+                  REAL* ZZ, REAL* omg, double* res) {
+  Runtime& R = rt();
+  const Geo G = make_geo(sz, idx, *g);
+  const size_t n = (size_t)G.total;
+  {
+    Arg<REAL> ax(x, n, true, true), am(msk, n, true, false), ar(rhs, n, true, false);
+    MafArgs M(XX, YY, ZZ, sz, *g);
+    Launch L = R.launch();
+    if (color >= 0) {
+      launch_pcr_lines_maf(L, G, *pn, color, 0, M.axes(), ax.dev(), am.dev(), ar.dev(), *omg, 0, false);
+    } else {
+      bool first = true;
+      for (int d = G.ist + G.jst; d <= G.ied + G.jed; ++d) {
+        launch_pcr_lines_maf(L, G, *pn, 3, d, M.axes(), ax.dev(), am.dev(), ar.dev(), *omg, 0, !first);
+        first = false;
+      }
+    }
+  }
+  *res += R.read_acc(0);
 }
 
 }  // namespace
@@ -253,9 +288,15 @@ void blas_calc_rk_(REAL* r, REAL* p, REAL* b, int* sz, int* idx, int* g, REAL* c
   launch_calc_rk(R.launch(), G, ar.dev(), ap.dev(), ab.dev(), cf);
 }
 
-// cz_blas.f90:947-1039.  Called unconditionally by the reference driver (cz_Evaluate.cpp:369)
-// but its result `pvt` feeds only the MAF solvers, which are out of scope: no-op.
-void search_pivot_(REAL*, int*, int*, int*, REAL*, REAL*, REAL*) {}
+// cz_blas.f90:947-1039: pvt = 1 / max |row coefficient| on the inner cells (called unconditionally by the
+// reference driver, cz_Evaluate.cpp:369; used by pbicgstab_maf only)
+void search_pivot_(REAL* pvt, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z) {
+  Runtime& R = rt();
+  const Geo G = make_geo(sz, idx, *g);
+  Arg<REAL> ap(pvt, (size_t)G.total, true, true);
+  MafArgs M(X, Y, Z, sz, *g);
+  launch_search_pivot(R.launch(), G, ap.dev(), M.axes());
+}
 
 // ------------------------------------------------------------------ cz_utility.f90
 void fileout_t_(int*, int*, REAL*, REAL*, REAL*, char*) {}   // compiled out unless _aurora_ (:33-44)
@@ -288,27 +329,118 @@ void err_t_(int* sz, int* idx, int* g, double* d, REAL* p, REAL* e, int* loc) {
   }
 }
 
-// ------------------------------------------------------------------ cz_maf.f90 (out of scope)
-void jacobi_maf_(REAL*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, double*, REAL*, REAL*, double*)
-{ maf_unsupported("jacobi_maf_"); }
-void psor_maf_(REAL*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, double*, double*)
-{ maf_unsupported("psor_maf_"); }
-void psor2sma_core_maf_(REAL*, int*, int*, int*, REAL*, REAL*, REAL*, int*, int*, REAL*, REAL*, double*, REAL*,
-                        double*) { maf_unsupported("psor2sma_core_maf_"); }
-void pcr_rb_maf_(int*, int*, int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
-                 REAL*, REAL*, REAL*, REAL*, double*, REAL*, double*) { maf_unsupported("pcr_rb_maf_"); }
-void pcr_rb_esa_maf_(int*, int*, int*, int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
-                     REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, double*, REAL*, double*)
-{ maf_unsupported("pcr_rb_esa_maf_"); }
-void pcr_maf_(int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
-              REAL*, REAL*, double*, REAL*, double*) { maf_unsupported("pcr_maf_"); }
-void pcr_eda_maf_(int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
-                  double*, REAL*, double*) { maf_unsupported("pcr_eda_maf_"); }
-void pcr_esa_maf_(int*, int*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*,
-                  REAL*, REAL*, REAL*, REAL*, double*, REAL*, double*) { maf_unsupported("pcr_esa_maf_"); }
-void calc_rk_maf_(REAL*, REAL*, REAL*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, double*)
-{ maf_unsupported("calc_rk_maf_"); }
-void calc_ax_maf_(REAL*, REAL*, int*, int*, int*, REAL*, REAL*, REAL*, REAL*, double*)
-{ maf_unsupported("calc_ax_maf_"); }
+// ------------------------------------------------------------------ cz_maf.f90:131-282
+void jacobi_maf_(REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z, REAL* omg, REAL* b, double* res,
+                 REAL* wk2, REAL* tmp, double* flop) {
+  (void)tmp;   // used by the reference only under _SVR
+  Runtime& R = rt();
+  const Geo G = make_geo(sz, idx, *g);
+  const size_t n = (size_t)G.total;
+  *flop += 66.0 * G.cells();
+  {
+    Arg<REAL> ap(p, n, true, true), ab(b, n, true, false), aw(wk2, n, true, true);
+    MafArgs M(X, Y, Z, sz, *g);
+    Launch L = R.launch();
+    launch_jacobi_maf(L, G, ap.dev(), aw.dev(), ab.dev(), M.axes(), *omg, 0, false);
+    launch_copy_inner(L, G, ap.dev(), aw.dev());   // cz_maf.f90:258-264
+  }
+  *res += R.read_acc(0);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:23-114
+void psor_maf_(REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z, REAL* omg, REAL* b, double* res,
+               double* flop) {
+  Runtime& R = rt();
+  const Geo G = make_geo(sz, idx, *g);
+  const size_t n = (size_t)G.total;
+  *flop += 66.0 * G.cells();
+  {
+    Arg<REAL> ap(p, n, true, true), ab(b, n, true, false);
+    MafArgs M(X, Y, Z, sz, *g);
+    launch_psor_sweep_maf(R.launch(), G, ap.dev(), ab.dev(), M.axes(), *omg, 0, false);
+  }
+  *res += R.read_acc(0);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:301-438
+void psor2sma_core_maf_(REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z, int* ip, int* color, REAL* omg,
+                        REAL* b, double* res, REAL* tmp, double* flop) {
+  (void)tmp;   // used by the reference only under _SVR
+  Runtime& R = rt();
+  const Geo G = make_geo(sz, idx, *g);
+  const size_t n = (size_t)G.total;
+  *flop += 66.0 * 0.5 * G.cells();
+  {
+    Arg<REAL> ap(p, n, true, true), ab(b, n, true, false);
+    MafArgs M(X, Y, Z, sz, *g);
+    launch_rb_color_maf(R.launch(), G, ap.dev(), ab.dev(), M.axes(), *omg, *ip + *color, 0, false);
+  }
+  *res += R.read_acc(0);
+}
+
+// The five MAF line routines: the work vectors a, c, d, aw, cw, dw and tmp of the reference are scratch (tmp is an
+// output nobody reads, cz_Poisson.cpp:565-567); the line solve lives in shared memory here.
+// ------------------------------------------------------------------ cz_maf.f90:442-668
+void pcr_rb_maf_(int* sz, int* idx, int* g, int* pn, int* ofst, int* color, REAL* x, REAL* msk, REAL* rhs, REAL* XX,
+                 REAL* YY, REAL* ZZ, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL* omg, double* res, REAL*,
+                 double* flop) {
+  (void)ofst;   // ip = ofst + color is computed but never used (cz_maf.f90:507, 526)
+  *flop += pcr_maf_flop(idx, *pn, 11.0, true);
+  pcr_maf_call(sz, idx, g, pn, *color, x, msk, rhs, XX, YY, ZZ, omg, res);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:1339-1560
+void pcr_rb_esa_maf_(int* sz, int* idx, int* g, int* pn, int* ofst, int* color, int* s, REAL* x, REAL* msk, REAL* rhs,
+                     REAL* XX, REAL* YY, REAL* ZZ, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL* omg, double* res,
+                     REAL*, double* flop) {
+  (void)ofst; (void)s;
+  *flop += pcr_maf_flop(idx, *pn, 11.0, true);
+  pcr_maf_call(sz, idx, g, pn, *color, x, msk, rhs, XX, YY, ZZ, omg, res);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:672-892
+void pcr_maf_(int* sz, int* idx, int* g, int* pn, REAL* x, REAL* msk, REAL* rhs, REAL* XX, REAL* YY, REAL* ZZ, REAL*,
+              REAL*, REAL*, REAL*, REAL*, REAL*, REAL* omg, double* res, REAL*, double* flop) {
+  *flop += pcr_maf_flop(idx, *pn, 11.0, false);
+  pcr_maf_call(sz, idx, g, pn, -1, x, msk, rhs, XX, YY, ZZ, omg, res);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:896-1113
+void pcr_eda_maf_(int* sz, int* idx, int* g, int* pn, REAL* x, REAL* msk, REAL* rhs, REAL* XX, REAL* YY, REAL* ZZ,
+                  REAL*, REAL*, REAL*, REAL* omg, double* res, REAL*, double* flop) {
+  *flop += pcr_maf_flop(idx, *pn, 9.0, false);
+  pcr_maf_call(sz, idx, g, pn, -1, x, msk, rhs, XX, YY, ZZ, omg, res);
+}
+
+// ------------------------------------------------------------------ cz_maf.f90:1117-1335
+void pcr_esa_maf_(int* sz, int* idx, int* g, int* pn, int* s, REAL* x, REAL* msk, REAL* rhs, REAL* XX, REAL* YY,
+                  REAL* ZZ, REAL*, REAL*, REAL*, REAL*, REAL*, REAL*, REAL* omg, double* res, REAL*, double* flop) {
+  (void)s;
+  *flop += pcr_maf_flop(idx, *pn, 9.0, false);
+  pcr_maf_call(sz, idx, g, pn, -1, x, msk, rhs, XX, YY, ZZ, omg, res);
+}
+
+// ------------------------------------------------------------------ cz_blas.f90:738-829
+void calc_rk_maf_(REAL* r, REAL* p, REAL* b, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z, REAL* pvt,
+                  double* flop) {
+  Runtime& R = rt();
+  const Geo G = make_geo(sz, idx, *g);
+  const size_t n = (size_t)G.total;
+  *flop += 63.0 * G.cells();
+  Arg<REAL> ar(r, n, true, true), ap(p, n, true, false), ab(b, n, true, false), av(pvt, n, true, false);
+  MafArgs M(X, Y, Z, sz, *g);
+  launch_calc_rk_maf(R.launch(), G, ar.dev(), ap.dev(), ab.dev(), M.axes(), av.dev());
+}
+
+// ------------------------------------------------------------------ cz_blas.f90:845-935
+void calc_ax_maf_(REAL* ap, REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL* Z, REAL* pvt, double* flop) {
+  Runtime& R = rt();
+  const Geo G = make_geo(sz, idx, *g);
+  const size_t n = (size_t)G.total;
+  *flop += 63.0 * G.cells();
+  Arg<REAL> aa(ap, n, true, true), a_p(p, n, true, false), av(pvt, n, true, false);
+  MafArgs M(X, Y, Z, sz, *g);
+  launch_calc_ax_maf(R.launch(), G, aa.dev(), a_p.dev(), M.axes(), av.dev(), nullptr, 0);
+}
 
 }  // extern "C"

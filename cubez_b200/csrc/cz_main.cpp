@@ -15,13 +15,17 @@ typedef CZB_REAL REAL_TYPE;
 #define GUIDE 2   // reference src/cz_cpp/cz_Define.h:40
 
 static const char* solver_names[] = {"jacobi", "psor", "sor2sma", "pbicgstab", "pcr_rb", "pcr_rb_esa", "pcr_j_esa",
-                                     "pcr", "pcr_eda", "pcr_esa", nullptr};
+                                     "pcr", "pcr_eda", "pcr_esa",
+                                     // stretched-grid twins on the driver's uniform mesh (cz_Evaluate.cpp:741-797)
+                                     "jacobi_maf", "psor_maf", "sor2sma_maf", "pbicgstab_maf", "pcr_rb_maf",
+                                     "pcr_rb_esa_maf", "pcr_maf", "pcr_eda_maf", "pcr_esa_maf", nullptr};
 
 int main(int argc, char* argv[]) {
   if (argc != 7 && argc != 8) {   // main.cpp:19-29 (gdv_x/y/z = CBrick division: not supported here)
     printf("\tUsage : ./cz gsz_x, gsz_y, gsz_z, linear_solver, IterationMax, acc_coef [precond]\n");
-    printf("\t\tlinear_solver = {jacobi | psor | sor2sma | pbicgstab | pcr | pcr_eda | pcr_esa | pcr_rb | pcr_rb_esa | pcr_j_esa}\n");
-    printf("\t\tprecond = {none | jacobi | psor | sor2sma | pcr | pcr_eda | pcr_rb | pcr_rb_esa}\n\n");
+    printf("\t\tlinear_solver = {jacobi | psor | sor2sma | pbicgstab | pcr | pcr_eda | pcr_esa | pcr_rb | pcr_rb_esa | pcr_j_esa\n");
+    printf("\t\t                 | jacobi_maf | psor_maf | sor2sma_maf | pbicgstab_maf | pcr_maf | pcr_eda_maf | pcr_esa_maf | pcr_rb_maf | pcr_rb_esa_maf}\n");
+    printf("\t\tprecond = {none | jacobi | psor | sor2sma | pcr | pcr_eda | pcr_rb | pcr_rb_esa | <the same>_maf}\n\n");
     printf("\t$ ./cz 64 64 64 jacobi 4000 0.8\n");
     printf("\t$ ./cz 64 64 64 pbicgstab 4000 1.1 sor2sma\n");
     return 0;
@@ -29,7 +33,8 @@ int main(int argc, char* argv[]) {
   int G_size[3] = {atoi(argv[1]), atoi(argv[2]), atoi(argv[3])};
   const char* q = argv[4];
   const char* precon = nullptr;
-  if (!strcasecmp(q, "pbicgstab")) {
+  const bool bicg = !strcasecmp(q, "pbicgstab") || !strcasecmp(q, "pbicgstab_maf");   // cz_Evaluate.cpp:63
+  if (bicg) {
     if (argc != 8) { printf("command line error : pbicgstab\n"); exit(0); }   // cz_Evaluate.cpp:63-70
     precon = argv[7];
   }
@@ -58,7 +63,7 @@ int main(int argc, char* argv[]) {
   int innerFidx[6] = {2, size[0] - 1, 2, size[1] - 1, 2, size[2] - 1};          // cz_miscel.cpp:20-52
   const double array_size = (double)(size[0] + 2 * GUIDE) * (size[1] + 2 * GUIDE) * (size[2] + 2 * GUIDE);
   const size_t bytes = (size_t)array_size * sizeof(REAL_TYPE);
-  const int nfields = 3 + (strcasecmp(q, "pbicgstab") ? 1 : 9);
+  const int nfields = 3 + (bicg ? 9 : 1);
   printf("\n----------\n\n");
   printf("\t>> Memory required for Solver (device) : %6.2f (MB)\n\n", array_size * sizeof(REAL_TYPE) * nfields / 1.0e6);
 
@@ -77,7 +82,6 @@ int main(int argc, char* argv[]) {
   const int itr = czb_solve(ctx, q, precon, P, RHS, ItrMax, ac1, &res, hist.data(), (int)hist.size(), &flop);
   if (itr == 0) { printf("\n\tSolver error.\n\n"); return -1; }                // main.cpp:45-52
 
-  const bool bicg = !strcasecmp(q, "pbicgstab");
   int nh = itr;
   if (bicg) { if (nh > ItrMax - 1) nh = ItrMax - 1; } else { if (nh > ItrMax) nh = ItrMax; }
   for (int i = 0; i < nh; ++i) fprintf(fph, "%6d, %13.6e\n", i + 1, hist[i]);   // cz_Poisson.cpp:71

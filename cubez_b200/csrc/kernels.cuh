@@ -77,6 +77,25 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
 // mask_is_inner: the caller guarantees msk == imask_k of G (1 on the inner range = on every cell of every
 // line); multiplying by exactly 1 changes nothing, so the warp-per-line kernel does not read it.
 
+// ---- stretched-grid (MAF) twins (maf.cu; cz_maf.f90, cz_blas.f90:738-1039) ------------------------
+// Device pointers to the coordinate vectors X(-1:sz(1)+2), Y(-1:sz(2)+2), Z(-1:sz(3)+2): Fortran index m -> [m+1].
+struct MafAxes { const REAL* X; const REAL* Y; const REAL* Z; };
+void launch_jacobi_maf(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const MafAxes& A,
+                       REAL omg, int slot, bool add);
+void launch_rb_color_maf(const Launch& L, const Geo& G, REAL* p, const REAL* b, const MafAxes& A, REAL omg, int kp,
+                         int slot, bool add);
+void launch_psor_sweep_maf(const Launch& L, const Geo& G, REAL* p, const REAL* b, const MafAxes& A, REAL omg, int slot,
+                           bool add);
+void launch_calc_ax_maf(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const MafAxes& A, const REAL* pvt,
+                        const REAL* dotwith, int slot);   // dotwith != null: acc[slot] = (ap, dotwith)
+void launch_calc_rk_maf(const Launch& L, const Geo& G, REAL* r, const REAL* p, const REAL* b, const MafAxes& A,
+                        const REAL* pvt);
+void launch_search_pivot(const Launch& L, const Geo& G, REAL* pvt, const MafAxes& A);
+// mode 0/1: lines with mod(i+j,2) == mode; mode 3: lines with i+j == diag.  acc[slot] (+)= 2 * sum dp^2 (the
+// reference's MAF line routines count every square twice, cz_maf.f90:635-636, 657-660).
+void launch_pcr_lines_maf(const Launch& L, const Geo& G, int pn, int mode, int diag, const MafAxes& A, REAL* x,
+                          const REAL* msk, const REAL* rhs, REAL omg, int slot, bool add);
+
 // ---- fused TMA-staged marching kernels (fused.cu); return false when the geometry is not
 // eligible (row pitch not a multiple of 16 B) and the caller must use the baseline kernels ----
 bool fused_eligible(const Geo& G);

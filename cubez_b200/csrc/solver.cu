@@ -102,6 +102,41 @@ void czb_ctx::Comm_SUM(int slot, int count) {
   if (comm && comm->nranks > 1) comm_allreduce_sum(comm, &d_state->acc[slot], count, rt().stream);
 }
 
+// ---- stretched-grid (MAF) state ---------------------------------------------------------------
+// Default mesh = the reference driver's: xc[i] = (REAL)(i-1)*pitch for i = 0..size+2*gc-1 (cz_Evaluate.cpp:342-362).
+// On j-slabs the GLOBAL index is used (i-1 + head-1), so that a slab sees the coordinates of the single domain
+// (same reasoning as bc_origin).
+void czb_ctx::set_mesh(const REAL* x, const REAL* y, const REAL* z) {
+  Runtime& R = rt();
+  REAL** dst[3] = {&xc, &yc, &zc};
+  const REAL* src[3] = {x, y, z};
+  for (int a = 0; a < 3; ++a) {
+    const size_t n = (size_t)size[a] + 2 * gc;
+    std::vector<REAL> h(n);
+    for (size_t i = 0; i < n; ++i)
+      h[i] = src[a] ? src[a][i] : (REAL)((int)i - 1 + head[a] - 1) * pitch;
+    if (!*dst[a]) CZB_CHECK(cudaMalloc(dst[a], sizeof(REAL) * n));
+    CZB_CHECK(cudaMemcpyAsync(*dst[a], h.data(), sizeof(REAL) * n, cudaMemcpyHostToDevice, R.stream));
+    R.sync();   // h goes out of scope
+  }
+  mesh_user = (x || y || z);
+  if (pvt) launch_search_pivot(launch(false), G, pvt, MafAxes{xc, yc, zc});
+}
+
+MafAxes czb_ctx::axes() {
+  if (!xc) set_mesh(nullptr, nullptr, nullptr);
+  return MafAxes{xc, yc, zc};
+}
+
+REAL* czb_ctx::pivot() {
+  if (!pvt) {
+    const MafAxes A = axes();
+    field(pvt);                                        // zero outside the inner cells, as czAllocR_S3D leaves it
+    launch_search_pivot(launch(false), G, pvt, A);
+  }
+  return pvt;
+}
+
 // cuStreamWaitValue32 through the runtime's driver entry point (no link dependency on libcuda)
 static void stream_wait_geq(cudaStream_t s, unsigned int* dev, unsigned int value) {
   typedef CUresult (*Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
@@ -208,7 +243,8 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     REAL* src = (it & 1) ? X : W;
     REAL* dst = (it & 1) ? W : X;
     Launch L = launch();
-    if (!(variant == 0 && launch_jacobi_fused(L, G, src, dst, B, cf, ac1, rs, false)))
+    if (maf) launch_jacobi_maf(L, G, src, dst, B, axes(), ac1, rs, false);   // cz_Poisson.cpp:45-52
+    else if (!(variant == 0 && launch_jacobi_fused(L, G, src, dst, B, cf, ac1, rs, false)))
       launch_jacobi(L, G, src, dst, B, cf, ac1, rs, false);
     Comm_S(dst, 1);
     if (converge_check) {
@@ -230,7 +266,7 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     launch_copy_inner(launch(false), G, X, W);
     if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // X missed the bc_k of an odd last iteration
   }
-  flop += 18.0 * G.cells() * done_iters;
+  flop += (maf ? 66.0 : 18.0) * G.cells() * done_iters;
   return itr;
 }
 
@@ -239,7 +275,8 @@ int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
   auto body = [&](int it) {
     Launch L = launch();
-    launch_psor_sweep(L, G, X, B, cf, ac1, rs, false);
+    if (maf) launch_psor_sweep_maf(L, G, X, B, axes(), ac1, rs, false);   // cz_Poisson.cpp:108-114
+    else     launch_psor_sweep(L, G, X, B, cf, ac1, rs, false);
     Comm_S(X, 1);
     if (converge_check) {
       Comm_SUM(0);
@@ -250,7 +287,7 @@ int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool
   int itr, done_iters;
   if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
   else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
-  flop += 18.0 * G.cells() * done_iters;
+  flop += (maf ? 66.0 : 18.0) * G.cells() * done_iters;
   return itr;
 }
 
@@ -260,7 +297,7 @@ int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool
 int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check) {
   const int ip = parity_ip();
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
-  const bool fused = (variant == 0) && fused_eligible(G);
+  const bool fused = !maf && (variant == 0) && fused_eligible(G);
   int itr, done_iters;
   if (fused) {
     // Both colours in one pass (fused.cu MODE_RB2), ping-pong between X and WRK.  Multi-rank: one
@@ -354,7 +391,8 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     auto body = [&](int it) {
       Launch L = launch();
       for (int color = 0; color < 2; ++color) {
-        launch_rb_color(L, G, X, B, cf, ac1, ip + color, rs, color == 1);
+        if (maf) launch_rb_color_maf(L, G, X, B, axes(), ac1, ip + color, rs, color == 1);   // cz_Poisson.cpp:190-200
+        else     launch_rb_color(L, G, X, B, cf, ac1, ip + color, rs, color == 1);
         Comm_S(X, 1);
       }
       if (converge_check) {
@@ -366,7 +404,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
     else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
   }
-  flop += 18.0 * G.cells() * done_iters;
+  flop += (maf ? 66.0 : 18.0) * G.cells() * done_iters;
   return itr;
 }
 
@@ -376,6 +414,15 @@ static double pcr_iter_flop(const Geo& G, int pn, bool last4, double per4) {
   const double f = last4 ? (nk * 6.0 + nk * (pn - 2) * 14.0 + ipow2(pn - 2) * per4 + nk * 6.0 + 6.0)
                          : (nk * 6.0 + nk * (pn - 1) * 14.0 + ipow2(pn - 1) * 9.0 + nk * 6.0 + 6.0);
   return lines * f;
+}
+
+// cz_maf.f90:493-505 (per iteration = both colours / all lines); per2 = 11 (pcr_rb_maf, pcr_rb_esa_maf, pcr_maf)
+// or 9 (pcr_eda_maf, pcr_esa_maf)
+static double pcr_maf_iter_flop(const Geo& G, int pn, double per2) {
+  const double nk = G.ked - G.kst + 1;
+  const double lines = (double)(G.jed - G.jst + 1) * (G.ied - G.ist + 1);
+  return lines * ((24.0 + 3.0 * 2.0 + 12.0) + nk * (11.0 + 10.0) + (nk - 2.0) * 6.0 + nk * (pn - 1) * 16.0 +
+                  ipow2(pn - 1) * per2 + nk * 6.0);
 }
 
 static REAL* ensure_mask(czb_ctx* c) {
@@ -392,14 +439,16 @@ int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flo
   const int pn = getNumStage(n);
   if (pn < 0) { printf("error : number of stage\n"); return 0; }
   PcrTables& T = last4 ? pcr4 : pcr2;
-  pcr_build_tables(rt().stream, T, n, pn, last4);
+  if (!maf) pcr_build_tables(rt().stream, T, n, pn, last4);
   REAL* M = ensure_mask(this);
   const int ofs = (head[0] + head[1]) & 1;   // global (i+j) parity; 0 on a single domain
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
   auto body = [&](int it) {
     Launch L = launch();
     for (int color = 0; color < 2; ++color) {
-      launch_pcr_lines(L, G, T, color, ofs, 0, X, X, M, B, ac1, rs, color == 1, true);
+      // MAF (cz_Poisson.cpp:559-570, 684-695): line-dependent coefficients, 2x2 last stage in both variants
+      if (maf) launch_pcr_lines_maf(L, G, pn, color ^ ofs, 0, axes(), X, M, B, ac1, rs, color == 1);
+      else     launch_pcr_lines(L, G, T, color, ofs, 0, X, X, M, B, ac1, rs, color == 1, true);
       Comm_S(X, 1);
     }
     if (converge_check) {
@@ -411,7 +460,7 @@ int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flo
   int itr, done_iters;
   if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
   else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
-  flop += pcr_iter_flop(G, pn, last4, 78.0) * done_iters;
+  flop += (maf ? pcr_maf_iter_flop(G, pn, 11.0) : pcr_iter_flop(G, pn, last4, 78.0)) * done_iters;
   return itr;
 }
 
@@ -423,14 +472,15 @@ int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, 
   const int pn = getNumStage(n);
   if (pn < 0) { printf("error : number of stage\n"); return 0; }
   PcrTables& T = last4 ? pcr4 : pcr2;
-  pcr_build_tables(rt().stream, T, n, pn, last4);
+  if (!maf) pcr_build_tables(rt().stream, T, n, pn, last4);
   REAL* M = ensure_mask(this);
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
   auto body = [&](int it) {
     Launch L = launch();
     bool first = true;
     for (int d = G.ist + G.jst; d <= G.ied + G.jed; ++d) {
-      launch_pcr_lines(L, G, T, 3, 0, d, X, X, M, B, ac1, rs, !first, true);
+      if (maf) launch_pcr_lines_maf(L, G, pn, 3, d, axes(), X, M, B, ac1, rs, !first);   // cz_Poisson.cpp:775-782, 858-865, 963-971
+      else     launch_pcr_lines(L, G, T, 3, 0, d, X, X, M, B, ac1, rs, !first, true);
       first = false;
     }
     Comm_S(X, 1);
@@ -443,7 +493,7 @@ int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, 
   int itr, done_iters;
   if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
   else { for (int it = 1; it <= itr_max; ++it) body(it); itr = itr_max + 1; done_iters = itr_max; }
-  flop += pcr_iter_flop(G, pn, last4, 74.0) * done_iters;
+  flop += (maf ? pcr_maf_iter_flop(G, pn, last4 ? 11.0 : 9.0) : pcr_iter_flop(G, pn, last4, 74.0)) * done_iters;
   return itr;
 }
 
@@ -496,23 +546,29 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
 void czb_ctx::Preconditioner(REAL* xx, REAL* bb, double& flop, int pc_type) {
   double res = 0.0;
   const int lc_max = 8;
+  const bool outer_maf = maf;
+  maf = pc_type >= LS_PSOR_MAF;   // the preconditioner's own kind decides, whatever the outer operator is (:282-317)
   switch (pc_type) {
-    case LS_JACOBI:     JACOBI(res, xx, bb, lc_max, flop, false); break;
-    case LS_PSOR:       PSOR(res, xx, bb, lc_max, flop, false); break;
-    case LS_SOR2SMA:    RBSOR(res, xx, bb, lc_max, flop, false); break;
-    case LS_PCR:        LSOR_PCR(res, xx, bb, lc_max, flop, true, false); break;
-    case LS_PCR_EDA:    LSOR_PCR(res, xx, bb, lc_max, flop, false, false); break;
-    case LS_PCR_RB:     LSOR_PCR_RB(res, xx, bb, lc_max, flop, false, false); break;
-    case LS_PCR_RB_ESA: LSOR_PCR_RB(res, xx, bb, lc_max, flop, true, false); break;
+    case LS_JACOBI:     case LS_JACOBI_MAF:     JACOBI(res, xx, bb, lc_max, flop, false); break;
+    case LS_PSOR:       case LS_PSOR_MAF:       PSOR(res, xx, bb, lc_max, flop, false); break;
+    case LS_SOR2SMA:    case LS_SOR2SMA_MAF:    RBSOR(res, xx, bb, lc_max, flop, false); break;
+    case LS_PCR:        case LS_PCR_MAF:        LSOR_PCR(res, xx, bb, lc_max, flop, true, false); break;
+    case LS_PCR_EDA:    case LS_PCR_EDA_MAF:    LSOR_PCR(res, xx, bb, lc_max, flop, false, false); break;
+    case LS_PCR_RB:     case LS_PCR_RB_MAF:     LSOR_PCR_RB(res, xx, bb, lc_max, flop, false, false); break;
+    case LS_PCR_RB_ESA: case LS_PCR_RB_ESA_MAF: LSOR_PCR_RB(res, xx, bb, lc_max, flop, true, false); break;
     default:
       CZB_CHECK(cudaMemcpyAsync(xx, bb, sizeof(REAL) * field_elems(), cudaMemcpyDeviceToDevice, rt().stream));
   }
+  maf = outer_maf;
 }
 
 // CZ::PBiCGSTAB (cz_Poisson.cpp:332-504).  Scalars rho/alpha/beta/omega live in LoopState.scal
 // on the device (k_bicg_scalar), the vector kernels read them from there.
-int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, int pc_type) {
+int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, int pc_type, bool maf_op) {
   Runtime& R = rt();
+  // pbicgstab_maf (:350-358, 415-419, 451-455): the operator is calc_ax_maf / calc_rk_maf scaled by pvt
+  const MafAxes MA = maf_op ? axes() : MafAxes{nullptr, nullptr, nullptr};
+  const REAL* PV = maf_op ? pivot() : nullptr;
   const size_t bytes = sizeof(REAL) * field_elems();
   REAL *p = field(pcg_p), *p_ = field(pcg_p_), *r = field(pcg_r), *r0 = field(pcg_r0), *q = field(pcg_q),
        *s = field(pcg_s), *s_ = field(pcg_s_), *t_ = field(pcg_t_);
@@ -527,7 +583,8 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
   {
     Launch L = launch();
     CZB_CHECK(cudaMemsetAsync(q, 0, bytes, R.stream));                       // :344
-    launch_calc_rk(L, G, r, X, B, cf);                                       // :356
+    if (maf_op) launch_calc_rk_maf(L, G, r, X, B, MA, PV);                   // :352
+    else        launch_calc_rk(L, G, r, X, B, cf);                           // :356
     Comm_S(r, 1);                                                            // :362
     CZB_CHECK(cudaMemcpyAsync(r0, r, bytes, cudaMemcpyDeviceToDevice, R.stream));   // :365
     k_bicg_scalar<<<1, 1, 0, R.stream>>>(d_state, -1, res_normal, eps, d_hist, hist_cap);
@@ -549,15 +606,17 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
     Comm_S(p, 1);                                                            // :402
     if (!zs) CZB_CHECK(cudaMemsetAsync(p_, 0, bytes, R.stream));             // :405 (zs: first sweep does not read p_)
     pre_zero_src = zs; Preconditioner(p_, p, pflop, pc_type); pre_zero_src = false;   // :409
-    if (!(variant == 0 && launch_ax_fused(L, G, q, p_, cf, r0, 1))) launch_calc_ax(L, G, q, p_, cf, r0, 1);
+    if (maf_op) launch_calc_ax_maf(L, G, q, p_, MA, PV, r0, 1);              // :417
+    else if (!(variant == 0 && launch_ax_fused(L, G, q, p_, cf, r0, 1))) launch_calc_ax(L, G, q, p_, cf, r0, 1);
     Comm_SUM(1); scalar(1);          // q = A p_, alpha :421-431
     launch_triad(L, G, s, q, r, 0, &sc[SC_NEG_ALPHA]);                       // s = r - alpha q :434
     Comm_S(s, 1);                                                            // :438
     if (!zs) CZB_CHECK(cudaMemsetAsync(s_, 0, bytes, R.stream));             // :441
     pre_zero_src = zs; Preconditioner(s_, s, pflop, pc_type); pre_zero_src = false;   // :445
     {   // t = A s_, (t,s), (t,t) :457-464
-      const int f = (variant == 0) ? launch_ax_fused(L, G, t_, s_, cf, s, 2, 3) : 0;
-      if (f == 0) launch_calc_ax(L, G, t_, s_, cf, s, 2);
+      const int f = (variant == 0 && !maf_op) ? launch_ax_fused(L, G, t_, s_, cf, s, 2, 3) : 0;
+      if (maf_op) launch_calc_ax_maf(L, G, t_, s_, MA, PV, s, 2);            // :453
+      else if (f == 0) launch_calc_ax(L, G, t_, s_, cf, s, 2);
       if (f != 2) launch_dot1(L, G, t_, 3);
     }
     Comm_SUM(2, 2); scalar(2);                                               // omega
@@ -593,7 +652,8 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
   }
   const int itr = end_loop(ItrMax, res, true);
   const int done_iters = h_state[0].itr;
-  flop += (14.0 + (double)done_iters * (2 + 4 + 13 + 2 + 2 + 13 + 4 + 4 + 2 + 2)) * G.cells();
+  const double f_ax = maf_op ? 63.0 : 13.0, f_rk = maf_op ? 63.0 : 14.0;
+  flop += (f_rk + (double)done_iters * (2 + 4 + f_ax + 2 + 2 + f_ax + 4 + 4 + 2 + 2)) * G.cells();
   if (launched > 0) flop += pflop * ((double)done_iters / (double)launched);
   return itr;
 }
@@ -626,6 +686,7 @@ czb_ctx* czb_ctx_create(const int sz[3], const int idx[6], const int nID[6], CZB
   c->G = make_geo(c->size, c->innerFidx, c->gc);
   c->res_normal = 1.0 / c->G.cells();
   c->wrk_guards_zero = false;
+  c->maf = false; c->mesh_user = false; c->xc = c->yc = c->zc = c->pvt = nullptr;
   c->pre_zero_src = false; c->cs = nullptr; c->cs_used = false; c->d_sig = nullptr; c->sig_target = 0;
   CZB_CHECK(cudaMalloc(&c->d_state, sizeof(LoopState)));
   CZB_CHECK(cudaMemset(c->d_state, 0, sizeof(LoopState)));
@@ -640,7 +701,7 @@ void czb_ctx_destroy(czb_ctx* c) {
   if (!c) return;
   rt().sync();
   REAL* fields[] = {c->WRK, c->MSK, c->pcg_p, c->pcg_p_, c->pcg_r, c->pcg_r0, c->pcg_q, c->pcg_s, c->pcg_s_,
-                    c->pcg_t_, c->Xd, c->Bd};
+                    c->pcg_t_, c->Xd, c->Bd, c->pvt, c->xc, c->yc, c->zc};
   for (REAL* f : fields) if (f) cudaFree(f);
   pcr_free_tables(c->pcr2); pcr_free_tables(c->pcr4);
   if (c->d_hist) cudaFree(c->d_hist);
@@ -672,6 +733,7 @@ void czb_ctx_bc_k(czb_ctx* c, CZB_REAL* p) {
   launch_bc_k(R.launch(), c->G, ap.dev(), c->pitch, c->bc_origin, c->nID, c->head[1] - 1);
 }
 void czb_ctx_set_variant(czb_ctx* c, int v) { c->variant = v; }
+void czb_ctx_set_mesh(czb_ctx* c, const CZB_REAL* x, const CZB_REAL* y, const CZB_REAL* z) { c->set_mesh(x, y, z); }
 double czb_last_solve_ms(czb_ctx* c) { return c->last_ms; }
 
 int czb_comm_unique_id(void* id128) { return comm_unique_id(id128); }
@@ -720,16 +782,14 @@ int czb_solve(czb_ctx* c, const char* solver, const char* precond, CZB_REAL* X, 
   Runtime& R = rt();
   const int ls = czb_parse_solver(solver);
   if (ls == 0) { printf("Invalid solver\n"); return 0; }           // CZ::setLS, cz_Evaluate.cpp:799-802
-  if (ls >= LS_PSOR_MAF) {
-    fprintf(stderr, "czb200: solver '%s' (stretched-grid MAF) is outside the accelerated hot path; no CPU fallback.\n", solver);
-    return 0;
-  }
   int pc = 0;
-  if (ls == LS_BICGSTAB) {
+  if (ls == LS_BICGSTAB || ls == LS_BICGSTAB_MAF) {
     pc = czb_parse_solver(precond);
     if (pc == 0 && precond) printf("precon=%s\n", precond);        // CZ::setStrPre falls through to copy
-    if (pc >= LS_PSOR_MAF || pc == LS_BICGSTAB || pc == LS_PCR_ESA || pc == LS_PCR_J_ESA) pc = 0;
+    // names CZ::setStrPre does not know (cz_Evaluate.cpp:571-619) leave pc_type unset -> copy
+    if (pc == LS_BICGSTAB || pc == LS_BICGSTAB_MAF || pc == LS_PCR_ESA || pc == LS_PCR_J_ESA || pc == LS_PCR_ESA_MAF) pc = 0;
   }
+  c->maf = (ls >= LS_PSOR_MAF && ls != LS_BICGSTAB_MAF);
   c->ac1 = omg;
   const size_t bytes = sizeof(REAL) * c->field_elems();
   REAL* Xdev = X; REAL* Bdev = B;
@@ -749,8 +809,19 @@ int czb_solve(czb_ctx* c, const char* solver, const char* precond, CZB_REAL* X, 
     case LS_PCR_RB:     itr = c->LSOR_PCR_RB(res, Xdev, Bdev, itr_max, flop, false); break;
     case LS_PCR_RB_ESA: itr = c->LSOR_PCR_RB(res, Xdev, Bdev, itr_max, flop, true); break;
     case LS_PCR_J_ESA:  itr = c->LSOR_PCR_J_ESA(res, Xdev, Bdev, itr_max, flop); break;
+    // stretched-grid twins (cz_Evaluate.cpp:418-480): same loops, MAF kernels (c->maf)
+    case LS_JACOBI_MAF:     itr = c->JACOBI(res, Xdev, Bdev, itr_max, flop); break;
+    case LS_PSOR_MAF:       itr = c->PSOR(res, Xdev, Bdev, itr_max, flop); break;
+    case LS_SOR2SMA_MAF:    itr = c->RBSOR(res, Xdev, Bdev, itr_max, flop); break;
+    case LS_BICGSTAB_MAF:   itr = c->PBiCGSTAB(res, Xdev, Bdev, itr_max, flop, pc, true); break;
+    case LS_PCR_MAF:        itr = c->LSOR_PCR(res, Xdev, Bdev, itr_max, flop, true); break;
+    case LS_PCR_ESA_MAF:    itr = c->LSOR_PCR(res, Xdev, Bdev, itr_max, flop, false); break;
+    case LS_PCR_EDA_MAF:    itr = c->LSOR_PCR(res, Xdev, Bdev, itr_max, flop, false); break;
+    case LS_PCR_RB_MAF:     itr = c->LSOR_PCR_RB(res, Xdev, Bdev, itr_max, flop, false); break;
+    case LS_PCR_RB_ESA_MAF: itr = c->LSOR_PCR_RB(res, Xdev, Bdev, itr_max, flop, true); break;
     default: break;
   }
+  c->maf = false;
   const int n_hist = c->h_state[0].itr;
   if (hist && hist_len > 0 && n_hist > 0) {
     const int m = n_hist < hist_len ? n_hist : hist_len;

@@ -40,6 +40,11 @@ struct czb_ctx {
   bool wrk_guards_zero;
   bool pre_zero_src;      // the next preconditioner call may skip reading its (all-zero) start vector
   czb::PcrTables pcr2, pcr4;
+  // ---- stretched-grid (MAF) twins: coordinate vectors xc, yc, zc (cz_Evaluate.cpp:246-248, 342-362) and the
+  // pivot field pvt (:243, 369) on the device; `maf` selects the MAF kernels inside the loops below
+  bool maf;
+  REAL *xc, *yc, *zc, *pvt;
+  bool mesh_user;         // mesh given through czb_ctx_set_mesh (else the reference driver's uniform mesh)
 
   czb::LoopState* d_state;
   czb::LoopState* h_state;   // pinned, 2 slots
@@ -60,6 +65,9 @@ struct czb_ctx {
   void Comm_S(REAL* f, int width = 1);            // cz_comm.cpp:23-38
   void Comm_SUM(int slot, int count = 1);         // cz_comm.cpp:74-140 on device scalars
   int parity_ip() const { return (head[0] + head[1] + head[2] + 1) % 2; }   // cz_Poisson.cpp:181
+  czb::MafAxes axes();                            // device mesh, created on first use
+  void set_mesh(const REAL* x, const REAL* y, const REAL* z);   // host vectors of size[a] + 2*gc entries
+  REAL* pivot();                                  // search_pivot (cz_blas.f90:947-1039), computed on first use
 
   // ---- iteration loops (cz_Poisson.cpp) ----
   int JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check = true);
@@ -69,7 +77,7 @@ struct czb_ctx {
   int LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool last4, bool converge_check = true);
   int LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check = true);
   void Preconditioner(REAL* xx, REAL* bb, double& flop, int pc_type);
-  int PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, int pc_type);
+  int PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, int pc_type, bool maf_op = false);
 
   // generic driver: enqueue `body(it)` for it = 1..itr_max in batches, polling the device
   // state without stalling the queue.  Returns the reference's iteration count.

@@ -17,7 +17,7 @@ REFERENCE_SYMBOLS = {
     "imask_k_": 4, "blas_clear_": 3, "blas_copy_": 4, "blas_copy_in_": 4, "blas_triad_": 8,
     "blas_dot1_": 6, "blas_dot2_": 7, "blas_bicg_1_": 9, "blas_bicg_2_": 9, "blas_calc_ax_": 7,
     "blas_calc_rk_": 8, "search_pivot_": 7, "fileout_t_": 6, "exact_t_": 5, "err_t_": 7,
-    # MAF twins: exported (abort when called), SURVEY.md §8f-2
+    # stretched-grid (MAF) twins, SURVEY.md §8f-2
     "jacobi_maf_": 13, "psor_maf_": 11, "psor2sma_core_maf_": 14, "pcr_rb_maf_": 22,
     "pcr_rb_esa_maf_": 23, "pcr_maf_": 20, "pcr_eda_maf_": 17, "pcr_esa_maf_": 21,
     "calc_rk_maf_": 11, "calc_ax_maf_": 10,
@@ -27,7 +27,7 @@ CZB_SYMBOLS = [
     "czb_real_bytes", "czb_version", "czb_init", "czb_set_stream", "czb_sync", "czb_malloc", "czb_free",
     "czb_memcpy_h2d", "czb_memcpy_d2h", "czb_launch_count", "czb_staged_bytes", "czb_slab_decompose",
     "czb_ctx_create", "czb_ctx_destroy", "czb_ctx_set_eps", "czb_ctx_set_res_normal", "czb_ctx_set_head",
-    "czb_ctx_set_variant", "czb_ctx_bc_k", "czb_comm_unique_id", "czb_ctx_comm_init", "czb_solve", "czb_last_solve_ms",
+    "czb_ctx_set_variant", "czb_ctx_set_mesh", "czb_ctx_bc_k", "czb_comm_unique_id", "czb_ctx_comm_init", "czb_solve", "czb_last_solve_ms",
     "czb_sweep_rbsor", "czb_sweep_jacobi", "czb_apply_ax",
 ]
 
@@ -60,6 +60,7 @@ def bind_czb_symbols(dll, real_ctype):
     dll.czb_ctx_set_res_normal.argtypes = [P, C.c_double]; dll.czb_ctx_set_res_normal.restype = None
     dll.czb_ctx_set_head.argtypes = [P, PI]; dll.czb_ctx_set_head.restype = None
     dll.czb_ctx_set_variant.argtypes = [P, C.c_int]; dll.czb_ctx_set_variant.restype = None
+    dll.czb_ctx_set_mesh.argtypes = [P, P, P, P]; dll.czb_ctx_set_mesh.restype = None
     dll.czb_ctx_bc_k.argtypes = [P, P]; dll.czb_ctx_bc_k.restype = None
     dll.czb_comm_unique_id.argtypes = [P]; dll.czb_comm_unique_id.restype = C.c_int
     dll.czb_ctx_comm_init.argtypes = [P, C.c_int, C.c_int, P]; dll.czb_ctx_comm_init.restype = C.c_int

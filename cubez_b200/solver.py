@@ -11,7 +11,10 @@ GUIDE = decomp.GUIDE
 EPS_DEFAULT = 1.0e-5  # reference src/cz_cpp/cz.h:162
 
 SOLVERS = ("jacobi", "psor", "sor2sma", "pbicgstab", "pcr", "pcr_eda", "pcr_esa", "pcr_rb", "pcr_rb_esa",
-           "pcr_j_esa")
+           "pcr_j_esa",
+           # stretched-grid twins, CZ::setLS cz_Evaluate.cpp:741-797
+           "jacobi_maf", "psor_maf", "sor2sma_maf", "pbicgstab_maf", "pcr_maf", "pcr_eda_maf", "pcr_esa_maf",
+           "pcr_rb_maf", "pcr_rb_esa_maf")
 
 
 def _iarr(v):
@@ -124,9 +127,22 @@ class CZ:
                                  C.byref(res), hist, n if want_history else 0, C.byref(flop))
         nh = 0
         if want_history and itr > 0:
-            nh = min(itr, itr_max - 1 if solver.lower() == "pbicgstab" else itr_max)
+            nh = min(itr, itr_max - 1 if solver.lower() in ("pbicgstab", "pbicgstab_maf") else itr_max)
         return dict(itr=itr, res=res.value, history=np.array(hist[:nh]) if want_history else None,
                     ms=self.dll.czb_last_solve_ms(self.ctx), flop=flop.value)
+
+    def set_mesh(self, xc=None, yc=None, zc=None):
+        """Coordinate vectors of the `*_maf` solvers (numpy, sz[a]+4 entries = Fortran X(-1:sz+2)); None = the
+        reference driver's uniform mesh (cz_Evaluate.cpp:342-362)."""
+        keep = []
+        for a, v in enumerate((xc, yc, zc)):
+            if v is None:
+                keep.append(None)
+                continue
+            v = np.ascontiguousarray(v, dtype=self.ndtype)
+            assert v.shape == (self.sz[a] + 2 * GUIDE,)
+            keep.append(v)
+        self.dll.czb_ctx_set_mesh(self.ctx, *[C.c_void_p(v.ctypes.data) if v is not None else None for v in keep])
 
     def variant(self, v):
         self.dll.czb_ctx_set_variant(self.ctx, int(v))

@@ -102,33 +102,40 @@ void fileout_t_(int* sz, int* g, CZB_REAL* s, CZB_REAL* dh, CZB_REAL* org, char*
 void exact_t_(int* sz, int* g, CZB_REAL* e, CZB_REAL* dh, CZB_REAL* org);
 void err_t_(int* sz, int* idx, int* g, double* d, CZB_REAL* p, CZB_REAL* e, int* loc);
 
-/* Stretched-grid ("MAF") twins, cz_maf.f90 + cz_blas.f90:738,845: OUT OF SCOPE (SURVEY.md
- * §8f-2).  Exported so the reference driver links; they abort with a message if reached. */
-void jacobi_maf_(CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-                 CZB_REAL*, double*, CZB_REAL*, CZB_REAL*, double*);
-void psor_maf_(CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-               double*, double*);
-void psor2sma_core_maf_(CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, int*, int*,
-                        CZB_REAL*, CZB_REAL*, double*, CZB_REAL*, double*);
-void pcr_rb_maf_(int*, int*, int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-                 CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-                 CZB_REAL*, CZB_REAL*, double*, CZB_REAL*, double*);
-void pcr_rb_esa_maf_(int*, int*, int*, int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-                     CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-                     CZB_REAL*, CZB_REAL*, CZB_REAL*, double*, CZB_REAL*, double*);
-void pcr_maf_(int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-              CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-              CZB_REAL*, double*, CZB_REAL*, double*);
-void pcr_eda_maf_(int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-                  CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, double*, CZB_REAL*,
-                  double*);
-void pcr_esa_maf_(int*, int*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-                  CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-                  CZB_REAL*, CZB_REAL*, double*, CZB_REAL*, double*);
-void calc_rk_maf_(CZB_REAL*, CZB_REAL*, CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*,
-                  CZB_REAL*, CZB_REAL*, double*);
-void calc_ax_maf_(CZB_REAL*, CZB_REAL*, int*, int*, int*, CZB_REAL*, CZB_REAL*, CZB_REAL*,
-                  CZB_REAL*, double*);
+/* Stretched-grid ("MAF") twins: cz_Ffunc.h <- cz_maf.f90 and cz_blas.f90:738-935.
+ * X, Y, Z are the coordinate vectors X(-1:sz(1)+2), Y(-1:sz(2)+2), Z(-1:sz(3)+2) (host or device); the
+ * metric coefficients are evaluated per cell in the reference's statement order.  The 1-D work vectors
+ * (a, c, d, aw, cw, dw) and tmp are the reference's scratch space and are not touched.  The five line
+ * routines add 2 * sum dp^2 to *res, as the reference does (cz_maf.f90:635-636, 657-660). */
+void jacobi_maf_(CZB_REAL* p, int* sz, int* idx, int* g, CZB_REAL* X, CZB_REAL* Y, CZB_REAL* Z, CZB_REAL* omg,
+                 CZB_REAL* b, double* res, CZB_REAL* wk2, CZB_REAL* tmp, double* flop);        /* :131-282 */
+void psor_maf_(CZB_REAL* p, int* sz, int* idx, int* g, CZB_REAL* X, CZB_REAL* Y, CZB_REAL* Z, CZB_REAL* omg,
+               CZB_REAL* b, double* res, double* flop);                                        /* :23-114 */
+void psor2sma_core_maf_(CZB_REAL* p, int* sz, int* idx, int* g, CZB_REAL* X, CZB_REAL* Y, CZB_REAL* Z, int* ip,
+                        int* color, CZB_REAL* omg, CZB_REAL* b, double* res, CZB_REAL* tmp,
+                        double* flop);                                                         /* :301-438 */
+void pcr_rb_maf_(int* sz, int* idx, int* g, int* pn, int* ofst, int* color, CZB_REAL* x, CZB_REAL* msk,
+                 CZB_REAL* rhs, CZB_REAL* XX, CZB_REAL* YY, CZB_REAL* ZZ, CZB_REAL* a, CZB_REAL* c, CZB_REAL* d,
+                 CZB_REAL* aw, CZB_REAL* cw, CZB_REAL* dw, CZB_REAL* omg, double* res, CZB_REAL* tmp,
+                 double* flop);                                                                /* :442-668 */
+void pcr_rb_esa_maf_(int* sz, int* idx, int* g, int* pn, int* ofst, int* color, int* s, CZB_REAL* x,
+                     CZB_REAL* msk, CZB_REAL* rhs, CZB_REAL* XX, CZB_REAL* YY, CZB_REAL* ZZ, CZB_REAL* a,
+                     CZB_REAL* c, CZB_REAL* d, CZB_REAL* aw, CZB_REAL* cw, CZB_REAL* dw, CZB_REAL* omg,
+                     double* res, CZB_REAL* tmp, double* flop);                                /* :1339-1560 */
+void pcr_maf_(int* sz, int* idx, int* g, int* pn, CZB_REAL* x, CZB_REAL* msk, CZB_REAL* rhs, CZB_REAL* XX,
+              CZB_REAL* YY, CZB_REAL* ZZ, CZB_REAL* a, CZB_REAL* c, CZB_REAL* d, CZB_REAL* aw, CZB_REAL* cw,
+              CZB_REAL* dw, CZB_REAL* omg, double* res, CZB_REAL* tmp, double* flop);          /* :672-892 */
+void pcr_eda_maf_(int* sz, int* idx, int* g, int* pn, CZB_REAL* x, CZB_REAL* msk, CZB_REAL* rhs, CZB_REAL* XX,
+                  CZB_REAL* YY, CZB_REAL* ZZ, CZB_REAL* aw, CZB_REAL* cw, CZB_REAL* dw, CZB_REAL* omg,
+                  double* res, CZB_REAL* tmp, double* flop);                                   /* :896-1113 */
+void pcr_esa_maf_(int* sz, int* idx, int* g, int* pn, int* s, CZB_REAL* x, CZB_REAL* msk, CZB_REAL* rhs,
+                  CZB_REAL* XX, CZB_REAL* YY, CZB_REAL* ZZ, CZB_REAL* a, CZB_REAL* c, CZB_REAL* d, CZB_REAL* aw,
+                  CZB_REAL* cw, CZB_REAL* dw, CZB_REAL* omg, double* res, CZB_REAL* tmp,
+                  double* flop);                                                               /* :1117-1335 */
+void calc_rk_maf_(CZB_REAL* r, CZB_REAL* p, CZB_REAL* b, int* sz, int* idx, int* g, CZB_REAL* X, CZB_REAL* Y,
+                  CZB_REAL* Z, CZB_REAL* pvt, double* flop);                     /* cz_blas.f90:738-829 */
+void calc_ax_maf_(CZB_REAL* ap, CZB_REAL* p, int* sz, int* idx, int* g, CZB_REAL* X, CZB_REAL* Y, CZB_REAL* Z,
+                  CZB_REAL* pvt, double* flop);                                  /* cz_blas.f90:845-935 */
 
 /* ===================================================================== PART 2 */
 
@@ -163,6 +170,10 @@ void czb_ctx_set_eps(czb_ctx* c, double eps);                /* default 1e-5, cz
 void czb_ctx_set_res_normal(czb_ctx* c, double res_normal);  /* default 1/inner cells */
 void czb_ctx_set_head(czb_ctx* c, const int head[3]);        /* global colouring offset */
 void czb_ctx_set_variant(czb_ctx* c, int variant);
+/* Coordinate vectors of the stretched-grid (`*_maf`) solvers: host arrays of sz[a]+4 entries (= Fortran
+ * X(-1:sz+2)); a NULL vector, or never calling this, gives the reference driver's uniform mesh
+ * x[i] = (REAL)(i-1)*dh (cz_Evaluate.cpp:342-362; global index on j-slabs). */
+void czb_ctx_set_mesh(czb_ctx* c, const CZB_REAL* x, const CZB_REAL* y, const CZB_REAL* z);
 /* bc_k with the context's geometry.  On a j-slab (head[1] > 1) y is evaluated from the GLOBAL plane
  * index, y = dh*(j_global-1), so that the Dirichlet data do not depend on the decomposition. */
 void czb_ctx_bc_k(czb_ctx* c, CZB_REAL* p);           /* 0 = auto (fused), 1 = baseline kernels */
@@ -187,7 +198,8 @@ int czb_apply_ax(czb_ctx* c, CZB_REAL* ap, const CZB_REAL* p, const CZB_REAL* w,
 
 /* Fused solve loop.  solver/precond names follow CZ::setLS / setStrPre
  * (cz_Evaluate.cpp:571-803): jacobi psor sor2sma pbicgstab pcr pcr_eda pcr_esa pcr_rb
- * pcr_rb_esa pcr_j_esa.  X (in/out) and B are device or host pointers, (sz+2g)^3 REALs.
+ * pcr_rb_esa pcr_j_esa and the stretched-grid twins jacobi_maf psor_maf sor2sma_maf pbicgstab_maf
+ * pcr_maf pcr_eda_maf pcr_esa_maf pcr_rb_maf pcr_rb_esa_maf.  X (in/out) and B are device or host pointers, (sz+2g)^3 REALs.
  * hist (host, may be NULL) receives the normalised residual of each iteration
  * (the reference's history file, cz_Poisson.cpp:71); *res the last residual.
  * Returns the reference's iteration count: the converging iteration, itr_max+1 (stationary)
