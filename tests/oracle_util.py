@@ -177,7 +177,8 @@ class OracleCZ:
 
     def sweep_maf(self, kind, X, B, res, mesh, ip=0):
         """One iteration of the MAF twin `kind` (jacobi_maf, psor_maf, sor2sma_maf, pcr_rb_maf, pcr_rb_esa_maf,
-        pcr_maf, pcr_eda_maf, pcr_esa_maf) with the argument lists of cz_Poisson.cpp:50,112,197,565,689,778,861,966."""
+        pcr_maf, pcr_eda_maf, pcr_esa_maf) with the argument lists of cz_Poisson.cpp:50,112,197,565,689,778,861,966.
+        Returns the flop count the kernels added."""
         d = self.dll
         flop = C.c_double(0); om = self.creal(self.ac1); cip = C.c_int(ip)
         xc, yc, zc = [ptr(m) for m in mesh]
@@ -187,17 +188,17 @@ class OracleCZ:
                 self.WRK = self.zeros()
             d.jacobi_maf_(ptr(X), self._sz, self._idx, self.g(), xc, yc, zc, C.byref(om), ptr(B), C.byref(res),
                           ptr(self.WRK), ptr(tmp), C.byref(flop))
-            return
+            return flop.value
         if kind == "psor_maf":
             d.psor_maf_(ptr(X), self._sz, self._idx, self.g(), xc, yc, zc, C.byref(om), ptr(B), C.byref(res),
                         C.byref(flop))
-            return
+            return flop.value
         if kind == "sor2sma_maf":
             for color in (0, 1):
                 cc = C.c_int(color)
                 d.psor2sma_core_maf_(ptr(X), self._sz, self._idx, self.g(), xc, yc, zc, C.byref(cip), C.byref(cc),
                                      C.byref(om), ptr(B), C.byref(res), ptr(tmp), C.byref(flop))
-            return
+            return flop.value
         n = self.idx[5] - self.idx[4] + 1
         pn = C.c_int(get_num_stage(n)); s = C.c_int(2 ** (pn.value - 2))
         M = self.mask(); w = [ptr(a) for a in self.work1d]
@@ -220,6 +221,7 @@ class OracleCZ:
             d.pcr_esa_maf_(*head, C.byref(s), ptr(X), ptr(M), ptr(B), xc, yc, zc, *w, *tail)
         else:
             raise ValueError(kind)
+        return flop.value
 
     # ---- loops (cz_Poisson.cpp) ------------------------------------------------------------
     def stationary(self, kind, X, B, itr_max, coef, converge_check=True, mesh=None):

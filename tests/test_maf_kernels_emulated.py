@@ -1,9 +1,16 @@
-"""CPU run of the DEVICE code of cubez_b200/csrc/maf.cu (tests/tools/emu: CUDA built-ins emulated, one thread per
-block, launches executed sequentially) against the oracle, bit for bit, on a stretched mesh with seeded random fields.
-Covers what a GPU-less container can: index arithmetic, launch geometry (make_tile), colour / wavefront line selection,
-shared-memory ping-pong, the folded 2x2 last stage and the reduction finishers.  The -m gpu tests
-(test_gpu_zz_maf.py) remain the parity tests proper."""
+"""CPU run of the LIBRARY ITSELF for the stretched-grid (MAF) row of SURVEY.md §8f-2: cubez_b200/csrc (abi.cu, solver.cu,
+kernels.cu, maf.cu, runtime.cu) compiled for the CPU by tests/tools/emu (CUDA built-ins emulated with one thread per
+block, launches executed sequentially, device memory = malloc) and driven through the same C ABI the GPU tests use.
+
+* kernel level: every `*_maf_` entry point on a stretched mesh with seeded random fields == the oracle, bit for bit;
+* loop level: czb_solve with the `*_maf` names == the golden histories written by the unmodified reference driver.
+
+This covers what a GPU-less container can: index arithmetic, launch geometry, colour / wavefront line selection,
+shared-memory ping-pong, the folded 2x2 last stage, reduction finishers, host-pointer staging and the loop control.
+It cannot show barrier placement or races; the -m gpu tests (test_gpu_zz_maf.py) remain the parity tests proper, and
+this emulated library is test infrastructure that never ships (the product aborts without a CUDA device)."""
 import ctypes as C
+import json
 import os
 import sys
 
@@ -16,14 +23,21 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(HERE, "tools", "emu"))
 import emu_build  # noqa: E402
 
+GOLDEN = json.load(open(os.path.join(HERE, "golden", "histories.json")))
 _LIBS = {}
 
 
 def _emu(real):
+    import cubez_b200.ffi as ffi
     if not _LIBS:
-        _LIBS.update({k: C.CDLL(v) for k, v in emu_build.build().items()})
+        for k, path in emu_build.build_lib().items():
+            dll = C.CDLL(path)
+            ffi.bind_reference_symbols(dll)
+            ffi.bind_czb_symbols(dll, C.c_float if k == "f32" else C.c_double)
+            dll.czb_init(0)
+            _LIBS[k] = dll
     lib = _LIBS[real]
-    assert lib.emu_real_bytes() == (4 if real == "f32" else 8)
+    assert lib.czb_real_bytes() == (4 if real == "f32" else 8)
     return lib
 
 
@@ -40,64 +54,159 @@ def test_emulated_maf_point_kernels_equal_oracle(real, sz):
     lib = _emu(real)
     o, X, B, mesh, mp = _case(real, sz)
     R = o.creal
-    # jacobi_maf
+    g = o.g()
+    cells = float((sz[0] - 2) * (sz[1] - 2) * (sz[2] - 2))
+    tmp = np.zeros(sz[2] + 4, dtype=o.dt)
+    # jacobi_maf_
     o.ac1 = o.dt(0.8)
-    Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("jacobi_maf", Xo, B, ro, mesh)
-    Xn = X.copy(); res = C.c_double(-1)
-    lib.emu_jacobi_maf(ou.ptr(X), ou.ptr(Xn), ou.ptr(B), o._sz, o._idx, *mp, R(0.8), C.byref(res))
-    assert np.array_equal(Xn, Xo)
+    Xo = X.copy(); ro = C.c_double(0.25); o.sweep_maf("jacobi_maf", Xo, B, ro, mesh)
+    Xe = X.copy(); W = np.zeros_like(X); res = C.c_double(0.25); flop = C.c_double(0); om = R(0.8)
+    lib.jacobi_maf_(ou.ptr(Xe), o._sz, o._idx, g, *mp, C.byref(om), ou.ptr(B), C.byref(res), ou.ptr(W), ou.ptr(tmp), C.byref(flop))
+    assert np.array_equal(Xe, Xo)
     assert res.value == pytest.approx(ro.value, rel=1e-12)
-    # red-black, colour 0 then 1 accumulated
+    assert flop.value == 66.0 * cells
+    # psor2sma_core_maf_, colour 0 then 1
     o.ac1 = o.dt(1.5)
     Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("sor2sma_maf", Xo, B, ro, mesh)
-    Xe = X.copy()
+    Xe = X.copy(); res = C.c_double(0); flop = C.c_double(0); om = R(1.5); ip = C.c_int(0)
     for color in (0, 1):
-        lib.emu_rb_color_maf(ou.ptr(Xe), ou.ptr(B), o._sz, o._idx, *mp, R(1.5), C.c_int(color), C.c_int(color), C.byref(res))
+        cc = C.c_int(color)
+        lib.psor2sma_core_maf_(ou.ptr(Xe), o._sz, o._idx, g, *mp, C.byref(ip), C.byref(cc), C.byref(om), ou.ptr(B),
+                               C.byref(res), ou.ptr(tmp), C.byref(flop))
     assert np.array_equal(Xe, Xo)
     assert res.value == pytest.approx(ro.value, rel=1e-12)
-    # lexicographic SOR through hyperplane wavefronts
+    assert flop.value == 66.0 * cells
+    # psor_maf_ through hyperplane wavefronts
     Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("psor_maf", Xo, B, ro, mesh)
-    Xe = X.copy()
-    lib.emu_psor_maf(ou.ptr(Xe), ou.ptr(B), o._sz, o._idx, *mp, R(1.5), C.byref(res))
+    Xe = X.copy(); res = C.c_double(0)
+    lib.psor_maf_(ou.ptr(Xe), o._sz, o._idx, g, *mp, C.byref(om), ou.ptr(B), C.byref(res), C.byref(flop))
     assert np.array_equal(Xe, Xo)
     assert res.value == pytest.approx(ro.value, rel=1e-12)
-    # pivot, operator (+ fused dot), residual vector
+    # search_pivot_, calc_ax_maf_, calc_rk_maf_
     Po = o.pivot(mesh)
-    Pe = np.zeros_like(X); lib.emu_search_pivot(ou.ptr(Pe), o._sz, o._idx, *mp)
+    Pe = np.zeros_like(X); lib.search_pivot_(ou.ptr(Pe), o._sz, o._idx, g, *mp)
     assert np.array_equal(Pe, Po)
-    flop = C.c_double(0)
-    Ao = np.zeros_like(X); o.dll.calc_ax_maf_(ou.ptr(Ao), ou.ptr(X), o._sz, o._idx, o.g(), *mp, ou.ptr(Po), C.byref(flop))
-    Ae = np.zeros_like(X); dot = C.c_double(0)
-    lib.emu_calc_ax_maf(ou.ptr(Ae), ou.ptr(X), o._sz, o._idx, *mp, ou.ptr(Pe), ou.ptr(B), C.byref(dot))
+    flop = C.c_double(0); fo = C.c_double(0)
+    Ao = np.zeros_like(X); o.dll.calc_ax_maf_(ou.ptr(Ao), ou.ptr(X), o._sz, o._idx, g, *mp, ou.ptr(Po), C.byref(fo))
+    Ae = np.zeros_like(X); lib.calc_ax_maf_(ou.ptr(Ae), ou.ptr(X), o._sz, o._idx, g, *mp, ou.ptr(Pe), C.byref(flop))
     assert np.array_equal(Ae, Ao)
-    assert dot.value == pytest.approx(float(o.dot2(Ao, B)), rel=1e-5 if real == "f32" else 1e-12)
-    Ro = np.zeros_like(X); o.dll.calc_rk_maf_(ou.ptr(Ro), ou.ptr(X), ou.ptr(B), o._sz, o._idx, o.g(), *mp, ou.ptr(Po), C.byref(flop))
-    Re = np.zeros_like(X); lib.emu_calc_rk_maf(ou.ptr(Re), ou.ptr(X), ou.ptr(B), o._sz, o._idx, *mp, ou.ptr(Pe))
+    Ro = np.zeros_like(X); o.dll.calc_rk_maf_(ou.ptr(Ro), ou.ptr(X), ou.ptr(B), o._sz, o._idx, g, *mp, ou.ptr(Po), C.byref(fo))
+    Re = np.zeros_like(X); lib.calc_rk_maf_(ou.ptr(Re), ou.ptr(X), ou.ptr(B), o._sz, o._idx, g, *mp, ou.ptr(Pe), C.byref(flop))
     assert np.array_equal(Re, Ro)
+    assert flop.value == fo.value == 2 * 63.0 * cells
 
 
 @pytest.mark.parametrize("real", ["f32", "f64"])
 @pytest.mark.parametrize("sz", [[9, 9, 9], [12, 7, 23], [10, 8, 34], [8, 6, 66], [6, 6, 131], [7, 5, 300]])
 def test_emulated_maf_line_kernel_equals_oracle(real, sz):
-    """k_pcr_lines_maf: red-black (both colours) and the i+j wavefronts of the lexicographic routines; line lengths of
-    2^m and 2^m +- 1 cells."""
+    """The five MAF line routines (k_pcr_lines_maf: colours and i+j wavefronts); line lengths of 2^m and 2^m +- 1."""
     lib = _emu(real)
     o, X, B, mesh, mp = _case(real, sz)
-    R = o.creal
     M = o.mask()
     o.ac1 = o.dt(1.3)
-    pn = ou.get_num_stage(o.idx[5] - o.idx[4] + 1)
-    res = C.c_double(-1)
-    Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("pcr_rb_maf", Xo, B, ro, mesh)
-    Xe = X.copy()
-    for color in (0, 1):
-        lib.emu_pcr_maf(ou.ptr(Xe), ou.ptr(M), ou.ptr(B), o._sz, o._idx, C.c_int(pn), C.c_int(color), *mp, R(1.3),
-                        C.c_int(color), C.byref(res))
-    assert np.array_equal(Xe, Xo), np.abs(Xe - Xo).max()
-    assert res.value == pytest.approx(ro.value, rel=1e-12)
-    Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("pcr_maf", Xo, B, ro, mesh)
-    Xe = X.copy()
-    lib.emu_pcr_maf(ou.ptr(Xe), ou.ptr(M), ou.ptr(B), o._sz, o._idx, C.c_int(pn), C.c_int(-1), *mp, R(1.3), C.c_int(0),
-                    C.byref(res))
-    assert np.array_equal(Xe, Xo), np.abs(Xe - Xo).max()
-    assert res.value == pytest.approx(ro.value, rel=1e-12)
+    pn = C.c_int(ou.get_num_stage(o.idx[5] - o.idx[4] + 1)); s = C.c_int(2 ** (pn.value - 2)); ip = C.c_int(0)
+    om = o.creal(1.3)
+    g = o.g()
+    w = [None] * 6
+    for kind in ("pcr_rb_maf", "pcr_rb_esa_maf", "pcr_maf", "pcr_eda_maf", "pcr_esa_maf"):
+        Xo = X.copy(); ro = C.c_double(0.5); fo = o.sweep_maf(kind, Xo, B, ro, mesh)
+        Xe = X.copy(); res = C.c_double(0.5); flop = C.c_double(0)
+        head = (o._sz, o._idx, g, C.byref(pn))
+        tail = (C.byref(om), C.byref(res), None, C.byref(flop))
+        fields = (ou.ptr(Xe), ou.ptr(M), ou.ptr(B))
+        if kind == "pcr_rb_maf":
+            for color in (0, 1):
+                cc = C.c_int(color)
+                lib.pcr_rb_maf_(*head, C.byref(ip), C.byref(cc), *fields, *mp, *w, *tail)
+        elif kind == "pcr_rb_esa_maf":
+            for color in (0, 1):
+                cc = C.c_int(color)
+                lib.pcr_rb_esa_maf_(*head, C.byref(ip), C.byref(cc), C.byref(s), *fields, *mp, *w, *tail)
+        elif kind == "pcr_maf":
+            lib.pcr_maf_(*head, *fields, *mp, *w, *tail)
+        elif kind == "pcr_eda_maf":
+            lib.pcr_eda_maf_(*head, *fields, *mp, *w[:3], *tail)
+        else:
+            lib.pcr_esa_maf_(*head, C.byref(s), *fields, *mp, *w, *tail)
+        assert np.array_equal(Xe, Xo), (kind, np.abs(Xe - Xo).max())
+        assert res.value == pytest.approx(ro.value, rel=1e-12), kind
+        assert flop.value == fo, kind
+
+
+def _solve(lib, real, n, solver, precond, itr_max, coef, mesh=None):
+    o = ou.OracleCZ([n] * 3, real)
+    P, RHS = o.setup_laplace()                         # Dirichlet data from the oracle's bc_k (host libm, as the library's table)
+    ctx = lib.czb_ctx_create(o._sz, o._idx, o._nID, o.creal(o.pitch), o._org)
+    if mesh is not None:
+        lib.czb_ctx_set_mesh(ctx, *[ou.ptr(m) for m in mesh])
+    hist = (C.c_double * (itr_max + 2))()
+    res = C.c_double(0); flop = C.c_double(0)
+    itr = lib.czb_solve(ctx, solver.encode(), precond.encode() if precond else None, ou.ptr(P), ou.ptr(RHS), itr_max,
+                        o.creal(coef), C.byref(res), hist, itr_max + 2, C.byref(flop))
+    lib.czb_ctx_destroy(ctx)
+    nh = min(itr, itr_max - 1 if solver.startswith("pbicgstab") else itr_max)
+    return o, itr, res.value, np.array(hist[:nh]), P, flop.value
+
+
+MAF = [i for i, g in enumerate(GOLDEN) if g["solver"].endswith("_maf") and g["real"] == "f32"] + \
+      [i for i, g in enumerate(GOLDEN) if g["solver"] == "sor2sma_maf" and g["real"] == "f64"]
+
+
+@pytest.mark.parametrize("gi", MAF, ids=lambda i: "%s-%d-%s-%s" % (
+    GOLDEN[i]["real"], GOLDEN[i]["n"], GOLDEN[i]["solver"], GOLDEN[i]["precond"]))
+def test_emulated_maf_solve_matches_reference_history(gi):
+    """czb_solve (solver.cu loops: batching, device-resident convergence flag, ping-pong, preconditioner dispatch,
+    BiCGstab scalars) with the MAF kernels against the golden histories of the unmodified reference driver."""
+    g = GOLDEN[gi]
+    real = g["real"]
+    lib = _emu(real)
+    o, itr, res, hist, P, flop = _solve(lib, real, g["n"], g["solver"], g["precond"], g["itr_max"], float(g["coef"]))
+    gh = np.array([float(h) for h in g["history"]])
+    if g["solver"] != "pbicgstab_maf":
+        assert itr == g["itr"]
+        assert len(hist) == len(gh)
+        np.testing.assert_allclose(hist, gh, rtol=2e-6)               # golden file has 7 digits
+        Po, RHSo = o.setup_laplace()
+        itr_o, res_o, hist_o = o.stationary(g["solver"], Po, RHSo, g["itr_max"], float(g["coef"]))
+        assert itr == itr_o
+        assert np.array_equal(P, Po), "field differs from the oracle (max %g)" % np.abs(P - Po).max()
+        np.testing.assert_allclose(hist, hist_o, rtol=1e-12)
+        assert flop > 0
+    else:
+        assert abs(itr - g["itr"]) <= 1
+        m = min(len(gh), len(hist))
+        assert m >= len(gh) - 1
+        if g["precond"] == "none":
+            np.testing.assert_allclose(hist[:6], gh[:6], rtol=1e-5)
+        else:
+            np.testing.assert_allclose(hist[:m], gh[:m], rtol=1e-4, atol=1e-12)
+
+
+def test_emulated_plain_solvers_still_match_golden():
+    """The same emulated library on the uniform-grid baseline kernels (kernels.cu; fused.cu is stubbed out, so the loops
+    take the per-colour path): guards the loop code shared by the plain and the MAF solvers."""
+    lib = _emu("f32")
+    for solver, coef in (("jacobi", "0.8"), ("sor2sma", "1.5"), ("psor", "1.5")):
+        g = [c for c in GOLDEN if c["real"] == "f32" and c["n"] == 32 and c["solver"] == solver and c["coef"] == coef][0]
+        o, itr, res, hist, P, flop = _solve(lib, "f32", 32, solver, None, g["itr_max"], float(coef))
+        assert itr == g["itr"]
+        np.testing.assert_allclose(hist, [float(h) for h in g["history"]], rtol=2e-6)
+    for pc in ("sor2sma", "jacobi"):
+        g = [c for c in GOLDEN if c["real"] == "f32" and c["n"] == 32 and c["solver"] == "pbicgstab" and c["precond"] == pc][0]
+        o, itr, res, hist, P, flop = _solve(lib, "f32", 32, "pbicgstab", pc, g["itr_max"], float(g["coef"]))
+        gh = np.array([float(h) for h in g["history"]])
+        assert abs(itr - g["itr"]) <= 1
+        m = min(len(gh), len(hist))
+        np.testing.assert_allclose(hist[:m], gh[:m], rtol=1e-4, atol=1e-12)
+
+
+def test_emulated_stretched_mesh_solve_equals_oracle():
+    lib = _emu("f32")
+    o = ou.OracleCZ([24] * 3, "f32")
+    mesh = o.mesh(stretch=0.2)
+    o2, itr, res, hist, P, flop = _solve(lib, "f32", 24, "sor2sma_maf", None, 500, 1.5, mesh=mesh)
+    Po, RHSo = o.setup_laplace()
+    itr_o, res_o, hist_o = o.stationary("sor2sma_maf", Po, RHSo, 500, 1.5, mesh=mesh)
+    assert itr == itr_o
+    assert np.array_equal(P, Po)
+    np.testing.assert_allclose(hist, hist_o, rtol=1e-12)

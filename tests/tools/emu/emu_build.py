@@ -1,7 +1,13 @@
-"""TEST INFRASTRUCTURE: builds tests/tools/emu/libemu_maf_{f32,f64}.so -- the device code of cubez_b200/csrc/maf.cu
-compiled for the CPU (see emu_maf.cpp).  The only source transformation is the launch syntax:
+"""TEST INFRASTRUCTURE: builds tests/tools/emu/_build/libczb200_emu_{f32,f64}.so -- the library compiled for the CPU:
+host code and every kernel that is plain CUDA C++ (kernels.cu, maf.cu, solver.cu's loop-control kernels) over an
+emulation of the CUDA built-ins (emu_prelude.h: one thread per block, launches executed sequentially) and of the
+runtime calls (emu_cudart.cpp: device memory = malloc).  With -ffp-contract=off the REAL arithmetic is the IEEE
+arithmetic nvcc emits under -fmad=false, so fields must equal the oracle bit for bit.  What this cannot show is anything
+that depends on real concurrency (barriers, races) or on fused.cu / pcr.cu (TMA, tensor memory, inline PTX: replaced by
+emu_stubs.cpp) -- that stays with the -m gpu tests.  The only source transformations are the launch syntax:
     k<<<grid, block, smem, stream>>>(args);   ->   emu_launch(grid, block, [&]{ k(args); });
-applied to maf.cu and to the headers it includes from cubez_b200/csrc (cells.cuh); everything else is compiled as is."""
+and `extern __shared__ T name[];` -> `static T name[1 << 16];`, applied to the .cu sources and to cells.cuh; everything
+else is compiled as is."""
 import os
 import re
 import subprocess
@@ -9,6 +15,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(HERE)))
 CSRC = os.path.join(ROOT, "cubez_b200", "csrc")
+DYN_SHARED = re.compile(r"extern\s+__shared__\s+(\w+)\s+(\w+)\[\];")
 LAUNCH = re.compile(r"(\b\w+(?:<[^<>;(){}]*>)?)\s*<<<\s*([^;]*?)>>>\s*\((.*?)\);", re.S)
 
 
@@ -16,38 +23,44 @@ def _rewrite(text):
     def sub(m):
         cfg = [c.strip() for c in m.group(2).split(",")]
         return "emu_launch(dim3(%s), dim3(%s), [&] { %s(%s); });" % (cfg[0], cfg[1], m.group(1), m.group(3))
+    text = DYN_SHARED.sub(r"static \1 \2[1 << 16];", text)   # dynamic shared memory -> a static pool (512 KB)
     return LAUNCH.sub(sub, text)
 
 
-def generate(outdir):
-    """maf.cu with cells.cuh inlined (both rewritten) -> maf_emu_gen.inc; kernels.cuh / common.cuh are included as is."""
-    maf = open(os.path.join(CSRC, "maf.cu")).read()
-    cells = open(os.path.join(CSRC, "cells.cuh")).read().replace("#pragma once", "")
-    cells = cells.replace('#include "kernels.cuh"', "")
-    maf = maf.replace('#include "cells.cuh"', _rewrite(cells))
-    gen = _rewrite(maf)
-    assert "<<<" not in gen
-    path = os.path.join(outdir, "maf_emu_gen.inc")
-    with open(path, "w") as f:
-        f.write(gen)
-    return path
+LIB_SOURCES = ("kernels.cu", "maf.cu", "runtime.cu", "abi.cu", "solver.cu", "comm.cpp")
 
 
-def build(outdir=None):
+def build_lib(outdir=None):
+    """libczb200_emu_{f32,f64}.so: the library's host code + every kernel that is plain CUDA C++ (kernels.cu, maf.cu,
+    the loop-control kernels of solver.cu) compiled for the CPU over emu_prelude.h / emu_cudart.cpp; fused.cu and
+    pcr.cu (TMA, tensor memory, inline PTX) are replaced by emu_stubs.cpp."""
     outdir = outdir or os.path.join(HERE, "_build")
-    os.makedirs(outdir, exist_ok=True)
-    generate(outdir)
+    gen = os.path.join(outdir, "lib")
+    os.makedirs(gen, exist_ok=True)
+    hdr = os.path.join(ROOT, "include", "czb200.h")
+    with open(os.path.join(gen, "cells.cuh"), "w") as f:      # found first by the generated sources' #include "cells.cuh"
+        f.write(_rewrite(open(os.path.join(CSRC, "cells.cuh")).read()))
+    srcs = []
+    for name in LIB_SOURCES:
+        text = _rewrite(open(os.path.join(CSRC, name)).read())
+        assert "<<<" not in text, name
+        text = text.replace('"../../include/czb200.h"', '"%s"' % hdr)
+        out = os.path.join(gen, name.replace(".cu", "_emu.cpp").replace("comm.cpp", "comm_emu.cpp"))
+        with open(out, "w") as f:
+            f.write('#include "emu_prelude.h"\n' + text)
+        srcs.append(out)
+    srcs += [os.path.join(HERE, "emu_cudart.cpp"), os.path.join(HERE, "emu_stubs.cpp")]
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
     cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
     libs = {}
     for real, flag in (("f32", []), ("f64", ["-D_REAL_IS_DOUBLE_"])):
-        so = os.path.join(outdir, "libemu_maf_%s.so" % real)
-        cmd = [cxx, "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-w", "-I" + outdir, "-I" + CSRC,
-               "-I" + cuda_inc] + flag + ["-o", so, os.path.join(HERE, "emu_maf.cpp")]
+        so = os.path.join(outdir, "libczb200_emu_%s.so" % real)
+        cmd = [cxx, "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-w", "-I" + HERE, "-I" + CSRC,
+               "-I" + cuda_inc] + flag + ["-Wl,-Bsymbolic", "-o", so] + srcs + ["-ldl"]
         subprocess.check_call(cmd)
         libs[real] = so
     return libs
 
 
 if __name__ == "__main__":
-    print(build())
+    print(build_lib())
