@@ -4,6 +4,7 @@
 // result is visible to the host.  Array arguments are device pointers (zero copy) or host
 // pointers (staged, runtime.h).  The flop formulas are the reference's analytic counts.
 #include "runtime.h"
+#include <vector>
 #include "../../include/czb200.h"
 
 using namespace czb;
@@ -299,7 +300,53 @@ void search_pivot_(REAL* pvt, int* sz, int* idx, int* g, REAL* X, REAL* Y, REAL*
 }
 
 // ------------------------------------------------------------------ cz_utility.f90
-void fileout_t_(int*, int*, REAL*, REAL*, REAL*, char*) {}   // compiled out unless _aurora_ (:33-44)
+// cz_utility.f90:17-44.  The reference compiles the body out unless _aurora_==1, so by default this is a no-op as
+// there; with CZB_FILEOUT=1 it writes the same .sph record sequence (Fortran unformatted sequential, 4-byte record
+// markers as gfortran writes them): (1,1) / (ix,jx,kx) / org(1:3) / (dh,dh,dh) / (nn=0, rtime=0) /
+// (((s(k,i,j), i=1,ix), j=1,jx), k=1,kx).  s may be a host or a device pointer.
+void fileout_t_(int* sz, int* g, REAL* s, REAL* dh, REAL* org, char* fname) {
+  static const bool on = getenv("CZB_FILEOUT") != nullptr;
+  if (!on) return;
+  const Geo G = make_geo(sz, nullptr, *g);
+  const size_t n = (size_t)G.total;
+  std::vector<REAL> host;
+  const REAL* h = s;
+  if (is_device_ptr(s)) {
+    Runtime& R = rt();
+    host.resize(n);
+    CZB_CHECK(cudaMemcpyAsync(host.data(), s, sizeof(REAL) * n, cudaMemcpyDeviceToHost, R.stream));
+    R.sync();
+    h = host.data();
+  }
+  char name[21];                                   // character*20, blank padded on the Fortran side
+  size_t len = 0;
+  while (len < 20 && fname[len] != '\0' && fname[len] != ' ') { name[len] = fname[len]; ++len; }
+  name[len] = '\0';
+  FILE* f = fopen(name, "wb");
+  if (!f) { fprintf(stderr, "czb200: fileout_t_: cannot open '%s'\n", name); return; }
+  auto record = [&](const void* data, size_t bytes) {
+    const int32_t m = (int32_t)bytes;
+    fwrite(&m, 4, 1, f); fwrite(data, 1, bytes, f); fwrite(&m, 4, 1, f);
+  };
+  const int one[2] = {1, 1};
+  record(one, sizeof(one));
+  const int dims[3] = {G.ix, G.jx, G.kx};
+  record(dims, sizeof(dims));
+  const REAL o3[3] = {org[0], org[1], org[2]};
+  record(o3, sizeof(o3));
+  const REAL d3[3] = {*dh, *dh, *dh};
+  record(d3, sizeof(d3));
+  unsigned char step[sizeof(int) + sizeof(REAL)] = {0};   // nn = 0 (integer), rtime = 0.0 (REAL), packed
+  record(step, sizeof(step));
+  std::vector<REAL> out((size_t)G.ix * G.jx * G.kx);
+  size_t q = 0;
+  for (int k = 1; k <= G.kx; ++k)
+    for (int j = 1; j <= G.jx; ++j)
+      for (int i = 1; i <= G.ix; ++i) out[q++] = h[G.at(k, i, j)];
+  if (out.size() * sizeof(REAL) > 0x7fffffffu) fprintf(stderr, "czb200: fileout_t_: record longer than 2 GiB, markers wrap\n");
+  record(out.data(), out.size() * sizeof(REAL));
+  fclose(f);
+}
 
 void exact_t_(int* sz, int* g, REAL* e, REAL* dh, REAL* org) {
   Runtime& R = rt();

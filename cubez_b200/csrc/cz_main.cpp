@@ -93,13 +93,20 @@ int main(int argc, char* argv[]) {
   const double ms = czb_last_solve_ms(ctx);
   const double cells = (double)(size[0] - 2) * (size[1] - 2) * (size[2] - 2);
   printf("\nSolver loop : %.3f ms on device, %.3f GLUPS (%d iterations)\n", ms, ms > 0 ? cells * nh / ms * 1e-6 : 0.0, nh);
+  // the reference reports its analytic flop counters per phase through PMlib (profiling.txt, cz_Evaluate.cpp:492-541)
+  printf("Flop count  : %.6e (the reference's analytic formulas), %.2f GFLOP/s\n", flop, ms > 0 ? flop / ms * 1e-6 : 0.0);
 
   // debug_mode==1 (always on, main.cpp:38-42): error against the analytic solution, :550-563
   REAL_TYPE* ERR = (REAL_TYPE*)czb_malloc(bytes);
   double errmax = 0.0; int loc[3];
+  char tmp_fname[30];
+  sprintf(tmp_fname, "p_%05d.sph", 0);
+  fileout_t_(size, &gc, P, pitch, origin, tmp_fname);                          // :554-555 (written when CZB_FILEOUT=1)
   exact_t_(size, &gc, ERR, pitch, origin);
   err_t_(size, innerFidx, &gc, &errmax, P, ERR, loc);
   printf("\nError max = %e at (%d %d %d)\n\n", errmax, loc[0], loc[1], loc[2]);
+  sprintf(tmp_fname, "e_%05d.sph", 0);
+  fileout_t_(size, &gc, ERR, pitch, origin, tmp_fname);                        // :560-561
 
   czb_free(ERR); czb_free(P); czb_free(RHS);
   czb_ctx_destroy(ctx);

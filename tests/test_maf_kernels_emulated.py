@@ -210,3 +210,55 @@ def test_emulated_stretched_mesh_solve_equals_oracle():
     assert itr == itr_o
     assert np.array_equal(P, Po)
     np.testing.assert_allclose(hist, hist_o, rtol=1e-12)
+
+
+def test_emulated_fileout_sph_records(tmp_path, monkeypatch):
+    """fileout_t_ (cz_utility.f90:17-44) with CZB_FILEOUT=1: the .sph record sequence of the reference's _aurora_ build.
+    Run in a fresh process because the switch is read once."""
+    import subprocess
+    code = r'''
+import ctypes as C, os, sys, struct
+import numpy as np
+sys.path.insert(0, %r); sys.path.insert(0, %r)
+import emu_build, cubez_b200.ffi as ffi
+dll = C.CDLL(emu_build.build_lib()["f32"]); ffi.bind_reference_symbols(dll)
+sz = (C.c_int * 3)(5, 4, 3); g = C.c_int(2)
+s = np.arange(9 * 8 * 7, dtype=np.float32).reshape(8, 9, 7)          # [j][i][k] with guards
+dh = C.c_float(0.25); org = (C.c_float * 3)(1.0, 2.0, 3.0)
+dll.fileout_t_(sz, C.byref(g), C.c_void_p(s.ctypes.data), C.byref(dh), org, b"p_00000.sph")
+raw = open("p_00000.sph", "rb").read()
+recs, o = [], 0
+while o < len(raw):
+    n = struct.unpack_from("<i", raw, o)[0]; recs.append(raw[o + 4:o + 4 + n]); assert struct.unpack_from("<i", raw, o + 4 + n)[0] == n; o += n + 8
+assert [len(r) for r in recs] == [8, 12, 12, 12, 8, 5 * 4 * 3 * 4], [len(r) for r in recs]
+assert struct.unpack("<2i", recs[0]) == (1, 1) and struct.unpack("<3i", recs[1]) == (5, 4, 3)
+assert struct.unpack("<3f", recs[2]) == (1.0, 2.0, 3.0) and struct.unpack("<3f", recs[3]) == (0.25, 0.25, 0.25)
+data = np.frombuffer(recs[5], dtype=np.float32).reshape(3, 4, 5)     # [k][j][i]
+assert np.array_equal(data, s[2:6, 2:7, 2:5].transpose(2, 0, 1))
+print("ok")
+''' % (os.path.join(HERE, "tools", "emu"), os.path.dirname(HERE))
+    env = dict(os.environ, CZB_FILEOUT="1")
+    p = subprocess.run([sys.executable, "-c", code], cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0 and "ok" in p.stdout, p.stdout + p.stderr
+
+
+def test_emulated_cz_driver_cli_maf(tmp_path):
+    """The product's `cz` driver (reference CLI, console and history-file format) over the emulated library: a `_maf`
+    run writes the golden history, reports the analytic flop count and, with CZB_FILEOUT=1, the two .sph dumps."""
+    import subprocess
+    exe = emu_build.build_cz()
+    g = [c for c in GOLDEN if c["real"] == "f32" and c["n"] == 32 and c["solver"] == "sor2sma_maf"][0]
+    p = subprocess.run([exe, "32", "32", "32", "sor2sma_maf", str(g["itr_max"]), g["coef"]], cwd=str(tmp_path),
+                       env=dict(os.environ, CZB_FILEOUT="1"), capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout + p.stderr
+    txt = open(os.path.join(str(tmp_path), "sor2sma_maf.txt")).read().split("\n")
+    assert txt[0] == "Itration      Residual"
+    assert "Iter = %d" % g["itr"] in p.stdout
+    hist = np.array([float(l.split(",")[1]) for l in txt[1:] if l.strip()])
+    np.testing.assert_allclose(hist, [float(h) for h in g["history"]], rtol=2e-6)
+    err = float(p.stdout.split("Error max = ")[1].split()[0])
+    assert abs(err - float(g["errmax"])) < 1e-6
+    flop = float(p.stdout.split("Flop count  : ")[1].split()[0])
+    assert flop == pytest.approx(66.0 * 30 ** 3 * g["itr"], rel=1e-6)        # cz_maf.f90:330-333, both colours
+    for name in ("p_00000.sph", "e_00000.sph"):
+        assert os.path.getsize(os.path.join(str(tmp_path), name)) == (8 + 12 + 12 + 12 + 8 + 32 ** 3 * 4) + 6 * 8

@@ -38,6 +38,11 @@ def build_lib(outdir=None):
     gen = os.path.join(outdir, "lib")
     os.makedirs(gen, exist_ok=True)
     hdr = os.path.join(ROOT, "include", "czb200.h")
+    done = {r: os.path.join(outdir, "libczb200_emu_%s.so" % r) for r in ("f32", "f64")}
+    deps = [hdr] + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h", ".cpp"))] + \
+           [os.path.join(HERE, f) for f in os.listdir(HERE) if f.endswith((".cpp", ".h", ".py"))]
+    if all(os.path.exists(so) and os.path.getmtime(so) >= max(os.path.getmtime(d) for d in deps) for so in done.values()):
+        return done
     with open(os.path.join(gen, "cells.cuh"), "w") as f:      # found first by the generated sources' #include "cells.cuh"
         f.write(_rewrite(open(os.path.join(CSRC, "cells.cuh")).read()))
     srcs = []
@@ -60,6 +65,17 @@ def build_lib(outdir=None):
         subprocess.check_call(cmd)
         libs[real] = so
     return libs
+
+
+def build_cz(outdir=None):
+    """cz_emu_f32: the product's `cz` driver (cubez_b200/csrc/cz_main.cpp, unchanged) linked to the emulated library."""
+    outdir = outdir or os.path.join(HERE, "_build")
+    libs = build_lib(outdir)
+    exe = os.path.join(outdir, "cz_emu_f32")
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    subprocess.check_call([cxx, "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-o", exe,
+                           os.path.join(CSRC, "cz_main.cpp"), libs["f32"], "-Wl,-rpath," + outdir])
+    return exe
 
 
 if __name__ == "__main__":
