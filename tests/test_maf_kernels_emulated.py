@@ -262,3 +262,41 @@ def test_emulated_cz_driver_cli_maf(tmp_path):
     assert flop == pytest.approx(66.0 * 30 ** 3 * g["itr"], rel=1e-6)        # cz_maf.f90:330-333, both colours
     for name in ("p_00000.sph", "e_00000.sph"):
         assert os.path.getsize(os.path.join(str(tmp_path), name)) == (8 + 12 + 12 + 12 + 8 + 32 ** 3 * 4) + 6 * 8
+
+
+@pytest.mark.parametrize("real,sz,color", [("f32", [8, 7, 34], 0), ("f32", [8, 7, 34], 1), ("f32", [6, 5, 131], -1),
+                                           ("f64", [7, 6, 70], 1), ("f32", [5, 5, 300], 0)])
+def test_line_kernel_with_real_threads_under_thread_sanitizer(real, sz, color, tmp_path):
+    """k_pcr_lines_maf with one std::thread per CUDA thread and std::barrier for __syncthreads, built with
+    -fsanitize=thread (tests/tools/emu/simt_line.cpp): no data race on the shared a / c / d rows (ThreadSanitizer
+    would make the program exit non-zero) and the field still equals the oracle bit for bit."""
+    import subprocess
+    exe = emu_build.build_simt()[real]
+    o, X, B, mesh, mp = _case(real, sz)
+    M = o.mask()
+    o.ac1 = o.dt(1.3)
+    pn = ou.get_num_stage(o.idx[5] - o.idx[4] + 1)
+    # oracle: one colour, or all lines in (j,i) order
+    Xo = X.copy(); ro = C.c_double(0)
+    if color >= 0:
+        flop = C.c_double(0); om = o.creal(1.3); cpn = C.c_int(pn); ip = C.c_int(0); cc = C.c_int(color)
+        tmp = np.zeros(sz[2] + 4, dtype=o.dt); w = [ou.ptr(a) for a in o.work1d]
+        o.dll.pcr_rb_maf_(o._sz, o._idx, o.g(), C.byref(cpn), C.byref(ip), C.byref(cc), ou.ptr(Xo), ou.ptr(M), ou.ptr(B), *mp, *w,
+                          C.byref(om), C.byref(ro), ou.ptr(tmp), C.byref(flop))
+    else:
+        o.sweep_maf("pcr_maf", Xo, B, ro, mesh)
+    inp, outp = os.path.join(str(tmp_path), "in.bin"), os.path.join(str(tmp_path), "out.bin")
+    with open(inp, "wb") as f:
+        f.write(np.array(list(sz) + list(o.idx) + [pn, color], dtype=np.int32).tobytes())
+        f.write(np.array([1.3], dtype=o.dt).tobytes())
+        for a in (X, M, B, *mesh):
+            f.write(np.ascontiguousarray(a, dtype=o.dt).tobytes())
+    p = subprocess.run([exe, inp, outp], capture_output=True, text=True, timeout=900,
+                       env=dict(os.environ, TSAN_OPTIONS="halt_on_error=0 exitcode=66"))
+    assert p.returncode == 0, "ThreadSanitizer / driver: rc %d\n%s" % (p.returncode, p.stderr[-3000:])
+    assert "WARNING: ThreadSanitizer" not in p.stderr
+    raw = open(outp, "rb").read()
+    Xs = np.frombuffer(raw[:X.nbytes], dtype=o.dt).reshape(X.shape)
+    res = np.frombuffer(raw[X.nbytes:], dtype=np.float64)[0]
+    assert np.array_equal(Xs, Xo), np.abs(Xs - Xo).max()
+    assert res == pytest.approx(ro.value, rel=1e-12)

@@ -78,5 +78,29 @@ def build_cz(outdir=None):
     return exe
 
 
+def build_simt(outdir=None):
+    """simt_line_{f32,f64}: maf.cu's line kernel with every CUDA thread of a block as a std::thread (simt_line.cpp),
+    built with ThreadSanitizer as a stand-alone program."""
+    outdir = outdir or os.path.join(HERE, "_build")
+    gen = os.path.join(outdir, "simt")
+    os.makedirs(gen, exist_ok=True)
+    maf = open(os.path.join(CSRC, "maf.cu")).read()
+    cells = open(os.path.join(CSRC, "cells.cuh")).read().replace("#pragma once", "").replace('#include "kernels.cuh"', "")
+    text = _rewrite(maf.replace('#include "cells.cuh"', cells))
+    assert "<<<" not in text
+    with open(os.path.join(gen, "maf_simt_gen.inc"), "w") as f:
+        f.write(text)
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+    libs = {}
+    for real, flag in (("f32", []), ("f64", ["-D_REAL_IS_DOUBLE_"])):
+        exe = os.path.join(outdir, "simt_line_%s" % real)
+        subprocess.check_call([cxx, "-O1", "-g", "-std=c++20", "-ffp-contract=off", "-fsanitize=thread", "-w",
+                               "-I" + gen, "-I" + CSRC, "-I" + cuda_inc] + flag +
+                              ["-o", exe, os.path.join(HERE, "simt_line.cpp"), "-lpthread"])
+        libs[real] = exe
+    return libs
+
+
 if __name__ == "__main__":
     print(build_lib())
