@@ -1,229 +1,26 @@
-"""GPU parity tests of the stretched-grid (MAF) twins, SURVEY.md §8f-2 (maf.cu): every `*_maf_` entry point of the
-reference's kernel ABI through ctypes against the CPU oracle on a STRETCHED mesh with seeded random fields (bit-exact
-REAL fields), and the `*_maf` solve loops against the golden histories the unmodified reference driver wrote.
+"""GPU parity of the stretched-grid (MAF) twins, SURVEY.md §8f-2: runs tests/gpu_maf_cases.py (42 cases: every `*_maf_`
+entry point against the oracle bit for bit, the `_maf` solve loops against the reference driver's golden histories,
+the unmodified reference driver on libczb200) in a CHILD process.
 
-STATUS: written after the round-1 GPU budget was spent, so none of this has run on hardware yet.  The tests are
-marked xfail(strict=False) for that one reason -- a pass shows up as XPASS, a failure as XFAIL, neither hides the
-result nor stops the rest of the suite -- and the mark is to be removed as soon as one hardware run is green."""
-import ctypes as C
-import json
+STATUS: maf.cu was written after the round-1 GPU budget was spent and has not run on hardware yet (on the CPU the same
+source is green against the oracle, tests/test_maf_kernels_emulated.py).  Hence two precautions, both to be removed after
+the first green hardware run: the child process (a device fault or a hang in new kernels must not take the main GPU
+suite down) and a non-strict xfail mark (XPASS = the 42 cases passed, XFAIL = see the captured output)."""
 import os
+import subprocess
+import sys
 
-import numpy as np
 import pytest
 
-import oracle_util as ou
-
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.xfail(strict=False, reason="MAF kernels: first hardware run pending (round-1 GPU budget exhausted)")]
-HERE = os.path.dirname(os.path.abspath(__file__))
-GOLDEN = json.load(open(os.path.join(HERE, "golden", "histories.json")))
-MAF = [i for i, g in enumerate(GOLDEN) if g["solver"].endswith("_maf")]
-SUM_RTOL = 1e-13
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _mk(sz, real):
-    import cubez_b200
-    cz = cubez_b200.CZ(sz, real)
-    o = ou.OracleCZ(sz, real)
-    return cz, o
-
-
-@pytest.mark.parametrize("real", ["f32", "f64"])
-@pytest.mark.parametrize("sz", [[12, 7, 23], [16, 16, 37], [40, 33, 66]])
-@pytest.mark.parametrize("host_ptrs", [False, True])
-def test_maf_point_sweeps_operator_and_pivot(real, sz, host_ptrs):
-    cz, o = _mk(sz, real)
-    X, B = ou.random_fields(o.shape, o.dt)
-    mesh = o.mesh(stretch=0.3)
-    mp = [ou.ptr(m) for m in mesh]                         # coordinate vectors stay on the host (staged per call)
-    g = C.byref(cz._g)
-    cells = float((sz[0] - 2) * (sz[1] - 2) * (sz[2] - 2))
-    tmp = np.zeros(sz[2] + 4, dtype=o.dt)
-
-    def dev(a):
-        return a.copy() if host_ptrs else cz.from_numpy(a)
-
-    def host(t):
-        return t if host_ptrs else t.cpu().numpy()
-
-    cz.sync_stream()
-    # jacobi_maf (cz_maf.f90:131-282)
-    o.ac1 = o.dt(0.8)
-    Xo = X.copy(); ro = C.c_double(0.25); o.sweep_maf("jacobi_maf", Xo, B, ro, mesh)
-    Xg, Bg, Wg = dev(X), dev(B), dev(np.zeros_like(X))
-    res = C.c_double(0.25); flop = C.c_double(0); om = cz.creal(0.8)
-    cz.dll.jacobi_maf_(cz._ptr(Xg), cz._sz, cz._idx, g, *mp, C.byref(om), cz._ptr(Bg), C.byref(res), cz._ptr(Wg),
-                       ou.ptr(tmp), C.byref(flop))
-    assert np.array_equal(host(Xg), Xo)
-    assert res.value == pytest.approx(ro.value, rel=SUM_RTOL)
-    assert flop.value == 66.0 * cells
-    # psor2sma_core_maf, colour 0 then 1 (cz_maf.f90:301-438)
-    o.ac1 = o.dt(1.5)
-    Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("sor2sma_maf", Xo, B, ro, mesh)
-    Xg = dev(X); res = C.c_double(0); flop = C.c_double(0); om = cz.creal(1.5); ip = C.c_int(0)
-    for color in (0, 1):
-        cc = C.c_int(color)
-        cz.dll.psor2sma_core_maf_(cz._ptr(Xg), cz._sz, cz._idx, g, *mp, C.byref(ip), C.byref(cc), C.byref(om),
-                                  cz._ptr(Bg), C.byref(res), ou.ptr(tmp), C.byref(flop))
-    assert np.array_equal(host(Xg), Xo)
-    assert res.value == pytest.approx(ro.value, rel=SUM_RTOL)
-    assert flop.value == 66.0 * cells
-    # psor_maf in the reference's 1-thread order (cz_maf.f90:23-114)
-    Xo = X.copy(); ro = C.c_double(0); o.sweep_maf("psor_maf", Xo, B, ro, mesh)
-    Xg = dev(X); res = C.c_double(0)
-    cz.dll.psor_maf_(cz._ptr(Xg), cz._sz, cz._idx, g, *mp, C.byref(om), cz._ptr(Bg), C.byref(res), C.byref(flop))
-    assert np.array_equal(host(Xg), Xo)
-    assert res.value == pytest.approx(ro.value, rel=SUM_RTOL)
-    # search_pivot, calc_ax_maf, calc_rk_maf (cz_blas.f90:738-1039)
-    Po = o.pivot(mesh)
-    Pg = dev(np.zeros_like(X))
-    cz.dll.search_pivot_(cz._ptr(Pg), cz._sz, cz._idx, g, *mp)
-    assert np.array_equal(host(Pg), Po)
-    flop = C.c_double(0); fo = C.c_double(0)
-    Ao = np.zeros_like(X); o.dll.calc_ax_maf_(ou.ptr(Ao), ou.ptr(X), o._sz, o._idx, o.g(), *mp, ou.ptr(Po), C.byref(fo))
-    Ag, Xg = dev(np.zeros_like(X)), dev(X)
-    cz.dll.calc_ax_maf_(cz._ptr(Ag), cz._ptr(Xg), cz._sz, cz._idx, g, *mp, cz._ptr(Pg), C.byref(flop))
-    assert np.array_equal(host(Ag), Ao)
-    Ro = np.zeros_like(X); o.dll.calc_rk_maf_(ou.ptr(Ro), ou.ptr(X), ou.ptr(B), o._sz, o._idx, o.g(), *mp, ou.ptr(Po), C.byref(fo))
-    Rg = dev(np.zeros_like(X))
-    cz.dll.calc_rk_maf_(cz._ptr(Rg), cz._ptr(Xg), cz._ptr(Bg), cz._sz, cz._idx, g, *mp, cz._ptr(Pg), C.byref(flop))
-    assert np.array_equal(host(Rg), Ro)
-    assert flop.value == fo.value == 2 * 63.0 * cells
-    cz.close()
-
-
-@pytest.mark.parametrize("real", ["f32", "f64"])
-@pytest.mark.parametrize("sz", [[9, 9, 9], [12, 7, 23], [10, 8, 34], [8, 6, 66], [6, 6, 131], [6, 5, 300]])
-def test_maf_line_sor_sweeps(real, sz):
-    """The five MAF line routines (pn-1 PCR stages + 2x2, line-dependent coefficients) incl. line lengths of 2^m and
-    2^m +- 1 cells; res is TWICE the sum of squares, as in the reference (cz_maf.f90:635-636, 657-660)."""
-    cz, o = _mk(sz, real)
-    X, B = ou.random_fields(o.shape, o.dt)
-    mesh = o.mesh(stretch=0.3)
-    M = o.mask()
-    o.ac1 = o.dt(1.3)
-    n = o.idx[5] - o.idx[4] + 1
-    pn = C.c_int(ou.get_num_stage(n)); s = C.c_int(2 ** (pn.value - 2)); ip = C.c_int(0)
-    om = cz.creal(1.3)
-    g = C.byref(cz._g)
-    import torch
-    md = [torch.from_numpy(m).to(cz.device) for m in mesh]    # coordinate vectors on the DEVICE this time
-    mp = [C.c_void_p(t.data_ptr()) for t in md]
-    Mg, Bg = cz.from_numpy(M), cz.from_numpy(B)
-    w = [None] * 6
-    tmp = None
-    cz.sync_stream()
-    for kind in ("pcr_rb_maf", "pcr_rb_esa_maf", "pcr_maf", "pcr_eda_maf", "pcr_esa_maf"):
-        Xo = X.copy(); ro = C.c_double(0.5); o.sweep_maf(kind, Xo, B, ro, mesh)
-        Xg = cz.from_numpy(X); res = C.c_double(0.5); flop = C.c_double(0)
-        head = (cz._sz, cz._idx, g, C.byref(pn))
-        tail = (C.byref(om), C.byref(res), tmp, C.byref(flop))
-        fields = (cz._ptr(Xg), cz._ptr(Mg), cz._ptr(Bg))
-        if kind == "pcr_rb_maf":
-            for color in (0, 1):
-                cc = C.c_int(color)
-                cz.dll.pcr_rb_maf_(*head, C.byref(ip), C.byref(cc), *fields, *mp, *w, *tail)
-        elif kind == "pcr_rb_esa_maf":
-            for color in (0, 1):
-                cc = C.c_int(color)
-                cz.dll.pcr_rb_esa_maf_(*head, C.byref(ip), C.byref(cc), C.byref(s), *fields, *mp, *w, *tail)
-        elif kind == "pcr_maf":
-            cz.dll.pcr_maf_(*head, *fields, *mp, *w, *tail)
-        elif kind == "pcr_eda_maf":
-            cz.dll.pcr_eda_maf_(*head, *fields, *mp, *w[:3], *tail)
-        else:
-            cz.dll.pcr_esa_maf_(*head, C.byref(s), *fields, *mp, *w, *tail)
-        Xr = Xg.cpu().numpy()
-        assert np.array_equal(Xr, Xo), (kind, np.abs(Xr - Xo).max())
-        assert res.value == pytest.approx(ro.value, rel=SUM_RTOL), kind
-        assert flop.value > 0
-    cz.close()
-
-
-@pytest.mark.parametrize("gi", MAF, ids=lambda i: "%s-%d-%s-%s" % (
-    GOLDEN[i]["real"], GOLDEN[i]["n"], GOLDEN[i]["solver"], GOLDEN[i]["precond"]))
-def test_maf_solve_matches_reference_history_and_field(gi):
-    """czb_solve with the `*_maf` names on the driver's uniform mesh against the golden histories of the unmodified
-    reference driver and the oracle loops (same criteria as test_gpu_solve.py)."""
-    import cubez_b200
-    g = GOLDEN[gi]
-    n, real = g["n"], g["real"]
-    tol = 1e-5 if real == "f32" else 1e-12
-    cz = cubez_b200.CZ([n] * 3, real)
-    P, RHS = cz.setup_laplace()
-    out = cz.solve(g["solver"], P, RHS, g["itr_max"], float(g["coef"]), g["precond"])
-    err, loc = cz.exact_error(P)
-    field = P.cpu().numpy()
-    cz.close()
-    gh = np.array([float(h) for h in g["history"]])
-    o = ou.OracleCZ([n] * 3, real)
-    Po, RHSo = o.setup_laplace()
-    bicg = g["solver"] == "pbicgstab_maf"
-    if not bicg:
-        assert out["itr"] == g["itr"]
-        assert len(out["history"]) == len(gh)
-        np.testing.assert_allclose(out["history"], gh, rtol=2e-6)
-        itr, res, hist = o.stationary(g["solver"], Po, RHSo, g["itr_max"], float(g["coef"]))
-        assert out["itr"] == itr
-        assert np.array_equal(field, Po), "field differs from the oracle (max %g)" % np.abs(field - Po).max()
-        np.testing.assert_allclose(out["history"], hist, rtol=1e-12)
-    else:
-        assert abs(out["itr"] - g["itr"]) <= 1
-        m = min(len(gh), len(out["history"]))
-        assert m >= len(gh) - 1
-        if g["precond"] == "none":
-            np.testing.assert_allclose(out["history"][:6], gh[:6], rtol=1e-5)
-        else:
-            np.testing.assert_allclose(out["history"][:m], gh[:m], rtol=10 * tol if real == "f32" else 2e-6, atol=1e-12)
-            itr, res, hist = o.pbicgstab(Po, RHSo, g["itr_max"], float(g["coef"]), g["precond"], maf=True)
-            if out["itr"] == itr:
-                scale = np.abs(Po).max()
-                np.testing.assert_allclose(field, Po, rtol=0, atol=(tol if real == "f32" else 1e-10) * scale)
-    assert abs(err - float(g["errmax"])) <= (1e-6 if real == "f32" else 1e-9) + (1e-3 * err if bicg else 0.0)
-
-
-def test_maf_stretched_mesh_solve_equals_oracle():
-    """A genuinely stretched mesh through czb_ctx_set_mesh: sor2sma_maf iteration count, history and field equal the
-    oracle loop on the same mesh."""
-    import cubez_b200
-    n = 24
-    cz = cubez_b200.CZ([n] * 3, "f32")
-    o = ou.OracleCZ([n] * 3, "f32")
-    mesh = o.mesh(stretch=0.2)
-    cz.set_mesh(*mesh)
-    P, RHS = cz.setup_laplace()
-    out = cz.solve("sor2sma_maf", P, RHS, 500, 1.5)
-    Po, RHSo = o.setup_laplace()
-    itr, res, hist = o.stationary("sor2sma_maf", Po, RHSo, 500, 1.5, mesh=mesh)
-    assert out["itr"] == itr
-    assert np.array_equal(P.cpu().numpy(), Po)
-    np.testing.assert_allclose(out["history"], hist, rtol=1e-12)
-    cz.close()
-
-
-@pytest.mark.parametrize("real,args", [
-    ("f32", ["32", "32", "32", "sor2sma_maf", "2000", "1.5"]),
-    ("f32", ["32", "32", "32", "pcr_rb_maf", "2000", "1.5"]),
-    ("f32", ["32", "32", "32", "pbicgstab_maf", "200", "1.1", "sor2sma_maf"]),
-])
-def test_unmodified_reference_driver_on_gpu_library_maf(real, args):
-    """A/B drop-in: the reference's own driver objects linked against libczb200 run the `_maf` solvers (search_pivot_,
-    *_maf_ kernels with host pointers, staged per call) and must write the history they wrote over the oracle kernels."""
-    import subprocess
-    import tempfile
-    exe = ou.ref_binary("cz_gpu_%s" % real)
-    if exe is None:
-        pytest.skip("oracle/_ref/cz_gpu_%s not built (needs /root/reference at build time)" % real)
-    g = [c for c in GOLDEN if c["real"] == real and str(c["n"]) == args[0] and c["solver"] == args[3]
-         and (c["precond"] == (args[6] if len(args) > 6 else None))][0]
-    with tempfile.TemporaryDirectory() as td:
-        p = subprocess.run([exe] + args, cwd=td, capture_output=True, text=True, timeout=900)
-        assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
-        lines = open(os.path.join(td, args[3] + ".txt")).read().split("\n")[1:]
-    hist = np.array([float(l.split(",")[1]) for l in lines if l.strip()])
-    gh = np.array([float(h) for h in g["history"]])
-    assert abs(len(hist) - len(gh)) <= 1
-    m = min(len(hist), len(gh))
-    bicg = args[3] == "pbicgstab_maf"
-    np.testing.assert_allclose(hist[:m], gh[:m], rtol=2e-6 if not bicg else 1e-4, atol=0 if not bicg else 1e-12)
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="MAF kernels: first hardware run pending (round-1 GPU budget exhausted)")
+def test_maf_gpu_cases_in_child_process():
+    p = subprocess.run([sys.executable, "-m", "pytest", os.path.join("tests", "gpu_maf_cases.py"), "-q", "-m", "gpu",
+                        "-p", "no:cacheprovider"], cwd=ROOT, capture_output=True, text=True, timeout=1500)
+    tail = (p.stdout[-6000:] + "\n" + p.stderr[-2000:])
+    print(tail)
+    assert p.returncode == 0, "tests/gpu_maf_cases.py: rc %d\n%s" % (p.returncode, tail)
+    assert " passed" in p.stdout and "failed" not in p.stdout.splitlines()[-1]

@@ -30,7 +30,7 @@ _LIBS = {}
 def _emu(real):
     import cubez_b200.ffi as ffi
     if not _LIBS:
-        for k, path in emu_build.build_lib().items():
+        for k, path in emu_build.build_lib(sanitize=os.environ.get("EMU_SANITIZE") or None).items():
             dll = C.CDLL(path)
             ffi.bind_reference_symbols(dll)
             ffi.bind_czb_symbols(dll, C.c_float if k == "f32" else C.c_double)
@@ -300,3 +300,22 @@ def test_line_kernel_with_real_threads_under_thread_sanitizer(real, sz, color, t
     res = np.frombuffer(raw[X.nbytes:], dtype=np.float64)[0]
     assert np.array_equal(Xs, Xo), np.abs(Xs - Xo).max()
     assert res == pytest.approx(ro.value, rel=1e-12)
+
+
+def test_emulated_kernels_under_address_sanitizer():
+    """The kernel-level cases above (and two solves) once more on an AddressSanitizer build of the emulated library:
+    every "device" allocation is a malloc block there, so an out-of-bounds load or store of a kernel -- the kind of bug
+    that would be an illegal-address fault on the GPU -- aborts the child process."""
+    import subprocess
+    if os.environ.get("EMU_SANITIZE"):
+        pytest.skip("already inside the sanitizer run")
+    asan = subprocess.run(["gcc", "-print-file-name=libasan.so"], capture_output=True, text=True).stdout.strip()
+    if not os.path.isabs(asan) or not os.path.exists(asan):
+        pytest.skip("libasan not available")
+    env = dict(os.environ, EMU_SANITIZE="address", LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0")
+    sel = "point_kernels or line_kernel_equals or stretched_mesh or sweeps_and_operator or blas1 or (solve_matches and (pcr_maf or pbicgstab_maf-sor2sma_maf))"
+    p = subprocess.run([sys.executable, "-m", "pytest", os.path.join(HERE, "test_maf_kernels_emulated.py"),
+                        os.path.join(HERE, "test_lib_emulated_plain.py"), "-x", "-q", "-p", "no:cacheprovider", "-k", sel],
+                       env=env, capture_output=True, text=True, timeout=1500)
+    assert p.returncode == 0 and " passed" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
+    assert "AddressSanitizer" not in p.stderr

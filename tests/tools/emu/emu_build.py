@@ -30,11 +30,13 @@ def _rewrite(text):
 LIB_SOURCES = ("kernels.cu", "maf.cu", "runtime.cu", "abi.cu", "solver.cu", "comm.cpp")
 
 
-def build_lib(outdir=None):
+def build_lib(outdir=None, sanitize=None):
     """libczb200_emu_{f32,f64}.so: the library's host code + every kernel that is plain CUDA C++ (kernels.cu, maf.cu,
     the loop-control kernels of solver.cu) compiled for the CPU over emu_prelude.h / emu_cudart.cpp; fused.cu and
-    pcr.cu (TMA, tensor memory, inline PTX) are replaced by emu_stubs.cpp."""
-    outdir = outdir or os.path.join(HERE, "_build")
+    pcr.cu (TMA, tensor memory, inline PTX) are replaced by emu_stubs.cpp.  sanitize="address": AddressSanitizer build
+    (every "device" allocation is a malloc block, so an out-of-bounds access of a kernel is reported)."""
+    outdir = outdir or os.path.join(HERE, "_build" + ("_" + sanitize if sanitize else ""))
+    opt = ["-O1", "-g", "-fsanitize=" + sanitize, "-fno-omit-frame-pointer"] if sanitize else ["-O2"]
     gen = os.path.join(outdir, "lib")
     os.makedirs(gen, exist_ok=True)
     hdr = os.path.join(ROOT, "include", "czb200.h")
@@ -60,7 +62,7 @@ def build_lib(outdir=None):
     libs = {}
     for real, flag in (("f32", []), ("f64", ["-D_REAL_IS_DOUBLE_"])):
         so = os.path.join(outdir, "libczb200_emu_%s.so" % real)
-        cmd = [cxx, "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-w", "-I" + HERE, "-I" + CSRC,
+        cmd = [cxx] + opt + ["-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-w", "-I" + HERE, "-I" + CSRC,
                "-I" + cuda_inc] + flag + ["-Wl,-Bsymbolic", "-o", so] + srcs + ["-ldl"]
         subprocess.check_call(cmd)
         libs[real] = so
