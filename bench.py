@@ -19,6 +19,9 @@ One JSON line on rank 0:
                against the measured HBM copy bandwidth of MEASURED_PEAKS.json
   cpu_baseline the CPU oracle port of the reference kernel (oracle/, "port") on all host cores,
                bounded sample, rank 0 / N=1 only
+  time_to_convergence  (N=1 only, optional) the metric's second half: BASELINE.json configs[0..3] solved to
+               res < 1e-5 in a CHILD process after the timed regions (iterations, device time of the solver loop);
+               left out if the child fails or times out -- it can never cost the headline line
 --impl reference times that CPU implementation alone (all host threads) and prints the same line.
 """
 import argparse
@@ -256,10 +259,58 @@ def run_gpu(args, rank, world, local_rank):
         line["cpu_baseline"] = cpu
     if also:
         line["also"] = also
+    if world == 1 and not args.no_ttc and not args.no_also:
+        ttc = time_to_convergence()
+        if ttc:
+            line["time_to_convergence"] = ttc
     print(json.dumps(line), flush=True)
     cz.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+# BASELINE.json configs[0..3] to convergence (eps = 1e-5, cz.h:162): (label, N, solver, ItrMax, omega, precond)
+TTC_CASES = (("jacobi 64^3 w=0.8", 64, "jacobi", 4000, 0.8, None),
+             ("sor2sma 256^3 w=1.95", 256, "sor2sma", 20000, 1.95, None),
+             ("pbicgstab+sor2sma 512^3 w=1.1", 512, "pbicgstab", 400, 1.1, "sor2sma"),
+             ("pcr_rb 512^3 w=1.9", 512, "pcr_rb", 8000, 1.9, None))
+
+
+def ttc_worker():
+    """Child process of time_to_convergence(): prints one JSON object."""
+    import torch
+    import cubez_b200
+    out = {}
+    for label, n, solver, itmax, omg, pre in TTC_CASES:
+        cz = cubez_b200.CZ([n] * 3, "f32")
+        P, RHS = cz.setup_laplace()
+        cz.solve(solver, P, RHS, 3, omg, precond=pre, want_history=False)          # warm-up (tables, work fields)
+        P, RHS = cz.setup_laplace()                                                # the reference's start: P = 0 + Dirichlet faces
+        torch.cuda.synchronize()
+        o = cz.solve(solver, P, RHS, itmax, omg, precond=pre, want_history=False)
+        out[label] = {"n": n, "solver": solver, "precond": pre, "omega": omg, "iterations": int(o["itr"]),
+                      "residual": float(o["res"]), "converged": bool(0 < o["itr"] and o["res"] < 1.0e-5),
+                      "solver_loop_ms": float(o["ms"])}
+        cz.close()
+        del P, RHS
+        torch.cuda.empty_cache()
+    print(json.dumps(out), flush=True)
+
+
+def time_to_convergence(timeout=300):
+    """Runs ttc_worker() in a child process; None on any failure (the headline line must not depend on it)."""
+    try:
+        p = subprocess.run([sys.executable, os.path.abspath(__file__), "--ttc-worker"], capture_output=True, text=True,
+                           timeout=timeout, env=dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0")))
+        if p.returncode != 0:
+            return None
+        for ln in reversed(p.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                d = json.loads(ln)
+                return d if isinstance(d, dict) and d else None
+    except Exception:
+        pass
+    return None
 
 
 def main():
@@ -270,7 +321,12 @@ def main():
     ap.add_argument("--impl", default="cubez_b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-also", action="store_true", help="skip the PBiCGstab / Jacobi / line-SOR side measurements")
+    ap.add_argument("--no-ttc", action="store_true", help="skip the time-to-convergence child process")
+    ap.add_argument("--ttc-worker", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
+    if args.ttc_worker:
+        ttc_worker()
+        return
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
