@@ -297,7 +297,7 @@ def ttc_worker():
     print(json.dumps(out), flush=True)
 
 
-def time_to_convergence(timeout=300):
+def time_to_convergence(timeout=180):
     """Runs ttc_worker() in a child process; None on any failure (the headline line must not depend on it)."""
     try:
         p = subprocess.run([sys.executable, os.path.abspath(__file__), "--ttc-worker"], capture_output=True, text=True,
