@@ -69,6 +69,19 @@ def build_lib(outdir=None, sanitize=None):
     return libs
 
 
+def build_nccl(outdir=None):
+    """libnccl_emu.so: file-based stand-in for the NCCL calls of comm.cpp (nccl_emu.cpp), for 2-process CPU runs."""
+    outdir = outdir or os.path.join(HERE, "_build")
+    os.makedirs(outdir, exist_ok=True)
+    so = os.path.join(outdir, "libnccl_emu.so")
+    src = os.path.join(HERE, "nccl_emu.cpp")
+    if not (os.path.exists(so) and os.path.getmtime(so) >= os.path.getmtime(src)):
+        cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+        cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+        subprocess.check_call([cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-w", "-I" + cuda_inc, "-o", so, src])
+    return so
+
+
 def build_cz(outdir=None):
     """cz_emu_f32: the product's `cz` driver (cubez_b200/csrc/cz_main.cpp, unchanged) linked to the emulated library."""
     outdir = outdir or os.path.join(HERE, "_build")
