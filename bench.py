@@ -144,7 +144,10 @@ def run_gpu(args, rank, world, local_rank):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n = N_CUBE
-    cz = cubez_b200.CZ([n, N_Y, n], "f32", device=local_rank, nranks=world, rank=rank, eps=0.0)  # eps=0: never stops early
+    # --weak (BASELINE.json configs[4] "weak": 1024 x (1024*G) x 1024, the j axis extended): per-GPU work fixed
+    weak = bool(getattr(args, "weak", False) or os.environ.get("CZB_BENCH_WEAK"))
+    ny = N_Y * world if weak else N_Y
+    cz = cubez_b200.CZ([n, ny, n], "f32", device=local_rank, nranks=world, rank=rank, eps=0.0)  # eps=0: never stops early
     if world > 1:
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
@@ -240,8 +243,9 @@ def run_gpu(args, rank, world, local_rank):
     line = {
         "metric": "stencil_glups", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "sor2sma %d^3 f32, omega=%.2f, both colours per step" % (n, OMEGA),
+        "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": ("sor2sma %dx%dx%d f32 (j extended with the GPU count), omega=%.2f, both colours per step" % (n, ny, n, OMEGA))
+                   if weak else "sor2sma %d^3 f32, omega=%.2f, both colours per step" % (n, OMEGA),
                    "parallelism": "j-slabs x%d" % world, "l2": "fields (%.1f GB each) far larger than the 126 MB L2"
                    % (field_bytes * world / 1e9), "residual_last": out["res"], "itr": out["itr"]},
         "e2e": {"value": e2e_glups, "unit": "GLUPS", "h2d_bytes_per_step": h2d_per_step,
@@ -322,6 +326,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-also", action="store_true", help="skip the PBiCGstab / Jacobi / line-SOR side measurements")
     ap.add_argument("--no-ttc", action="store_true", help="skip the time-to-convergence child process")
+    ap.add_argument("--weak", action="store_true", help="weak scaling: 1024 x (1024*N) x 1024 instead of the fixed cube")
     ap.add_argument("--ttc-worker", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
     if args.ttc_worker:
@@ -338,6 +343,7 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29511"),
                os.path.abspath(__file__), "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)]
+        cmd += ["--weak"] if args.weak else []
         sys.exit(subprocess.call(cmd))
     run_gpu(args, rank, world, local_rank)
 
