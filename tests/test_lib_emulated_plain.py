@@ -88,3 +88,68 @@ def test_emulated_blas1_mask_boundary_and_error(real):
     rel = 1e-6 if real == "f32" else 1e-13
     assert emu["d1"] == pytest.approx(ref["d1"], rel=rel) and emu["d2"] == pytest.approx(ref["d2"], rel=rel, abs=rel)
     assert emu["err"] == ref["err"] and emu["loc"] == ref["loc"] and emu["flop"] == ref["flop"]
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+@pytest.mark.parametrize("sz", [[9, 9, 9], [10, 8, 34], [6, 6, 131]])
+def test_emulated_line_sor_per_call_abi(real, sz):
+    """pcr_rb_, pcr_rb_esa_, pcr_, pcr_eda_, pcr_esa_, pcr_j_esa_ (abi.cu -> k_pcr_tables + k_pcr_lines, the
+    block-per-line path) against the oracle, bit for bit."""
+    lib = _emu(real)
+    o = ou.OracleCZ(sz, real)
+    X, B = ou.random_fields(o.shape, o.dt)
+    M = o.mask()
+    n = o.idx[5] - o.idx[4] + 1
+    pn = C.c_int(ou.get_num_stage(n)); s = C.c_int(2 ** (pn.value - 2)); ip = C.c_int(0)
+    om = o.creal(1.3)
+    w = [ou.ptr(a) for a in o.work1d]
+    for kind in ("pcr_rb", "pcr_rb_esa", "pcr", "pcr_eda", "pcr_esa", "pcr_j_esa"):
+        if pn.value < 3 and kind in ("pcr_rb_esa", "pcr", "pcr_esa"):
+            continue
+        out = []
+        for dll in (o.dll, lib):
+            x = X.copy(); res = C.c_double(0.5); flop = C.c_double(0)
+            head = (o._sz, o._idx, o.g(), C.byref(pn))
+            tail = (C.byref(om), C.byref(res), C.byref(flop))
+            f3 = (ou.ptr(x), ou.ptr(M), ou.ptr(B))
+            if kind == "pcr_rb":
+                for color in (0, 1):
+                    cc = C.c_int(color)
+                    dll.pcr_rb_(*head, C.byref(ip), C.byref(cc), *f3, *w, *tail)
+            elif kind == "pcr_rb_esa":
+                for color in (0, 1):
+                    cc = C.c_int(color)
+                    dll.pcr_rb_esa_(*head, C.byref(ip), C.byref(cc), C.byref(s), *f3, *w, *tail)
+            elif kind == "pcr":
+                dll.pcr_(*head, *f3, *w, *tail)
+            elif kind == "pcr_eda":
+                dll.pcr_eda_(*head, *f3, *w[:3], *tail)
+            elif kind == "pcr_esa":
+                dll.pcr_esa_(*head, C.byref(s), *f3, *w, *tail)
+            else:
+                src = np.zeros_like(X); wrk = np.zeros_like(X)
+                dll.pcr_j_esa_(*head, C.byref(s), *f3, *w, ou.ptr(src), ou.ptr(wrk), *tail)
+            out.append((x, res.value, flop.value))
+        assert np.array_equal(out[0][0], out[1][0]), (kind, np.abs(out[0][0] - out[1][0]).max())
+        assert out[0][1] == pytest.approx(out[1][1], rel=1e-12), kind
+        assert out[0][2] == out[1][2], kind
+
+
+def test_emulated_line_sor_solves_match_golden():
+    """czb_solve with the uniform-grid line-SOR names (LSOR_PCR_RB / LSOR_PCR / LSOR_PCR_J_ESA loops of solver.cu) and
+    PBiCGstab with a line-SOR preconditioner against the reference driver's golden histories."""
+    from test_maf_kernels_emulated import GOLDEN, _solve
+    lib = _emu("f32")
+    for solver in ("pcr_rb", "pcr_rb_esa", "pcr_j_esa", "pcr", "pcr_eda", "pcr_esa"):
+        g = [c for c in GOLDEN if c["real"] == "f32" and c["n"] == 32 and c["solver"] == solver][0]
+        o, itr, res, hist, P, flop = _solve(lib, "f32", 32, solver, None, g["itr_max"], float(g["coef"]))
+        assert itr == g["itr"], solver
+        np.testing.assert_allclose(hist, [float(h) for h in g["history"]], rtol=2e-6, err_msg=solver)
+        Po, RHSo = o.setup_laplace()
+        itr_o, res_o, hist_o = o.stationary(solver, Po, RHSo, g["itr_max"], float(g["coef"]))
+        assert np.array_equal(P, Po), solver
+    g = [c for c in GOLDEN if c["real"] == "f32" and c["n"] == 32 and c["solver"] == "pbicgstab" and c["precond"] == "pcr_rb"][0]
+    o, itr, res, hist, P, flop = _solve(lib, "f32", 32, "pbicgstab", "pcr_rb", g["itr_max"], float(g["coef"]))
+    assert abs(itr - g["itr"]) <= 1
+    m = min(len(hist), len(g["history"]))
+    np.testing.assert_allclose(hist[:m], [float(h) for h in g["history"]][:m], rtol=1e-4, atol=1e-12)

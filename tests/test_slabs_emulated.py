@@ -29,7 +29,7 @@ def _run(tmp, nranks, n, solver, pre, omega, iters, eps):
 
 
 CASES = [("sor2sma", None, 1.5, 25), ("jacobi", None, 0.8, 25), ("sor2sma_maf", None, 1.5, 25), ("jacobi_maf", None, 0.8, 20),
-         ("pcr_rb_maf", None, 1.5, 15), ("pcr_rb_esa_maf", None, 1.5, 6)]
+         ("pcr_rb_maf", None, 1.5, 15), ("pcr_rb_esa_maf", None, 1.5, 6), ("pcr_rb", None, 1.5, 12), ("pcr_j_esa", None, 0.9, 12)]
 
 
 @pytest.mark.parametrize("solver,pre,omega,iters", CASES)

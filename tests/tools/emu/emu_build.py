@@ -27,13 +27,27 @@ def _rewrite(text):
     return LAUNCH.sub(sub, text)
 
 
-LIB_SOURCES = ("kernels.cu", "maf.cu", "runtime.cu", "abi.cu", "solver.cu", "comm.cpp")
+LIB_SOURCES = ("kernels.cu", "maf.cu", "pcr.cu", "runtime.cu", "abi.cu", "solver.cu", "comm.cpp")
+
+
+def _pcr_plain(text):
+    """pcr.cu without its warp-per-line kernels (warp shuffles, packed f32x2 PTX, tensor memory, TMA bulk copies: device
+    only): keeps k_pcr_tables, the block-per-line kernel k_pcr_lines, the table management and the tail of
+    launch_pcr_lines that launches k_pcr_lines -- the path the GPU takes for double precision and for lines the warp
+    kernels do not cover.  Marker based; fails loudly if pcr.cu is reorganised."""
+    a = text.index("// One WARP per line, the right-hand side d in registers.")
+    a = text.rindex("\n// ----", 0, a) + 1
+    b = text.index("}  // namespace\n\nvoid pcr_build_tables")
+    text = text[:a] + text[b:]
+    a = text.index("#ifndef _REAL_IS_DOUBLE_\n  static const bool no_warp")
+    b = text.index("#endif\n  if (T.last4) {", a)
+    return text[:a] + text[b + len("#endif\n"):]
 
 
 def build_lib(outdir=None, sanitize=None):
     """libczb200_emu_{f32,f64}.so: the library's host code + every kernel that is plain CUDA C++ (kernels.cu, maf.cu,
-    the loop-control kernels of solver.cu) compiled for the CPU over emu_prelude.h / emu_cudart.cpp; fused.cu and
-    pcr.cu (TMA, tensor memory, inline PTX) are replaced by emu_stubs.cpp.  sanitize="address": AddressSanitizer build
+    the loop-control kernels of solver.cu, the block-per-line part of pcr.cu) compiled for the CPU over emu_prelude.h /
+    emu_cudart.cpp; fused.cu (TMA, inline PTX) is replaced by emu_stubs.cpp, the warp-per-line kernels of pcr.cu are cut.  sanitize="address": AddressSanitizer build
     (every "device" allocation is a malloc block, so an out-of-bounds access of a kernel is reported)."""
     outdir = outdir or os.path.join(HERE, "_build" + ("_" + sanitize if sanitize else ""))
     opt = ["-O1", "-g", "-fsanitize=" + sanitize, "-fno-omit-frame-pointer"] if sanitize else ["-O2"]
@@ -49,8 +63,11 @@ def build_lib(outdir=None, sanitize=None):
         f.write(_rewrite(open(os.path.join(CSRC, "cells.cuh")).read()))
     srcs = []
     for name in LIB_SOURCES:
-        text = _rewrite(open(os.path.join(CSRC, name)).read())
-        assert "<<<" not in text, name
+        text = open(os.path.join(CSRC, name)).read()
+        if name == "pcr.cu":
+            text = _pcr_plain(text)
+        text = _rewrite(text)
+        assert "<<<" not in text and "asm(" not in text and "asm volatile" not in text, name
         text = text.replace('"../../include/czb200.h"', '"%s"' % hdr)
         out = os.path.join(gen, name.replace(".cu", "_emu.cpp").replace("comm.cpp", "comm_emu.cpp"))
         with open(out, "w") as f:
