@@ -13,6 +13,7 @@
 #include <cmath>
 #include <strings.h>
 #include <cuda.h>
+#include <nvtx3/nvToolsExt.h>   // header-only; a no-op unless a profiler is attached (reference: PUSH_RANGE / POP_RANGE, cz.h:46-70)
 
 using namespace czb;
 
@@ -63,6 +64,11 @@ int getNumStage(int n) {   // cz.h:293-300
 }
 
 inline double ipow2(int e) { return (double)(1LL << e); }
+
+struct NvtxRange {   // scoped PUSH_RANGE / POP_RANGE
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 }  // namespace
 
@@ -544,6 +550,7 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
 // CZ::Preconditioner (cz_Poisson.cpp:273-322): lc_max = 8 sweeps without convergence check,
 // starting from the caller-cleared xx; unknown / "none" -> copy.
 void czb_ctx::Preconditioner(REAL* xx, REAL* bb, double& flop, int pc_type) {
+  NvtxRange range("Preconditioner");
   double res = 0.0;
   const int lc_max = 8;
   const bool outer_maf = maf;
@@ -790,6 +797,7 @@ int czb_solve(czb_ctx* c, const char* solver, const char* precond, CZB_REAL* X, 
     if (pc == LS_BICGSTAB || pc == LS_BICGSTAB_MAF || pc == LS_PCR_ESA || pc == LS_PCR_J_ESA || pc == LS_PCR_ESA_MAF) pc = 0;
   }
   c->maf = (ls >= LS_PSOR_MAF && ls != LS_BICGSTAB_MAF);
+  NvtxRange range(solver);
   c->ac1 = omg;
   const size_t bytes = sizeof(REAL) * c->field_elems();
   REAL* Xdev = X; REAL* Bdev = B;
