@@ -1,28 +1,33 @@
 #!/usr/bin/env python
-"""bench.py -- headline benchmark of cubez_b200 (BASELINE.json: "Stencil GLUPS ... HBM GB/s vs peak").
+"""bench.py -- headline benchmark of cubez_b200 (BASELINE.json: "Stencil GLUPS & time-to-convergence at
+1/2/4/8 B200; HBM GB/s vs peak").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--weak] [--impl reference]
     torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
 
-Workload (config.workload): red-black SOR ("sor2sma", both colours = one step) on the 1024^3
-float cube of BASELINE.json configs[4]; it fits one B200, so it is also the N=1 workload.
-N>1 = STRONG scaling: the same cube cut into N j-slabs, one process per GPU, halo planes
-exchanged with NCCL, residual all-reduced (cubez_b200/csrc/comm.cpp).
+Workload (config.workload): red-black SOR ("sor2sma", both colours = one step) on the 1024^3 float cube of
+BASELINE.json configs[4]; it fits one B200, so it is also the N=1 workload.  N>1 = STRONG scaling: the same cube
+cut into N j-slabs, one process per GPU (cubez_b200/csrc/comm.cpp); --weak extends the j axis with N instead.
+The start field is a hash of the GLOBAL node index (cubez_b200/synth.py), i.e. the same problem for every N.
 
 One JSON line on rank 0:
-  value        GLUPS (1e9 lattice updates/s, whole job), fields resident in HBM, K iterations timed
-               with CUDA events on the launching stream, max over ranks
+  value        GLUPS (1e9 lattice updates/s, whole job), fields resident in HBM.  NWIN windows of exactly K
+               iterations each are timed with CUDA events on the launching stream between barriers, max over
+               ranks per window; value / ms_per_step come from the MEDIAN window, all windows are listed
+  parity_vs_n1 PAR_ITERS iterations from the start field before the timed region: residual history and an exact
+               order-independent checksum of the field against tests/golden/bench_parity.json, which was written
+               by the CPU ORACLE on the single domain (tests/golden/make_bench_parity.py)
   e2e          the same K iterations through the public call CZ.solve() with HOST (pinned) arrays:
                H2D of X and B, the solve loop, D2H of X and of the residual history, all timed
-  roofline     dominant kernel (fused two-colour sweep k_rb2_pk): algorithmic bytes
-               (4R = 16 B per cell.iteration) / measured time per iteration,
-               against the measured HBM copy bandwidth of MEASURED_PEAKS.json
-  cpu_baseline the CPU oracle port of the reference kernel (oracle/, "port") on all host cores,
-               bounded sample, rank 0 / N=1 only
-  time_to_convergence  (N=1 only, optional) the metric's second half: BASELINE.json configs[0..3] solved to
-               res < 1e-5 in a CHILD process after the timed regions (iterations, device time of the solver loop);
-               left out if the child fails or times out -- it can never cost the headline line
---impl reference times that CPU implementation alone (all host threads) and prints the same line.
+  roofline     dominant kernel (fused two-colour sweep k_rb2_pk): algorithmic bytes (4R = 16 B per
+               cell.iteration) / measured time per iteration, against the measured HBM copy bandwidth
+  cpu_baseline the CPU oracle port of the reference kernel (oracle/, "port") on all host cores, bounded sample,
+               in a CHILD process whose OpenMP team size is set explicitly and reported from omp_get_max_threads()
+  also         PBiCGstab+sor2sma, Jacobi and line SOR on the same grid; f64 sor2sma / PBiCGstab at 512^3 (N=1)
+  time_to_convergence  BASELINE.json configs[0..3] (+ the 1024^3 solvers of configs[4]) solved to res < 1e-5:
+               iterations and device time of the solver loop, next to the oracle's iteration count (committed
+               golden, tests/golden/baseline_configs.json) and the CPU port's seconds on this box
+--impl reference times the CPU implementation alone (all host threads) on the same workload, same line.
 """
 import argparse
 import ctypes as C
@@ -41,7 +46,13 @@ N_Y = int(os.environ.get("CZB_BENCH_NY", str(N_CUBE)))     # experiments only: s
 OMEGA = 1.5
 SOLVER = "sor2sma"
 ALGO_BYTES_PER_CELL = 16.0      # red-black SOR, float, 4R per cell.iteration
-NCU_TRAFFIC_PER_ITER = 14.24e9     # dram read+write bytes per k_rb2_pk launch (profiles/r01_rb2_summary.md, 1 GPU)
+NWIN = 5                        # timed windows of --steps iterations each (median reported)
+PAR_ITERS = 8                   # iterations of the parity leg
+GOLDEN_PARITY = os.path.join(ROOT, "tests", "golden", "bench_parity.json")
+GOLDEN_CONFIGS = os.path.join(ROOT, "tests", "golden", "baseline_configs.json")
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE k_rb2_pk launch at N=1, 1024^3 (profiles/*_rb2_summary.md);
+# null for any other N / grid: the figure is a property of that capture, not of this run
+NCU_TRAFFIC_N1 = {"bytes": 14.24e9, "source": "profiles/r01_rb2_summary.md"}
 
 
 def measured_peak():
@@ -51,91 +62,238 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clock and throttle reasons sampled DURING the timed windows, in a thread, through NVML (no fork near
+    the timed region); falls back to one `nvidia-smi -lms` child started before the first barrier."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+    def __init__(self, torch_index):
+        self.index, self.rows, self.proc, self.h, self.stop_flag, self.th = torch_index, [], None, None, False, None
+        self.active = False      # rows are kept only while a timed window is open
+        self.mx = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            uuid = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+            self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode() if hasattr(uuid, "encode") else uuid)
+            self.nv = pynvml
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.th = threading.Thread(target=self._poll, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            self.h = None
+        try:
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = vis.split(",")[self.index] if vis else str(self.index)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", phys, "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        nv = self.nv
+        bits = [nv.nvmlClocksEventReasonHwSlowdown, nv.nvmlClocksEventReasonHwThermalSlowdown,
+                nv.nvmlClocksEventReasonSwThermalSlowdown, nv.nvmlClocksEventReasonSwPowerCap] \
+            if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else \
+            [nv.nvmlClocksThrottleReasonHwSlowdown, nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+             nv.nvmlClocksThrottleReasonSwThermalSlowdown, nv.nvmlClocksThrottleReasonSwPowerCap]
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            if self.active:
+                try:
+                    sm = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                    r = int(get_reasons(self.h))
+                    self.rows.append([sm] + [bool(r & b) for b in bits])
+                except Exception:
+                    pass
+            time.sleep(0.004)
+
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            x = [v.strip() for v in line.split(",")]
+            if self.active and len(x) >= 6 and x[0].replace(".", "").isdigit():
+                self.mx = float(x[1]) if x[1].replace(".", "").isdigit() else self.mx
+                self.rows.append([float(x[0])] + [x[2 + i].startswith("Active") for i in range(4)])
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm = sorted(float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit())
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].startswith("Active")})
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        if self.h is None and self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no NVML / nvidia-smi"], "samples": 0}
+        sm = sorted(r[0] for r in self.rows)
+        reasons = sorted({self.NAMES[i] for r in self.rows for i in range(4) if r[1 + i]})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.mx, "reasons": reasons,
+                "samples": len(sm), "source": "nvml thread" if self.h is not None else "nvidia-smi -lms 20"}
 
 
-def cpu_port_glups(steps, warmup, sample_planes=128, n=N_CUBE):
-    """Time the oracle port of psor2sma_core (the reference's CPU kernel restated in C++,
-    oracle/cz_f90_port.cpp) on all host cores: a j-slab of the workload per step."""
+# ======================================================================================= CPU arm (child process)
+# BASELINE.json configs[0..3] to convergence (eps = 1e-5, cz.h:162): (label, N, solver, ItrMax, omega, precond, real)
+TTC_CASES = (("jacobi 64^3 w=0.8", 64, "jacobi", 4000, 0.8, None, "f32"),
+             ("sor2sma 256^3 w=1.95", 256, "sor2sma", 20000, 1.95, None, "f32"),
+             ("pbicgstab+sor2sma 512^3 w=1.1", 512, "pbicgstab", 400, 1.1, "sor2sma", "f32"),
+             ("pbicgstab+sor2sma 512^3 w=1.1 f64", 512, "pbicgstab", 400, 1.1, "sor2sma", "f64"),
+             ("pcr_rb 512^3 w=1.9", 512, "pcr_rb", 8000, 1.9, None, "f32"))
+# configs[4]: the 1024^3 solvers of the north-star target, to convergence, at every N
+TTC_BIG = (("sor2sma 1024^3 w=1.99", 1024, "sor2sma", 20000, 1.99, None, "f32"),
+           ("pbicgstab+sor2sma 1024^3 w=1.1", 1024, "pbicgstab", 600, 1.1, "sor2sma", "f32"))
+
+
+def golden_key(real, n, solver, omg, pre):
+    return "%s %d %s %s %s" % (real, n, solver, ("%g" % omg), pre)
+
+
+def load_golden_configs():
+    try:
+        return json.load(open(GOLDEN_CONFIGS))
+    except Exception:
+        return {}
+
+
+def cpu_worker(mode, steps, warmup):
+    """Child process of the CPU legs (the ONLY code of this file that executes oracle/).  Prints one JSON object."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import numpy as np
     import oracle_util as ou
-    cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
-    os.environ.setdefault("OMP_PROC_BIND", "close")
-    sz = [n, min(sample_planes, n), n]
-    o = ou.OracleCZ([n, n, n], "f32", sz=sz)
-    X, B = o.setup_laplace()
-    rng = np.random.default_rng(1)
-    X[2:-2, 2:-2, 2:-2] = rng.uniform(-1, 1, size=X[2:-2, 2:-2, 2:-2].shape).astype(np.float32)
-    o.ac1 = np.float32(OMEGA)
-    cells = (sz[0] - 2) * (sz[1] - 2) * (sz[2] - 2)
-    res = C.c_double(0)
-    for _ in range(max(warmup, 1)):
-        o.sweep_rb(X, B, res)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        o.sweep_rb(X, B, res)
-    dt = time.perf_counter() - t0
-    return cells * steps / dt / 1e9, dt / steps * 1e3, cores, \
-        "%d iterations of sor2sma on a %dx%dx%d slab of the %d^3 grid (oracle port, OpenMP %d threads)" % (
-            steps, sz[0], sz[1], sz[2], n, cores)
+    cores = host_cores()
+    lib = ou.load("f32")
+    lib.oracle_set_threads(cores)
+    threads = int(lib.oracle_max_threads())
+    n = N_CUBE
+    if mode in ("sample", "full"):
+        # psor2sma_core (cz_solver.f90:404-493) restated in oracle/cz_f90_port.cpp, both colours per step
+        ny = n if mode == "full" else min(128, n)
+        o = ou.OracleCZ([n, n, n], "f32", sz=[n, ny, n])
+        X, B = o.setup_laplace()
+        from cubez_b200 import synth
+        synth.fill(X, o.sz)
+        o.bc_k(X)
+        o.ac1 = np.float32(OMEGA)
+        cells = (n - 2) * (ny - 2) * (n - 2)
+        res = C.c_double(0)
+        for _ in range(max(warmup, 1)):
+            o.sweep_rb(X, B, res)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            o.sweep_rb(X, B, res)
+        dt = time.perf_counter() - t0
+        what = ("the whole %d^3 grid" % n) if ny == n else ("a %dx%dx%d j-slab of the %d^3 grid" % (n, ny, n, n))
+        print(json.dumps({"value": cells * steps / dt / 1e9, "ms": dt / steps * 1e3, "cores": threads,
+                          "sample": "%d iterations of sor2sma (oracle port of psor2sma_core, OpenMP %d threads = "
+                                    "omp_get_max_threads(), %d usable cores) on %s per step" % (steps, threads, cores, what)}),
+              flush=True)
+        return
+    # mode == "ttc": the reference's timed region is the solver loop (cz_Evaluate.cpp:419-421).  Small configs run to
+    # convergence; the 512^3 ones are timed over a bounded window and extrapolated with the oracle's committed
+    # iteration count (the full CPU runs take minutes: see wall_seconds in tests/golden/baseline_configs.json).
+    gold = load_golden_configs()
+    out = {}
+    for label, nn, solver, itmax, omg, pre, real in TTC_CASES:
+        g = gold.get(golden_key(real, nn, solver, omg, pre))
+        lr = ou.load(real)
+        lr.oracle_set_threads(cores)
+        o = ou.OracleCZ([nn] * 3, real)
+        X, B = o.setup_laplace()
+        full = nn <= 256
+        window = itmax if full else (3 if solver == "pbicgstab" else 6)
+        t0 = time.perf_counter()
+        if solver == "pbicgstab":
+            itr, res, hist = o.pbicgstab(X, B, window + 1 if not full else itmax, omg, pre)
+            done = len(hist)
+        else:
+            itr, res, hist = o.stationary(solver, X, B, window, omg)
+            done = len(hist)
+        dt = time.perf_counter() - t0
+        e = {"threads": threads, "iterations_timed": int(done), "seconds_timed": dt}
+        if full:
+            e.update({"kind": "measured to convergence", "iterations": int(itr), "seconds": dt, "residual": float(res)})
+        elif g:
+            e.update({"kind": "extrapolated: seconds per iteration of a %d-iteration window x the oracle's iteration count" % done,
+                      "iterations": int(g["itr"]), "seconds": dt / max(done, 1) * int(g["itr"])})
+        out[label] = e
+        del o, X, B
+    print(json.dumps(out), flush=True)
+
+
+def run_cpu_child(mode, steps=3, warmup=1, timeout=600):
+    """The CPU legs run in a child whose environment sets the OpenMP team explicitly: under torchrun the parent has
+    OMP_NUM_THREADS=1 exported and libgomp has already read it."""
+    cores = host_cores()
+    env = dict(os.environ, OMP_NUM_THREADS=str(cores), OMP_PROC_BIND="close", OMP_DYNAMIC="FALSE", CUDA_VISIBLE_DEVICES="")
+    try:
+        p = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-worker", mode, "--steps", str(steps),
+                            "--warmup", str(warmup)], capture_output=True, text=True, timeout=timeout, env=env)
+        if p.returncode != 0:
+            sys.stderr.write("bench.py: cpu child (%s) rc=%d\n%s\n" % (mode, p.returncode, p.stderr[-2000:]))
+            return None
+        for ln in reversed(p.stdout.strip().splitlines()):
+            if ln.startswith("{"):
+                return json.loads(ln)
+    except Exception as ex:
+        sys.stderr.write("bench.py: cpu child (%s) failed: %r\n" % (mode, ex))
+    return None
+
+
+def workload_string(n, ny, weak):
+    if weak:
+        return "sor2sma %dx%dx%d f32 (j extended with the GPU count), omega=%.2f, both colours per step" % (n, ny, n, OMEGA)
+    if ny != n:
+        return "sor2sma %dx%dx%d f32, omega=%.2f, both colours per step" % (n, ny, n, OMEGA)
+    return "sor2sma %d^3 f32, omega=%.2f, both colours per step" % (n, OMEGA)
 
 
 def run_reference(args, rank):
     if rank != 0:
         return
-    v, ms, cores, sample = cpu_port_glups(args.steps, args.warmup)
+    # the whole cube per step when the run stays within ~2 minutes at ~1 GLUPS, else a j-slab sample
+    cells = float(N_CUBE - 2) ** 3
+    mode = "full" if cells * (args.steps + args.warmup) / 1.0e9 < 120.0 else "sample"
+    r = run_cpu_child(mode, args.steps, args.warmup, timeout=1500)
+    if r is None:
+        print(json.dumps({"impl": "reference", "unavailable": "the CPU oracle child process failed (see stderr)"}), flush=True)
+        return
     print(json.dumps({
-        "impl": "reference", "metric": "stencil_glups", "value": v, "unit": "GLUPS", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "impl": "reference", "metric": "stencil_glups", "value": r["value"], "unit": "GLUPS", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "sor2sma %d^3 f32, omega=%.2f (CPU: j-slab sample per step)" % (N_CUBE, OMEGA)},
-        "cpu_baseline": {"value": v, "unit": "GLUPS", "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": v, "unit": "GLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "config": {"workload": workload_string(N_CUBE, N_Y, False)},
+        "cpu_baseline": {"value": r["value"], "unit": "GLUPS", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": "GLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
+
+
+# ======================================================================================= GPU arm
+def median(v):
+    s = sorted(v)
+    return s[len(s) // 2]
 
 
 def run_gpu(args, rank, world, local_rank):
     import numpy as np
     import torch
     import cubez_b200
+    from cubez_b200 import synth
 
     torch.cuda.set_device(local_rank)
     dist = None
@@ -147,13 +305,6 @@ def run_gpu(args, rank, world, local_rank):
     # --weak (BASELINE.json configs[4] "weak": 1024 x (1024*G) x 1024, the j axis extended): per-GPU work fixed
     weak = bool(getattr(args, "weak", False) or os.environ.get("CZB_BENCH_WEAK"))
     ny = N_Y * world if weak else N_Y
-    cz = cubez_b200.CZ([n, ny, n], "f32", device=local_rank, nranks=world, rank=rank, eps=0.0)  # eps=0: never stops early
-    if world > 1:
-        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt.copy_(torch.frombuffer(bytearray(cz.comm_unique_id()), dtype=torch.uint8))
-        dist.broadcast(idt, 0)
-        cz.comm_init(bytes(idt.cpu().numpy().tobytes()))
 
     def barrier():
         torch.cuda.synchronize()
@@ -168,27 +319,81 @@ def run_gpu(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- device-resident: fields stay in HBM ---------------------------------------------------
-    P, RHS = cz.setup_laplace()
-    gen = torch.Generator(device="cuda").manual_seed(1234 + rank)
-    P[2:-2, 2:-2, 2:-2] = torch.rand(P[2:-2, 2:-2, 2:-2].shape, generator=gen, device="cuda") * 2 - 1   # synthetic state
-    cz.bc_k(P)
-    cz.solve(SOLVER, P, RHS, max(args.warmup, 3), OMEGA, want_history=False)     # warm-up (>= 3 steps)
-    barrier()
+    def sum_over_ranks_int(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)      # wraps modulo 2^64 like the single-domain checksum
+        return int(t.item())
+
+    def make_cz(gsz, real="f32", eps=0.0):
+        cz = cubez_b200.CZ(gsz, real, device=local_rank, nranks=world, rank=rank, eps=eps)
+        if world > 1:
+            idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                idt.copy_(torch.frombuffer(bytearray(cz.comm_unique_id()), dtype=torch.uint8))
+            dist.broadcast(idt, 0)
+            cz.comm_init(bytes(idt.cpu().numpy().tobytes()))
+        return cz
+
+    def start_state(cz):
+        P, RHS = cz.setup_laplace()
+        synth.fill(P, cz.sz, head_j=cz.head[1], gny=cz.gsz[1])
+        cz.bc_k(P)
+        return P, RHS
+
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
-        sampler.start()
-    l0 = cz.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    cz.sync_stream()
-    ev0.record()
-    out = cz.solve(SOLVER, P, RHS, args.steps, OMEGA, want_history=False)
-    ev1.record()
-    barrier()
-    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
-    ms_loop = max_over_ranks(out["ms"])           # the library's own events around the iteration loop
-    launches = cz.launch_count() - l0
+        sampler.start()                    # before any barrier; rows are recorded only inside the windows
+    cz = make_cz([n, ny, n])               # eps = 0: never stops early
+
+    # ---- parity leg: same problem at every N, compared with the ORACLE's single-domain result -------------
+    P, RHS = start_state(cz)
+    outp = cz.solve(SOLVER, P, RHS, PAR_ITERS, OMEGA, want_history=True)
+    chk = sum_over_ranks_int(synth.checksum_owned(P, cz.idx))
+    parity = {"iterations": PAR_ITERS, "history": [float(x) for x in outp["history"]], "field_checksum": chk}
+    gold = {}
+    try:
+        gold = json.load(open(GOLDEN_PARITY)).get("%dx%dx%d" % (n, ny, n), {})
+    except Exception:
+        pass
+    if gold:
+        gh = np.array(gold["history"][:PAR_ITERS], dtype=np.float64)
+        rel = float(np.max(np.abs(np.array(parity["history"]) - gh) / gh))
+        parity.update({"max_rel_diff_history": rel, "checksum_equal": chk == int(gold["field_checksum"]),
+                       "ok": bool(rel <= 1e-12 and chk == int(gold["field_checksum"])), "golden": gold.get("made_by", "oracle")})
+    else:
+        parity.update({"ok": None, "note": "no committed single-domain golden for this grid"})
+    del parity["history"]
+    parity["history_last"] = float(outp["history"][-1])
+
+    # ---- device-resident: fields stay in HBM ---------------------------------------------------
+    P, RHS = start_state(cz)
+    warm = max(args.warmup, 3)
+    cz.solve(SOLVER, P, RHS, warm, OMEGA, want_history=False)     # warm-up (>= 3 steps)
+    windows, loops = [], []
+    launches = 0
+    out = None
+    for w in range(NWIN):
+        barrier()
+        l0 = cz.launch_count()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        cz.sync_stream()
+        barrier()                          # second barrier + synchronize immediately before the start event
+        if sampler:
+            sampler.active = True
+        ev0.record()
+        out = cz.solve(SOLVER, P, RHS, args.steps, OMEGA, want_history=False)
+        ev1.record()
+        barrier()
+        if sampler:
+            sampler.active = False
+        windows.append(max_over_ranks(ev0.elapsed_time(ev1)))
+        loops.append(max_over_ranks(out["ms"]))        # the library's own events around the iteration loop
+        launches = cz.launch_count() - l0
     clocks = sampler.stop() if sampler else None
+    ms_total = median(windows)
+    ms_loop = median(loops)
     cells = float(cz.inner_cells_global)
     glups = cells * args.steps / (ms_total * 1e-3) / 1e9
     ms_iter = ms_loop / args.steps
@@ -199,18 +404,19 @@ def run_gpu(args, rank, world, local_rank):
     if not args.no_also:
         for name, pre, omg, bpc, k in (("pbicgstab", "sor2sma", OMEGA, 340.0, 6), ("jacobi", None, 0.8, 12.0, 10),
                                        ("pcr_rb", None, OMEGA, 20.0, 8)):
-            P2, R2 = cz.setup_laplace()
-            P2[2:-2, 2:-2, 2:-2] = torch.rand(P2[2:-2, 2:-2, 2:-2].shape, generator=gen, device="cuda") * 2 - 1
-            cz.bc_k(P2)
+            P2, R2 = start_state(cz)
             cz.solve(name, P2, R2, 3, omg, precond=pre, want_history=False)
-            barrier()
-            o2 = cz.solve(name, P2, R2, k, omg, precond=pre, want_history=False)
-            barrier()
-            done = (k - 1) if name == "pbicgstab" else k
-            ms2 = max_over_ranks(o2["ms"]) / done
-            gl = cells / (ms2 * 1e-3) / 1e9
+            ms2 = []
+            for w in range(3):
+                barrier()
+                o2 = cz.solve(name, P2, R2, k, omg, precond=pre, want_history=False)
+                barrier()
+                done = (k - 1) if name == "pbicgstab" else k
+                ms2.append(max_over_ranks(o2["ms"]) / done)
+            m2 = median(ms2)
+            gl = cells / (m2 * 1e-3) / 1e9
             also[name + ("+" + pre if pre else "")] = {
-                "value": gl, "unit": "G cell-iterations/s", "ms_per_iteration": ms2,
+                "value": gl, "unit": "G cell-iterations/s", "ms_per_iteration": m2,
                 "algorithmic_bytes_per_cell": bpc, "hbm_frac_of_measured": gl * bpc / world / measured_peak()[0]}
             del P2, R2
         torch.cuda.empty_cache()
@@ -231,77 +437,152 @@ def run_gpu(args, rank, world, local_rank):
     field_bytes = float(np.prod(cz.shape)) * 4.0
     h2d_per_step = 2.0 * field_bytes / args.steps
     d2h_per_step = (field_bytes + 8.0 * args.steps) / args.steps
+    del Ph, Bh, Pn, Bn
+    cz.close()
 
-    if rank != 0:
-        return
     peak, peak_src = measured_peak()
     achieved = (cells / world) * ALGO_BYTES_PER_CELL / (ms_iter * 1e-3) / 1e9      # GB/s per GPU
-    cpu = None
-    if world == 1 and not args.no_cpu:
-        v, cms, cores, sample = cpu_port_glups(3, 1)
-        cpu = {"value": v, "unit": "GLUPS", "cores": cores, "kind": "port", "sample": sample}
+    traffic = NCU_TRAFFIC_N1["bytes"] if (world == 1 and n == 1024 and ny == 1024) else None
     line = {
         "metric": "stencil_glups", "value": glups, "unit": "GLUPS", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+        "warmup": warm, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
         "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": ("sor2sma %dx%dx%d f32 (j extended with the GPU count), omega=%.2f, both colours per step" % (n, ny, n, OMEGA))
-                   if weak else "sor2sma %d^3 f32, omega=%.2f, both colours per step" % (n, OMEGA),
+        "config": {"workload": workload_string(n, ny, weak),
                    "parallelism": "j-slabs x%d" % world, "l2": "fields (%.1f GB each) far larger than the 126 MB L2"
-                   % (field_bytes * world / 1e9), "residual_last": out["res"], "itr": out["itr"]},
+                   % (field_bytes * world / 1e9), "residual_last": out["res"], "itr": out["itr"],
+                   "start_field": "hash of the global node index (cubez_b200/synth.py): the same problem at every N"},
+        "windows_ms": windows, "windows": NWIN, "window_stat": "median",
         "e2e": {"value": e2e_glups, "unit": "GLUPS", "h2d_bytes_per_step": h2d_per_step,
                 "d2h_bytes_per_step": d2h_per_step, "seconds": t_e2e,
                 "note": "CZ.solve() with pinned host X,B: 2 fields H2D, K iterations, X + history D2H"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": NCU_TRAFFIC_PER_ITER, "peak_source": peak_src,
+                     "traffic": traffic, "traffic_source": NCU_TRAFFIC_N1["source"] if traffic else None,
+                     "peak_source": peak_src,
                      "kernel": "k_rb2_pk (fused two-colour sweep, TMA-staged, packed f32x2)",
                      "algorithmic_bytes_per_cell": ALGO_BYTES_PER_CELL, "ms_per_launch": ms_iter,
                      "frac_of_8000": achieved / 8000.0},
+        "parity_vs_n1": parity,
         "clocks": clocks,
     }
-    if cpu:
-        line["cpu_baseline"] = cpu
     if also:
         line["also"] = also
-    if world == 1 and not args.no_ttc and not args.no_also:
-        ttc = time_to_convergence()
-        if ttc:
-            line["time_to_convergence"] = ttc
-    print(json.dumps(line), flush=True)
-    cz.close()
+
+    # ---- everything below can only ADD keys: a watchdog prints the line as it stands if a later leg hangs ----
+    printed = threading.Event()
+
+    def emit():
+        if rank == 0 and not printed.is_set():
+            printed.set()
+            print(json.dumps(line), flush=True)
+
+    def bail():
+        emit()
+        os._exit(0)
+    dog = threading.Timer(float(os.environ.get("CZB_BENCH_TAIL_S", "420")), bail)
+    dog.daemon = True
+    dog.start()
+    try:
+        if world == 1 and not args.no_cpu and rank == 0:
+            r = run_cpu_child("sample", 3, 1)
+            if r:
+                line["cpu_baseline"] = {"value": r["value"], "unit": "GLUPS", "cores": r["cores"], "kind": "port",
+                                        "sample": r["sample"]}
+        if not args.no_ttc and not args.no_also:
+            if world == 1:
+                ttc = time_to_convergence()
+                cpu = run_cpu_child("ttc", timeout=400) if (ttc and not args.no_cpu) else None
+            else:
+                ttc = ttc_cases(make_cz, barrier, max_over_ranks, TTC_CASES[1:] + TTC_BIG, torch)
+                cpu = None
+            if ttc:
+                gold = load_golden_configs()
+                for label, nn, solver, itmax, omg, pre, real in TTC_CASES + TTC_BIG:
+                    if label in ttc:
+                        g = gold.get(golden_key(real, nn, solver, omg, pre))
+                        if g:
+                            ttc[label]["oracle_iterations"] = int(g["itr"])
+                            ttc[label]["oracle_residual"] = float(g["res"])
+                        if cpu and label in cpu:
+                            ttc[label]["cpu"] = cpu[label]
+                if "also_f64" in ttc:
+                    line["also_f64"] = ttc.pop("also_f64")
+                line["time_to_convergence"] = ttc
+    except Exception as ex:      # never lose the headline
+        sys.stderr.write("bench.py: optional legs failed: %r\n" % (ex,))
+    dog.cancel()
+    emit()
     if dist is not None:
         dist.destroy_process_group()
 
 
-# BASELINE.json configs[0..3] to convergence (eps = 1e-5, cz.h:162): (label, N, solver, ItrMax, omega, precond)
-TTC_CASES = (("jacobi 64^3 w=0.8", 64, "jacobi", 4000, 0.8, None),
-             ("sor2sma 256^3 w=1.95", 256, "sor2sma", 20000, 1.95, None),
-             ("pbicgstab+sor2sma 512^3 w=1.1", 512, "pbicgstab", 400, 1.1, "sor2sma"),
-             ("pcr_rb 512^3 w=1.9", 512, "pcr_rb", 8000, 1.9, None))
-
-
-def ttc_worker():
-    """Child process of time_to_convergence(): prints one JSON object."""
-    import torch
-    import cubez_b200
+def ttc_cases(make_cz, barrier, max_over_ranks, cases, torch):
+    """Solve each case to res < 1e-5 from the reference's start field (P = 0 + Dirichlet faces, cz_Evaluate.cpp:375-390);
+    time = the library's own CUDA events around the solver loop, max over ranks."""
     out = {}
-    for label, n, solver, itmax, omg, pre in TTC_CASES:
-        cz = cubez_b200.CZ([n] * 3, "f32")
+    for label, n, solver, itmax, omg, pre, real in cases:
+        cz = make_cz([n] * 3, real, eps=1.0e-5)
         P, RHS = cz.setup_laplace()
         cz.solve(solver, P, RHS, 3, omg, precond=pre, want_history=False)          # warm-up (tables, work fields)
-        P, RHS = cz.setup_laplace()                                                # the reference's start: P = 0 + Dirichlet faces
-        torch.cuda.synchronize()
+        P, RHS = cz.setup_laplace()
+        barrier()
         o = cz.solve(solver, P, RHS, itmax, omg, precond=pre, want_history=False)
-        out[label] = {"n": n, "solver": solver, "precond": pre, "omega": omg, "iterations": int(o["itr"]),
-                      "residual": float(o["res"]), "converged": bool(0 < o["itr"] and o["res"] < 1.0e-5),
-                      "solver_loop_ms": float(o["ms"])}
+        barrier()
+        ms = max_over_ranks(float(o["ms"]))
+        it = int(o["itr"])
+        out[label] = {"n": n, "solver": solver, "precond": pre, "omega": omg, "real": real, "iterations": it,
+                      "residual": float(o["res"]), "converged": bool(0 < it and o["res"] < 1.0e-5),
+                      "solver_loop_ms": ms, "ms_per_iteration": ms / max(it, 1)}
         cz.close()
         del P, RHS
         torch.cuda.empty_cache()
+    return out
+
+
+# double precision on configs[2]'s grid (BASELINE.json: "512^3 float and double"): (label, solver, precond, omega, B/cell, k)
+F64_ALSO = (("sor2sma", "sor2sma", None, 1.5, 32.0, 12), ("pbicgstab+sor2sma", "pbicgstab", "sor2sma", 1.5, 680.0, 6),
+            ("jacobi", "jacobi", None, 0.8, 24.0, 12), ("pcr_rb", "pcr_rb", None, 1.5, 40.0, 8))
+
+
+def ttc_worker():
+    """Child process of time_to_convergence() at N = 1: prints one JSON object."""
+    import torch
+    import cubez_b200
+    from cubez_b200 import synth
+
+    def make_cz(gsz, real="f32", eps=1.0e-5):
+        return cubez_b200.CZ(gsz, real, eps=eps)
+
+    def barrier():
+        torch.cuda.synchronize()
+    out = ttc_cases(make_cz, barrier, lambda x: x, TTC_CASES + TTC_BIG, torch)
+    # f64 throughput at 512^3, device resident
+    f64 = {}
+    n = 512
+    cz = cubez_b200.CZ([n] * 3, "f64", eps=0.0)
+    cells = float(cz.inner_cells_global)
+    peak = measured_peak()[0]
+    for label, solver, pre, omg, bpc, k in F64_ALSO:
+        P, RHS = cz.setup_laplace()
+        synth.fill(P, cz.sz)
+        cz.bc_k(P)
+        cz.solve(solver, P, RHS, 3, omg, precond=pre, want_history=False)
+        ms = []
+        for w in range(3):
+            torch.cuda.synchronize()
+            o = cz.solve(solver, P, RHS, k, omg, precond=pre, want_history=False)
+            ms.append(float(o["ms"]) / ((k - 1) if solver == "pbicgstab" else k))
+        m = sorted(ms)[1]
+        gl = cells / (m * 1e-3) / 1e9
+        f64[label] = {"value": gl, "unit": "G cell-iterations/s", "n": n, "ms_per_iteration": m,
+                      "algorithmic_bytes_per_cell": bpc, "hbm_frac_of_measured": gl * bpc / peak}
+        del P, RHS
+    cz.close()
+    out["also_f64"] = f64
     print(json.dumps(out), flush=True)
 
 
-def time_to_convergence(timeout=180):
+def time_to_convergence(timeout=300):
     """Runs ttc_worker() in a child process; None on any failure (the headline line must not depend on it)."""
     try:
         p = subprocess.run([sys.executable, os.path.abspath(__file__), "--ttc-worker"], capture_output=True, text=True,
@@ -325,12 +606,16 @@ def main():
     ap.add_argument("--impl", default="cubez_b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-also", action="store_true", help="skip the PBiCGstab / Jacobi / line-SOR side measurements")
-    ap.add_argument("--no-ttc", action="store_true", help="skip the time-to-convergence child process")
+    ap.add_argument("--no-ttc", action="store_true", help="skip the time-to-convergence leg")
     ap.add_argument("--weak", action="store_true", help="weak scaling: 1024 x (1024*N) x 1024 instead of the fixed cube")
     ap.add_argument("--ttc-worker", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--cpu-worker", default=None, help=argparse.SUPPRESS)
     args = ap.parse_args()
     if args.ttc_worker:
         ttc_worker()
+        return
+    if args.cpu_worker:
+        cpu_worker(args.cpu_worker, args.steps, args.warmup)
         return
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -344,6 +629,8 @@ def main():
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29511"),
                os.path.abspath(__file__), "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)]
         cmd += ["--weak"] if args.weak else []
+        cmd += ["--no-also"] if args.no_also else []
+        cmd += ["--no-ttc"] if args.no_ttc else []
         sys.exit(subprocess.call(cmd))
     run_gpu(args, rank, world, local_rank)
 

@@ -659,7 +659,7 @@ int march_rows(int cfg) {
 // returns 0 = not eligible, 1 = done, 2 = done including the second accumulator slot2 (packed MODE_AX)
 int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_or_w, REAL* out, const REAL* cf,
           REAL omg, int ip, int jr0, int jr1, int slot, bool add, int slot2 = -1, bool zsrc = false, int part = 0,
-          unsigned int* sig = nullptr, int* sig_ctas = nullptr) {
+          unsigned int* sig = nullptr, int* sig_ctas = nullptr, bool dry = false) {
   if (!fused_eligible(G)) return 0;
   MarchArgs a;
   a.G = G;
@@ -721,6 +721,7 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
   if (sig_ctas) *sig_ctas = a.ntk * a.nti;
   a.zsrc = (zsrc && packed && !lin) ? 1 : 0;
   if (zsrc && !a.zsrc) return 0;   // only the packed two-colour kernel can skip the source
+  if (dry) return 1;               // eligibility probe: every early-out above has been passed, nothing is launched
   const size_t T = (size_t)a.ei * EKB;
   const CUtensorMap& tp = tmap_for(p, G, a.ei);
   const CUtensorMap& tb = (mode == MODE_AX) ? tp : tmap_for(b_or_w, G, a.ei);
@@ -760,6 +761,13 @@ bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, 
                       int ip, int jr0, int jr1, int slot, bool add, bool zero_src, int part, unsigned int* sig,
                       int* sig_ctas) {
   return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add, -1, zero_src, part, sig, sig_ctas) != 0;
+}
+// Would launch_rb2_fused with these options launch?  (Same early-outs as march(), nothing enqueued.)  The solve
+// loops decide ONCE, before choosing the fused / overlapped loop, so an iteration can never become a silent no-op.
+bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part, bool with_sig) {
+  static unsigned int dummy_sig[2];
+  return march(MODE_RB2, L, G, nullptr, nullptr, nullptr, cf, (REAL)1, 0, G.jst, G.jed, 0, false, -1, zero_src, part,
+               with_sig ? dummy_sig : nullptr, nullptr, true) != 0;
 }
 bool rb2_zero_src_supported(const Geo& G, const REAL* cf) {
 #ifdef _REAL_IS_DOUBLE_

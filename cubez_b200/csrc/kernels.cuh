@@ -108,6 +108,7 @@ bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, 
 // the first two owned planes are stored everywhere, sig[1] when the last chunk (scheduled first) is complete.
 // zero_src: p is known to be all zero and is not read at all (packed float kernel only; check first)
 bool rb2_zero_src_supported(const Geo& G, const REAL* cf);
+bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part, bool with_sig);
 // part = 1: only the two planes at each end of the owned j range (what a slab sends to its neighbours),
 // part = 2: only the planes between; 1 then 2 equals one part = 0 sweep (packed float kernel only; check first)
 bool rb2_parts_supported(const Geo& G, const REAL* cf);

@@ -50,6 +50,46 @@ double Runtime::read_acc(int slot) {
   return h_state->acc[slot];
 }
 
+void* Runtime::mirror_acquire(const void* host, size_t bytes) {
+  if (mirror_cap == 0) {
+    const char* e = getenv("CZB_MIRROR_CAP_MB");
+    if (e) mirror_cap = (size_t)atoll(e) << 20;
+    else { size_t fr = 0, tot = 0; CZB_CHECK(cudaMemGetInfo(&fr, &tot)); mirror_cap = tot / 4; }
+    if (mirror_cap == 0) mirror_cap = 1;
+  }
+  auto it = mirrors.find(host);
+  if (it != mirrors.end() && it->second.bytes < bytes && it->second.pins == 0) {   // grown: replace
+    CZB_CHECK(cudaStreamSynchronize(stream));
+    cudaFree(it->second.dev); mirror_bytes -= it->second.bytes; mirrors.erase(it); it = mirrors.end();
+  }
+  if (it != mirrors.end() && it->second.bytes < bytes) {
+    fprintf(stderr, "czb200: host array %p is passed twice with different sizes in one call\n", host); abort();
+  }
+  if (it == mirrors.end()) {
+    // evict least-recently-used, unpinned mirrors until the new one fits under the cap
+    while (!mirrors.empty() && (mirror_bytes + bytes > mirror_cap || mirrors.size() >= 64)) {
+      auto victim = mirrors.end();
+      for (auto m = mirrors.begin(); m != mirrors.end(); ++m)
+        if (m->second.pins == 0 && (victim == mirrors.end() || m->second.stamp < victim->second.stamp)) victim = m;
+      if (victim == mirrors.end()) break;          // everything left is in use by the current call
+      CZB_CHECK(cudaStreamSynchronize(stream));
+      cudaFree(victim->second.dev); mirror_bytes -= victim->second.bytes; mirrors.erase(victim);
+    }
+    void* d = nullptr;
+    CZB_CHECK(cudaMalloc(&d, bytes));
+    it = mirrors.emplace(host, Mirror{d, bytes, 0ull, 0}).first;
+    mirror_bytes += bytes;
+  }
+  it->second.stamp = ++mirror_clock;
+  it->second.pins++;
+  return it->second.dev;
+}
+
+void Runtime::mirror_release(const void* host) {
+  auto it = mirrors.find(host);
+  if (it != mirrors.end() && it->second.pins > 0) it->second.pins--;
+}
+
 bool is_device_ptr(const void* p) {
   cudaPointerAttributes at;
   cudaError_t e = cudaPointerGetAttributes(&at, p);

@@ -9,7 +9,9 @@ namespace czb {
 
 long long launch_count();
 
-struct Mirror { void* dev; size_t bytes; };
+// Device mirror of a caller's host array (per-call reference ABI).  The cache is bounded: least recently used
+// mirrors that no call is using are freed once the total exceeds Runtime::mirror_cap bytes or 64 entries.
+struct Mirror { void* dev; size_t bytes; unsigned long long stamp; int pins; };
 
 struct Runtime {
   bool inited = false;
@@ -22,6 +24,10 @@ struct Runtime {
   LoopState* h_state = nullptr;       // pinned host copy
   unsigned long long* d_err = nullptr;
   std::unordered_map<const void*, Mirror> mirrors;
+  size_t mirror_bytes = 0, mirror_cap = 0;   // cap: CZB_MIRROR_CAP_MB, default a quarter of the device memory
+  unsigned long long mirror_clock = 0;
+  void* mirror_acquire(const void* host, size_t bytes);   // pins the mirror until mirror_release
+  void mirror_release(const void* host);
   PcrTables pcr2{0, 0, 0, 0, nullptr, nullptr};
   PcrTables pcr4{0, 0, 0, 0, nullptr, nullptr};
   size_t h2d_bytes = 0, d2h_bytes = 0;   // staged traffic (per-call ABI with host pointers)
@@ -51,14 +57,7 @@ class Arg {
     if (!p_ || is_device_ptr(p_)) { d_ = p_; staged_ = false; return; }
     Runtime& R = rt();
     const size_t bytes = sizeof(T) * n_;
-    auto it = R.mirrors.find((const void*)p_);
-    if (it == R.mirrors.end() || it->second.bytes < bytes) {
-      if (it != R.mirrors.end()) { cudaFree(it->second.dev); R.mirrors.erase(it); }
-      void* d = nullptr;
-      CZB_CHECK(cudaMalloc(&d, bytes));
-      it = R.mirrors.emplace((const void*)p_, Mirror{d, bytes}).first;
-    }
-    d_ = (T*)it->second.dev;
+    d_ = (T*)R.mirror_acquire((const void*)p_, bytes);
     staged_ = true;
     if (in) {
       CZB_CHECK(cudaMemcpyAsync(d_, p_, bytes, cudaMemcpyHostToDevice, R.stream));
@@ -66,13 +65,17 @@ class Arg {
     }
   }
   ~Arg() {
-    if (staged_ && out_) {
-      Runtime& R = rt();
+    if (!staged_) return;
+    Runtime& R = rt();
+    if (out_) {
       CZB_CHECK(cudaMemcpyAsync((void*)p_, d_, sizeof(T) * n_, cudaMemcpyDeviceToHost, R.stream));
       CZB_CHECK(cudaStreamSynchronize(R.stream));
       R.d2h_bytes += sizeof(T) * n_;
     }
+    R.mirror_release((const void*)p_);
   }
+  Arg(const Arg&) = delete;
+  Arg& operator=(const Arg&) = delete;
   T* dev() const { return d_; }
   bool staged() const { return staged_; }
  private:

@@ -256,8 +256,10 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      // bc_k (cz_Poisson.cpp:73) is idempotent once both ping-pong buffers hold the Dirichlet values (see RBSOR)
-      if (it <= 2) launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
+      // bc_k (cz_Poisson.cpp:73) is idempotent once both ping-pong buffers hold the Dirichlet values (see RBSOR).
+      // It is launched WITHOUT the done gate (here and in every loop below): the reference calls it before
+      // `if (res < eps) break` (cz_Poisson.cpp:73-77, 495-497), i.e. also on the converging iteration.
+      if (it <= 2) launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
     }
   };
   int itr, done_iters;
@@ -287,7 +289,7 @@ int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 1) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -303,7 +305,15 @@ int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool
 int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool converge_check) {
   const int ip = parity_ip();
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
-  const bool fused = !maf && (variant == 0) && fused_eligible(G);
+  // Eligibility of every launch form the loop below uses is decided ONCE, here (march() refuses e.g. grids with
+  // more tiles than reduction slots); a refused launch inside the loop would make the iteration a silent no-op.
+  const bool zs_wanted = !converge_check && pre_zero_src;
+  const bool fused = !maf && (variant == 0) && fused_eligible(G) &&
+                     rb2_fused_launchable(launch(), G, cf, false, 0, false) &&
+                     (!zs_wanted || rb2_fused_launchable(launch(), G, cf, true, 0, false));
+  auto must = [](bool ok) {
+    if (!ok) { fprintf(stderr, "czb200: the fused red-black sweep refused a launch it had accepted at set-up\n"); abort(); }
+  };
   int itr, done_iters;
   if (fused) {
     // Both colours in one pass (fused.cu MODE_RB2), ping-pong between X and WRK.  Multi-rank: one
@@ -327,10 +337,14 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     // converged field (it writes the other ping-pong buffer), iteration k+2 waits for the test of k, so
     // iteration counts, histories and the returned field are those of a loop that tests every iteration.
     static const bool no_ovl = getenv("CZB_NO_OVERLAP") != nullptr;
-    const bool ovl = comm && comm->nranks > 1 && !no_ovl && rb2_parts_supported(G, cf);
-    if (ovl) ensure_comm_stream();
     static const bool no_sig = getenv("CZB_NO_SIGNAL") != nullptr;   // fall back to edge launch + interior launch
-    const bool use_sig = ovl && !no_sig;
+    const bool ovl_ok = comm && comm->nranks > 1 && !no_ovl && rb2_parts_supported(G, cf);
+    const bool sig_ok = ovl_ok && !no_sig && rb2_fused_launchable(launch(), G, cf, zs_wanted, 0, true);
+    const bool parts_ok = ovl_ok && rb2_fused_launchable(launch(), G, cf, zs_wanted, 1, false) &&
+                          rb2_fused_launchable(launch(), G, cf, zs_wanted, 2, false);
+    const bool ovl = sig_ok || parts_ok;
+    if (ovl) ensure_comm_stream();
+    const bool use_sig = sig_ok;
     auto body_ovl = [&](int it) {
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
@@ -342,19 +356,19 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (use_sig) {
         // one launch; the communication stream is released by the kernel's edge counters
         int ctas = 0;
-        launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 0, d_sig, &ctas);
+        must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 0, d_sig, &ctas));
         sig_target += (unsigned int)ctas;
         stream_wait_geq(cs, d_sig, sig_target);
         stream_wait_geq(cs, d_sig + 1, sig_target);
         comm_halo(comm, dst, G, 2, cs);
         CZB_CHECK(cudaEventRecord(ev_halo[it & 1], cs));
       } else {
-        launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 1);
+        must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 1));
         CZB_CHECK(cudaEventRecord(ev_edge, R.stream));
         CZB_CHECK(cudaStreamWaitEvent(cs, ev_edge, 0));
         comm_halo(comm, dst, G, 2, cs);
         CZB_CHECK(cudaEventRecord(ev_halo[it & 1], cs));
-        launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, true, zs, 2);
+        must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, true, zs, 2));
       }
       if (converge_check) {
         CZB_CHECK(cudaEventRecord(ev_int, R.stream));
@@ -365,7 +379,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
         CZB_CHECK(cudaEventRecord(ev_fin[it & 1], cs));
         if (it <= 2) {   // bc_k after the exchange, as in the plain loop below
           CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_halo[it & 1], 0));
-          launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
+          launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
         }
       }
       cs_used = true;
@@ -376,7 +390,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       REAL* dst = (it & 1) ? W : X;
       Launch L = launch();
       // first preconditioner sweep: xx is all zero by contract (cz_Poisson.cpp:405,441) and is not read
-      launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, rs, false, !converge_check && it == 1 && pre_zero_src);
+      must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, rs, false, !converge_check && it == 1 && pre_zero_src));
       Comm_S(dst, 2);
       if (converge_check) {
         Comm_SUM(0);
@@ -384,7 +398,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
         // bc_k (cz_Poisson.cpp:226) is idempotent: the sweep never changes a boundary node and carries
         // the boundary nodes it stores over from src, so once both ping-pong buffers have received the
         // Dirichlet values (iterations 1 and 2) every later call would rewrite identical data.
-        if (it <= 2) launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
+        if (it <= 2) launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
@@ -404,7 +418,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (converge_check) {
         Comm_SUM(0);
         launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-        if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+        if (it <= 1) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
@@ -460,7 +474,7 @@ int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flo
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 1) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -493,7 +507,7 @@ int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, 
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 1) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -526,7 +540,7 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
       Comm_S(dst, 1);
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 2) launch_bc_k(L, G, dst, pitch, bc_origin, nID, head[1] - 1);
+      if (it <= 2) launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
     };
     itr = run_checked(itr_max, res, body);
     done_iters = h_state[0].itr;
@@ -636,7 +650,7 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
     }
     Comm_S(X, 1); Comm_SUM(4);                                               // :486-488
     scalar(3);                                                               // :490-500
-    launch_bc_k(L, G, X, pitch, bc_origin, nID, head[1] - 1);                                // :495
+    launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);                                // :495
   };
   // for (itr=1; itr<ItrMax; itr++)  (cz_Poisson.cpp:373)
   const int n_it = ItrMax - 1;

@@ -1093,4 +1093,23 @@ void calc_ax_maf_(REAL* ap, REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y
   });
 }
 
+// ------------------------------------------------------------------ harness helpers (not reference symbols)
+// bench.py's CPU arm: the OpenMP runtime reads OMP_NUM_THREADS once, when it is loaded; a launcher
+// (torchrun) may have exported OMP_NUM_THREADS=1 before that.  These two calls set / report the team
+// size the kernels above actually run with (cz_Evaluate.cpp:34-39 reads the same value for its banner).
+void oracle_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+int oracle_max_threads() {
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+
 }  // extern "C"

@@ -31,5 +31,43 @@ def test_ttc_cases_are_the_baseline_configs():
     labels = [c[0] for c in bench.TTC_CASES]
     assert any("jacobi 64^3" in x for x in labels) and any("sor2sma 256^3" in x for x in labels)
     assert any("pbicgstab+sor2sma 512^3" in x for x in labels) and any("pcr_rb 512^3" in x for x in labels)
-    for label, n, solver, itmax, omg, pre in bench.TTC_CASES:
-        assert solver in ("jacobi", "sor2sma", "pbicgstab", "pcr_rb") and 0 < omg < 2 and itmax > 0
+    for label, n, solver, itmax, omg, pre, real in bench.TTC_CASES + bench.TTC_BIG:
+        assert solver in ("jacobi", "sor2sma", "pbicgstab", "pcr_rb") and 0 < omg < 2 and itmax > 0 and real in ("f32", "f64")
+    assert any("f64" in x for x in labels)                      # configs[2] asks for float AND double
+    assert any("1024^3" in c[0] for c in bench.TTC_BIG)         # configs[4]
+
+
+def test_cpu_arm_runs_with_an_explicit_openmp_team(monkeypatch):
+    """under torchrun OMP_NUM_THREADS=1 is exported; the CPU arm must run in a child whose environment sets
+    the team size, and must report omp_get_max_threads(), not os.cpu_count()."""
+    monkeypatch.setenv("OMP_NUM_THREADS", "1")
+    monkeypatch.setenv("CZB_BENCH_N", "48")
+    r = bench.run_cpu_child("sample", steps=2, warmup=1, timeout=300)
+    assert r is not None and r["value"] > 0
+    assert r["cores"] == bench.host_cores()
+    assert "omp_get_max_threads" in r["sample"]
+
+
+def test_golden_keys_of_the_ttc_cases_exist():
+    gold = bench.load_golden_configs()
+    for label, n, solver, itmax, omg, pre, real in bench.TTC_CASES:
+        assert bench.golden_key(real, n, solver, omg, pre) in gold, label
+
+
+def test_start_field_is_decomposition_independent():
+    import numpy as np
+    from cubez_b200 import decomp, synth
+    gsz = [20, 37, 18]
+    full = np.zeros(decomp.field_shape(gsz), np.float32)
+    synth.fill(full, gsz)
+    tot = 0
+    for nr in (2, 3, 5):
+        tot = 0
+        for r in range(nr):
+            d = decomp.slab_decompose(gsz, nr, r)
+            f = np.zeros(decomp.field_shape(d["sz"]), np.float32)
+            synth.fill(f, d["sz"], head_j=d["head"][1])
+            j0 = d["head"][1]                         # local plane 1 = global plane head
+            assert np.array_equal(f[2:-2, 2:-2, 2:-2], full[j0 + 1:j0 + 1 + d["sz"][1], 2:-2, 2:-2])
+            tot += synth.checksum_owned(f, d["idx"])
+        assert tot == synth.checksum_owned(full, [2, gsz[0] - 1, 2, gsz[1] - 1, 2, gsz[2] - 1])

@@ -2,9 +2,8 @@
 reference's kernel ABI through ctypes against the CPU oracle on a STRETCHED mesh with seeded random fields (bit-exact
 REAL fields), and the `*_maf` solve loops against the golden histories the unmodified reference driver wrote.
 
-Not collected by the default run (the file name does not match test_*.py): tests/test_gpu_zz_maf.py runs this file in a
-child process, so that a device fault in these not-yet-hardware-tested kernels cannot take the main GPU suite down.
-Run directly with:  python -m pytest tests/gpu_maf_cases.py -m gpu -q"""
+First hardware run: the round-1 driver box (GPUTEST_r01: all 42 cases passed inside the then child-process / xfail
+wrapper); since round 2 the cases are collected directly, one test id each."""
 import ctypes as C
 import json
 import os

@@ -1,0 +1,157 @@
+"""GPU parity against the CPU ORACLE at BASELINE.json's own grid sizes (VERDICT r1 "weak" item 2: the full-size
+tests of test_gpu_fullsize.py compare one CUDA path with another; these call the oracle).
+
+* a few iterations of every solver of configs[1..3] at 256^3 / 512^3, float and double, from a non-trivial start
+  field (hash of the global node index, cubez_b200/synth.py; right-hand side != 0): stationary solvers must give
+  bit-identical fields and residual sums within 1e-12; one PBiCGstab iteration within the north_star tolerance
+  (its scalars are REAL-rounded dot products whose last bit depends on the summation order);
+* one iteration of the 1024^3 cube (configs[4]) checked on a 36-plane window at j ~ 900 (byte offsets beyond
+  2^31, full-width 1028-cell rows and lines) against the oracle run on that slab alone: a cell of plane j after one
+  two-colour sweep depends on the old planes j-2 .. j+2 only;
+* configs[1] and configs[2] solved to convergence against the committed histories of the reference's unmodified
+  driver on the oracle kernels (tests/golden/baseline_configs.json): same iteration count (BiCGstab +-1).
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle_util as ou
+from cubez_b200 import synth
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _start(cz_or_oracle, is_gpu):
+    """P = hash field with Dirichlet faces, B = 0.05 * hash of a shifted index on inner nodes."""
+    c = cz_or_oracle
+    P, B = c.setup_laplace()
+    synth.fill(P, c.sz)
+    c.bc_k(P)
+    T = c.zeros()
+    synth.fill(T, c.sz, head_j=1 + 7)          # a different pattern for the right-hand side
+    if is_gpu:
+        B[3:-3, 3:-3, 3:-3] = T[3:-3, 3:-3, 3:-3] * 0.05
+    else:
+        B[3:-3, 3:-3, 3:-3] = T[3:-3, 3:-3, 3:-3] * c.dt(0.05)
+    return P, B
+
+
+STATIONARY = [
+    ("sor2sma", 256, 1.5, 3, "f32"), ("sor2sma", 512, 1.5, 3, "f32"), ("jacobi", 512, 0.8, 3, "f32"),
+    ("pcr_rb", 512, 1.5, 2, "f32"), ("pcr_rb_esa", 512, 1.5, 2, "f32"), ("pcr_j_esa", 256, 0.9, 2, "f32"),
+    ("sor2sma", 512, 1.5, 2, "f64"), ("jacobi", 256, 0.8, 3, "f64"), ("pcr_rb", 256, 1.5, 2, "f64"),
+]
+
+
+@pytest.mark.parametrize("solver,n,coef,iters,real", STATIONARY, ids=lambda v: str(v))
+def test_stationary_iterations_equal_oracle(solver, n, coef, iters, real):
+    import cubez_b200
+    cz = cubez_b200.CZ([n] * 3, real, eps=0.0)
+    P, B = _start(cz, True)
+    out = cz.solve(solver, P, B, iters, coef)
+    got = P.cpu().numpy()
+    cz.close()
+    o = ou.OracleCZ([n] * 3, real, eps=0.0)
+    Po, Bo = _start(o, False)
+    itr, res, hist = o.stationary(solver, Po, Bo, iters, coef)
+    assert out["itr"] == itr == iters + 1
+    assert np.array_equal(got[2:-2, 2:-2, 2:-2], Po[2:-2, 2:-2, 2:-2]), \
+        "%s %d^3 %s: field differs from the oracle (max %g)" % (solver, n, real, np.abs(got - Po).max())
+    np.testing.assert_allclose(out["history"], hist, rtol=1e-12)
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+def test_pbicgstab_iteration_512_equals_oracle(real):
+    """configs[2]: ItrMax = 3 -> two PBiCGstab + sor2sma iterations (16 sweeps each) at 512^3."""
+    import cubez_b200
+    n = 512
+    cz = cubez_b200.CZ([n] * 3, real, eps=0.0)
+    P, B = _start(cz, True)
+    out = cz.solve("pbicgstab", P, B, 3, 1.1, "sor2sma")
+    got = P.cpu().numpy()
+    cz.close()
+    o = ou.OracleCZ([n] * 3, real, eps=0.0)
+    Po, Bo = _start(o, False)
+    itr, res, hist = o.pbicgstab(Po, Bo, 3, 1.1, "sor2sma")
+    assert out["itr"] == itr
+    tol = 1e-5 if real == "f32" else 1e-12
+    np.testing.assert_allclose(out["history"], hist, rtol=10 * tol if real == "f32" else 1e-9)
+    scale = np.abs(Po).max()
+    np.testing.assert_allclose(got[2:-2, 2:-2, 2:-2], Po[2:-2, 2:-2, 2:-2], rtol=0, atol=(tol if real == "f32" else 1e-10) * scale)
+
+
+@pytest.mark.parametrize("solver,coef", [("sor2sma", 1.5), ("jacobi", 0.8), ("pcr_rb", 1.5)])
+def test_1024_cube_window_equals_oracle_slab(solver, coef):
+    """configs[4]: one iteration on the whole 1024^3 cube; planes J0+2 .. J0+37 (J0 = 901, element offsets beyond
+    2^31 bytes) against the oracle sweeping the 40-plane slab J0 .. J0+39 of the same start field."""
+    import torch
+    import cubez_b200
+    n, J0, NS = 1024, 901, 40
+    cz = cubez_b200.CZ([n] * 3, "f32", eps=0.0)
+    P, B = _start(cz, True)
+    # local C plane index of global Fortran plane j is j + 1; take planes J0-2 .. J0+NS+1
+    lo, hi = J0 - 2 + 1, J0 + NS + 1 + 2
+    X0 = P[lo:hi].cpu().numpy().copy()
+    B0 = B[lo:hi].cpu().numpy().copy()
+    out = cz.solve(solver, P, B, 1, coef)
+    assert out["itr"] == 2
+    got = P[lo:hi].cpu().numpy()
+    cz.close()
+    del P, B
+    torch.cuda.empty_cache()
+    # the slab as a sub-domain with neighbours on both j faces: every local plane 1..NS is "inner"
+    o = ou.OracleCZ([n, n, n], "f32", sz=[n, NS, n], idx=[2, n - 1, 1, NS, 2, n - 1], nID=[-1, -1, 0, 0, -1, -1],
+                    head=[1, J0, 1], eps=0.0)
+    assert X0.shape == o.shape
+    o.ac1 = np.float32(coef)
+    res = C.c_double(0)
+    if solver == "sor2sma":
+        o.sweep_rb(X0, B0, res, ip=(1 + J0 + 1 + 1) % 2)       # cz_Poisson.cpp:181 with head = (1, J0, 1)
+    elif solver == "jacobi":
+        o.sweep_jacobi(X0, B0, res)
+    else:
+        assert (J0 - 1) % 2 == 0                                  # pcr_rb colours lines by the LOCAL i+j (cz_solver.f90:549)
+        o.sweep_pcr("pcr_rb", X0, B0, res)
+    # local planes 3 .. NS-2 (C index +1) are free of the stale-halo influence
+    a, b = 3 + 1, NS - 2 + 2
+    assert np.array_equal(got[a:b, 3:-3, 3:-3], X0[a:b, 3:-3, 3:-3]), \
+        "%s 1024^3: window differs from the oracle (max %g)" % (solver, np.abs(got[a:b] - X0[a:b]).max())
+
+
+def _golden(real, n, solver, coef, pre):
+    g = json.load(open(os.path.join(HERE, "golden", "baseline_configs.json")))
+    return g.get("%s %d %s %s %s" % (real, n, solver, coef, pre))
+
+
+@pytest.mark.parametrize("real,n,solver,itmax,coef,pre", [
+    ("f32", 64, "jacobi", 4000, "0.8", None),
+    ("f32", 256, "sor2sma", 20000, "1.95", None),
+    ("f64", 256, "sor2sma", 20000, "1.95", None),
+    ("f32", 512, "pbicgstab", 400, "1.1", "sor2sma"),
+    ("f64", 512, "pbicgstab", 400, "1.1", "sor2sma"),
+    ("f32", 512, "pbicgstab", 400, "0.8", "jacobi"),
+    ("f32", 256, "pcr_rb", 8000, "1.9", None),
+    ("f32", 512, "pcr_rb", 8000, "1.9", None),
+])
+def test_baseline_configs_converge_like_the_reference_driver(real, n, solver, itmax, coef, pre):
+    import cubez_b200
+    g = _golden(real, n, solver, coef, pre)
+    if g is None:
+        pytest.skip("no golden for this case yet (tests/golden/make_golden_baseline.py)")
+    cz = cubez_b200.CZ([n] * 3, real)
+    P, RHS = cz.setup_laplace()
+    out = cz.solve(solver, P, RHS, itmax, float(coef), pre)
+    err, loc = cz.exact_error(P)
+    cz.close()
+    bicg = solver == "pbicgstab"
+    assert abs(out["itr"] - g["itr"]) <= (1 if bicg else 0), (out["itr"], g["itr"])
+    h = out["history"]
+    for k, v in g["history_at"].items():
+        k = int(k)
+        if k < len(h) and (not bicg or k < 12):
+            assert abs(h[k] - float(v)) <= (2e-6 if not bicg else (1e-4 if real == "f32" else 2e-6)) * float(v), (k, h[k], v)
+    assert abs(err - float(g["errmax"])) <= 1e-6 + (2e-2 * err if bicg else 1e-6 * err)

@@ -44,7 +44,7 @@ def _oracle_case(g):
     return itr, res, hist, P
 
 
-PLAIN = [i for i, g in enumerate(GOLDEN) if not g["solver"].endswith("_maf")]   # the `_maf` cases: test_gpu_zz_maf.py
+PLAIN = [i for i, g in enumerate(GOLDEN) if not g["solver"].endswith("_maf")]   # the `_maf` cases: test_gpu_maf.py
 
 
 @pytest.mark.parametrize("variant", [1, 0])

@@ -7,7 +7,7 @@ block, launches executed sequentially, device memory = malloc) and driven throug
 
 This covers what a GPU-less container can: index arithmetic, launch geometry, colour / wavefront line selection,
 shared-memory ping-pong, the folded 2x2 last stage, reduction finishers, host-pointer staging and the loop control.
-It cannot show barrier placement or races; the -m gpu tests (test_gpu_zz_maf.py) remain the parity tests proper, and
+It cannot show barrier placement or races; the -m gpu tests (test_gpu_maf.py) remain the parity tests proper, and
 this emulated library is test infrastructure that never ships (the product aborts without a CUDA device)."""
 import ctypes as C
 import json
