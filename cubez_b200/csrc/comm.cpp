@@ -106,8 +106,82 @@ Comm* comm_create(int nranks, int rank, const void* id128, int lo, int hi) {
 
 void comm_destroy(Comm* c) {
   if (!c) return;
+  for (int d = 0; d < 2; ++d) if (c->peer_block[d]) cudaIpcCloseMemHandle(c->peer_block[d]);
+  if (c->block) cudaFree(c->block);
   if (c->nccl) api().CommDestroy((ncclComm_t)c->nccl);
   delete c;
+}
+
+// Header of the exported block; the inbox starts at the next 1 KB boundary (TMA needs 16-byte aligned planes).
+static const size_t kP2pHeader = 1024;
+
+bool comm_p2p_setup(Comm* c, size_t plane_elems, cudaStream_t s, bool want) {
+  if (!c || c->nranks <= 1 || !c->nccl) return false;
+  if (c->p2p_tried) return c->p2p && c->plane_elems == plane_elems;   // decided once per communicator (collectively)
+  c->p2p_tried = true;
+  static const bool off = getenv("CZB_NO_P2P") != nullptr;
+  NcclApi& A = api();
+  ncclComm_t comm = (ncclComm_t)c->nccl;
+  int ok = (off || !want) ? 0 : 1;
+  struct Wire { cudaIpcMemHandle_t h; int ok; int pad[15]; };   // 128 bytes
+  static_assert(sizeof(Wire) == 128, "wire record");
+  Wire mine; memset(&mine, 0, sizeof(mine));
+  const size_t bytes = kP2pHeader + 8 * plane_elems * sizeof(REAL);
+  if (ok && cudaMalloc(&c->block, bytes) != cudaSuccess) { cudaGetLastError(); c->block = nullptr; ok = 0; }
+  if (ok) {
+    CZB_CHECK(cudaMemsetAsync(c->block, 0, bytes, s));
+    if (cudaIpcGetMemHandle(&mine.h, c->block) != cudaSuccess) { cudaGetLastError(); ok = 0; }
+  }
+  mine.ok = ok;
+  // exchange the records with both neighbours (device staging: NCCL moves device memory)
+  Wire* d = nullptr;
+  CZB_CHECK(cudaMalloc((void**)&d, 3 * sizeof(Wire)));
+  CZB_CHECK(cudaMemsetAsync(d, 0, 3 * sizeof(Wire), s));
+  CZB_CHECK(cudaMemcpyAsync(d, &mine, sizeof(Wire), cudaMemcpyHostToDevice, s));
+  CZB_NCCL(A.GroupStart());
+  if (c->lo >= 0) { CZB_NCCL(A.Send(d, sizeof(Wire), ncclChar, c->lo, comm, s)); CZB_NCCL(A.Recv(d + 1, sizeof(Wire), ncclChar, c->lo, comm, s)); }
+  if (c->hi >= 0) { CZB_NCCL(A.Send(d, sizeof(Wire), ncclChar, c->hi, comm, s)); CZB_NCCL(A.Recv(d + 2, sizeof(Wire), ncclChar, c->hi, comm, s)); }
+  CZB_NCCL(A.GroupEnd());
+  Wire got[3];
+  CZB_CHECK(cudaMemcpyAsync(got, d, 3 * sizeof(Wire), cudaMemcpyDeviceToHost, s));
+  CZB_CHECK(cudaStreamSynchronize(s));
+  const int nb[2] = {c->lo, c->hi};
+  for (int side = 0; side < 2 && ok; ++side) {
+    if (nb[side] < 0) continue;
+    if (!got[1 + side].ok) { ok = 0; break; }
+    void* p = nullptr;
+    if (cudaIpcOpenMemHandle(&p, got[1 + side].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0; break; }
+    c->peer_block[side] = p;
+  }
+  // all ranks or none: a ring with one NCCL link would deadlock the stream waits
+  double* flag = nullptr;
+  CZB_CHECK(cudaMalloc((void**)&flag, sizeof(double)));
+  const double f = ok ? 0.0 : 1.0;
+  CZB_CHECK(cudaMemcpyAsync(flag, &f, sizeof(double), cudaMemcpyHostToDevice, s));
+  CZB_NCCL(A.AllReduce(flag, flag, 1, ncclFloat64, ncclSum, comm, s));
+  double bad = 0.0;
+  CZB_CHECK(cudaMemcpyAsync(&bad, flag, sizeof(double), cudaMemcpyDeviceToHost, s));
+  CZB_CHECK(cudaStreamSynchronize(s));
+  cudaFree(flag); cudaFree(d);
+  if (bad != 0.0) {
+    for (int side = 0; side < 2; ++side) if (c->peer_block[side]) { cudaIpcCloseMemHandle(c->peer_block[side]); c->peer_block[side] = nullptr; }
+    if (c->block) { cudaFree(c->block); c->block = nullptr; }
+    if (!off && c->rank == 0) fprintf(stderr, "czb200: peer transport unavailable (IPC mapping failed on some rank); halo exchange stays on NCCL\n");
+    return false;
+  }
+  c->plane_elems = plane_elems;
+  c->mbox = (unsigned int*)c->block;
+  c->inbox = (REAL*)((char*)c->block + kP2pHeader);
+  for (int side = 0; side < 2; ++side) {
+    if (!c->peer_block[side]) continue;
+    // we are the UPPER neighbour of our lower neighbour: our signals count in its from_hi (word 1), and vice versa
+    c->peer_mbox[side] = (unsigned int*)c->peer_block[side] + (side == 0 ? 1 : 0);
+    c->peer_ready[side] = (unsigned int*)c->peer_block[side] + (side == 0 ? 3 : 2);
+    c->peer_inbox[side] = (REAL*)((char*)c->peer_block[side] + kP2pHeader);
+  }
+  c->tgt[0] = c->tgt[1] = 0u; c->tgt_ready = 0u;
+  c->p2p = true;
+  return true;
 }
 
 void comm_halo(Comm* c, REAL* f, const Geo& G, int w, cudaStream_t s) {

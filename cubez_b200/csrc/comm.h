@@ -19,6 +19,25 @@ struct Comm {
   int nranks = 1, rank = 0;
   int lo = -1, hi = -1;     // neighbour ranks along j (-1: none)
   void* nccl = nullptr;     // ncclComm_t
+  // ---- peer transport (NVLink peer memory, no NCCL kernel in the halo path) ------------------------------
+  // Every rank owns one IPC-exported block:  mailbox {from_lo, from_hi, ready_lo, ready_hi} (32-bit counters the
+  // NEIGHBOURS increment with system-scope atomics: edge planes delivered / "my inbox is prepared, you may write")
+  // followed by the halo inbox  [2 slots][2 sides][2 planes]  of
+  // plane_elems REALs each (side 0 = planes owned by the lower neighbour, 1 = by the upper one).  A sweep of
+  // iteration `it` stores its edge planes into the neighbours' inbox slot it&1 and reads its own halos from
+  // slot (it-1)&1; the consumer's STREAM waits on the mailbox counters (cuStreamWaitValue32), no kernel spins.
+  bool p2p = false;
+  size_t plane_elems = 0;
+  void* block = nullptr;                    // local block (cudaMalloc)
+  unsigned int* mbox = nullptr;             // local counters {from_lo, from_hi}
+  REAL* inbox = nullptr;                    // local inbox, 8 planes
+  void* peer_block[2] = {nullptr, nullptr};  // mapped blocks of the lower / upper neighbour
+  unsigned int* peer_mbox[2] = {nullptr, nullptr};   // the word of THEIR mailbox that counts OUR signals
+  REAL* peer_inbox[2] = {nullptr, nullptr};
+  unsigned int* peer_ready[2] = {nullptr, nullptr};  // the word of THEIR mailbox that counts OUR "ready" posts
+  unsigned int tgt[2] = {0u, 0u};           // value from_lo / from_hi reach once every launch enqueued so far has signalled
+  unsigned int tgt_ready = 0u;              // loops started so far (each posts one "ready" to both neighbours)
+  bool p2p_tried = false;
 };
 
 int comm_unique_id(void* id128);
@@ -26,6 +45,11 @@ Comm* comm_create(int nranks, int rank, const void* id128, int lo, int hi);
 void comm_destroy(Comm* c);
 // Exchange `width` j-planes with both neighbours (guard planes <- neighbour's edge planes).
 void comm_halo(Comm* c, REAL* field, const Geo& G, int width, cudaStream_t s);
+// Set up the peer transport for fields with planes of `plane_elems` REALs: allocate and export the local block,
+// exchange the IPC handles with the ring neighbours, map theirs.  Collective over the communicator; returns true
+// only if EVERY rank succeeded (otherwise all ranks keep the NCCL transport).  CZB_NO_P2P=1 disables it.
+bool comm_p2p_setup(Comm* c, size_t plane_elems, cudaStream_t s, bool want = true);
+// `want`: this rank can use the transport (kernel eligibility); the result is the AND over all ranks.
 // In-place sum over ranks of `count` doubles in device memory.
 void comm_allreduce_sum(Comm* c, double* dev, int count, cudaStream_t s);
 

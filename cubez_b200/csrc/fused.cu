@@ -91,7 +91,13 @@ struct MarchArgs {
   int slot2;              // packed MODE_AX: second accumulator (ap, ap), -1 = none
   int zsrc;               // packed MODE_RB2: the source field is all zero and is not read
   int edges;              // packed MODE_RB2: relax only the first and last jl planes of jb0..jb1 (grid.y = 2)
-  unsigned int* sig;      // packed MODE_RB2: edge-plane completion counters {low, high} or null (fused_pk.cuh)
+  // packed MODE_RB2 on a j-slab (fused_pk.cuh, SIG instantiation): edge-plane completion counters, and -- peer
+  // transport -- the neighbours' halo inboxes (pre-biased so that the element offset inside OUR field applies) and
+  // the first plane index of our own inbox regions (tensor map tm_h), -1 = no neighbour on that side
+  unsigned int* sig_lo; unsigned int* sig_hi;
+  int p2p;
+  REAL* peer_lo; REAL* peer_hi;
+  int hin_lo, hin_hi;
 };
 
 struct FinStoreF {
@@ -604,7 +610,7 @@ void launch_march_cfg(int cfg, const Launch& L, const MarchArgs& a, const CUtens
 
 #ifndef _REAL_IS_DOUBLE_
 template <int NT, int CPT, int NSP_, int NSB_>
-void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const REAL* b) {
+void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const REAL* b, const REAL* inbox, bool sig) {
   constexpr int EI = NT / 32 * CPT;
   dim3 grid(a.ntk * a.nti, a.njc, 1);
   const size_t smem = (size_t)(NSP_ + NSB_ + NDE) * EI * EKB * sizeof(float) + 1024;
@@ -614,10 +620,15 @@ void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const R
     CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT, NSP_, NSB_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     set = true;
   }
-  const CUtensorMap& tp = tmap_for(p, a.G, EI);
-  const CUtensorMap& tb = tmap_for(b, a.G, EI);
-  if (a.sig) k_rb2_pk<NT, CPT, NSP_, NSB_, true><<<grid, NT, smem, L.s>>>(tp, tb, a);    // j-slab with edge-plane signals
-  else       k_rb2_pk<NT, CPT, NSP_, NSB_, false><<<grid, NT, smem, L.s>>>(tp, tb, a);
+  const CUtensorMap tp = tmap_for(p, a.G, EI);
+  const CUtensorMap tb = tmap_for(b, a.G, EI);
+  if (sig) {   // j-slab with edge-plane signals; halo inbox = a field of 8 planes (2 slots x 2 sides x 2 planes)
+    Geo H = a.G; H.nj = 8;
+    const CUtensorMap th = inbox ? tmap_for(inbox, H, EI) : tp;
+    k_rb2_pk<NT, CPT, NSP_, NSB_, true><<<grid, NT, smem, L.s>>>(tp, tb, th, a);
+  } else {
+    k_rb2_pk<NT, CPT, NSP_, NSB_, false><<<grid, NT, smem, L.s>>>(tp, tb, tp, a);
+  }
   CZB_CHECK(cudaGetLastError());
   count_launch();
 }
@@ -659,7 +670,7 @@ int march_rows(int cfg) {
 // returns 0 = not eligible, 1 = done, 2 = done including the second accumulator slot2 (packed MODE_AX)
 int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_or_w, REAL* out, const REAL* cf,
           REAL omg, int ip, int jr0, int jr1, int slot, bool add, int slot2 = -1, bool zsrc = false, int part = 0,
-          unsigned int* sig = nullptr, int* sig_ctas = nullptr, bool dry = false) {
+          const Rb2Sig* sig = nullptr, int* sig_ctas = nullptr, bool dry = false) {
   if (!fused_eligible(G)) return 0;
   MarchArgs a;
   a.G = G;
@@ -716,8 +727,21 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
   a.st = L.st; a.acc_st = L.acc_st; a.slot = slot; a.add = add ? 1 : 0;
   a.rb = L.rb;
   a.slot2 = lin ? slot2 : -1;
-  a.sig = (packed && !lin && part == 0) ? sig : nullptr;
-  if (sig && !a.sig) return 0;
+  const bool with_sig = sig && packed && !lin && part == 0;
+  if (sig && !with_sig) return 0;
+  a.sig_lo = a.sig_hi = nullptr; a.p2p = 0; a.peer_lo = a.peer_hi = nullptr; a.hin_lo = a.hin_hi = -1;
+  if (with_sig) {
+    a.sig_lo = sig->sig_lo; a.sig_hi = sig->sig_hi; a.p2p = sig->p2p;
+    if (sig->p2p) {
+      if (jhi - jlo + 1 < 4) return 0;               // the two edge-plane pairs must not overlap
+      // inbox layout (comm.h): plane index = slot*4 + side*2 + p ; side 0 = planes from the lower neighbour
+      const long long P = G.plane;
+      if (sig->peer_lo) a.peer_lo = sig->peer_lo + ((long long)(sig->out_slot * 4 + 2) - (jlo + G.g - 1)) * P;
+      if (sig->peer_hi) a.peer_hi = sig->peer_hi + ((long long)(sig->out_slot * 4 + 0) - (jhi - 1 + G.g - 1)) * P;
+      if (sig->has_lo) a.hin_lo = sig->in_slot * 4 + 0;
+      if (sig->has_hi) a.hin_hi = sig->in_slot * 4 + 2;
+    }
+  }
   if (sig_ctas) *sig_ctas = a.ntk * a.nti;
   a.zsrc = (zsrc && packed && !lin) ? 1 : 0;
   if (zsrc && !a.zsrc) return 0;   // only the packed two-colour kernel can skip the source
@@ -734,10 +758,11 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
     return (mode == MODE_AX && slot2 >= 0) ? 2 : 1;
   }
   if (packed) {   // look-ahead (raw TMA slots for p, b): cfg 2 = 3+3, 3 = 4+3, 4 = 5+4, 5 = 5+5
-    if (cfg == 3)      launch_rb2_pk_t<512, 2, 4, 3>(L, a, p, b_or_w);
-    else if (cfg == 4) launch_rb2_pk_t<512, 2, 5, 4>(L, a, p, b_or_w);
-    else if (cfg == 5) launch_rb2_pk_t<512, 2, 5, 5>(L, a, p, b_or_w);
-    else               launch_rb2_pk_t<512, 2, 3, 3>(L, a, p, b_or_w);
+    const REAL* inbox = (with_sig && sig->p2p) ? sig->inbox : nullptr;
+    if (cfg == 3)      launch_rb2_pk_t<512, 2, 4, 3>(L, a, p, b_or_w, inbox, with_sig);
+    else if (cfg == 4) launch_rb2_pk_t<512, 2, 5, 4>(L, a, p, b_or_w, inbox, with_sig);
+    else if (cfg == 5) launch_rb2_pk_t<512, 2, 5, 5>(L, a, p, b_or_w, inbox, with_sig);
+    else               launch_rb2_pk_t<512, 2, 3, 3>(L, a, p, b_or_w, inbox, with_sig);
     return 1;
   }
 #endif
@@ -758,16 +783,17 @@ bool fused_eligible(const Geo& G) {
 }
 
 bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf, REAL omg,
-                      int ip, int jr0, int jr1, int slot, bool add, bool zero_src, int part, unsigned int* sig,
+                      int ip, int jr0, int jr1, int slot, bool add, bool zero_src, int part, const Rb2Sig* sig,
                       int* sig_ctas) {
   return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add, -1, zero_src, part, sig, sig_ctas) != 0;
 }
 // Would launch_rb2_fused with these options launch?  (Same early-outs as march(), nothing enqueued.)  The solve
 // loops decide ONCE, before choosing the fused / overlapped loop, so an iteration can never become a silent no-op.
-bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part, bool with_sig) {
-  static unsigned int dummy_sig[2];
+bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part, bool with_sig, bool p2p) {
+  Rb2Sig sg{};
+  sg.p2p = p2p ? 1 : 0;
   return march(MODE_RB2, L, G, nullptr, nullptr, nullptr, cf, (REAL)1, 0, G.jst, G.jed, 0, false, -1, zero_src, part,
-               with_sig ? dummy_sig : nullptr, nullptr, true) != 0;
+               with_sig ? &sg : nullptr, nullptr, true) != 0;
 }
 bool rb2_zero_src_supported(const Geo& G, const REAL* cf) {
 #ifdef _REAL_IS_DOUBLE_

@@ -130,7 +130,8 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t addr, uint32_t parity) {   
 // of look-ahead), one plane is stored, one __syncthreads.
 template <int NT, int CPT, int NSP_, int NSB_, bool SIG>
 __global__ void __launch_bounds__(NT, 1)
-k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b, const MarchArgs a) {
+k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b,
+         const __grid_constant__ CUtensorMap tm_h, const MarchArgs a) {
   constexpr int RPW = NT / 32;             // tile rows covered by one pass of the CTA (one warp per row)
   constexpr int EI = RPW * CPT;            // tile rows
   constexpr int T = EI * EKB;              // cells per tile plane
@@ -150,15 +151,22 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   const int lane = tid & 31, wrow = tid >> 5;
 
   // ---- tile / chunk geometry ------------------------------------------------------------
-  // a.sig (j-slab of a multi-GPU run): the last chunk is scheduled first and counts its finished CTAs in
-  // sig[1], the CTAs of the first chunk count in sig[0] once their first two planes are stored; the
-  // communication stream waits on the two counters (stream memory operation) and sends the slab's edge
-  // planes while the rest of this launch is still running.
+  // SIG (j-slab of a multi-GPU run): the last chunk is scheduled first and counts its finished CTAs in
+  // *sig_hi, the CTAs of the first chunk count in *sig_lo once their first two planes are stored.
+  //  - NCCL transport: the counters are local; the communication stream waits on them (stream memory
+  //    operation) and sends the slab's edge planes while the rest of this launch is still running.
+  //  - peer transport (a.p2p): the edge planes are ALSO stored, by the same threads, into the neighbour's halo
+  //    inbox (peer memory over NVLink, a.peer_lo / a.peer_hi) and the counters live in the NEIGHBOUR's mailbox
+  //    (system-scope fence + atomic); the neighbour's stream waits on them before its next sweep, whose TMA loads
+  //    take the planes beyond the slab from its inbox (tm_h) instead of the field.  No copy kernel, no NCCL.
   // SIG is a template parameter: the single-GPU instantiation carries none of this.
   const int jc = (SIG && a.njc > 1) ? (blockIdx.y == 0 ? a.njc - 1 : (int)blockIdx.y - 1) : (int)blockIdx.y;
   const bool sig_lo = SIG && jc == 0, sig_hi = SIG && jc == a.njc - 1;
   if (a.st && a.st->done) {   // converged: nothing to do, but the counters must still advance
-    if (threadIdx.x == 0) { if (sig_lo) atomicAdd(a.sig, 1u); if (sig_hi) atomicAdd(a.sig + 1, 1u); }
+    if (SIG && threadIdx.x == 0) {
+      if (sig_lo && a.sig_lo) { if (a.p2p) atomicAdd_system(a.sig_lo, 1u); else atomicAdd(a.sig_lo, 1u); }
+      if (sig_hi && a.sig_hi) { if (a.p2p) atomicAdd_system(a.sig_hi, 1u); else atomicAdd(a.sig_hi, 1u); }
+    }
     return;
   }
   const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk;
@@ -187,7 +195,14 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
                  ::"r"(dst), "l"(tm), "r"(bar), "r"(2 * P0), "r"(R0), "r"(plane) : "memory");
   };
   auto issue_p = [&](int t) {   // plane pl0+t -> slot t % NSP_
-    issue_plane(raw_p + (uint32_t)(t % NSP_) * TB, bar0 + 8u * (uint32_t)(t % NSP_), &tm_p, pl0 + t + G.g - 1);
+    const int pl = pl0 + t;
+    const CUtensorMap* tm = &tm_p;
+    int cpl = pl + G.g - 1;
+    if (SIG && a.p2p) {         // planes of a neighbour slab: inbox[slot][side][2] (comm.h)
+      if (a.hin_lo >= 0 && pl < a.jb0) { tm = &tm_h; cpl = a.hin_lo + (pl - (a.jb0 - 2)); }
+      else if (a.hin_hi >= 0 && pl > a.jb1) { tm = &tm_h; cpl = a.hin_hi + (pl - (a.jb1 + 1)); }
+    }
+    issue_plane(raw_p + (uint32_t)(t % NSP_) * TB, bar0 + 8u * (uint32_t)(t % NSP_), tm, cpl);
   };
   auto issue_b = [&](int t) {
     issue_plane(raw_b + (uint32_t)(t % NSB_) * TB, bar0 + 8u * (uint32_t)(NSP_ + t % NSB_), &tm_b, bpl0 + t + G.g - 1);
@@ -337,6 +352,13 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
     const unsigned fRO = (do_red && red_owned) ? (XB ? (fl >> 12) : (fl >> 8)) & 0xfu : 0u;
     const unsigned fK = do_black ? (XB ? (fl >> 8) : (fl >> 12)) & 0xfu : 0u;      // blacks sit at !XB
     const unsigned fS = do_black ? (fl >> 16) & 0x3u : 0u;
+    // peer transport: plane s-1 is one of the two planes a neighbour needs -> second store into its inbox.
+    // peer_lo / peer_hi are pre-biased by the host so that the element offset inside OUR field applies.
+    float* peer_dst = nullptr;
+    if (SIG && a.p2p) {
+      if (a.peer_lo && (s - 1 == a.jb0 || s - 1 == a.jb0 + 1)) peer_dst = a.peer_lo;
+      else if (a.peer_hi && (s - 1 == a.jb1 - 1 || s - 1 == a.jb1)) peer_dst = a.peer_hi;
+    }
 
     F2 numR[CPT], numK[CPT], jnR[CPT], jsR[CPT], bbR[CPT], jnK[CPT];
 #pragma unroll
@@ -392,6 +414,7 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
       acc[0] += (double)lo(d2K);
       acc[0] += (double)hi(d2K);
       stg_unit_if(outp[m], wm1[m], (fS >> m) & 1u);
+      if (SIG && peer_dst) stg_unit_if(peer_dst + (outp[m] - a.out), wm1[m], (fS >> m) & 1u);
       outp[m] += G.plane;
       hb[C & 1][m] = XB ? bc[m].a : bc[m].b;     // right-hand side of the blacks of plane s+1 (used at step u+2)
     }
@@ -412,9 +435,9 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   // checked between the unrolled groups of four steps, i.e. after step 7, or at the end of a shorter chunk
   bool lo_pending = sig_lo;
   auto signal_lo = [&]() {
-    __threadfence();
+    if (a.p2p) __threadfence_system(); else __threadfence();
     __syncthreads();
-    if (tid == 0) atomicAdd(a.sig, 1u);
+    if (tid == 0 && a.sig_lo) { if (a.p2p) atomicAdd_system(a.sig_lo, 1u); else atomicAdd(a.sig_lo, 1u); }
     lo_pending = false;
   };
   if (((par + (unsigned)(pl0 + 1)) & 1u) == 0u) {
@@ -442,9 +465,9 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   }
   if (SIG && lo_pending) signal_lo();
   if (sig_hi) {
-    __threadfence();
+    if (a.p2p) __threadfence_system(); else __threadfence();
     __syncthreads();
-    if (tid == 0) atomicAdd(a.sig + 1, 1u);
+    if (tid == 0 && a.sig_hi) { if (a.p2p) atomicAdd_system(a.sig_hi, 1u); else atomicAdd(a.sig_hi, 1u); }
   }
   grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
 }

@@ -101,14 +101,25 @@ void launch_pcr_lines_maf(const Launch& L, const Geo& G, int pn, int mode, int d
 bool fused_eligible(const Geo& G);
 // both colours of one red-black SOR iteration, p -> pnew (ping-pong). Reds are relaxed on planes
 // jr0..jr1 (includes halo planes owned by a neighbour rank), blacks/stores on jst..jed.
+// Edge-plane signalling of a j-slab sweep (part 0, packed float kernel only).  The launch adds *sig_ctas to each
+// counter: *sig_lo as soon as the first two owned planes are stored everywhere, *sig_hi when the last chunk
+// (scheduled first) is complete.  NCCL transport (p2p = 0): local counters, a communication stream waits on them
+// and sends the planes.  Peer transport (p2p = 1, comm.h): the counters are the NEIGHBOURS' mailbox words, the
+// edge planes are also stored into the neighbours' halo inboxes (slot out_slot), and the planes beyond the slab
+// are read from our own inbox (slot in_slot) instead of the field's guard planes.
+struct Rb2Sig {
+  unsigned int* sig_lo; unsigned int* sig_hi;   // null = no neighbour on that side (p2p)
+  int p2p;
+  const REAL* inbox; int in_slot; bool has_lo, has_hi;
+  REAL* peer_lo; REAL* peer_hi; int out_slot;
+};
 bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
                       REAL omg, int ip, int jr0, int jr1, int slot, bool add, bool zero_src = false, int part = 0,
-                      unsigned int* sig = nullptr, int* sig_ctas = nullptr);
-// sig (part 0, packed float kernel only): two device counters; the launch adds *sig_ctas to each, sig[0] as soon as
-// the first two owned planes are stored everywhere, sig[1] when the last chunk (scheduled first) is complete.
+                      const Rb2Sig* sig = nullptr, int* sig_ctas = nullptr);
 // zero_src: p is known to be all zero and is not read at all (packed float kernel only; check first)
 bool rb2_zero_src_supported(const Geo& G, const REAL* cf);
-bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part, bool with_sig);
+bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part, bool with_sig,
+                          bool p2p = false);
 // part = 1: only the two planes at each end of the owned j range (what a slab sends to its neighbours),
 // part = 2: only the planes between; 1 then 2 equals one part = 0 sweep (packed float kernel only; check first)
 bool rb2_parts_supported(const Geo& G, const REAL* cf);

@@ -57,6 +57,14 @@ __global__ void k_bicg_scalar(LoopState* st, int phase, double res_normal, doubl
   }
 }
 
+// peer transport: tell the ring neighbours that our halo inbox is prepared (stream-ordered after the copies that
+// fill it); a system-scope atomic into their mailbox words, which their streams wait on.
+__global__ void k_post_ready(unsigned int* lo, unsigned int* hi) {
+  __threadfence_system();
+  if (lo) atomicAdd_system(lo, 1u);
+  if (hi) atomicAdd_system(hi, 1u);
+}
+
 int getNumStage(int n) {   // cz.h:293-300
   int b = 1;
   for (int i = 1; i < 20; i++) { b *= 2; if (n < b) return i; }
@@ -219,6 +227,10 @@ int czb_ctx::run_checked(int itr_max, double& res, Body body) {
     for (int q = 0; q < m; ++q) body(launched + q + 1);
     launched += m;
     const int slot = nb & 1;
+    // Convergence tests that run on the communication stream must be part of the snapshot: every rank has to see
+    // the SAME state after the same batch, or the ranks would enqueue different numbers of iterations (and of
+    // halo exchanges / signals) and hang.
+    join_comm_stream();
     CZB_CHECK(cudaMemcpyAsync(&h_state[1 + slot], d_state, sizeof(LoopState), cudaMemcpyDeviceToHost, R.stream));
     CZB_CHECK(cudaEventRecord(ev[slot], R.stream));
     if (nb >= 1) {   // look at the batch before this one while this one runs
@@ -345,6 +357,60 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     const bool ovl = sig_ok || parts_ok;
     if (ovl) ensure_comm_stream();
     const bool use_sig = sig_ok;
+    // Peer transport (comm.h): decided once per communicator, collectively (every rank or none).
+    bool p2p = false;
+    if (comm && comm->nranks > 1 && !no_ovl) {
+      const bool want = ovl_ok && !no_sig && rb2_fused_launchable(launch(), G, cf, false, 0, true, true) &&
+                        (!rb2_zero_src_supported(G, cf) || rb2_fused_launchable(launch(), G, cf, true, 0, true, true));
+      p2p = comm_p2p_setup(comm, (size_t)G.plane, R.stream, want) && want;
+    }
+    const size_t pl2 = 2 * (size_t)G.plane;          // two planes
+    REAL* const glo = X;                                                   // X's guard planes -1, 0
+    REAL* const ghi = X + (long long)(G.jx + G.g) * G.plane;               // X's guard planes jx+1, jx+2
+    if (p2p) {
+      // Prepare the inbox: both slots start as X's own guard planes (exchanged above / all zero in the
+      // preconditioner), so the cells the neighbours' sweeps never store (boundary rows) hold the right values and
+      // iteration 1 finds its halos in slot 0.  Then tell the neighbours they may write, and wait for their word.
+      for (int sl = 0; sl < 2; ++sl) {
+        if (comm->lo >= 0) CZB_CHECK(cudaMemcpyAsync(comm->inbox + (size_t)(sl * 4 + 0) * G.plane, glo, sizeof(REAL) * pl2, cudaMemcpyDeviceToDevice, R.stream));
+        if (comm->hi >= 0) CZB_CHECK(cudaMemcpyAsync(comm->inbox + (size_t)(sl * 4 + 2) * G.plane, ghi, sizeof(REAL) * pl2, cudaMemcpyDeviceToDevice, R.stream));
+      }
+      k_post_ready<<<1, 1, 0, R.stream>>>(comm->peer_ready[0], comm->peer_ready[1]);
+      count_launch();
+      comm->tgt_ready += 1u;
+      if (comm->lo >= 0) stream_wait_geq(R.stream, comm->mbox + 2, comm->tgt_ready);
+      if (comm->hi >= 0) stream_wait_geq(R.stream, comm->mbox + 3, comm->tgt_ready);
+    }
+    auto wait_edges = [&]() {   // the neighbours' edge planes of every sweep enqueued so far have landed in our inbox
+      if (comm->lo >= 0) stream_wait_geq(R.stream, comm->mbox + 0, comm->tgt[0]);
+      if (comm->hi >= 0) stream_wait_geq(R.stream, comm->mbox + 1, comm->tgt[1]);
+    };
+    auto body_p2p = [&](int it) {
+      REAL* src = (it & 1) ? X : W;
+      REAL* dst = (it & 1) ? W : X;
+      Launch L = launch();
+      const int slot = converge_check ? ((it & 1) ? 0 : 6) : rs;
+      const bool zs = !converge_check && it == 1 && pre_zero_src;
+      if (it >= 2) wait_edges();
+      if (converge_check && it >= 3) CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_fin[(it - 2) & 1], 0));
+      Rb2Sig sg;
+      sg.sig_lo = comm->peer_mbox[0]; sg.sig_hi = comm->peer_mbox[1]; sg.p2p = 1;
+      sg.inbox = comm->inbox; sg.in_slot = (it - 1) & 1; sg.has_lo = comm->lo >= 0; sg.has_hi = comm->hi >= 0;
+      sg.peer_lo = comm->peer_inbox[0]; sg.peer_hi = comm->peer_inbox[1]; sg.out_slot = it & 1;
+      int ctas = 0;
+      must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 0, &sg, &ctas));
+      comm->tgt[0] += (unsigned int)ctas; comm->tgt[1] += (unsigned int)ctas;   // every rank launches the same tile grid
+      if (converge_check) {
+        CZB_CHECK(cudaEventRecord(ev_int, R.stream));
+        CZB_CHECK(cudaStreamWaitEvent(cs, ev_int, 0));
+        comm_allreduce_sum(comm, &d_state->acc[slot], 1, cs);
+        Launch Lc = L; Lc.s = cs;
+        launch_finish_iteration(Lc, d_state, slot, res_normal, eps, d_hist, hist_cap);
+        CZB_CHECK(cudaEventRecord(ev_fin[it & 1], cs));
+        if (it <= 2) launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+        cs_used = true;
+      }
+    };
     auto body_ovl = [&](int it) {
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
@@ -356,7 +422,9 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (use_sig) {
         // one launch; the communication stream is released by the kernel's edge counters
         int ctas = 0;
-        must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 0, d_sig, &ctas));
+        Rb2Sig sg{};
+        sg.sig_lo = d_sig; sg.sig_hi = d_sig + 1;
+        must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 0, &sg, &ctas));
         sig_target += (unsigned int)ctas;
         stream_wait_geq(cs, d_sig, sig_target);
         stream_wait_geq(cs, d_sig + 1, sig_target);
@@ -385,6 +453,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       cs_used = true;
     };
     auto body = [&](int it) {
+      if (p2p) { body_p2p(it); return; }
       if (ovl) { body_ovl(it); return; }
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
@@ -406,6 +475,16 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     if (done_iters & 1) {
       launch_copy_inner(launch(false), G, X, W);
       if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
+    }
+    if (p2p) {
+      // Quiesce the ring: the neighbours' last edge planes have arrived (and, by the same signal, they have read
+      // everything we sent), then give X the halo of its final state, as a Comm_S(X, 2) would have.
+      wait_edges();
+      if (done_iters >= 1) {
+        const int sl = done_iters & 1;
+        if (comm->lo >= 0) CZB_CHECK(cudaMemcpyAsync(glo, comm->inbox + (size_t)(sl * 4 + 0) * G.plane, sizeof(REAL) * pl2, cudaMemcpyDeviceToDevice, R.stream));
+        if (comm->hi >= 0) CZB_CHECK(cudaMemcpyAsync(ghi, comm->inbox + (size_t)(sl * 4 + 2) * G.plane, sizeof(REAL) * pl2, cudaMemcpyDeviceToDevice, R.stream));
+      }
     }
   } else {
     auto body = [&](int it) {

@@ -22,11 +22,16 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     n = int(os.environ.get("CZB_MGPU_N", "64"))
     n2 = int(os.environ.get("CZB_MGPU_N2", "200"))   # long lines: tensor-memory line-SOR kernels on slabs
-    cases = [(n, "sor2sma", None, 1.5, 60, 0), (n, "sor2sma", None, 1.5, 60, 1), (n, "jacobi", None, 0.8, 40, 0),
-             (n, "pcr_rb", None, 1.5, 30, 0), (n, "pbicgstab", "sor2sma", 1.1, 30, 0),
-             (n2, "pcr_rb", None, 1.5, 8, 0), (n2, "pcr_rb_esa", None, 1.5, 8, 0), (n2, "sor2sma", None, 1.5, 12, 0)]
+    # last field: start from the global-index hash field (cubez_b200/synth.py) instead of P = 0 -> the halos matter
+    # from the first sweep on; eps = 0 there, so every iteration runs
+    cases = [(n, "sor2sma", None, 1.5, 60, 0, 0), (n, "sor2sma", None, 1.5, 60, 1, 0), (n, "jacobi", None, 0.8, 40, 0, 0),
+             (n, "pcr_rb", None, 1.5, 30, 0, 0), (n, "pbicgstab", "sor2sma", 1.1, 30, 0, 0),
+             (n2, "pcr_rb", None, 1.5, 8, 0, 0), (n2, "pcr_rb_esa", None, 1.5, 8, 0, 0), (n2, "sor2sma", None, 1.5, 12, 0, 0),
+             (n, "sor2sma", None, 1.5, 37, 0, 1), (n2, "sor2sma", None, 1.8, 21, 0, 1), (n2, "jacobi", None, 0.8, 9, 0, 1),
+             (n2, "pcr_rb", None, 1.5, 5, 0, 1), (n, "sor2sma", None, 1.5, 400, 0, 2)]
     ok = True
-    for n, solver, pc, omega, iters, variant in cases:
+    from cubez_b200 import synth
+    for n, solver, pc, omega, iters, variant, start in cases:
         cz = cubez_b200.CZ([n, n, n], "f32", device=lr, nranks=world, rank=rank, eps=1e-5 if solver == "pbicgstab" else 0.0)
         cz.variant(variant)
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -35,7 +40,14 @@ def main():
         dist.broadcast(idt, 0)
         cz.comm_init(idt.cpu().numpy().tobytes())
         P, RHS = cz.setup_laplace()
+        if start == 1:
+            synth.fill(P, cz.sz, head_j=cz.head[1], gny=n)
+            cz.bc_k(P)
+        if start == 2:          # converges inside the run: the ranks must agree on the iteration it stops at
+            cz.dll.czb_ctx_set_eps(cz.ctx, 1.0e-5)
         out = cz.solve(solver, P, RHS, iters, omega, pc)
+        if start == 1:          # a second solve on the same context continues from the first (inbox / counters reused)
+            cz.solve(solver, P, RHS, 3, omega, pc)
         own = P[cz.idx[2] + 1:cz.idx[3] + 2].contiguous()          # owned inner planes (local C indices)
         sizes = [None] * world
         dist.all_gather_object(sizes, own.shape[0])
@@ -48,7 +60,14 @@ def main():
             c1 = cubez_b200.CZ([n, n, n], "f32", device=lr, eps=1e-5 if solver == "pbicgstab" else 0.0)
             c1.variant(variant)
             P1, R1 = c1.setup_laplace()
+            if start == 1:
+                synth.fill(P1, c1.sz)
+                c1.bc_k(P1)
+            if start == 2:
+                c1.dll.czb_ctx_set_eps(c1.ctx, 1.0e-5)
             o1 = c1.solve(solver, P1, R1, iters, omega, pc)
+            if start == 1:
+                c1.solve(solver, P1, R1, 3, omega, pc)
             ref = P1[3:-3].cpu().numpy()
             same_itr = o1["itr"] == out["itr"]
             m = min(len(o1["history"]), len(out["history"]))
@@ -57,8 +76,8 @@ def main():
                 good = good and np.allclose(out["history"][:m - 1], o1["history"][:m - 1], rtol=1e-3)
             else:
                 good = same_itr and np.array_equal(full, ref) and np.allclose(out["history"][:m], o1["history"][:m], rtol=1e-12)
-            print("mgpu n=%d %-10s pc=%-8s variant=%d ranks=%d itr %d/%d maxdiff %.3e %s" % (
-                n, solver, pc, variant, world, out["itr"], o1["itr"], float(np.abs(full - ref).max()),
+            print("mgpu n=%d %-10s pc=%-8s variant=%d start=%d ranks=%d itr %d/%d maxdiff %.3e %s" % (
+                n, solver, pc, variant, start, world, out["itr"], o1["itr"], float(np.abs(full - ref).max()),
                 "OK" if good else "FAIL"), flush=True)
             ok = ok and good
             c1.close()
