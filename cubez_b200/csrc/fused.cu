@@ -88,6 +88,7 @@ struct MarchArgs {
   const LoopState* st;
   LoopState* acc_st; int slot; int add;
   RedBuf rb;
+  FinishSpec fin;         // convergence test folded into the reduction epilogue (single rank)
   int slot2;              // packed MODE_AX: second accumulator (ap, ap), -1 = none
   int zsrc;               // packed MODE_RB2: the source field is all zero and is not read
   int edges;              // packed MODE_RB2: relax only the first and last jl planes of jb0..jb1 (grid.y = 2)
@@ -102,8 +103,21 @@ struct MarchArgs {
 
 struct FinStoreF {
   LoopState* st; int slot; int add;
+  FinishSpec fin;
   __device__ void operator()(double (&tot)[1]) const {
-    if (st) st->acc[slot] = (add ? st->acc[slot] : 0.0) + tot[0];
+    if (!st) return;
+    const double sum = (add ? st->acc[slot] : 0.0) + tot[0];
+    st->acc[slot] = sum;
+    if (fin.enable) {             // = k_finish_iteration (kernels.cu), cz_Poisson.cpp:69-77
+      double res = sum;
+      res *= fin.res_normal;
+      res = sqrt(res);
+      st->res = res;
+      const int it = st->itr;
+      if (fin.hist && it < fin.hist_len) fin.hist[it] = res;
+      st->itr = it + 1;
+      if (res < fin.eps) st->done = 1;
+    }
   }
 };
 
@@ -529,7 +543,7 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
     if (u + 3 >= nsteps) break;
     step(u + 3, c2, cm1, c0, c1, bcur, bprev);
   }
-  grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
+  grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add, a.fin});
 }
 
 #ifndef _REAL_IS_DOUBLE_
@@ -726,6 +740,7 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
   a.out = out; a.w = (mode == MODE_AX) ? b_or_w : nullptr;
   a.st = L.st; a.acc_st = L.acc_st; a.slot = slot; a.add = add ? 1 : 0;
   a.rb = L.rb;
+  a.fin = L.fin;
   a.slot2 = lin ? slot2 : -1;
   const bool with_sig = sig && packed && !lin && part == 0;
   if (sig && !with_sig) return 0;

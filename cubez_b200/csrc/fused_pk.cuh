@@ -469,7 +469,7 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
     __syncthreads();
     if (tid == 0 && a.sig_hi) { if (a.p2p) atomicAdd_system(a.sig_hi, 1u); else atomicAdd(a.sig_hi, 1u); }
   }
-  grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
+  grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add, a.fin});
 }
 
 // ================================================================================================
@@ -721,7 +721,7 @@ k_lin_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   }
   if (MODE == MODE_JAC) {
     double a1[1] = {acc[0]};
-    grid_reduce<1>(a1, a.rb, FinStoreF{a.acc_st, a.slot, a.add});
+    grid_reduce<1>(a1, a.rb, FinStoreF{a.acc_st, a.slot, a.add, a.fin});
   } else {
     grid_reduce<2>(acc, a.rb, FinStore2F{a.acc_st, a.slot, a.slot2});
   }

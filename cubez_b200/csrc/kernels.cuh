@@ -6,12 +6,18 @@
 
 namespace czb {
 
+// Convergence test folded into the sweep (single rank): the CTA that finishes the grid-wide reduction also does
+// what k_finish_iteration does -- res = sqrt(sum * res_normal), history, ++itr, done = res < eps
+// (cz_Poisson.cpp:69-77) -- which saves one launch per iteration.  Honoured by the fused marching kernels only.
+struct FinishSpec { int enable; double res_normal, eps; double* hist; int hist_len; };
+
 struct Launch {           // what every launcher needs
   cudaStream_t s;
   RedBuf rb;              // reduction scratch (sized for rb_blocks blocks)
   size_t rb_blocks;
   const LoopState* st;    // done-flag source (may be null)
   LoopState* acc_st;      // where reduction totals go: acc_st->acc[slot]
+  FinishSpec fin{0, 0.0, 0.0, nullptr, 0};
 };
 
 void count_launch(int n = 1);

@@ -194,6 +194,13 @@ __global__ void __launch_bounds__(256) k_pcr_lines(Geo G, int n, int pn, int sta
 // the fields are done in the "cyclic" layout k = lane + 32*m (coalesced 128 B per instruction); the two
 // layouts are exchanged through a small per-warp shared buffer.  Arithmetic and its order are those of
 // k_pcr_lines (= cz_solver.f90:569-648), so results are bit-identical.
+// four consecutive REALs of a lane: one 128-bit (float) or two 128-bit (double) shared-memory accesses
+#ifdef _REAL_IS_DOUBLE_
+struct alignas(16) R4 { double x, y, z, w; };
+#else
+typedef float4 R4;
+#endif
+
 template <int EPL>
 struct PcrLay {
   static constexpr int NQ = EPL / 4;            // 16-byte chunks per lane
@@ -206,7 +213,7 @@ struct PcrLay {
 };
 
 template <int EPL>
-__global__ void __launch_bounds__(EPL == 32 ? 512 : 256, EPL == 32 ? 1 : 2) k_pcr_warp(Geo G, int n, int pn, int stages, const REAL* __restrict__ tab,
+__global__ void __launch_bounds__(EPL == 32 ? 512 : 256, (EPL == 32 || sizeof(REAL) == 8) ? 1 : 2) k_pcr_warp(Geo G, int n, int pn, int stages, const REAL* __restrict__ tab,
                                                   const REAL* __restrict__ fin, LineSel sel, const REAL* x, REAL* dst,
                                                   const REAL* __restrict__ msk, const REAL* __restrict__ rhs, REAL omg,
                                                   const LoopState* st, RedBuf rb, FinStoreP finst) {
@@ -280,7 +287,7 @@ __global__ void __launch_bounds__(EPL == 32 ? 512 : 256, EPL == 32 ? 1 : 2) k_pc
     REAL d[EPL];
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
-      const float4 v = *reinterpret_cast<const float4*>(wb + q * LY::QSTR + lane * 4);
+      const R4 v = *reinterpret_cast<const R4*>(wb + q * LY::QSTR + lane * 4);
       d[4 * q] = v.x; d[4 * q + 1] = v.y; d[4 * q + 2] = v.z; d[4 * q + 3] = v.w;
     }
     // ---- PCR stages: d1(k) = e*(d(k) - ap*d(k-s) - cp*d(k+s))  (cz_solver.f90:602) ----
@@ -293,9 +300,9 @@ __global__ void __launch_bounds__(EPL == 32 ? 512 : 256, EPL == 32 ? 1 : 2) k_pc
         REAL dn[EPL];
 #pragma unroll
         for (int q = 0; q < NQ; ++q) {
-          const float4 ap4 = *reinterpret_cast<const float4*>(tp + q * LY::QSTR);
-          const float4 cp4 = *reinterpret_cast<const float4*>(tp + ROW + q * LY::QSTR);
-          const float4 e4 = *reinterpret_cast<const float4*>(tp + 2 * ROW + q * LY::QSTR);
+          const R4 ap4 = *reinterpret_cast<const R4*>(tp + q * LY::QSTR);
+          const R4 cp4 = *reinterpret_cast<const R4*>(tp + ROW + q * LY::QSTR);
+          const R4 e4 = *reinterpret_cast<const R4*>(tp + 2 * ROW + q * LY::QSTR);
           const REAL apv[4] = {ap4.x, ap4.y, ap4.z, ap4.w}, cpv[4] = {cp4.x, cp4.y, cp4.z, cp4.w};
           const REAL ev[4] = {e4.x, e4.y, e4.z, e4.w};
 #pragma unroll
@@ -324,9 +331,9 @@ __global__ void __launch_bounds__(EPL == 32 ? 512 : 256, EPL == 32 ? 1 : 2) k_pc
     __syncwarp();
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
-      const float4 f1 = *reinterpret_cast<const float4*>(F1 + q * LY::QSTR + lane * 4);
-      const float4 f2 = *reinterpret_cast<const float4*>(F2 + q * LY::QSTR + lane * 4);
-      float4 o;
+      const R4 f1 = *reinterpret_cast<const R4*>(F1 + q * LY::QSTR + lane * 4);
+      const R4 f2 = *reinterpret_cast<const R4*>(F2 + q * LY::QSTR + lane * 4);
+      R4 o;
       REAL pr[4];
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
@@ -337,7 +344,7 @@ __global__ void __launch_bounds__(EPL == 32 ? 512 : 256, EPL == 32 ? 1 : 2) k_pc
       o.y = (d[4 * q + 1] - f1.y * pr[1]) * f2.y;
       o.z = (d[4 * q + 2] - f1.z * pr[2]) * f2.z;
       o.w = (d[4 * q + 3] - f1.w * pr[3]) * f2.w;
-      *reinterpret_cast<float4*>(wb + q * LY::QSTR + lane * 4) = o;
+      *reinterpret_cast<R4*>(wb + q * LY::QSTR + lane * 4) = o;
     }
     __syncwarp();
     // ---- relaxation in the cyclic layout (cz_solver.f90:642-648) ----
@@ -1082,6 +1089,31 @@ void launch_pcr_lines(const Launch& L, const Geo& G, const PcrTables& T, int mod
     else if (n <= 256) go(std::integral_constant<int, 8>{});
     else if (n <= 512) go(std::integral_constant<int, 16>{});
     else               go(std::integral_constant<int, 32>{});
+    CZB_CHECK(cudaGetLastError());
+    count_launch();
+    return;
+  }
+#else
+  // double precision: the warp-per-line kernel with the tables in shared memory (2x2 last stage, 17..512 cells;
+  // 1024-cell lines would need 390 KB of tables + exchange buffers)
+  static const bool no_warp = getenv("CZB_PCR_BLOCK") != nullptr;
+  if (!T.last4 && !no_warp && n >= 17 && n <= 512) {
+    auto go = [&](auto epl) {
+      constexpr int EPL = decltype(epl)::value;
+      typedef PcrLay<EPL> LY;
+      const int wpb = 8;
+      const size_t sm = sizeof(REAL) * ((size_t)T.stages * 3 * LY::ROW + 2 * LY::ROW + (size_t)wpb * LY::ROW);
+      int g = (sel.nlines + wpb - 1) / wpb;
+      const int cap = 148 * (int)(sm > 110 * 1024 ? 1 : 2);
+      if (g > cap) g = cap;
+      if ((size_t)g > L.rb_blocks) g = (int)L.rb_blocks;
+      static size_t sm_set = 0;
+      if (sm > sm_set) { CZB_CHECK(cudaFuncSetAttribute(k_pcr_warp<EPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); sm_set = sm; }
+      k_pcr_warp<EPL><<<g, wpb * 32, sm, L.s>>>(G, n, T.pn, T.stages, T.tab, T.fin, sel, x, dst, mask_is_inner ? nullptr : msk, rhs, omg, L.st, L.rb, fs);
+    };
+    if (n <= 128)      go(std::integral_constant<int, 4>{});
+    else if (n <= 256) go(std::integral_constant<int, 8>{});
+    else               go(std::integral_constant<int, 16>{});
     CZB_CHECK(cudaGetLastError());
     count_launch();
     return;

@@ -222,9 +222,36 @@ int czb_ctx::run_checked(int itr_max, double& res, Body body) {
   const int batch = 16;
   int launched = 0, nb = 0;
   bool stop = false;
+  // Single rank: the second batch (iterations 17..32; the first one carries the bc_k launches of iterations 1, 2) is
+  // captured into a CUDA graph and REPLAYED for every later full batch.  body(it) depends on `it` only through its
+  // parity (ping-pong roles) once it > 2 and every batch starts at an odd iteration, so the captured launches are
+  // exactly those a direct enqueue would make; the kernels read their iteration state (done, itr) on the device.
+  static const bool no_graph = getenv("CZB_NO_GRAPH") != nullptr;
+  bool graphs = !no_graph && !(comm && comm->nranks > 1) && itr_max >= 3 * batch;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t gexec = nullptr;
+  long long graph_launches = 0;
   while (launched < itr_max && !stop) {
     const int m = (itr_max - launched < batch) ? itr_max - launched : batch;
-    for (int q = 0; q < m; ++q) body(launched + q + 1);
+    if (graphs && m == batch && nb >= 1 && !gexec &&
+        cudaStreamBeginCapture(R.stream, cudaStreamCaptureModeRelaxed) != cudaSuccess) {
+      cudaGetLastError();
+      graphs = false;            // stream capture unavailable (e.g. the stream is already being captured by the caller)
+    }
+    if (graphs && m == batch && nb >= 1) {
+      if (!gexec) {
+        const long long l0 = launch_count();
+        for (int q = 0; q < m; ++q) body(launched + q + 1);
+        CZB_CHECK(cudaStreamEndCapture(R.stream, &graph));
+        graph_launches = launch_count() - l0;
+        CZB_CHECK(cudaGraphInstantiate(&gexec, graph, 0));
+      } else {
+        count_launch((int)graph_launches);
+      }
+      CZB_CHECK(cudaGraphLaunch(gexec, R.stream));
+    } else {
+      for (int q = 0; q < m; ++q) body(launched + q + 1);
+    }
     launched += m;
     const int slot = nb & 1;
     // Convergence tests that run on the communication stream must be part of the snapshot: every rank has to see
@@ -240,7 +267,10 @@ int czb_ctx::run_checked(int itr_max, double& res, Body body) {
     }
     ++nb;
   }
-  return end_loop(itr_max, res, false);
+  const int itr = end_loop(itr_max, res, false);
+  if (gexec) cudaGraphExecDestroy(gexec);
+  if (graph) cudaGraphDestroy(graph);
+  return itr;
 }
 
 // ============================================================================ loops
@@ -261,13 +291,18 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     REAL* src = (it & 1) ? X : W;
     REAL* dst = (it & 1) ? W : X;
     Launch L = launch();
+    // single rank: the convergence test rides in the sweep's reduction epilogue (FinishSpec), no extra launch
+    const bool fold = converge_check && !(comm && comm->nranks > 1);
+    Launch Lf = L;
+    if (fold) Lf.fin = FinishSpec{1, res_normal, eps, d_hist, hist_cap};
+    bool folded = false;
     if (maf) launch_jacobi_maf(L, G, src, dst, B, axes(), ac1, rs, false);   // cz_Poisson.cpp:45-52
-    else if (!(variant == 0 && launch_jacobi_fused(L, G, src, dst, B, cf, ac1, rs, false)))
-      launch_jacobi(L, G, src, dst, B, cf, ac1, rs, false);
+    else if (variant == 0 && launch_jacobi_fused(Lf, G, src, dst, B, cf, ac1, rs, false)) folded = fold;
+    else launch_jacobi(L, G, src, dst, B, cf, ac1, rs, false);
     Comm_S(dst, 1);
     if (converge_check) {
       Comm_SUM(0);
-      launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+      if (!folded) launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
       // bc_k (cz_Poisson.cpp:73) is idempotent once both ping-pong buffers hold the Dirichlet values (see RBSOR).
       // It is launched WITHOUT the done gate (here and in every loop below): the reference calls it before
       // `if (res < eps) break` (cz_Poisson.cpp:73-77, 495-497), i.e. also on the converging iteration.
@@ -285,6 +320,7 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
   if (done_iters & 1) {
     launch_copy_inner(launch(false), G, X, W);
     if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // X missed the bc_k of an odd last iteration
+    Comm_S(X, 1);   // the last exchange filled WRK's guard planes; X leaves with the halo of its final state (cz_Poisson.cpp:63)
   }
   flop += (maf ? 66.0 : 18.0) * G.cells() * done_iters;
   return itr;
@@ -357,6 +393,10 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     const bool ovl = sig_ok || parts_ok;
     if (ovl) ensure_comm_stream();
     const bool use_sig = sig_ok;
+    // Timing experiments only (results are WRONG with them): CZB_EXP_NOCOMM skips the halo traffic / waits and the
+    // residual all-reduce of the overlapped loops; CZB_EXP_NOALLREDUCE only the all-reduce.
+    static const bool exp_nocomm = getenv("CZB_EXP_NOCOMM") != nullptr;
+    static const bool exp_noar = exp_nocomm || getenv("CZB_EXP_NOALLREDUCE") != nullptr;
     // Peer transport (comm.h): decided once per communicator, collectively (every rank or none).
     bool p2p = false;
     if (comm && comm->nranks > 1 && !no_ovl) {
@@ -382,6 +422,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (comm->hi >= 0) stream_wait_geq(R.stream, comm->mbox + 3, comm->tgt_ready);
     }
     auto wait_edges = [&]() {   // the neighbours' edge planes of every sweep enqueued so far have landed in our inbox
+      if (exp_nocomm) return;
       if (comm->lo >= 0) stream_wait_geq(R.stream, comm->mbox + 0, comm->tgt[0]);
       if (comm->hi >= 0) stream_wait_geq(R.stream, comm->mbox + 1, comm->tgt[1]);
     };
@@ -397,13 +438,15 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       sg.sig_lo = comm->peer_mbox[0]; sg.sig_hi = comm->peer_mbox[1]; sg.p2p = 1;
       sg.inbox = comm->inbox; sg.in_slot = (it - 1) & 1; sg.has_lo = comm->lo >= 0; sg.has_hi = comm->hi >= 0;
       sg.peer_lo = comm->peer_inbox[0]; sg.peer_hi = comm->peer_inbox[1]; sg.out_slot = it & 1;
+      static const bool exp_nopeer = getenv("CZB_EXP_NOPEERSTORE") != nullptr;   // timing experiment, results wrong
+      if (exp_nopeer) sg.peer_lo = sg.peer_hi = nullptr;
       int ctas = 0;
       must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 0, &sg, &ctas));
       comm->tgt[0] += (unsigned int)ctas; comm->tgt[1] += (unsigned int)ctas;   // every rank launches the same tile grid
       if (converge_check) {
         CZB_CHECK(cudaEventRecord(ev_int, R.stream));
         CZB_CHECK(cudaStreamWaitEvent(cs, ev_int, 0));
-        comm_allreduce_sum(comm, &d_state->acc[slot], 1, cs);
+        if (!exp_noar) comm_allreduce_sum(comm, &d_state->acc[slot], 1, cs);
         Launch Lc = L; Lc.s = cs;
         launch_finish_iteration(Lc, d_state, slot, res_normal, eps, d_hist, hist_cap);
         CZB_CHECK(cudaEventRecord(ev_fin[it & 1], cs));
@@ -428,7 +471,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
         sig_target += (unsigned int)ctas;
         stream_wait_geq(cs, d_sig, sig_target);
         stream_wait_geq(cs, d_sig + 1, sig_target);
-        comm_halo(comm, dst, G, 2, cs);
+        if (!exp_nocomm) comm_halo(comm, dst, G, 2, cs);
         CZB_CHECK(cudaEventRecord(ev_halo[it & 1], cs));
       } else {
         must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 1));
@@ -441,7 +484,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (converge_check) {
         CZB_CHECK(cudaEventRecord(ev_int, R.stream));
         CZB_CHECK(cudaStreamWaitEvent(cs, ev_int, 0));
-        comm_allreduce_sum(comm, &d_state->acc[slot], 1, cs);
+        if (!exp_noar) comm_allreduce_sum(comm, &d_state->acc[slot], 1, cs);
         Launch Lc = L; Lc.s = cs;
         launch_finish_iteration(Lc, d_state, slot, res_normal, eps, d_hist, hist_cap);
         CZB_CHECK(cudaEventRecord(ev_fin[it & 1], cs));
@@ -458,12 +501,18 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
       Launch L = launch();
+      const bool fold = converge_check && !(comm && comm->nranks > 1);   // convergence test inside the sweep (FinishSpec)
+      if (fold) L.fin = FinishSpec{1, res_normal, eps, d_hist, hist_cap};
+      static const bool force_sig = getenv("CZB_EXP_FORCE_SIG") != nullptr;   // timing experiment: the slab instantiation on one rank
+      Rb2Sig sg{};
+      if (force_sig) { ensure_comm_stream(); sg.sig_lo = d_sig; sg.sig_hi = d_sig + 1; }
       // first preconditioner sweep: xx is all zero by contract (cz_Poisson.cpp:405,441) and is not read
-      must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, rs, false, !converge_check && it == 1 && pre_zero_src));
+      must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, rs, false, !converge_check && it == 1 && pre_zero_src, 0,
+                            force_sig ? &sg : nullptr));
       Comm_S(dst, 2);
       if (converge_check) {
         Comm_SUM(0);
-        launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+        if (!fold) launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
         // bc_k (cz_Poisson.cpp:226) is idempotent: the sweep never changes a boundary node and carries
         // the boundary nodes it stores over from src, so once both ping-pong buffers have received the
         // Dirichlet values (iterations 1 and 2) every later call would rewrite identical data.
@@ -475,6 +524,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     if (done_iters & 1) {
       launch_copy_inner(launch(false), G, X, W);
       if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
+      if (!p2p) Comm_S(X, 2);   // the last exchange filled WRK's guard planes
     }
     if (p2p) {
       // Quiesce the ring: the neighbours' last edge planes have arrived (and, by the same signal, they have read
@@ -626,6 +676,7 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
     if (done_iters & 1) {
       launch_copy_inner(launch(false), G, X, W);
       launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
+      Comm_S(X, 1);   // the last exchange filled WRK's guard planes
     }
   } else {
     for (int it = 1; it <= itr_max; ++it) {

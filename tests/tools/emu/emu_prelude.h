@@ -33,10 +33,12 @@ using std::max;
 #define __shared__              // one thread per block: shared variables are plain locals
 #define __syncthreads() ((void)0)
 #define __threadfence() ((void)0)
+#define __threadfence_system() ((void)0)
 template <class T> static inline T __ldg(const T* p) { return *p; }
 template <class T> static inline T __ldcg(const T* p) { return *p; }
 static inline double __shfl_xor_sync(unsigned, double, int) { return 0.0; }   // the other 31 lanes do not exist
 static inline unsigned int atomicAdd(unsigned int* p, unsigned int v) { unsigned int o = *p; *p += v; return o; }
+static inline unsigned int atomicAdd_system(unsigned int* p, unsigned int v) { return atomicAdd(p, v); }
 static inline unsigned long long atomicCAS(unsigned long long* p, unsigned long long c, unsigned long long v) {
   unsigned long long o = *p; if (o == c) *p = v; return o;
 }
