@@ -3,6 +3,8 @@
 // Comm_SUM_1 (MPI_Allreduce, :74-140) -> ncclAllReduce of device-resident doubles.
 #include "comm.h"
 #include <nccl.h>
+#include <cuda.h>
+#include "kernels.cuh"
 #include <dlfcn.h>
 #include <cstring>
 
@@ -176,12 +178,58 @@ bool comm_p2p_setup(Comm* c, size_t plane_elems, cudaStream_t s, bool want) {
     if (!c->peer_block[side]) continue;
     // we are the UPPER neighbour of our lower neighbour: our signals count in its from_hi (word 1), and vice versa
     c->peer_mbox[side] = (unsigned int*)c->peer_block[side] + (side == 0 ? 1 : 0);
-    c->peer_ready[side] = (unsigned int*)c->peer_block[side] + (side == 0 ? 3 : 2);
     c->peer_inbox[side] = (REAL*)((char*)c->peer_block[side] + kP2pHeader);
   }
-  c->tgt[0] = c->tgt[1] = 0u; c->tgt_ready = 0u;
+  c->tgt[0] = c->tgt[1] = 0u;
   c->p2p = true;
   return true;
+}
+
+namespace {
+// one thread: make the preceding copies of this stream visible system-wide, then count the push in the neighbours' mailboxes
+__global__ void k_post(unsigned int* lo, unsigned int* hi) {
+  __threadfence_system();
+  if (lo) atomicAdd_system(lo, 1u);
+  if (hi) atomicAdd_system(hi, 1u);
+}
+}  // namespace
+
+void stream_wait_geq(cudaStream_t s, unsigned int* dev, unsigned int value) {
+  typedef CUresult (*Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+  static Fn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    CZB_CHECK(cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q));
+    if (!p || q != cudaDriverEntryPointSuccess) { fprintf(stderr, "czb200: cuStreamWaitValue32 unavailable\n"); abort(); }
+    fn = (Fn)p;
+  }
+  const CUresult r = fn((CUstream)s, (CUdeviceptr)(uintptr_t)dev, value, CU_STREAM_WAIT_VALUE_GEQ);
+  if (r != CUDA_SUCCESS) { fprintf(stderr, "czb200: cuStreamWaitValue32 failed (%d)\n", (int)r); abort(); }
+}
+
+void comm_p2p_push(Comm* c, const REAL* lo_planes, const REAL* hi_planes, int w, int slot, cudaStream_t s) {
+  const size_t P = c->plane_elems, bytes = sizeof(REAL) * P * (size_t)w;
+  // inbox plane index = slot*4 + side*2 + p ; we are the UPPER neighbour (side 1) of our lower neighbour and vice versa
+  if (c->lo >= 0) { CZB_CHECK(cudaMemcpyAsync(c->peer_inbox[0] + (size_t)(slot * 4 + 2) * P, lo_planes, bytes, cudaMemcpyDeviceToDevice, s)); c->tgt[0] += 1u; }
+  if (c->hi >= 0) { CZB_CHECK(cudaMemcpyAsync(c->peer_inbox[1] + (size_t)(slot * 4 + 0) * P, hi_planes, bytes, cudaMemcpyDeviceToDevice, s)); c->tgt[1] += 1u; }
+  k_post<<<1, 1, 0, s>>>(c->lo >= 0 ? c->peer_mbox[0] : nullptr, c->hi >= 0 ? c->peer_mbox[1] : nullptr);
+  CZB_CHECK(cudaGetLastError());
+  count_launch();
+}
+
+void comm_p2p_wait(Comm* c, cudaStream_t s) {
+  if (c->lo >= 0) stream_wait_geq(s, c->mbox + 0, c->tgt[0]);
+  if (c->hi >= 0) stream_wait_geq(s, c->mbox + 1, c->tgt[1]);
+}
+
+void comm_p2p_fetch(Comm* c, REAL* lo_guard, REAL* hi_guard, int w, int slot, cudaStream_t s) {
+  const size_t P = c->plane_elems, bytes = sizeof(REAL) * P * (size_t)w;
+  // the neighbour's planes are stored from plane 0 of its region: with w = 1 the plane next to us is plane 0 of
+  // side 1 (its first owned plane) but plane 0 of side 0 is its LAST owned plane only if it pushed w = 1 -- the
+  // sender always passes the w planes adjacent to the interface in ascending j order
+  if (c->lo >= 0) CZB_CHECK(cudaMemcpyAsync(lo_guard, c->inbox + (size_t)(slot * 4 + 0) * P, bytes, cudaMemcpyDeviceToDevice, s));
+  if (c->hi >= 0) CZB_CHECK(cudaMemcpyAsync(hi_guard, c->inbox + (size_t)(slot * 4 + 2) * P, bytes, cudaMemcpyDeviceToDevice, s));
 }
 
 void comm_halo(Comm* c, REAL* f, const Geo& G, int w, cudaStream_t s) {

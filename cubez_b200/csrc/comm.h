@@ -19,25 +19,23 @@ struct Comm {
   int nranks = 1, rank = 0;
   int lo = -1, hi = -1;     // neighbour ranks along j (-1: none)
   void* nccl = nullptr;     // ncclComm_t
-  // ---- peer transport (NVLink peer memory, no NCCL kernel in the halo path) ------------------------------
-  // Every rank owns one IPC-exported block:  mailbox {from_lo, from_hi, ready_lo, ready_hi} (32-bit counters the
-  // NEIGHBOURS increment with system-scope atomics: edge planes delivered / "my inbox is prepared, you may write")
-  // followed by the halo inbox  [2 slots][2 sides][2 planes]  of
-  // plane_elems REALs each (side 0 = planes owned by the lower neighbour, 1 = by the upper one).  A sweep of
-  // iteration `it` stores its edge planes into the neighbours' inbox slot it&1 and reads its own halos from
-  // slot (it-1)&1; the consumer's STREAM waits on the mailbox counters (cuStreamWaitValue32), no kernel spins.
+  // ---- peer transport (NVLink peer memory through the copy engines, no NCCL and no SM in the halo path) ----------
+  // Every rank owns one IPC-exported block:  mailbox {from_lo, from_hi} (32-bit counters the NEIGHBOURS increment
+  // with a system-scope atomic after each push) followed by the halo inbox  [2 slots][2 sides][2 planes]  of
+  // plane_elems REALs each (side 0 = planes owned by the lower neighbour, 1 = by the upper one).  Iteration `it`
+  // of a solve loop pushes the slab's edge planes into the neighbours' slot it&1 with cudaMemcpyAsync over the
+  // mapped pointers (DMA, overlaps the interior kernel), then posts; the consumer's STREAM waits on its mailbox
+  // (cuStreamWaitValue32 -- no kernel spins) and copies the planes from its inbox into its guard planes.
   bool p2p = false;
+  bool p2p_tried = false;
   size_t plane_elems = 0;
   void* block = nullptr;                    // local block (cudaMalloc)
   unsigned int* mbox = nullptr;             // local counters {from_lo, from_hi}
   REAL* inbox = nullptr;                    // local inbox, 8 planes
   void* peer_block[2] = {nullptr, nullptr};  // mapped blocks of the lower / upper neighbour
-  unsigned int* peer_mbox[2] = {nullptr, nullptr};   // the word of THEIR mailbox that counts OUR signals
+  unsigned int* peer_mbox[2] = {nullptr, nullptr};   // the word of THEIR mailbox that counts OUR pushes
   REAL* peer_inbox[2] = {nullptr, nullptr};
-  unsigned int* peer_ready[2] = {nullptr, nullptr};  // the word of THEIR mailbox that counts OUR "ready" posts
-  unsigned int tgt[2] = {0u, 0u};           // value from_lo / from_hi reach once every launch enqueued so far has signalled
-  unsigned int tgt_ready = 0u;              // loops started so far (each posts one "ready" to both neighbours)
-  bool p2p_tried = false;
+  unsigned int tgt[2] = {0u, 0u};           // value from_lo / from_hi reach once every push expected so far has landed
 };
 
 int comm_unique_id(void* id128);
@@ -50,6 +48,16 @@ void comm_halo(Comm* c, REAL* field, const Geo& G, int width, cudaStream_t s);
 // only if EVERY rank succeeded (otherwise all ranks keep the NCCL transport).  CZB_NO_P2P=1 disables it.
 bool comm_p2p_setup(Comm* c, size_t plane_elems, cudaStream_t s, bool want = true);
 // `want`: this rank can use the transport (kernel eligibility); the result is the AND over all ranks.
+// Push `w` (1 or 2) planes starting at lo_planes (-> lower neighbour) and hi_planes (-> upper neighbour) into the
+// neighbours' inbox slot, then post to their mailboxes; everything on stream s.  The neighbours run the same program,
+// so every push also raises the value comm_p2p_wait will wait for.
+void comm_p2p_push(Comm* c, const REAL* lo_planes, const REAL* hi_planes, int w, int slot, cudaStream_t s);
+// Stream s waits until every push expected so far has landed in our inbox.
+void comm_p2p_wait(Comm* c, cudaStream_t s);
+// Copy `w` planes per side from our inbox slot into the guard planes lo_guard / hi_guard (device pointers).
+void comm_p2p_fetch(Comm* c, REAL* lo_guard, REAL* hi_guard, int w, int slot, cudaStream_t s);
+// cuStreamWaitValue32(GEQ) through the runtime's driver entry point (no link dependency on libcuda)
+void stream_wait_geq(cudaStream_t s, unsigned int* dev, unsigned int value);
 // In-place sum over ranks of `count` doubles in device memory.
 void comm_allreduce_sum(Comm* c, double* dev, int count, cudaStream_t s);
 

@@ -33,7 +33,6 @@ namespace czb {
 namespace {
 
 enum { MODE_RB2 = 0, MODE_JAC = 1, MODE_AX = 2 };
-constexpr int RB2_EDGE = 2;     // planes a j-slab sends to each neighbour after a two-colour sweep
 
 constexpr int PR = 64;          // pairs per tile row  -> box width EKB = 128 cells
 constexpr int EKB = 2 * PR;
@@ -78,6 +77,7 @@ struct MarchArgs {
   Geo G;
   int ei;                 // tile rows (box height); owned rows = ei - 4
   int ntk, nti, njc;      // tiles along k, i and chunks along j
+  int ngy;                // chunks launched by this call (grid.y)
   int jl;                 // planes per j-chunk
   int jr0, jr1;           // planes on which reds are relaxed (Fortran j)
   int jb0, jb1;           // owned planes (blacks relaxed, results stored, residual counted)
@@ -91,14 +91,7 @@ struct MarchArgs {
   FinishSpec fin;         // convergence test folded into the reduction epilogue (single rank)
   int slot2;              // packed MODE_AX: second accumulator (ap, ap), -1 = none
   int zsrc;               // packed MODE_RB2: the source field is all zero and is not read
-  int edges;              // packed MODE_RB2: relax only the first and last jl planes of jb0..jb1 (grid.y = 2)
-  // packed MODE_RB2 on a j-slab (fused_pk.cuh, SIG instantiation): edge-plane completion counters, and -- peer
-  // transport -- the neighbours' halo inboxes (pre-biased so that the element offset inside OUR field applies) and
-  // the first plane index of our own inbox regions (tensor map tm_h), -1 = no neighbour on that side
-  unsigned int* sig_lo; unsigned int* sig_hi;
-  int p2p;
-  REAL* peer_lo; REAL* peer_hi;
-  int hin_lo, hin_hi;
+  int jc_first, jc_step;  // chunk of a CTA = jc_first + blockIdx.y * jc_step (all chunks: 0, 1; see `part` in march())
 };
 
 struct FinStoreF {
@@ -300,7 +293,7 @@ k_march(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtens
   const int tid = threadIdx.x;
 
   // ---- tile / chunk geometry ------------------------------------------------------------
-  const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk, jc = blockIdx.y;
+  const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk, jc = a.jc_first + (int)blockIdx.y * a.jc_step;
   const int kst_c = G.kst + G.g - 1, ist_c = G.ist + G.g - 1;     // C offsets of the first inner cell
   const int P0 = (kst_c >> 1) - 1 + tk * (PR - 2);                 // first (halo) pair of the box
   const int R0 = ist_c - 2 + ti * (EI - 4);                        // first (halo) row of the box
@@ -594,7 +587,7 @@ CUtensorMap tmap_for(const REAL* base, const Geo& G, int ei) {
 
 template <int MODE, int NT, int CPT>
 void launch_march_t(const Launch& L, const MarchArgs& a, const CUtensorMap& tp, const CUtensorMap& tb, bool fast, size_t smem) {
-  dim3 grid(a.ntk * a.nti, a.njc, 1);
+  dim3 grid(a.ntk * a.nti, a.ngy, 1);
   if (fast) {   // unit off-diagonals and dd == 6: the CubeZ operator (cz.h:169-172)
     static bool set = false;
     if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_march<MODE, NT, CPT, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
@@ -624,25 +617,18 @@ void launch_march_cfg(int cfg, const Launch& L, const MarchArgs& a, const CUtens
 
 #ifndef _REAL_IS_DOUBLE_
 template <int NT, int CPT, int NSP_, int NSB_>
-void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const REAL* b, const REAL* inbox, bool sig) {
+void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const REAL* b) {
   constexpr int EI = NT / 32 * CPT;
-  dim3 grid(a.ntk * a.nti, a.njc, 1);
+  dim3 grid(a.ntk * a.nti, a.ngy, 1);
   const size_t smem = (size_t)(NSP_ + NSB_ + NDE) * EI * EKB * sizeof(float) + 1024;
   static bool set = false;
   if (!set) {
-    CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT, NSP_, NSB_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT, NSP_, NSB_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CZB_CHECK(cudaFuncSetAttribute(k_rb2_pk<NT, CPT, NSP_, NSB_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     set = true;
   }
   const CUtensorMap tp = tmap_for(p, a.G, EI);
   const CUtensorMap tb = tmap_for(b, a.G, EI);
-  if (sig) {   // j-slab with edge-plane signals; halo inbox = a field of 8 planes (2 slots x 2 sides x 2 planes)
-    Geo H = a.G; H.nj = 8;
-    const CUtensorMap th = inbox ? tmap_for(inbox, H, EI) : tp;
-    k_rb2_pk<NT, CPT, NSP_, NSB_, true><<<grid, NT, smem, L.s>>>(tp, tb, th, a);
-  } else {
-    k_rb2_pk<NT, CPT, NSP_, NSB_, false><<<grid, NT, smem, L.s>>>(tp, tb, tp, a);
-  }
+  k_rb2_pk<NT, CPT, NSP_, NSB_><<<grid, NT, smem, L.s>>>(tp, tb, a);
   CZB_CHECK(cudaGetLastError());
   count_launch();
 }
@@ -652,7 +638,7 @@ void launch_rb2_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const R
 template <int MODE, int NT, int CPT, int NSP_, int NSB_>
 void launch_lin_pk_t(const Launch& L, const MarchArgs& a, const REAL* p, const REAL* b) {
   constexpr int EI = NT / 32 * CPT;
-  dim3 grid(a.ntk * a.nti, a.njc, 1);
+  dim3 grid(a.ntk * a.nti, a.ngy, 1);
   const size_t smem = (size_t)(NSP_ + (MODE == MODE_JAC ? NSB_ : 0) + 2) * EI * EKB * sizeof(float) + 1024;
   static bool set = false;
   if (!set) { CZB_CHECK(cudaFuncSetAttribute(k_lin_pk<MODE, NT, CPT, NSP_, NSB_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); set = true; }
@@ -684,7 +670,7 @@ int march_rows(int cfg) {
 // returns 0 = not eligible, 1 = done, 2 = done including the second accumulator slot2 (packed MODE_AX)
 int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_or_w, REAL* out, const REAL* cf,
           REAL omg, int ip, int jr0, int jr1, int slot, bool add, int slot2 = -1, bool zsrc = false, int part = 0,
-          const Rb2Sig* sig = nullptr, int* sig_ctas = nullptr, bool dry = false) {
+          bool dry = false) {
   if (!fused_eligible(G)) return 0;
   MarchArgs a;
   a.G = G;
@@ -708,10 +694,10 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
     const int npairs = (ked_c >> 1) - (kst_c >> 1) + 1;
     a.ntk = (npairs + PR - 3) / (PR - 2);
   }
-  // part (packed MODE_RB2 only): 0 = all owned planes, 1 = the RB2_EDGE first and last planes, 2 = the planes between
-  if (part != 0 && !(packed && !lin)) return 0;
-  const int jlo = (part == 2) ? G.jst + RB2_EDGE : G.jst, jhi = (part == 2) ? G.jed - RB2_EDGE : G.jed;
-  if (part != 0 && G.jed - G.jst + 1 < 2 * RB2_EDGE + 1) return 0;
+  // part: 0 = every j-chunk; 1 = the first and the last chunk (the planes a j-slab's neighbours wait for);
+  // 2 = the chunks between.  1 and 2 together launch exactly the CTAs of 0 (chunks are independent of each other:
+  // each recomputes the reds next to it), so a slab can relax its edges on one stream and its interior on another.
+  const int jlo = G.jst, jhi = G.jed;
   const int ni = G.ied - G.ist + 1, nj = jhi - jlo + 1;
   a.nti = lin ? (ni + a.ei - 3) / (a.ei - 2) : (ni + a.ei - 5) / (a.ei - 4);
   // j-chunks: enough CTAs for ~8 rounds over the SMs, chunks no shorter than 32 planes (measured flat between 4 and
@@ -726,12 +712,13 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
     njc = (148 + a.ntk * a.nti - 1) / (a.ntk * a.nti);
     if (njc > (nj + 7) / 8) njc = (nj + 7) / 8;
   }
-  { static const char* e = getenv("CZB_NJC"); if (e && part == 0) njc = atoi(e); }   // experiments
+  { static const char* e = getenv("CZB_NJC"); if (e) njc = atoi(e); }   // experiments
   if (njc < 1) njc = 1;
   a.jl = (nj + njc - 1) / njc;
   a.njc = (nj + a.jl - 1) / a.jl;
-  a.edges = 0;
-  if (part == 1) { a.edges = 1; a.jl = RB2_EDGE; a.njc = 2; }
+  a.jc_first = 0; a.jc_step = 1; a.ngy = a.njc;
+  if (part == 1 && a.njc >= 2) { a.jc_step = a.njc - 1; a.ngy = 2; }
+  if (part == 2) { a.jc_first = 1; a.ngy = a.njc - 2; }
   if ((size_t)a.ntk * a.nti * a.njc > L.rb_blocks) return 0;
   a.jr0 = jr0; a.jr1 = jr1; a.jb0 = jlo; a.jb1 = jhi;
   a.ip = ip;
@@ -742,25 +729,10 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
   a.rb = L.rb;
   a.fin = L.fin;
   a.slot2 = lin ? slot2 : -1;
-  const bool with_sig = sig && packed && !lin && part == 0;
-  if (sig && !with_sig) return 0;
-  a.sig_lo = a.sig_hi = nullptr; a.p2p = 0; a.peer_lo = a.peer_hi = nullptr; a.hin_lo = a.hin_hi = -1;
-  if (with_sig) {
-    a.sig_lo = sig->sig_lo; a.sig_hi = sig->sig_hi; a.p2p = sig->p2p;
-    if (sig->p2p) {
-      if (jhi - jlo + 1 < 4) return 0;               // the two edge-plane pairs must not overlap
-      // inbox layout (comm.h): plane index = slot*4 + side*2 + p ; side 0 = planes from the lower neighbour
-      const long long P = G.plane;
-      if (sig->peer_lo) a.peer_lo = sig->peer_lo + ((long long)(sig->out_slot * 4 + 2) - (jlo + G.g - 1)) * P;
-      if (sig->peer_hi) a.peer_hi = sig->peer_hi + ((long long)(sig->out_slot * 4 + 0) - (jhi - 1 + G.g - 1)) * P;
-      if (sig->has_lo) a.hin_lo = sig->in_slot * 4 + 0;
-      if (sig->has_hi) a.hin_hi = sig->in_slot * 4 + 2;
-    }
-  }
-  if (sig_ctas) *sig_ctas = a.ntk * a.nti;
   a.zsrc = (zsrc && packed && !lin) ? 1 : 0;
   if (zsrc && !a.zsrc) return 0;   // only the packed two-colour kernel can skip the source
   if (dry) return 1;               // eligibility probe: every early-out above has been passed, nothing is launched
+  if (a.ngy <= 0) return 3;        // part 2 of a slab with one or two chunks: nothing between the edge chunks
   const size_t T = (size_t)a.ei * EKB;
   const CUtensorMap& tp = tmap_for(p, G, a.ei);
   const CUtensorMap& tb = (mode == MODE_AX) ? tp : tmap_for(b_or_w, G, a.ei);
@@ -773,11 +745,10 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
     return (mode == MODE_AX && slot2 >= 0) ? 2 : 1;
   }
   if (packed) {   // look-ahead (raw TMA slots for p, b): cfg 2 = 3+3, 3 = 4+3, 4 = 5+4, 5 = 5+5
-    const REAL* inbox = (with_sig && sig->p2p) ? sig->inbox : nullptr;
-    if (cfg == 3)      launch_rb2_pk_t<512, 2, 4, 3>(L, a, p, b_or_w, inbox, with_sig);
-    else if (cfg == 4) launch_rb2_pk_t<512, 2, 5, 4>(L, a, p, b_or_w, inbox, with_sig);
-    else if (cfg == 5) launch_rb2_pk_t<512, 2, 5, 5>(L, a, p, b_or_w, inbox, with_sig);
-    else               launch_rb2_pk_t<512, 2, 3, 3>(L, a, p, b_or_w, inbox, with_sig);
+    if (cfg == 3)      launch_rb2_pk_t<512, 2, 4, 3>(L, a, p, b_or_w);
+    else if (cfg == 4) launch_rb2_pk_t<512, 2, 5, 4>(L, a, p, b_or_w);
+    else if (cfg == 5) launch_rb2_pk_t<512, 2, 5, 5>(L, a, p, b_or_w);
+    else               launch_rb2_pk_t<512, 2, 3, 3>(L, a, p, b_or_w);
     return 1;
   }
 #endif
@@ -798,17 +769,13 @@ bool fused_eligible(const Geo& G) {
 }
 
 bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf, REAL omg,
-                      int ip, int jr0, int jr1, int slot, bool add, bool zero_src, int part, const Rb2Sig* sig,
-                      int* sig_ctas) {
-  return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add, -1, zero_src, part, sig, sig_ctas) != 0;
+                      int ip, int jr0, int jr1, int slot, bool add, bool zero_src, int part) {
+  return march(MODE_RB2, L, G, p, b, pnew, cf, omg, ip, jr0, jr1, slot, add, -1, zero_src, part) != 0;
 }
 // Would launch_rb2_fused with these options launch?  (Same early-outs as march(), nothing enqueued.)  The solve
 // loops decide ONCE, before choosing the fused / overlapped loop, so an iteration can never become a silent no-op.
-bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part, bool with_sig, bool p2p) {
-  Rb2Sig sg{};
-  sg.p2p = p2p ? 1 : 0;
-  return march(MODE_RB2, L, G, nullptr, nullptr, nullptr, cf, (REAL)1, 0, G.jst, G.jed, 0, false, -1, zero_src, part,
-               with_sig ? &sg : nullptr, nullptr, true) != 0;
+bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part) {
+  return march(MODE_RB2, L, G, nullptr, nullptr, nullptr, cf, (REAL)1, 0, G.jst, G.jed, 0, false, -1, zero_src, part, true) != 0;
 }
 bool rb2_zero_src_supported(const Geo& G, const REAL* cf) {
 #ifdef _REAL_IS_DOUBLE_
@@ -818,16 +785,16 @@ bool rb2_zero_src_supported(const Geo& G, const REAL* cf) {
   return fused_eligible(G) && unit && march_cfg() >= 2 && (G.nk % 4 == 0);
 #endif
 }
-bool rb2_parts_supported(const Geo& G, const REAL* cf) {
-  return rb2_zero_src_supported(G, cf) && (G.jed - G.jst + 1 >= 2 * RB2_EDGE + 1);
+bool jacobi_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, int part) {
+  return march(MODE_JAC, L, G, nullptr, nullptr, nullptr, cf, (REAL)1, 0, G.jst, G.jed, 0, false, -1, false, part, true) != 0;
 }
 bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
-                         REAL omg, int slot, bool add) {
-  return march(MODE_JAC, L, G, p, b, pnew, cf, omg, 0, G.jst, G.jed, slot, add) != 0;
+                         REAL omg, int slot, bool add, int part) {
+  return march(MODE_JAC, L, G, p, b, pnew, cf, omg, 0, G.jst, G.jed, slot, add, -1, false, part) != 0;
 }
 int launch_ax_fused(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf, const REAL* dotwith,
-                    int slot, int slot2) {
-  return march(MODE_AX, L, G, p, dotwith, ap, cf, (REAL)0, 0, G.jst, G.jed, slot, false, slot2);
+                    int slot, int slot2, int part) {
+  return march(MODE_AX, L, G, p, dotwith, ap, cf, (REAL)0, 0, G.jst, G.jed, slot, false, slot2, false, part);
 }
 
 }  // namespace czb

@@ -128,10 +128,9 @@ __device__ __forceinline__ void mbar_wait_a(uint32_t addr, uint32_t parity) {   
 // streams (the blacks trail the reds by two planes instead of one), which doubles the ILP of the
 // dependent add/divide chains.  Per step: one TMA plane of p and one of b arrive (NSP_/NSB_ slots
 // of look-ahead), one plane is stored, one __syncthreads.
-template <int NT, int CPT, int NSP_, int NSB_, bool SIG>
+template <int NT, int CPT, int NSP_, int NSB_>
 __global__ void __launch_bounds__(NT, 1)
-k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b,
-         const __grid_constant__ CUtensorMap tm_h, const MarchArgs a) {
+k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_b, const MarchArgs a) {
   constexpr int RPW = NT / 32;             // tile rows covered by one pass of the CTA (one warp per row)
   constexpr int EI = RPW * CPT;            // tile rows
   constexpr int T = EI * EKB;              // cells per tile plane
@@ -151,31 +150,17 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   const int lane = tid & 31, wrow = tid >> 5;
 
   // ---- tile / chunk geometry ------------------------------------------------------------
-  // SIG (j-slab of a multi-GPU run): the last chunk is scheduled first and counts its finished CTAs in
-  // *sig_hi, the CTAs of the first chunk count in *sig_lo once their first two planes are stored.
-  //  - NCCL transport: the counters are local; the communication stream waits on them (stream memory
-  //    operation) and sends the slab's edge planes while the rest of this launch is still running.
-  //  - peer transport (a.p2p): the edge planes are ALSO stored, by the same threads, into the neighbour's halo
-  //    inbox (peer memory over NVLink, a.peer_lo / a.peer_hi) and the counters live in the NEIGHBOUR's mailbox
-  //    (system-scope fence + atomic); the neighbour's stream waits on them before its next sweep, whose TMA loads
-  //    take the planes beyond the slab from its inbox (tm_h) instead of the field.  No copy kernel, no NCCL.
-  // SIG is a template parameter: the single-GPU instantiation carries none of this.
-  const int jc = (SIG && a.njc > 1) ? (blockIdx.y == 0 ? a.njc - 1 : (int)blockIdx.y - 1) : (int)blockIdx.y;
-  const bool sig_lo = SIG && jc == 0, sig_hi = SIG && jc == a.njc - 1;
-  if (a.st && a.st->done) {   // converged: nothing to do, but the counters must still advance
-    if (SIG && threadIdx.x == 0) {
-      if (sig_lo && a.sig_lo) { if (a.p2p) atomicAdd_system(a.sig_lo, 1u); else atomicAdd(a.sig_lo, 1u); }
-      if (sig_hi && a.sig_hi) { if (a.p2p) atomicAdd_system(a.sig_hi, 1u); else atomicAdd(a.sig_hi, 1u); }
-    }
-    return;
-  }
+  // Chunk of this CTA: jc_first + blockIdx.y * jc_step.  A j-slab of a multi-GPU run launches its first and last
+  // chunk (jc_step = njc - 1) on a high-priority stream and the chunks between (jc_first = 1) on the main stream, so
+  // that the slab's edge planes can travel to the neighbours while the interior is still being relaxed (solver.cu).
+  const int jc = a.jc_first + (int)blockIdx.y * a.jc_step;
+  if (a.st && a.st->done) return;
   const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk;
   const int kst_c = G.kst + G.g - 1, ist_c = G.ist + G.g - 1;     // C offsets of the first inner cell
   const int P0 = (((kst_c >> 1) & ~1) - PKH) + tk * (PR - 2 * PKH);   // first (halo) pair of the box, even
   const int R0 = ist_c - 2 + ti * (EI - 4);                        // first (halo) row of the box
-  // owned planes of this chunk; a.edges: two chunks of a.jl planes at the two ends of jb0..jb1 (the planes
-  // a j-slab sends to its neighbours, relaxed first so that the exchange overlaps the interior launch)
-  const int ja = a.edges ? (jc == 0 ? a.jb0 : a.jb1 - a.jl + 1) : a.jb0 + jc * a.jl;
+  // owned planes of this chunk
+  const int ja = a.jb0 + jc * a.jl;
   const int jb = min(ja + a.jl - 1, a.jb1);
   const int pl0 = ja - 2;                                          // first p plane fetched
   const int bpl0 = ja - 1;                                         // first b plane fetched
@@ -195,14 +180,7 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
                  ::"r"(dst), "l"(tm), "r"(bar), "r"(2 * P0), "r"(R0), "r"(plane) : "memory");
   };
   auto issue_p = [&](int t) {   // plane pl0+t -> slot t % NSP_
-    const int pl = pl0 + t;
-    const CUtensorMap* tm = &tm_p;
-    int cpl = pl + G.g - 1;
-    if (SIG && a.p2p) {         // planes of a neighbour slab: inbox[slot][side][2] (comm.h)
-      if (a.hin_lo >= 0 && pl < a.jb0) { tm = &tm_h; cpl = a.hin_lo + (pl - (a.jb0 - 2)); }
-      else if (a.hin_hi >= 0 && pl > a.jb1) { tm = &tm_h; cpl = a.hin_hi + (pl - (a.jb1 + 1)); }
-    }
-    issue_plane(raw_p + (uint32_t)(t % NSP_) * TB, bar0 + 8u * (uint32_t)(t % NSP_), tm, cpl);
+    issue_plane(raw_p + (uint32_t)(t % NSP_) * TB, bar0 + 8u * (uint32_t)(t % NSP_), &tm_p, pl0 + t + G.g - 1);
   };
   auto issue_b = [&](int t) {
     issue_plane(raw_b + (uint32_t)(t % NSB_) * TB, bar0 + 8u * (uint32_t)(NSP_ + t % NSB_), &tm_b, bpl0 + t + G.g - 1);
@@ -352,13 +330,6 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
     const unsigned fRO = (do_red && red_owned) ? (XB ? (fl >> 12) : (fl >> 8)) & 0xfu : 0u;
     const unsigned fK = do_black ? (XB ? (fl >> 8) : (fl >> 12)) & 0xfu : 0u;      // blacks sit at !XB
     const unsigned fS = do_black ? (fl >> 16) & 0x3u : 0u;
-    // peer transport: plane s-1 is one of the two planes a neighbour needs -> second store into its inbox.
-    // peer_lo / peer_hi are pre-biased by the host so that the element offset inside OUR field applies.
-    float* peer_dst = nullptr;
-    if (SIG && a.p2p) {
-      if (a.peer_lo && (s - 1 == a.jb0 || s - 1 == a.jb0 + 1)) peer_dst = a.peer_lo;
-      else if (a.peer_hi && (s - 1 == a.jb1 - 1 || s - 1 == a.jb1)) peer_dst = a.peer_hi;
-    }
 
     F2 numR[CPT], numK[CPT], jnR[CPT], jsR[CPT], bbR[CPT], jnK[CPT];
 #pragma unroll
@@ -414,7 +385,6 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
       acc[0] += (double)lo(d2K);
       acc[0] += (double)hi(d2K);
       stg_unit_if(outp[m], wm1[m], (fS >> m) & 1u);
-      if (SIG && peer_dst) stg_unit_if(peer_dst + (outp[m] - a.out), wm1[m], (fS >> m) & 1u);
       outp[m] += G.plane;
       hb[C & 1][m] = XB ? bc[m].a : bc[m].b;     // right-hand side of the blacks of plane s+1 (used at step u+2)
     }
@@ -431,18 +401,8 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   // so the 4x unrolled body exists in two variants (A-B-A-B and B-A-B-A) chosen once.
   using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
   using I2 = std::integral_constant<int, 2>; using I3 = std::integral_constant<int, 3>;
-  // first chunk of a j-slab: its planes ja, ja+1 are stored once step 4 is done (step u stores plane ja-3+u);
-  // checked between the unrolled groups of four steps, i.e. after step 7, or at the end of a shorter chunk
-  bool lo_pending = sig_lo;
-  auto signal_lo = [&]() {
-    if (a.p2p) __threadfence_system(); else __threadfence();
-    __syncthreads();
-    if (tid == 0 && a.sig_lo) { if (a.p2p) atomicAdd_system(a.sig_lo, 1u); else atomicAdd(a.sig_lo, 1u); }
-    lo_pending = false;
-  };
   if (((par + (unsigned)(pl0 + 1)) & 1u) == 0u) {
     for (int u = 0; u < nsteps; u += 4) {
-      if (SIG && lo_pending && u >= 8) signal_lo();
       step(u, I0{}, std::false_type{});
       if (u + 1 >= nsteps) break;
       step(u + 1, I1{}, std::true_type{});
@@ -453,7 +413,6 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
     }
   } else {
     for (int u = 0; u < nsteps; u += 4) {
-      if (SIG && lo_pending && u >= 8) signal_lo();
       step(u, I0{}, std::true_type{});
       if (u + 1 >= nsteps) break;
       step(u + 1, I1{}, std::false_type{});
@@ -462,12 +421,6 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
       if (u + 3 >= nsteps) break;
       step(u + 3, I3{}, std::false_type{});
     }
-  }
-  if (SIG && lo_pending) signal_lo();
-  if (sig_hi) {
-    if (a.p2p) __threadfence_system(); else __threadfence();
-    __syncthreads();
-    if (tid == 0 && a.sig_hi) { if (a.p2p) atomicAdd_system(a.sig_hi, 1u); else atomicAdd(a.sig_hi, 1u); }
   }
   grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add, a.fin});
 }
@@ -507,7 +460,7 @@ k_lin_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   const int tid = threadIdx.x;
   const int lane = tid & 31, wrow = tid >> 5;
 
-  const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk, jc = blockIdx.y;
+  const int tk = blockIdx.x % a.ntk, ti = blockIdx.x / a.ntk, jc = a.jc_first + (int)blockIdx.y * a.jc_step;
   const int kst_c = G.kst + G.g - 1, ist_c = G.ist + G.g - 1;
   const int P0 = (((kst_c >> 1) & ~1) - PKH) + tk * (PR - 2 * PKH);
   const int R0 = ist_c - 1 + ti * (EI - 2);

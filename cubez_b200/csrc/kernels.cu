@@ -313,9 +313,10 @@ __global__ void k_state_reset(LoopState* st) {
 }
 
 __global__ void k_finish_iteration(LoopState* st, int slot, double res_normal, double eps, double* hist,
-                                   int hist_len) {
+                                   int hist_len, int slot2) {
   if (st->done) return;
   double res = st->acc[slot];
+  if (slot2 >= 0) res += st->acc[slot2];     // edge launch + interior launch of a j-slab
   res *= res_normal;          // cz_Poisson.cpp:69-70
   res = sqrt(res);
   st->res = res;
@@ -480,8 +481,8 @@ void launch_state_reset(const Launch& L, LoopState* st) {
 }
 
 void launch_finish_iteration(const Launch& L, LoopState* st, int slot, double res_normal, double eps, double* hist,
-                             int hist_len) {
-  k_finish_iteration<<<1, 1, 0, L.s>>>(st, slot, res_normal, eps, hist, hist_len);
+                             int hist_len, int slot2) {
+  k_finish_iteration<<<1, 1, 0, L.s>>>(st, slot, res_normal, eps, hist, hist_len, slot2);
   CZB_CHECK(cudaGetLastError());
   count_launch();
 }

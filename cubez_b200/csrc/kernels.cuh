@@ -107,40 +107,27 @@ void launch_pcr_lines_maf(const Launch& L, const Geo& G, int pn, int mode, int d
 bool fused_eligible(const Geo& G);
 // both colours of one red-black SOR iteration, p -> pnew (ping-pong). Reds are relaxed on planes
 // jr0..jr1 (includes halo planes owned by a neighbour rank), blacks/stores on jst..jed.
-// Edge-plane signalling of a j-slab sweep (part 0, packed float kernel only).  The launch adds *sig_ctas to each
-// counter: *sig_lo as soon as the first two owned planes are stored everywhere, *sig_hi when the last chunk
-// (scheduled first) is complete.  NCCL transport (p2p = 0): local counters, a communication stream waits on them
-// and sends the planes.  Peer transport (p2p = 1, comm.h): the counters are the NEIGHBOURS' mailbox words, the
-// edge planes are also stored into the neighbours' halo inboxes (slot out_slot), and the planes beyond the slab
-// are read from our own inbox (slot in_slot) instead of the field's guard planes.
-struct Rb2Sig {
-  unsigned int* sig_lo; unsigned int* sig_hi;   // null = no neighbour on that side (p2p)
-  int p2p;
-  const REAL* inbox; int in_slot; bool has_lo, has_hi;
-  REAL* peer_lo; REAL* peer_hi; int out_slot;
-};
+// part: 0 = every j-chunk of the launch, 1 = the first and the last chunk only, 2 = the chunks between (1 + 2 launch
+// exactly the CTAs of 0; a j-slab relaxes its edge chunks on a high-priority stream and sends their outermost planes
+// to the neighbours while the interior chunks run).  part 2 of a slab with fewer than three chunks launches nothing.
 bool launch_rb2_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
-                      REAL omg, int ip, int jr0, int jr1, int slot, bool add, bool zero_src = false, int part = 0,
-                      const Rb2Sig* sig = nullptr, int* sig_ctas = nullptr);
+                      REAL omg, int ip, int jr0, int jr1, int slot, bool add, bool zero_src = false, int part = 0);
 // zero_src: p is known to be all zero and is not read at all (packed float kernel only; check first)
 bool rb2_zero_src_supported(const Geo& G, const REAL* cf);
-bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part, bool with_sig,
-                          bool p2p = false);
-// part = 1: only the two planes at each end of the owned j range (what a slab sends to its neighbours),
-// part = 2: only the planes between; 1 then 2 equals one part = 0 sweep (packed float kernel only; check first)
-bool rb2_parts_supported(const Geo& G, const REAL* cf);
+bool rb2_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, bool zero_src, int part);
+bool jacobi_fused_launchable(const Launch& L, const Geo& G, const REAL* cf, int part);
 bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pnew, const REAL* b, const REAL* cf,
-                         REAL omg, int slot, bool add);
+                         REAL omg, int slot, bool add, int part = 0);
 // ap = A p on inner cells, 0 on the other cells of stored pairs; acc[slot] = (ap, dotwith).
 // Returns 0 = not eligible (use launch_calc_ax), 1 = done, 2 = done and acc[slot2] = (ap, ap) as well
 // (slot2 < 0: not wanted).
 int launch_ax_fused(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf, const REAL* dotwith,
-                    int slot, int slot2 = -1);
+                    int slot, int slot2 = -1, int part = 0);
 
 // ---- loop control (tiny kernels) --------------------------------------------------------
 void launch_state_reset(const Launch& L, LoopState* st);
 // res = sqrt(acc[slot]*res_normal); hist[itr] = res; ++itr; done |= res < eps
 void launch_finish_iteration(const Launch& L, LoopState* st, int slot, double res_normal, double eps,
-                             double* hist, int hist_len);
+                             double* hist, int hist_len, int slot2 = -1);   // slot2 >= 0: acc[slot] += acc[slot2] first
 
 }  // namespace czb

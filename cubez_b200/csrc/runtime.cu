@@ -36,6 +36,7 @@ void Runtime::init(int dev) {
   CZB_CHECK(cudaMallocHost(&h_state, sizeof(LoopState) * 4));
   CZB_CHECK(cudaMalloc(&d_err, sizeof(unsigned long long) * 4));
   CZB_CHECK(cudaDeviceSynchronize());
+  { const char* e = getenv("CZB_PROFILE"); prof.on = e && atoi(e) != 0; }
   inited = true;
 }
 
@@ -88,6 +89,56 @@ void* Runtime::mirror_acquire(const void* host, size_t bytes) {
 void Runtime::mirror_release(const void* host) {
   auto it = mirrors.find(host);
   if (it != mirrors.end() && it->second.pins > 0) it->second.pins--;
+}
+
+// ---- phase profile ---------------------------------------------------------------------------------------------
+int PhaseProf::id(const char* label) {
+  for (size_t i = 0; i < acc.size(); ++i) if (acc[i].label == label) return (int)i;
+  Acc a; a.label = label;
+  acc.push_back(a);
+  return (int)acc.size() - 1;
+}
+void PhaseProf::begin(const char* label, double flop, cudaStream_t s) {
+  if (cur >= 0) return;                 // sections are exclusive: an inner one is folded into the running one
+  if (open.size() >= 8192) drain();
+  Rec r; r.label = id(label); r.flop = flop;
+  for (cudaEvent_t* e : {&r.e0, &r.e1}) {
+    if (!pool.empty()) { *e = pool.back(); pool.pop_back(); }
+    else CZB_CHECK(cudaEventCreate(e));
+  }
+  CZB_CHECK(cudaEventRecord(r.e0, s));
+  open.push_back(r);
+  cur = (int)open.size() - 1;
+}
+void PhaseProf::end(cudaStream_t s) {
+  if (cur < 0) return;
+  CZB_CHECK(cudaEventRecord(open[cur].e1, s));
+  cur = -1;
+}
+void PhaseProf::drain() {
+  for (const Rec& r : open) {
+    float ms = 0.f;
+    CZB_CHECK(cudaEventSynchronize(r.e1));
+    CZB_CHECK(cudaEventElapsedTime(&ms, r.e0, r.e1));
+    Acc& a = acc[r.label];
+    a.ms += ms; a.flop += r.flop; a.calls += 1;
+    pool.push_back(r.e0); pool.push_back(r.e1);
+  }
+  open.clear();
+  cur = -1;
+}
+void PhaseProf::reset() { drain(); acc.clear(); }
+void PhaseProf::report(FILE* f, const char* title) {
+  drain();
+  double tot = 0.0;
+  for (const Acc& a : acc) tot += a.ms;
+  fprintf(f, "# %s -- device time per section (CUDA events on the solve stream; labels = the reference's PMlib sections,\n", title);
+  fprintf(f, "# src/cz_cpp/cz_miscel.cpp:177-262; flop = the reference's analytic counts)\n");
+  fprintf(f, "%-22s %10s %12s %8s %14s %10s\n", "Section", "call", "time[ms]", "[%]", "flop", "GFLOP/s");
+  for (const Acc& a : acc)
+    fprintf(f, "%-22s %10lld %12.3f %8.2f %14.6e %10.2f\n", a.label.c_str(), a.calls, a.ms, tot > 0 ? 100.0 * a.ms / tot : 0.0,
+            a.flop, a.ms > 0 ? a.flop / a.ms * 1.0e-6 : 0.0);
+  fprintf(f, "%-22s %10s %12.3f %8.2f\n", "Total (exclusive)", "", tot, 100.0);
 }
 
 bool is_device_ptr(const void* p) {
@@ -157,6 +208,22 @@ void czb_memcpy_d2h(void* dst, const void* src, size_t bytes) {
 }
 
 long long czb_launch_count(void) { return czb::launch_count(); }
+
+void czb_profile(int on) {
+  Runtime& R = rt();
+  R.prof.reset();
+  R.prof.on = on != 0;
+}
+
+int czb_profile_report(const char* path, const char* title) {
+  Runtime& R = rt();
+  R.sync();
+  FILE* f = path ? fopen(path, "w") : stdout;
+  if (!f) return -1;
+  R.prof.report(f, title ? title : "czb200");
+  if (path) fclose(f);
+  return (int)R.prof.acc.size();
+}
 
 void czb_staged_bytes(double* h2d, double* d2h) {
   Runtime& R = rt();

@@ -4,6 +4,8 @@
 #include "kernels.cuh"
 #include <unordered_map>
 #include <cstring>
+#include <string>
+#include <vector>
 
 namespace czb {
 
@@ -12,6 +14,26 @@ long long launch_count();
 // Device mirror of a caller's host array (per-call reference ABI).  The cache is bounded: least recently used
 // mirrors that no call is using are freed once the total exceeds Runtime::mirror_cap bytes or 64 entries.
 struct Mirror { void* dev; size_t bytes; unsigned long long stamp; int pins; };
+
+// Per-phase device times keyed by the reference's PMlib labels (src/cz_cpp/cz_miscel.cpp:177-262, the sections its
+// TIMING_start/TIMING_stop bracket in cz_Poisson.cpp) -- the data of its profiling.txt (cz_Evaluate.cpp:506-544).
+// Off by default (two event records per section); czb_profile(1) or CZB_PROFILE=1 switches it on, which also keeps
+// the solve loops from replaying CUDA graphs (events cannot be timed inside a captured batch).
+struct PhaseProf {
+  bool on = false;
+  struct Acc { std::string label; double ms = 0.0, flop = 0.0; long long calls = 0; };
+  struct Rec { int label; cudaEvent_t e0, e1; double flop; };
+  std::vector<Acc> acc;                 // first-use order
+  std::vector<Rec> open;                // sections whose elapsed time has not been read yet
+  std::vector<cudaEvent_t> pool;
+  int cur = -1;                         // index into `open` of the running section
+  int id(const char* label);
+  void begin(const char* label, double flop, cudaStream_t s);
+  void end(cudaStream_t s);
+  void drain();                         // synchronises the events and accumulates
+  void reset();
+  void report(FILE* f, const char* title);
+};
 
 struct Runtime {
   bool inited = false;
@@ -31,6 +53,7 @@ struct Runtime {
   PcrTables pcr2{0, 0, 0, 0, nullptr, nullptr};
   PcrTables pcr4{0, 0, 0, 0, nullptr, nullptr};
   size_t h2d_bytes = 0, d2h_bytes = 0;   // staged traffic (per-call ABI with host pointers)
+  PhaseProf prof;
 
   void init(int dev);
   Launch launch(const LoopState* st = nullptr, LoopState* acc = nullptr) {
@@ -43,6 +66,15 @@ struct Runtime {
 };
 
 Runtime& rt();   // initialises lazily on the current device (or CZB_DEVICE)
+
+// Scoped section of the phase profile on the runtime's stream; costs one branch when profiling is off.
+struct Phase {
+  bool live;
+  Phase(const char* label, double flop = 0.0) : live(rt().prof.on) { if (live) rt().prof.begin(label, flop, rt().stream); }
+  ~Phase() { if (live) rt().prof.end(rt().stream); }
+  Phase(const Phase&) = delete;
+  Phase& operator=(const Phase&) = delete;
+};
 
 // Is `p` usable directly by kernels (device or managed memory)?
 bool is_device_ptr(const void* p);

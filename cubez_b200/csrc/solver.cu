@@ -57,12 +57,10 @@ __global__ void k_bicg_scalar(LoopState* st, int phase, double res_normal, doubl
   }
 }
 
-// peer transport: tell the ring neighbours that our halo inbox is prepared (stream-ordered after the copies that
-// fill it); a system-scope atomic into their mailbox words, which their streams wait on.
-__global__ void k_post_ready(unsigned int* lo, unsigned int* hi) {
-  __threadfence_system();
-  if (lo) atomicAdd_system(lo, 1u);
-  if (hi) atomicAdd_system(hi, 1u);
+// bc_k inside a solve loop = the reference's "BoundaryCondition" section (cz_Poisson.cpp:73-75 and alike)
+void phase_bc_k(const Launch& L, const Geo& G, REAL* p, REAL dh, const REAL* org, const int* nID, int joff) {
+  Phase ph("BoundaryCondition");
+  launch_bc_k(L, G, p, dh, org, nID, joff);
 }
 
 int getNumStage(int n) {   // cz.h:293-300
@@ -109,11 +107,11 @@ Launch czb_ctx::launch(bool with_state) {
 }
 
 void czb_ctx::Comm_S(REAL* f, int width) {
-  if (comm && comm->nranks > 1) comm_halo(comm, f, G, width, rt().stream);
+  if (comm && comm->nranks > 1) { Phase ph("Comm_Poisson"); comm_halo(comm, f, G, width, rt().stream); }
 }
 
 void czb_ctx::Comm_SUM(int slot, int count) {
-  if (comm && comm->nranks > 1) comm_allreduce_sum(comm, &d_state->acc[slot], count, rt().stream);
+  if (comm && comm->nranks > 1) { Phase ph("Comm_Res_Poisson"); comm_allreduce_sum(comm, &d_state->acc[slot], count, rt().stream); }
 }
 
 // ---- stretched-grid (MAF) state ---------------------------------------------------------------
@@ -151,31 +149,125 @@ REAL* czb_ctx::pivot() {
   return pvt;
 }
 
-// cuStreamWaitValue32 through the runtime's driver entry point (no link dependency on libcuda)
-static void stream_wait_geq(cudaStream_t s, unsigned int* dev, unsigned int value) {
-  typedef CUresult (*Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
-  static Fn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    CZB_CHECK(cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q));
-    if (!p || q != cudaDriverEntryPointSuccess) { fprintf(stderr, "czb200: cuStreamWaitValue32 unavailable\n"); abort(); }
-    fn = (Fn)p;
-  }
-  const CUresult r = fn((CUstream)s, (CUdeviceptr)(uintptr_t)dev, value, CU_STREAM_WAIT_VALUE_GEQ);
-  if (r != CUDA_SUCCESS) { fprintf(stderr, "czb200: cuStreamWaitValue32 failed (%d)\n", (int)r); abort(); }
-}
-
 void czb_ctx::ensure_comm_stream() {
   if (cs) return;
-  CZB_CHECK(cudaMalloc(&d_sig, 2 * sizeof(unsigned int)));
-  CZB_CHECK(cudaMemset(d_sig, 0, 2 * sizeof(unsigned int)));
-  sig_target = 0;
   int lo = 0, hi = 0;
   CZB_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
   CZB_CHECK(cudaStreamCreateWithPriority(&cs, cudaStreamNonBlocking, hi));
-  cudaEvent_t* evs[] = {&ev_edge, &ev_int, &ev_halo[0], &ev_halo[1], &ev_fin[0], &ev_fin[1], &ev_join};
+  CZB_CHECK(cudaStreamCreateWithPriority(&ov.es, cudaStreamNonBlocking, hi));
+  cudaEvent_t* evs[] = {&ev_fin[0], &ev_fin[1], &ev_join, &ov.ev_a[0], &ov.ev_a[1], &ov.ev_b[0], &ov.ev_b[1], &ov.ev_start, &ov.ev_join_e};
   for (cudaEvent_t* e : evs) CZB_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  Runtime& R = rt();
+  CZB_CHECK(cudaMalloc(&ov.rb_edge.partial, sizeof(double) * R.rb_blocks * CZB_MAX_ACC));
+  CZB_CHECK(cudaMalloc(&ov.rb_edge.ticket, sizeof(unsigned int)));
+  CZB_CHECK(cudaMemset(ov.rb_edge.ticket, 0, sizeof(unsigned int)));
+}
+
+// ---- SlabOverlap ---------------------------------------------------------------------------------------------------
+bool czb_ctx::slab_overlap_begin(bool local_ok, int w) {
+  if (!comm || comm->nranks <= 1) return false;
+  static const bool no_ovl = getenv("CZB_NO_OVERLAP") != nullptr;
+  if (no_ovl) return false;
+  // local_ok depends on the solver and on the geometry in k and i only (tile counts, row pitch), which every slab of a
+  // run shares; a solver that cannot split its sweeps stays on the plain loop without a collective
+  if (!local_ok) return false;
+  Runtime& R = rt();
+  if (!ov.decided) {   // one collective decision per context: a ring that mixes the two loop forms would hang
+    ov.p2p = comm_p2p_setup(comm, (size_t)G.plane, R.stream, local_ok);     // true only if every rank is able AND willing
+    ov.all_ok = ov.p2p;
+    if (!ov.p2p) {     // peer transport unavailable or refused: do all ranks at least want the split launches (NCCL exchange)?
+      double* flag = nullptr;
+      CZB_CHECK(cudaMalloc((void**)&flag, sizeof(double)));
+      const double f = local_ok ? 0.0 : 1.0;
+      CZB_CHECK(cudaMemcpyAsync(flag, &f, sizeof(double), cudaMemcpyHostToDevice, R.stream));
+      comm_allreduce_sum(comm, flag, 1, R.stream);
+      double bad = 1.0;
+      CZB_CHECK(cudaMemcpyAsync(&bad, flag, sizeof(double), cudaMemcpyDeviceToHost, R.stream));
+      R.sync();
+      cudaFree(flag);
+      ov.all_ok = (bad == 0.0);
+    }
+    ov.decided = true;
+  }
+  if (!ov.all_ok) return false;
+  (void)w;
+  ensure_comm_stream();
+  ov.deferred = false;
+  return true;
+}
+
+void czb_ctx::slab_exchange(REAL* dst, int w, int it) {
+  Phase ph("Comm_Poisson");
+  if (ov.p2p) comm_p2p_push(comm, dst + (long long)G.g * G.plane, dst + (long long)(G.jx - w + G.g) * G.plane, w, it & 1, ov.es);
+  else        comm_halo(comm, dst, G, w, ov.es);
+}
+
+void czb_ctx::slab_overlap_edges_begin(int it, REAL* src, int w, bool converge_check, Launch& LE, Launch& LM) {
+  Runtime& R = rt();
+  LM = launch();
+  LE = launch(); LE.s = ov.es; LE.rb = ov.rb_edge;
+  if (it == 1) {   // everything queued on the solve stream so far (state reset, initial exchanges, WRK copy) comes first
+    CZB_CHECK(cudaEventRecord(ov.ev_start, R.stream));
+    CZB_CHECK(cudaStreamWaitEvent(ov.es, ov.ev_start, 0));
+    CZB_CHECK(cudaStreamWaitEvent(cs, ov.ev_start, 0));
+  } else {
+    // the edge chunks read two planes of the interior launch of iteration it-1; their guard planes come from the
+    // neighbours' edge launches of iteration it-1
+    CZB_CHECK(cudaStreamWaitEvent(ov.es, ov.ev_b[(it - 1) & 1], 0));
+    if (ov.p2p) {
+      comm_p2p_wait(comm, ov.es);
+      comm_p2p_fetch(comm, src + (long long)(G.g - w) * G.plane, src + (long long)(G.jx + G.g) * G.plane, w, (it - 1) & 1, ov.es);
+    }
+    CZB_CHECK(cudaStreamWaitEvent(R.stream, ov.ev_a[(it - 1) & 1], 0));   // the interior chunks read the edge chunks' planes
+  }
+  if (converge_check && it >= 3) {   // the test of iteration it-2 decides whether this one still runs
+    CZB_CHECK(cudaStreamWaitEvent(ov.es, ev_fin[(it - 2) & 1], 0));
+    CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_fin[(it - 2) & 1], 0));
+  }
+}
+
+void czb_ctx::slab_overlap_edges_end(int it, REAL* dst, int w, bool defer_exchange) {
+  CZB_CHECK(cudaEventRecord(ov.ev_a[it & 1], ov.es));
+  ov.deferred = defer_exchange;
+  if (!defer_exchange) slab_exchange(dst, w, it);
+}
+
+void czb_ctx::slab_overlap_iteration_end(int it, REAL* dst, int w, bool converge_check, int slot_a, int slot_b) {
+  Runtime& R = rt();
+  CZB_CHECK(cudaEventRecord(ov.ev_b[it & 1], R.stream));
+  if (ov.deferred) {
+    CZB_CHECK(cudaStreamWaitEvent(ov.es, ov.ev_b[it & 1], 0));
+    slab_exchange(dst, w, it);
+    ov.deferred = false;
+  }
+  if (converge_check) {
+    CZB_CHECK(cudaStreamWaitEvent(cs, ov.ev_a[it & 1], 0));
+    CZB_CHECK(cudaStreamWaitEvent(cs, ov.ev_b[it & 1], 0));
+    static const bool exp_noar = getenv("CZB_EXP_NOALLREDUCE") != nullptr;   // timing experiment only (wrong results)
+    if (!exp_noar) comm_allreduce_sum(comm, &d_state->acc[slot_a], slot_b == slot_a + 1 ? 2 : 1, cs);
+    Launch Lc = launch(); Lc.s = cs;
+    launch_finish_iteration(Lc, d_state, slot_a, res_normal, eps, d_hist, hist_cap, slot_b == slot_a + 1 ? slot_b : -1);
+    CZB_CHECK(cudaEventRecord(ev_fin[it & 1], cs));
+    cs_used = true;
+  }
+}
+
+void czb_ctx::slab_overlap_finish(REAL* X, int w, int done_iters) {
+  Runtime& R = rt();
+  CZB_CHECK(cudaEventRecord(ov.ev_join_e, ov.es));
+  CZB_CHECK(cudaStreamWaitEvent(R.stream, ov.ev_join_e, 0));
+  join_comm_stream();
+  // a launch that ran while `done` became visible may have left its reduction ticket behind (see end_loop)
+  CZB_CHECK(cudaMemsetAsync(ov.rb_edge.ticket, 0, sizeof(unsigned int), R.stream));
+  if (ov.p2p) {
+    // Quiesce the ring (every push we are owed has landed, so the neighbours have also finished reading what we sent),
+    // then give X the halo of its final state, as a Comm_S(X, w) would have.
+    comm_p2p_wait(comm, R.stream);
+    if (done_iters >= 1)
+      comm_p2p_fetch(comm, X + (long long)(G.g - w) * G.plane, X + (long long)(G.jx + G.g) * G.plane, w, done_iters & 1, R.stream);
+  } else if (done_iters & 1) {
+    Comm_S(X, w);   // the last exchange filled WRK's guard planes
+  }
 }
 
 void czb_ctx::join_comm_stream() {
@@ -227,7 +319,7 @@ int czb_ctx::run_checked(int itr_max, double& res, Body body) {
   // parity (ping-pong roles) once it > 2 and every batch starts at an odd iteration, so the captured launches are
   // exactly those a direct enqueue would make; the kernels read their iteration state (done, itr) on the device.
   static const bool no_graph = getenv("CZB_NO_GRAPH") != nullptr;
-  bool graphs = !no_graph && !(comm && comm->nranks > 1) && itr_max >= 3 * batch;
+  bool graphs = !no_graph && !rt().prof.on && !(comm && comm->nranks > 1) && itr_max >= 3 * batch;
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t gexec = nullptr;
   long long graph_launches = 0;
@@ -287,7 +379,29 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     wrk_guards_zero = true;
   }
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
+  // multi-rank: edge chunks + one plane to each neighbour while the interior chunks run (SlabOverlap, see RBSOR)
+  const bool ovl = slab_overlap_begin(!maf && variant == 0 && fused_eligible(G) && jacobi_fused_launchable(launch(), G, cf, 0) &&
+                                      jacobi_fused_launchable(launch(), G, cf, 1), 1);
+  auto body_ovl = [&](int it) {
+    REAL* src = (it & 1) ? X : W;
+    REAL* dst = (it & 1) ? W : X;
+    const int sa = converge_check ? ((it & 1) ? 0 : 5) : rs, sb = converge_check ? sa + 1 : rs;
+    Launch LE, LM;
+    slab_overlap_edges_begin(it, src, 1, converge_check, LE, LM);
+    {
+      Phase ph("JACOBI_kernel", 18.0 * G.cells());
+      if (!launch_jacobi_fused(LE, G, src, dst, B, cf, ac1, sa, false, 1)) { fprintf(stderr, "czb200: fused Jacobi sweep refused a launch\n"); abort(); }
+    }
+    slab_overlap_edges_end(it, dst, 1, converge_check && it <= 2);
+    launch_jacobi_fused(LM, G, src, dst, B, cf, ac1, sb, false, 2);
+    if (converge_check && it <= 2) {
+      CZB_CHECK(cudaStreamWaitEvent(R.stream, ov.ev_a[it & 1], 0));
+      phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+    }
+    slab_overlap_iteration_end(it, dst, 1, converge_check, sa, sb);
+  };
   auto body = [&](int it) {
+    if (ovl) { body_ovl(it); return; }
     REAL* src = (it & 1) ? X : W;
     REAL* dst = (it & 1) ? W : X;
     Launch L = launch();
@@ -296,9 +410,12 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     Launch Lf = L;
     if (fold) Lf.fin = FinishSpec{1, res_normal, eps, d_hist, hist_cap};
     bool folded = false;
-    if (maf) launch_jacobi_maf(L, G, src, dst, B, axes(), ac1, rs, false);   // cz_Poisson.cpp:45-52
-    else if (variant == 0 && launch_jacobi_fused(Lf, G, src, dst, B, cf, ac1, rs, false)) folded = fold;
-    else launch_jacobi(L, G, src, dst, B, cf, ac1, rs, false);
+    {
+      Phase ph(maf ? "JACOBI_MAF_kernel" : "JACOBI_kernel", (maf ? 66.0 : 18.0) * G.cells());   // cz_Poisson.cpp:48-59
+      if (maf) launch_jacobi_maf(L, G, src, dst, B, axes(), ac1, rs, false);   // cz_Poisson.cpp:45-52
+      else if (variant == 0 && launch_jacobi_fused(Lf, G, src, dst, B, cf, ac1, rs, false)) folded = fold;
+      else launch_jacobi(L, G, src, dst, B, cf, ac1, rs, false);
+    }
     Comm_S(dst, 1);
     if (converge_check) {
       Comm_SUM(0);
@@ -306,7 +423,7 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
       // bc_k (cz_Poisson.cpp:73) is idempotent once both ping-pong buffers hold the Dirichlet values (see RBSOR).
       // It is launched WITHOUT the done gate (here and in every loop below): the reference calls it before
       // `if (res < eps) break` (cz_Poisson.cpp:73-77, 495-497), i.e. also on the converging iteration.
-      if (it <= 2) launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+      if (it <= 2) phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
     }
   };
   int itr, done_iters;
@@ -317,11 +434,13 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     for (int it = 1; it <= itr_max; ++it) body(it);
     itr = itr_max + 1; done_iters = itr_max;
   }
+  if (!converge_check) join_comm_stream();
   if (done_iters & 1) {
     launch_copy_inner(launch(false), G, X, W);
-    if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // X missed the bc_k of an odd last iteration
-    Comm_S(X, 1);   // the last exchange filled WRK's guard planes; X leaves with the halo of its final state (cz_Poisson.cpp:63)
+    if (converge_check) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // X missed the bc_k of an odd last iteration
   }
+  if (ovl) slab_overlap_finish(X, 1, done_iters);
+  else if (done_iters & 1) Comm_S(X, 1);   // the last exchange filled WRK's guard planes; X leaves with the halo of its final state (cz_Poisson.cpp:63)
   flop += (maf ? 66.0 : 18.0) * G.cells() * done_iters;
   return itr;
 }
@@ -331,13 +450,16 @@ int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool
   const int rs = converge_check ? 0 : 7;   // reduction slot (7 = scratch inside the preconditioner)
   auto body = [&](int it) {
     Launch L = launch();
-    if (maf) launch_psor_sweep_maf(L, G, X, B, axes(), ac1, rs, false);   // cz_Poisson.cpp:108-114
-    else     launch_psor_sweep(L, G, X, B, cf, ac1, rs, false);
+    {
+      Phase ph(maf ? "SOR_MAF_kernel" : "SOR_kernel", (maf ? 66.0 : 18.0) * G.cells());   // cz_Poisson.cpp:110-120
+      if (maf) launch_psor_sweep_maf(L, G, X, B, axes(), ac1, rs, false);   // cz_Poisson.cpp:108-114
+      else     launch_psor_sweep(L, G, X, B, cf, ac1, rs, false);
+    }
     Comm_S(X, 1);
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -357,8 +479,8 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
   // more tiles than reduction slots); a refused launch inside the loop would make the iteration a silent no-op.
   const bool zs_wanted = !converge_check && pre_zero_src;
   const bool fused = !maf && (variant == 0) && fused_eligible(G) &&
-                     rb2_fused_launchable(launch(), G, cf, false, 0, false) &&
-                     (!zs_wanted || rb2_fused_launchable(launch(), G, cf, true, 0, false));
+                     rb2_fused_launchable(launch(), G, cf, false, 0) &&
+                     (!zs_wanted || rb2_fused_launchable(launch(), G, cf, true, 0));
   auto must = [](bool ok) {
     if (!ok) { fprintf(stderr, "czb200: the fused red-black sweep refused a launch it had accepted at set-up\n"); abort(); }
   };
@@ -369,6 +491,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     // locally from them, which keeps the result equal to the single-domain one.
     Runtime& R = rt();
     REAL* W = field(WRK);
+    const bool mr = comm && comm->nranks > 1;
     if (converge_check) {
       Comm_S(X, 2);
       CZB_CHECK(cudaMemcpyAsync(W, X, sizeof(REAL) * field_elems(), cudaMemcpyDeviceToDevice, R.stream));
@@ -379,136 +502,47 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     }
     Comm_S(B, 2);
     const int jr0 = G.jst - (nID[2] >= 0 ? 1 : 0), jr1 = G.jed + (nID[3] >= 0 ? 1 : 0);
-    // Multi-rank overlap: the two planes at each end of the slab are relaxed first (part 1) and sent while
-    // the planes between are relaxed (part 2); the residual all-reduce and the convergence test of
-    // iteration k run on the communication stream next to iteration k+1.  Iteration k+1 only reads the
-    // converged field (it writes the other ping-pong buffer), iteration k+2 waits for the test of k, so
-    // iteration counts, histories and the returned field are those of a loop that tests every iteration.
+    // Multi-rank overlap (SlabOverlap below): the first and the last j-chunk of the sweep run on a high-priority
+    // stream and their outermost planes travel to the neighbours -- copy engines over NVLink peer memory, or NCCL --
+    // while the chunks between run on the main stream.  Both launches are the SAME kernel a single GPU runs.  The
+    // residual all-reduce and the convergence test of iteration k run on a third stream next to iteration k+1, which
+    // only READS the converged field (it writes the other ping-pong buffer); iteration k+2 waits for the test of k,
+    // so iteration counts, histories and the returned field are those of a loop that tests every iteration.
     static const bool no_ovl = getenv("CZB_NO_OVERLAP") != nullptr;
-    static const bool no_sig = getenv("CZB_NO_SIGNAL") != nullptr;   // fall back to edge launch + interior launch
-    const bool ovl_ok = comm && comm->nranks > 1 && !no_ovl && rb2_parts_supported(G, cf);
-    const bool sig_ok = ovl_ok && !no_sig && rb2_fused_launchable(launch(), G, cf, zs_wanted, 0, true);
-    const bool parts_ok = ovl_ok && rb2_fused_launchable(launch(), G, cf, zs_wanted, 1, false) &&
-                          rb2_fused_launchable(launch(), G, cf, zs_wanted, 2, false);
-    const bool ovl = sig_ok || parts_ok;
-    if (ovl) ensure_comm_stream();
-    const bool use_sig = sig_ok;
-    // Timing experiments only (results are WRONG with them): CZB_EXP_NOCOMM skips the halo traffic / waits and the
-    // residual all-reduce of the overlapped loops; CZB_EXP_NOALLREDUCE only the all-reduce.
-    static const bool exp_nocomm = getenv("CZB_EXP_NOCOMM") != nullptr;
-    static const bool exp_noar = exp_nocomm || getenv("CZB_EXP_NOALLREDUCE") != nullptr;
-    // Peer transport (comm.h): decided once per communicator, collectively (every rank or none).
-    bool p2p = false;
-    if (comm && comm->nranks > 1 && !no_ovl) {
-      const bool want = ovl_ok && !no_sig && rb2_fused_launchable(launch(), G, cf, false, 0, true, true) &&
-                        (!rb2_zero_src_supported(G, cf) || rb2_fused_launchable(launch(), G, cf, true, 0, true, true));
-      p2p = comm_p2p_setup(comm, (size_t)G.plane, R.stream, want) && want;
-    }
-    const size_t pl2 = 2 * (size_t)G.plane;          // two planes
-    REAL* const glo = X;                                                   // X's guard planes -1, 0
-    REAL* const ghi = X + (long long)(G.jx + G.g) * G.plane;               // X's guard planes jx+1, jx+2
-    if (p2p) {
-      // Prepare the inbox: both slots start as X's own guard planes (exchanged above / all zero in the
-      // preconditioner), so the cells the neighbours' sweeps never store (boundary rows) hold the right values and
-      // iteration 1 finds its halos in slot 0.  Then tell the neighbours they may write, and wait for their word.
-      for (int sl = 0; sl < 2; ++sl) {
-        if (comm->lo >= 0) CZB_CHECK(cudaMemcpyAsync(comm->inbox + (size_t)(sl * 4 + 0) * G.plane, glo, sizeof(REAL) * pl2, cudaMemcpyDeviceToDevice, R.stream));
-        if (comm->hi >= 0) CZB_CHECK(cudaMemcpyAsync(comm->inbox + (size_t)(sl * 4 + 2) * G.plane, ghi, sizeof(REAL) * pl2, cudaMemcpyDeviceToDevice, R.stream));
-      }
-      k_post_ready<<<1, 1, 0, R.stream>>>(comm->peer_ready[0], comm->peer_ready[1]);
-      count_launch();
-      comm->tgt_ready += 1u;
-      if (comm->lo >= 0) stream_wait_geq(R.stream, comm->mbox + 2, comm->tgt_ready);
-      if (comm->hi >= 0) stream_wait_geq(R.stream, comm->mbox + 3, comm->tgt_ready);
-    }
-    auto wait_edges = [&]() {   // the neighbours' edge planes of every sweep enqueued so far have landed in our inbox
-      if (exp_nocomm) return;
-      if (comm->lo >= 0) stream_wait_geq(R.stream, comm->mbox + 0, comm->tgt[0]);
-      if (comm->hi >= 0) stream_wait_geq(R.stream, comm->mbox + 1, comm->tgt[1]);
-    };
-    auto body_p2p = [&](int it) {
-      REAL* src = (it & 1) ? X : W;
-      REAL* dst = (it & 1) ? W : X;
-      Launch L = launch();
-      const int slot = converge_check ? ((it & 1) ? 0 : 6) : rs;
-      const bool zs = !converge_check && it == 1 && pre_zero_src;
-      if (it >= 2) wait_edges();
-      if (converge_check && it >= 3) CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_fin[(it - 2) & 1], 0));
-      Rb2Sig sg;
-      sg.sig_lo = comm->peer_mbox[0]; sg.sig_hi = comm->peer_mbox[1]; sg.p2p = 1;
-      sg.inbox = comm->inbox; sg.in_slot = (it - 1) & 1; sg.has_lo = comm->lo >= 0; sg.has_hi = comm->hi >= 0;
-      sg.peer_lo = comm->peer_inbox[0]; sg.peer_hi = comm->peer_inbox[1]; sg.out_slot = it & 1;
-      static const bool exp_nopeer = getenv("CZB_EXP_NOPEERSTORE") != nullptr;   // timing experiment, results wrong
-      if (exp_nopeer) sg.peer_lo = sg.peer_hi = nullptr;
-      int ctas = 0;
-      must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 0, &sg, &ctas));
-      comm->tgt[0] += (unsigned int)ctas; comm->tgt[1] += (unsigned int)ctas;   // every rank launches the same tile grid
-      if (converge_check) {
-        CZB_CHECK(cudaEventRecord(ev_int, R.stream));
-        CZB_CHECK(cudaStreamWaitEvent(cs, ev_int, 0));
-        if (!exp_noar) comm_allreduce_sum(comm, &d_state->acc[slot], 1, cs);
-        Launch Lc = L; Lc.s = cs;
-        launch_finish_iteration(Lc, d_state, slot, res_normal, eps, d_hist, hist_cap);
-        CZB_CHECK(cudaEventRecord(ev_fin[it & 1], cs));
-        if (it <= 2) launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
-        cs_used = true;
-      }
-    };
+    const bool ovl_local = mr && !no_ovl && rb2_fused_launchable(launch(), G, cf, false, 1) &&
+                           (!rb2_zero_src_supported(G, cf) || rb2_fused_launchable(launch(), G, cf, true, 1));
+    const bool ovl = slab_overlap_begin(ovl_local, 2);          // collective decision, opens the edge stream
     auto body_ovl = [&](int it) {
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
-      Launch L = launch();
-      const int slot = converge_check ? ((it & 1) ? 0 : 6) : rs;
+      const int sa = converge_check ? ((it & 1) ? 0 : 5) : rs, sb = converge_check ? sa + 1 : rs;
       const bool zs = !converge_check && it == 1 && pre_zero_src;
-      if (it >= 2) CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_halo[(it - 1) & 1], 0));   // halo planes of src
-      if (converge_check && it >= 3) CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_fin[(it - 2) & 1], 0));
-      if (use_sig) {
-        // one launch; the communication stream is released by the kernel's edge counters
-        int ctas = 0;
-        Rb2Sig sg{};
-        sg.sig_lo = d_sig; sg.sig_hi = d_sig + 1;
-        must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 0, &sg, &ctas));
-        sig_target += (unsigned int)ctas;
-        stream_wait_geq(cs, d_sig, sig_target);
-        stream_wait_geq(cs, d_sig + 1, sig_target);
-        if (!exp_nocomm) comm_halo(comm, dst, G, 2, cs);
-        CZB_CHECK(cudaEventRecord(ev_halo[it & 1], cs));
-      } else {
-        must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, false, zs, 1));
-        CZB_CHECK(cudaEventRecord(ev_edge, R.stream));
-        CZB_CHECK(cudaStreamWaitEvent(cs, ev_edge, 0));
-        comm_halo(comm, dst, G, 2, cs);
-        CZB_CHECK(cudaEventRecord(ev_halo[it & 1], cs));
-        must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, slot, true, zs, 2));
+      Launch LE, LM;
+      slab_overlap_edges_begin(it, src, 2, converge_check, LE, LM);
+      {
+        Phase ph("SOR2SMA_kernel", 18.0 * G.cells());
+        must(launch_rb2_fused(LE, G, src, dst, B, cf, ac1, ip, jr0, jr1, sa, false, zs, 1));
       }
-      if (converge_check) {
-        CZB_CHECK(cudaEventRecord(ev_int, R.stream));
-        CZB_CHECK(cudaStreamWaitEvent(cs, ev_int, 0));
-        if (!exp_noar) comm_allreduce_sum(comm, &d_state->acc[slot], 1, cs);
-        Launch Lc = L; Lc.s = cs;
-        launch_finish_iteration(Lc, d_state, slot, res_normal, eps, d_hist, hist_cap);
-        CZB_CHECK(cudaEventRecord(ev_fin[it & 1], cs));
-        if (it <= 2) {   // bc_k after the exchange, as in the plain loop below
-          CZB_CHECK(cudaStreamWaitEvent(R.stream, ev_halo[it & 1], 0));
-          launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
-        }
+      slab_overlap_edges_end(it, dst, 2, converge_check && it <= 2);
+      must(launch_rb2_fused(LM, G, src, dst, B, cf, ac1, ip, jr0, jr1, sb, false, zs, 2));
+      if (converge_check && it <= 2) {   // bc_k after both launches, before the edge planes leave (see SlabOverlap)
+        CZB_CHECK(cudaStreamWaitEvent(R.stream, ov.ev_a[it & 1], 0));
+        phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
       }
-      cs_used = true;
+      slab_overlap_iteration_end(it, dst, 2, converge_check, sa, sb);
     };
     auto body = [&](int it) {
-      if (p2p) { body_p2p(it); return; }
       if (ovl) { body_ovl(it); return; }
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
       Launch L = launch();
-      const bool fold = converge_check && !(comm && comm->nranks > 1);   // convergence test inside the sweep (FinishSpec)
+      const bool fold = converge_check && !mr;   // convergence test inside the sweep (FinishSpec)
       if (fold) L.fin = FinishSpec{1, res_normal, eps, d_hist, hist_cap};
-      static const bool force_sig = getenv("CZB_EXP_FORCE_SIG") != nullptr;   // timing experiment: the slab instantiation on one rank
-      Rb2Sig sg{};
-      if (force_sig) { ensure_comm_stream(); sg.sig_lo = d_sig; sg.sig_hi = d_sig + 1; }
-      // first preconditioner sweep: xx is all zero by contract (cz_Poisson.cpp:405,441) and is not read
-      must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, rs, false, !converge_check && it == 1 && pre_zero_src, 0,
-                            force_sig ? &sg : nullptr));
+      {
+        Phase ph("SOR2SMA_kernel", 18.0 * G.cells());   // cz_Poisson.cpp:203-210 (both colours)
+        // first preconditioner sweep: xx is all zero by contract (cz_Poisson.cpp:405,441) and is not read
+        must(launch_rb2_fused(L, G, src, dst, B, cf, ac1, ip, jr0, jr1, rs, false, !converge_check && it == 1 && pre_zero_src));
+      }
       Comm_S(dst, 2);
       if (converge_check) {
         Comm_SUM(0);
@@ -516,38 +550,32 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
         // bc_k (cz_Poisson.cpp:226) is idempotent: the sweep never changes a boundary node and carries
         // the boundary nodes it stores over from src, so once both ping-pong buffers have received the
         // Dirichlet values (iterations 1 and 2) every later call would rewrite identical data.
-        if (it <= 2) launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+        if (it <= 2) phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
     else { for (int it = 1; it <= itr_max; ++it) body(it); join_comm_stream(); itr = itr_max + 1; done_iters = itr_max; }
     if (done_iters & 1) {
       launch_copy_inner(launch(false), G, X, W);
-      if (converge_check) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
-      if (!p2p) Comm_S(X, 2);   // the last exchange filled WRK's guard planes
+      if (converge_check) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
     }
-    if (p2p) {
-      // Quiesce the ring: the neighbours' last edge planes have arrived (and, by the same signal, they have read
-      // everything we sent), then give X the halo of its final state, as a Comm_S(X, 2) would have.
-      wait_edges();
-      if (done_iters >= 1) {
-        const int sl = done_iters & 1;
-        if (comm->lo >= 0) CZB_CHECK(cudaMemcpyAsync(glo, comm->inbox + (size_t)(sl * 4 + 0) * G.plane, sizeof(REAL) * pl2, cudaMemcpyDeviceToDevice, R.stream));
-        if (comm->hi >= 0) CZB_CHECK(cudaMemcpyAsync(ghi, comm->inbox + (size_t)(sl * 4 + 2) * G.plane, sizeof(REAL) * pl2, cudaMemcpyDeviceToDevice, R.stream));
-      }
-    }
+    if (ovl) slab_overlap_finish(X, 2, done_iters);          // X leaves with the halo of its final state
+    else if (done_iters & 1) Comm_S(X, 2);                   // the last exchange filled WRK's guard planes
   } else {
     auto body = [&](int it) {
       Launch L = launch();
       for (int color = 0; color < 2; ++color) {
-        if (maf) launch_rb_color_maf(L, G, X, B, axes(), ac1, ip + color, rs, color == 1);   // cz_Poisson.cpp:190-200
-        else     launch_rb_color(L, G, X, B, cf, ac1, ip + color, rs, color == 1);
+        {
+          Phase ph(maf ? "SOR2SMA_MAF_kernel" : "SOR2SMA_kernel", (maf ? 33.0 : 9.0) * G.cells());
+          if (maf) launch_rb_color_maf(L, G, X, B, axes(), ac1, ip + color, rs, color == 1);   // cz_Poisson.cpp:190-200
+          else     launch_rb_color(L, G, X, B, cf, ac1, ip + color, rs, color == 1);
+        }
         Comm_S(X, 1);
       }
       if (converge_check) {
         Comm_SUM(0);
         launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-        if (it <= 1) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+        if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
@@ -596,14 +624,17 @@ int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flo
     Launch L = launch();
     for (int color = 0; color < 2; ++color) {
       // MAF (cz_Poisson.cpp:559-570, 684-695): line-dependent coefficients, 2x2 last stage in both variants
-      if (maf) launch_pcr_lines_maf(L, G, pn, color ^ ofs, 0, axes(), X, M, B, ac1, rs, color == 1);
-      else     launch_pcr_lines(L, G, T, color, ofs, 0, X, X, M, B, ac1, rs, color == 1, true);
+      {
+        Phase ph(maf ? "PCR_RB_MAF" : "PCR_RB", 0.5 * (maf ? pcr_maf_iter_flop(G, pn, 11.0) : pcr_iter_flop(G, pn, last4, 78.0)));
+        if (maf) launch_pcr_lines_maf(L, G, pn, color ^ ofs, 0, axes(), X, M, B, ac1, rs, color == 1);
+        else     launch_pcr_lines(L, G, T, color, ofs, 0, X, X, M, B, ac1, rs, color == 1, true);
+      }
       Comm_S(X, 1);
     }
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -627,16 +658,19 @@ int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, 
   auto body = [&](int it) {
     Launch L = launch();
     bool first = true;
-    for (int d = G.ist + G.jst; d <= G.ied + G.jed; ++d) {
-      if (maf) launch_pcr_lines_maf(L, G, pn, 3, d, axes(), X, M, B, ac1, rs, !first);   // cz_Poisson.cpp:775-782, 858-865, 963-971
-      else     launch_pcr_lines(L, G, T, 3, 0, d, X, X, M, B, ac1, rs, !first, true);
-      first = false;
+    {
+      Phase ph(maf ? "PCR_MAF" : "PCR", maf ? pcr_maf_iter_flop(G, pn, last4 ? 11.0 : 9.0) : pcr_iter_flop(G, pn, last4, 74.0));
+      for (int d = G.ist + G.jst; d <= G.ied + G.jed; ++d) {
+        if (maf) launch_pcr_lines_maf(L, G, pn, 3, d, axes(), X, M, B, ac1, rs, !first);   // cz_Poisson.cpp:775-782, 858-865, 963-971
+        else     launch_pcr_lines(L, G, T, 3, 0, d, X, X, M, B, ac1, rs, !first, true);
+        first = false;
+      }
     }
     Comm_S(X, 1);
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -665,17 +699,17 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
       Launch L = launch();
-      launch_pcr_lines(L, G, pcr2, 2, 0, 0, src, dst, M, B, ac1, rs, false, true);
+      { Phase ph("PCR_J", pcr_iter_flop(G, pn, false, 0.0)); launch_pcr_lines(L, G, pcr2, 2, 0, 0, src, dst, M, B, ac1, rs, false, true); }
       Comm_S(dst, 1);
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 2) launch_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+      if (it <= 2) phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
     };
     itr = run_checked(itr_max, res, body);
     done_iters = h_state[0].itr;
     if (done_iters & 1) {
       launch_copy_inner(launch(false), G, X, W);
-      launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
+      phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
       Comm_S(X, 1);   // the last exchange filled WRK's guard planes
     }
   } else {
@@ -733,11 +767,15 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
   begin_loop(ItrMax);
   {
     Launch L = launch();
-    CZB_CHECK(cudaMemsetAsync(q, 0, bytes, R.stream));                       // :344
-    if (maf_op) launch_calc_rk_maf(L, G, r, X, B, MA, PV);                   // :352
-    else        launch_calc_rk(L, G, r, X, B, cf);                           // :356
+    const double nc = G.cells();
+    { Phase ph("Blas_Clear"); CZB_CHECK(cudaMemsetAsync(q, 0, bytes, R.stream)); }   // :344
+    {
+      Phase ph("Blas_Residual", (maf_op ? 63.0 : 14.0) * nc);
+      if (maf_op) launch_calc_rk_maf(L, G, r, X, B, MA, PV);                 // :352
+      else        launch_calc_rk(L, G, r, X, B, cf);                         // :356
+    }
     Comm_S(r, 1);                                                            // :362
-    CZB_CHECK(cudaMemcpyAsync(r0, r, bytes, cudaMemcpyDeviceToDevice, R.stream));   // :365
+    { Phase ph("Blas_Copy"); CZB_CHECK(cudaMemcpyAsync(r0, r, bytes, cudaMemcpyDeviceToDevice, R.stream)); }   // :365
     k_bicg_scalar<<<1, 1, 0, R.stream>>>(d_state, -1, res_normal, eps, d_hist, hist_cap);
     count_launch();
   }
@@ -747,24 +785,34 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
   };
   auto body = [&](int itr) {
     Launch L = launch();
-    if (itr == 1 || variant != 0) launch_dot2(L, G, r, r0, 0);              // rho :376-383 (later: fused into the tail)
+    const double nc = G.cells(), f_axp = maf_op ? 63.0 : 13.0;
+    // The sections carry the reference's labels (cz_Poisson.cpp:376-477).  Where this library fuses several of the
+    // reference's passes into one kernel the time is booked under the FIRST of them and the flop of all of them:
+    // Blas_AX includes its dot products (Dot2 / Dot1), Blas_BiCG_2 includes the following TRIAD, Dot1 and Dot2.
+    if (itr == 1 || variant != 0) { Phase ph("Dot2", 2.0 * nc); launch_dot2(L, G, r, r0, 0); }   // rho :376-383 (later: fused into the tail)
     Comm_SUM(0); scalar(0);
     if (itr == 1) {
+      Phase ph("Blas_Copy");
       CZB_CHECK(cudaMemcpyAsync(p, r, bytes, cudaMemcpyDeviceToDevice, R.stream));   // :388
     } else {
+      Phase ph("Blas_BiCG_1", 4.0 * nc);
       launch_bicg1(L, G, p, r, q, 0, 0, &sc[SC_BETA], &sc[SC_OMEGA]);        // :397
     }
     Comm_S(p, 1);                                                            // :402
-    if (!zs) CZB_CHECK(cudaMemsetAsync(p_, 0, bytes, R.stream));             // :405 (zs: first sweep does not read p_)
+    if (!zs) { Phase ph("Blas_Clear"); CZB_CHECK(cudaMemsetAsync(p_, 0, bytes, R.stream)); }   // :405 (zs: first sweep does not read p_)
     pre_zero_src = zs; Preconditioner(p_, p, pflop, pc_type); pre_zero_src = false;   // :409
-    if (maf_op) launch_calc_ax_maf(L, G, q, p_, MA, PV, r0, 1);              // :417
-    else if (!(variant == 0 && launch_ax_fused(L, G, q, p_, cf, r0, 1))) launch_calc_ax(L, G, q, p_, cf, r0, 1);
+    {
+      Phase ph("Blas_AX", (f_axp + 2.0) * nc);
+      if (maf_op) launch_calc_ax_maf(L, G, q, p_, MA, PV, r0, 1);            // :417
+      else if (!(variant == 0 && launch_ax_fused(L, G, q, p_, cf, r0, 1))) launch_calc_ax(L, G, q, p_, cf, r0, 1);
+    }
     Comm_SUM(1); scalar(1);          // q = A p_, alpha :421-431
-    launch_triad(L, G, s, q, r, 0, &sc[SC_NEG_ALPHA]);                       // s = r - alpha q :434
+    { Phase ph("Blas_TRIAD", 2.0 * nc); launch_triad(L, G, s, q, r, 0, &sc[SC_NEG_ALPHA]); }   // s = r - alpha q :434
     Comm_S(s, 1);                                                            // :438
-    if (!zs) CZB_CHECK(cudaMemsetAsync(s_, 0, bytes, R.stream));             // :441
+    if (!zs) { Phase ph("Blas_Clear"); CZB_CHECK(cudaMemsetAsync(s_, 0, bytes, R.stream)); }   // :441
     pre_zero_src = zs; Preconditioner(s_, s, pflop, pc_type); pre_zero_src = false;   // :445
     {   // t = A s_, (t,s), (t,t) :457-464
+      Phase ph("Blas_AX", (f_axp + 4.0) * nc);
       const int f = (variant == 0 && !maf_op) ? launch_ax_fused(L, G, t_, s_, cf, s, 2, 3) : 0;
       if (maf_op) launch_calc_ax_maf(L, G, t_, s_, MA, PV, s, 2);            // :453
       else if (f == 0) launch_calc_ax(L, G, t_, s_, cf, s, 2);
@@ -772,15 +820,16 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
     }
     Comm_SUM(2, 2); scalar(2);                                               // omega
     if (variant == 0) {   // x += alpha p_ + omega s_ :470, r = s - omega t :476, (r,r) :481, (r,r0) :376 in one pass
+      Phase ph("Blas_BiCG_2", (4.0 + 2.0 + 2.0 + 2.0) * nc);
       launch_bicg_tail(L, G, X, p_, s_, r, t_, s, r0, &sc[SC_ALPHA], &sc[SC_OMEGA], &sc[SC_NEG_OMEGA], 4, 0);
     } else {
-      launch_bicg2(L, G, X, p_, s_, 0, 0, &sc[SC_ALPHA], &sc[SC_OMEGA]);
-      launch_triad(L, G, r, t_, s, 0, &sc[SC_NEG_OMEGA]);
-      launch_dot1(L, G, r, 4);
+      { Phase ph("Blas_BiCG_2", 4.0 * nc); launch_bicg2(L, G, X, p_, s_, 0, 0, &sc[SC_ALPHA], &sc[SC_OMEGA]); }
+      { Phase ph("Blas_TRIAD", 2.0 * nc); launch_triad(L, G, r, t_, s, 0, &sc[SC_NEG_OMEGA]); }
+      { Phase ph("Dot1", 2.0 * nc); launch_dot1(L, G, r, 4); }
     }
     Comm_S(X, 1); Comm_SUM(4);                                               // :486-488
     scalar(3);                                                               // :490-500
-    launch_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);                                // :495
+    phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);                                // :495
   };
   // for (itr=1; itr<ItrMax; itr++)  (cz_Poisson.cpp:373)
   const int n_it = ItrMax - 1;
@@ -838,7 +887,8 @@ czb_ctx* czb_ctx_create(const int sz[3], const int idx[6], const int nID[6], CZB
   c->res_normal = 1.0 / c->G.cells();
   c->wrk_guards_zero = false;
   c->maf = false; c->mesh_user = false; c->xc = c->yc = c->zc = c->pvt = nullptr;
-  c->pre_zero_src = false; c->cs = nullptr; c->cs_used = false; c->d_sig = nullptr; c->sig_target = 0;
+  c->pre_zero_src = false; c->cs = nullptr; c->cs_used = false;
+  memset((void*)&c->ov, 0, sizeof(c->ov));
   CZB_CHECK(cudaMalloc(&c->d_state, sizeof(LoopState)));
   CZB_CHECK(cudaMemset(c->d_state, 0, sizeof(LoopState)));
   CZB_CHECK(cudaMallocHost(&c->h_state, sizeof(LoopState) * 4));
@@ -860,10 +910,12 @@ void czb_ctx_destroy(czb_ctx* c) {
   cudaEventDestroy(c->ev[0]); cudaEventDestroy(c->ev[1]); cudaEventDestroy(c->ev_t0); cudaEventDestroy(c->ev_t1);
   if (c->cs) {
     cudaStreamSynchronize(c->cs);
-    cudaEvent_t evs[] = {c->ev_edge, c->ev_int, c->ev_halo[0], c->ev_halo[1], c->ev_fin[0], c->ev_fin[1], c->ev_join};
+    cudaStreamSynchronize(c->ov.es);
+    cudaEvent_t evs[] = {c->ev_fin[0], c->ev_fin[1], c->ev_join, c->ov.ev_a[0], c->ov.ev_a[1], c->ov.ev_b[0], c->ov.ev_b[1],
+                         c->ov.ev_start, c->ov.ev_join_e};
     for (cudaEvent_t e : evs) cudaEventDestroy(e);
-    cudaStreamDestroy(c->cs);
-    cudaFree(c->d_sig);
+    cudaStreamDestroy(c->cs); cudaStreamDestroy(c->ov.es);
+    cudaFree(c->ov.rb_edge.partial); cudaFree(c->ov.rb_edge.ticket);
   }
   comm_destroy(c->comm);
   delete c;

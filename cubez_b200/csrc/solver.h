@@ -52,10 +52,17 @@ struct czb_ctx {
   cudaEvent_t ev[2], ev_t0, ev_t1;
   double last_ms;
   // multi-rank overlap (RBSOR): halo exchange / residual all-reduce run on a second, high-priority stream
-  cudaStream_t cs; cudaEvent_t ev_edge, ev_int, ev_halo[2], ev_fin[2], ev_join;
+  cudaStream_t cs; cudaEvent_t ev_fin[2], ev_join;
   bool cs_used;
-  unsigned int* d_sig;         // edge-plane completion counters {low, high} of the two-colour kernel
-  unsigned int sig_target;     // value both counters reach when the launches enqueued so far are done
+  // multi-rank overlap of ping-pong sweeps (see slab_overlap_* below)
+  struct SlabOverlap {
+    cudaStream_t es;             // edge stream (high priority): first + last j-chunk of a sweep, then the halo traffic
+    czb::RedBuf rb_edge;         // reduction scratch of the edge launch (it runs next to the interior launch)
+    cudaEvent_t ev_a[2], ev_b[2], ev_start, ev_join_e;   // edge / interior launch of iteration parity done
+    bool decided, all_ok;        // every rank can split its sweeps (decided once, collectively)
+    bool p2p;                    // halo planes travel through NVLink peer memory (comm.h), else NCCL send/recv
+    bool deferred;               // this iteration's exchange waits for the interior launch (bc_k in between)
+  } ov;
   int hist_len_req;
 
   // ---- helpers ----
@@ -84,6 +91,15 @@ struct czb_ctx {
   template <class Body> int run_checked(int itr_max, double& res, Body body);
   void ensure_comm_stream();
   void join_comm_stream();                        // the solve stream waits for everything queued on cs
+  // ---- SlabOverlap: a ping-pong sweep of a j-slab as two launches of the single-GPU kernel -----------------------
+  // edge chunks (part 1) on ov.es, then the `w` outermost planes of dst go to the neighbours (peer DMA or NCCL) while
+  // the interior chunks (part 2) run on the solve stream; the residual all-reduce + convergence test run on cs.
+  bool slab_overlap_begin(bool local_ok, int w);                       // collective; false = use the plain loop
+  void slab_overlap_edges_begin(int it, REAL* src, int w, bool converge_check, czb::Launch& LE, czb::Launch& LM);
+  void slab_overlap_edges_end(int it, REAL* dst, int w, bool defer_exchange);
+  void slab_overlap_iteration_end(int it, REAL* dst, int w, bool converge_check, int slot_a, int slot_b);
+  void slab_overlap_finish(REAL* X, int w, int done_iters);
+  void slab_exchange(REAL* dst, int w, int it);
   void begin_loop(int itr_max);
   int end_loop(int itr_max, double& res, bool bicg);
 };

@@ -152,6 +152,13 @@ void czb_memcpy_h2d(void* dst, const void* src, size_t bytes);   /* synchronous 
 void czb_memcpy_d2h(void* dst, const void* src, size_t bytes);
 long long czb_launch_count(void);         /* kernels launched by this library so far */
 void czb_staged_bytes(double* h2d, double* d2h);   /* bytes staged for host-pointer arguments */
+/* Per-phase report, the counterpart of the reference's PMlib profiling.txt (cz_Evaluate.cpp:506-544): device time,
+ * calls and the reference's analytic flop counts per section, keyed by the reference's labels (cz_miscel.cpp:177-262:
+ * JACOBI_kernel, SOR2SMA_kernel, PCR_RB, Blas_AX, BoundaryCondition, Comm_Poisson ...).  czb_profile(1) resets and
+ * enables it (CZB_PROFILE=1 does so at start-up), czb_profile_report writes the table to `path` (NULL = stdout) and
+ * returns the number of sections. */
+void czb_profile(int on);
+int czb_profile_report(const char* path, const char* title);
 
 /* Slab decomposition along j (the slowest axis), SURVEY.md §8(e).  Pure host logic. ------ */
 /* For global size gsz[3] and `nranks` slabs: local size, 1-based head index, neighbour table

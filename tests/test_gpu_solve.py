@@ -188,3 +188,33 @@ def test_line_sor_long_lines(sz, solver, coef):
     assert np.array_equal(got, X), "field differs from the oracle (max %g)" % np.abs(got - X).max()
     np.testing.assert_allclose(out["history"], hist, rtol=1e-12)
     cz.close()
+
+
+def test_phase_profile_report(tmp_path):
+    """per-phase report keyed by the reference's PMlib labels (cz_miscel.cpp:177-262), the counterpart
+    of its profiling.txt (cz_Evaluate.cpp:506-544)."""
+    import cubez_b200
+    cz = cubez_b200.CZ([64] * 3, "f32")
+    cz.dll.czb_profile(1)
+    P, RHS = cz.setup_laplace()
+    out = cz.solve("pbicgstab", P, RHS, 50, 1.1, "sor2sma")
+    path = str(tmp_path / "profiling.txt")
+    n = cz.dll.czb_profile_report(path.encode(), b"test")
+    cz.dll.czb_profile(0)
+    cz.close()
+    txt = open(path).read()
+    assert n >= 6
+    for label in ("SOR2SMA_kernel", "Blas_AX", "Blas_BiCG_2", "Blas_TRIAD", "BoundaryCondition", "Blas_Residual"):
+        assert label in txt, txt
+    rows = {l.split()[0]: l.split() for l in txt.splitlines() if l and not l.startswith("#") and not l.startswith("Section")}
+    its = out["itr"]
+    # lc_max = 8 sweeps, twice per iteration (cz_Poisson.cpp:280,409,445); iterations are enqueued in batches of 4, the
+    # ones after convergence are no-ops on the device but still counted here
+    assert int(rows["SOR2SMA_kernel"][1]) >= 16 * its and int(rows["SOR2SMA_kernel"][1]) % 16 == 0
+    assert int(rows["Blas_AX"][1]) * 8 == int(rows["SOR2SMA_kernel"][1])
+    assert float(rows["SOR2SMA_kernel"][2]) > 0.0
+    # the driver writes the same table when CZB_PROFILE=1
+    exe = os.path.join(ou.ROOT, "cubez_b200", "cz_f32")
+    p = subprocess.run([exe, "64", "64", "64", "sor2sma", "4000", "1.9"], cwd=str(tmp_path), capture_output=True, text=True,
+                       timeout=600, env=dict(os.environ, CZB_PROFILE="1"))
+    assert p.returncode == 0 and "SOR2SMA_kernel" in open(str(tmp_path / "profiling.txt")).read()

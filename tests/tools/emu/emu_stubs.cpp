@@ -8,10 +8,10 @@
 namespace czb {
 bool fused_eligible(const Geo&) { return false; }
 bool launch_rb2_fused(const Launch&, const Geo&, const REAL*, REAL*, const REAL*, const REAL*, REAL, int, int, int, int, bool,
-                      bool, int, const Rb2Sig*, int*) { return false; }
+                      bool, int) { return false; }
 bool rb2_zero_src_supported(const Geo&, const REAL*) { return false; }
-bool rb2_fused_launchable(const Launch&, const Geo&, const REAL*, bool, int, bool, bool) { return false; }
-bool rb2_parts_supported(const Geo&, const REAL*) { return false; }
-bool launch_jacobi_fused(const Launch&, const Geo&, const REAL*, REAL*, const REAL*, const REAL*, REAL, int, bool) { return false; }
-int launch_ax_fused(const Launch&, const Geo&, REAL*, const REAL*, const REAL*, const REAL*, int, int) { return 0; }
+bool rb2_fused_launchable(const Launch&, const Geo&, const REAL*, bool, int) { return false; }
+bool jacobi_fused_launchable(const Launch&, const Geo&, const REAL*, int) { return false; }
+bool launch_jacobi_fused(const Launch&, const Geo&, const REAL*, REAL*, const REAL*, const REAL*, REAL, int, bool, int) { return false; }
+int launch_ax_fused(const Launch&, const Geo&, REAL*, const REAL*, const REAL*, const REAL*, int, int, int) { return 0; }
 }  // namespace czb
