@@ -700,17 +700,29 @@ int march(int mode, const Launch& L, const Geo& G, const REAL* p, const REAL* b_
   const int jlo = G.jst, jhi = G.jed;
   const int ni = G.ied - G.ist + 1, nj = jhi - jlo + 1;
   a.nti = lin ? (ni + a.ei - 3) / (a.ei - 2) : (ni + a.ei - 5) / (a.ei - 4);
-  // j-chunks: enough CTAs for ~8 rounds over the SMs, chunks no shorter than 32 planes (measured flat between 4 and
-  // 16 rounds at 512^3)
-  static int rounds = -1;
-  if (rounds < 0) { const char* e = getenv("CZB_ROUNDS"); rounds = e ? atoi(e) : 8; }
-  int njc = (148 * rounds + a.ntk * a.nti - 1) / (a.ntk * a.nti);
-  if (njc > (nj + 31) / 32) njc = (nj + 31) / 32;
-  // small grids: fewer tiles than SMs even with 32-plane chunks -> shorter chunks (>= 8 planes) until every SM has one
-  static const bool no_small = getenv("CZB_NO_SMALL") != nullptr;
-  if (!no_small && a.ntk * a.nti * njc < 148) {
-    njc = (148 + a.ntk * a.nti - 1) / (a.ntk * a.nti);
-    if (njc > (nj + 7) / 8) njc = (nj + 7) / 8;
+  // j-chunks.  Every CTA marches one chunk of jl planes and pays a fixed price per chunk: the pipeline fill (3 extra
+  // steps for the two-colour sweep, 0 for the one-plane kernels) plus ~6 steps' worth of start-up (barrier set-up, first
+  // TMA round trip, reduction epilogue).  With R = tiles * njc / 148 rounds over the SMs the launch takes about
+  //     (R <= 1 ? 1 : R + 0.5) * (jl + fill + 6)   steps
+  // (one round exactly while every CTA is resident at once; beyond that the hardware scheduler evens the tail out to
+  // about half a round).  The chunk count that minimises it is chosen, >= 8 planes per chunk; a j-slab that splits
+  // its sweep into an edge and an interior launch (part != 0) needs at least three chunks.  Measured on B200
+  // (profiles/r02_chunks.md): 1024^3 -> 4-5 chunks, 512^3 -> 6, 256^3 -> 4, a 128-plane slab of an 8-GPU run -> 3.
+  int njc = 1;
+  {
+    const long long tiles = (long long)a.ntk * a.nti;
+    const int fill = (mode == MODE_RB2) ? 3 : 0;
+    double best = -1.0;
+    const int nmax = nj / 8 > 1 ? (nj / 8 < 256 ? nj / 8 : 256) : 1;
+    const int nmin = (part != 0 && nmax >= 3) ? 3 : 1;
+    for (int c = nmin; c <= nmax; ++c) {
+      const int jl = (nj + c - 1) / c;
+      const int cc = (nj + jl - 1) / jl;                       // chunks really needed with this length
+      if (cc < nmin) continue;
+      const double r = (double)(tiles * cc) / 148.0;
+      const double cost = (r <= 1.0 ? 1.0 : r + 0.5) * (double)(jl + fill + 6);
+      if (best < 0.0 || cost < best) { best = cost; njc = cc; }
+    }
   }
   { static const char* e = getenv("CZB_NJC"); if (e) njc = atoi(e); }   // experiments
   if (njc < 1) njc = 1;

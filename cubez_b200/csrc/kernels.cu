@@ -307,6 +307,25 @@ __global__ void __launch_bounds__(256) k_err(Geo G, int jlen, const REAL* __rest
   }
 }
 
+// dst <- src on every cell that is NOT an inner cell (guard cells, boundary nodes): what the second buffer of a
+// ping-pong loop must share with the first before the first sweep (the sweeps store every inner cell and carry the
+// other cells of the units they store over from their source).  One block row per (plane, rows), threads along k.
+__global__ void __launch_bounds__(128) k_copy_shell(Geo G, REAL* __restrict__ dst, const REAL* __restrict__ src) {
+  const int jc = blockIdx.y, jF = jc - G.g + 1;
+  const bool whole = jF < G.jst || jF > G.jed;
+  const int klo = G.kst + G.g - 1, khi = G.ked + G.g - 1;      // first / last inner C index along k
+  for (int ic = blockIdx.x; ic < G.ni; ic += gridDim.x) {
+    const int iF = ic - G.g + 1;
+    const long long row = (long long)jc * G.plane + (long long)ic * G.nk;
+    if (whole || iF < G.ist || iF > G.ied) {
+      for (int k = threadIdx.x; k < G.nk; k += blockDim.x) dst[row + k] = src[row + k];
+    } else {
+      for (int k = threadIdx.x; k < klo; k += blockDim.x) dst[row + k] = src[row + k];
+      for (int k = khi + 1 + threadIdx.x; k < G.nk; k += blockDim.x) dst[row + k] = src[row + k];
+    }
+  }
+}
+
 __global__ void k_state_reset(LoopState* st) {
   st->done = 0; st->itr = 0; st->status = 0; st->pad = 0; st->res = 0.0;
   for (int a = 0; a < 8; ++a) { st->acc[a] = 0.0; st->scal[a] = 0.0; }
@@ -472,6 +491,12 @@ void launch_psor_sweep(const Launch& L, const Geo& G, REAL* p, const REAL* b, co
     count_launch();
   }
   CZB_CHECK(cudaGetLastError());
+}
+
+void launch_copy_shell(const Launch& L, const Geo& G, REAL* dst, const REAL* src) {
+  k_copy_shell<<<dim3(32, G.nj, 1), 128, 0, L.s>>>(G, dst, src);
+  CZB_CHECK(cudaGetLastError());
+  count_launch();
 }
 
 void launch_state_reset(const Launch& L, LoopState* st) {

@@ -35,6 +35,8 @@ void launch_psor_sweep(const Launch& L, const Geo& G, REAL* p, const REAL* b, co
                        int slot, bool add);
 // copy inner cells src -> dst (jacobi copy-back cz_solver.f90:369-375, pcr_j_esa :1659-1665)
 void launch_copy_inner(const Launch& L, const Geo& G, REAL* dst, const REAL* src);
+// copy every cell that is NOT an inner cell (guards + boundary nodes): the shell a ping-pong partner must share
+void launch_copy_shell(const Launch& L, const Geo& G, REAL* dst, const REAL* src);
 
 // ---- BLAS-1 / operator (cz_blas.f90) --------------------------------------------------
 void launch_calc_ax(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf,

@@ -372,7 +372,7 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
   Runtime& R = rt();
   REAL* W = field(WRK);
   if (converge_check) {
-    CZB_CHECK(cudaMemcpyAsync(W, X, sizeof(REAL) * field_elems(), cudaMemcpyDeviceToDevice, R.stream));
+    launch_copy_shell(launch(false), G, W, X);   // WRK only needs X's guard cells and boundary nodes: every inner cell is stored by sweep 1
     wrk_guards_zero = false;
   } else if (!wrk_guards_zero) {   // preconditioner call: xx is all-zero outside the inner cells
     CZB_CHECK(cudaMemsetAsync(W, 0, sizeof(REAL) * field_elems(), R.stream));
@@ -494,7 +494,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     const bool mr = comm && comm->nranks > 1;
     if (converge_check) {
       Comm_S(X, 2);
-      CZB_CHECK(cudaMemcpyAsync(W, X, sizeof(REAL) * field_elems(), cudaMemcpyDeviceToDevice, R.stream));
+      launch_copy_shell(launch(false), G, W, X);   // WRK only needs X's guard cells and boundary nodes: every inner cell is stored by sweep 1
       wrk_guards_zero = false;
     } else if (!wrk_guards_zero) {
       CZB_CHECK(cudaMemsetAsync(W, 0, sizeof(REAL) * field_elems(), R.stream));
@@ -694,7 +694,7 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
   if (converge_check) {
     // The reference writes the new lines to wrk and copies them back (cz_solver.f90:1632-1665); here X and WRK
     // alternate as source and destination (both hold the same boundary / guard values), as in JACOBI.
-    CZB_CHECK(cudaMemcpyAsync(W, X, sizeof(REAL) * field_elems(), cudaMemcpyDeviceToDevice, rt().stream));
+    launch_copy_shell(launch(false), G, W, X);   // guard cells + boundary nodes; the lines' cells are all stored by the first pass
     auto body = [&](int it) {
       REAL* src = (it & 1) ? X : W;
       REAL* dst = (it & 1) ? W : X;
