@@ -106,6 +106,24 @@ Comm* comm_create(int nranks, int rank, const void* id128, int lo, int hi) {
   return c;
 }
 
+// First use of a NCCL peer connection / of the all-reduce ring costs hundreds of milliseconds (transport set-up);
+// pay it when the communicator is made, not inside the first timed solver loop.
+void comm_warmup(Comm* c, cudaStream_t s) {
+  if (!c || c->nranks <= 1 || !c->nccl) return;
+  NcclApi& A = api();
+  ncclComm_t comm = (ncclComm_t)c->nccl;
+  double* d = nullptr;
+  CZB_CHECK(cudaMalloc((void**)&d, 8 * sizeof(double)));
+  CZB_CHECK(cudaMemsetAsync(d, 0, 8 * sizeof(double), s));
+  CZB_NCCL(A.GroupStart());
+  if (c->lo >= 0) { CZB_NCCL(A.Send(d, 1, ncclFloat64, c->lo, comm, s)); CZB_NCCL(A.Recv(d + 1, 1, ncclFloat64, c->lo, comm, s)); }
+  if (c->hi >= 0) { CZB_NCCL(A.Send(d + 2, 1, ncclFloat64, c->hi, comm, s)); CZB_NCCL(A.Recv(d + 3, 1, ncclFloat64, c->hi, comm, s)); }
+  CZB_NCCL(A.GroupEnd());
+  CZB_NCCL(A.AllReduce(d + 4, d + 4, 1, ncclFloat64, ncclSum, comm, s));
+  CZB_CHECK(cudaStreamSynchronize(s));
+  cudaFree(d);
+}
+
 void comm_destroy(Comm* c) {
   if (!c) return;
   for (int d = 0; d < 2; ++d) if (c->peer_block[d]) cudaIpcCloseMemHandle(c->peer_block[d]);

@@ -41,6 +41,7 @@ struct Comm {
 int comm_unique_id(void* id128);
 Comm* comm_create(int nranks, int rank, const void* id128, int lo, int hi);
 void comm_destroy(Comm* c);
+void comm_warmup(Comm* c, cudaStream_t s);   // one tiny exchange with each neighbour + one all-reduce (connection set-up)
 // Exchange `width` j-planes with both neighbours (guard planes <- neighbour's edge planes).
 void comm_halo(Comm* c, REAL* field, const Geo& G, int width, cudaStream_t s);
 // Set up the peer transport for fields with planes of `plane_elems` REALs: allocate and export the local block,

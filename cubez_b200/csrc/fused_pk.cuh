@@ -284,9 +284,12 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
 
   // One step.  C = u % 4 (which register set holds which plane), XB = the red cells of plane s+1 (and the
   // black cells of plane s-1... of the OTHER position) -- both compile-time, see the unrolled loop below.
-  auto step = [&](int u, auto cc, auto xb) {
+  // RO ("reds only"): the first three steps of a chunk have no black plane yet (s-1 < ja); their instantiation
+  // leaves the black half out instead of computing it under all-zero flags (2 of the 46 steps of a 43-plane chunk).
+  auto step = [&](int u, auto cc, auto xb, auto ro) {
     constexpr int C = decltype(cc)::value;
     constexpr bool XB = decltype(xb)::value;       // position of the reds of plane s+1; blacks of plane s-1 are !XB
+    constexpr bool RO = decltype(ro)::value;
     constexpr int XO = XB ? HPB : 0, YO = XB ? 0 : HPB;
     U4 (&wm1)[CPT] = P[(C + 3) & 3];
     U4 (&w0)[CPT] = P[C];
@@ -325,7 +328,7 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
     // step-uniform activity: reds of plane s+1, blacks of plane s-1
     const bool do_red = (s + 1 >= a.jr0 && s + 1 <= a.jr1);
     const bool red_owned = (s + 1 >= ja && s + 1 <= jb);
-    const bool do_black = (s - 1 >= ja && s - 1 <= jb);
+    const bool do_black = !RO && (s - 1 >= ja && s - 1 <= jb);
     const unsigned fR = do_red ? (XB ? (fl >> 4) : fl) & 0xfu : 0u;                 // bit m*2+e
     const unsigned fRO = (do_red && red_owned) ? (XB ? (fl >> 12) : (fl >> 8)) & 0xfu : 0u;
     const unsigned fK = do_black ? (XB ? (fl >> 8) : (fl >> 12)) & 0xfu : 0u;      // blacks sit at !XB
@@ -338,10 +341,14 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
       jnK[m] = XB ? w0[m].a : w0[m].b;
     }
     numer(xb, e1, w1, jnR, jsR, bbR, numR);
-    numer(std::integral_constant<bool, !XB>{}, em1, wm1, jnK, jsk, hb[C & 1], numK);
+    if constexpr (!RO) numer(std::integral_constant<bool, !XB>{}, em1, wm1, jnK, jsk, hb[C & 1], numK);
+    else {
+#pragma unroll
+      for (int m = 0; m < CPT; ++m) numK[m] = numR[m];     // keeps the range test below one code path
+    }
     F2 quoR[CPT], quoK[CPT];
 #pragma unroll
-    for (int m = 0; m < CPT; ++m) { quoR[m] = div6_2(numR[m]); quoK[m] = div6_2(numK[m]); }
+    for (int m = 0; m < CPT; ++m) { quoR[m] = div6_2(numR[m]); quoK[m] = RO ? quoR[m] : div6_2(numK[m]); }
     {  // numerators outside the verified range of the fast division (tiny, huge, -0, non-finite): rare
       float mx = 0.0f, mn = 3.0e38f;
       unsigned orb = 0u;
@@ -356,9 +363,11 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
         const float4 f = div6_fix4(make_float4(lo(numR[0]), hi(numR[0]), lo(numR[1]), hi(numR[1])),
                                    make_float4(lo(quoR[0]), hi(quoR[0]), lo(quoR[1]), hi(quoR[1])));
         quoR[0] = pk(f.x, f.y); quoR[1] = pk(f.z, f.w);
-        const float4 h = div6_fix4(make_float4(lo(numK[0]), hi(numK[0]), lo(numK[1]), hi(numK[1])),
-                                   make_float4(lo(quoK[0]), hi(quoK[0]), lo(quoK[1]), hi(quoK[1])));
-        quoK[0] = pk(h.x, h.y); quoK[1] = pk(h.z, h.w);
+        if constexpr (!RO) {
+          const float4 h = div6_fix4(make_float4(lo(numK[0]), hi(numK[0]), lo(numK[1]), hi(numK[1])),
+                                     make_float4(lo(quoK[0]), hi(quoK[0]), lo(quoK[1]), hi(quoK[1])));
+          quoK[0] = pk(h.x, h.y); quoK[1] = pk(h.z, h.w);
+        }
       }
     }
     // A cell that must not move gets dp = -0.0: p + (-0) == p bit for bit (also for p = +-0) and
@@ -374,17 +383,19 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
       sts64<XO>(e1 + ad[m], nvR);
       const F2 dkR = sel(bit(fRO, m * 2), dpR, nz2, bit(fRO, m * 2 + 1));
       const F2 d2R = mul2(dkR, dkR);
-      // blacks of plane s-1
-      const F2 ppK = XB ? wm1[m].a : wm1[m].b;
-      const F2 dkK = sel(bit(fK, m * 2), mul2(sub2(quoK[m], ppK), omg2), nz2, bit(fK, m * 2 + 1));
-      const F2 nvK = add2(ppK, dkK);
-      if (XB) wm1[m].a = nvK; else wm1[m].b = nvK;
-      const F2 d2K = mul2(dkK, dkK);
       acc[0] += (double)lo(d2R);
       acc[0] += (double)hi(d2R);
-      acc[0] += (double)lo(d2K);
-      acc[0] += (double)hi(d2K);
-      stg_unit_if(outp[m], wm1[m], (fS >> m) & 1u);
+      if constexpr (!RO) {
+        // blacks of plane s-1
+        const F2 ppK = XB ? wm1[m].a : wm1[m].b;
+        const F2 dkK = sel(bit(fK, m * 2), mul2(sub2(quoK[m], ppK), omg2), nz2, bit(fK, m * 2 + 1));
+        const F2 nvK = add2(ppK, dkK);
+        if (XB) wm1[m].a = nvK; else wm1[m].b = nvK;
+        const F2 d2K = mul2(dkK, dkK);
+        acc[0] += (double)lo(d2K);
+        acc[0] += (double)hi(d2K);
+        stg_unit_if(outp[m], wm1[m], (fS >> m) & 1u);
+      }
       outp[m] += G.plane;
       hb[C & 1][m] = XB ? bc[m].a : bc[m].b;     // right-hand side of the blacks of plane s+1 (used at step u+2)
     }
@@ -401,27 +412,25 @@ k_rb2_pk(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUten
   // so the 4x unrolled body exists in two variants (A-B-A-B and B-A-B-A) chosen once.
   using I0 = std::integral_constant<int, 0>; using I1 = std::integral_constant<int, 1>;
   using I2 = std::integral_constant<int, 2>; using I3 = std::integral_constant<int, 3>;
-  if (((par + (unsigned)(pl0 + 1)) & 1u) == 0u) {
-    for (int u = 0; u < nsteps; u += 4) {
-      step(u, I0{}, std::false_type{});
+  auto run = [&](auto x0) {                       // X0 = position of the reds in step 0
+    constexpr bool X0 = decltype(x0)::value;
+    using TX = std::integral_constant<bool, X0>; using TY = std::integral_constant<bool, !X0>;
+    // nsteps = jl + 3 >= 4: the first three steps relax reds only
+    step(0, I0{}, TX{}, std::true_type{});
+    step(1, I1{}, TY{}, std::true_type{});
+    step(2, I2{}, TX{}, std::true_type{});
+    step(3, I3{}, TY{}, std::false_type{});
+    for (int u = 4; u < nsteps; u += 4) {
+      step(u, I0{}, TX{}, std::false_type{});
       if (u + 1 >= nsteps) break;
-      step(u + 1, I1{}, std::true_type{});
+      step(u + 1, I1{}, TY{}, std::false_type{});
       if (u + 2 >= nsteps) break;
-      step(u + 2, I2{}, std::false_type{});
+      step(u + 2, I2{}, TX{}, std::false_type{});
       if (u + 3 >= nsteps) break;
-      step(u + 3, I3{}, std::true_type{});
+      step(u + 3, I3{}, TY{}, std::false_type{});
     }
-  } else {
-    for (int u = 0; u < nsteps; u += 4) {
-      step(u, I0{}, std::true_type{});
-      if (u + 1 >= nsteps) break;
-      step(u + 1, I1{}, std::false_type{});
-      if (u + 2 >= nsteps) break;
-      step(u + 2, I2{}, std::true_type{});
-      if (u + 3 >= nsteps) break;
-      step(u + 3, I3{}, std::false_type{});
-    }
-  }
+  };
+  if (((par + (unsigned)(pl0 + 1)) & 1u) == 0u) run(std::false_type{}); else run(std::true_type{});
   grid_reduce<1>(acc, a.rb, FinStoreF{a.acc_st, a.slot, a.add, a.fin});
 }
 

@@ -945,6 +945,7 @@ int czb_ctx_comm_init(czb_ctx* c, int nranks, int rank, const void* id128) {
   rt();
   if (c->comm) comm_destroy(c->comm);
   c->comm = comm_create(nranks, rank, id128, c->nID[2], c->nID[3]);
+  comm_warmup(c->comm, rt().stream);
   return 0;
 }
 
