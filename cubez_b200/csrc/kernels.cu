@@ -494,7 +494,8 @@ void launch_psor_sweep(const Launch& L, const Geo& G, REAL* p, const REAL* b, co
 }
 
 void launch_copy_shell(const Launch& L, const Geo& G, REAL* dst, const REAL* src) {
-  k_copy_shell<<<dim3(32, G.nj, 1), 128, 0, L.s>>>(G, dst, src);
+  const dim3 grid(32, G.nj, 1);
+  k_copy_shell<<<grid, 128, 0, L.s>>>(G, dst, src);
   CZB_CHECK(cudaGetLastError());
   count_launch();
 }

@@ -27,7 +27,11 @@ void Runtime::init(int dev) {
   CZB_CHECK(cudaSetDevice(device));
   CZB_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
   own_stream = true;
+#ifdef CZB_EMU_BUILD   // tests/tools/emu: one emulated block per CUDA thread, so grids are blockDim times larger
+  rb_blocks = (size_t)1 << 20;
+#else
   rb_blocks = (size_t)1 << 17;
+#endif
   CZB_CHECK(cudaMalloc(&rb.partial, sizeof(double) * rb_blocks * CZB_MAX_ACC));
   CZB_CHECK(cudaMalloc(&rb.ticket, sizeof(unsigned int)));
   CZB_CHECK(cudaMemset(rb.ticket, 0, sizeof(unsigned int)));

@@ -18,6 +18,7 @@ static dim3 blockDim, gridDim;
 using std::min;
 using std::max;
 
+#define CZB_EMU_BUILD 1
 #define __CUDACC__ 1            // let common.cuh define warp_sum / grid_reduce
 #undef __global__
 #undef __device__
@@ -51,7 +52,7 @@ static inline long long __double_as_longlong(double d) { long long v; memcpy(&v,
 template <class Body>
 static void emu_launch(dim3 g, dim3 b, Body body) {
   const dim3 G(g.x * b.x, g.y * b.y, g.z * b.z);
-  if ((long long)G.x * G.y * G.z > (1LL << 17)) { fprintf(stderr, "emu: grid too large for the reduction scratch\n"); abort(); }
+  if ((long long)G.x * G.y * G.z > (1LL << 20)) { fprintf(stderr, "emu: grid too large for the reduction scratch\n"); abort(); }
   gridDim = G; blockDim = dim3(1, 1, 1);
   threadIdx.x = threadIdx.y = threadIdx.z = 0;
   for (unsigned z = 0; z < G.z; ++z)
