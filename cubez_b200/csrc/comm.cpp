@@ -250,23 +250,28 @@ void comm_p2p_fetch(Comm* c, REAL* lo_guard, REAL* hi_guard, int w, int slot, cu
   if (c->hi >= 0) CZB_CHECK(cudaMemcpyAsync(hi_guard, c->inbox + (size_t)(slot * 4 + 2) * P, bytes, cudaMemcpyDeviceToDevice, s));
 }
 
-void comm_halo(Comm* c, REAL* f, const Geo& G, int w, cudaStream_t s) {
+void comm_halo_n(Comm* c, REAL* const* fields, int nf, const Geo& G, int w, cudaStream_t s) {
   if (!c || c->nranks <= 1 || (c->lo < 0 && c->hi < 0)) return;
   NcclApi& A = api();
   ncclComm_t comm = (ncclComm_t)c->nccl;
   const size_t cnt = (size_t)w * (size_t)G.plane;
   const long long P = G.plane;
-  CZB_NCCL(A.GroupStart());
-  if (c->lo >= 0) {   // my planes 1..w -> lower neighbour's guard; its top planes -> my planes 1-w..0
-    CZB_NCCL(A.Send(f + (long long)G.g * P, cnt, real_type(), c->lo, comm, s));
-    CZB_NCCL(A.Recv(f + (long long)(G.g - w) * P, cnt, real_type(), c->lo, comm, s));
-  }
-  if (c->hi >= 0) {   // my planes jx-w+1..jx -> upper neighbour's guard; its planes 1..w -> my jx+1..jx+w
-    CZB_NCCL(A.Send(f + (long long)(G.jx - w + G.g) * P, cnt, real_type(), c->hi, comm, s));
-    CZB_NCCL(A.Recv(f + (long long)(G.jx + G.g) * P, cnt, real_type(), c->hi, comm, s));
+  CZB_NCCL(A.GroupStart());          // one group = one NCCL launch for all fields and both neighbours
+  for (int q = 0; q < nf; ++q) {
+    REAL* f = fields[q];
+    if (c->lo >= 0) {   // my planes 1..w -> lower neighbour's guard; its top planes -> my planes 1-w..0
+      CZB_NCCL(A.Send(f + (long long)G.g * P, cnt, real_type(), c->lo, comm, s));
+      CZB_NCCL(A.Recv(f + (long long)(G.g - w) * P, cnt, real_type(), c->lo, comm, s));
+    }
+    if (c->hi >= 0) {   // my planes jx-w+1..jx -> upper neighbour's guard; its planes 1..w -> my jx+1..jx+w
+      CZB_NCCL(A.Send(f + (long long)(G.jx - w + G.g) * P, cnt, real_type(), c->hi, comm, s));
+      CZB_NCCL(A.Recv(f + (long long)(G.jx + G.g) * P, cnt, real_type(), c->hi, comm, s));
+    }
   }
   CZB_NCCL(A.GroupEnd());
 }
+
+void comm_halo(Comm* c, REAL* f, const Geo& G, int w, cudaStream_t s) { comm_halo_n(c, &f, 1, G, w, s); }
 
 void comm_allreduce_sum(Comm* c, double* dev, int count, cudaStream_t s) {
   if (!c || c->nranks <= 1) return;

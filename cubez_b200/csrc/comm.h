@@ -44,6 +44,8 @@ void comm_destroy(Comm* c);
 void comm_warmup(Comm* c, cudaStream_t s);   // one tiny exchange with each neighbour + one all-reduce (connection set-up)
 // Exchange `width` j-planes with both neighbours (guard planes <- neighbour's edge planes).
 void comm_halo(Comm* c, REAL* field, const Geo& G, int width, cudaStream_t s);
+// the same for several fields in ONE NCCL group (one launch): the exchanges that open a solve loop
+void comm_halo_n(Comm* c, REAL* const* fields, int nf, const Geo& G, int width, cudaStream_t s);
 // Set up the peer transport for fields with planes of `plane_elems` REALs: allocate and export the local block,
 // exchange the IPC handles with the ring neighbours, map theirs.  Collective over the communicator; returns true
 // only if EVERY rank succeeded (otherwise all ranks keep the NCCL transport).  CZB_NO_P2P=1 disables it.

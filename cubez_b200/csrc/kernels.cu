@@ -309,20 +309,24 @@ __global__ void __launch_bounds__(256) k_err(Geo G, int jlen, const REAL* __rest
 
 // dst <- src on every cell that is NOT an inner cell (guard cells, boundary nodes): what the second buffer of a
 // ping-pong loop must share with the first before the first sweep (the sweeps store every inner cell and carry the
-// other cells of the units they store over from their source).  One block row per (plane, rows), threads along k.
-__global__ void __launch_bounds__(128) k_copy_shell(Geo G, REAL* __restrict__ dst, const REAL* __restrict__ src) {
-  const int jc = blockIdx.y, jF = jc - G.g + 1;
-  const bool whole = jF < G.jst || jF > G.jed;
+// other cells of the units they store over from their source).  The whole planes below jst / above jed are two
+// contiguous blocks (copied by the launcher); this kernel does the planes between: one block per plane, a THREAD per
+// row for the few cells left and right of the inner k range (so that a plane costs one memory round trip, not one per
+// row), all threads together for the whole rows below ist / above ied, which are contiguous at both ends of a plane.
+__global__ void __launch_bounds__(256) k_copy_shell(Geo G, REAL* __restrict__ dst, const REAL* __restrict__ src) {
   const int klo = G.kst + G.g - 1, khi = G.ked + G.g - 1;      // first / last inner C index along k
-  for (int ic = blockIdx.x; ic < G.ni; ic += gridDim.x) {
-    const int iF = ic - G.g + 1;
-    const long long row = (long long)jc * G.plane + (long long)ic * G.nk;
-    if (whole || iF < G.ist || iF > G.ied) {
-      for (int k = threadIdx.x; k < G.nk; k += blockDim.x) dst[row + k] = src[row + k];
-    } else {
-      for (int k = threadIdx.x; k < klo; k += blockDim.x) dst[row + k] = src[row + k];
-      for (int k = khi + 1 + threadIdx.x; k < G.nk; k += blockDim.x) dst[row + k] = src[row + k];
+  const int ilo = G.ist + G.g - 1, ihi = G.ied + G.g - 1;      // first / last inner C row
+  const long long nlow = (long long)ilo * G.nk, nhigh = (long long)(G.ni - 1 - ihi) * G.nk;
+  for (int jF = G.jst + blockIdx.x; jF <= G.jed; jF += gridDim.x) {
+    const long long pl = (long long)(jF + G.g - 1) * G.plane;
+    for (int ic = ilo + threadIdx.x; ic <= ihi; ic += blockDim.x) {
+      const long long row = pl + (long long)ic * G.nk;
+      for (int k = 0; k < klo; ++k) dst[row + k] = src[row + k];
+      for (int k = khi + 1; k < G.nk; ++k) dst[row + k] = src[row + k];
     }
+    const long long hi0 = pl + (long long)(ihi + 1) * G.nk;
+    for (long long e = threadIdx.x; e < nlow; e += blockDim.x) dst[pl + e] = src[pl + e];
+    for (long long e = threadIdx.x; e < nhigh; e += blockDim.x) dst[hi0 + e] = src[hi0 + e];
   }
 }
 
@@ -494,10 +498,17 @@ void launch_psor_sweep(const Launch& L, const Geo& G, REAL* p, const REAL* b, co
 }
 
 void launch_copy_shell(const Launch& L, const Geo& G, REAL* dst, const REAL* src) {
-  const dim3 grid(32, G.nj, 1);
-  k_copy_shell<<<grid, 128, 0, L.s>>>(G, dst, src);
-  CZB_CHECK(cudaGetLastError());
-  count_launch();
+  // whole planes: C planes 0 .. jst+g-2 and jed+g .. nj-1
+  const long long lo = (long long)(G.jst + G.g - 1) * G.plane, hi0 = (long long)(G.jed + G.g) * G.plane;
+  if (lo > 0) CZB_CHECK(cudaMemcpyAsync(dst, src, sizeof(REAL) * lo, cudaMemcpyDeviceToDevice, L.s));
+  if (G.total > hi0) CZB_CHECK(cudaMemcpyAsync(dst + hi0, src + hi0, sizeof(REAL) * (G.total - hi0), cudaMemcpyDeviceToDevice, L.s));
+  const int npj = G.jed - G.jst + 1;
+  if (npj > 0) {
+    const int grid = npj < 4096 ? npj : 4096;
+    k_copy_shell<<<grid, 256, 0, L.s>>>(G, dst, src);
+    CZB_CHECK(cudaGetLastError());
+    count_launch();
+  }
 }
 
 void launch_state_reset(const Launch& L, LoopState* st) {

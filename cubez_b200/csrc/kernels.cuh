@@ -126,6 +126,16 @@ bool launch_jacobi_fused(const Launch& L, const Geo& G, const REAL* p, REAL* pne
 int launch_ax_fused(const Launch& L, const Geo& G, REAL* ap, const REAL* p, const REAL* cf, const REAL* dotwith,
                     int slot, int slot2 = -1, int part = 0);
 
+// ---- persistent cooperative sweeps for L2-resident grids (persist.cu) --------------------------------------
+// nfields = number of fields the loop touches (Jacobi: X, WRK, B; red-black SOR in place: X, B)
+bool persist_eligible(const Geo& G, int nfields);
+// Runs iterations it_first..it_last of CZ::JACOBI (mode 0: ping-pong, iteration `it` reads X when it is odd) or of
+// CZ::RBSOR (mode 1: both colours in place on X, kp = colour offset) in ONE cooperative launch, convergence test,
+// history and LoopState update included.  Returns at once when st->done is already set.
+void launch_persist(const Launch& L, const Geo& G, int mode, REAL* X, REAL* W, const REAL* B, const REAL* cf, REAL omg,
+                    int kp, int it_first, int it_last, LoopState* st, double res_normal, double eps, double* hist,
+                    int hist_len);
+
 // ---- loop control (tiny kernels) --------------------------------------------------------
 void launch_state_reset(const Launch& L, LoopState* st);
 // res = sqrt(acc[slot]*res_normal); hist[itr] = res; ++itr; done |= res < eps

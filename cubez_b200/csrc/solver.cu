@@ -270,6 +270,14 @@ void czb_ctx::slab_overlap_finish(REAL* X, int w, int done_iters) {
   }
 }
 
+// The persistent cooperative loop (persist.cu) serves single-rank solves of grids whose fields fit L2; the phase
+// profile wants one section per kernel call and keeps the per-iteration launches.
+bool czb_ctx::persist_ok(int nfields) {
+  if (comm && comm->nranks > 1) return false;
+  if (rt().prof.on || maf || variant != 0) return false;      // variant 1 = the baseline per-call kernels
+  return persist_eligible(G, nfields);
+}
+
 void czb_ctx::join_comm_stream() {
   if (!cs || !cs_used) return;
   CZB_CHECK(cudaEventRecord(ev_join, cs));
@@ -427,7 +435,15 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     }
   };
   int itr, done_iters;
-  if (converge_check) {
+  if (converge_check && persist_ok(3)) {
+    // L2-resident grid: iterations 1 and 2 as below (they carry the bc_k calls that give both ping-pong buffers the
+    // Dirichlet data), every later one inside ONE cooperative launch (persist.cu)
+    begin_loop(itr_max);
+    for (int it = 1; it <= 2 && it <= itr_max; ++it) body(it);
+    { Phase ph("JACOBI_kernel"); launch_persist(launch(), G, 0, X, W, B, cf, ac1, 0, 3, itr_max, d_state, res_normal, eps, d_hist, hist_cap); }
+    itr = end_loop(itr_max, res, false);
+    done_iters = h_state[0].itr;
+  } else if (converge_check) {
     itr = run_checked(itr_max, res, body);
     done_iters = h_state[0].itr;
   } else {
@@ -485,7 +501,23 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     if (!ok) { fprintf(stderr, "czb200: the fused red-black sweep refused a launch it had accepted at set-up\n"); abort(); }
   };
   int itr, done_iters;
-  if (fused) {
+  if (converge_check && persist_ok(2)) {
+    // L2-resident grid: iteration 1 with the per-colour kernels (it carries the bc_k call, cz_Poisson.cpp:226), every
+    // later one inside ONE cooperative launch that relaxes both colours in place (persist.cu)
+    begin_loop(itr_max);
+    {
+      Launch L = launch();
+      for (int color = 0; color < 2; ++color) {
+        Phase ph("SOR2SMA_kernel", 9.0 * G.cells());
+        launch_rb_color(L, G, X, B, cf, ac1, ip + color, 0, color == 1);
+      }
+      launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
+      phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
+    }
+    { Phase ph("SOR2SMA_kernel"); launch_persist(launch(), G, 1, X, nullptr, B, cf, ac1, ip, 2, itr_max, d_state, res_normal, eps, d_hist, hist_cap); }
+    itr = end_loop(itr_max, res, false);
+    done_iters = h_state[0].itr;
+  } else if (fused) {
     // Both colours in one pass (fused.cu MODE_RB2), ping-pong between X and WRK.  Multi-rank: one
     // exchange of TWO planes per iteration; the reds of the neighbour's edge plane are recomputed
     // locally from them, which keeps the result equal to the single-domain one.
@@ -493,14 +525,16 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
     REAL* W = field(WRK);
     const bool mr = comm && comm->nranks > 1;
     if (converge_check) {
-      Comm_S(X, 2);
+      if (mr) { Phase ph("Comm_Poisson"); REAL* both[2] = {X, B}; comm_halo_n(comm, both, 2, G, 2, R.stream); }   // X and B in one NCCL group
       launch_copy_shell(launch(false), G, W, X);   // WRK only needs X's guard cells and boundary nodes: every inner cell is stored by sweep 1
       wrk_guards_zero = false;
-    } else if (!wrk_guards_zero) {
-      CZB_CHECK(cudaMemsetAsync(W, 0, sizeof(REAL) * field_elems(), R.stream));
-      wrk_guards_zero = true;
+    } else {
+      if (!wrk_guards_zero) {
+        CZB_CHECK(cudaMemsetAsync(W, 0, sizeof(REAL) * field_elems(), R.stream));
+        wrk_guards_zero = true;
+      }
+      Comm_S(B, 2);
     }
-    Comm_S(B, 2);
     const int jr0 = G.jst - (nID[2] >= 0 ? 1 : 0), jr1 = G.jed + (nID[3] >= 0 ? 1 : 0);
     // Multi-rank overlap (SlabOverlap below): the first and the last j-chunk of the sweep run on a high-priority
     // stream and their outermost planes travel to the neighbours -- copy engines over NVLink peer memory, or NCCL --

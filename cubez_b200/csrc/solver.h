@@ -90,6 +90,7 @@ struct czb_ctx {
   // state without stalling the queue.  Returns the reference's iteration count.
   template <class Body> int run_checked(int itr_max, double& res, Body body);
   void ensure_comm_stream();
+  bool persist_ok(int nfields);                    // single rank, plain kernels, fields fit L2 (persist.cu)
   void join_comm_stream();                        // the solve stream waits for everything queued on cs
   // ---- SlabOverlap: a ping-pong sweep of a j-slab as two launches of the single-GPU kernel -----------------------
   // edge chunks (part 1) on ov.es, then the `w` outermost planes of dst go to the neighbours (peer DMA or NCCL) while

@@ -218,3 +218,39 @@ def test_phase_profile_report(tmp_path):
     p = subprocess.run([exe, "64", "64", "64", "sor2sma", "4000", "1.9"], cwd=str(tmp_path), capture_output=True, text=True,
                        timeout=600, env=dict(os.environ, CZB_PROFILE="1"))
     assert p.returncode == 0 and "SOR2SMA_kernel" in open(str(tmp_path / "profiling.txt")).read()
+
+
+# Persistent cooperative loop (persist.cu): grids whose fields fit L2 run all iterations after the first ones inside one
+# launch with grid barriers.  It must stop at the same iteration with the same field as the per-iteration launches
+# (CZB_PERSIST_MB=0 switches it off) and as the oracle, for sizes that give the row loop 1, 2 and many rows per warp, odd
+# and even iteration counts (Jacobi's ping-pong exit) and both precisions.
+@pytest.mark.parametrize("real", ["f32", "f64"])
+@pytest.mark.parametrize("n,solver,coef,itmax", [
+    (18, "jacobi", 0.8, 4000), (33, "sor2sma", 1.5, 4000), (64, "jacobi", 0.8, 151), (64, "sor2sma", 1.9, 4000),
+    (100, "sor2sma", 1.8, 60), (100, "jacobi", 0.9, 2), (100, "jacobi", 0.9, 3), (130, "jacobi", 0.8, 40),
+])
+def test_persistent_loop_equals_per_iteration_launches(real, n, solver, coef, itmax, monkeypatch):
+    import cubez_b200
+    runs = {}
+    for mb in ("40", "0"):
+        monkeypatch.setenv("CZB_PERSIST_MB", mb)
+        cz = cubez_b200.CZ([n] * 3, real)
+        P, RHS = cz.setup_laplace()
+        l0 = cz.launch_count()
+        out = cz.solve(solver, P, RHS, itmax, coef)
+        runs[mb] = (out, P.cpu().numpy(), cz.launch_count() - l0)
+        cz.close()
+    a, b = runs["40"], runs["0"]
+    assert a[0]["itr"] == b[0]["itr"]
+    assert np.array_equal(a[1], b[1]), "persistent loop differs from the per-iteration launches (max %g)" % np.abs(a[1] - b[1]).max()
+    np.testing.assert_allclose(a[0]["history"], b[0]["history"], rtol=1e-12)
+    assert abs(a[0]["res"] - b[0]["res"]) <= 1e-12 * b[0]["res"]
+    if itmax > 40:
+        assert a[2] < 16 and a[2] < b[2], "the persistent path did not run (%d vs %d launches)" % (a[2], b[2])
+    if n <= 64:
+        o = ou.OracleCZ([n] * 3, real)
+        Po, Ro = o.setup_laplace()
+        itr, res, hist = o.stationary(solver, Po, Ro, itmax, coef)
+        assert a[0]["itr"] == itr
+        assert np.array_equal(a[1], Po)
+        np.testing.assert_allclose(a[0]["history"], hist, rtol=1e-12)
