@@ -31,6 +31,30 @@ int slab_decompose(const int gsz[3], int nranks, int rank, int sz[3], int head[3
   return 0;
 }
 
+// General 3-D brick decomposition (the CBrick role, cz_Evaluate.cpp:103-159): every axis is cut like the j axis of
+// slab_decompose; rank = ri + gdv[0] * (rj + gdv[1] * rk), so gdv = {1, N, 1} gives exactly the j-slabs.
+int brick_decompose(const int gsz[3], const int gdv[3], int rank, int sz[3], int head[3], int nID[6], int idx[6]) {
+  const int nranks = gdv[0] * gdv[1] * gdv[2];
+  if (gdv[0] < 1 || gdv[1] < 1 || gdv[2] < 1 || rank < 0 || rank >= nranks) return -1;
+  const int r3[3] = {rank % gdv[0], (rank / gdv[0]) % gdv[1], rank / (gdv[0] * gdv[1])};
+  const int stride[3] = {1, gdv[0], gdv[0] * gdv[1]};
+  for (int a = 0; a < 3; ++a) {
+    const int n = gsz[a] - 2, parts = gdv[a], r = r3[a];
+    if (n < parts) return -1;
+    const int base = n / parts, rem = n % parts;
+    const int cnt = base + (r < rem ? 1 : 0);
+    const int first = 2 + r * base + (r < rem ? r : rem);   // global index of the first owned inner node
+    const bool lo_edge = (r == 0), hi_edge = (r == parts - 1);
+    sz[a] = cnt + (lo_edge ? 1 : 0) + (hi_edge ? 1 : 0);
+    head[a] = lo_edge ? 1 : first;
+    nID[2 * a] = lo_edge ? -1 : rank - stride[a];            // X_MINUS, X_PLUS, Y_MINUS, ... (cz_fparam.fi:10-16)
+    nID[2 * a + 1] = hi_edge ? -1 : rank + stride[a];
+    idx[2 * a] = lo_edge ? 2 : 1;
+    idx[2 * a + 1] = hi_edge ? sz[a] - 1 : sz[a];
+  }
+  return 0;
+}
+
 namespace {
 
 struct NcclApi {
@@ -93,9 +117,10 @@ int comm_unique_id(void* id128) {
   return 0;
 }
 
-Comm* comm_create(int nranks, int rank, const void* id128, int lo, int hi) {
+Comm* comm_create(int nranks, int rank, const void* id128, const int nID[6]) {
   Comm* c = new Comm;
-  c->nranks = nranks; c->rank = rank; c->lo = lo; c->hi = hi;
+  c->nranks = nranks; c->rank = rank; c->lo = nID[2]; c->hi = nID[3];
+  for (int f = 0; f < 6; ++f) c->nb[f] = nID[f];
   if (nranks > 1) {
     ncclUniqueId id;
     memcpy(&id, id128, 128);
@@ -107,20 +132,29 @@ Comm* comm_create(int nranks, int rank, const void* id128, int lo, int hi) {
 }
 
 // First use of a NCCL peer connection / of the all-reduce ring costs hundreds of milliseconds (transport set-up);
-// pay it when the communicator is made, not inside the first timed solver loop.
+// pay it when the communicator is made, not inside the first timed solver loop.  The all-reduce also carries the
+// one collective fact every rank must agree on: whether the decomposition has i or k neighbours anywhere (bricks).
 void comm_warmup(Comm* c, cudaStream_t s) {
   if (!c || c->nranks <= 1 || !c->nccl) return;
   NcclApi& A = api();
   ncclComm_t comm = (ncclComm_t)c->nccl;
   double* d = nullptr;
-  CZB_CHECK(cudaMalloc((void**)&d, 8 * sizeof(double)));
-  CZB_CHECK(cudaMemsetAsync(d, 0, 8 * sizeof(double), s));
+  CZB_CHECK(cudaMalloc((void**)&d, 16 * sizeof(double)));
+  CZB_CHECK(cudaMemsetAsync(d, 0, 16 * sizeof(double), s));
+  const double mine = (c->nb[0] >= 0 || c->nb[1] >= 0 || c->nb[4] >= 0 || c->nb[5] >= 0) ? 1.0 : 0.0;
+  CZB_CHECK(cudaMemcpyAsync(d + 12, &mine, sizeof(double), cudaMemcpyHostToDevice, s));
   CZB_NCCL(A.GroupStart());
-  if (c->lo >= 0) { CZB_NCCL(A.Send(d, 1, ncclFloat64, c->lo, comm, s)); CZB_NCCL(A.Recv(d + 1, 1, ncclFloat64, c->lo, comm, s)); }
-  if (c->hi >= 0) { CZB_NCCL(A.Send(d + 2, 1, ncclFloat64, c->hi, comm, s)); CZB_NCCL(A.Recv(d + 3, 1, ncclFloat64, c->hi, comm, s)); }
+  for (int f = 0; f < 6; ++f)
+    if (c->nb[f] >= 0) {
+      CZB_NCCL(A.Send(d + 2 * f, 1, ncclFloat64, c->nb[f], comm, s));
+      CZB_NCCL(A.Recv(d + 2 * f + 1, 1, ncclFloat64, c->nb[f], comm, s));
+    }
   CZB_NCCL(A.GroupEnd());
-  CZB_NCCL(A.AllReduce(d + 4, d + 4, 1, ncclFloat64, ncclSum, comm, s));
+  CZB_NCCL(A.AllReduce(d + 12, d + 12, 1, ncclFloat64, ncclSum, comm, s));
+  double any = 0.0;
+  CZB_CHECK(cudaMemcpyAsync(&any, d + 12, sizeof(double), cudaMemcpyDeviceToHost, s));
   CZB_CHECK(cudaStreamSynchronize(s));
+  c->brick = any > 0.0;
   cudaFree(d);
 }
 
@@ -128,6 +162,7 @@ void comm_destroy(Comm* c) {
   if (!c) return;
   for (int d = 0; d < 2; ++d) if (c->peer_block[d]) cudaIpcCloseMemHandle(c->peer_block[d]);
   if (c->block) cudaFree(c->block);
+  if (c->stage) cudaFree(c->stage);
   if (c->nccl) api().CommDestroy((ncclComm_t)c->nccl);
   delete c;
 }
@@ -250,13 +285,61 @@ void comm_p2p_fetch(Comm* c, REAL* lo_guard, REAL* hi_guard, int w, int slot, cu
   if (c->hi >= 0) CZB_CHECK(cudaMemcpyAsync(hi_guard, c->inbox + (size_t)(slot * 4 + 2) * P, bytes, cudaMemcpyDeviceToDevice, s));
 }
 
+namespace {
+// Box [k0, k0+nkb) x [i0, i0+nib) x all nj planes of f  <->  dense buffer buf[(jc * nib + ir) * nkb + kq]
+__global__ void k_box(Geo G, REAL* f, REAL* buf, int k0, int nkb, int i0, int nib, int to_buf) {
+  const long long total = (long long)nkb * nib * G.nj;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    const int kq = (int)(e % nkb);
+    const long long r = e / nkb;
+    const int ir = (int)(r % nib), jc = (int)(r / nib);
+    const long long off = (long long)jc * G.plane + (long long)(i0 + ir) * G.nk + (k0 + kq);
+    if (to_buf) buf[e] = f[off]; else f[off] = buf[e];
+  }
+}
+
+void box_copy(const Geo& G, REAL* f, REAL* buf, int k0, int nkb, int i0, int nib, int to_buf, cudaStream_t s) {
+  const long long total = (long long)nkb * nib * G.nj;
+  int grid = (int)((total + 255) / 256);
+  if (grid > 1184) grid = 1184;
+  if (grid < 1) grid = 1;
+  k_box<<<grid, 256, 0, s>>>(G, f, buf, k0, nkb, i0, nib, to_buf);
+  CZB_CHECK(cudaGetLastError());
+  count_launch();
+}
+}  // namespace
+
 void comm_halo_n(Comm* c, REAL* const* fields, int nf, const Geo& G, int w, cudaStream_t s) {
-  if (!c || c->nranks <= 1 || (c->lo < 0 && c->hi < 0)) return;
+  if (!c || c->nranks <= 1) return;
+  bool any = false;
+  for (int f = 0; f < 6; ++f) any = any || c->nb[f] >= 0;
+  if (!any) return;
   NcclApi& A = api();
   ncclComm_t comm = (ncclComm_t)c->nccl;
   const size_t cnt = (size_t)w * (size_t)G.plane;
   const long long P = G.plane;
-  CZB_NCCL(A.GroupStart());          // one group = one NCCL launch for all fields and both neighbours
+  // i faces: w rows of nk cells in every plane; k faces: w cells of every row -- strided, so they travel through
+  // dense staging buffers: [field][face X- X+ Z- Z+][send, recv]
+  const size_t ei = (size_t)w * G.nk * G.nj, ek = (size_t)w * G.ni * G.nj;
+  const bool ik = c->nb[0] >= 0 || c->nb[1] >= 0 || c->nb[4] >= 0 || c->nb[5] >= 0;
+  const size_t per_field = 4 * ei + 4 * ek;
+  if (ik && c->stage_elems < per_field * (size_t)nf) {
+    if (c->stage) { CZB_CHECK(cudaStreamSynchronize(s)); cudaFree(c->stage); }
+    c->stage_elems = per_field * (size_t)nf;
+    CZB_CHECK(cudaMalloc((void**)&c->stage, sizeof(REAL) * c->stage_elems));
+  }
+  auto sbuf = [&](int q, int face) -> REAL* {   // face: 0 X-, 1 X+, 2 Z-, 3 Z+
+    return c->stage + (size_t)q * per_field + (face < 2 ? (size_t)face * 2 * ei : 4 * ei + (size_t)(face - 2) * 2 * ek);
+  };
+  const int g = G.g;
+  if (ik)
+    for (int q = 0; q < nf; ++q) {   // pack the owned edge layers
+      if (c->nb[0] >= 0) box_copy(G, fields[q], sbuf(q, 0), 0, G.nk, g, w, 1, s);
+      if (c->nb[1] >= 0) box_copy(G, fields[q], sbuf(q, 1), 0, G.nk, G.ix + g - w, w, 1, s);
+      if (c->nb[4] >= 0) box_copy(G, fields[q], sbuf(q, 2), g, w, 0, G.ni, 1, s);
+      if (c->nb[5] >= 0) box_copy(G, fields[q], sbuf(q, 3), G.kx + g - w, w, 0, G.ni, 1, s);
+    }
+  CZB_NCCL(A.GroupStart());          // one group = one NCCL launch for all fields and all neighbours
   for (int q = 0; q < nf; ++q) {
     REAL* f = fields[q];
     if (c->lo >= 0) {   // my planes 1..w -> lower neighbour's guard; its top planes -> my planes 1-w..0
@@ -267,8 +350,22 @@ void comm_halo_n(Comm* c, REAL* const* fields, int nf, const Geo& G, int w, cuda
       CZB_NCCL(A.Send(f + (long long)(G.jx - w + G.g) * P, cnt, real_type(), c->hi, comm, s));
       CZB_NCCL(A.Recv(f + (long long)(G.jx + G.g) * P, cnt, real_type(), c->hi, comm, s));
     }
+    const int fnb[4] = {c->nb[0], c->nb[1], c->nb[4], c->nb[5]};
+    for (int face = 0; face < 4; ++face)
+      if (fnb[face] >= 0) {
+        const size_t e = face < 2 ? ei : ek;
+        CZB_NCCL(A.Send(sbuf(q, face), e, real_type(), fnb[face], comm, s));
+        CZB_NCCL(A.Recv(sbuf(q, face) + e, e, real_type(), fnb[face], comm, s));
+      }
   }
   CZB_NCCL(A.GroupEnd());
+  if (ik)
+    for (int q = 0; q < nf; ++q) {   // unpack into the guard layers
+      if (c->nb[0] >= 0) box_copy(G, fields[q], sbuf(q, 0) + ei, 0, G.nk, g - w, w, 0, s);
+      if (c->nb[1] >= 0) box_copy(G, fields[q], sbuf(q, 1) + ei, 0, G.nk, G.ix + g, w, 0, s);
+      if (c->nb[4] >= 0) box_copy(G, fields[q], sbuf(q, 2) + ek, g - w, w, 0, G.ni, 0, s);
+      if (c->nb[5] >= 0) box_copy(G, fields[q], sbuf(q, 3) + ek, G.kx + g, w, 0, G.ni, 0, s);
+    }
 }
 
 void comm_halo(Comm* c, REAL* f, const Geo& G, int w, cudaStream_t s) { comm_halo_n(c, &f, 1, G, w, s); }

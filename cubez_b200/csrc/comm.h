@@ -15,9 +15,16 @@ namespace czb {
 // neighbour's plane lives in the guard layer).
 int slab_decompose(const int gsz[3], int nranks, int rank, int sz[3], int head[3], int nID[6], int idx[6]);
 
+// 3-D bricks: gdv = divisions along i (x), j (y), k (z); see comm.cpp
+int brick_decompose(const int gsz[3], const int gdv[3], int rank, int sz[3], int head[3], int nID[6], int idx[6]);
+
 struct Comm {
   int nranks = 1, rank = 0;
   int lo = -1, hi = -1;     // neighbour ranks along j (-1: none)
+  int nb[6] = {-1, -1, -1, -1, -1, -1};   // all six neighbours: X_MINUS X_PLUS Y_MINUS Y_PLUS Z_MINUS Z_PLUS (i, j, k axes)
+  bool brick = false;       // some rank of the communicator has an i or k neighbour (decided collectively in comm_warmup)
+  REAL* stage = nullptr;    // pack / unpack buffers of the i and k faces (strided in memory; j planes are contiguous)
+  size_t stage_elems = 0;
   void* nccl = nullptr;     // ncclComm_t
   // ---- peer transport (NVLink peer memory through the copy engines, no NCCL and no SM in the halo path) ----------
   // Every rank owns one IPC-exported block:  mailbox {from_lo, from_hi} (32-bit counters the NEIGHBOURS increment
@@ -39,10 +46,12 @@ struct Comm {
 };
 
 int comm_unique_id(void* id128);
-Comm* comm_create(int nranks, int rank, const void* id128, int lo, int hi);
+Comm* comm_create(int nranks, int rank, const void* id128, const int nID[6]);
 void comm_destroy(Comm* c);
 void comm_warmup(Comm* c, cudaStream_t s);   // one tiny exchange with each neighbour + one all-reduce (connection set-up)
-// Exchange `width` j-planes with both neighbours (guard planes <- neighbour's edge planes).
+// Exchange `width` guard layers with the neighbours (guard cells <- neighbour's edge cells): j-planes directly; on
+// bricks also the i and k faces, packed into dense buffers by a kernel, all in one NCCL group.  Faces only -- the
+// 7-point stencil reads no edge or corner guard cell.
 void comm_halo(Comm* c, REAL* field, const Geo& G, int width, cudaStream_t s);
 // the same for several fields in ONE NCCL group (one launch): the exchanges that open a solve loop
 void comm_halo_n(Comm* c, REAL* const* fields, int nf, const Geo& G, int width, cudaStream_t s);

@@ -5,8 +5,8 @@
 //   ./cz gsz_x gsz_y gsz_z linear_solver IterationMax acc_coef [precond] [gdv_x gdv_y gdv_z] [--gpus N]
 //
 // Multi-GPU (the reference binary is the multi-rank entry: MPI_Init in main.cpp:31-36, CBrick division in
-// cz_Evaluate.cpp:103-159): `--gpus N` or the reference's own division arguments `1 N 1` cut the grid into N j-slabs,
-// one PROCESS per GPU.  The driver is its own launcher: the parent makes the NCCL id, re-executes itself N times
+// cz_Evaluate.cpp:103-159): `--gpus N` cuts the grid into N j-slabs, the reference's own division arguments
+// `gdv_x gdv_y gdv_z` into bricks (`1 N 1` = the same j-slabs), one PROCESS per GPU.  The driver is its own launcher: the parent makes the NCCL id, re-executes itself N times
 // (CZB_RANK / CZB_NRANKS / CZB_NCCL_ID / CZB_DEVICE in the environment), and prints the global "Error max" from the
 // ranks' local maxima; rank 0 writes the console output and the history file exactly as the serial run does.
 #include "czb200.h"
@@ -91,17 +91,17 @@ int main(int argc, char* argv[]) {
     av.push_back(argv[i]);
   }
   int ac = (int)av.size();
+  int gdv[3] = {1, 0, 1};   // gdv[1] = 0: j-slabs over `gpus` processes
   if (ac == 10 || ac == 11) {
     const int gx = atoi(av[ac - 3]), gy = atoi(av[ac - 2]), gz = atoi(av[ac - 1]);
-    if (gx != 1 || gz != 1 || gy < 1) {
-      printf("\tThis build divides the grid along y only (j-slabs): use gdv = 1 N 1.\n");
-      return 0;
-    }
-    if (gpus != 0 && gpus != gy) { printf("\tThe number of proceees does not agree with the division size.\n"); return 0; }
-    gpus = gy;
+    if (gx < 1 || gy < 1 || gz < 1) { printf("\tInvalid division.\n"); return 0; }
+    if (gpus != 0 && gpus != gx * gy * gz) { printf("\tThe number of proceees does not agree with the division size.\n"); return 0; }   // cz_Evaluate.cpp:79-83
+    gpus = gx * gy * gz;
+    gdv[0] = gx; gdv[1] = gy; gdv[2] = gz;
     ac -= 3;
   }
   if (gpus < 1) gpus = 1;
+  if (gdv[1] == 0) gdv[1] = gpus;
   const char* rk = getenv("CZB_RANK");
   const int nranks = rk ? atoi(getenv("CZB_NRANKS")) : 1;
   const int myRank = rk ? atoi(rk) : 0;
@@ -135,13 +135,14 @@ int main(int argc, char* argv[]) {
   const REAL_TYPE ac1 = (REAL_TYPE)atof(argv[6]);                             // cz_Evaluate.cpp:99
   REAL_TYPE pitch[3];
   pitch[0] = pitch[1] = pitch[2] = (REAL_TYPE)(1.0 / (REAL_TYPE)(G_size[2] - 1));   // :88
-  // sub-domain of this rank (cz_Evaluate.cpp:103-159: CBrick findOptimalDivision -> here czb_slab_decompose along j)
+  // sub-domain of this rank (cz_Evaluate.cpp:103-159: CBrick setDivision / findOptimalDivision -> czb_brick_decompose;
+  // without division arguments the grid is cut along j only, the decomposition the fused sweeps overlap)
   int size[3] = {G_size[0], G_size[1], G_size[2]};
   int head[3] = {1, 1, 1};
   int nID[6] = {-1, -1, -1, -1, -1, -1};
   int innerFidx[6] = {2, size[0] - 1, 2, size[1] - 1, 2, size[2] - 1};          // cz_miscel.cpp:20-52
-  if (nranks > 1 && czb_slab_decompose(G_size, nranks, myRank, size, head, nID, innerFidx) != 0) {
-    Hostonly_ printf("\tThe grid has fewer inner planes along y than processes.\n");
+  if (nranks > 1 && czb_brick_decompose(G_size, gdv, myRank, size, head, nID, innerFidx) != 0) {
+    Hostonly_ printf("\tThe grid has fewer inner nodes along an axis than divisions.\n");
     return -1;
   }
   REAL_TYPE origin[3];                                                         // :136-138, G_origin = 0
@@ -151,7 +152,7 @@ int main(int argc, char* argv[]) {
   czb_init(-1);                                  // CZB_DEVICE selects the GPU of this rank
   Hostonly_ printf("Iterative Mehtod = %s\n", q);
   Hostonly_ { if (precon) printf("Preconditioner = %s\n", precon); }
-  Hostonly_ { if (nranks > 1) printf("Division = 1 x %d x 1 (j-slabs, one process per GPU)\n", nranks); }
+  Hostonly_ { if (nranks > 1) printf("Division = %d x %d x %d (%s, one process per GPU)\n", gdv[0], gdv[1], gdv[2], (gdv[0] == 1 && gdv[2] == 1) ? "j-slabs" : "bricks"); }
 
   std::string fname = std::string(q) + ".txt";                                 // CZ::setLS
   for (auto& ch : fname) ch = (char)tolower(ch);

@@ -209,7 +209,7 @@ __device__ __forceinline__ REAL real_pi() {
 #endif
 }
 
-struct BcArgs { REAL dh, ox, oy; int face[6]; const REAL* tbl; int joff; };
+struct BcArgs { REAL dh, ox, oy; int face[6]; const REAL* tbl; int joff, ioff; };
 
 // bc_k (cz_solver.f90:22-191).  K faces: sin(pi x) sin(pi y); I/J faces: 0.  `tbl` (ix*jx values,
 // see bc_table below) holds the K-face Dirichlet data; tbl == null evaluates it on the device.
@@ -230,7 +230,7 @@ __global__ void k_bc(Geo G, BcArgs a, const LoopState* st, REAL* __restrict__ p)
       val = a.tbl[(size_t)(j - 1) * G.ix + (i - 1)];
     } else {
       const REAL pi = real_pi();
-      const REAL x = a.ox + a.dh * (REAL)(i - 1);
+      const REAL x = a.ox + a.dh * (REAL)(i + a.ioff - 1);
       const REAL y = a.oy + a.dh * (REAL)(j + a.joff - 1);
       val = real_sin(pi * x) * real_sin(pi * y);
     }
@@ -424,25 +424,25 @@ void launch_copy_in(const Launch& L, const Geo& G, REAL* y, const REAL* x) {   /
 // the ix*jx table is evaluated once per (size, dh, origin) with the same libm calls and uploaded;
 // writing the faces every iteration stays a device kernel.  CZB_BC_SIN=device evaluates
 // sin() on the device instead (differs by <= 1 ulp at a few boundary nodes).
-struct BcTable { int ix, jx, joff; REAL dh, ox, oy; REAL* dev; };
+struct BcTable { int ix, jx, joff, ioff; REAL dh, ox, oy; REAL* dev; };
 static std::vector<BcTable> g_bc_tables;
 
-static const REAL* bc_table(const Geo& G, REAL dh, REAL ox, REAL oy, int joff, cudaStream_t s) {
+static const REAL* bc_table(const Geo& G, REAL dh, REAL ox, REAL oy, int joff, int ioff, cudaStream_t s) {
   static int mode = -1;
   if (mode < 0) { const char* e = getenv("CZB_BC_SIN"); mode = (e && !strcmp(e, "device")) ? 1 : 0; }
   if (mode == 1) return nullptr;
   for (const BcTable& t : g_bc_tables)
-    if (t.ix == G.ix && t.jx == G.jx && t.joff == joff && t.dh == dh && t.ox == ox && t.oy == oy) return t.dev;
+    if (t.ix == G.ix && t.jx == G.jx && t.joff == joff && t.ioff == ioff && t.dh == dh && t.ox == ox && t.oy == oy) return t.dev;
   std::vector<REAL> h((size_t)G.ix * G.jx);
   const REAL pi = (REAL)2.0 * std::asin((REAL)1.0);
   std::vector<REAL> sx(G.ix);
-  for (int i = 1; i <= G.ix; ++i) { const REAL x = ox + dh * (REAL)(i - 1); sx[i - 1] = std::sin(pi * x); }
+  for (int i = 1; i <= G.ix; ++i) { const REAL x = ox + dh * (REAL)(i + ioff - 1); sx[i - 1] = std::sin(pi * x); }   // ioff = 0 in the reference; bricks use global i
   for (int j = 1; j <= G.jx; ++j) {
     const REAL y = oy + dh * (REAL)(j + joff - 1);   // joff = 0 in the reference; slabs use global j
     const REAL sy = std::sin(pi * y);
     for (int i = 1; i <= G.ix; ++i) h[(size_t)(j - 1) * G.ix + (i - 1)] = sx[i - 1] * sy;
   }
-  BcTable t{G.ix, G.jx, joff, dh, ox, oy, nullptr};
+  BcTable t{G.ix, G.jx, joff, ioff, dh, ox, oy, nullptr};
   CZB_CHECK(cudaMalloc(&t.dev, sizeof(REAL) * h.size()));
   CZB_CHECK(cudaMemcpyAsync(t.dev, h.data(), sizeof(REAL) * h.size(), cudaMemcpyHostToDevice, s));
   CZB_CHECK(cudaStreamSynchronize(s));
@@ -451,12 +451,12 @@ static const REAL* bc_table(const Geo& G, REAL dh, REAL ox, REAL oy, int joff, c
   return t.dev;
 }
 
-void launch_bc_k(const Launch& L, const Geo& G, REAL* p, REAL dh, const REAL* org, const int* nID, int joff) {
-  BcArgs a; a.dh = dh; a.ox = org[0]; a.oy = org[1]; a.tbl = nullptr; a.joff = joff;
+void launch_bc_k(const Launch& L, const Geo& G, REAL* p, REAL dh, const REAL* org, const int* nID, int joff, int ioff) {
+  BcArgs a; a.dh = dh; a.ox = org[0]; a.oy = org[1]; a.tbl = nullptr; a.joff = joff; a.ioff = ioff;
   bool any = false;
   for (int f = 0; f < 6; ++f) { a.face[f] = nID[f] < 0 ? 1 : 0; any |= a.face[f] != 0; }
   if (!any) return;
-  if (a.face[4] || a.face[5]) a.tbl = bc_table(G, dh, org[0], org[1], joff, L.s);
+  if (a.face[4] || a.face[5]) a.tbl = bc_table(G, dh, org[0], org[1], joff, ioff, L.s);
   int m = G.ix; if (G.jx > m) m = G.jx; if (G.kx > m) m = G.kx;
   dim3 block(32, 8, 1), grid((m + 31) / 32, (m + 7) / 8, 6);
   k_bc<<<grid, block, 0, L.s>>>(G, a, L.st, p);

@@ -62,8 +62,8 @@ void launch_copy_in(const Launch& L, const Geo& G, REAL* y, const REAL* x);
 
 // ---- boundary / utility (cz_solver.f90:22-191, cz_utility.f90) --------------------------
 // joff: added to j before evaluating y (0 = reference semantics; j-slabs pass head_j-1 with the GLOBAL
-// origin so that the Dirichlet data are bit-identical to the single-domain ones)
-void launch_bc_k(const Launch& L, const Geo& G, REAL* p, REAL dh, const REAL* org, const int* nID, int joff = 0);
+// origin so that the Dirichlet data are bit-identical to the single-domain ones); ioff: the same for i (bricks)
+void launch_bc_k(const Launch& L, const Geo& G, REAL* p, REAL dh, const REAL* org, const int* nID, int joff = 0, int ioff = 0);
 void launch_exact(const Launch& L, const Geo& G, REAL* e, REAL dh, const REAL* org);
 // err_t: e <- p - e on inner cells; out[0] = max |p-e| as double bits, out[1] = order index of
 // the first maximum in (j,i,k) loop order.

@@ -2,7 +2,7 @@
 //
 // On a 64^3 .. ~160^3 grid one iteration of CZ::JACOBI / CZ::RBSOR (cz_Poisson.cpp:30-82, 159-235) moves a few MB:
 // the plane-marching TMA kernels of fused.cu spend their time filling pipelines and every iteration is a kernel
-// launch (19 us per Jacobi iteration at 64^3 although the data of a sweep would stream from HBM in 0.3 us).  Here ONE
+// launch (19 - 31 us per Jacobi iteration at 64^3 although the data of a sweep would stream from HBM in 0.3 us).  Here ONE
 // cooperative launch (one CTA per SM, all co-resident) runs the whole iteration loop: a sweep over the CTA's rows with
 // loads that bypass L1 (ld.global.cg: the fields stay in the 126 MB L2, no stale line can be hit), a grid barrier, the
 // residual summed by every CTA from the per-CTA partials in the same fixed order -- so all CTAs take the same
@@ -157,10 +157,14 @@ bool probe() {
 
 }  // namespace
 
-// Fields of at most CZB_PERSIST_MB megabytes in total (X, W / B; default 40, 0 switches the path off) stay in L2.
+// Where the persistent loop wins (B200, f32, per-iteration launches of the TMA kernels vs this loop): Jacobi 64^3 30.8 ->
+// 5.2 us / iteration, 128^3 25.0 -> 14.5, 160^3 33.9 -> 22.9; red-black SOR 64^3 21.2 -> 7.3, 128^3 23.3 -> 18.6,
+// 160^3 29.4 -> 30.3 (break-even), 200^3 39.8 -> 51.8.  Hence: fields (X, WRK, B for Jacobi; X, B for red-black SOR) of
+// at most 72 MB resp. 30 MB in total, i.e. ~180^3 resp. ~155^3 cells in float.  CZB_PERSIST_MB overrides the limit
+// (0 switches the path off); it is read per solve so that tests can flip it.
 bool persist_eligible(const Geo& G, int nfields) {
-  const char* e = getenv("CZB_PERSIST_MB");       // read per solve: tests switch the path on and off
-  const double mb = e ? atof(e) : 40.0;
+  const char* e = getenv("CZB_PERSIST_MB");
+  const double mb = e ? atof(e) : (nfields >= 3 ? 72.0 : 30.0);
   if (mb <= 0.0) return false;
   if ((double)G.total * sizeof(REAL) * nfields > mb * 1.0e6) return false;
   if (G.ked < G.kst || G.ied < G.ist || G.jed < G.jst) return false;

@@ -58,9 +58,9 @@ __global__ void k_bicg_scalar(LoopState* st, int phase, double res_normal, doubl
 }
 
 // bc_k inside a solve loop = the reference's "BoundaryCondition" section (cz_Poisson.cpp:73-75 and alike)
-void phase_bc_k(const Launch& L, const Geo& G, REAL* p, REAL dh, const REAL* org, const int* nID, int joff) {
+void phase_bc_k(const Launch& L, const Geo& G, REAL* p, REAL dh, const REAL* org, const int* nID, int joff, int ioff) {
   Phase ph("BoundaryCondition");
-  launch_bc_k(L, G, p, dh, org, nID, joff);
+  launch_bc_k(L, G, p, dh, org, nID, joff, ioff);
 }
 
 int getNumStage(int n) {   // cz.h:293-300
@@ -166,6 +166,7 @@ void czb_ctx::ensure_comm_stream() {
 // ---- SlabOverlap ---------------------------------------------------------------------------------------------------
 bool czb_ctx::slab_overlap_begin(bool local_ok, int w) {
   if (!comm || comm->nranks <= 1) return false;
+  if (comm->brick) return false;      // i / k faces need the packed exchange: plain loop (the flag is collective)
   static const bool no_ovl = getenv("CZB_NO_OVERLAP") != nullptr;
   if (no_ovl) return false;
   // local_ok depends on the solver and on the geometry in k and i only (tile counts, row pitch), which every slab of a
@@ -404,7 +405,7 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
     launch_jacobi_fused(LM, G, src, dst, B, cf, ac1, sb, false, 2);
     if (converge_check && it <= 2) {
       CZB_CHECK(cudaStreamWaitEvent(R.stream, ov.ev_a[it & 1], 0));
-      phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+      phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);
     }
     slab_overlap_iteration_end(it, dst, 1, converge_check, sa, sb);
   };
@@ -431,7 +432,7 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
       // bc_k (cz_Poisson.cpp:73) is idempotent once both ping-pong buffers hold the Dirichlet values (see RBSOR).
       // It is launched WITHOUT the done gate (here and in every loop below): the reference calls it before
       // `if (res < eps) break` (cz_Poisson.cpp:73-77, 495-497), i.e. also on the converging iteration.
-      if (it <= 2) phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+      if (it <= 2) phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);
     }
   };
   int itr, done_iters;
@@ -453,7 +454,7 @@ int czb_ctx::JACOBI(double& res, REAL* X, REAL* B, int itr_max, double& flop, bo
   if (!converge_check) join_comm_stream();
   if (done_iters & 1) {
     launch_copy_inner(launch(false), G, X, W);
-    if (converge_check) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // X missed the bc_k of an odd last iteration
+    if (converge_check) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);   // X missed the bc_k of an odd last iteration
   }
   if (ovl) slab_overlap_finish(X, 1, done_iters);
   else if (done_iters & 1) Comm_S(X, 1);   // the last exchange filled WRK's guard planes; X leaves with the halo of its final state (cz_Poisson.cpp:63)
@@ -475,7 +476,7 @@ int czb_ctx::PSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, bool
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -494,7 +495,9 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
   // Eligibility of every launch form the loop below uses is decided ONCE, here (march() refuses e.g. grids with
   // more tiles than reduction slots); a refused launch inside the loop would make the iteration a silent no-op.
   const bool zs_wanted = !converge_check && pre_zero_src;
-  const bool fused = !maf && (variant == 0) && fused_eligible(G) &&
+  // bricks: the two-colour kernel would have to recompute the neighbours' reds in the i and k guard layers as it does
+  // along j -> the per-colour kernels with an exchange after each colour
+  const bool fused = !maf && (variant == 0) && !(comm && comm->brick) && fused_eligible(G) &&
                      rb2_fused_launchable(launch(), G, cf, false, 0) &&
                      (!zs_wanted || rb2_fused_launchable(launch(), G, cf, true, 0));
   auto must = [](bool ok) {
@@ -512,7 +515,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
         launch_rb_color(L, G, X, B, cf, ac1, ip + color, 0, color == 1);
       }
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
+      phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);
     }
     { Phase ph("SOR2SMA_kernel"); launch_persist(launch(), G, 1, X, nullptr, B, cf, ac1, ip, 2, itr_max, d_state, res_normal, eps, d_hist, hist_cap); }
     itr = end_loop(itr_max, res, false);
@@ -561,7 +564,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       must(launch_rb2_fused(LM, G, src, dst, B, cf, ac1, ip, jr0, jr1, sb, false, zs, 2));
       if (converge_check && it <= 2) {   // bc_k after both launches, before the edge planes leave (see SlabOverlap)
         CZB_CHECK(cudaStreamWaitEvent(R.stream, ov.ev_a[it & 1], 0));
-        phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+        phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);
       }
       slab_overlap_iteration_end(it, dst, 2, converge_check, sa, sb);
     };
@@ -584,14 +587,14 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
         // bc_k (cz_Poisson.cpp:226) is idempotent: the sweep never changes a boundary node and carries
         // the boundary nodes it stores over from src, so once both ping-pong buffers have received the
         // Dirichlet values (iterations 1 and 2) every later call would rewrite identical data.
-        if (it <= 2) phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+        if (it <= 2) phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
     else { for (int it = 1; it <= itr_max; ++it) body(it); join_comm_stream(); itr = itr_max + 1; done_iters = itr_max; }
     if (done_iters & 1) {
       launch_copy_inner(launch(false), G, X, W);
-      if (converge_check) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
+      if (converge_check) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);
     }
     if (ovl) slab_overlap_finish(X, 2, done_iters);          // X leaves with the halo of its final state
     else if (done_iters & 1) Comm_S(X, 2);                   // the last exchange filled WRK's guard planes
@@ -609,7 +612,7 @@ int czb_ctx::RBSOR(double& res, REAL* X, REAL* B, int itr_max, double& flop, boo
       if (converge_check) {
         Comm_SUM(0);
         launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-        if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+        if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);   // in place: boundary nodes never change afterwards
       }
     };
     if (converge_check) { itr = run_checked(itr_max, res, body); done_iters = h_state[0].itr; }
@@ -668,7 +671,7 @@ int czb_ctx::LSOR_PCR_RB(double& res, REAL* X, REAL* B, int itr_max, double& flo
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -704,7 +707,7 @@ int czb_ctx::LSOR_PCR(double& res, REAL* X, REAL* B, int itr_max, double& flop, 
     if (converge_check) {
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);   // in place: boundary nodes never change afterwards
+      if (it <= 1) phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);   // in place: boundary nodes never change afterwards
     }
   };
   int itr, done_iters;
@@ -737,13 +740,13 @@ int czb_ctx::LSOR_PCR_J_ESA(double& res, REAL* X, REAL* B, int itr_max, double& 
       Comm_S(dst, 1);
       Comm_SUM(0);
       launch_finish_iteration(L, d_state, 0, res_normal, eps, d_hist, hist_cap);
-      if (it <= 2) phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1);
+      if (it <= 2) phase_bc_k(launch(false), G, dst, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);
     };
     itr = run_checked(itr_max, res, body);
     done_iters = h_state[0].itr;
     if (done_iters & 1) {
       launch_copy_inner(launch(false), G, X, W);
-      phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);
+      phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);
       Comm_S(X, 1);   // the last exchange filled WRK's guard planes
     }
   } else {
@@ -863,7 +866,7 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
     }
     Comm_S(X, 1); Comm_SUM(4);                                               // :486-488
     scalar(3);                                                               // :490-500
-    phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1);                                // :495
+    phase_bc_k(launch(false), G, X, pitch, bc_origin, nID, head[1] - 1, head[0] - 1);                                // :495
   };
   // for (itr=1; itr<ItrMax; itr++)  (cz_Poisson.cpp:373)
   const int n_it = ItrMax - 1;
@@ -897,6 +900,10 @@ extern "C" {
 
 int czb_slab_decompose(const int gsz[3], int nranks, int rank, int sz[3], int head[3], int nID[6], int idx[6]) {
   return czb::slab_decompose(gsz, nranks, rank, sz, head, nID, idx);
+}
+
+int czb_brick_decompose(const int gsz[3], const int gdv[3], int rank, int sz[3], int head[3], int nID[6], int idx[6]) {
+  return czb::brick_decompose(gsz, gdv, rank, sz, head, nID, idx);
 }
 
 czb_ctx* czb_ctx_create(const int sz[3], const int idx[6], const int nID[6], CZB_REAL dh, const CZB_REAL org[3]) {
@@ -962,12 +969,13 @@ void czb_ctx_set_head(czb_ctx* c, const int head[3]) {
   // Dirichlet data in global coordinates: y = G_origin + dh*(j_global-1) with G_origin = 0 (cz.h),
   // instead of the reference's origin + dh*(j_local-1), whose rounding depends on the decomposition
   c->bc_origin[1] = (head[1] > 1) ? (REAL)0 : c->origin[1];
+  c->bc_origin[0] = (head[0] > 1) ? (REAL)0 : c->origin[0];   // the same along i on bricks
 }
 
 void czb_ctx_bc_k(czb_ctx* c, CZB_REAL* p) {
   Runtime& R = rt();
   Arg<REAL> ap(p, c->field_elems(), true, true);
-  launch_bc_k(R.launch(), c->G, ap.dev(), c->pitch, c->bc_origin, c->nID, c->head[1] - 1);
+  launch_bc_k(R.launch(), c->G, ap.dev(), c->pitch, c->bc_origin, c->nID, c->head[1] - 1, c->head[0] - 1);
 }
 void czb_ctx_set_variant(czb_ctx* c, int v) { c->variant = v; }
 void czb_ctx_set_mesh(czb_ctx* c, const CZB_REAL* x, const CZB_REAL* y, const CZB_REAL* z) { c->set_mesh(x, y, z); }
@@ -978,7 +986,7 @@ int czb_comm_unique_id(void* id128) { return comm_unique_id(id128); }
 int czb_ctx_comm_init(czb_ctx* c, int nranks, int rank, const void* id128) {
   rt();
   if (c->comm) comm_destroy(c->comm);
-  c->comm = comm_create(nranks, rank, id128, c->nID[2], c->nID[3]);
+  c->comm = comm_create(nranks, rank, id128, c->nID);
   comm_warmup(c->comm, rt().stream);
   return 0;
 }
@@ -1026,6 +1034,15 @@ int czb_solve(czb_ctx* c, const char* solver, const char* precond, CZB_REAL* X, 
     if (pc == 0 && precond) printf("precon=%s\n", precond);        // CZ::setStrPre falls through to copy
     // names CZ::setStrPre does not know (cz_Evaluate.cpp:571-619) leave pc_type unset -> copy
     if (pc == LS_BICGSTAB || pc == LS_BICGSTAB_MAF || pc == LS_PCR_ESA || pc == LS_PCR_J_ESA || pc == LS_PCR_ESA_MAF) pc = 0;
+  }
+  {   // line solvers need whole k-lines: a division along z cuts them (the reference has no distributed PCR either)
+    auto is_line = [](int v) { return v == LS_PCR || v == LS_PCR_EDA || v == LS_PCR_ESA || v == LS_PCR_RB || v == LS_PCR_RB_ESA ||
+                                      v == LS_PCR_J_ESA || v == LS_PCR_MAF || v == LS_PCR_EDA_MAF || v == LS_PCR_ESA_MAF ||
+                                      v == LS_PCR_RB_MAF || v == LS_PCR_RB_ESA_MAF; };
+    if ((c->nID[4] >= 0 || c->nID[5] >= 0) && (is_line(ls) || is_line(pc))) {
+      printf("\tLine solvers (pcr*) need undivided k-lines: use gdv_z = 1.\n");
+      return 0;
+    }
   }
   c->maf = (ls >= LS_PSOR_MAF && ls != LS_BICGSTAB_MAF);
   NvtxRange range(solver);

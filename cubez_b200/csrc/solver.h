@@ -71,7 +71,9 @@ struct czb_ctx {
   czb::Launch launch(bool with_state = true);
   void Comm_S(REAL* f, int width = 1);            // cz_comm.cpp:23-38
   void Comm_SUM(int slot, int count = 1);         // cz_comm.cpp:74-140 on device scalars
-  int parity_ip() const { return (head[0] + head[1] + head[2] + 1) % 2; }   // cz_Poisson.cpp:181
+  // cz_Poisson.cpp:181 for kst = 2; the sweeps start a line at kst + mod(i+j+kp, 2) (cz_solver.f90:466), so a brick whose
+  // k range starts at kst = 1 (lower k neighbour) shifts by one to keep the GLOBAL colour i+j+k
+  int parity_ip() const { return (head[0] + head[1] + head[2] + 1 + (innerFidx[4] - 2)) & 1; }
   czb::MafAxes axes();                            // device mesh, created on first use
   void set_mesh(const REAL* x, const REAL* y, const REAL* z);   // host vectors of size[a] + 2*gc entries
   REAL* pivot();                                  // search_pivot (cz_blas.f90:947-1039), computed on first use

@@ -1,5 +1,5 @@
-"""Pure-Python mirror of czb_slab_decompose (cubez_b200/csrc/comm.cpp): 1-D slab decomposition
-of the cube along j, the slowest axis.  Kept bit-for-bit in sync with the C++
+"""Pure-Python mirror of czb_slab_decompose / czb_brick_decompose (cubez_b200/csrc/comm.cpp): 1-D slab decomposition
+of the cube along j, the slowest axis, and general 3-D bricks (§8 f-4).  Kept bit-for-bit in sync with the C++
 version by tests/test_decomp.py."""
 
 GUIDE = 2  # reference src/cz_cpp/cz_Define.h:40
@@ -19,6 +19,31 @@ def slab_decompose(gsz, nranks, rank):
     head = [1, 1 if lo_edge else first, 1]
     nID = [-1, -1, -1 if lo_edge else rank - 1, -1 if hi_edge else rank + 1, -1, -1]
     idx = [2, sz[0] - 1, 2 if lo_edge else 1, sz[1] - 1 if hi_edge else sz[1], 2, sz[2] - 1]
+    return dict(sz=sz, head=head, nID=nID, idx=idx)
+
+
+def brick_decompose(gsz, gdv, rank):
+    """Mirror of czb_brick_decompose: gdv = divisions along x (i), y (j), z (k); rank = ri + gdv[0]*(rj + gdv[1]*rk)."""
+    nranks = gdv[0] * gdv[1] * gdv[2]
+    if min(gdv) < 1 or rank < 0 or rank >= nranks:
+        raise ValueError("bad division %r / rank %d" % (gdv, rank))
+    r3 = [rank % gdv[0], (rank // gdv[0]) % gdv[1], rank // (gdv[0] * gdv[1])]
+    stride = [1, gdv[0], gdv[0] * gdv[1]]
+    sz, head, nID, idx = [0] * 3, [0] * 3, [-1] * 6, [0] * 6
+    for a in range(3):
+        n, parts, r = gsz[a] - 2, gdv[a], r3[a]
+        if n < parts:
+            raise ValueError("cannot cut %d inner nodes into %d parts" % (n, parts))
+        base, rem = divmod(n, parts)
+        cnt = base + (1 if r < rem else 0)
+        first = 2 + r * base + min(r, rem)
+        lo_edge, hi_edge = r == 0, r == parts - 1
+        sz[a] = cnt + int(lo_edge) + int(hi_edge)
+        head[a] = 1 if lo_edge else first
+        nID[2 * a] = -1 if lo_edge else rank - stride[a]
+        nID[2 * a + 1] = -1 if hi_edge else rank + stride[a]
+        idx[2 * a] = 2 if lo_edge else 1
+        idx[2 * a + 1] = sz[a] - 1 if hi_edge else sz[a]
     return dict(sz=sz, head=head, nID=nID, idx=idx)
 
 

@@ -25,7 +25,7 @@ REFERENCE_SYMBOLS = {
 
 CZB_SYMBOLS = [
     "czb_real_bytes", "czb_version", "czb_init", "czb_set_stream", "czb_sync", "czb_malloc", "czb_free",
-    "czb_memcpy_h2d", "czb_memcpy_d2h", "czb_launch_count", "czb_staged_bytes", "czb_slab_decompose",
+    "czb_memcpy_h2d", "czb_memcpy_d2h", "czb_launch_count", "czb_staged_bytes", "czb_slab_decompose", "czb_brick_decompose",
     "czb_ctx_create", "czb_ctx_destroy", "czb_ctx_set_eps", "czb_ctx_set_res_normal", "czb_ctx_set_head",
     "czb_ctx_set_variant", "czb_ctx_set_mesh", "czb_ctx_bc_k", "czb_comm_unique_id", "czb_ctx_comm_init", "czb_solve", "czb_last_solve_ms",
     "czb_sweep_rbsor", "czb_sweep_jacobi", "czb_apply_ax", "czb_profile", "czb_profile_report",
@@ -54,6 +54,7 @@ def bind_czb_symbols(dll, real_ctype):
     dll.czb_launch_count.restype = C.c_longlong
     dll.czb_staged_bytes.argtypes = [PD, PD]; dll.czb_staged_bytes.restype = None
     dll.czb_slab_decompose.argtypes = [PI, C.c_int, C.c_int, PI, PI, PI, PI]; dll.czb_slab_decompose.restype = C.c_int
+    dll.czb_brick_decompose.argtypes = [PI, PI, C.c_int, PI, PI, PI, PI]; dll.czb_brick_decompose.restype = C.c_int
     dll.czb_ctx_create.argtypes = [PI, PI, PI, real_ctype, C.POINTER(real_ctype)]; dll.czb_ctx_create.restype = P
     dll.czb_ctx_destroy.argtypes = [P]; dll.czb_ctx_destroy.restype = None
     dll.czb_ctx_set_eps.argtypes = [P, C.c_double]; dll.czb_ctx_set_eps.restype = None

@@ -26,10 +26,11 @@ class CZ:
 
     gsz: global nodes per axis (the reference's gsz_x gsz_y gsz_z, boundary nodes included);
     real: 'f32' | 'f64' (the reference's real_type build option);
-    nranks/rank: j-slab decomposition (one process per GPU).
+    nranks/rank: j-slab decomposition (one process per GPU); gdv = (gdv_x, gdv_y, gdv_z): general 3-D bricks
+    instead (the reference's trailing command-line arguments, main.cpp:19-29), nranks = their product.
     """
 
-    def __init__(self, gsz, real="f32", device=None, nranks=1, rank=0, eps=EPS_DEFAULT):
+    def __init__(self, gsz, real="f32", device=None, nranks=1, rank=0, eps=EPS_DEFAULT, gdv=None):
         import torch
         self.torch = torch
         if not torch.cuda.is_available():
@@ -45,7 +46,10 @@ class CZ:
         self.creal = C.c_float if real == "f32" else C.c_double
         self.gsz = [int(x) for x in gsz]
         self.nranks, self.rank = nranks, rank
-        d = decomp.slab_decompose(self.gsz, nranks, rank)
+        self.gdv = [int(v) for v in gdv] if gdv is not None else None
+        if self.gdv is not None and self.gdv[0] * self.gdv[1] * self.gdv[2] != nranks:
+            raise ValueError("The number of proceees does not agree with the division size.")   # cz_Evaluate.cpp:79-83
+        d = decomp.brick_decompose(self.gsz, self.gdv, rank) if self.gdv is not None else decomp.slab_decompose(self.gsz, nranks, rank)
         self.sz, self.head, self.nID, self.idx = d["sz"], d["head"], d["nID"], d["idx"]
         # cz_Evaluate.cpp:88  pitch = 1/(G_size[2]-1) on all axes, computed in REAL
         self.pitch = self.ndtype(1.0) / self.ndtype(self.gsz[2] - 1)

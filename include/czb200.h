@@ -166,6 +166,15 @@ int czb_profile_report(const char* path, const char* title);
  * Returns 0, or -1 when nranks exceeds the number of inner planes. */
 int czb_slab_decompose(const int gsz[3], int nranks, int rank, int sz[3], int head[3],
                        int nID[6], int idx[6]);
+/* General 3-D brick decomposition inside the node, the role of CBrick in the reference (cz_Evaluate.cpp:103-159,
+ * `gdv_x gdv_y gdv_z` of main.cpp:19-29): gdv[3] = divisions along x (i), y (j), z (k); every axis is cut like the j
+ * axis above; rank = ri + gdv[0]*(rj + gdv[1]*rk), so gdv = {1, N, 1} is czb_slab_decompose.  Halo exchange: j faces
+ * as contiguous planes, i and k faces packed by a kernel, all in one NCCL group.  The fused two-colour sweep and the
+ * overlapped exchange are j-slab features; bricks with i / k neighbours run the per-colour kernels with an exchange
+ * after each colour.  Line solvers (pcr*) need gdv[2] = 1.  Returns 0, or -1 when an axis has fewer inner nodes than
+ * divisions. */
+int czb_brick_decompose(const int gsz[3], const int gdv[3], int rank, int sz[3], int head[3],
+                        int nID[6], int idx[6]);
 
 /* Solver context = the state CZ::Evaluate sets up (cz_Evaluate.cpp:56-390) -------------- */
 typedef struct czb_ctx czb_ctx;
@@ -175,7 +184,7 @@ czb_ctx* czb_ctx_create(const int sz[3], const int idx[6], const int nID[6], CZB
 void czb_ctx_destroy(czb_ctx* c);
 void czb_ctx_set_eps(czb_ctx* c, double eps);                /* default 1e-5, cz.h:162 */
 void czb_ctx_set_res_normal(czb_ctx* c, double res_normal);  /* default 1/inner cells */
-void czb_ctx_set_head(czb_ctx* c, const int head[3]);        /* global colouring offset */
+void czb_ctx_set_head(czb_ctx* c, const int head[3]);        /* global colouring offset, global Dirichlet / mesh index */
 void czb_ctx_set_variant(czb_ctx* c, int variant);
 /* Coordinate vectors of the stretched-grid (`*_maf`) solvers: host arrays of sz[a]+4 entries (= Fortran
  * X(-1:sz+2)); a NULL vector, or never calling this, gives the reference driver's uniform mesh

@@ -85,6 +85,56 @@ def main():
             dist.send(own, 0)
         dist.barrier()
         cz.close()
+    # ---- 3-D bricks: i / k faces travel packed, per-colour sweeps with an exchange after each colour,
+    # Jacobi and the BiCGstab operator on the fused one-plane kernels with guard rows / cells from the neighbours ----
+    from cubez_b200 import decomp
+    divisions = {2: [(2, 1, 1), (1, 1, 2)], 4: [(2, 1, 2), (2, 2, 1)], 8: [(2, 2, 2), (4, 1, 2)]}.get(world, [])
+    bcases = [(n, "sor2sma", None, 1.5, 60), (n, "jacobi", None, 0.8, 60), (n, "pbicgstab", "sor2sma", 1.1, 30),
+              (n2, "jacobi", None, 0.8, 12), (n2, "sor2sma", None, 1.7, 12)]
+    for gdv in divisions:
+        for n, solver, pc, omega, iters in bcases:
+            eps = 1e-5 if solver == "pbicgstab" else 0.0
+            cz = cubez_b200.CZ([n, n, n], "f32", device=lr, nranks=world, rank=rank, eps=eps, gdv=gdv)
+            idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                idt.copy_(torch.frombuffer(bytearray(cz.comm_unique_id()), dtype=torch.uint8))
+            dist.broadcast(idt, 0)
+            cz.comm_init(idt.cpu().numpy().tobytes())
+            P, RHS = cz.setup_laplace()
+            out = cz.solve(solver, P, RHS, iters, omega, pc)
+            ix = cz.idx
+            own = P[ix[2] + 1:ix[3] + 2, ix[0] + 1:ix[1] + 2, ix[4] + 1:ix[5] + 2].contiguous()
+            if rank == 0:
+                full = torch.full((n - 2, n - 2, n - 2), float("nan"), dtype=own.dtype, device="cuda")
+                for r in range(world):
+                    d = decomp.brick_decompose([n, n, n], list(gdv), r)
+                    shp = (d["idx"][3] - d["idx"][2] + 1, d["idx"][1] - d["idx"][0] + 1, d["idx"][5] - d["idx"][4] + 1)
+                    if r == 0:
+                        t = own
+                    else:
+                        t = torch.empty(shp, dtype=own.dtype, device="cuda"); dist.recv(t, r)
+                    j0, i0, k0 = d["head"][1] + d["idx"][2] - 3, d["head"][0] + d["idx"][0] - 3, d["head"][2] + d["idx"][4] - 3
+                    full[j0:j0 + shp[0], i0:i0 + shp[1], k0:k0 + shp[2]] = t
+                full = full.cpu().numpy()
+                c1 = cubez_b200.CZ([n, n, n], "f32", device=lr, eps=eps)
+                P1, R1 = c1.setup_laplace()
+                o1 = c1.solve(solver, P1, R1, iters, omega, pc)
+                ref = P1[3:-3, 3:-3, 3:-3].cpu().numpy()
+                m = min(len(o1["history"]), len(out["history"]))
+                if solver == "pbicgstab":
+                    good = abs(o1["itr"] - out["itr"]) <= 1 and np.allclose(full, ref, rtol=0, atol=1e-5 * np.abs(ref).max())
+                    good = good and np.allclose(out["history"][:m - 1], o1["history"][:m - 1], rtol=1e-3)
+                else:
+                    good = o1["itr"] == out["itr"] and np.array_equal(full, ref) and np.allclose(out["history"][:m], o1["history"][:m], rtol=1e-12)
+                print("mgpu n=%d %-10s pc=%-8s bricks %dx%dx%d itr %d/%d maxdiff %.3e %s" % (
+                    n, solver, pc, gdv[0], gdv[1], gdv[2], out["itr"], o1["itr"], float(np.nanmax(np.abs(full - ref))),
+                    "OK" if good else "FAIL"), flush=True)
+                ok = ok and good
+                c1.close()
+            else:
+                dist.send(own, 0)
+            dist.barrier()
+            cz.close()
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, 0)
     dist.destroy_process_group()

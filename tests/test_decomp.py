@@ -42,6 +42,39 @@ def test_slab_decompose_cpp_matches_python_and_tiles_the_cube(gsz):
         assert max(sizes) - min(sizes) <= 1                  # balanced
 
 
+@pytest.mark.parametrize("gsz,gdv", [([64, 64, 64], [2, 2, 2]), ([16, 9, 12], [3, 1, 2]), ([1024, 1024, 1024], [1, 8, 1]),
+                                     ([32, 35, 32], [2, 3, 1]), ([20, 20, 20], [1, 1, 4])])
+def test_brick_decompose_cpp_matches_python_and_tiles_the_cube(gsz, gdv):
+    """3-D bricks (reference: CBrick division, cz_Evaluate.cpp:103-159): C++ == Python mirror, the bricks
+    tile the inner nodes exactly once, neighbour tables are mutual, gdv = {1, N, 1} is the j-slab decomposition."""
+    d = lib.load("f32")
+    sz, head, nid, idx = (C.c_int * 3)(), (C.c_int * 3)(), (C.c_int * 6)(), (C.c_int * 6)()
+    R = gdv[0] * gdv[1] * gdv[2]
+    seen = np.zeros((gsz[0] + 1, gsz[1] + 1, gsz[2] + 1), np.int32)
+    parts = []
+    for r in range(R):
+        assert d.czb_brick_decompose((C.c_int * 3)(*gsz), (C.c_int * 3)(*gdv), r, sz, head, nid, idx) == 0
+        p = decomp.brick_decompose(gsz, gdv, r)
+        assert (list(sz), list(head), list(nid), list(idx)) == (p["sz"], p["head"], p["nID"], p["idx"])
+        parts.append(p)
+        g = [(p["head"][a] + p["idx"][2 * a] - 1, p["head"][a] + p["idx"][2 * a + 1] - 1) for a in range(3)]
+        seen[g[0][0]:g[0][1] + 1, g[1][0]:g[1][1] + 1, g[2][0]:g[2][1] + 1] += 1
+        if gdv[0] == 1 and gdv[2] == 1:
+            assert p == decomp.slab_decompose(gsz, R, r)
+    assert (seen[2:gsz[0], 2:gsz[1], 2:gsz[2]] == 1).all() and seen.sum() == (gsz[0] - 2) * (gsz[1] - 2) * (gsz[2] - 2)
+    for r, p in enumerate(parts):
+        for f in range(6):
+            nb = p["nID"][f]
+            if nb >= 0:
+                assert parts[nb]["nID"][f ^ 1] == r        # my X+ neighbour has me as its X-
+                a = f // 2                                  # adjacent along axis a: its first node follows my last
+                lo, hi = (parts[nb], p) if f % 2 == 0 else (p, parts[nb])
+                assert lo["head"][a] + lo["idx"][2 * a + 1] == hi["head"][a] + hi["idx"][2 * a] - 1
+    assert d.czb_brick_decompose((C.c_int * 3)(*gsz), (C.c_int * 3)(gsz[0], 1, 1), 0, sz, head, nid, idx) == -1
+    with pytest.raises(ValueError):
+        decomp.brick_decompose(gsz, [gsz[0], 1, 1], 0)
+
+
 def _worker(rank, world, port, n, solver, iters, omega, q):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)

@@ -232,7 +232,7 @@ def test_phase_profile_report(tmp_path):
 def test_persistent_loop_equals_per_iteration_launches(real, n, solver, coef, itmax, monkeypatch):
     import cubez_b200
     runs = {}
-    for mb in ("40", "0"):
+    for mb in ("200", "0"):
         monkeypatch.setenv("CZB_PERSIST_MB", mb)
         cz = cubez_b200.CZ([n] * 3, real)
         P, RHS = cz.setup_laplace()
@@ -240,7 +240,7 @@ def test_persistent_loop_equals_per_iteration_launches(real, n, solver, coef, it
         out = cz.solve(solver, P, RHS, itmax, coef)
         runs[mb] = (out, P.cpu().numpy(), cz.launch_count() - l0)
         cz.close()
-    a, b = runs["40"], runs["0"]
+    a, b = runs["200"], runs["0"]
     assert a[0]["itr"] == b[0]["itr"]
     assert np.array_equal(a[1], b[1]), "persistent loop differs from the per-iteration launches (max %g)" % np.abs(a[1] - b[1]).max()
     np.testing.assert_allclose(a[0]["history"], b[0]["history"], rtol=1e-12)

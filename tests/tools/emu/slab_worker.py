@@ -2,8 +2,9 @@
 tests/mgpu_worker.py.  One OS process per rank; NCCL is the file-based stand-in nccl_emu.cpp, selected through
 comm.cpp's CZB_NCCL_LIB switch.
 
-    python slab_worker.py RANK NRANKS WORKDIR N SOLVER PRECOND|- OMEGA ITERS EPS
-writes WORKDIR/out_RANK.npz (owned inner planes, iteration count, history)."""
+    python slab_worker.py RANK NRANKS WORKDIR N SOLVER PRECOND|- OMEGA ITERS EPS [GX,GY,GZ]
+writes WORKDIR/out_RANK.npz (owned inner planes -- with a division GX,GY,GZ the owned inner box and its global C offsets
+-- iteration count, history)."""
 import ctypes as C
 import os
 import sys
@@ -28,7 +29,8 @@ def main():
     ffi.bind_reference_symbols(dll); ffi.bind_czb_symbols(dll, C.c_float)
     dll.czb_init(0)
     gsz = [n, n, n]
-    d = decomp.slab_decompose(gsz, nranks, rank)
+    gdv = [int(v) for v in sys.argv[10].split(",")] if len(sys.argv) > 10 else None
+    d = decomp.brick_decompose(gsz, gdv, rank) if gdv else decomp.slab_decompose(gsz, nranks, rank)
     sz, head, nID, idx = d["sz"], d["head"], d["nID"], d["idx"]
     dt = np.float32
     pitch = dt(1.0) / dt(gsz[2] - 1)
@@ -61,7 +63,11 @@ def main():
                         iters, C.c_float(omega), C.byref(res), hist, iters + 2, C.byref(flop))
     nh = min(itr, iters - 1 if solver.startswith("pbicgstab") else iters)
     own = P[idx[2] + 1:idx[3] + 2].copy()          # owned inner planes (local C indices)
-    np.savez(os.path.join(work, "out_%d.npz" % rank), own=own, itr=itr, hist=np.array(hist[:max(nh, 0)]), res=res.value)
+    extra = {}
+    if gdv:   # owned inner box and where it sits in the global (j, i, k) array of inner + boundary + guard cells
+        own = P[idx[2] + 1:idx[3] + 2, idx[0] + 1:idx[1] + 2, idx[4] + 1:idx[5] + 2].copy()
+        extra["at"] = np.array([head[1] + idx[2], head[0] + idx[0], head[2] + idx[4]])   # global C index of the first owned cell
+    np.savez(os.path.join(work, "out_%d.npz" % rank), own=own, itr=itr, hist=np.array(hist[:max(nh, 0)]), res=res.value, **extra)
     dll.czb_ctx_destroy(ctx)
 
 
