@@ -799,7 +799,7 @@ int czb_ctx::PBiCGSTAB(double& res, REAL* X, REAL* B, int ItrMax, double& flop, 
   // With the packed two-colour kernel as preconditioner the first of the 8 sweeps treats its source as zero
   // without reading it, so p_ / s_ need no clearing: every cell the sweeps do not store stays at the zero
   // the field was allocated with (czb_malloc), every stored cell is rewritten by sweep 2.
-  const bool zs = (pc_type == LS_SOR2SMA) && variant == 0 && rb2_zero_src_supported(G, cf);
+  const bool zs = (pc_type == LS_SOR2SMA) && variant == 0 && !(comm && comm->brick) && rb2_zero_src_supported(G, cf);   // bricks sweep per colour and read p_
 
   begin_loop(ItrMax);
   {
