@@ -28,7 +28,7 @@ CZB_SYMBOLS = [
     "czb_memcpy_h2d", "czb_memcpy_d2h", "czb_launch_count", "czb_staged_bytes", "czb_slab_decompose", "czb_brick_decompose",
     "czb_ctx_create", "czb_ctx_destroy", "czb_ctx_set_eps", "czb_ctx_set_res_normal", "czb_ctx_set_head",
     "czb_ctx_set_variant", "czb_ctx_set_mesh", "czb_ctx_bc_k", "czb_comm_unique_id", "czb_ctx_comm_init", "czb_solve", "czb_last_solve_ms",
-    "czb_sweep_rbsor", "czb_sweep_jacobi", "czb_apply_ax", "czb_profile", "czb_profile_report",
+    "czb_sweep_rbsor", "czb_sweep_jacobi", "czb_apply_ax", "czb_profile", "czb_profile_report", "czb_dot2_noalloc",
 ]
 
 
@@ -72,5 +72,6 @@ def bind_czb_symbols(dll, real_ctype):
     dll.czb_sweep_jacobi.argtypes = [P, P, P, P, real_ctype, PD]; dll.czb_sweep_jacobi.restype = C.c_int
     dll.czb_apply_ax.argtypes = [P, P, P, P, PD, PD]; dll.czb_apply_ax.restype = C.c_int
     dll.czb_profile.argtypes = [C.c_int]; dll.czb_profile.restype = None
+    dll.czb_dot2_noalloc.argtypes = [P, P, PI, PI, C.c_int, P, P]; dll.czb_dot2_noalloc.restype = C.c_int
     dll.czb_profile_report.argtypes = [C.c_char_p, C.c_char_p]; dll.czb_profile_report.restype = C.c_int
     return dll

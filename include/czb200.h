@@ -212,6 +212,23 @@ int czb_sweep_rbsor(czb_ctx* c, const CZB_REAL* x, CZB_REAL* xnew, const CZB_REA
 int czb_sweep_jacobi(czb_ctx* c, const CZB_REAL* x, CZB_REAL* xnew, const CZB_REAL* b, CZB_REAL omg, double* res);
 int czb_apply_ax(czb_ctx* c, CZB_REAL* ap, const CZB_REAL* p, const CZB_REAL* w, double* dot_w, double* dot_self);
 
+/* Allocation-free inner product.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same sum as blas_dot2_ above -- REAL products of x and y over the inner cells idx = {ist,ied,jst,jed,kst,ked} of a
+ * field with sz[3] nodes and g guard cells, accumulated in double -- but the per-block partial sums and the ticket live
+ * in a file-scope static __device__ array (64.25 KB, held by every GPU that loads the library until exit) instead of
+ * the runtime's cudaMalloc'ed scratch: the call performs no cudaMalloc / cudaFree / allocating library routine and
+ * does not touch the library's runtime object.  x, y (inputs) and out_dev (one double, output) are DEVICE pointers
+ * supplied by the caller; everything is enqueued on `stream` (a cudaStream_t, NULL = default stream), nothing is
+ * synchronised.  Limit: the inner (k,i) plane may need at most CZB_NOALLOC_MAX_BLOCKS blocks of 256 cells (about 2.1
+ * million cells per plane, e.g. 1446 x 1446; the j axis is chunked to fit); larger grids are rejected with a message.
+ * All calls share the static array and it keeps the last call's contents (the ticket is cleared on `stream` before
+ * each launch): calls that overlap on the GPU -- different streams without an ordering between them -- race.
+ * Returns 0, -1 grid beyond the limit, -2 bad argument (null / host pointer), -3 CUDA error or no device. */
+#define CZB_NOALLOC_MAX_BLOCKS 8192
+int czb_dot2_noalloc(const CZB_REAL* x, const CZB_REAL* y, const int sz[3], const int idx[6], int g,
+                     double* out_dev, void* stream);
+
 /* Fused solve loop.  solver/precond names follow CZ::setLS / setStrPre
  * (cz_Evaluate.cpp:571-803): jacobi psor sor2sma pbicgstab pcr pcr_eda pcr_esa pcr_rb
  * pcr_rb_esa pcr_j_esa and the stretched-grid twins jacobi_maf psor_maf sor2sma_maf pbicgstab_maf
