@@ -18,7 +18,8 @@ One JSON line on rank 0:
                order-independent checksum of the field against tests/golden/bench_parity.json, which was written
                by the CPU ORACLE on the single domain (tests/golden/make_bench_parity.py)
   e2e          the same K iterations through the public call CZ.solve() with HOST (pinned) arrays:
-               H2D of X and B, the solve loop, D2H of X and of the residual history, all timed
+               H2D of X and B, the solve loop, D2H of X and of the residual history, all timed;
+               e2e.to_convergence (N=1): the same call run until res < 1e-5 (256^3 and 1024^3 sor2sma)
   roofline     dominant kernel (fused two-colour sweep k_rb2_pk): algorithmic bytes (4R = 16 B per
                cell.iteration) / measured time per iteration, against the measured HBM copy bandwidth
   cpu_baseline the CPU oracle port of the reference kernel (oracle/, "port") on all host cores, bounded sample,
@@ -52,7 +53,7 @@ GOLDEN_PARITY = os.path.join(ROOT, "tests", "golden", "bench_parity.json")
 GOLDEN_CONFIGS = os.path.join(ROOT, "tests", "golden", "baseline_configs.json")
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_rb2_pk launch at N=1, 1024^3 (profiles/*_rb2_summary.md);
 # null for any other N / grid: the figure is a property of that capture, not of this run
-NCU_TRAFFIC_N1 = {"bytes": 14.24e9, "source": "profiles/r01_rb2_summary.md"}
+NCU_TRAFFIC_N1 = {"bytes": 14.25e9, "source": "profiles/r02_rb2_summary.md"}
 
 
 def measured_peak():
@@ -516,6 +517,8 @@ def run_gpu(args, rank, world, local_rank):
                             ttc[label]["cpu"] = cpu[label]
                 if "also_f64" in ttc:
                     line["also_f64"] = ttc.pop("also_f64")
+                if "e2e_to_convergence" in ttc:
+                    line["e2e"]["to_convergence"] = ttc.pop("e2e_to_convergence")
                 line["time_to_convergence"] = ttc
     except Exception as ex:      # never lose the headline
         sys.stderr.write("bench.py: optional legs failed: %r\n" % (ex,))
@@ -588,6 +591,31 @@ def ttc_worker():
         del P, RHS
     cz.close()
     out["also_f64"] = f64
+    # end to end TO CONVERGENCE: the public call with pinned HOST arrays (H2D of X and B, the solver loop until
+    # res < 1e-5, D2H of X and of the history) timed on the host clock -- the API-level figure at an iteration count a
+    # user runs, next to the 20-step `e2e` that mostly measures the PCIe link
+    e2c = {}
+    for label, n, solver, itmax, omg, pre, real in (TTC_CASES[1], TTC_BIG[0]):
+        cz = cubez_b200.CZ([n] * 3, real, eps=1.0e-5)
+        P, RHS = cz.setup_laplace()
+        cz.solve(solver, P, RHS, 3, omg, precond=pre, want_history=False)          # warm-up (work fields, tables)
+        P, RHS = cz.setup_laplace()
+        Ph, Bh = P.cpu().pin_memory(), RHS.cpu().pin_memory()
+        del P, RHS
+        torch.cuda.empty_cache()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        o = cz.solve(solver, Ph.numpy(), Bh.numpy(), itmax, omg, precond=pre, want_history=True)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        it = int(o["itr"])
+        fb = float(Ph.numel()) * Ph.element_size()
+        e2c[label] = {"iterations": it, "seconds": dt, "solver_loop_ms": float(o["ms"]), "residual": float(o["res"]),
+                      "value": float(cz.inner_cells_global) * it / dt / 1e9, "unit": "GLUPS",
+                      "h2d_bytes": 2.0 * fb, "d2h_bytes": fb + 8.0 * it}
+        cz.close()
+        del Ph, Bh
+    out["e2e_to_convergence"] = e2c
     print(json.dumps(out), flush=True)
 
 
