@@ -143,7 +143,8 @@ extern "C" int czb_dot2_noalloc(const CZB_REAL* x, const CZB_REAL* y, const int 
   if (!scratch) return -3;
   // the ticket must start at zero whatever an earlier (possibly aborted) call left behind
   if (cudaMemsetAsync(scratch, 0, sizeof(unsigned int), s) != cudaSuccess) { cudaGetLastError(); return -3; }
-  k_dot2_noalloc<<<dim3((unsigned)gx, (unsigned)gy, (unsigned)gz), dim3(bx, by, 1), 0, s>>>(G, jlen, x, y, scratch, out_dev);
+  const dim3 grid((unsigned)gx, (unsigned)gy, (unsigned)gz), block(bx, by, 1);
+  k_dot2_noalloc<<<grid, block, 0, s>>>(G, jlen, x, y, scratch, out_dev);
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { fprintf(stderr, "czb200: czb_dot2_noalloc: launch failed: %s\n", cudaGetErrorString(e)); return -3; }
   return 0;

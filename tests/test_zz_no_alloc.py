@@ -11,7 +11,6 @@ import pytest
 
 import oracle_util as ou
 
-pytestmark = pytest.mark.gpu
 
 
 def _dot2_existing(cz, Xg, Yg):
@@ -26,6 +25,7 @@ def _dot2_noalloc(cz, Xg, Yg, out, stream=None):
     return rc
 
 
+@pytest.mark.gpu
 @pytest.mark.parametrize("real", ["f32", "f64"])
 @pytest.mark.parametrize("sz", [[16, 16, 16], [37, 21, 50], [130, 96, 258]])
 def test_dot2_noalloc_equals_blas_dot2_on_two_calls_in_a_row(real, sz):
@@ -58,6 +58,7 @@ def test_dot2_noalloc_equals_blas_dot2_on_two_calls_in_a_row(real, sz):
     cz.close()
 
 
+@pytest.mark.gpu
 def test_dot2_noalloc_allocates_nothing_and_rejects_what_it_cannot_hold():
     import torch
     import cubez_b200
@@ -87,3 +88,40 @@ def test_dot2_noalloc_allocates_nothing_and_rejects_what_it_cannot_hold():
     torch.cuda.synchronize()
     assert float(out.item()) == float(vals[0].item())
     cz.close()
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+def test_dot2_noalloc_host_logic_on_the_emulated_library(real):
+    """CPU: noalloc.cu compiled into the CPU-emulated library (tests/tools/emu; the static `__device__` array is a host
+    array there): launch geometry, j chunking, ticket handling, argument checks and the size limit -- against the
+    oracle's blas_dot2 on two calls in a row.  No GPU involved; the GPU tests above are the parity tests proper."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(ou.ROOT, "tests", "tools", "emu"))
+    import emu_build
+    from cubez_b200 import ffi
+    dll = C.CDLL(emu_build.build_lib()[real])
+    creal = C.c_float if real == "f32" else C.c_double
+    ffi.bind_reference_symbols(dll); ffi.bind_czb_symbols(dll, creal)
+    dll.czb_init(0)
+    # the emulation runs one block per CUDA THREAD, so the grids here are kept below 8192 threads in total
+    for sz in ([12, 9, 20], [20, 6, 40]):
+        o = ou.OracleCZ(sz, real)
+        X, Y = ou.random_fields(o.shape, o.dt, n=2)
+        nb = X.nbytes
+        dx, dy, dout = dll.czb_malloc(nb), dll.czb_malloc(nb), dll.czb_malloc(8)
+        dll.czb_memcpy_h2d(dx, X.ctypes.data, nb); dll.czb_memcpy_h2d(dy, Y.ctypes.data, nb)
+        ro, flop = creal(0), C.c_double(0)
+        o.dll.blas_dot2_(C.byref(ro), ou.ptr(X), ou.ptr(Y), o._sz, o._idx, o.g(), C.byref(flop))
+        for _ in range(2):
+            got = C.c_double(float("nan"))
+            dll.czb_memcpy_h2d(dout, C.addressof(got), 8)
+            assert dll.czb_dot2_noalloc(dx, dy, o._sz, o._idx, 2, dout, None) == 0
+            dll.czb_memcpy_d2h(C.addressof(got), dout, 8)
+            assert float(o.dt(got.value)) == pytest.approx(float(ro.value), rel=2e-6 if real == "f32" else 1e-11,
+                                                             abs=1e-3 if real == "f32" else 1e-10)
+        assert dll.czb_dot2_noalloc(X.ctypes.data, dy, o._sz, o._idx, 2, dout, None) == -2        # host pointer refused
+        big, bidx = (C.c_int * 3)(3000, 8, 3000), (C.c_int * 6)(2, 2999, 2, 7, 2, 2999)
+        assert dll.czb_dot2_noalloc(dx, dy, big, bidx, 2, dout, None) == -1                       # beyond the static scratch
+        for d in (dx, dy, dout):
+            dll.czb_free(d)

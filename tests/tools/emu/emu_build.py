@@ -27,7 +27,7 @@ def _rewrite(text):
     return LAUNCH.sub(sub, text)
 
 
-LIB_SOURCES = ("kernels.cu", "maf.cu", "pcr.cu", "runtime.cu", "abi.cu", "solver.cu", "comm.cpp")
+LIB_SOURCES = ("kernels.cu", "maf.cu", "pcr.cu", "noalloc.cu", "runtime.cu", "abi.cu", "solver.cu", "comm.cpp")
 
 
 def _pcr_plain(text):

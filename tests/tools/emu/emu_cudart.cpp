@@ -28,6 +28,8 @@ cudaError_t cudaFree(void* p) { if (p) { allocs().erase((const char*)p); free(p)
 cudaError_t cudaMallocHost(void** p, size_t n) { *p = calloc(1, n ? n : 1); return *p ? cudaSuccess : cudaErrorMemoryAllocation; }
 cudaError_t cudaHostAlloc(void** p, size_t n, unsigned int) { return cudaMallocHost(p, n); }   // cuda_runtime.h's C++ cudaMallocHost overload
 cudaError_t cudaMemGetInfo(size_t* fr, size_t* tot) { *fr = *tot = (size_t)8 << 30; return cudaSuccess; }
+// a `static __device__` array is a plain host array here: its own address is its "device" address
+cudaError_t cudaGetSymbolAddress(void** p, const void* sym) { *p = const_cast<void*>(sym); return cudaSuccess; }
 cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t*, void*) { return cudaErrorNotSupported; }
 cudaError_t cudaIpcOpenMemHandle(void**, cudaIpcMemHandle_t, unsigned int) { return cudaErrorNotSupported; }
 cudaError_t cudaIpcCloseMemHandle(void*) { return cudaSuccess; }
