@@ -16,8 +16,11 @@
 // (oracle/Makefile -> oracle/_ref/cz_ref_*), reproducing the analytic-solution check
 // `Error max` of cz_Evaluate.cpp:550-563, (2) the known answers of example/tri/test1.cpp,
 // test3.cpp, test5.cpp for the tridiagonal line solves, (3) doc/Memo.md:131-134 (pcr_eda
-// history == pcr history).  Kernel arithmetic itself is "parity unpinned by reference
-// outputs" because no Fortran build of the reference can be produced in this image.
+// history == pcr history), (4) OUTPUTS OF THE REFERENCE'S OWN C++ PCR (src/cz_cpp/cz_pcr.cpp, compiled
+// unmodified behind oracle/ref_pcr_harness.cpp): the stage loop below (line_pcr_stages) equals them bit for
+// bit in double, tests/golden/ref_pcr_stages.json.  The rest of the kernel arithmetic (point sweeps, BLAS-1,
+// last-stage direct solves) is "parity unpinned by reference outputs" because no Fortran build of the
+// reference can be produced in this image or on the GPU box.
 //
 // Reduction mode: env ORACLE_SUM=double (default) -> REAL products, double
 // accumulation, j-plane partials summed in j order (deterministic for any thread count);
@@ -778,6 +781,19 @@ void oracle_pcr_line_(int* n_, int* mode, REAL* a, REAL* c, REAL* d, REAL* xout)
   if (*mode == 0) { line_pcr_stages(w, pn - 1); line_last_2x2(w, pn); }
   else            { line_pcr_stages(w, pn - 2); line_last_4x4(w, pn); }
   for (int k = 1; k <= n; ++k) xout[k - 1] = w.d1[w.o(k)];
+}
+
+// The PCR reduction stages alone, for pinning against the reference's own C++ PCR (src/cz_cpp/cz_pcr.cpp:42-96,
+// CZ::pcr / CZ::pcr_kernel -- the same recurrences as cz_solver.f90:584-608): a, c, d hold cells 1..n on entry and the
+// coefficients / right-hand side after `stages` stages on return.  See oracle/ref_pcr_harness.cpp.
+void oracle_pcr_stages_(int* n_, int* stages, REAL* a, REAL* c, REAL* d) {
+  const int n = *n_;
+  int pn = -1, b = 1;
+  for (int i = 1; i < 20; ++i) { b *= 2; if (n < b) { pn = i; break; } }  // cz.h:293-300
+  LineWork w(1, n, pn);
+  for (int k = 1; k <= n; ++k) { w.a[w.o(k)] = a[k - 1]; w.c[w.o(k)] = c[k - 1]; w.d[w.o(k)] = d[k - 1]; }
+  line_pcr_stages(w, *stages);
+  for (int k = 1; k <= n; ++k) { a[k - 1] = w.a[w.o(k)]; c[k - 1] = w.c[w.o(k)]; d[k - 1] = w.d[w.o(k)]; }
 }
 
 int oracle_real_bytes_() { return (int)sizeof(REAL); }

@@ -297,3 +297,57 @@ def test_port_equals_numpy_restatement_psor_maf(real):
     Xn = X.copy(); rn = npr.psor_maf(Xn, B, o.idx, *mesh, 1.5)
     assert np.array_equal(Xo, Xn)
     assert ro.value == pytest.approx(rn, rel=1e-12)
+
+
+# ---- the oracle's PCR stage recurrences against OUTPUTS OF THE REFERENCE ITSELF ------------------------------------------
+# src/cz_cpp/cz_pcr.cpp (CZ::pcr / CZ::pcr_kernel, :42-96) is the reference's own C++ statement of the recurrences the
+# Fortran line solvers run (cz_solver.f90:584-608).  oracle/Makefile compiles it unmodified behind an exact-I/O harness
+# (oracle/ref_pcr_harness.cpp -> oracle/_ref/ref_pcr_*); tests/golden/ref_pcr_stages.json holds its outputs
+# (tests/golden/make_ref_pcr.py).  Double: the port must agree bit for bit.  Float: the C++ evaluates
+# 1.0 / (1.0 - ap*c - cp*a) with double literals where the Fortran stays in REAL -> a few ulp.
+def _port_stages(real, n, stages, a, c, d):
+    dll = ou.load(real)
+    oa, oc, od = a.copy(), c.copy(), d.copy()
+    dll.oracle_pcr_stages_(C.byref(C.c_int(n)), C.byref(C.c_int(stages)), ou.ptr(oa), ou.ptr(oc), ou.ptr(od))
+    return oa, oc, od
+
+
+def _check_stages(real, got, ref):
+    for g, r in zip(got, ref):
+        if real == "f64":
+            assert np.array_equal(g, r), np.abs(g - r).max()
+        else:
+            np.testing.assert_allclose(g.astype(np.float64), r, rtol=3e-6, atol=1e-30)   # <= 1 ulp of the denominator per stage, up to 7 stages
+
+
+def test_pcr_stages_equal_the_reference_cpp_pcr_golden():
+    gold = json.load(open(os.path.join(HERE, "golden", "ref_pcr_stages.json")))
+    assert len(gold["cases"]) >= 40
+    for cs in gold["cases"]:
+        dt = np.float64 if cs["real"] == "f64" else np.float32
+        a, c, d = (np.array([float.fromhex(v) for v in cs[k]], dtype=dt) for k in ("a", "c", "d"))
+        ref = [np.array([float.fromhex(v) for v in cs[k]], dtype=np.float64) for k in ("ref_a", "ref_c", "ref_d")]
+        _check_stages(cs["real"], _port_stages(cs["real"], cs["n"], cs["stages"], a, c, d), ref)
+
+
+@pytest.mark.parametrize("real", ["f64", "f32"])
+def test_pcr_stages_equal_the_reference_cpp_pcr_live(real):
+    """The same against the harness run here (skipped where /root/reference was absent at build time), on the line lengths
+    of the BASELINE configs (62, 254, 510, 1022 cells) with the solver's own stage counts pn-1 and pn-2."""
+    exe = ou.ref_binary("ref_pcr_%s" % real)
+    if exe is None:
+        pytest.skip("oracle/_ref/ref_pcr_%s not built (needs /root/reference at build time)" % real)
+    import subprocess
+    dt = np.float64 if real == "f64" else np.float32
+    rng = np.random.default_rng(11)
+    for n in (62, 254, 510, 1022):
+        pn = int(np.floor(np.log2(n))) + 1
+        r = dt(1.0) / dt(6.0)
+        a = np.full(n, -r, dt); c = np.full(n, -r, dt); a[0] = 0; c[-1] = 0
+        d = rng.uniform(-1, 1, n).astype(dt)
+        for stages in (pn - 1, pn - 2):
+            inp = "%d %d\n" % (n, stages) + "\n".join(" ".join(float(v).hex() for v in arr) for arr in (a, c, d)) + "\n"
+            p = subprocess.run([exe], input=inp, capture_output=True, text=True, timeout=60)
+            assert p.returncode == 0, p.stderr
+            ref = [np.array([float.fromhex(t) for t in line.split()]) for line in p.stdout.strip().split("\n")]
+            _check_stages(real, _port_stages(real, n, stages, a, c, d), ref)
