@@ -99,8 +99,8 @@ void launch_calc_ax_maf(const Launch& L, const Geo& G, REAL* ap, const REAL* p, 
 void launch_calc_rk_maf(const Launch& L, const Geo& G, REAL* r, const REAL* p, const REAL* b, const MafAxes& A,
                         const REAL* pvt);
 void launch_search_pivot(const Launch& L, const Geo& G, REAL* pvt, const MafAxes& A);
-// mode 0/1: lines with mod(i+j,2) == mode; mode 3: lines with i+j == diag.  acc[slot] (+)= 2 * sum dp^2 (the
-// reference's MAF line routines count every square twice, cz_maf.f90:635-636, 657-660).
+// mode 0/1: lines with mod(i+j,2) == mode; mode 3: lines with i+j == diag.  acc[slot] (+)= sum dp^2
+// (cz_maf.f90:642-646: one of the two accumulation statements per build, never both).
 void launch_pcr_lines_maf(const Launch& L, const Geo& G, int pn, int mode, int diag, const MafAxes& A, REAL* x,
                           const REAL* msk, const REAL* rhs, REAL omg, int slot, bool add);
 

@@ -259,14 +259,9 @@ __global__ void __launch_bounds__(256) k_pcr_lines_maf(Geo G, int n, int pn, Maf
   grid_reduce<1>(acc, rb, fin);
 }
 
-// every dp*dp is added to res1 AND to tmp(k), and tmp is summed into res1 (cz_maf.f90:635-636, 657-660):
-// the five MAF line routines return TWICE the sum of squares
-struct FinStoreTwice {
-  LoopState* st; int slot; int add;
-  __device__ void operator()(double (&tot)[1]) const {
-    if (st) st->acc[slot] = (add ? st->acc[slot] : 0.0) + 2.0 * tot[0];
-  }
-};
+// The five MAF line routines add every dp*dp ONCE: `tmp(k) = tmp(k) + dp*dp` (summed into res1 afterwards) under
+// -D_SVR, `res1 = res1 + dp*dp` otherwise -- the two statements are the branches of one #ifdef (cz_maf.f90:642-646,
+// 659-663).  (Round 1 read both as unconditional and doubled the sum; found by executing the reference's Fortran.)
 
 }  // namespace
 
@@ -334,7 +329,7 @@ void launch_pcr_lines_maf(const Launch& L, const Geo& G, int pn, int mode, int d
   int grid = sel.nlines < 148 * 8 ? sel.nlines : 148 * 8;
   if ((size_t)grid > L.rb_blocks) grid = (int)L.rb_blocks;
   const size_t smem = 6 * (size_t)n * sizeof(REAL);
-  typedef FinStoreTwice F;
+  typedef FinStore F;
   static size_t sm_set = 0;
   if (smem > sm_set) {
     CZB_CHECK(cudaFuncSetAttribute(k_pcr_lines_maf<F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -11,16 +11,20 @@
 // cpu_baseline / --impl reference legs may load this.  The product path (cubez_b200/) never
 // links or calls it.
 //
-// PARITY PINNING: the reference ships no golden vectors for this path.  What
-// pins this oracle is (1) the reference's own UNMODIFIED C++ driver linked against it
-// (oracle/Makefile -> oracle/_ref/cz_ref_*), reproducing the analytic-solution check
-// `Error max` of cz_Evaluate.cpp:550-563, (2) the known answers of example/tri/test1.cpp,
-// test3.cpp, test5.cpp for the tridiagonal line solves, (3) doc/Memo.md:131-134 (pcr_eda
-// history == pcr history), (4) OUTPUTS OF THE REFERENCE'S OWN C++ PCR (src/cz_cpp/cz_pcr.cpp, compiled
-// unmodified behind oracle/ref_pcr_harness.cpp): the stage loop below (line_pcr_stages) equals them bit for
-// bit in double, tests/golden/ref_pcr_stages.json.  The rest of the kernel arithmetic (point sweeps, BLAS-1,
-// last-stage direct solves) is "parity unpinned by reference outputs" because no Fortran build of the
-// reference can be produced in this image or on the GPU box.
+// PARITY PINNING: the reference ships no golden vectors for this path.  What pins this oracle:
+// (1) OUTPUTS OF THE REFERENCE'S OWN FORTRAN, executed through a mechanical Fortran -> C translation of the unmodified
+// src/cz_f90/*.f90 (oracle/f90_to_c.py -> oracle/_ref/libczf90c_*.so; no Fortran compiler exists here): every routine
+// below, float and double, equals it bit for bit in every array argument -- and in res / flop / the dot products
+// with ORACLE_SUM=real -- and the reference's unmodified driver prints identical history files and console lines over
+// either library (tests/test_f90c_pin.py; committed vectors tests/golden/f90c_digests.json, f90c_histories.json);
+// (2) OUTPUTS OF THE REFERENCE'S OWN C++ PCR (src/cz_cpp/cz_pcr.cpp, compiled unmodified behind
+// oracle/ref_pcr_harness.cpp): the stage loop below (line_pcr_stages) equals them bit for bit in double,
+// tests/golden/ref_pcr_stages.json; (3) the reference's own UNMODIFIED C++ driver linked against this file
+// (oracle/Makefile -> oracle/_ref/cz_ref_*), reproducing the analytic-solution check `Error max` of
+// cz_Evaluate.cpp:550-563; (4) the known answers of example/tri/test1.cpp, test3.cpp, test5.cpp for the tridiagonal
+// line solves and doc/Memo.md:131-134 (pcr_eda history == pcr history); (5) an independent numpy restatement
+// (oracle/np_restatement.py).  Not covered by any of these: the reference's OpenMP reduction ORDER (it is order
+// dependent) -- hence the two reduction modes below.
 //
 // Reduction mode: env ORACLE_SUM=double (default) -> REAL products, double
 // accumulation, j-plane partials summed in j order (deterministic for any thread count);
@@ -70,13 +74,13 @@ struct Range {
   }
 };
 
+int g_sum_mode = -1;     // -1: read ORACLE_SUM on first use; 0 double, 1 real (oracle_set_sum_mode)
 bool real_mode() {
-  static int m = -1;
-  if (m < 0) {
+  if (g_sum_mode < 0) {
     const char* e = std::getenv("ORACLE_SUM");
-    m = (e && !strcmp(e, "real")) ? 1 : 0;
+    g_sum_mode = (e && !strcmp(e, "real")) ? 1 : 0;
   }
-  return m == 1;
+  return g_sum_mode == 1;
 }
 
 struct Acc {
@@ -387,6 +391,21 @@ void pcr_rb_(int* sz, int* idx, int* g, int* pn, int* ofst, int* color, REAL* x,
   const double nk = R.ked - R.kst + 1;
   *flop += (double)(R.jed - R.jst + 1) * (R.ied - R.ist + 1) *
            (nk * 6.0 + nk * (*pn - 1) * 14.0 + ipow2(*pn - 1) * 9.0 + nk * 6.0 + 6.0) * 0.5;
+  if (real_mode()) {
+    // 1-thread reference order: `res = res + dp*dp` (:647) adds every REAL product straight to the double
+    // argument, line after line -- no REAL partial sum in this routine (res1 is commented out, :646,659)
+    Acc acc;
+    acc.rm = false;
+    acc.d = *res;
+    LineWork w(R.kst, R.ked, *pn);
+    for (int j = R.jst; j <= R.jed; ++j)
+      for (int i = R.ist; i <= R.ied; ++i) {
+        if (((i + j) % 2 + 2) % 2 != *color) continue;
+        solve_line(w, G, x, x, rhs, msk, i, j, *pn, *omg, LAST_2X2, acc);
+      }
+    *res = acc.d;
+    return;
+  }
   const double s = reduce_planes(R.jst, R.jed, true, [&](int j, Acc& acc) {
     LineWork w(R.kst, R.ked, *pn);
     for (int i = R.ist; i <= R.ied; ++i) {
@@ -846,7 +865,7 @@ inline REAL maf_point_dp(const MafCell& m, const Grid& G, const REAL* p, long q,
 // coefficients that are exactly zero).
 void solve_line_maf(LineWork& w, const Grid& G, REAL* x, const REAL* rhs, const REAL* msk,
                     const REAL* XX, const REAL* YY, const REAL* ZZ, int i, int j, int pn, REAL omg,
-                    Acc& acc, REAL* tmp) {
+                    Acc& acc) {
   const REAL half = (REAL)0.5, two = (REAL)2.0;
   const int kst = w.kst, ked = w.ked;
   const REAL GX = two / (XX[i + 2] - XX[i]);
@@ -895,8 +914,7 @@ void solve_line_maf(LineWork& w, const Grid& G, REAL* x, const REAL* rhs, const 
     const REAL pp = x[q];
     const REAL dp = (w.d1[w.o(k)] - pp) * omg * msk[q];
     x[q] = pp + dp;
-    if (tmp) tmp[k + 1] = tmp[k + 1] + dp * dp;
-    acc.add(dp * dp);
+    acc.add(dp * dp);                                                  // :645 (the #else branch: _SVR undefined)
   }
 }
 
@@ -908,40 +926,35 @@ double pcr_maf_flop(const Range& R, int pn, double per2) {
                   ipow2(pn - 1) * per2 + nk * 6.0);
 }
 
-// The five MAF line routines add every dp*dp TWICE: once into res1 and once into tmp(k), and
-// tmp is summed into res1 at the end (cz_maf.f90:635-636, 657-660).  Double mode: 2 * sum;
-// real mode: the reference's 1-thread REAL accumulation order.
+// Residual of the five MAF line routines: `tmp(k) = tmp(k) + dp*dp` (+ `res1 = res1 + tmp(k)` after the loops) and
+// `res1 = res1 + dp*dp` are the two branches of `#ifdef _SVR` (cz_maf.f90:642-646, 659-663; -D_SVR only with
+// enable_VectorReduction=ON, CMakeLists.txt:227-230): every square is counted once, `tmp` is not touched in the
+// default build.  (Until round 2 this port read both statements as unconditional and doubled the sum; executing the
+// reference's own Fortran through oracle/f90_to_c.py showed the error.)
 void pcr_maf_sweep(int* sz, int* idx, int* g, int pn, int color /* <0: all lines, (j,i) order */, REAL* x,
                    REAL* msk, REAL* rhs, REAL* XX, REAL* YY, REAL* ZZ, REAL omg, double* res, REAL* tmp) {
+  (void)tmp;
   const Grid G(sz, *g);
   const Range R(idx);
-  for (int k = 0; k < sz[2] + 4; ++k) tmp[k] = (REAL)0;                // "tmp = 0.0"
   if (real_mode() || color < 0) {
     Acc acc;
     LineWork w(R.kst, R.ked, pn);
-    const bool rm = real_mode();
     for (int j = R.jst; j <= R.jed; ++j)
       for (int i = R.ist; i <= R.ied; ++i) {
         if (color >= 0 && ((i + j) % 2 + 2) % 2 != color) continue;
-        solve_line_maf(w, G, x, rhs, msk, XX, YY, ZZ, i, j, pn, omg, acc, rm ? tmp : nullptr);
+        solve_line_maf(w, G, x, rhs, msk, XX, YY, ZZ, i, j, pn, omg, acc);
       }
-    if (rm) {
-      REAL r1 = acc.r;
-      for (int k = R.kst; k <= R.ked; ++k) r1 = r1 + tmp[k + 1];
-      *res += (double)r1;
-    } else {
-      *res += 2.0 * acc.value();
-    }
+    *res += acc.value();
     return;
   }
   const double s = reduce_planes(R.jst, R.jed, true, [&](int j, Acc& acc) {
     LineWork w(R.kst, R.ked, pn);
     for (int i = R.ist; i <= R.ied; ++i) {
       if (((i + j) % 2 + 2) % 2 != color) continue;
-      solve_line_maf(w, G, x, rhs, msk, XX, YY, ZZ, i, j, pn, omg, acc, nullptr);
+      solve_line_maf(w, G, x, rhs, msk, XX, YY, ZZ, i, j, pn, omg, acc);
     }
   });
-  *res += 2.0 * s;
+  *res += s;
 }
 
 }  // namespace
@@ -1113,6 +1126,8 @@ void calc_ax_maf_(REAL* ap, REAL* p, int* sz, int* idx, int* g, REAL* X, REAL* Y
 // bench.py's CPU arm: the OpenMP runtime reads OMP_NUM_THREADS once, when it is loaded; a launcher
 // (torchrun) may have exported OMP_NUM_THREADS=1 before that.  These two calls set / report the team
 // size the kernels above actually run with (cz_Evaluate.cpp:34-39 reads the same value for its banner).
+// ORACLE_SUM from the harness: 1 = "real" (the reference's 1-thread order, one REAL accumulator), 0 = "double"
+void oracle_set_sum_mode(int real_order) { g_sum_mode = real_order ? 1 : 0; }
 void oracle_set_threads(int n) {
 #ifdef _OPENMP
   if (n > 0) omp_set_num_threads(n);

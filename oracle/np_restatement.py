@@ -6,8 +6,10 @@ independent.  Its only job is to pin the C++ oracle port (oracle/cz_f90_port.cpp
 separately, in different languages and with different loop structures, must agree bit for bit on random input
 (tests/test_oracle.py).  numpy's elementwise float32 / float64 arithmetic is IEEE, unfused and evaluated in the
 order written, which is what the reference's un-contracted CPU build does per cell.  The Fortran cannot be
-compiled in this image (no Fortran compiler), so this is the strongest check of the port available here;
-parity with reference OUTPUTS stays unpinned, see DESIGN.md section 2.
+compiled in this image (no Fortran compiler); since round 2 the port is ALSO pinned to the reference's own Fortran
+executed through a mechanical translation (oracle/f90_to_c.py, tests/test_f90c_pin.py) -- which
+caught the one error both restatements shared (the doubled residual of the _maf line routines, read off the same
+misunderstood #ifdef).
 
 Arrays follow tests/oracle_util.py: C order [j][i][k] with g = 2 guard layers, i.e. Fortran p(k,i,j).
 `idx` = (ist, ied, jst, jed, kst, ked) in Fortran indices (1-based inner numbering)."""
@@ -455,7 +457,7 @@ def _relax_lines_maf(x, msk, rhs, idx, pn, omg, jc, ic, XX, YY, ZZ):
     pp = x[jc, ic, ks]
     dp = (sol[:, P:P + n] - pp) * t(omg) * mk              # :630-637
     x[jc, ic, ks] = pp + dp
-    return 2.0 * float(np.sum((dp * dp).astype(np.float64)))   # every dp*dp is added to res1 AND tmp(k): :635-636, 657-660
+    return float(np.sum((dp * dp).astype(np.float64)))   # :645 (`tmp(k)` at :643 is the other branch of #ifdef _SVR)
 
 
 def pcr_rb_maf(x, msk, rhs, idx, pn, color, omg, XX, YY, ZZ):

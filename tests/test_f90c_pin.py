@@ -1,0 +1,213 @@
+"""Pins the oracle port (oracle/cz_f90_port.cpp) to OUTPUTS OF THE REFERENCE'S OWN FORTRAN.
+
+No Fortran compiler exists in this image or on the GPU box, so the reference's kernels (src/cz_f90/*.f90) are executed
+through a mechanical Fortran -> C translation of their unmodified text (oracle/f90_to_c.py; `make -C oracle f90c` builds
+oracle/_ref/libczf90c_*.so and links the reference's unmodified C++ driver to it -> oracle/_ref/cz_f90c_*).
+
+* everywhere (no /root/reference, no oracle/_ref needed): the port reproduces the committed golden vectors that the
+  translated Fortran wrote -- every array argument of every routine bit for bit, residual sums and dot products bit
+  for bit in the 1-thread summation order (tests/golden/f90c_digests.json), and the driver's residual histories digit
+  for digit (tests/golden/f90c_histories.json);
+* where oracle/_ref/libczf90c_*.so exists (this container; it also travels to the GPU box): the same comparison live,
+  on more grids, plus the bounds-check build's findings;
+* where /root/reference exists: the committed vectors and signatures are regenerated and must be unchanged.
+"""
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import f90c_harness as H
+import oracle_util as ou
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "golden"))
+import make_f90c_golden as MG   # noqa: E402
+
+DIGESTS = json.load(open(os.path.join(HERE, "golden", "f90c_digests.json")))
+HISTORIES = json.load(open(os.path.join(HERE, "golden", "f90c_histories.json")))
+SIGS = {s["name"]: s for s in json.load(open(H.SIG_JSON))}
+ROUTINES = [n for n in SIGS if n not in H.SKIP]
+HAVE_F90C = all(os.path.exists(H.f90c_path(r, c)) for r in ("f32", "f64") for c in (False, True))
+HAVE_REF = os.path.isdir(H.REF_F90)
+needs_f90c = pytest.mark.skipif(not HAVE_F90C, reason="oracle/_ref/libczf90c_*.so not built (needs /root/reference once)")
+
+
+@pytest.fixture(autouse=True)
+def _restore_sum_mode():
+    yield
+    for real in ("f32", "f64"):
+        ou.load(real).oracle_set_sum_mode(0)
+
+
+def _port(real, real_order):
+    lib = ou.load(real)
+    lib.oracle_set_sum_mode(1 if real_order else 0)
+    return lib
+
+
+def test_signature_table_covers_the_fortran_core():
+    """39 subroutines = the five files of the reference's FCORE library (src/cz_f90/CMakeLists.txt); the 35 symbols of
+    cz_Ffunc.h that the path uses are all among them, with the argument counts cubez_b200/ffi.py binds."""
+    import cubez_b200.ffi as ffi
+    assert len(SIGS) == 39
+    for sym, nargs in ffi.REFERENCE_SYMBOLS.items():
+        assert sym[:-1] in SIGS, sym
+        assert len(SIGS[sym[:-1]]["args"]) == nargs, sym
+    if HAVE_REF:
+        assert json.loads(json.dumps(H.signatures())) == list(SIGS.values()), "regenerate: tests/golden/make_f90c_golden.py"
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+def test_port_reproduces_the_reference_fortran_golden_vectors(real):
+    """Runs without the reference: 200 (routine, grid) cases per precision.  Summation in the reference's 1-thread
+    order (ORACLE_SUM=real) makes residuals and dot products comparable bit for bit as well."""
+    port = _port(real, True)
+    n = 0
+    for case in DIGESTS:
+        if case["real"] != real:
+            continue
+        sig = SIGS[case["routine"]]
+        got = MG.record(sig, MG.run_routine(port, sig, real, case["sz"]))
+        assert got == case["out"], (case["routine"], case["sz"], [k for k in got if got[k] != case["out"][k]])
+        n += 1
+    assert n >= 190
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+def test_port_default_summation_differs_in_the_sums_only(real):
+    """ORACLE_SUM=double (what the GPU tests compare with): identical fields, sums within the accumulation error."""
+    port = _port(real, False)
+    tol = 3e-6 if real == "f32" else 1e-13
+    for case in DIGESTS:
+        if case["real"] != real or case["sz"] != MG.SIZES[0]:
+            continue
+        sig = SIGS[case["routine"]]
+        got = MG.record(sig, MG.run_routine(port, sig, real, case["sz"]))
+        for k, v in got.items():
+            if k in ("res", "r"):
+                assert float.fromhex(v) == pytest.approx(float.fromhex(case["out"][k]), rel=tol), (case["routine"], k)
+            else:
+                assert v == case["out"][k], (case["routine"], k)
+
+
+def _oracle_history(c):
+    o = ou.OracleCZ([c["n"]] * 3, c["real"])
+    P, RHS = o.setup_laplace()
+    if c["solver"].startswith("pbicgstab"):
+        itr, res, hist = o.pbicgstab(P, RHS, c["itr_max"], float(c["coef"]), c["precond"], maf=c["solver"].endswith("_maf"))
+    else:
+        itr, res, hist = o.stationary(c["solver"], P, RHS, c["itr_max"], float(c["coef"]))
+    return ["%13.6e" % h for h in hist]
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+def test_solver_loops_over_the_port_reproduce_the_reference_fortran_histories(real):
+    """The reference's unmodified driver over its own (translated) Fortran wrote these histories; the Python mirror of
+    the driver loops (tests/oracle_util.py) over the port prints the same digits, iteration for iteration."""
+    _port(real, True)
+    n = 0
+    for c in HISTORIES:
+        if c["real"] != real or c["n"] > 32:
+            continue
+        assert _oracle_history(c) == ["%13s" % h for h in c["history"]], (c["solver"], c["precond"])
+        n += 1
+    assert n >= 8
+
+
+# ------------------------------------------------------------------------------------------------------------
+# live comparison against the translated Fortran
+# ------------------------------------------------------------------------------------------------------------
+
+LIVE_SIZES = [[12, 7, 23], [9, 10, 34], [6, 5, 66], [5, 6, 18], [7, 5, 31], [5, 5, 50], [4, 4, 258]]
+
+
+@needs_f90c
+@pytest.mark.parametrize("real", ["f32", "f64"])
+@pytest.mark.parametrize("routine", ROUTINES)
+def test_port_equals_translated_fortran_live(real, routine):
+    sig = SIGS[routine]
+    port = _port(real, True)
+    ref = H.load_f90c(real)
+    for sz in LIVE_SIZES:
+        if not MG.in_reference_domain(routine, sz):
+            continue
+        a = MG.run_routine(port, sig, real, sz)
+        b = MG.run_routine(ref, sig, real, sz)
+        for nm in H.compared(sig):
+            assert np.array_equal(a[nm].view(np.uint8), b[nm].view(np.uint8)), (routine, sz, nm)
+
+
+@needs_f90c
+def test_bounds_check_build_same_results_and_known_findings():
+    """The F2C_BOUNDS build (index check on every array reference, the access itself unchanged) gives the same bits.
+    On the driver's own line lengths (2^m - 2: 62 here; 14..510 checked when the golden vectors were made) NO access of
+    any routine leaves its declared bounds.  On other lengths (32 here) the zero-padded line routines (pcr_eda, pcr_esa,
+    pcr_rb_esa, pcr_j_esa and their _maf twins) read a, d(k + 2^(pn-1)) beyond idx(5)+s and store d1 / dw beyond
+    sz(3)+2 -- past the driver's work arrays too (cz_Evaluate.cpp:255-263, 300-311); the port's zero padding is the
+    defined reading of those accesses, and pcr_eda's are excluded (MG.in_reference_domain) because it ALLOCATES a, c, d."""
+    chk = H.load_f90c("f32", True)
+    ref = H.load_f90c("f32", False)
+    found = {}
+    for routine in ROUTINES:
+        sig = SIGS[routine]
+        for sz in ([6, 6, 64], [5, 5, 34]):     # 62- and 32-cell lines
+            if not MG.in_reference_domain(routine, sz):
+                continue
+            chk.f2c_bounds_reset()
+            a = MG.run_routine(chk, sig, "f32", sz)
+            b = MG.run_routine(ref, sig, "f32", sz)
+            for nm in H.compared(sig):
+                assert np.array_equal(a[nm].view(np.uint8), b[nm].view(np.uint8)), (routine, sz, nm)
+            for (loc, arr, d, i, lo, hi, cnt) in H.bounds_report(chk):
+                found.setdefault((routine, sz[2] - 2), []).append((loc, arr, i, lo, hi))
+    assert not {k: v for k, v in found.items() if k[1] == 62}
+    assert sorted({k[0] for k in found}) == ["pcr_esa", "pcr_esa_maf", "pcr_j_esa", "pcr_rb_esa", "pcr_rb_esa_maf"]
+    assert {arr for v in found.values() for (_, arr, _, _, _) in v} == {"a", "d", "d1", "dw"}
+    point = [r for r in ROUTINES if not r.startswith(("pcr", "tdma"))]
+    assert not [k for k in found if k[0] in point], "point kernels / BLAS-1 stay inside their declared bounds"
+
+
+def _run_driver(exe, c, env_extra):
+    return MG.driver_case(exe, c["real"], c["n"], c["solver"], c["itr_max"], c["coef"], c["precond"], env_extra)
+
+
+@pytest.mark.skipif(not (ou.ref_binary("cz_f90c_f32") and ou.ref_binary("cz_ref_f32")), reason="oracle/_ref drivers not built")
+def test_reference_driver_prints_the_same_over_port_and_over_its_own_fortran():
+    """Same unmodified driver binary sources, two kernel libraries: the history files and the console lines
+    (Iter / Res / Error max and its location) are text-identical.  32^3 cases (the 64^3 ones take a minute)."""
+    n = 0
+    for c in HISTORIES:
+        if c["n"] > 32:
+            continue
+        a = _run_driver("cz_ref", c, {"ORACLE_SUM": "real"})
+        b = _run_driver("cz_f90c", c, None)
+        assert a["history"] == b["history"] == c["history"], (c["solver"], c["precond"])
+        assert a["console"] == b["console"] == c["console"], (c["solver"], c["precond"])
+        n += 1
+    assert n >= 30
+
+
+@pytest.mark.skipif(not HAVE_REF, reason="needs /root/reference")
+def test_translator_is_deterministic_and_rejects_what_it_does_not_know(tmp_path):
+    sys.path.insert(0, os.path.join(ou.ROOT, "oracle"))
+    import f90_to_c
+    src = os.path.join(H.REF_F90, "cz_solver.f90")
+    a, names = f90_to_c.translate_file(src, "f32")
+    b, _ = f90_to_c.translate_file(src, "f32")
+    assert a == b and "psor2sma_core" in names
+    # Fortran's grammar, not C's: -e*ap*a(kl) negates the product; REAL literals are single precision in f32
+    assert "(-((v_e * v_ap) * v_a[" in a and "(1.0f / 6.0f)" in a
+    assert "(18.0f * ((double)" in a and "(18.0e0 * 0.5e0)" in a     # 18.0 is REAL, 18.0d0*0.5d0 double
+    bad = tmp_path / "bad.f90"
+    for text in ("subroutine s(x)\nimplicit none\nreal :: x\nx = y\nend subroutine s\n",                  # undeclared name
+                 "subroutine s(x)\nimplicit none\nreal :: x\nx = x**2.0\nend subroutine s\n",             # real power
+                 "subroutine s(x)\nimplicit none\nreal :: x\ncall t(x)\nend subroutine s\n",              # call
+                 "subroutine s(x)\nimplicit none\nreal :: x\nwhere (x > 0) x = 1\nend subroutine s\n"):   # where
+        bad.write_text(text)
+        with pytest.raises((SyntaxError, NameError, TypeError)):
+            f90_to_c.translate_file(str(bad), "f32")

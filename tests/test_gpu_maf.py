@@ -95,7 +95,7 @@ def test_maf_point_sweeps_operator_and_pivot(real, sz, host_ptrs):
 @pytest.mark.parametrize("sz", [[9, 9, 9], [12, 7, 23], [10, 8, 34], [8, 6, 66], [6, 6, 131], [6, 5, 300]])
 def test_maf_line_sor_sweeps(real, sz):
     """The five MAF line routines (pn-1 PCR stages + 2x2, line-dependent coefficients) incl. line lengths of 2^m and
-    2^m +- 1 cells; res is TWICE the sum of squares, as in the reference (cz_maf.f90:635-636, 657-660)."""
+    2^m +- 1 cells; res is the sum of squares (cz_maf.f90:645; the `tmp(k)` statement at :643 is the -D_SVR branch)."""
     cz, o = _mk(sz, real)
     X, B = ou.random_fields(o.shape, o.dt)
     mesh = o.mesh(stretch=0.3)

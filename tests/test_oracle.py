@@ -228,11 +228,11 @@ def test_maf_twins_on_the_uniform_mesh_reproduce_the_plain_solvers():
         a, b = _golden(real, 32, solver), _golden(real, 32, solver + "_maf")
         assert a["itr"] == b["itr"]
         np.testing.assert_allclose([float(h) for h in b["history"]], [float(h) for h in a["history"]], rtol=rel)
-    # the five MAF line routines add every dp^2 twice (cz_maf.f90:635-636, 657-660): residuals are sqrt(2) larger
+    # the line routines too (round 1 had their residual sqrt(2) too large: `tmp(k) = tmp(k) + dp*dp` and
+    # `res1 = res1 + dp*dp` are the two branches of #ifdef _SVR, cz_maf.f90:642-646, not two statements)
     a, b = _golden("f64", 32, "pcr_rb"), _golden("f64", 32, "pcr_rb_maf")
-    m = min(len(a["history"]), len(b["history"]))
-    np.testing.assert_allclose([float(h) for h in b["history"][:m]], np.sqrt(2.0) * np.array([float(h) for h in a["history"][:m]]),
-                               rtol=2e-6)
+    assert a["itr"] == b["itr"]
+    np.testing.assert_allclose([float(h) for h in b["history"]], [float(h) for h in a["history"]], rtol=2e-4)
     assert _golden("f32", 32, "pcr_maf")["history"] == _golden("f32", 32, "pcr_eda_maf")["history"] == _golden("f32", 32, "pcr_esa_maf")["history"]
     assert _golden("f32", 32, "pcr_rb_maf")["history"] == _golden("f32", 32, "pcr_rb_esa_maf")["history"]
     for c in GOLDEN:
