@@ -145,3 +145,33 @@ def digest(vals, names):
         h.update(nm.encode())
         h.update(np.ascontiguousarray(vals[nm]).tobytes())
     return h.hexdigest()
+
+
+def check_library_against_fortran_vectors(lib, real, sizes, digests, sigs, run_routine, record):
+    """A library that exports the reference's symbols (the product, or its CPU-emulated build) against the committed
+    outputs of the reference's translated Fortran: every array argument bit for bit; double-accumulated sums (the
+    library sums REAL products in double, the 1-thread reference in REAL) and the analytic field within a tolerance.
+    Not compared: `src` of pcr_j_esa (a work field the library does not fill), tdma_* (not on the path)."""
+    sum_tol = 3e-6 if real == "f32" else 1e-13
+    n = 0
+    for case in digests:
+        name = case["routine"]
+        if case["real"] != real or case["sz"] not in sizes or name.startswith("tdma"):
+            continue
+        sig = sigs[name]
+        vals = run_routine(lib, sig, real, case["sz"])
+        got = record(sig, vals)
+        for k, v in got.items():
+            want = case["out"][k]
+            if k in ("res", "r"):
+                assert abs(float.fromhex(v) - float.fromhex(want)) <= sum_tol * max(abs(float.fromhex(want)), 1e-30), (name, case["sz"], k)
+            elif k == "flop":
+                assert abs(float.fromhex(v) - float.fromhex(want)) <= 1e-12 * abs(float.fromhex(want)), (name, k)
+            elif k == "src" and name == "pcr_j_esa":
+                continue
+            elif k == "e" and name == "exact_t":
+                continue      # device sin / sinh: <= 8 ulp, tests/test_gpu_kernels.py::test_bc_exact_err
+            else:
+                assert v == want, (name, case["sz"], k)
+        n += 1
+    return n

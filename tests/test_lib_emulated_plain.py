@@ -153,3 +153,21 @@ def test_emulated_line_sor_solves_match_golden():
     assert abs(itr - g["itr"]) <= 1
     m = min(len(hist), len(g["history"]))
     np.testing.assert_allclose(hist[:m], [float(h) for h in g["history"]][:m], rtol=1e-4, atol=1e-12)
+
+
+@pytest.mark.parametrize("real", ["f32", "f64"])
+def test_emulated_library_reproduces_the_reference_fortran_vectors(real):
+    """The library's own per-call ABI (CPU-emulated build) against the committed outputs of the reference's Fortran
+    executed through oracle/f90_to_c.py: every array argument bit for bit on non-unit coefficients and a stretched mesh
+    (the -m gpu twin is tests/test_gpu_f90c_vectors.py)."""
+    import json
+    import os
+    import sys
+    import f90c_harness as H
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, os.path.join(here, "golden"))
+    import make_f90c_golden as MG
+    digests = json.load(open(os.path.join(here, "golden", "f90c_digests.json")))
+    sigs = {s["name"]: s for s in json.load(open(H.SIG_JSON))}
+    n = H.check_library_against_fortran_vectors(_emu(real), real, MG.SIZES[:4], digests, sigs, MG.run_routine, MG.record)
+    assert n >= 130
