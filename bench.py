@@ -22,8 +22,11 @@ One JSON line on rank 0:
                e2e.to_convergence (N=1): the same call run until res < 1e-5 (256^3 and 1024^3 sor2sma)
   roofline     dominant kernel (fused two-colour sweep k_rb2_pk): algorithmic bytes (4R = 16 B per
                cell.iteration) / measured time per iteration, against the measured HBM copy bandwidth
-  cpu_baseline the CPU oracle port of the reference kernel (oracle/, "port") on all host cores, bounded sample,
-               in a CHILD process whose OpenMP team size is set explicitly and reported from omp_get_max_threads()
+  cpu_baseline the reference's own psor2sma_core -- its Fortran text with its OpenMP directives, translated mechanically
+               to C (oracle/f90_to_c.py --openmp -> oracle/_ref/libczf90c_omp_f32.so, gcc -O3 -fopenmp; kind "reference")
+               -- or, where that prebuilt file is absent, the hand-written port (oracle/cz_f90_port.cpp, kind "port"),
+               on all host cores, bounded sample, in a CHILD process whose OpenMP team size is set explicitly and
+               reported from omp_get_max_threads()
   also         PBiCGstab+sor2sma, Jacobi and line SOR on the same grid; f64 sor2sma / PBiCGstab at 512^3 (N=1)
   time_to_convergence  BASELINE.json configs[0..3] (+ the 1024^3 solvers of configs[4]) solved to res < 1e-5:
                iterations and device time of the solver loop, next to the oracle's iteration count (committed
@@ -183,9 +186,19 @@ def cpu_worker(mode, steps, warmup):
     threads = int(lib.oracle_max_threads())
     n = N_CUBE
     if mode in ("sample", "full"):
-        # psor2sma_core (cz_solver.f90:404-493) restated in oracle/cz_f90_port.cpp, both colours per step
+        # psor2sma_core (cz_solver.f90:404-493), both colours per step.  Preferred: the reference's OWN Fortran text
+        # with its OpenMP directives, translated mechanically to C (oracle/f90_to_c.py --openmp) and compiled with the
+        # reference's GNU flags (-O3 -fopenmp) -> oracle/_ref/libczf90c_omp_f32.so, kind "reference".  Without that
+        # prebuilt file (it needs /root/reference once): the hand-written port oracle/cz_f90_port.cpp, kind "port".
         ny = n if mode == "full" else min(128, n)
         o = ou.OracleCZ([n, n, n], "f32", sz=[n, ny, n])
+        kind, what_code = "port", "oracle port of psor2sma_core"
+        ref_so = os.path.join(ROOT, "oracle", "_ref", "libczf90c_omp_f32.so")
+        if os.path.exists(ref_so) and os.environ.get("CZB_BENCH_CPU", "") != "port":
+            import cubez_b200.ffi as ffi
+            o.dll = ffi.bind_reference_symbols(C.CDLL(ref_so))     # same libgomp, same team size as reported below
+            kind, what_code = "reference", ("the reference's psor2sma_core, cz_solver.f90:404-493 with its !$OMP "
+                                            "directives, translated to C by oracle/f90_to_c.py, gcc -O3 -fopenmp")
         X, B = o.setup_laplace()
         from cubez_b200 import synth
         synth.fill(X, o.sz)
@@ -200,9 +213,10 @@ def cpu_worker(mode, steps, warmup):
             o.sweep_rb(X, B, res)
         dt = time.perf_counter() - t0
         what = ("the whole %d^3 grid" % n) if ny == n else ("a %dx%dx%d j-slab of the %d^3 grid" % (n, ny, n, n))
-        print(json.dumps({"value": cells * steps / dt / 1e9, "ms": dt / steps * 1e3, "cores": threads,
-                          "sample": "%d iterations of sor2sma (oracle port of psor2sma_core, OpenMP %d threads = "
-                                    "omp_get_max_threads(), %d usable cores) on %s per step" % (steps, threads, cores, what)}),
+        print(json.dumps({"value": cells * steps / dt / 1e9, "ms": dt / steps * 1e3, "cores": threads, "kind": kind,
+                          "sample": "%d iterations of sor2sma (%s; OpenMP %d threads = "
+                                    "omp_get_max_threads(), %d usable cores) on %s per step"
+                                    % (steps, what_code, threads, cores, what)}),
               flush=True)
         return
     # mode == "ttc": the reference's timed region is the solver loop (cz_Evaluate.cpp:419-421).  Small configs run to
@@ -279,7 +293,7 @@ def run_reference(args, rank):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"], "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_string(N_CUBE, N_Y, False)},
-        "cpu_baseline": {"value": r["value"], "unit": "GLUPS", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "cpu_baseline": {"value": r["value"], "unit": "GLUPS", "cores": r["cores"], "kind": r.get("kind", "port"), "sample": r["sample"]},
         "e2e": {"value": r["value"], "unit": "GLUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
 
@@ -496,8 +510,8 @@ def run_gpu(args, rank, world, local_rank):
         if world == 1 and not args.no_cpu and rank == 0:
             r = run_cpu_child("sample", 3, 1)
             if r:
-                line["cpu_baseline"] = {"value": r["value"], "unit": "GLUPS", "cores": r["cores"], "kind": "port",
-                                        "sample": r["sample"]}
+                line["cpu_baseline"] = {"value": r["value"], "unit": "GLUPS", "cores": r["cores"],
+                                        "kind": r.get("kind", "port"), "sample": r["sample"]}
         if not args.no_ttc and not args.no_also:
             if world == 1:
                 ttc = time_to_convergence()

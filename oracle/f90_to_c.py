@@ -98,11 +98,25 @@ def strip_comment(text):
     return text
 
 
-def logical_statements(path, defines):
-    """Join continuation lines, lower-case outside strings, split at `;`, expand `include`."""
+def logical_statements(path, defines, openmp=False):
+    """Join continuation lines, lower-case outside strings, split at `;`, expand `include`.  openmp: `!$omp` sentinel
+    lines (with their own `&` continuation) are kept as statements "!$omp <directive>" instead of being comments."""
     stmts = []
     cur, cur_loc = "", None
+    omp, omp_loc = "", None
     for (f, n, raw) in preprocess(path, defines):
+        if openmp and raw.strip().lower().startswith("!$omp"):
+            body = strip_comment(raw.strip()[5:]).strip()
+            if omp and body.startswith("&"):
+                body = body[1:].lstrip()
+            if omp_loc is None:
+                omp_loc = (f, n)
+            if body.endswith("&"):
+                omp += body[:-1] + " "
+                continue
+            stmts.append((omp_loc[0], omp_loc[1], "!$omp " + " ".join((omp + body).lower().split())))
+            omp, omp_loc = "", None
+            continue
         t = strip_comment(raw).strip()
         if not t:
             continue
@@ -127,7 +141,7 @@ def logical_statements(path, defines):
         m = re.match(r"include\s+['\"](.+)['\"]$", s)
         if m:
             inc = os.path.join(os.path.dirname(f), m.group(1))
-            out.extend(logical_statements(inc, defines))
+            out.extend(logical_statements(inc, defines, openmp))
         else:
             out.append((f, n, s))
     return out
@@ -626,7 +640,51 @@ def parse_decl(u, s, loc):
     return True
 
 
-def translate_unit(u, em):
+class OmpUnsupported(Exception):
+    pass
+
+
+def omp_clauses(text, u, where, extra_private=()):
+    """Fortran OpenMP clause list -> C clause list.  Only local scalars may be privatised / reduced (dummy arguments
+    are pointers in C, whole arrays would need copies): anything else raises OmpUnsupported and the caller translates
+    the subroutine without its directives."""
+    out, listed = [], set()
+    rest = text.strip()
+    while rest:
+        m = re.match(r"^(schedule|collapse|reduction|private|firstprivate)\s*\(([^)]*)\)\s*", rest)
+        if not m:
+            raise OmpUnsupported("%s: clause %r" % (where, rest))
+        kw, arg = m.group(1), m.group(2).strip()
+        rest = rest[m.end():]
+        if kw == "schedule":
+            if arg != "static":
+                raise OmpUnsupported("%s: schedule(%s)" % (where, arg))
+            out.append("schedule(static)")
+        elif kw == "collapse":
+            out.append("collapse(%d)" % int(arg))
+        else:
+            op = ""
+            if kw == "reduction":
+                op, arg = [x.strip() for x in arg.split(":", 1)]
+                if op != "+":
+                    raise OmpUnsupported("%s: reduction(%s)" % (where, op))
+                op = "+:"
+            names = [x.strip() for x in arg.split(",") if x.strip()]
+            for nm in names:
+                sy = u.syms.get(nm)
+                if sy is None or sy.is_arg or sy.dims is not None or sy.param is not None:
+                    raise OmpUnsupported("%s: %s(%s) is not a local scalar" % (where, kw, nm))
+                listed.add(nm)
+            out.append("%s(%s%s)" % (kw, op, ", ".join("v_" + nm for nm in names)))
+    more = [nm for nm in extra_private if nm not in listed]
+    if more:
+        # Fortran: the iteration variable of a sequential loop inside a parallel construct is private (OpenMP 2.9.1.1);
+        # in C it is shared unless listed
+        out.append("private(%s)" % ", ".join("v_" + nm for nm in more))
+    return " ".join(out)
+
+
+def translate_unit(u, em, openmp=False):
     C = []
     # ---- specification part
     k = 0
@@ -698,7 +756,8 @@ def translate_unit(u, em):
                      % (nm, em.ctype(s.type), " * ".join(total), em.ctype(s.type)))
     # ---- executable part
     ind = 1
-    blocks = []        # "do" | "if"
+    blocks = []        # "do" | "if" | "omp" | "do_omp_outer" | "do_omp_inner"
+    omp_skip = [0]
     tmp = [0]
 
     def P(where):
@@ -718,12 +777,14 @@ def translate_unit(u, em):
     def simple(s, where):
         """one action statement -> C text (no trailing newline)"""
         if s == "cycle":
-            if "do" not in blocks:
+            if not any(b.startswith("do") for b in blocks):
                 raise SyntaxError("%s: cycle outside do" % where)
             return "continue;"
         if s == "exit":
-            if "do" not in blocks:
+            if not any(b.startswith("do") for b in blocks):
                 raise SyntaxError("%s: exit outside do" % where)
+            if blocks and blocks[-1].startswith("do_omp"):
+                raise OmpUnsupported("%s: exit from a worksharing loop" % where)
             return "break;"
         if s == "return":
             return "goto f2c_return;"
@@ -773,12 +834,91 @@ def translate_unit(u, em):
         # Fortran converts the value to the type of the variable on assignment; so does C
         return "%s = %s;" % (em.gen(lhs, u.syms, where), em.gen(rhs, u.syms, where))
 
-    for (f, n, s) in exe:
+    DO_RE = re.compile(r"^do\s+(\w+)\s*=\s*(.*)$")
+
+    def region_do_vars(start, end_marker):
+        """iteration variables of every do statement between exe[start] and the matching `!$omp end ...`"""
+        names = []
+        for (_, _, t) in exe[start:]:
+            if t.startswith("!$omp " + end_marker):
+                return names
+            mm = DO_RE.match(t)
+            if mm and mm.group(1) not in names:
+                names.append(mm.group(1))
+        raise OmpUnsupported("%s: no `!$omp %s`" % (u.loc, end_marker))
+
+    omp_for = None      # pending (pragma text, collapse count) for the next do statement(s)
+    for pos, (f, n, s) in enumerate(exe):
         where = "%s:%d" % (os.path.basename(f), n)
         pad = "  " * ind
+        if s.startswith("!$omp "):
+            d = s[6:].strip()
+            if d.startswith("end parallel do") or d.startswith("end do"):
+                continue
+            if d.startswith("end parallel"):
+                if not blocks or blocks.pop() != "omp":
+                    raise OmpUnsupported("%s: end parallel" % where)
+                ind -= 1
+                C.append("%s}   /* %s: end parallel */" % ("  " * ind, where))
+                continue
+            if omp_for is not None:
+                raise OmpUnsupported("%s: directive between `do` directive and loop" % where)
+            if d.startswith("parallel do"):
+                cl = omp_clauses(d[len("parallel do"):], u, where, region_do_vars(pos + 1, "end parallel do"))
+                omp_for = ("#pragma omp parallel for " + cl, where)
+            elif d.startswith("parallel"):
+                cl = omp_clauses(d[len("parallel"):], u, where, region_do_vars(pos + 1, "end parallel"))
+                C.append("%s/* %s */" % (pad, where))
+                C.append("#pragma omp parallel " + cl)
+                C.append("%s{" % pad)
+                blocks.append("omp")
+                ind += 1
+            elif d.startswith("do"):
+                nowait = ""
+                for (_, _, t) in exe[pos + 1:]:
+                    if t.startswith("!$omp end do"):
+                        nowait = " nowait" if "nowait" in t else ""
+                        break
+                omp_for = ("#pragma omp for " + omp_clauses(d[2:], u, where) + nowait, where)
+            else:
+                raise OmpUnsupported("%s: directive %r" % (where, d))
+            continue
         if DECL_RE.match(s) or s.startswith("parameter"):
             raise SyntaxError("%s: declaration after the first executable statement" % where)
-        m = re.match(r"^do\s+(\w+)\s*=\s*(.*)$", s)
+        m = DO_RE.match(s)
+        if omp_for is not None:
+            # the loops associated with the worksharing construct, in OpenMP's canonical form: upper bounds hoisted
+            # (Fortran evaluates them once anyway), unit stride, nothing between the collapsed loops
+            pragma, pwhere = omp_for
+            omp_for = None
+            mc = re.search(r"collapse\((\d+)\)", pragma)
+            ncol = int(mc.group(1)) if mc else 1
+            loops = []
+            for (ff, nn, t) in exe[pos:pos + ncol]:
+                mm = DO_RE.match(t)
+                if not mm or len(split_top(mm.group(2))) != 2:
+                    raise OmpUnsupported("%s: collapse(%d) needs %d unit-stride do statements" % (pwhere, ncol, ncol))
+                w2 = "%s:%d" % (os.path.basename(ff), nn)
+                lo, hi = split_top(mm.group(2))
+                sy = u.syms.get(mm.group(1))
+                if sy is None or sy.type != "int" or sy.dims is not None or sy.is_arg:
+                    raise TypeError("%s: do variable %s" % (w2, mm.group(1)))
+                tmp[0] += 1
+                loops.append((mm.group(1), expr(lo, w2, "int"), expr(hi, w2, "int"), tmp[0], w2))
+            C.append("%s/* %s */ { const int %s;" % (pad, pwhere, ", ".join("f2c_hi%d = %s" % (t, hi) for (_, _, hi, t, _) in loops)))
+            C.append(pragma)
+            for k2, (var, lo, hi, t, w2) in enumerate(loops):
+                C.append("%sfor (v_%s = %s; v_%s <= f2c_hi%d; v_%s += 1) {   /* %s */" % (pad, var, lo, var, t, var, w2))
+                blocks.append("do_omp_outer" if k2 == 0 else "do_omp_inner")
+                ind += 1
+            skip_do = ncol - 1
+            omp_skip[0] = skip_do
+            continue
+        if omp_skip[0] > 0:
+            if not m:
+                raise OmpUnsupported("%s: statement between collapsed loops" % where)
+            omp_skip[0] -= 1
+            continue
         if m and u.syms.get(m.group(1)) is not None and len(split_top(m.group(2))) in (2, 3):
             var = m.group(1)
             sy = u.syms[var]
@@ -798,10 +938,11 @@ def translate_unit(u, em):
             ind += 1
             continue
         if re.match(r"^end\s*do$", s):
-            if not blocks or blocks.pop() != "do":
+            kind = blocks.pop() if blocks else None
+            if kind not in ("do", "do_omp_outer", "do_omp_inner"):
                 raise SyntaxError("%s: end do without do" % where)
             ind -= 1
-            C.append("%s} }" % ("  " * ind))
+            C.append("%s%s" % ("  " * ind, "}" if kind == "do_omp_inner" else "} }"))
             continue
         if s.startswith("if") and re.match(r"^if\s*\(", s):
             i0 = s.index("(")
@@ -886,13 +1027,27 @@ int f2c_bounds_report(char* buf, int len) {
 """
 
 
-def translate_file(path, real, defines=None):
-    stmts = logical_statements(path, defines or {})
-    units = parse_units(stmts)
+def translate_file(path, real, defines=None, openmp=False, report=None):
+    """openmp: map the reference's `!$OMP` directives to C pragmas, subroutine by subroutine; a subroutine whose
+    directives need what the mapping does not cover (dummy arguments or arrays in private / reduction clauses) is
+    translated without them, i.e. serially.  report: dict name -> "openmp" | reason it stayed serial."""
     em = Emitter(real)
     out = [PRELUDE % {"src": path, "real": real}]
+    serial = {u.name: u for u in parse_units(logical_statements(path, defines or {}))}
+    units = parse_units(logical_statements(path, defines or {}, openmp)) if openmp else list(serial.values())
     for u in units:
-        out.append(translate_unit(u, em))
+        if not openmp:
+            out.append(translate_unit(u, em))
+            continue
+        try:
+            text = translate_unit(u, em, openmp=True)
+            how = "openmp" if "#pragma omp" in text else "no directives"
+        except OmpUnsupported as ex:
+            text = translate_unit(serial[u.name], em)
+            how = "serial: " + str(ex)
+        if report is not None:
+            report[u.name] = how
+        out.append(text)
     return "\n".join(out), [u.name for u in units]
 
 
@@ -912,17 +1067,23 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--real", choices=("f32", "f64"), required=True)
     ap.add_argument("--out", required=True)
+    ap.add_argument("--openmp", action="store_true", help="map the !$OMP directives to C pragmas where possible")
     ap.add_argument("files", nargs="+")
     a = ap.parse_args()
     os.makedirs(a.out, exist_ok=True)
+    report = {}
     for f in a.files:
-        text, names = translate_file(f, a.real)
+        text, names = translate_file(f, a.real, openmp=a.openmp, report=report)
         dst = os.path.join(a.out, os.path.splitext(os.path.basename(f))[0] + ".c")
         with open(dst, "w") as fh:
             fh.write(text)
         print("%s -> %s: %s" % (f, dst, " ".join(names)), file=sys.stderr)
     with open(os.path.join(a.out, "f2c_runtime.c"), "w") as fh:
         fh.write(RUNTIME)
+    if a.openmp:
+        with open(os.path.join(a.out, "openmp_report.txt"), "w") as fh:
+            for k, v in report.items():
+                fh.write("%s: %s\n" % (k, v))
 
 
 if __name__ == "__main__":

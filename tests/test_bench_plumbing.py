@@ -46,6 +46,11 @@ def test_cpu_arm_runs_with_an_explicit_openmp_team(monkeypatch):
     assert r is not None and r["value"] > 0
     assert r["cores"] == bench.host_cores()
     assert "omp_get_max_threads" in r["sample"]
+    # the reference's own Fortran (translated, OpenMP mapped) when it was built here, else the hand-written port
+    have = os.path.exists(os.path.join(os.path.dirname(os.path.abspath(bench.__file__)), "oracle", "_ref", "libczf90c_omp_f32.so"))
+    assert r["kind"] == ("reference" if have else "port")
+    monkeypatch.setenv("CZB_BENCH_CPU", "port")
+    assert bench.run_cpu_child("sample", steps=1, warmup=1, timeout=300)["kind"] == "port"
 
 
 def test_golden_keys_of_the_ttc_cases_exist():

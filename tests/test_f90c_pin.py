@@ -211,3 +211,42 @@ def test_translator_is_deterministic_and_rejects_what_it_does_not_know(tmp_path)
         bad.write_text(text)
         with pytest.raises((SyntaxError, NameError, TypeError)):
             f90_to_c.translate_file(str(bad), "f32")
+
+
+OMP_SO = {r: os.path.join(ou.ROOT, "oracle", "_ref", "libczf90c_omp_%s.so" % r) for r in ("f32", "f64")}
+
+
+@pytest.mark.skipif(not (HAVE_F90C and all(os.path.exists(p) for p in OMP_SO.values())), reason="oracle/_ref/libczf90c_omp_*.so not built")
+@pytest.mark.parametrize("real", ["f32", "f64"])
+def test_openmp_translation_gives_the_serial_fields(real):
+    """`f90_to_c.py --openmp` maps the reference's `!$OMP` directives to C pragmas (the CPU arm bench.py times).  With 4
+    threads every array of the race-free routines equals the serial translation bit for bit; sums differ by the
+    reduction order only.  Not compared: `psor`, `psor_maf` (in-place Gauss-Seidel inside a parallel loop), `err_t`
+    (unsynchronised max) and `jacobi`, `jacobi_maf`: their `END DO NOWAIT` lets a thread start the copy-back
+    `p = wk2` while its neighbours still read `p` (cz_solver.f90:355-372) -- races of the reference itself, which is
+    why the oracle states the 1-thread order."""
+    gomp = C.CDLL("libgomp.so.1")
+    ser, omp = H.load_f90c(real), C.CDLL(OMP_SO[real])
+    report = dict(l.strip().split(": ", 1) for l in open(os.path.join(ou.ROOT, "oracle", "_ref", "f90c_omp", real, "openmp_report.txt")))
+    mapped = [k for k, v in report.items() if v == "openmp"]
+    assert {"psor2sma_core", "jacobi", "blas_triad", "blas_bicg_1", "blas_bicg_2", "blas_calc_ax", "blas_calc_rk",
+            "psor2sma_core_maf", "calc_ax_maf", "calc_rk_maf", "bc_k", "imask_k"} <= set(mapped)
+    assert all(v.startswith("serial") for k, v in report.items() if k.startswith("pcr"))     # private(dummy arrays)
+    prev = gomp.omp_get_max_threads()
+    try:
+        for threads in (4, 1):
+            gomp.omp_set_num_threads(threads)
+            racy = () if threads == 1 else ("psor", "psor_maf", "err_t", "jacobi", "jacobi_maf")
+            for name in mapped:
+                if name in racy or name in H.SKIP:
+                    continue
+                for sz in ([12, 7, 23], [20, 33, 64]):
+                    a = MG.run_routine(ser, SIGS[name], real, sz)
+                    b = MG.run_routine(omp, SIGS[name], real, sz)
+                    for nm in H.compared(SIGS[name]):
+                        if nm in ("res", "r") and threads > 1:
+                            assert b[nm][0] == pytest.approx(a[nm][0], rel=3e-6 if real == "f32" else 1e-13), (name, nm)
+                        else:
+                            assert np.array_equal(a[nm].view(np.uint8), b[nm].view(np.uint8)), (name, sz, nm, threads)
+    finally:
+        gomp.omp_set_num_threads(prev)
