@@ -250,3 +250,146 @@ def test_openmp_translation_gives_the_serial_fields(real):
                             assert np.array_equal(a[nm].view(np.uint8), b[nm].view(np.uint8)), (name, sz, nm, threads)
     finally:
         gomp.omp_set_num_threads(prev)
+
+
+def test_translator_implements_fortran_semantics_on_a_known_answer_program(tmp_path):
+    """The translator on a small Fortran program whose answers follow from the Fortran standard alone (nothing of CubeZ):
+    operator precedence and associativity, integer division, integer power, mixed-type promotion, REAL vs double
+    literals, intrinsics by type, array lower bounds and column-major order, do-loop trip counts (bounds evaluated once,
+    zero-trip, negative stride, value after the loop), cycle / exit, one-line if, else if, allocate with bounds,
+    preprocessor branches, continuation lines and `;`."""
+    sys.path.insert(0, os.path.join(ou.ROOT, "oracle"))
+    import f90_to_c
+    src = tmp_path / "known.f90"
+    src.write_text("""
+subroutine known (n, iv, rv, dv, a, b)
+implicit none
+integer                       :: n, i, j, k, m, cnt
+integer, dimension(20)        :: iv
+real, dimension(20)           :: rv
+double precision, dimension(20) :: dv
+real, dimension(-1:n, 0:2)    :: a
+real, dimension(:), allocatable :: w
+real                          :: x, y
+double precision              :: b
+
+iv(1) = 7/2*2            ! (7/2)*2 = 6
+iv(2) = -2**2            ! -(2**2) = -4
+iv(3) = 2**3**2          ! 2**(3**2) = 512
+iv(4) = mod(-7, 2)       ! sign of the dividend: -1
+iv(5) = 2 + 3 * 4 - 10 / 4   ! 2 + 12 - 2 = 12
+iv(6) = max(3, 9, 5) - min(4, 2, 8)
+iv(7) = abs(-5) + 2**(n-8)   ! n = 10: 5 + 4
+iv(8) = 17 - 5 - 3       ! left to right: 9
+
+rv(1) = 7/2*2.0          ! integer division first: 6.0
+rv(2) = real(7)/2        ! 3.5
+rv(3) = 1.0/3.0          ! REAL division
+rv(4) = -1.5*2.0*3.0     ! -((1.5*2.0)*3.0)
+rv(5) = 0.1              ! REAL literal: float(0.1)
+rv(6) = sqrt(2.0) * &
+        sqrt(2.0)        ! REAL sqrt, REAL product
+rv(7) = abs(-2.5) + max(1.5, 0.5)
+rv(8) = 16777216.0 + 1.0 ! REAL: 2^24 + 1 rounds to 2^24
+x = 3.0 ; y = 4.0
+rv(9) = x - y - 1.0      ! (3-4)-1 = -2
+
+dv(1) = 1.0/3.0          ! REAL quotient converted on assignment
+dv(2) = 1.0d0/3.0d0      ! double
+dv(3) = dble(1.0)/3.0    ! REAL 3.0 promoted: double quotient
+dv(4) = 0.1d0
+dv(5) = 16777216.0 + 1.0d0   ! promoted to double: exact
+dv(6) = real(0.1d0, kind=8) + real(n)  ! stays double; real(n) REAL
+b = b + 18.0d0*0.5d0 * dble(n)
+
+! column-major with declared lower bounds: a(i,j) at (i+1) + (n+2)*j
+do j = 0, 2
+do i = -1, n
+a(i, j) = real(100*j + i)
+end do
+end do
+
+! trip count fixed at entry; value of the variable after the loop
+m = 3
+cnt = 0
+do i = 1, m
+m = 10
+cnt = cnt + 1
+end do
+iv(9) = cnt              ! 3
+iv(10) = i               ! 4
+cnt = 0
+do i = 5, 1              ! zero trip
+cnt = cnt + 1
+end do
+iv(11) = cnt + 10*i      ! 0 + 50
+cnt = 0
+do i = 10, 1, -3         ! 10 7 4 1
+cnt = cnt + i
+end do
+iv(12) = cnt             ! 22
+iv(13) = i               ! -2
+cnt = 0
+do i = 1, 10
+if (mod(i, 2) == 0) cycle
+if (i > 7) exit
+cnt = cnt + i            ! 1 + 3 + 5 + 7
+end do
+iv(14) = cnt
+
+if (n < 5) then
+iv(15) = 1
+else if (n .ge. 10 .and. .not. (n == 11)) then
+iv(15) = 2
+else
+iv(15) = 3
+endif
+
+k = 4
+allocate(w(-k:k))
+do i = -k, k
+w(i) = real(i*i)
+end do
+rv(10) = w(-4) + w(0) + w(3)   ! 16 + 0 + 9
+deallocate(w)
+
+#ifdef _NOT_DEFINED
+iv(16) = 111
+#else
+iv(16) = 222
+#endif
+#ifndef _NOT_DEFINED
+iv(17) = 333
+#endif
+return
+end subroutine known
+""")
+    text, names = f90_to_c.translate_file(str(src), "f32")
+    assert names == ["known"]
+    (tmp_path / "known.c").write_text(text)
+    so = tmp_path / "known.so"
+    subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fno-builtin", "-fPIC", "-shared", "-w", "-o", str(so),
+                           str(tmp_path / "known.c"), "-lm"])
+    lib = C.CDLL(str(so))
+    n = np.array([10], dtype=np.int32)
+    iv = np.zeros(20, dtype=np.int32); rv = np.zeros(20, dtype=np.float32); dv = np.zeros(20, dtype=np.float64)
+    a = np.zeros((3, 12), dtype=np.float32)          # Fortran a(-1:10, 0:2), first index contiguous
+    b = np.array([1.0], dtype=np.float64)
+    lib.known_(*[C.c_void_p(v.ctypes.data) for v in (n, iv, rv, dv, a, b)])
+    f = np.float32
+    assert list(iv[:17]) == [6, -4, 512, -1, 12, 7, 9, 9, 3, 4, 50, 22, -2, 16, 2, 222, 333]
+    want = [f(6.0), f(3.5), f(1.0) / f(3.0), f(-9.0), f(0.1), np.sqrt(f(2.0)) * np.sqrt(f(2.0)), f(4.0), f(16777216.0), f(-2.0), f(25.0)]
+    assert [x.tobytes() for x in rv[:10]] == [np.float32(x).tobytes() for x in want]
+    assert dv[0] == float(f(1.0) / f(3.0)) and dv[1] == 1.0 / 3.0 and dv[2] == 1.0 / 3.0 and dv[3] == 0.1
+    assert dv[4] == 16777217.0 and dv[5] == 0.1 + 10.0
+    assert b[0] == 1.0 + 9.0 * 10.0
+    assert np.array_equal(a, np.array([[100 * j + i for i in range(-1, 11)] for j in range(3)], dtype=np.float32))
+    # double-precision build (-fdefault-real-8 -fdefault-double-8): REAL literals and variables become double
+    text64, _ = f90_to_c.translate_file(str(src), "f64")
+    (tmp_path / "known64.c").write_text(text64)
+    subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-fno-builtin", "-fPIC", "-shared", "-w", "-o", str(tmp_path / "known64.so"),
+                           str(tmp_path / "known64.c"), "-lm"])
+    lib64 = C.CDLL(str(tmp_path / "known64.so"))
+    rv64 = np.zeros(20); a64 = np.zeros((3, 12)); iv[:] = 0
+    lib64.known_(*[C.c_void_p(v.ctypes.data) for v in (n, iv, rv64, dv, a64, b)])
+    assert rv64[2] == 1.0 / 3.0 and rv64[4] == 0.1 and rv64[7] == 16777217.0 and dv[0] == 1.0 / 3.0
