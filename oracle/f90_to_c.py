@@ -514,7 +514,9 @@ static inline float f2c_max_f(float a, float b) { return a > b ? a : b; }
 static inline float f2c_min_f(float a, float b) { return a < b ? a : b; }
 static inline double f2c_max_d(double a, double b) { return a > b ? a : b; }
 static inline double f2c_min_d(double a, double b) { return a < b ? a : b; }
-static void* f2c_alloc(long n, size_t sz) { void* p = calloc((size_t)(n > 0 ? n : 1), sz); if (!p) { fprintf(stderr, "f2c: out of memory\n"); abort(); } return p; }
+/* automatic / allocated / per-thread arrays: zero-filled, with slack behind the declared extent -- the reference's padded
+ * line routines index up to 3*2^(pn-2) elements past it on line lengths other than 2^m - 2 (F2C_BOUNDS reports them) */
+static void* f2c_alloc(long n, size_t sz) { void* p = calloc((size_t)(n > 0 ? n : 1) + 4096, sz); if (!p) { fprintf(stderr, "f2c: out of memory\n"); abort(); } return p; }
 """
 
 DECL_RE = re.compile(r"^(integer|real|double\s+precision|character\s*\*\s*\d+|logical)\b(.*)$")
@@ -644,11 +646,16 @@ class OmpUnsupported(Exception):
     pass
 
 
-def omp_clauses(text, u, where, extra_private=()):
-    """Fortran OpenMP clause list -> C clause list.  Only local scalars may be privatised / reduced (dummy arguments
-    are pointers in C, whole arrays would need copies): anything else raises OmpUnsupported and the caller translates
-    the subroutine without its directives."""
-    out, listed = [], set()
+def omp_clauses(text, u, em, where, extra_private=()):
+    """Fortran OpenMP clause list -> dict(loop=[C clauses of the worksharing loop], data=[C data-sharing clauses],
+    pre=[C lines before the construct], open=[C lines at the top of the construct's block, run by every thread],
+    close=[... at its bottom], post=[... after it]).
+    Local scalars map to the C clause of the same name.  What C cannot express directly is restated with the same
+    meaning: a privatised ARRAY (dummy or allocatable: a pointer in C) becomes a per-thread buffer declared inside the
+    block under the same name (copied from the original for firstprivate); a reduction on a dummy-argument scalar
+    (a pointer in C) goes through a local accumulator that is added to the argument after the construct."""
+    cl = {"loop": [], "data": [], "pre": [], "open": [], "close": [], "post": []}
+    listed = set()
     rest = text.strip()
     while rest:
         m = re.match(r"^(schedule|collapse|reduction|private|firstprivate)\s*\(([^)]*)\)\s*", rest)
@@ -659,29 +666,48 @@ def omp_clauses(text, u, where, extra_private=()):
         if kw == "schedule":
             if arg != "static":
                 raise OmpUnsupported("%s: schedule(%s)" % (where, arg))
-            out.append("schedule(static)")
-        elif kw == "collapse":
-            out.append("collapse(%d)" % int(arg))
-        else:
-            op = ""
-            if kw == "reduction":
-                op, arg = [x.strip() for x in arg.split(":", 1)]
-                if op != "+":
-                    raise OmpUnsupported("%s: reduction(%s)" % (where, op))
-                op = "+:"
-            names = [x.strip() for x in arg.split(",") if x.strip()]
-            for nm in names:
-                sy = u.syms.get(nm)
-                if sy is None or sy.is_arg or sy.dims is not None or sy.param is not None:
-                    raise OmpUnsupported("%s: %s(%s) is not a local scalar" % (where, kw, nm))
-                listed.add(nm)
-            out.append("%s(%s%s)" % (kw, op, ", ".join("v_" + nm for nm in names)))
+            cl["loop"].append("schedule(static)")
+            continue
+        if kw == "collapse":
+            cl["loop"].append("collapse(%d)" % int(arg))
+            continue
+        if kw == "reduction":
+            op, arg = [x.strip() for x in arg.split(":", 1)]
+            if op != "+":
+                raise OmpUnsupported("%s: reduction(%s)" % (where, op))
+        scal = []
+        for nm in [x.strip() for x in arg.split(",") if x.strip()]:
+            sy = u.syms.get(nm)
+            if sy is None or sy.param is not None or sy.char:
+                raise OmpUnsupported("%s: %s(%s)" % (where, kw, nm))
+            listed.add(nm)
+            ct = em.ctype(sy.type)
+            if sy.dims is None and not sy.is_arg:
+                scal.append("v_" + nm)
+            elif sy.dims is None and kw == "reduction":
+                cl["pre"].append("%s f2c_red_%s = 0;" % (ct, nm))
+                cl["data"].append("reduction(+:f2c_red_%s)" % nm)
+                cl["open"].append("%s* v_%s = &f2c_red_%s;   /* reduction(+:%s) on a dummy argument */" % (ct, nm, nm, nm))
+                cl["post"].append("(*v_%s) += f2c_red_%s;" % (nm, nm))
+            elif sy.dims is not None and kw in ("private", "firstprivate"):
+                total = " * ".join("%s_n%d" % (nm, d) for d in range(1, len(sy.dims) + 1))
+                if kw == "firstprivate":
+                    cl["pre"].append("%s* const f2c_orig_%s = v_%s;" % (ct, nm, nm))
+                cl["open"].append("%s* v_%s = (%s*)f2c_alloc(%s, sizeof(%s));   /* %s(%s): per-thread copy */"
+                                  % (ct, nm, ct, total, ct, kw, nm))
+                if kw == "firstprivate":
+                    cl["open"].append("memcpy(v_%s, f2c_orig_%s, (size_t)(%s) * sizeof(%s));" % (nm, nm, total, ct))
+                cl["close"].append("free(v_%s);" % nm)
+            else:
+                raise OmpUnsupported("%s: %s(%s)" % (where, kw, nm))
+        if scal:
+            cl["data"].append("%s(%s%s)" % (kw, "+:" if kw == "reduction" else "", ", ".join(scal)))
     more = [nm for nm in extra_private if nm not in listed]
     if more:
         # Fortran: the iteration variable of a sequential loop inside a parallel construct is private (OpenMP 2.9.1.1);
         # in C it is shared unless listed
-        out.append("private(%s)" % ", ".join("v_" + nm for nm in more))
-    return " ".join(out)
+        cl["data"].append("private(%s)" % ", ".join("v_" + nm for nm in more))
+    return cl
 
 
 def translate_unit(u, em, openmp=False):
@@ -847,41 +873,75 @@ def translate_unit(u, em, openmp=False):
                 names.append(mm.group(1))
         raise OmpUnsupported("%s: no `!$omp %s`" % (u.loc, end_marker))
 
-    omp_for = None      # pending (pragma text, collapse count) for the next do statement(s)
+    omp_for = None      # pending (pragma text, where) for the next do statement(s)
+    omp_open = []       # constructs whose block is open: dict(kind, close, post)
+
+    def open_block(cl, where, pragma):
+        """pre lines; [pragma]; `{`; per-thread open lines"""
+        nonlocal ind
+        pad0 = "  " * ind
+        C.append("%s/* %s */ {" % (pad0, where))
+        for ln in cl["pre"]:
+            C.append("%s  %s" % (pad0, ln))
+        if pragma:
+            C.append(pragma)
+        C.append("%s  {" % pad0)
+        for ln in cl["open"]:
+            C.append("%s    %s" % (pad0, ln))
+        ind += 2
+
+    def close_block(entry, where):
+        nonlocal ind
+        ind -= 2
+        pad0 = "  " * ind
+        for ln in entry["close"]:
+            C.append("%s    %s" % (pad0, ln))
+        C.append("%s  }   /* %s */" % (pad0, where))
+        for ln in entry["post"]:
+            C.append("%s  %s" % (pad0, ln))
+        C.append("%s}" % pad0)
+
     for pos, (f, n, s) in enumerate(exe):
         where = "%s:%d" % (os.path.basename(f), n)
         pad = "  " * ind
         if s.startswith("!$omp "):
             d = s[6:].strip()
-            if d.startswith("end parallel do") or d.startswith("end do"):
-                continue
-            if d.startswith("end parallel"):
-                if not blocks or blocks.pop() != "omp":
-                    raise OmpUnsupported("%s: end parallel" % where)
-                ind -= 1
-                C.append("%s}   /* %s: end parallel */" % ("  " * ind, where))
+            if d.startswith("end "):
+                kind = "parallel do" if d.startswith("end parallel do") else ("parallel" if d.startswith("end parallel") else "do")
+                if not d.startswith("end " + kind) or not omp_open or omp_open[-1]["kind"] != kind or blocks[-1:] != ["omp"]:
+                    raise OmpUnsupported("%s: unmatched `%s`" % (where, d))
+                blocks.pop()
+                close_block(omp_open.pop(), where + ": " + d)
                 continue
             if omp_for is not None:
                 raise OmpUnsupported("%s: directive between `do` directive and loop" % where)
             if d.startswith("parallel do"):
-                cl = omp_clauses(d[len("parallel do"):], u, where, region_do_vars(pos + 1, "end parallel do"))
-                omp_for = ("#pragma omp parallel for " + cl, where)
+                cl = omp_clauses(d[len("parallel do"):], u, em, where, region_do_vars(pos + 1, "end parallel do"))
+                open_block(cl, where, "#pragma omp parallel " + " ".join(cl["data"]))
+                omp_for = ("#pragma omp for " + " ".join(cl["loop"]), where)
+                kind = "parallel do"
             elif d.startswith("parallel"):
-                cl = omp_clauses(d[len("parallel"):], u, where, region_do_vars(pos + 1, "end parallel"))
-                C.append("%s/* %s */" % (pad, where))
-                C.append("#pragma omp parallel " + cl)
-                C.append("%s{" % pad)
-                blocks.append("omp")
-                ind += 1
+                cl = omp_clauses(d[len("parallel"):], u, em, where, region_do_vars(pos + 1, "end parallel"))
+                if cl["loop"]:
+                    raise OmpUnsupported("%s: loop clause on `parallel`" % where)
+                open_block(cl, where, "#pragma omp parallel " + " ".join(cl["data"]))
+                kind = "parallel"
             elif d.startswith("do"):
                 nowait = ""
                 for (_, _, t) in exe[pos + 1:]:
                     if t.startswith("!$omp end do"):
                         nowait = " nowait" if "nowait" in t else ""
                         break
-                omp_for = ("#pragma omp for " + omp_clauses(d[2:], u, where) + nowait, where)
+                cl = omp_clauses(d[2:], u, em, where)
+                if cl["post"] or cl["pre"] and not cl["open"]:
+                    raise OmpUnsupported("%s: reduction on a dummy argument at a `do` directive" % where)
+                open_block(cl, where, None)       # a plain block every thread of the team runs: per-thread copies
+                omp_for = ("#pragma omp for " + " ".join(cl["loop"] + cl["data"]) + nowait, where)
+                kind = "do"
             else:
                 raise OmpUnsupported("%s: directive %r" % (where, d))
+            omp_open.append({"kind": kind, "close": cl["close"], "post": cl["post"]})
+            blocks.append("omp")
             continue
         if DECL_RE.match(s) or s.startswith("parameter"):
             raise SyntaxError("%s: declaration after the first executable statement" % where)

@@ -221,31 +221,34 @@ OMP_SO = {r: os.path.join(ou.ROOT, "oracle", "_ref", "libczf90c_omp_%s.so" % r) 
 def test_openmp_translation_gives_the_serial_fields(real):
     """`f90_to_c.py --openmp` maps the reference's `!$OMP` directives to C pragmas (the CPU arm bench.py times).  With 4
     threads every array of the race-free routines equals the serial translation bit for bit; sums differ by the
-    reduction order only.  Not compared: `psor`, `psor_maf` (in-place Gauss-Seidel inside a parallel loop), `err_t`
-    (unsynchronised max) and `jacobi`, `jacobi_maf`: their `END DO NOWAIT` lets a thread start the copy-back
-    `p = wk2` while its neighbours still read `p` (cz_solver.f90:355-372) -- races of the reference itself, which is
-    why the oracle states the 1-thread order."""
+    reduction order only.  Not compared at 4 threads, because the REFERENCE races there: `psor`, `psor_maf`, `pcr`,
+    `pcr_eda`, `pcr_esa` and their `_maf` twins (in-place Gauss-Seidel between cells / lines inside a parallel loop),
+    `err_t` (unsynchronised max), and `jacobi`, `jacobi_maf`, whose `END DO NOWAIT` lets a thread start the copy-back
+    `p = wk2` while its neighbours still read `p` (cz_solver.f90:355-372) -- which is why the oracle states the
+    1-thread order.  With 1 thread everything equals the serial translation."""
     gomp = C.CDLL("libgomp.so.1")
     ser, omp = H.load_f90c(real), C.CDLL(OMP_SO[real])
     report = dict(l.strip().split(": ", 1) for l in open(os.path.join(ou.ROOT, "oracle", "_ref", "f90c_omp", real, "openmp_report.txt")))
     mapped = [k for k, v in report.items() if v == "openmp"]
-    assert {"psor2sma_core", "jacobi", "blas_triad", "blas_bicg_1", "blas_bicg_2", "blas_calc_ax", "blas_calc_rk",
-            "psor2sma_core_maf", "calc_ax_maf", "calc_rk_maf", "bc_k", "imask_k"} <= set(mapped)
-    assert all(v.startswith("serial") for k, v in report.items() if k.startswith("pcr"))     # private(dummy arrays)
+    # every subroutine that has directives is mapped (tdma_mp's are malformed: no END PARALLEL DO; not on the path)
+    assert sorted(k for k, v in report.items() if v != "openmp") == ["fileout_t", "tdma_0", "tdma_1", "tdma_mp", "tdma_p"]
+    racy_mt = ("psor", "psor_maf", "err_t", "jacobi", "jacobi_maf", "pcr", "pcr_eda", "pcr_esa", "pcr_maf", "pcr_eda_maf", "pcr_esa_maf")
     prev = gomp.omp_get_max_threads()
     try:
         for threads in (4, 1):
             gomp.omp_set_num_threads(threads)
-            racy = () if threads == 1 else ("psor", "psor_maf", "err_t", "jacobi", "jacobi_maf")
+            racy = () if threads == 1 else racy_mt
             for name in mapped:
                 if name in racy or name in H.SKIP:
                     continue
                 for sz in ([12, 7, 23], [20, 33, 64]):
+                    if not MG.in_reference_domain(name, sz):
+                        continue
                     a = MG.run_routine(ser, SIGS[name], real, sz)
                     b = MG.run_routine(omp, SIGS[name], real, sz)
                     for nm in H.compared(SIGS[name]):
-                        if nm in ("res", "r") and threads > 1:
-                            assert b[nm][0] == pytest.approx(a[nm][0], rel=3e-6 if real == "f32" else 1e-13), (name, nm)
+                        if nm in ("res", "r"):      # (a reduction starts from 0 and is added to the incoming value at the end)
+                            assert b[nm][0] == pytest.approx(a[nm][0], rel=5e-5 if real == "f32" else 1e-12), (name, nm)   # REAL accumulators, other order
                         else:
                             assert np.array_equal(a[nm].view(np.uint8), b[nm].view(np.uint8)), (name, sz, nm, threads)
     finally:
