@@ -168,9 +168,11 @@ def golden_key(real, n, solver, omg, pre):
     return "%s %d %s %s %s" % (real, n, solver, ("%g" % omg), pre)
 
 
-def load_golden_configs():
+def load_golden_configs(which=None):
+    """which = "f90c": the same configurations run by the reference PROGRAM (its unmodified driver over its own Fortran +
+    OpenMP, translated to C; tests/golden/make_f90c_baseline.py) instead of the driver over the oracle port."""
     try:
-        return json.load(open(GOLDEN_CONFIGS))
+        return json.load(open(GOLDEN_CONFIGS if which is None else GOLDEN_CONFIGS.replace(".json", "_%s.json" % which)))
     except Exception:
         return {}
 
@@ -229,6 +231,17 @@ def cpu_worker(mode, steps, warmup):
         lr = ou.load(real)
         lr.oracle_set_threads(cores)
         o = ou.OracleCZ([nn] * 3, real)
+        ref_so = os.path.join(ROOT, "oracle", "_ref", "libczf90c_omp_%s.so" % real)
+        kind_cpu, nthr = "port", threads
+        if os.path.exists(ref_so) and os.environ.get("CZB_BENCH_CPU", "") != "port":
+            # the reference's own kernels (Fortran + OpenMP directives translated to C); its Jacobi races with more than
+            # one thread (END DO NOWAIT before the copy-back, cz_solver.f90:355-372): one thread there
+            import cubez_b200.ffi as ffi
+            o.dll = ffi.bind_reference_symbols(C.CDLL(ref_so))
+            kind_cpu = "reference"
+            if solver == "jacobi" or pre == "jacobi":
+                lr.oracle_set_threads(1)
+                nthr = 1
         X, B = o.setup_laplace()
         full = nn <= 256
         window = itmax if full else (3 if solver == "pbicgstab" else 6)
@@ -240,7 +253,7 @@ def cpu_worker(mode, steps, warmup):
             itr, res, hist = o.stationary(solver, X, B, window, omg)
             done = len(hist)
         dt = time.perf_counter() - t0
-        e = {"threads": threads, "iterations_timed": int(done), "seconds_timed": dt}
+        e = {"threads": nthr, "code": kind_cpu, "iterations_timed": int(done), "seconds_timed": dt}
         if full:
             e.update({"kind": "measured to convergence", "iterations": int(itr), "seconds": dt, "residual": float(res)})
         elif g:
@@ -521,12 +534,19 @@ def run_gpu(args, rank, world, local_rank):
                 cpu = None
             if ttc:
                 gold = load_golden_configs()
+                gold_ref = load_golden_configs("f90c")
                 for label, nn, solver, itmax, omg, pre, real in TTC_CASES + TTC_BIG:
                     if label in ttc:
                         g = gold.get(golden_key(real, nn, solver, omg, pre))
                         if g:
                             ttc[label]["oracle_iterations"] = int(g["itr"])
                             ttc[label]["oracle_residual"] = float(g["res"])
+                        g = gold_ref.get(golden_key(real, nn, solver, omg, pre))
+                        if g:       # the reference program's own run (committed; made in the build container)
+                            ttc[label]["reference_iterations"] = int(g["itr"])
+                            ttc[label]["reference_residual"] = float(g["res"])
+                            ttc[label]["reference_seconds_build_container"] = {"seconds": g["wall_seconds_this_container"],
+                                                                               "threads": g["threads"]}
                         if cpu and label in cpu:
                             ttc[label]["cpu"] = cpu[label]
                 if "also_f64" in ttc:
