@@ -40,7 +40,7 @@ import sys
 # 1. source -> logical statements
 # ----------------------------------------------------------------------------------------------
 
-def preprocess(path, defines, seen=None):
+def preprocess(path, defines):
     """cpp-like pass: #ifdef/#ifndef/#if NAME==V/#else/#endif with `defines`; returns [(file, line, text)]."""
     out = []
     stack = []          # (parent_active, this_branch_taken)
@@ -785,9 +785,6 @@ def translate_unit(u, em, openmp=False):
     blocks = []        # "do" | "if" | "omp" | "do_omp_outer" | "do_omp_inner"
     omp_skip = [0]
     tmp = [0]
-
-    def P(where):
-        return lambda text: Parser(tokenize(text, where), u.syms, where)
 
     def expr(text, where, want=None):
         p = Parser(tokenize(text, where), u.syms, where)

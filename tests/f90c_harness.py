@@ -5,7 +5,6 @@ argument after the call.  Argument lists, types and array ranks come from the DE
 (f90_to_c.signatures) or from the committed copy of them (tests/golden/f90c_signatures.json), never from a table
 written by hand."""
 import ctypes as C
-import hashlib
 import json
 import os
 
@@ -135,16 +134,6 @@ def compared(sig):
     return [a["name"] for a in sig["args"]
             if not (a["type"] == "real" and a["dims"] and len(a["dims"]) == 1 and a["name"] in SCRATCH_1D
                     and not sig["name"].startswith("tdma"))]
-
-
-def digest(vals, names):
-    h = hashlib.sha256()
-    for nm in names:
-        if nm == "flop":
-            continue
-        h.update(nm.encode())
-        h.update(np.ascontiguousarray(vals[nm]).tobytes())
-    return h.hexdigest()
 
 
 def check_library_against_fortran_vectors(lib, real, sizes, digests, sigs, run_routine, record):
