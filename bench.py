@@ -226,7 +226,8 @@ def cpu_worker(mode, steps, warmup):
     # iteration count (the full CPU runs take minutes: see wall_seconds in tests/golden/baseline_configs.json).
     gold = load_golden_configs()
     out = {}
-    for label, nn, solver, itmax, omg, pre, real in TTC_CASES:
+    # one-thread cases (the reference's racy OpenMP Jacobi) last: the team size is only ever lowered
+    for label, nn, solver, itmax, omg, pre, real in sorted(TTC_CASES, key=lambda c: c[2] == "jacobi" or c[5] == "jacobi"):
         g = gold.get(golden_key(real, nn, solver, omg, pre))
         lr = ou.load(real)
         lr.oracle_set_threads(cores)
