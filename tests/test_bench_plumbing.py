@@ -55,8 +55,12 @@ def test_cpu_arm_runs_with_an_explicit_openmp_team(monkeypatch):
 
 def test_golden_keys_of_the_ttc_cases_exist():
     gold = bench.load_golden_configs()
+    ref = bench.load_golden_configs("f90c")      # the reference program's own runs of the same configurations
     for label, n, solver, itmax, omg, pre, real in bench.TTC_CASES:
-        assert bench.golden_key(real, n, solver, omg, pre) in gold, label
+        k = bench.golden_key(real, n, solver, omg, pre)
+        assert k in gold, label
+        assert k in ref and int(ref[k]["itr"]) > 0 and float(ref[k]["res"]) < 1.0e-5, label
+        assert {"wall_seconds_this_container", "threads"} <= set(ref[k])
 
 
 def test_start_field_is_decomposition_independent():
