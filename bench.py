@@ -534,22 +534,7 @@ def run_gpu(args, rank, world, local_rank):
                 ttc = ttc_cases(make_cz, barrier, max_over_ranks, TTC_CASES[1:] + TTC_BIG, torch)
                 cpu = None
             if ttc:
-                gold = load_golden_configs()
-                gold_ref = load_golden_configs("f90c")
-                for label, nn, solver, itmax, omg, pre, real in TTC_CASES + TTC_BIG:
-                    if label in ttc:
-                        g = gold.get(golden_key(real, nn, solver, omg, pre))
-                        if g:
-                            ttc[label]["oracle_iterations"] = int(g["itr"])
-                            ttc[label]["oracle_residual"] = float(g["res"])
-                        g = gold_ref.get(golden_key(real, nn, solver, omg, pre))
-                        if g:       # the reference program's own run (committed; made in the build container)
-                            ttc[label]["reference_iterations"] = int(g["itr"])
-                            ttc[label]["reference_residual"] = float(g["res"])
-                            ttc[label]["reference_seconds_build_container"] = {"seconds": g["wall_seconds_this_container"],
-                                                                               "threads": g["threads"]}
-                        if cpu and label in cpu:
-                            ttc[label]["cpu"] = cpu[label]
+                attach_golden(ttc, cpu)
                 if "also_f64" in ttc:
                     line["also_f64"] = ttc.pop("also_f64")
                 if "e2e_to_convergence" in ttc:
@@ -561,6 +546,28 @@ def run_gpu(args, rank, world, local_rank):
     emit()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def attach_golden(ttc, cpu):
+    """Beside every time-to-convergence entry: the oracle's iteration count, the reference program's own (both committed
+    goldens) and the CPU child's record for the same configuration."""
+    gold = load_golden_configs()
+    gold_ref = load_golden_configs("f90c")
+    for label, nn, solver, itmax, omg, pre, real in TTC_CASES + TTC_BIG:
+        if label not in ttc:
+            continue
+        g = gold.get(golden_key(real, nn, solver, omg, pre))
+        if g:
+            ttc[label]["oracle_iterations"] = int(g["itr"])
+            ttc[label]["oracle_residual"] = float(g["res"])
+        g = gold_ref.get(golden_key(real, nn, solver, omg, pre))
+        if g:       # the reference program's own run (made in the build container)
+            ttc[label]["reference_iterations"] = int(g["itr"])
+            ttc[label]["reference_residual"] = float(g["res"])
+            ttc[label]["reference_seconds_build_container"] = {"seconds": g["wall_seconds_this_container"], "threads": g["threads"]}
+        if cpu and label in cpu:
+            ttc[label]["cpu"] = cpu[label]
+    return ttc
 
 
 def ttc_cases(make_cz, barrier, max_over_ranks, cases, torch):

@@ -1,5 +1,6 @@
 """CPU checks of bench.py's host-side plumbing (no GPU work): the optional time-to-convergence child process can only
 ever add a key to the headline JSON line, never cost it."""
+import json
 import os
 import subprocess
 import sys
@@ -80,3 +81,17 @@ def test_start_field_is_decomposition_independent():
             assert np.array_equal(f[2:-2, 2:-2, 2:-2], full[j0 + 1:j0 + 1 + d["sz"][1], 2:-2, 2:-2])
             tot += synth.checksum_owned(f, d["idx"])
         assert tot == synth.checksum_owned(full, [2, gsz[0] - 1, 2, gsz[1] - 1, 2, gsz[2] - 1])
+
+
+def test_golden_records_are_attached_to_the_time_to_convergence_entries():
+    labels = [c[0] for c in bench.TTC_CASES + bench.TTC_BIG]
+    ttc = {lab: {"iterations": 1} for lab in labels}
+    ttc["also_f64"] = {"x": 1}
+    cpu = json.load(open(os.path.join(os.path.dirname(os.path.abspath(bench.__file__)), "profiles", "r02_cpu_ttc_reference.json")))
+    out = bench.attach_golden(ttc, cpu)
+    for c in bench.TTC_CASES:
+        e = out[c[0]]
+        assert e["oracle_iterations"] > 0 and e["reference_iterations"] > 0 and e["cpu"]["code"] == "reference", c[0]
+        assert abs(e["oracle_iterations"] - e["reference_iterations"]) <= 2, c[0]
+    assert out["also_f64"] == {"x": 1}
+    json.dumps(out)
