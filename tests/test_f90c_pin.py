@@ -123,7 +123,7 @@ def test_solver_loops_over_the_port_reproduce_the_reference_fortran_histories(re
 # live comparison against the translated Fortran
 # ------------------------------------------------------------------------------------------------------------
 
-LIVE_SIZES = [[12, 7, 23], [9, 10, 34], [6, 5, 66], [5, 6, 18], [7, 5, 31], [5, 5, 50], [4, 4, 258]]
+LIVE_SIZES = [[12, 7, 23], [9, 10, 34], [6, 5, 66], [5, 6, 18], [7, 5, 31], [5, 5, 50], [4, 4, 258], [130, 6, 300], [5, 40, 1024]]
 
 
 @needs_f90c
