@@ -6,7 +6,7 @@ reference's OWN statements -- read from the unmodified files where they lie unde
 /root/reference/src/cz_f90 -- can be executed in an image that has no Fortran front-end
 (gfortran / flang / nvfortran are absent here and on the GPU box).
 
-    python oracle/f90_to_c.py --real f32|f64 --out DIR  FILE.f90 [FILE.f90 ...]
+    python oracle/f90_to_c.py --real f32|f64 [--openmp] --out DIR  FILE.f90 [FILE.f90 ...]
 
 writes one DIR/<name>.c per input file; every Fortran subroutine `foo` becomes `void foo_(...)` with
 gfortran's calling convention (lower case, trailing underscore, every argument by reference), i.e. the
@@ -28,7 +28,15 @@ What "mechanical" means here -- the translator knows Fortran, not CubeZ:
     intrinsics by argument type (`abs`, `max`, `min`, `mod`, `sqrt`, `sin`, `sinh`, `asin`, `dble`, `real`);
   * `--real f64` = gfortran's `-fdefault-real-8 -fdefault-double-8` (CompileOptionSelector.cmake:193).
 Compile the output with `-O2 -ffp-contract=off` (baseline x86-64 gfortran emits no FMA either).
-`-DF2C_BOUNDS` adds an index check on every array reference (reports the Fortran file:line).
+`-DF2C_BOUNDS` adds an index check on every array reference (records the Fortran file:line, then performs the access
+exactly as the unchecked build does).
+`--openmp` keeps the `!$OMP` sentinel lines and maps them to C pragmas with the same meaning (PARALLEL, DO, PARALLEL DO;
+SCHEDULE(static), COLLAPSE, REDUCTION(+), PRIVATE, FIRSTPRIVATE, END DO NOWAIT): the associated loops in OpenMP's
+canonical form, sequential loop variables privatised as Fortran does implicitly, privatised arrays as per-thread
+buffers, reductions on dummy arguments through a local accumulator.  Compile that output with the reference's GNU flags
+(-O3 -fopenmp): it is the CPU arm bench.py times and the kernel library of oracle/_ref/cz_f90c_omp_*, the reference
+program.  A subroutine whose directives the mapping does not cover is translated serially and listed in
+openmp_report.txt.
 Anything outside the subset raises an error naming the file and line; nothing is skipped silently.
 """
 import argparse
