@@ -37,6 +37,13 @@ CASES = [
     ("f64", 256, "sor2sma", 20000, "1.95", None),
     ("f32", 512, "pbicgstab", 400, "0.8", "jacobi"),
     ("f32", 256, "pcr_rb", 8000, "1.9", None),
+    # configs[1]'s relaxation-factor sweep (SURVEY section 8(d) cfg 2: w in {1.0, 1.1, 1.5, 1.8, 1.9, 1.95, 1.97}; 1.95 is above)
+    ("f32", 256, "sor2sma", 100000, "1.0", None),
+    ("f32", 256, "sor2sma", 100000, "1.1", None),
+    ("f32", 256, "sor2sma", 100000, "1.5", None),
+    ("f32", 256, "sor2sma", 100000, "1.8", None),
+    ("f32", 256, "sor2sma", 100000, "1.9", None),
+    ("f32", 256, "sor2sma", 100000, "1.97", None),
 ]
 
 

@@ -429,10 +429,23 @@ def test_reference_program_converges_like_the_oracle_at_the_baseline_configs():
             common = [i for i in r["history_at"] if i in p["history_at"] and int(i) < 18]
             tol = 1e-2      # the very first residual already differs by 6e-4: one REAL dot product over 1.3e8 cells
         else:
-            assert r["itr"] == p["itr"], k
             common = [i for i in r["history_at"] if i in p["history_at"]]
             tol = 2e-3 if r["real"] == "f32" else 1e-9
-            assert r["errmax"] == p["errmax"] and r["errloc"] == p["errloc"], k
+            # Where the residual CREEPS to eps (the relaxation-factor sweep of config 2 at w <= 1.5: it falls by 2e-4 ..
+            # 5e-4 per iteration at the end), the 3e-4 by which the reference's REAL sum over 16.6 M squares sits below
+            # the double-accumulated one is worth one or two iterations: 5735 / 5640 / 4234 against the oracle's 5737 /
+            # 5641 / 4235 at w = 1.0 / 1.1 / 1.5.  Window = that offset / the decay per iteration, rounded up; 0 (the
+            # same iteration) wherever the residual falls by more than 1e-3 per iteration (w >= 1.8: 2214, 1301, 734, 443).
+            tail = sorted(int(i) for i in p["history_at"])[-2:]
+            decay = 1.0 - float(p["history_at"][str(tail[1])]) / float(p["history_at"][str(tail[0])])
+            last = str(max(int(i) for i in common))
+            offset = abs(1.0 - float(r["history_at"][last]) / float(p["history_at"][last]))
+            slack = int(np.ceil(offset / decay)) if decay < 1e-3 else 0
+            assert slack <= 2 and abs(r["itr"] - p["itr"]) <= slack, (k, r["itr"], p["itr"], slack)
+            if r["itr"] == p["itr"]:
+                assert r["errmax"] == p["errmax"] and r["errloc"] == p["errloc"], k
+            else:
+                assert float(r["errmax"]) == pytest.approx(float(p["errmax"]), rel=1e-3), k
         assert len(common) >= 15, k
         for i in common:
             assert float(r["history_at"][i]) == pytest.approx(float(p["history_at"][i]), rel=tol), (k, i)

@@ -136,6 +136,13 @@ def _golden(real, n, solver, coef, pre):
     ("f32", 512, "pbicgstab", 400, "0.8", "jacobi"),
     ("f32", 256, "pcr_rb", 8000, "1.9", None),
     ("f32", 512, "pcr_rb", 8000, "1.9", None),
+    # config 2's relaxation-factor sweep (SURVEY section 8(d) cfg 2); oracle: 5737 / 5641 / 4235 / 2214 / 1301 / 443 iterations
+    ("f32", 256, "sor2sma", 100000, "1.0", None),
+    ("f32", 256, "sor2sma", 100000, "1.1", None),
+    ("f32", 256, "sor2sma", 100000, "1.5", None),
+    ("f32", 256, "sor2sma", 100000, "1.8", None),
+    ("f32", 256, "sor2sma", 100000, "1.9", None),
+    ("f32", 256, "sor2sma", 100000, "1.97", None),
 ])
 def test_baseline_configs_converge_like_the_reference_driver(real, n, solver, itmax, coef, pre):
     import cubez_b200
