@@ -16,6 +16,7 @@
 #include <string>
 #include <strings.h>
 #include <vector>
+#include <signal.h>
 #include <unistd.h>
 #include <sys/wait.h>
 
@@ -65,16 +66,47 @@ static int launch_ranks(int nranks, char* argv[]) {
     close(fd[1]);
     pids[r] = pid; rfd[r] = fd[0];
   }
-  int rc = 0;
+  // Reap the ranks as they end.  A rank that fails (no such device, out of memory, a refused configuration) would leave
+  // its peers waiting in an NCCL rendezvous or exchange for ever -- mpirun's job under the reference; here the launcher
+  // gives them CZB_RANK_GRACE_S seconds (default 10) and then ends them.
+  int rc = 0, live = nranks;
   double emax = -1.0; int eloc[3] = {0, 0, 0};
-  for (int r = 0; r < nranks; ++r) {
-    char buf[256]; size_t n = 0; ssize_t k;
-    while (n + 1 < sizeof(buf) && (k = read(rfd[r], buf + n, sizeof(buf) - 1 - n)) > 0) n += (size_t)k;
-    buf[n] = 0; close(rfd[r]);
-    int st = 0; waitpid(pids[r], &st, 0);
-    if (!WIFEXITED(st) || WEXITSTATUS(st) != 0) rc = -1;
-    double e; int a, b, c;
-    if (sscanf(buf, "%lf %d %d %d", &e, &a, &b, &c) == 4 && e > emax) { emax = e; eloc[0] = a; eloc[1] = b; eloc[2] = c; }
+  std::vector<char> done(nranks, 0);
+  const char* ge = getenv("CZB_RANK_GRACE_S");
+  const double grace = ge ? atof(ge) : 10.0;
+  double waited = -1.0;                       // seconds since the first failure, < 0: none yet
+  bool terminated = false;
+  while (live > 0) {
+    bool progress = false;
+    for (int r = 0; r < nranks; ++r) {
+      if (done[r]) continue;
+      int st = 0;
+      const pid_t w = waitpid(pids[r], &st, WNOHANG);
+      if (w == 0) continue;
+      done[r] = 1; --live; progress = true;
+      char buf[256]; size_t n = 0; ssize_t k;   // the writer is gone: this reads what it left and then end-of-file
+      while (n + 1 < sizeof(buf) && (k = read(rfd[r], buf + n, sizeof(buf) - 1 - n)) > 0) n += (size_t)k;
+      buf[n] = 0; close(rfd[r]);
+      if (w < 0 || !WIFEXITED(st) || WEXITSTATUS(st) != 0) {
+        if (rc == 0 && !terminated) fprintf(stderr, "cz: rank %d ended abnormally (status 0x%x)\n", r, st);
+        rc = -1;
+        if (waited < 0) waited = 0.0;
+      }
+      double e; int a, b, c;
+      if (sscanf(buf, "%lf %d %d %d", &e, &a, &b, &c) == 4 && e > emax) { emax = e; eloc[0] = a; eloc[1] = b; eloc[2] = c; }
+    }
+    if (live == 0) break;
+    if (!progress) {
+      usleep(20000);
+      if (waited >= 0) waited += 0.02;
+    }
+    if (waited >= grace && !terminated) {
+      for (int r = 0; r < nranks; ++r) if (!done[r]) kill(pids[r], SIGTERM);
+      terminated = true; waited = 0.0;
+    } else if (terminated && waited >= 5.0) {
+      for (int r = 0; r < nranks; ++r) if (!done[r]) kill(pids[r], SIGKILL);
+      waited = 0.0;
+    }
   }
   if (rc != 0) { printf("\n\tSolver error.\n\n"); return -1; }
   // global node indices (the reference prints LOCAL indices of the rank that holds the maximum, cz_Evaluate.cpp:556-559)

@@ -121,3 +121,61 @@ def test_line_solvers_refuse_a_division_along_k(tmp_path):
         assert p.returncode == 0, o[-2000:]
         assert "gdv_z = 1" in o
     assert all(int(np.load(os.path.join(work, "out_%d.npz" % r))["itr"]) == 0 for r in range(nranks))
+
+
+# ---- the `cz` driver as its own launcher (cubez_b200/csrc/cz_main.cpp: launch_ranks) ------------------------------------------
+def _cz_env(work):
+    sys.path.insert(0, os.path.join(HERE, "tools", "emu"))
+    import emu_build
+    return emu_build.build_cz(), dict(os.environ, CZB_NCCL_LIB=emu_build.build_nccl(), CZB_NCCL_EMU_DIR=work, CZB_RANK_GRACE_S="1")
+
+
+def test_cz_driver_launches_its_ranks_and_writes_the_serial_history(tmp_path):
+    """`cz ... --gpus 2` and the reference's own `gdv_x gdv_y gdv_z` form (main.cpp:19-29): the parent re-executes itself once
+    per rank; rank 0 writes the history file of the serial run, the parent prints the global Error max."""
+    one, two, three = [os.path.join(str(tmp_path), d) for d in ("one", "two", "three")]
+    res = {}
+    for work, extra in ((one, []), (two, ["--gpus", "2"]), (three, ["1", "2", "1"])):
+        os.makedirs(work)
+        exe, env = _cz_env(work)
+        p = subprocess.run([exe, "32", "32", "32", "sor2sma", "400", "1.5"] + extra, cwd=work, env=env, capture_output=True,
+                           text=True, timeout=600)
+        assert p.returncode == 0, p.stdout + p.stderr
+        res[work] = (open(os.path.join(work, "sor2sma.txt")).read(), p.stdout.split("Error max = ")[1].split()[0],
+                     p.stdout.split("Iter = ")[1].split()[0])
+    h1 = [float(l.split(",")[1]) for l in res[one][0].split("\n")[1:] if l.strip()]
+    for work in (two, three):
+        assert res[work][2] == res[one][2]                       # the same iteration count
+        assert res[work][1] == res[one][1]                       # bit-identical field -> the same Error max digits
+        h = [float(l.split(",")[1]) for l in res[work][0].split("\n")[1:] if l.strip()]
+        np.testing.assert_allclose(h, h1, rtol=2e-6)             # residual sums differ by summation order only
+
+
+def test_cz_launcher_ends_the_job_when_a_rank_dies(tmp_path):
+    """A rank that dies would leave its peer waiting in the next exchange for ever (mpirun's job under the reference):
+    the launcher notices, gives the rest CZB_RANK_GRACE_S seconds, ends them and reports a solver error."""
+    import signal
+    import time
+    work = str(tmp_path)
+    exe, env = _cz_env(work)
+    q = subprocess.Popen([exe, "48", "48", "48", "jacobi", "2000000", "0.8", "--gpus", "2"], cwd=work, env=dict(env, CZ_EPS="0"),
+                         stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    try:
+        kids = []
+        for _ in range(100):                                     # the two ranks are the parent's only children
+            time.sleep(0.1)
+            kids = open("/proc/%d/task/%d/children" % (q.pid, q.pid)).read().split()
+            if len(kids) == 2:
+                break
+        assert len(kids) == 2, kids
+        time.sleep(1.0)
+        os.kill(int(kids[1]), signal.SIGKILL)
+        t0 = time.time()
+        out, err = q.communicate(timeout=120)
+    finally:
+        if q.poll() is None:
+            q.kill()
+    assert q.returncode != 0 and "Solver error" in out and "rank 1 ended abnormally" in err, (q.returncode, out, err)
+    assert time.time() - t0 < 30
+    for k in kids:                                               # both ranks were reaped by the launcher
+        assert not os.path.exists("/proc/%s" % k), k
