@@ -179,3 +179,40 @@ def test_cz_launcher_ends_the_job_when_a_rank_dies(tmp_path):
     assert time.time() - t0 < 30
     for k in kids:                                               # both ranks were reaped by the launcher
         assert not os.path.exists("/proc/%s" % k), k
+
+
+def test_cz_driver_on_ragged_grids_and_random_divisions(tmp_path):
+    """Seeded random non-cubic grids cut into random bricks through the `cz` launcher (2 .. 12 processes): the history
+    file and the iteration count are those of the undivided run.  "Error max" is compared to 1e-5 only: a rank evaluates
+    the analytic solution from ITS origin (`origin + (i - 1) * pitch` in REAL, cz_Evaluate.cpp:136-138), which rounds
+    differently from the global expression -- the reference does the same."""
+    import re
+    rng = np.random.default_rng(5)
+    solvers = ["jacobi", "sor2sma", "pcr_rb", "pcr_j_esa", "jacobi_maf", "sor2sma_maf", "pcr_rb_maf", "pbicgstab", "pbicgstab_maf"]
+
+    def run(work, args):
+        os.makedirs(work)
+        exe, env = _cz_env(work)
+        p = subprocess.run([exe] + args, cwd=work, env=env, capture_output=True, text=True, timeout=600)
+        assert p.returncode == 0, (args, p.stdout[-2000:], p.stderr[-2000:])
+        h = [float(l.split(",")[1]) for l in open(os.path.join(work, args[3] + ".txt")).read().split("\n")[1:] if l.strip()]
+        return int(re.search(r"Iter = (\d+)", p.stdout).group(1)), float(p.stdout.split("Error max = ")[1].split()[0]), h
+
+    for t in range(12):
+        sz = [int(rng.integers(6, 20)) for _ in range(3)]
+        solver = solvers[int(rng.integers(len(solvers)))]
+        gdv = [int(rng.integers(1, 3)), int(rng.integers(1, 4)), 1 if "pcr" in solver else int(rng.integers(1, 3))]
+        if gdv == [1, 1, 1]:
+            gdv = [1, 2, 1]
+        bicg = solver.startswith("pbicgstab")
+        pre = [str(rng.choice(["sor2sma", "jacobi", "none"]))] if bicg else []
+        if bicg and solver.endswith("_maf") and pre[0] != "none":
+            pre = [pre[0] + "_maf"]
+        coef = "0.8" if ("jacobi" in solver or (pre and "jacobi" in pre[0])) else str(rng.choice(["1.0", "1.5", "1.8"]))
+        args = [str(s) for s in sz] + [solver, str(int(rng.integers(3, 15))), coef] + pre
+        a = run(os.path.join(str(tmp_path), "a%d" % t), args)
+        b = run(os.path.join(str(tmp_path), "b%d" % t), args + [str(g) for g in gdv])
+        assert a[0] == b[0], (args, gdv)
+        assert len(a[2]) == len(b[2]), (args, gdv)
+        np.testing.assert_allclose(b[2], a[2], rtol=2e-3 if bicg else 2e-6, err_msg=str((args, gdv)))
+        assert b[1] == pytest.approx(a[1], rel=1e-5 if not bicg else 1e-3), (args, gdv)
