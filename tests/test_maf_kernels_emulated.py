@@ -313,9 +313,10 @@ def test_emulated_kernels_under_address_sanitizer():
     if not os.path.isabs(asan) or not os.path.exists(asan):
         pytest.skip("libasan not available")
     env = dict(os.environ, EMU_SANITIZE="address", LD_PRELOAD=asan, ASAN_OPTIONS="detect_leaks=0")
-    sel = "point_kernels or line_kernel_equals or stretched_mesh or sweeps_and_operator or blas1 or (solve_matches and (pcr_maf or pbicgstab_maf-sor2sma_maf))"
+    sel = "point_kernels or line_kernel_equals or stretched_mesh or sweeps_and_operator or blas1 or (solve_matches and (pcr_maf or pbicgstab_maf-sor2sma_maf)) or tiny"
     p = subprocess.run([sys.executable, "-m", "pytest", os.path.join(HERE, "test_maf_kernels_emulated.py"),
-                        os.path.join(HERE, "test_lib_emulated_plain.py"), "-x", "-q", "-p", "no:cacheprovider", "-k", sel],
+                        os.path.join(HERE, "test_lib_emulated_plain.py"), os.path.join(HERE, "test_emulated_ragged.py"),   # "tiny": grids from 3 nodes per axis
+                        "-x", "-q", "-p", "no:cacheprovider", "-k", sel],
                        env=env, capture_output=True, text=True, timeout=1500)
     assert p.returncode == 0 and " passed" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
     assert "AddressSanitizer" not in p.stderr
