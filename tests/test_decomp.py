@@ -47,6 +47,20 @@ def test_slab_decompose_cpp_matches_python_and_tiles_the_cube(gsz):
 def test_brick_decompose_cpp_matches_python_and_tiles_the_cube(gsz, gdv):
     """3-D bricks (reference: CBrick division, cz_Evaluate.cpp:103-159): C++ == Python mirror, the bricks
     tile the inner nodes exactly once, neighbour tables are mutual, gdv = {1, N, 1} is the j-slab decomposition."""
+    _check_bricks(gsz, gdv)
+
+
+def test_brick_decompose_on_random_grids_and_divisions():
+    """The same properties on 40 seeded random (grid, division) pairs, incl. divisions that leave one inner node per brick."""
+    rng = np.random.default_rng(11)
+    for _ in range(40):
+        gsz = [int(rng.integers(4, 40)) for _ in range(3)]
+        gdv = [int(rng.integers(1, min(5, gsz[a] - 2) + 1)) for a in range(3)]
+        _check_bricks(gsz, gdv)
+    _check_bricks([6, 5, 7], [4, 3, 5])                        # one inner node per brick along every axis
+
+
+def _check_bricks(gsz, gdv):
     d = lib.load("f32")
     sz, head, nid, idx = (C.c_int * 3)(), (C.c_int * 3)(), (C.c_int * 6)(), (C.c_int * 6)()
     R = gdv[0] * gdv[1] * gdv[2]
