@@ -320,3 +320,21 @@ def test_emulated_kernels_under_address_sanitizer():
                        env=env, capture_output=True, text=True, timeout=1500)
     assert p.returncode == 0 and " passed" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
     assert "AddressSanitizer" not in p.stderr
+
+
+def test_emulated_kernels_under_undefined_behaviour_sanitizer():
+    """The ragged / tiny-grid cases and the plain per-call ABI cases on a -fsanitize=undefined build of the emulated
+    library: no signed overflow, misaligned or out-of-range index arithmetic, bad shift or float-to-int conversion in
+    the host code and the plain-CUDA kernels (UBSan reports "runtime error" on stderr and carries on)."""
+    import subprocess
+    if os.environ.get("EMU_SANITIZE"):
+        pytest.skip("already inside the sanitizer run")
+    ubsan = subprocess.run(["gcc", "-print-file-name=libubsan.so"], capture_output=True, text=True).stdout.strip()
+    if not os.path.isabs(ubsan) or not os.path.exists(ubsan):
+        pytest.skip("libubsan not available")
+    env = dict(os.environ, EMU_SANITIZE="undefined", LD_PRELOAD=ubsan)
+    p = subprocess.run([sys.executable, "-m", "pytest", os.path.join(HERE, "test_emulated_ragged.py"),
+                        os.path.join(HERE, "test_lib_emulated_plain.py"), "-x", "-q", "-s", "-p", "no:cacheprovider"],
+                       env=env, capture_output=True, text=True, timeout=1500)
+    assert p.returncode == 0 and " passed" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
+    assert "runtime error" not in p.stdout + p.stderr, (p.stdout + p.stderr)[-3000:]
